@@ -1,0 +1,160 @@
+/*
+ * b200sd.h — C-ABI of the B200 (sm_100a) DDPM denoising hot path.
+ *
+ * The reference (wangze22/StableDiffusion-PyTorch) has no FFI: its boundary is the Python module surface
+ * (SURVEY.md §8b). Each entry point below replaces the library kernels that one reference call site launches
+ * through PyTorch; the reference file:line is cited per function. Host code (models/, scheduler/, cim_layers/)
+ * binds these with ctypes and passes raw device pointers + sizes. No torch types cross
+ * this boundary.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative B200SD_ERR_* code; b200sd_last_error() has the text
+ *   - the caller owns every buffer; the library never allocates or frees device memory and keeps no pointer
+ *     past return (it caches only host-side TMA descriptors keyed by pointer+shape)
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing synchronises, so every
+ *     call is CUDA-graph capturable
+ *   - activations are NHWC ("pixel-major") bf16 unless stated: a (N,H,W,C) tensor is a row-major
+ *     [N*H*W, C] matrix, which is also the (B, L, C) token layout attention uses
+ */
+#ifndef B200SD_H
+#define B200SD_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200SD_OK 0
+#define B200SD_ERR_ARG (-1)         /* bad shape / null pointer / misalignment */
+#define B200SD_ERR_UNSUPPORTED (-2) /* valid request this build has no kernel for (never a CPU fallback) */
+#define B200SD_ERR_CUDA (-3)        /* CUDA runtime / driver error; text in b200sd_last_error() */
+
+#define B200SD_ACT_NONE 0
+#define B200SD_ACT_SILU 1
+#define B200SD_ACT_RELU 2
+
+#define B200SD_DT_BF16 0
+#define B200SD_DT_F32 1
+
+const char* b200sd_last_error(void);
+int b200sd_version(void);
+/* number of kernels this library has launched since load (bench.py's gpu_launches counter) */
+int64_t b200sd_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------ scheduler
+ * LinearNoiseScheduler.add_noise — scheduler/linear_noise_scheduler.py:26-48.
+ * out[b,i] = sqrt_acp[t[b]] * x0[b,i] + sqrt_1m_acp[t[b]] * noise[b,i]; fp32, products and sum individually
+ * rounded (no FMA contraction) so the result is bit-identical to the reference's separate torch ops.
+ * t: int64 on device, shape (batch,), or (1,) when t_len == 1 (broadcast). Tables: fp32 on device, length T. */
+int b200sd_sched_add_noise(const float* x0, const float* noise, const int64_t* t, int64_t t_len,
+                           const float* sqrt_acp, const float* sqrt_1m_acp, int num_timesteps, float* out,
+                           int64_t batch, int64_t per_sample, void* stream);
+
+/* LinearNoiseScheduler.sample_prev_timestep — scheduler/linear_noise_scheduler.py:50-78.
+ * x0 = clamp((xt - sqrt_1m_acp[t]*eps)/sqrt(acp[t]), -1, 1); mean = (xt - betas[t]*eps/sqrt_1m_acp[t])/sqrt(alphas[t]);
+ * x_prev = mean (t == 0) or mean + sqrt((1-acp[t-1])/(1-acp[t])*betas[t]) * z.
+ * t is one timestep shared by the batch: read from t_dev (int64 on device) when non-null, else t_host.
+ * z: injected N(0,1) noise (parity path) or NULL to draw it in-kernel with Philox4x32-10 (seed, offset).
+ * Optional classifier-free guidance fused in (tools/sample_ddpm_text_image_cond.py:84-86):
+ * eps = eps_uncond + cfg_scale*(eps - eps_uncond) when eps_uncond is non-null. */
+int b200sd_sched_prev_step(const float* xt, const float* eps, const float* eps_uncond, float cfg_scale,
+                           const float* z, const int64_t* t_dev, int64_t t_host, const float* betas,
+                           const float* alphas, const float* acp, const float* sqrt_1m_acp, int num_timesteps,
+                           float* x_prev, float* x0, int64_t n, uint64_t seed, uint64_t offset, void* stream);
+
+/* get_time_embedding — models/blocks.py:5-24 (and models/transformer.py:18-40).
+ * out[b, j] = sin(t[b]/f_j), out[b, half+j] = cos(t[b]/f_j), f_j = 10000^(j/half); t int64 (t_len = batch or 1).
+ * out is bf16 or fp32 [batch, dim]. */
+int b200sd_time_embedding(const int64_t* t, int64_t t_len, void* out, int out_dtype, int64_t batch, int dim,
+                          void* stream);
+
+/* ------------------------------------------------------------------------------------ implicit-GEMM core
+ * One tcgen05/TMEM kernel serves nn.Conv2d 3x3/1x1/4x4-s2, nn.ConvTranspose2d 4x4-s2 (as 4 sub-pixel phases)
+ * and nn.Linear (models/blocks.py:45-109,339,457; models/unet_cond_base.py:67-83,122).
+ *
+ *   acc[p, n]  = sum over segments s, channels c:  A_s[pixel p shifted by (dy_s, dx_s), c0_s + c] * Wt[n, k(s, c)]
+ *   v          = acc + bias[n] + rowbias[img(p), n]          (each optional)
+ *   v          = act(v)
+ *   v          = gate[img(p), n] * v  (optional)  + residual[p, n] (optional)
+ *   out[p, n]  = v   (bf16 or fp32)
+ *
+ * A sources are 4-D views (C, W, H, N) of NHWC bf16 tensors given as base pointer + byte strides, read by TMA
+ * with out-of-bounds zero fill (this is the conv padding). The weight is bf16 [n_out, k_total] row-major
+ * (K contiguous) with k running over segments in order, 64-channel chunk by chunk. */
+typedef struct {
+    const void* base;  /* bf16 */
+    int32_t dims[4];   /* C, W, H, N extents */
+    int64_t strides[3]; /* byte strides of W, H, N (C is contiguous) */
+} b200sd_src;
+
+typedef struct {
+    int32_t src;    /* index into srcs[] */
+    int32_t dy, dx; /* tap offset added to the output pixel coordinate */
+    int32_t c0;     /* first channel read from the source */
+    int32_t nchunk; /* number of 64-channel chunks (source channels beyond dims[0] read as zero) */
+} b200sd_seg;
+
+typedef struct {
+    int32_t n_src, n_seg;
+    b200sd_src srcs[4];
+    b200sd_seg segs[20];
+    const void* weight; /* bf16 [n_out, k_total], k_total = 64 * sum(nchunk) */
+    int32_t n_out;
+    /* output pixel grid and its addressing (element strides; out/residual share geometry, not pointers) */
+    int32_t on, oh, ow;
+    void* out;
+    int32_t out_dtype;
+    int64_t out_sn, out_sy, out_sx; /* element strides of image, row, column in `out` */
+    const float* bias;              /* fp32 [n_out] or NULL */
+    const void* rowbias;            /* bf16 [on, rowbias_ld] or NULL (time-embedding add, blocks.py:118) */
+    int64_t rowbias_ld;
+    const void* gate; /* bf16 [on, gate_ld] or NULL (adaLN-Zero gate, transformer_layer.py:90) */
+    int64_t gate_ld;
+    const void* residual; /* bf16, same pixel geometry as out, or NULL */
+    int64_t res_sn, res_sy, res_sx;
+    int32_t act;
+    /* optional per-(image, channel) sum / sum-of-squares of the bf16-rounded output, fp32 [on, n_out, 2],
+       accumulated with atomics: the GroupNorm statistics of the next layer without re-reading the tensor */
+    float* stats;
+} b200sd_igemm_params;
+
+int b200sd_igemm(const b200sd_igemm_params* p, void* stream);
+
+/* ------------------------------------------------------------------------------------------- normalisation
+ * nn.GroupNorm(G, C) (+ SiLU / ReLU) — models/blocks.py:48-49,67-68,126,136; unet_cond_base.py:179-180.
+ * x: NHWC bf16 [n, hw, ld_x] (C contiguous); statistics over (hw, C/G) per image and group, biased variance,
+ * eps inside the sqrt, fp32 arithmetic; y = act((x-mean)*rstd*gamma + beta) written as bf16 [n, hw, ld_y]. */
+int b200sd_groupnorm(const void* x, int64_t ld_x, void* y, int64_t ld_y, const float* gamma, const float* beta,
+                     int64_t n, int64_t hw, int c, int groups, float eps, int act, void* stream);
+
+/* ----------------------------------------------------------------------------------------------- attention
+ * softmax(Q K^T / sqrt(d)) V per (batch, head) — nn.MultiheadAttention call sites models/blocks.py:128,140,242,
+ * 254,480,495; CustomMultiheadAttention models/multihead_attention.py:41-80; DiT Attention models/attention.py:33-78.
+ * q: bf16 rows of length ld_q, head h at columns [h*d, (h+1)*d); likewise k, v with their own ld; row index =
+ * b*L + token. out: bf16 [batch*lq, ld_o]. Scores, softmax and the PV accumulation are fp32. */
+int b200sd_attention(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v,
+                     void* out, int64_t ld_o, int64_t batch, int heads, int lq, int lk, int d, float scale,
+                     void* stream);
+
+/* ------------------------------------------------------------------------------------- layout / glue
+ * NCHW fp32 -> NHWC bf16 channel slice: dst[n, p, c_off + c] = bf16(src[n, c, p]), c < c. */
+int b200sd_nchw_to_nhwc(const float* src, void* dst, int64_t ld_dst, int c_off, int64_t n, int c, int64_t hw,
+                        void* stream);
+/* NHWC (bf16 or fp32) -> NCHW fp32: dst[n, c, p] = src[n, p, c]. */
+int b200sd_nhwc_to_nchw(const void* src, int src_dtype, int64_t ld_src, float* dst, int64_t n, int c, int64_t hw,
+                        void* stream);
+/* Mask conditioning — models/unet_cond_base.py:134-138: nearest-neighbour resize of mask (n, cin, mh, mw) fp32 to
+ * (h, w) (src index = floor(dst * mh / h)), 1x1 conv cin->cout without bias (w: fp32 [cout, cin]), written as bf16
+ * into channels [c_off, c_off+cout) of the NHWC conv_in input. Reads only the h*w sampled pixels. */
+int b200sd_mask_cond(const float* mask, const float* w, void* dst, int64_t ld_dst, int c_off, int64_t n, int cin,
+                     int cout, int mh, int mw, int h, int wd, void* stream);
+/* dst[r, c_off + c] = act(src[r, c]) for a [rows, c] bf16 matrix (SiLU before the time-embedding Linear,
+ * blocks.py:58-61; copy of the skip tensor into the concat buffer, blocks.py:464). */
+int b200sd_copy_act(const void* src, int64_t ld_src, void* dst, int64_t ld_dst, int c_off, int64_t rows, int c,
+                    int act, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

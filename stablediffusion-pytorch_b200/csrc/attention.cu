@@ -1,0 +1,257 @@
+// Fused attention forward: softmax(Q K^T * scale) V per (batch, head), flash-style online softmax,
+// never materialising the L x L score matrix the reference builds (models/attention.py:59-60,
+// models/multihead_attention.py:58-61).
+//
+// Head dims on this path are 8..64 (16 heads over 128..768 channels; VQVAE 4 heads x 64; DiT 9 x 32). At these
+// sizes the kernel is bound by the exp (MUFU) and fp32 softmax arithmetic, not by the MMA rate: QK^T costs 2*d
+// flops per score against one exp per score, so the tensor pipe is <10 % busy whatever instruction feeds it.
+// The MMAs are therefore warp-level mma.sync.m16n8k16 (bf16 in, fp32 accumulate) straight from registers, which
+// keeps P in registers between the two GEMMs; tcgen05 would add a TMEM round trip per tile for no gain here.
+//
+// CTA = 4 warps = 64 queries of one (batch, head); KV streamed in 64-key tiles, double-buffered with cp.async.
+#include "host.h"
+#include <cuda_bf16.h>
+
+namespace b200 {
+
+constexpr int ATT_BQ = 64;
+constexpr int ATT_BKV = 64;
+constexpr int ATT_THREADS = 128;
+
+__device__ __forceinline__ void cp_async16(void* dst, const void* src, int src_bytes) {
+    uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(dst));
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], const void* p) {
+    uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(p));
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(a));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], const void* p) {
+    uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(p));
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(a));
+}
+__device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// DP: head dim padded to a multiple of 16. Smem row pitch DP*2+16 B makes every ldmatrix conflict-free.
+template <int DP>
+__global__ void __launch_bounds__(ATT_THREADS)
+    attention_kernel(const __nv_bfloat16* __restrict__ q, long long ld_q, const __nv_bfloat16* __restrict__ k,
+                     long long ld_k, const __nv_bfloat16* __restrict__ v, long long ld_v,
+                     __nv_bfloat16* __restrict__ out, long long ld_o, int lq, int lk, int d, float scale_log2) {
+    constexpr int PITCH = DP + 8;  // elements
+    extern __shared__ __align__(16) uint8_t att_smem[];
+    __nv_bfloat16* sQ = reinterpret_cast<__nv_bfloat16*>(att_smem);
+    __nv_bfloat16* sK = sQ + ATT_BQ * PITCH;        // 2 stages
+    __nv_bfloat16* sV = sK + 2 * ATT_BKV * PITCH;   // 2 stages
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int q0 = blockIdx.x * ATT_BQ;
+    const int head = blockIdx.y;
+    const long long b = blockIdx.z;
+    const __nv_bfloat16* qg = q + (b * lq) * ld_q + head * d;
+    const __nv_bfloat16* kg = k + (b * lk) * ld_k + head * d;
+    const __nv_bfloat16* vg = v + (b * lk) * ld_v + head * d;
+    const int cpr = d >> 3;  // valid 16-byte chunks per row
+
+    // zero the padding columns [d, PITCH) of every buffer once; cp.async only ever writes [0, d)
+    if (d < PITCH) {
+        const int padw = PITCH - d;
+        for (int i = tid; i < (ATT_BQ + 4 * ATT_BKV) * padw; i += ATT_THREADS) {
+            const int row = i / padw, c = d + i % padw;
+            sQ[row * PITCH + c] = __float2bfloat16(0.f);
+        }
+    }
+    auto load_rows = [&](__nv_bfloat16* dst, const __nv_bfloat16* src, long long ld, int row0, int nrows_valid) {
+        for (int i = tid; i < 64 * cpr; i += ATT_THREADS) {
+            const int r = i / cpr, c = i - r * cpr;
+            const bool ok = (row0 + r) < nrows_valid;
+            const __nv_bfloat16* s = src + (long long)(ok ? row0 + r : 0) * ld + c * 8;
+            cp_async16(dst + r * PITCH + c * 8, s, ok ? 16 : 0);
+        }
+    };
+    load_rows(sQ, qg, ld_q, q0, lq);
+    load_rows(sK, kg, ld_k, 0, lk);
+    load_rows(sV, vg, ld_v, 0, lk);
+    cp_async_commit();
+
+    const int ntiles = (lk + ATT_BKV - 1) / ATT_BKV;
+    float o[DP / 8][4];
+#pragma unroll
+    for (int i = 0; i < DP / 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+    uint32_t qf[DP / 16][4];
+
+    for (int t = 0; t < ntiles; ++t) {
+        const int st = t & 1;
+        if (t + 1 < ntiles) {
+            load_rows(sK + (st ^ 1) * ATT_BKV * PITCH, kg, ld_k, (t + 1) * ATT_BKV, lk);
+            load_rows(sV + (st ^ 1) * ATT_BKV * PITCH, vg, ld_v, (t + 1) * ATT_BKV, lk);
+            cp_async_commit();
+            cp_async_wait<1>();
+        } else {
+            cp_async_wait<0>();
+        }
+        __syncthreads();
+        if (t == 0) {
+#pragma unroll
+            for (int kb = 0; kb < DP / 16; ++kb)
+                ldsm_x4(qf[kb], sQ + (warp * 16 + (lane & 7) + 8 * ((lane >> 3) & 1)) * PITCH + kb * 16 + 8 * (lane >> 4));
+        }
+        const __nv_bfloat16* tK = sK + st * ATT_BKV * PITCH;
+        const __nv_bfloat16* tV = sV + st * ATT_BKV * PITCH;
+
+        // S = Q K^T : 16 x 64 per warp
+        float s[8][4];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f;
+#pragma unroll
+        for (int kb = 0; kb < DP / 16; ++kb) {
+#pragma unroll
+            for (int np = 0; np < 4; ++np) {
+                uint32_t bf[4];
+                ldsm_x4(bf, tK + (np * 16 + (lane & 7) + 8 * (lane >> 4)) * PITCH + kb * 16 + 8 * ((lane >> 3) & 1));
+                mma16816(s[2 * np], qf[kb], bf[0], bf[1]);
+                mma16816(s[2 * np + 1], qf[kb], bf[2], bf[3]);
+            }
+        }
+        // mask keys beyond lk, running max
+        const int kbase = t * ATT_BKV + (lane & 3) * 2;
+        float mx0 = m0, mx1 = m1;
+#pragma unroll
+        for (int nb = 0; nb < 8; ++nb) {
+            const int key = kbase + nb * 8;
+            if (key >= lk) s[nb][0] = s[nb][2] = -INFINITY;
+            if (key + 1 >= lk) s[nb][1] = s[nb][3] = -INFINITY;
+            mx0 = fmaxf(mx0, fmaxf(s[nb][0], s[nb][1]));
+            mx1 = fmaxf(mx1, fmaxf(s[nb][2], s[nb][3]));
+        }
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        const float a0 = exp2f((m0 - mx0) * scale_log2), a1 = exp2f((m1 - mx1) * scale_log2);
+        m0 = mx0, m1 = mx1;
+        const float ms0 = mx0 * scale_log2, ms1 = mx1 * scale_log2;
+        float rs0 = 0.f, rs1 = 0.f;
+#pragma unroll
+        for (int nb = 0; nb < 8; ++nb) {
+            s[nb][0] = exp2f(s[nb][0] * scale_log2 - ms0);
+            s[nb][1] = exp2f(s[nb][1] * scale_log2 - ms0);
+            s[nb][2] = exp2f(s[nb][2] * scale_log2 - ms1);
+            s[nb][3] = exp2f(s[nb][3] * scale_log2 - ms1);
+            rs0 += s[nb][0] + s[nb][1];
+            rs1 += s[nb][2] + s[nb][3];
+        }
+        l0 = l0 * a0 + rs0;
+        l1 = l1 * a1 + rs1;
+#pragma unroll
+        for (int i = 0; i < DP / 8; ++i) {
+            o[i][0] *= a0, o[i][1] *= a0;
+            o[i][2] *= a1, o[i][3] *= a1;
+        }
+        // O += P V
+#pragma unroll
+        for (int kb = 0; kb < 4; ++kb) {
+            uint32_t pf[4];
+            pf[0] = pack_bf16(s[2 * kb][0], s[2 * kb][1]);
+            pf[1] = pack_bf16(s[2 * kb][2], s[2 * kb][3]);
+            pf[2] = pack_bf16(s[2 * kb + 1][0], s[2 * kb + 1][1]);
+            pf[3] = pack_bf16(s[2 * kb + 1][2], s[2 * kb + 1][3]);
+#pragma unroll
+            for (int dp = 0; dp < DP / 16; ++dp) {
+                uint32_t bf[4];
+                ldsm_x4_t(bf, tV + (kb * 16 + (lane & 7) + 8 * ((lane >> 3) & 1)) * PITCH + dp * 16 + 8 * (lane >> 4));
+                mma16816(o[2 * dp], pf, bf[0], bf[1]);
+                mma16816(o[2 * dp + 1], pf, bf[2], bf[3]);
+            }
+        }
+        __syncthreads();  // everyone done with stage st before it is refilled at iteration t+1
+    }
+    // finalise: row sums across the quad, normalise, store
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    const float i0 = 1.f / l0, i1 = 1.f / l1;
+    const int r0 = q0 + warp * 16 + (lane >> 2), r1 = r0 + 8;
+    __nv_bfloat16* og = out + (b * lq) * ld_o + head * d;
+#pragma unroll
+    for (int nb = 0; nb < DP / 8; ++nb) {
+        const int col = nb * 8 + (lane & 3) * 2;
+        if (col < d) {
+            if (r0 < lq)
+                *reinterpret_cast<__nv_bfloat162*>(og + (long long)r0 * ld_o + col) =
+                    __floats2bfloat162_rn(o[nb][0] * i0, o[nb][1] * i0);
+            if (r1 < lq)
+                *reinterpret_cast<__nv_bfloat162*>(og + (long long)r1 * ld_o + col) =
+                    __floats2bfloat162_rn(o[nb][2] * i1, o[nb][3] * i1);
+        }
+    }
+}
+
+template <int DP>
+static int launch_attention(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v,
+                            void* out, int64_t ld_o, int64_t batch, int heads, int lq, int lk, int d, float scale,
+                            cudaStream_t st) {
+    constexpr int PITCH = DP + 8;
+    const size_t smem = (size_t)(ATT_BQ + 4 * ATT_BKV) * PITCH * 2;
+    static bool configured = false;
+    if (!configured) {
+        cudaFuncSetAttribute(attention_kernel<DP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        configured = true;
+    }
+    dim3 grid((lq + ATT_BQ - 1) / ATT_BQ, heads, (unsigned)batch);
+    attention_kernel<DP><<<grid, ATT_THREADS, smem, st>>>(
+        static_cast<const __nv_bfloat16*>(q), ld_q, static_cast<const __nv_bfloat16*>(k), ld_k,
+        static_cast<const __nv_bfloat16*>(v), ld_v, static_cast<__nv_bfloat16*>(out), ld_o, lq, lk, d,
+        scale * 1.4426950408889634f);
+    B200_CHECK_LAUNCH("attention");
+    return B200SD_OK;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200sd_attention(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v,
+                                void* out, int64_t ld_o, int64_t batch, int heads, int lq, int lk, int d, float scale,
+                                void* stream) {
+    B200_REQUIRE(q && k && v && out, "attention: null pointer");
+    B200_REQUIRE(batch >= 0 && heads >= 1 && lq >= 1 && lk >= 1, "attention: bad sizes");
+    B200_REQUIRE(batch <= 65535 && heads <= 65535, "attention: batch/heads exceed grid limits");
+    if (d % 8 != 0 || d < 8 || d > 64) {
+        set_error("attention: head dim %d unsupported (need a multiple of 8 in [8, 64])", d);
+        return B200SD_ERR_UNSUPPORTED;
+    }
+    B200_REQUIRE(ld_q % 8 == 0 && ld_k % 8 == 0 && ld_v % 8 == 0 && ld_o % 2 == 0, "attention: leading dims unaligned");
+    B200_REQUIRE(((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(k) | reinterpret_cast<uintptr_t>(v)) & 15) == 0 &&
+                     (reinterpret_cast<uintptr_t>(out) & 3) == 0,
+                 "attention: pointers unaligned");
+    if (batch == 0) return B200SD_OK;
+    cudaStream_t st = as_stream(stream);
+    const int dp = (d + 15) / 16 * 16;
+    switch (dp) {
+        case 16: return launch_attention<16>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, d, scale, st);
+        case 32: return launch_attention<32>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, d, scale, st);
+        case 48: return launch_attention<48>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, d, scale, st);
+        default: return launch_attention<64>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, d, scale, st);
+    }
+}

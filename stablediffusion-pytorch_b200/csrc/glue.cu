@@ -1,0 +1,171 @@
+// Layout and conditioning glue (SURVEY K14 + boundary conversions). All HBM-bound, coalesced on the side that
+// dominates traffic; tiny next to the GEMMs but each replaces several ATen launches in the reference.
+#include "host.h"
+#include <cuda_bf16.h>
+
+namespace b200 {
+
+__device__ __forceinline__ float glue_act(float v, int act) {
+    if (act == B200SD_ACT_SILU) return v / (1.f + __expf(-v));
+    if (act == B200SD_ACT_RELU) return fmaxf(v, 0.f);
+    return v;
+}
+
+// src NCHW fp32 -> dst NHWC bf16 slice. Thread per (n, p): reads are coalesced over p for each c.
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long ld,
+                                    int c_off, long long n, int c, long long hw) {
+    const long long total = n * hw;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long img = i / hw, p = i - img * hw;
+        const float* s = src + img * c * hw + p;
+        __nv_bfloat16* d = dst + i * ld + c_off;
+        for (int k = 0; k < c; ++k) d[k] = __float2bfloat16_rn(s[(long long)k * hw]);
+    }
+}
+
+template <typename T>
+__global__ void nhwc_to_nchw_kernel(const T* __restrict__ src, long long ld, float* __restrict__ dst, long long n,
+                                    int c, long long hw) {
+    const long long total = n * hw;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long img = i / hw, p = i - img * hw;
+        const T* s = src + i * ld;
+        float* d = dst + img * c * hw + p;
+        for (int k = 0; k < c; ++k) d[(long long)k * hw] = static_cast<float>(s[k]);
+    }
+}
+
+// Mask path: nearest resize + 1x1 conv (no bias) + write into the conv_in input slice. Thread per output pixel.
+// F.interpolate(mode='nearest') picks src = floor(dst * scale) with scale = in/out computed in fp32.
+__global__ void mask_cond_kernel(const float* __restrict__ mask, const float* __restrict__ w,
+                                 __nv_bfloat16* __restrict__ dst, long long ld, int c_off, long long n, int cin,
+                                 int cout, int mh, int mw, int h, int wd) {
+    extern __shared__ float sw[];  // [cout, cin]
+    for (int i = threadIdx.x; i < cout * cin; i += blockDim.x) sw[i] = w[i];
+    __syncthreads();
+    const float sy = (float)mh / (float)h, sx = (float)mw / (float)wd;
+    const long long total = n * h * wd;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int x = (int)(i % wd);
+        const int yy = (int)((i / wd) % h);
+        const long long img = i / ((long long)wd * h);
+        const int srcy = min((int)floorf(yy * sy), mh - 1);
+        const int srcx = min((int)floorf(x * sx), mw - 1);
+        const float* m = mask + (img * cin * mh + srcy) * (long long)mw + srcx;
+        float acc[8];
+        for (int o = 0; o < cout; ++o) acc[o] = 0.f;
+        for (int k = 0; k < cin; ++k) {
+            // autocast semantics: the conv sees bf16 inputs and weights, accumulates fp32
+            const float mv = __bfloat162float(__float2bfloat16_rn(m[(long long)k * mh * mw]));
+            for (int o = 0; o < cout; ++o)
+                acc[o] += mv * __bfloat162float(__float2bfloat16_rn(sw[o * cin + k]));
+        }
+        __nv_bfloat16* d = dst + i * ld + c_off;
+        for (int o = 0; o < cout; ++o) d[o] = __float2bfloat16_rn(acc[o]);
+    }
+}
+
+__global__ void copy_act_kernel(const __nv_bfloat16* __restrict__ src, long long ld_src,
+                                __nv_bfloat16* __restrict__ dst, long long ld_dst, int c_off, long long rows, int c,
+                                int act, int vec) {
+    if (vec) {  // 8 channels (16 B) per thread
+        const int vpr = c >> 3;
+        const long long total = rows * vpr;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+             i += (long long)gridDim.x * blockDim.x) {
+            const long long r = i / vpr;
+            const int v = (int)(i - r * vpr);
+            uint4 u = *reinterpret_cast<const uint4*>(src + r * ld_src + v * 8);
+            if (act != B200SD_ACT_NONE) {
+                __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    float2 f = __bfloat1622float2(h[j]);
+                    h[j] = __floats2bfloat162_rn(glue_act(f.x, act), glue_act(f.y, act));
+                }
+            }
+            *reinterpret_cast<uint4*>(dst + r * ld_dst + c_off + v * 8) = u;
+        }
+    } else {
+        const long long total = rows * c;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+             i += (long long)gridDim.x * blockDim.x) {
+            const long long r = i / c;
+            const int k = (int)(i - r * c);
+            dst[r * ld_dst + c_off + k] =
+                __float2bfloat16_rn(glue_act(__bfloat162float(src[r * ld_src + k]), act));
+        }
+    }
+}
+
+static inline int glue_grid(long long items, int threads) {
+    long long b = (items + threads - 1) / threads;
+    long long cap = (long long)sm_count() * 8;
+    return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200sd_nchw_to_nhwc(const float* src, void* dst, int64_t ld_dst, int c_off, int64_t n, int c,
+                                   int64_t hw, void* stream) {
+    B200_REQUIRE(src && dst, "nchw_to_nhwc: null pointer");
+    B200_REQUIRE(c_off >= 0 && c_off + c <= ld_dst, "nchw_to_nhwc: channel slice [%d,%d) exceeds ld %lld", c_off,
+                 c_off + c, (long long)ld_dst);
+    if (n * hw == 0) return B200SD_OK;
+    nchw_to_nhwc_kernel<<<glue_grid(n * hw, 256), 256, 0, as_stream(stream)>>>(
+        src, static_cast<__nv_bfloat16*>(dst), ld_dst, c_off, n, c, hw);
+    B200_CHECK_LAUNCH("nchw_to_nhwc");
+    return B200SD_OK;
+}
+
+extern "C" int b200sd_nhwc_to_nchw(const void* src, int src_dtype, int64_t ld_src, float* dst, int64_t n, int c,
+                                   int64_t hw, void* stream) {
+    B200_REQUIRE(src && dst, "nhwc_to_nchw: null pointer");
+    B200_REQUIRE(c <= ld_src, "nhwc_to_nchw: c=%d exceeds ld %lld", c, (long long)ld_src);
+    if (n * hw == 0) return B200SD_OK;
+    const int grid = glue_grid(n * hw, 256);
+    if (src_dtype == B200SD_DT_BF16)
+        nhwc_to_nchw_kernel<__nv_bfloat16>
+            <<<grid, 256, 0, as_stream(stream)>>>(static_cast<const __nv_bfloat16*>(src), ld_src, dst, n, c, hw);
+    else if (src_dtype == B200SD_DT_F32)
+        nhwc_to_nchw_kernel<float><<<grid, 256, 0, as_stream(stream)>>>(static_cast<const float*>(src), ld_src, dst, n, c, hw);
+    else {
+        set_error("nhwc_to_nchw: bad dtype %d", src_dtype);
+        return B200SD_ERR_ARG;
+    }
+    B200_CHECK_LAUNCH("nhwc_to_nchw");
+    return B200SD_OK;
+}
+
+extern "C" int b200sd_mask_cond(const float* mask, const float* w, void* dst, int64_t ld_dst, int c_off, int64_t n,
+                                int cin, int cout, int mh, int mw, int h, int wd, void* stream) {
+    B200_REQUIRE(mask && w && dst, "mask_cond: null pointer");
+    B200_REQUIRE(cout >= 1 && cout <= 8, "mask_cond: %d output channels (max 8)", cout);
+    B200_REQUIRE(c_off >= 0 && c_off + cout <= ld_dst, "mask_cond: channel slice exceeds ld");
+    B200_REQUIRE(cin >= 1 && cin * cout * 4 <= 48 * 1024, "mask_cond: weight too large for shared memory");
+    if (n == 0) return B200SD_OK;
+    mask_cond_kernel<<<glue_grid(n * h * wd, 128), 128, cin * cout * sizeof(float), as_stream(stream)>>>(
+        mask, w, static_cast<__nv_bfloat16*>(dst), ld_dst, c_off, n, cin, cout, mh, mw, h, wd);
+    B200_CHECK_LAUNCH("mask_cond");
+    return B200SD_OK;
+}
+
+extern "C" int b200sd_copy_act(const void* src, int64_t ld_src, void* dst, int64_t ld_dst, int c_off, int64_t rows,
+                               int c, int act, void* stream) {
+    B200_REQUIRE(src && dst, "copy_act: null pointer");
+    B200_REQUIRE(c <= ld_src && c_off >= 0 && c_off + c <= ld_dst, "copy_act: slice exceeds leading dimension");
+    if (rows * c == 0) return B200SD_OK;
+    const int vec = (c % 8 == 0) && (ld_src % 8 == 0) && (ld_dst % 8 == 0) && (c_off % 8 == 0) &&
+                    ((reinterpret_cast<uintptr_t>(src) & 15) == 0) && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0);
+    const long long items = vec ? rows * (c / 8) : rows * c;
+    copy_act_kernel<<<glue_grid(items, 256), 256, 0, as_stream(stream)>>>(
+        static_cast<const __nv_bfloat16*>(src), ld_src, static_cast<__nv_bfloat16*>(dst), ld_dst, c_off, rows, c, act,
+        vec);
+    B200_CHECK_LAUNCH("copy_act");
+    return B200SD_OK;
+}

@@ -1,0 +1,175 @@
+// GroupNorm (+SiLU/ReLU) over NHWC bf16 activations. HBM-bound: one read + one write per element.
+// A CTA owns one image and a slab of `gpc` adjacent groups (cw = gpc * C/G channels); the slab is staged in shared
+// memory when it fits so that the three passes (mean, centred variance, normalise) touch HBM once for the read
+// and once for the write. Mean/variance use the two-pass form in fp32 (no E[x^2]-E[x]^2 cancellation).
+#include "host.h"
+#include <cuda_bf16.h>
+
+namespace b200 {
+
+__device__ __forceinline__ float act_apply(float v, int act) {
+    if (act == B200SD_ACT_SILU) return v / (1.f + __expf(-v));
+    if (act == B200SD_ACT_RELU) return fmaxf(v, 0.f);
+    return v;
+}
+
+// VEC = channels per thread item (2 -> bf16x2 accesses; 1 -> scalar, for odd channels-per-group)
+template <int VEC>
+__global__ void __launch_bounds__(512)
+    groupnorm_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, __nv_bfloat16* __restrict__ y,
+                     long long ld_y, const float* __restrict__ gamma, const float* __restrict__ beta, long long hw,
+                     int c, int cpg, int gpc, float eps, int act, int cached, int rows_per_pass) {
+    extern __shared__ __align__(16) uint8_t gn_smem[];
+    __shared__ float s_sum[64];
+    __shared__ float s_mean[64];
+    __shared__ float s_rstd[64];
+
+    const int cw = gpc * cpg;
+    const int vpr = cw / VEC;  // vector items per pixel row of the slab
+    const int chunks = c / cw;
+    const int img = blockIdx.x / chunks;
+    const int c0 = (blockIdx.x % chunks) * cw;
+    const int tid = threadIdx.x;
+    const bool active = tid < vpr * rows_per_pass;
+    const int v = tid % vpr;           // constant per thread: blockDim is used in whole rows
+    const int row0 = tid / vpr;
+    const int g_local = (v * VEC) / cpg;  // VEC divides cpg, so an item never straddles groups
+    const __nv_bfloat16* xs = x + (long long)img * hw * ld_x + c0 + v * VEC;
+    __nv_bfloat16* ys = y + (long long)img * hw * ld_y + c0 + v * VEC;
+    __nv_bfloat16* cache = reinterpret_cast<__nv_bfloat16*>(gn_smem);
+    const float inv_cnt = 1.f / (float)(hw * cpg);
+
+    if (tid < 64) s_sum[tid] = 0.f;
+    __syncthreads();
+
+    // pass 1: sum (and fill the cache)
+    float acc = 0.f;
+    if (active) {
+        for (long long r = row0; r < hw; r += rows_per_pass) {
+            if (VEC == 2) {
+                __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(xs + r * ld_x);
+                if (cached) *reinterpret_cast<__nv_bfloat162*>(cache + r * cw + v * 2) = h;
+                float2 f = __bfloat1622float2(h);
+                acc += f.x + f.y;
+            } else {
+                __nv_bfloat16 h = xs[r * ld_x];
+                if (cached) cache[r * cw + v] = h;
+                acc += __bfloat162float(h);
+            }
+        }
+        atomicAdd(&s_sum[g_local], acc);
+    }
+    __syncthreads();
+    if (tid < gpc) s_mean[tid] = s_sum[tid] * inv_cnt;
+    __syncthreads();
+    if (tid < 64) s_sum[tid] = 0.f;
+    __syncthreads();
+
+    // pass 2: centred sum of squares
+    if (active) {
+        const float m = s_mean[g_local];
+        acc = 0.f;
+        for (long long r = row0; r < hw; r += rows_per_pass) {
+            if (VEC == 2) {
+                __nv_bfloat162 h = cached ? *reinterpret_cast<const __nv_bfloat162*>(cache + r * cw + v * 2)
+                                          : *reinterpret_cast<const __nv_bfloat162*>(xs + r * ld_x);
+                float2 f = __bfloat1622float2(h);
+                acc += (f.x - m) * (f.x - m) + (f.y - m) * (f.y - m);
+            } else {
+                float f = __bfloat162float(cached ? cache[r * cw + v] : xs[r * ld_x]);
+                acc += (f - m) * (f - m);
+            }
+        }
+        atomicAdd(&s_sum[g_local], acc);
+    }
+    __syncthreads();
+    if (tid < gpc) s_rstd[tid] = rsqrtf(s_sum[tid] * inv_cnt + eps);
+    __syncthreads();
+
+    // pass 3: normalise, affine, activation, store
+    if (active) {
+        const float m = s_mean[g_local], rs = s_rstd[g_local];
+        const int ch = c0 + v * VEC;
+        const float g0 = gamma ? gamma[ch] : 1.f, b0 = beta ? beta[ch] : 0.f;
+        const float sc0 = rs * g0, sh0 = b0 - m * rs * g0;
+        float sc1 = 0.f, sh1 = 0.f;
+        if (VEC == 2) {
+            const float g1 = gamma ? gamma[ch + 1] : 1.f, b1 = beta ? beta[ch + 1] : 0.f;
+            sc1 = rs * g1, sh1 = b1 - m * rs * g1;
+        }
+        for (long long r = row0; r < hw; r += rows_per_pass) {
+            if (VEC == 2) {
+                __nv_bfloat162 h = cached ? *reinterpret_cast<const __nv_bfloat162*>(cache + r * cw + v * 2)
+                                          : *reinterpret_cast<const __nv_bfloat162*>(xs + r * ld_x);
+                float2 f = __bfloat1622float2(h);
+                f.x = act_apply(f.x * sc0 + sh0, act);
+                f.y = act_apply(f.y * sc1 + sh1, act);
+                *reinterpret_cast<__nv_bfloat162*>(ys + r * ld_y) = __floats2bfloat162_rn(f.x, f.y);
+            } else {
+                float f = __bfloat162float(cached ? cache[r * cw + v] : xs[r * ld_x]);
+                ys[r * ld_y] = __float2bfloat16_rn(act_apply(f * sc0 + sh0, act));
+            }
+        }
+    }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200sd_groupnorm(const void* x, int64_t ld_x, void* y, int64_t ld_y, const float* gamma,
+                                const float* beta, int64_t n, int64_t hw, int c, int groups, float eps, int act,
+                                void* stream) {
+    B200_REQUIRE(x && y, "groupnorm: null pointer");
+    B200_REQUIRE(groups > 0 && c > 0 && c % groups == 0, "groupnorm: %d channels not divisible by %d groups", c,
+                 groups);
+    B200_REQUIRE(ld_x >= c && ld_y >= c, "groupnorm: leading dimension smaller than channel count");
+    if (n == 0 || hw == 0) return B200SD_OK;
+    const int cpg = c / groups;
+    const bool vec2 = (cpg % 2 == 0) && (ld_x % 2 == 0) && (ld_y % 2 == 0) &&
+                      ((reinterpret_cast<uintptr_t>(x) & 3) == 0) && ((reinterpret_cast<uintptr_t>(y) & 3) == 0);
+    const int VEC = vec2 ? 2 : 1;
+    // groups per CTA: widen the slab towards 64 B of contiguous channels per pixel while it still fits a 64 KB
+    // stage and while the grid keeps >= 2 CTAs per SM
+    int gpc = 1;
+    const long long min_ctas = 2ll * sm_count();
+    while (true) {
+        int next = gpc * 2;
+        if (groups % next != 0) break;
+        long long cw = (long long)next * cpg;
+        if (cw > 128 || next > 64) break;
+        if (cw / VEC > 256) break;
+        if (hw * cw * 2 > 65536 && hw * (long long)gpc * cpg * 2 <= 65536) break;
+        if ((long long)gpc * cpg * 2 >= 64 && n * (groups / next) < min_ctas) break;
+        gpc = next;
+    }
+    const int cw = gpc * cpg;
+    const int vpr = cw / VEC;
+    B200_REQUIRE(vpr <= 512, "groupnorm: %d channels per group slab is too wide", cw);
+    int rows_per_pass = 512 / vpr;
+    if (rows_per_pass > hw) rows_per_pass = (int)hw;
+    if (rows_per_pass < 1) rows_per_pass = 1;
+    int threads = ((vpr * rows_per_pass + 31) / 32) * 32;
+    const long long slab = hw * cw * 2;
+    const int cached = slab <= 65536 ? 1 : 0;
+    const size_t smem = cached ? (size_t)slab : 0;
+    const long long grid = n * (c / cw);
+    B200_REQUIRE(grid < (1ll << 31), "groupnorm: grid too large");
+    cudaStream_t st = as_stream(stream);
+    static bool configured = false;
+    if (!configured) {
+        cudaFuncSetAttribute(groupnorm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536);
+        cudaFuncSetAttribute(groupnorm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536);
+        configured = true;
+    }
+    if (VEC == 2)
+        groupnorm_kernel<2><<<(int)grid, threads, smem, st>>>(
+            static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y, gamma, beta, hw, c, cpg,
+            gpc, eps, act, cached, rows_per_pass);
+    else
+        groupnorm_kernel<1><<<(int)grid, threads, smem, st>>>(
+            static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y, gamma, beta, hw, c, cpg,
+            gpc, eps, act, cached, rows_per_pass);
+    B200_CHECK_LAUNCH("groupnorm");
+    return B200SD_OK;
+}

@@ -1,0 +1,215 @@
+"""Per-kernel numerics through the C-ABI against plain PyTorch fp32 references of the same op (floating-point
+kernels) on bf16-rounded inputs. Tolerances are written at each assert. Model-level parity against the oracle and
+the golden fixtures lives in test_parity_gpu.py."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return torch.device("cuda:0")
+
+
+def relerr(a, b):
+    """max |a-b| / max |b| — the 'max relative error' used throughout (per-element ratios blow up at zeros)."""
+    return ((a.float() - b.float()).abs().max() / b.float().abs().max().clamp_min(1e-20)).item()
+
+
+def bf(x):
+    return x.to(torch.bfloat16)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (256, 256, 512), (1000, 384, 200), (64, 1536, 512),
+                                   (4096, 192, 1152), (77 * 4, 96, 512), (128, 4, 128), (8192, 768, 768)])
+def test_linear(rt, M, N, K):
+    dev = _dev()
+    from sdb200 import ops
+    g = torch.Generator(device="cpu").manual_seed(M * 7 + N * 3 + K)
+    Kld = (K + 7) // 8 * 8
+    a = torch.zeros(M, Kld, dtype=torch.bfloat16)
+    a[:, :K] = bf(torch.randn(M, K, generator=g))
+    w = torch.randn(N, K, generator=g) / K ** 0.5
+    b = torch.randn(N, generator=g)
+    a_d = a.to(dev)[:, :K] if Kld != K else a.to(dev)
+    wp = ops.pack_linear_weight(w.to(dev))
+    out = rt.linear(a_d, wp, bias=b.to(dev))
+    torch.cuda.synchronize()
+    ref = a[:, :K].float() @ bf(w).float().t() + b
+    # fp32 accumulate of bf16 products, one bf16 rounding at the output: 2^-8 relative
+    assert relerr(out.cpu(), ref) < 6e-3
+
+
+def test_linear_epilogue(rt):
+    dev = _dev()
+    from sdb200 import ops
+    g = torch.Generator().manual_seed(5)
+    B, L, K, N = 3, 256, 288, 288
+    a = bf(torch.randn(B * L, K, generator=g))
+    w = torch.randn(N, K, generator=g) / K ** 0.5
+    b = torch.randn(N, generator=g)
+    res = bf(torch.randn(B * L, N, generator=g))
+    gate = bf(torch.randn(B, N, generator=g))
+    rowb = bf(torch.randn(B, N, generator=g))
+    wp = ops.pack_linear_weight(w.to(dev))
+    out = rt.linear(a.to(dev), wp, bias=b.to(dev), act="silu", residual=res.to(dev), rows_per_img=L,
+                    rowbias=rowb.to(dev), gate=gate.to(dev))
+    torch.cuda.synchronize()
+    v = a.float() @ bf(w).float().t() + b + rowb.float().repeat_interleave(L, 0)
+    ref = F.silu(v) * gate.float().repeat_interleave(L, 0) + res.float()
+    assert relerr(out.cpu(), ref) < 6e-3
+    out32 = rt.linear(a.to(dev), wp, bias=b.to(dev), act="relu", out_dtype=torch.float32)
+    ref32 = F.relu(a.float() @ bf(w).float().t() + b)
+    assert relerr(out32.cpu(), ref32) < 1e-4  # fp32 output: only accumulation-order differences remain
+
+
+CONV_CASES = [  # n, h, w, cin, cout, k
+    (2, 32, 32, 64, 128, 3), (3, 16, 16, 128, 192, 3), (5, 8, 8, 192, 256, 3), (9, 4, 4, 256, 64, 3),
+    (1, 64, 64, 64, 64, 3), (1, 128, 128, 64, 32, 3), (2, 32, 32, 7, 64, 3), (2, 32, 32, 128, 4, 3),
+    (2, 16, 16, 320, 96, 1), (1, 256, 256, 64, 3, 3),
+]
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout,k", CONV_CASES)
+def test_conv_same(rt, n, h, w, cin, cout, k):
+    dev = _dev()
+    from sdb200 import ops
+    g = torch.Generator().manual_seed(n * 100 + h + cin + cout)
+    x = bf(torch.randn(n, cin, h, w, generator=g))
+    wt = torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5
+    b = torch.randn(cout, generator=g)
+    ld = (cin + 7) // 8 * 8
+    xh = torch.zeros(n * h * w, ld, dtype=torch.bfloat16)
+    xh[:, :cin] = x.permute(0, 2, 3, 1).reshape(-1, cin)
+    out = ops.conv_same(xh.to(dev), n, h, w, cin, ops.pack_conv_weight(wt.to(dev)), cout, k, bias=b.to(dev), ld_x=ld)
+    torch.cuda.synchronize()
+    ref = F.conv2d(x.float(), bf(wt).float(), b, padding=k // 2).permute(0, 2, 3, 1).reshape(-1, cout)
+    assert relerr(out.cpu(), ref) < 6e-3
+
+
+def test_resnet_second_half_fused(rt):
+    """conv3x3(h) + temb row bias, then conv3x3 + fused 1x1 residual conv of the block input (blocks.py:115-119)."""
+    dev = _dev()
+    from sdb200 import ops
+    g = torch.Generator().manual_seed(11)
+    n, h, w, cin, cout = 3, 16, 16, 128, 192
+    x = bf(torch.randn(n, cin, h, w, generator=g))
+    hmid = bf(torch.randn(n, cout, h, w, generator=g))
+    w2 = torch.randn(cout, cout, 3, 3, generator=g) / (cout * 9) ** 0.5
+    wr = torch.randn(cout, cin, 1, 1, generator=g) / cin ** 0.5
+    b2, br = torch.randn(cout, generator=g), torch.randn(cout, generator=g)
+    temb = bf(torch.randn(n, cout, generator=g))
+    to_nhwc = lambda t: t.permute(0, 2, 3, 1).reshape(-1, t.shape[1]).contiguous()
+    wcat = torch.cat([ops.pack_conv_weight(w2.to(dev)), ops.pack_conv_weight(wr.to(dev))], dim=1).contiguous()
+    out = ops.conv_same(to_nhwc(hmid).to(dev), n, h, w, cout, wcat, cout, 3, bias=(b2 + br).to(dev),
+                        extra=(to_nhwc(x).to(dev), cin, cin), rowbias=temb.to(dev))
+    torch.cuda.synchronize()
+    ref = F.conv2d(hmid.float(), bf(w2).float(), b2, padding=1) + F.conv2d(x.float(), bf(wr).float(), br)
+    ref = ref + temb.float()[:, :, None, None]
+    assert relerr(out.cpu(), to_nhwc(ref)) < 6e-3
+
+
+@pytest.mark.parametrize("n,h,w,c", [(2, 32, 32, 128), (3, 16, 16, 64), (5, 8, 8, 192)])
+def test_conv_down_up(rt, n, h, w, c):
+    dev = _dev()
+    from sdb200 import ops
+    g = torch.Generator().manual_seed(h + c)
+    x = bf(torch.randn(n, c, h, w, generator=g))
+    to_nhwc = lambda t: t.permute(0, 2, 3, 1).reshape(-1, t.shape[1]).contiguous()
+    wd = torch.randn(c, c, 4, 4, generator=g) / (c * 16) ** 0.5
+    b = torch.randn(c, generator=g)
+    out = ops.conv_down4x4(to_nhwc(x).to(dev), n, h, w, c, ops.pack_conv_weight(wd.to(dev)), c, bias=b.to(dev))
+    torch.cuda.synchronize()
+    ref = F.conv2d(x.float(), bf(wd).float(), b, stride=2, padding=1)
+    assert relerr(out.cpu(), to_nhwc(ref)) < 6e-3
+    wu = torch.randn(c, c, 4, 4, generator=g) / (c * 4) ** 0.5
+    # into a channel slice of a wider buffer, as the up blocks do before the skip concat
+    buf = torch.zeros(n * 4 * h * w, 2 * c, dtype=torch.bfloat16, device=dev)
+    ops.conv_up4x4(to_nhwc(x).to(dev), n, h, w, c, ops.pack_convT_weight(wu.to(dev)), c, bias=b.to(dev), out=buf)
+    torch.cuda.synchronize()
+    ref = F.conv_transpose2d(x.float(), bf(wu).float(), b, stride=2, padding=1)
+    assert relerr(buf[:, :c].cpu(), to_nhwc(ref)) < 6e-3
+    assert buf[:, c:].abs().max().item() == 0.0
+
+
+@pytest.mark.parametrize("n,hw,c,groups,act", [(2, 1024, 384, 32, "silu"), (3, 256, 512, 32, None),
+                                               (4, 16, 768, 32, "silu"), (2, 1024, 128, 32, "relu"),
+                                               (1, 65536, 64, 32, "silu"), (2, 64, 48, 16, "silu"),
+                                               (2, 1024, 7 * 8, 8, None)])
+def test_groupnorm(rt, n, hw, c, groups, act):
+    dev = _dev()
+    g = torch.Generator().manual_seed(hw + c)
+    x = bf(torch.randn(n, hw, c, generator=g) * 2 + 0.7)
+    gamma, beta = torch.randn(c, generator=g), torch.randn(c, generator=g)
+    out = rt.groupnorm(x.reshape(-1, c).to(dev), n, hw, c, groups, gamma.to(dev), beta.to(dev), act=act)
+    torch.cuda.synchronize()
+    ref = F.group_norm(x.float().permute(0, 2, 1), groups, gamma, beta, 1e-5).permute(0, 2, 1)
+    ref = {"silu": F.silu, "relu": F.relu, None: lambda t: t}[act](ref)
+    assert relerr(out.cpu().reshape(n, hw, c), ref) < 6e-3
+
+
+@pytest.mark.parametrize("b,heads,lq,lk,d", [(2, 16, 1024, 1024, 24), (3, 16, 256, 256, 32), (2, 16, 64, 64, 48),
+                                             (5, 16, 16, 16, 32), (2, 16, 1024, 77, 8), (2, 16, 256, 77, 16),
+                                             (1, 4, 1024, 1024, 64), (2, 9, 256, 256, 32), (3, 16, 16, 77, 32)])
+def test_attention(rt, b, heads, lq, lk, d):
+    dev = _dev()
+    g = torch.Generator().manual_seed(lq + lk + d)
+    C = heads * d
+    qkv = bf(torch.randn(b * lq, 3 * C, generator=g))
+    if lk == lq:
+        q, k, v = qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:]
+        qd = qkv.to(dev)
+        out = rt.attention(qd[:, :C], qd[:, C:2 * C], qd[:, 2 * C:], b, heads, lq, lk, d)
+    else:
+        q = qkv[:, :C]
+        kv = bf(torch.randn(b * lk, 2 * C, generator=g))
+        k, v = kv[:, :C], kv[:, C:]
+        kvd = kv.to(dev)
+        out = rt.attention(q.contiguous().to(dev), kvd[:, :C], kvd[:, C:], b, heads, lq, lk, d)
+    torch.cuda.synchronize()
+    sh = lambda t, L: t.float().reshape(b, L, heads, d).transpose(1, 2)
+    ref = F.scaled_dot_product_attention(sh(q, lq), sh(k, lk), sh(v, lk)).transpose(1, 2).reshape(b * lq, C)
+    # P is rounded to bf16 before the PV product and the output is bf16
+    assert relerr(out.cpu(), ref) < 1e-2
+
+
+def test_attention_unsupported_head_dim(rt):
+    dev = _dev()
+    x = torch.zeros(16, 3 * 16 * 3, dtype=torch.bfloat16, device=dev)
+    with pytest.raises(rt.B200Error):
+        rt.attention(x, x, x, 1, 16, 16, 16, 3)
+
+
+def test_layout_and_mask(rt):
+    dev = _dev()
+    g = torch.Generator().manual_seed(3)
+    n, h, w = 3, 32, 32
+    x = torch.randn(n, 4, h, w, generator=g)
+    mask = (torch.rand(n, 18, 512, 512, generator=g) > 0.5).float()
+    wc = torch.randn(3, 18, generator=g)
+    buf = torch.zeros(n * h * w, 8, dtype=torch.bfloat16, device=dev)
+    rt.nchw_to_nhwc(x.to(dev), buf, 0)
+    rt.mask_cond(mask.to(dev), wc.to(dev), buf, 4, h, w)
+    torch.cuda.synchronize()
+    ref_m = F.conv2d(F.interpolate(mask, size=(h, w)), bf(wc).float()[:, :, None, None])
+    ref = torch.cat([x, ref_m], 1).permute(0, 2, 3, 1).reshape(-1, 7)
+    assert relerr(buf[:, :7].cpu(), ref) < 5e-3
+    assert buf[:, 7].abs().max().item() == 0
+    back = rt.nhwc_to_nchw(buf, n, 7, h, w, ld=8)
+    assert torch.equal(back.cpu(), buf[:, :7].float().cpu().reshape(n, h, w, 7).permute(0, 3, 1, 2))
+
+
+def test_time_embedding(rt):
+    dev = _dev()
+    t = torch.tensor([0, 1, 17, 500, 999], dtype=torch.int64)
+    out = rt.time_embedding(t.to(dev), 5, 512, dtype=torch.float32)
+    half = 256
+    factor = 10000 ** (torch.arange(0, half, dtype=torch.float32) / half)
+    e = t[:, None].repeat(1, half) / factor
+    ref = torch.cat([torch.sin(e), torch.cos(e)], -1)
+    assert (out.cpu() - ref).abs().max().item() < 2e-4  # fp32 sin/cos of arguments up to 999 (ulp of arg ~6e-5)
+    out1 = rt.time_embedding(t[2:3].to(dev), 4, 512, dtype=torch.float32)  # (1,) t broadcast over the batch
+    assert torch.equal(out1.cpu(), out.cpu()[2:3].expand(4, -1))
