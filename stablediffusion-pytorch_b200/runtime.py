@@ -108,6 +108,8 @@ def sched_add_noise(x0, noise, t, sqrt_acp, sqrt_1m_acp):
     _cuda(x0, torch.float32, "original"), _cuda(noise, torch.float32, "noise"), _cuda(t, torch.int64, "t")
     x0, noise, t = x0.contiguous(), noise.contiguous(), t.contiguous()
     out = torch.empty_like(x0)
+    if x0.numel() == 0:
+        return out
     batch = x0.shape[0] if x0.dim() > 0 else 1
     per = x0.numel() // max(batch, 1)
     check(lib().b200sd_sched_add_noise(_p(x0), _p(noise), _p(t), t.numel(), _p(sqrt_acp), _p(sqrt_1m_acp),
