@@ -154,6 +154,12 @@ int b200sd_mask_cond(const float* mask, const float* w, void* dst, int64_t ld_ds
 int b200sd_copy_act(const void* src, int64_t ld_src, void* dst, int64_t ld_dst, int c_off, int64_t rows, int c,
                     int act, void* stream);
 
+/* dst[i] = bf16(src[i]) — the autocast cast of fp32 inputs (text context, utils/text_utils.py:32 output). */
+int b200sd_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
+
+/* out[i] = a[i] + b[i] on contiguous bf16 (residual add when a quantised leaf prevents epilogue fusion). */
+int b200sd_add_bf16(const void* a, const void* b, void* out, int64_t n, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,198 @@
+"""Shared implementation of the three reference UNet variants (models/unet_base.py, models/unet_cond_base.py,
+models/unet_cond_base_relu.py). Module names and creation order follow the reference so checkpoints and seeded
+initialisation are interchangeable; `forward` drives the fused sm_100a engine."""
+import torch
+import torch.nn as nn
+from einops import einsum  # noqa: F401  (kept importable for callers that star-import like the reference)
+
+import sdb200  # noqa: F401
+from sdb200 import engine as E
+from sdb200 import runtime as rt
+
+
+def get_config_value(config, key, default_value):
+    return config[key] if key in config else default_value
+
+
+def validate_class_config(condition_config):
+    assert 'class_condition_config' in condition_config, \
+        "Class conditioning desired but class condition config missing"
+    assert 'num_classes' in condition_config['class_condition_config'], \
+        "num_class missing in class condition config"
+
+
+def validate_text_config(condition_config):
+    assert 'text_condition_config' in condition_config, \
+        "Text conditioning desired but text condition config missing"
+    assert 'text_embed_dim' in condition_config['text_condition_config'], \
+        "text_embed_dim missing in text condition config"
+
+
+def validate_image_conditional_input(cond_input, x):
+    assert 'image' in cond_input, \
+        "Model initialized with image conditioning but cond_input has no image information"
+    assert cond_input['image'].shape[0] == x.shape[0], \
+        "Batch size mismatch of image condition and input"
+    assert cond_input['image'].shape[2] % x.shape[2] == 0, \
+        "Height/Width of image condition must be divisible by latent input"
+
+
+def validate_class_conditional_input(cond_input, x, num_classes):
+    assert 'class' in cond_input, \
+        "Model initialized with class conditioning but cond_input has no class information"
+    assert cond_input['class'].shape == (x.shape[0], num_classes), \
+        "Shape of class condition input must match (Batch Size, )"
+
+
+class UnetCore(nn.Module):
+    """conv_in -> DownBlocks (skips pushed before each) -> MidBlocks -> UpBlockUnets (skips popped) ->
+    GroupNorm/act/conv_out, with optional text (cross-attention), mask-image (concat) and class (time-embedding
+    add) conditioning — reference models/unet_cond_base.py:15-183 and models/unet_base.py:13-100."""
+    CONDITIONED = True
+    ACT = nn.SiLU
+
+    def _blocks(self):
+        raise NotImplementedError
+
+    def __init__(self, im_channels, model_config):
+        super().__init__()
+        Down, Mid, Up = self._blocks()
+        cfg = model_config
+        self.down_channels = cfg['down_channels']
+        self.mid_channels = cfg['mid_channels']
+        self.t_emb_dim = cfg['time_emb_dim']
+        self.down_sample = cfg['down_sample']
+        self.num_down_layers = cfg['num_down_layers']
+        self.num_mid_layers = cfg['num_mid_layers']
+        self.num_up_layers = cfg['num_up_layers']
+        self.attns = cfg['attn_down']
+        self.norm_channels = cfg['norm_channels']
+        self.num_heads = cfg['num_heads']
+        self.conv_out_channels = cfg['conv_out_channels']
+        self.im_channels = im_channels
+
+        assert self.mid_channels[0] == self.down_channels[-1]
+        assert self.mid_channels[-1] == self.down_channels[-2]
+        assert len(self.down_sample) == len(self.down_channels) - 1
+        assert len(self.attns) == len(self.down_channels) - 1
+
+        self.class_cond = self.text_cond = self.image_cond = False
+        self.text_embed_dim = None
+        self.condition_config = get_config_value(cfg, 'condition_config', None) if self.CONDITIONED else None
+        if self.condition_config is not None:
+            assert 'condition_types' in self.condition_config, 'Condition Type not provided in model config'
+            kinds = self.condition_config['condition_types']
+            if 'class' in kinds:
+                validate_class_config(self.condition_config)
+                self.class_cond = True
+                self.num_classes = self.condition_config['class_condition_config']['num_classes']
+            if 'text' in kinds:
+                validate_text_config(self.condition_config)
+                self.text_cond = True
+                self.text_embed_dim = self.condition_config['text_condition_config']['text_embed_dim']
+            if 'image' in kinds:
+                self.image_cond = True
+                icfg = self.condition_config['image_condition_config']
+                self.im_cond_input_ch = icfg['image_condition_input_channels']
+                self.im_cond_output_ch = icfg['image_condition_output_channels']
+
+        # ---- parameter creation: the order below is the reference's, variant by variant, so that a seeded
+        # construction consumes the RNG identically
+        def make_t_proj():
+            self.t_proj = nn.Sequential(nn.Linear(self.t_emb_dim, self.t_emb_dim), self.ACT(),
+                                        nn.Linear(self.t_emb_dim, self.t_emb_dim))
+
+        if self.CONDITIONED:
+            if self.class_cond:
+                self.class_emb = nn.Embedding(self.num_classes, self.t_emb_dim)
+            if self.image_cond:
+                self.cond_conv_in = nn.Conv2d(self.im_cond_input_ch, self.im_cond_output_ch, kernel_size=1, bias=False)
+                self.conv_in_concat = nn.Conv2d(im_channels + self.im_cond_output_ch, self.down_channels[0],
+                                                kernel_size=3, padding=1)
+            else:
+                self.conv_in = nn.Conv2d(im_channels, self.down_channels[0], kernel_size=3, padding=1)
+            self.cond = self.text_cond or self.image_cond or self.class_cond
+            make_t_proj()
+        else:
+            self.cond = False
+            make_t_proj()
+            self.conv_in = nn.Conv2d(im_channels, self.down_channels[0], kernel_size=3, padding=1)
+
+        self.up_sample = list(reversed(self.down_sample))
+        cross = dict(cross_attn=self.text_cond, context_dim=self.text_embed_dim) if self.CONDITIONED else {}
+        nd = len(self.down_channels) - 1
+        self.downs = nn.ModuleList([
+            Down(self.down_channels[i], self.down_channels[i + 1], self.t_emb_dim, down_sample=self.down_sample[i],
+                 num_heads=self.num_heads, num_layers=self.num_down_layers, attn=self.attns[i],
+                 norm_channels=self.norm_channels, **cross) for i in range(nd)])
+        self.mids = nn.ModuleList([
+            Mid(self.mid_channels[i], self.mid_channels[i + 1], self.t_emb_dim, num_heads=self.num_heads,
+                num_layers=self.num_mid_layers, norm_channels=self.norm_channels, **cross)
+            for i in range(len(self.mid_channels) - 1)])
+        self.ups = nn.ModuleList([
+            Up(self.down_channels[i] * 2, self.down_channels[i - 1] if i != 0 else self.conv_out_channels,
+               self.t_emb_dim, up_sample=self.down_sample[i], num_heads=self.num_heads,
+               num_layers=self.num_up_layers, norm_channels=self.norm_channels, **cross)
+            for i in reversed(range(nd))])
+        self.norm_out = nn.GroupNorm(self.norm_channels, self.conv_out_channels)
+        self.conv_out = nn.Conv2d(self.conv_out_channels, im_channels, kernel_size=3, padding=1)
+
+    # ------------------------------------------------------------------------------------------------ forward
+    def forward(self, x, t, cond_input=None):
+        if not x.is_cuda:
+            raise rt.B200Error("Unet.forward: CUDA tensors required (this package has no CPU implementation; "
+                               "the reference itself is the CPU path)")
+        if self.cond:
+            assert cond_input is not None, "Model initialized with conditioning so cond_input cannot be None"
+        n, c, h, w = x.shape
+        dev = x.device
+
+        # ---- input assembly: latent (+ mask conditioning) -> NHWC bf16, then conv_in
+        if self.image_cond:
+            validate_image_conditional_input(cond_input, x)
+            mask = cond_input['image']
+            cin = c + self.im_cond_output_ch
+            ld = (cin + 7) // 8 * 8
+            buf = torch.empty(n * h * w, ld, device=dev, dtype=torch.bfloat16)
+            rt.nchw_to_nhwc(x.float(), buf, 0)
+            if type(self.cond_conv_in) is not nn.Conv2d:
+                raise rt.B200Error("cond_conv_in: quantised leaf on the mask path is not supported yet")
+            rt.mask_cond(mask.float(), self.cond_conv_in.weight.detach().reshape(self.im_cond_output_ch, -1), buf, c,
+                         h, w)
+            out = E.conv2d(E.Act(buf, n, h, w, cin), self.conv_in_concat)
+        else:
+            out = E.conv2d(E.Act.from_nchw(x), self.conv_in)
+
+        # ---- time embedding: sinusoid -> t_proj; every block then applies act + its own Linear
+        tt = torch.as_tensor(t).to(device=dev, dtype=torch.int64).reshape(-1)
+        if tt.numel() not in (1, n):
+            raise RuntimeError(f"t has {tt.numel()} entries for batch size {n}")
+        emb = rt.time_embedding(tt, n, self.t_emb_dim, dtype=torch.bfloat16)
+        emb = E.linear(emb, self.t_proj[0], act=E._act_name(self.t_proj[1]))
+        emb = E.linear(emb, self.t_proj[2], out_dtype=torch.float32 if self.class_cond else torch.bfloat16)
+        if self.class_cond:
+            validate_class_conditional_input(cond_input, x, self.num_classes)
+            emb = emb + cond_input['class'].float() @ self.class_emb.weight.detach()
+        temb_act = E.activate_temb(emb, self.ACT)
+
+        ctx = None
+        if self.text_cond:
+            assert 'text' in cond_input, \
+                "Model initialized with text conditioning but cond_input has no text information"
+            text = cond_input['text']
+            assert text.shape[0] == n and text.shape[-1] == self.text_embed_dim
+            ctx = E.prepare_context(text)
+
+        skips = []
+        for down in self.downs:
+            skips.append(out)
+            out = down.run(out, temb_act, ctx) if self.CONDITIONED else down.run(out, temb_act)
+        for mid in self.mids:
+            out = mid.run(out, temb_act, ctx) if self.CONDITIONED else mid.run(out, temb_act)
+        for up in self.ups:
+            skip = skips.pop()
+            out = up.run(out, skip, temb_act, ctx) if self.CONDITIONED else up.run(out, skip, temb_act)
+
+        out = E.group_norm(out, self.norm_out, act=E._act_name(self.ACT()))
+        out = E.conv2d(out, self.conv_out, out_dtype=torch.float32)
+        return out.to_nchw()

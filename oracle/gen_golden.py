@@ -1,0 +1,173 @@
+"""Generate tests/golden/*.pt by running the REAL reference (/root/reference, importable only in the build
+container) on seeded inputs, and check the oracle restatements against it while doing so.
+
+    python oracle/gen_golden.py            # regenerates every fixture; exits non-zero if the oracle disagrees
+
+A fixture holds: the model config, the construction seed (weights are NOT stored: `torch.manual_seed(seed)` followed
+by constructing the module reproduces them bit-for-bit — tests/test_structure.py proves our modules consume the RNG
+exactly like the reference's), the inputs, the reference fp32 output, and for information the error of the
+reference's own bf16-autocast run against its fp32 run (the yardstick for the bf16 tolerance).
+"""
+import importlib.util
+import os
+import sys
+
+import torch
+import yaml
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = "/root/reference"
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def _load(path, name):
+    spec = importlib.util.spec_from_file_location(name, path)
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+def relerr(a, b):
+    return ((a.float() - b.float()).abs().max() / b.float().abs().max()).item()
+
+
+SMALL_COND = {
+    'down_channels': [64, 128, 192, 256], 'mid_channels': [256, 192], 'down_sample': [True, True, True],
+    'attn_down': [True, True, True], 'time_emb_dim': 128, 'norm_channels': 16, 'num_heads': 8,
+    'conv_out_channels': 64, 'num_down_layers': 2, 'num_mid_layers': 2, 'num_up_layers': 2,
+    'condition_config': {
+        'condition_types': ['text', 'image'],
+        'text_condition_config': {'text_embed_model': 'clip', 'train_text_embed_model': False, 'text_embed_dim': 128,
+                                  'cond_drop_prob': 0.1},
+        'image_condition_config': {'image_condition_input_channels': 18, 'image_condition_output_channels': 3,
+                                   'image_condition_h': 64, 'image_condition_w': 64, 'cond_drop_prob': 0.1}}}
+SMALL_UNCOND = {k: v for k, v in SMALL_COND.items() if k != 'condition_config'}
+SMALL_UNCOND['attn_down'] = [True, False, True]
+SMALL_UNCOND['down_sample'] = [True, True, False]
+
+
+def make_inputs(seed, batch, cfg, hw=32, ctx_len=77):
+    """Synthetic inputs of SURVEY §8d: latents N(0,1), t ~ U[0,1000), text N(0,1), mask one-hot of a random class
+    map with the background class dropped (stored compactly as the uint8 class map)."""
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(batch, 4, hw, hw, generator=g)
+    t = torch.randint(0, 1000, (batch,), generator=g)
+    out = {"x": x, "t": t}
+    cc = cfg.get('condition_config')
+    if cc:
+        if 'text' in cc['condition_types']:
+            out["text"] = torch.randn(batch, ctx_len, cc['text_condition_config']['text_embed_dim'], generator=g)
+        if 'image' in cc['condition_types']:
+            ic = cc['image_condition_config']
+            out["mask_classes"] = torch.randint(0, ic['image_condition_input_channels'] + 1,
+                                                (batch, ic['image_condition_h'], ic['image_condition_w']),
+                                                generator=g).to(torch.uint8)
+    return out
+
+
+def expand_mask(classes, channels):
+    """dataset/celeb_dataset.py:172-179: one-hot over channels+1 classes, background (class 0) dropped."""
+    oh = torch.nn.functional.one_hot(classes.long(), channels + 1)[..., 1:]
+    return oh.permute(0, 3, 1, 2).float().contiguous()
+
+
+def cond_of(inp, cfg):
+    cc = cfg.get('condition_config')
+    if not cc:
+        return None
+    c = {}
+    if "text" in inp:
+        c["text"] = inp["text"]
+    if "mask_classes" in inp:
+        c["image"] = expand_mask(inp["mask_classes"], cc['image_condition_config']['image_condition_input_channels'])
+    return c
+
+
+def main():
+    sys.path.insert(0, REF)
+    from models.unet_cond_base import Unet as RefCond
+    from models.unet_base import Unet as RefUncond
+    from models.unet_cond_base_relu import Unet as RefCondRelu
+    from models.vqvae import VQVAE as RefVQVAE
+    sys.path.pop(0)
+    O = _load(os.path.join(ROOT, "oracle", "unet_torch.py"), "oracle_unet_torch")
+    os.makedirs(GOLD, exist_ok=True)
+    full_cond = yaml.safe_load(open(os.path.join(REF, "config/celebhq_text_image_cond.yaml")))
+    full_uncond = yaml.safe_load(open(os.path.join(REF, "config/celebhq.yaml")))
+    cases = [
+        ("unet_small_cond", RefCond, SMALL_COND, 3, False),
+        ("unet_small_uncond", RefUncond, SMALL_UNCOND, 2, False),
+        ("unet_small_cond_relu", RefCondRelu, SMALL_COND, 2, True),
+        ("unet_full_cond", RefCond, full_cond['ldm_params'], 2, False),
+        ("unet_full_uncond", RefUncond, full_uncond['ldm_params'], 2, False),
+    ]
+    ok = True
+    for name, cls, cfg, batch, relu in cases:
+        seed = 1111
+        torch.manual_seed(seed)
+        model = cls(4, cfg).eval()
+        inp = make_inputs(seed + 1, batch, cfg)
+        cond = cond_of(inp, cfg)
+        with torch.no_grad():
+            args = (inp["x"], inp["t"]) + ((cond,) if cond is not None else ())
+            ref = model(*args)
+            model.train()  # train-mode MHA takes the non-fused path (SURVEY §8c trap ii): must agree
+            ref_train = model(*args)
+            model.eval()
+            with torch.autocast("cpu", dtype=torch.bfloat16):
+                ref_bf16 = model(*args).float()
+            orc = O.unet_forward(model.state_dict(), cfg, inp["x"], inp["t"], cond, relu=relu)
+        e_or, e_tr, e_bf = relerr(orc, ref), relerr(ref_train, ref), relerr(ref_bf16, ref)
+        print(f"{name}: oracle-vs-ref {e_or:.2e}  ref train-vs-eval {e_tr:.2e}  ref bf16-autocast-vs-fp32 {e_bf:.2e}")
+        ok &= e_or < 1e-5
+        torch.save({"config": cfg, "seed": seed, "relu": relu, "inputs": inp, "output": ref,
+                    "ref_bf16_autocast_relerr": e_bf}, os.path.join(GOLD, name + ".pt"))
+
+    # VQVAE decoder
+    acfg = full_uncond['autoencoder_params']
+    torch.manual_seed(1111)
+    vae = RefVQVAE(3, acfg).eval()
+    z = torch.randn(1, 4, 32, 32, generator=torch.Generator().manual_seed(5))
+    with torch.no_grad():
+        ref = vae.decode(z)
+        orc = O.vqvae_decode(vae.state_dict(), acfg, z)
+        with torch.autocast("cpu", dtype=torch.bfloat16):
+            ref_bf16 = vae.decode(z).float()
+    e_or, e_bf = relerr(orc, ref), relerr(ref_bf16, ref)
+    print(f"vqvae_decode: oracle-vs-ref {e_or:.2e}  ref bf16-autocast-vs-fp32 {e_bf:.2e}")
+    ok &= e_or < 1e-5
+    torch.save({"config": acfg, "seed": 1111, "inputs": {"z": z}, "output": ref.to(torch.float16),
+                "ref_bf16_autocast_relerr": e_bf}, os.path.join(GOLD, "vqvae_decode.pt"))
+
+    # scheduler: outputs of the reference class itself
+    sys.path.insert(0, REF)
+    from scheduler.linear_noise_scheduler import LinearNoiseScheduler as RefSched
+    sys.path.pop(0)
+    import numpy as np
+    fx = {}
+    for T, b0, b1 in [(1000, 0.00085, 0.012), (1000, 0.0015, 0.0195)]:
+        s = RefSched(T, b0, b1)
+        g = torch.Generator().manual_seed(T + int(b0 * 1e6))
+        x, n = torch.randn(4, 4, 32, 32, generator=g), torch.randn(4, 4, 32, 32, generator=g)
+        t = torch.tensor([0, 1, 500, T - 1])
+        key = f"T{T}_b{b0}"
+        fx[key + "_x"], fx[key + "_n"], fx[key + "_t"] = x.numpy(), n.numpy(), t.numpy()
+        fx[key + "_add_noise"] = s.add_noise(x, n, t).numpy()
+        for step in [T - 1, 500, 1, 0]:
+            torch.manual_seed(step)
+            xp, x0 = s.sample_prev_timestep(x, n, torch.as_tensor(step))
+            torch.manual_seed(step)
+            z = torch.randn(x.shape)
+            fx[f"{key}_prev{step}_z"], fx[f"{key}_prev{step}_xp"], fx[f"{key}_prev{step}_x0"] = \
+                z.numpy(), xp.numpy(), x0.numpy()
+        fx[key + "_betas"] = s.betas.numpy()
+        fx[key + "_acp"] = s.alpha_cum_prod.numpy()
+    np.savez_compressed(os.path.join(GOLD, "scheduler.npz"), **fx)
+    print("scheduler fixtures written")
+    if not ok:
+        print("ORACLE DISAGREES WITH THE REFERENCE")
+        sys.exit(1)
+
+
+if __name__ == "__main__":
+    main()

@@ -101,6 +101,39 @@ __global__ void copy_act_kernel(const __nv_bfloat16* __restrict__ src, long long
     }
 }
 
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n4,
+                                     long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4;
+         i += (long long)gridDim.x * blockDim.x) {
+        float4 f = reinterpret_cast<const float4*>(src)[i];
+        uint2 u;
+        *reinterpret_cast<__nv_bfloat162*>(&u.x) = __floats2bfloat162_rn(f.x, f.y);
+        *reinterpret_cast<__nv_bfloat162*>(&u.y) = __floats2bfloat162_rn(f.z, f.w);
+        reinterpret_cast<uint2*>(dst)[i] = u;
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+        const long long j = (n & ~3ll) + threadIdx.x;
+        dst[j] = __float2bfloat16_rn(src[j]);
+    }
+}
+
+__global__ void add_bf16_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ o,
+                                long long n8) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8;
+         i += (long long)gridDim.x * blockDim.x) {
+        uint4 x = a[i], y = b[i], r;
+        const __nv_bfloat162* hx = reinterpret_cast<const __nv_bfloat162*>(&x);
+        const __nv_bfloat162* hy = reinterpret_cast<const __nv_bfloat162*>(&y);
+        __nv_bfloat162* hr = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float2 fx = __bfloat1622float2(hx[j]), fy = __bfloat1622float2(hy[j]);
+            hr[j] = __floats2bfloat162_rn(fx.x + fy.x, fx.y + fy.y);
+        }
+        o[i] = r;
+    }
+}
+
 static inline int glue_grid(long long items, int threads) {
     long long b = (items + threads - 1) / threads;
     long long cap = (long long)sm_count() * 8;
@@ -167,5 +200,28 @@ extern "C" int b200sd_copy_act(const void* src, int64_t ld_src, void* dst, int64
         static_cast<const __nv_bfloat16*>(src), ld_src, static_cast<__nv_bfloat16*>(dst), ld_dst, c_off, rows, c, act,
         vec);
     B200_CHECK_LAUNCH("copy_act");
+    return B200SD_OK;
+}
+
+extern "C" int b200sd_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream) {
+    B200_REQUIRE(src && dst, "cast: null pointer");
+    B200_REQUIRE(((reinterpret_cast<uintptr_t>(src) & 15) == 0) && ((reinterpret_cast<uintptr_t>(dst) & 7) == 0),
+                 "cast: pointers unaligned");
+    if (n == 0) return B200SD_OK;
+    cast_f32_bf16_kernel<<<glue_grid((n + 3) / 4, 256), 256, 0, as_stream(stream)>>>(
+        src, static_cast<__nv_bfloat16*>(dst), n / 4, n);
+    B200_CHECK_LAUNCH("cast_f32_bf16");
+    return B200SD_OK;
+}
+
+extern "C" int b200sd_add_bf16(const void* a, const void* b, void* out, int64_t n, void* stream) {
+    B200_REQUIRE(a && b && out, "add: null pointer");
+    B200_REQUIRE(n % 8 == 0, "add: element count %lld is not a multiple of 8", (long long)n);
+    B200_REQUIRE(((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(out)) & 15) == 0,
+                 "add: pointers unaligned");
+    if (n == 0) return B200SD_OK;
+    add_bf16_kernel<<<glue_grid(n / 8, 256), 256, 0, as_stream(stream)>>>(
+        static_cast<const uint4*>(a), static_cast<const uint4*>(b), static_cast<uint4*>(out), n / 8);
+    B200_CHECK_LAUNCH("add_bf16");
     return B200SD_OK;
 }

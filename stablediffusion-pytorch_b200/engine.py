@@ -1,0 +1,287 @@
+"""Fused execution engine: runs the reference's block structure on the sm_100a kernels.
+
+The engine never owns a model definition. It reads the LIVE torch module tree every call (leaf types, channel
+counts, parameters) so that callers which swap leaves — the cim_qn_train module surgery, SURVEY §7 "the callers do
+module surgery" — change what executes. Leaves of exact type nn.Conv2d / nn.Linear / nn.GroupNorm /
+nn.MultiheadAttention run on the fused kernels; a leaf exposing `forward_act(act)` (the cim_layers drop-ins)
+supplies its own CUDA path; anything else is an error (there is no PyTorch fallback).
+
+Activations travel as `Act`: NHWC bf16, a 2-D [n*h*w, ld] tensor — the conv "pixel x channel" matrix and the
+attention (B, L, C) token matrix are the same memory, so no transposes exist anywhere on the path
+(the reference does reshape/transpose round trips around every attention, blocks.py:125-131).
+"""
+import weakref
+
+import torch
+import torch.nn as nn
+
+from . import ops
+from . import runtime as rt
+
+
+class Act:
+    __slots__ = ("t", "n", "h", "w", "c")
+
+    def __init__(self, t, n, h, w, c):
+        self.t, self.n, self.h, self.w, self.c = t, n, h, w, c
+
+    @property
+    def ld(self):
+        return self.t.stride(0)
+
+    @property
+    def hw(self):
+        return self.h * self.w
+
+    @staticmethod
+    def empty(n, h, w, c, device):
+        return Act(torch.empty(n * h * w, c, device=device, dtype=torch.bfloat16), n, h, w, c)
+
+    @staticmethod
+    def from_nchw(x):
+        n, c, h, w = x.shape
+        ld = (c + 7) // 8 * 8
+        a = Act(torch.empty(n * h * w, ld, device=x.device, dtype=torch.bfloat16), n, h, w, c)
+        if ld != c:
+            a.t.zero_()
+        rt.nchw_to_nhwc(x.float(), a.t, 0)
+        return a
+
+    def to_nchw(self):
+        return rt.nhwc_to_nchw(self.t, self.n, self.c, self.h, self.w, ld=self.ld)
+
+
+# ------------------------------------------------------------------------------------------ packed-weight cache
+class _Cache:
+    """Repacked (bf16, K-major) weights per leaf module, invalidated when any source parameter is modified in
+    place (tensor._version) or replaced (data_ptr)."""
+
+    def __init__(self):
+        self._d = weakref.WeakKeyDictionary()
+
+    def get(self, mod, key, params, build):
+        stamp = tuple((p.data_ptr(), p._version) for p in params if p is not None)
+        slot = self._d.setdefault(mod, {})
+        hit = slot.get(key)
+        if hit is not None and hit[0] == stamp:
+            return hit[1]
+        with torch.no_grad():
+            val = build()
+        slot[key] = (stamp, val)
+        return val
+
+
+CACHE = _Cache()
+
+
+def _f32(p):
+    return None if p is None else p.detach()
+
+
+def _require_leaf(mod, kinds, what):
+    if type(mod) not in kinds:
+        raise rt.B200Error(f"{what}: no CUDA path for leaf of type {type(mod).__module__}.{type(mod).__name__}")
+
+
+def _act_name(m):
+    if isinstance(m, nn.SiLU):
+        return "silu"
+    if isinstance(m, nn.ReLU):
+        return "relu"
+    if isinstance(m, nn.Identity):
+        return None
+    raise rt.B200Error(f"unsupported activation module {type(m).__name__}")
+
+
+# ------------------------------------------------------------------------------------------ leaf operators
+def group_norm(a, mod, act=None):
+    _require_leaf(mod, (nn.GroupNorm,), "GroupNorm")
+    out = Act.empty(a.n, a.h, a.w, a.c, a.t.device)
+    rt.groupnorm(a.t, a.n, a.hw, a.c, mod.num_groups, _f32(mod.weight), _f32(mod.bias), mod.eps, act=act, out=out.t,
+                 ld_x=a.ld, ld_y=a.c)
+    return out
+
+
+def conv2d(a, mod, rowbias=None, extra=None, act=None, out=None, c_off=0, out_dtype=torch.bfloat16):
+    """nn.Conv2d leaf on an Act. `extra` = (Act, 1x1 nn.Conv2d) fuses a second 1x1 convolution of another tensor
+    into the same accumulator (ResNet shortcut)."""
+    if hasattr(mod, "forward_act") and extra is None and rowbias is None:
+        return mod.forward_act(a)
+    _require_leaf(mod, (nn.Conv2d,), "Conv2d")
+    k, s, p = mod.kernel_size, mod.stride, mod.padding
+    if mod.groups != 1 or mod.dilation != (1, 1):
+        raise rt.B200Error("Conv2d: groups/dilation are not supported")
+    cout = mod.out_channels
+    if k in ((3, 3), (1, 1)) and s == (1, 1) and p == (k[0] // 2, k[0] // 2):
+        if extra is None:
+            wmat = CACHE.get(mod, "w", (mod.weight,), lambda: ops.pack_conv_weight(mod.weight))
+            bias = _f32(mod.bias)
+            ex = None
+        else:
+            xa, xm = extra
+            _require_leaf(xm, (nn.Conv2d,), "Conv2d(shortcut)")
+            if xm.kernel_size != (1, 1) or xm.stride != (1, 1):
+                raise rt.B200Error("fused shortcut must be a 1x1 stride-1 convolution")
+            wmat = CACHE.get(mod, "w+res", (mod.weight, xm.weight), lambda: torch.cat(
+                [ops.pack_conv_weight(mod.weight), ops.pack_conv_weight(xm.weight)], dim=1).contiguous())
+            bias = CACHE.get(mod, "b+res", (mod.bias, xm.bias), lambda: (
+                (mod.bias if mod.bias is not None else 0) + (xm.bias if xm.bias is not None else 0)).float().contiguous())
+            ex = (xa.t, xa.c, xa.ld)
+        if out is None:
+            o = torch.empty(a.n * a.hw, cout, device=a.t.device, dtype=out_dtype)
+        else:
+            o = out.t
+        ops.conv_same(a.t, a.n, a.h, a.w, a.c, wmat, cout, k[0], bias=bias, ld_x=a.ld, out=o, c_off=c_off,
+                      rowbias=rowbias, act=act, extra=ex)
+        return out if out is not None else Act(o, a.n, a.h, a.w, cout)
+    if k == (4, 4) and s == (2, 2) and p == (1, 1) and extra is None and rowbias is None:
+        if a.h % 2 or a.w % 2:
+            raise rt.B200Error("4x4 stride-2 convolution needs even spatial size")
+        wmat = CACHE.get(mod, "w", (mod.weight,), lambda: ops.pack_conv_weight(mod.weight))
+        o = Act.empty(a.n, a.h // 2, a.w // 2, cout, a.t.device) if out is None else out
+        ops.conv_down4x4(a.t, a.n, a.h, a.w, a.c, wmat, cout, bias=_f32(mod.bias), ld_x=a.ld, out=o.t)
+        return o
+    raise rt.B200Error(f"Conv2d: kernel {k} stride {s} padding {p} has no CUDA path")
+
+
+def conv_transpose2d(a, mod, out=None, c_off=0):
+    _require_leaf(mod, (nn.ConvTranspose2d,), "ConvTranspose2d")
+    if mod.kernel_size != (4, 4) or mod.stride != (2, 2) or mod.padding != (1, 1) or mod.output_padding != (0, 0):
+        raise rt.B200Error("ConvTranspose2d: only kernel 4 stride 2 padding 1 has a CUDA path")
+    phases = CACHE.get(mod, "w", (mod.weight,), lambda: ops.pack_convT_weight(mod.weight))
+    cout = mod.out_channels
+    o = Act.empty(a.n, 2 * a.h, 2 * a.w, cout, a.t.device) if out is None else out
+    ops.conv_up4x4(a.t, a.n, a.h, a.w, a.c, phases, cout, bias=_f32(mod.bias), ld_x=a.ld, out=o.t, c_off=c_off)
+    return o
+
+
+def linear(x, mod, act=None, residual=None, out_dtype=torch.bfloat16, rows_per_img=None, rowbias=None, gate=None):
+    """nn.Linear leaf on a 2-D bf16 matrix."""
+    if hasattr(mod, "forward_rows") and residual is None and gate is None and rowbias is None:
+        return mod.forward_rows(x, act=act)
+    _require_leaf(mod, (nn.Linear, nn.modules.linear.NonDynamicallyQuantizableLinear), "Linear")
+    wmat = CACHE.get(mod, "w", (mod.weight,), lambda: ops.pack_linear_weight(mod.weight))
+    return rt.linear(x, wmat, bias=_f32(mod.bias), act=act, residual=residual, out_dtype=out_dtype,
+                     rows_per_img=rows_per_img, rowbias=rowbias, gate=gate)
+
+
+def _mha_weights(mha):
+    """(w_q, b_q, w_kv, b_kv, w_qkv, b_qkv, out_proj) for nn.MultiheadAttention (packed in_proj, blocks.py:83) or
+    the reference's CustomMultiheadAttention (separate q/k/v Linear, models/multihead_attention.py:34-37)."""
+    if isinstance(mha, nn.MultiheadAttention):
+        if mha.in_proj_weight is None:
+            raise rt.B200Error("MultiheadAttention with kdim/vdim != embed_dim has no CUDA path")
+        w, b = mha.in_proj_weight, mha.in_proj_bias
+        srcs = (w, b)
+        get_w = lambda: w
+        get_b = lambda: b
+    elif all(hasattr(mha, k) for k in ("q_proj", "k_proj", "v_proj", "out_proj")):
+        for k in ("q_proj", "k_proj", "v_proj"):
+            _require_leaf(getattr(mha, k), (nn.Linear,), f"attention {k}")
+        ws = [mha.q_proj.weight, mha.k_proj.weight, mha.v_proj.weight]
+        bs = [mha.q_proj.bias, mha.k_proj.bias, mha.v_proj.bias]
+        srcs = tuple(ws + bs)
+        get_w = lambda: torch.cat(ws, 0)
+        get_b = lambda: None if bs[0] is None else torch.cat(bs, 0)
+    else:
+        raise rt.B200Error(f"attention module {type(mha).__name__} has no CUDA path")
+
+    def build():
+        w, b = get_w(), get_b()
+        C = w.shape[1]
+        bf = None if b is None else b.float().contiguous()
+        return {
+            "qkv": ops.pack_linear_weight(w), "b_qkv": bf,
+            "q": ops.pack_linear_weight(w[:C]), "b_q": None if bf is None else bf[:C].contiguous(),
+            "kv": ops.pack_linear_weight(w[C:]), "b_kv": None if bf is None else bf[C:].contiguous(),
+        }
+
+    return CACHE.get(mha, "in_proj", srcs, build)
+
+
+def self_attention(a, norm, mha):
+    """x + out_proj(MHA(GN(x))) — blocks.py:122-131. One QKV GEMM, flash attention, out-proj GEMM with the residual
+    add in its epilogue."""
+    C, heads = a.c, mha.num_heads
+    xn = group_norm(a, norm)
+    pk = _mha_weights(mha)
+    qkv = rt.linear(xn.t, pk["qkv"], bias=pk["b_qkv"])
+    o = rt.attention(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], a.n, heads, a.hw, a.hw, C // heads)
+    out = linear(o, mha.out_proj, residual=a.t)
+    return Act(out, a.n, a.h, a.w, C)
+
+
+def cross_attention(a, norm, mha, ctx_proj_mod, ctx, lk):
+    """x + out_proj(MHA(q=GN(x), k=v=context_proj(ctx))) — blocks.py:133-145. ctx: bf16 [n*lk, ctx_dim]."""
+    C, heads = a.c, mha.num_heads
+    xn = group_norm(a, norm)
+    pk = _mha_weights(mha)
+    q = rt.linear(xn.t, pk["q"], bias=pk["b_q"])
+    cp = linear(ctx, ctx_proj_mod)
+    kv = rt.linear(cp, pk["kv"], bias=pk["b_kv"])
+    o = rt.attention(q, kv[:, :C], kv[:, C:], a.n, heads, a.hw, lk, C // heads)
+    out = linear(o, mha.out_proj, residual=a.t)
+    return Act(out, a.n, a.h, a.w, C)
+
+
+def resnet(a, first, temb_layer, second, shortcut, temb_act):
+    """GN-act-conv3x3 (+ time-embedding row bias) -> GN-act-conv3x3 + 1x1 shortcut of the block input, the shortcut
+    fused into the second conv's accumulator — blocks.py:113-119. `first`/`second` are the reference's
+    nn.Sequential(GroupNorm, activation, Conv2d); temb_layer is nn.Sequential(activation, Linear) or None."""
+    act = _act_name(first[1])
+    h = group_norm(a, first[0], act=act)
+    rowbias = None
+    if temb_layer is not None:
+        rowbias = linear(temb_act, temb_layer[1])
+    h = conv2d(h, first[2], rowbias=rowbias)
+    h = group_norm(h, second[0], act=_act_name(second[1]))
+    if type(second[2]) is nn.Conv2d and type(shortcut) is nn.Conv2d:
+        return conv2d(h, second[2], extra=(a, shortcut))
+    # quantised leaves: run the two convolutions separately and add
+    h = conv2d(h, second[2])
+    s = conv2d(a, shortcut)
+    return add(h, s)
+
+
+def add(a, b):
+    out = Act.empty(a.n, a.h, a.w, a.c, a.t.device)
+    rt.add_bf16(a.t, b.t, out.t)
+    return out
+
+
+def activate_temb(t_emb, act_cls):
+    """act(t_emb) as bf16 [B, D]: the shared first half of every block's t_emb_layers (blocks.py:57-62)."""
+    src = t_emb if t_emb.dtype == torch.bfloat16 else rt.cast_bf16(t_emb.float())
+    out = torch.empty_like(src)
+    rt.copy_act(src, out, 0, act=_act_name(act_cls()))
+    return out
+
+
+def prepare_context(context):
+    """(B, L, D) fp32 text context -> (bf16 [B*L, D], L, D): the autocast cast, done once per forward instead of
+    once per cross-attention site."""
+    b, l, d = context.shape
+    if d % 8:
+        raise rt.B200Error("context dimension must be a multiple of 8")
+    t = context if context.dtype == torch.bfloat16 else rt.cast_bf16(context.float())
+    return t.reshape(b * l, d), l, d
+
+
+def upsample_concat(a, up_conv, skip):
+    """x = up_sample_conv(x); x = cat([x, out_down], dim=1) — blocks.py:461-464. The transposed convolution writes
+    straight into the left channel slice of the concat buffer; the skip tensor is copied into the right slice."""
+    if up_conv is None and skip is None:
+        return a
+    h, w = (2 * a.h, 2 * a.w) if up_conv is not None else (a.h, a.w)
+    c_up = up_conv.out_channels if up_conv is not None else a.c
+    c_tot = c_up + (skip.c if skip is not None else 0)
+    if skip is not None and (skip.h, skip.w, skip.n) != (h, w, a.n):
+        raise rt.B200Error("skip tensor shape does not match the upsampled tensor")
+    out = Act.empty(a.n, h, w, c_tot, a.t.device)
+    if up_conv is not None:
+        conv_transpose2d(a, up_conv, out=out, c_off=0)
+    else:
+        rt.copy_act(a.t, out.t, 0)
+    if skip is not None:
+        rt.copy_act(skip.t[:, :skip.c] if skip.ld != skip.c else skip.t, out.t, c_up)
+    return out

@@ -18,7 +18,7 @@ _ACT = {None: 0, "none": 0, "silu": 1, "relu": 2}
 EXPORTS = [
     "b200sd_last_error", "b200sd_version", "b200sd_launch_count", "b200sd_sched_add_noise",
     "b200sd_sched_prev_step", "b200sd_time_embedding", "b200sd_igemm", "b200sd_groupnorm", "b200sd_attention",
-    "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act",
+    "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16",
 ]
 
 
@@ -72,6 +72,8 @@ def lib():
         L.b200sd_nhwc_to_nchw.argtypes = [vp, i32, i64, vp, i64, i32, i64, vp]
         L.b200sd_mask_cond.argtypes = [vp, vp, vp, i64, i32, i64, i32, i32, i32, i32, i32, i32, vp]
         L.b200sd_copy_act.argtypes = [vp, i64, vp, i64, i32, i64, i32, i32, vp]
+        L.b200sd_cast_f32_bf16.argtypes = [vp, vp, i64, vp]
+        L.b200sd_add_bf16.argtypes = [vp, vp, vp, i64, vp]
         _lib = L
     return _lib
 
@@ -266,3 +268,16 @@ def copy_act(src, dst, c_off=0, act=None):
     check(lib().b200sd_copy_act(_p(src), src.stride(0), _p(dst), dst.stride(0), c_off, rows, c, _ACT[act],
                                  stream_ptr()), "copy_act")
     return dst
+
+
+def cast_bf16(src):
+    _cuda(src, torch.float32, "src")
+    src = src.contiguous()
+    out = torch.empty(src.shape, device=src.device, dtype=torch.bfloat16)
+    check(lib().b200sd_cast_f32_bf16(_p(src), _p(out), src.numel(), stream_ptr()), "cast_f32_bf16")
+    return out
+
+
+def add_bf16(a, b, out):
+    check(lib().b200sd_add_bf16(_p(a), _p(b), _p(out), a.numel(), stream_ptr()), "add_bf16")
+    return out

@@ -1,0 +1,33 @@
+import os
+
+import torch
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def relerr(a, b):
+    """max |a-b| / max |b|: the 'max relative error' of the parity gate (per-element ratios diverge at zeros)."""
+    return ((a.float() - b.float()).abs().max() / b.float().abs().max().clamp_min(1e-30)).item()
+
+
+def load_golden(name):
+    return torch.load(os.path.join(GOLD, name + ".pt"), weights_only=False)
+
+
+def expand_mask(classes, channels):
+    oh = torch.nn.functional.one_hot(classes.long(), channels + 1)[..., 1:]
+    return oh.permute(0, 3, 1, 2).float().contiguous()
+
+
+def cond_of(inp, cfg, device=None):
+    cc = cfg.get('condition_config')
+    if not cc:
+        return None
+    c = {}
+    if "text" in inp:
+        c["text"] = inp["text"]
+    if "mask_classes" in inp:
+        c["image"] = expand_mask(inp["mask_classes"], cc['image_condition_config']['image_condition_input_channels'])
+    if device is not None:
+        c = {k: v.to(device) for k, v in c.items()}
+    return c
