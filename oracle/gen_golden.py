@@ -31,6 +31,10 @@ def relerr(a, b):
     return ((a.float() - b.float()).abs().max() / b.float().abs().max()).item()
 
 
+def l2err(a, b):
+    return ((a.float() - b.float()).norm() / b.float().norm()).item()
+
+
 SMALL_COND = {
     'down_channels': [64, 128, 192, 256], 'mid_channels': [256, 192], 'down_sample': [True, True, True],
     'attn_down': [True, True, True], 'time_emb_dim': 128, 'norm_channels': 16, 'num_heads': 8,
@@ -120,8 +124,10 @@ def main():
         e_or, e_tr, e_bf = relerr(orc, ref), relerr(ref_train, ref), relerr(ref_bf16, ref)
         print(f"{name}: oracle-vs-ref {e_or:.2e}  ref train-vs-eval {e_tr:.2e}  ref bf16-autocast-vs-fp32 {e_bf:.2e}")
         ok &= e_or < 1e-5
+        print(f"    rel-L2: ref bf16-autocast-vs-fp32 {l2err(ref_bf16, ref):.2e}")
         torch.save({"config": cfg, "seed": seed, "relu": relu, "inputs": inp, "output": ref,
-                    "ref_bf16_autocast_relerr": e_bf}, os.path.join(GOLD, name + ".pt"))
+                    "ref_bf16_autocast_relerr": e_bf, "ref_bf16_autocast_l2err": l2err(ref_bf16, ref)},
+                   os.path.join(GOLD, name + ".pt"))
 
     # VQVAE decoder
     acfg = full_uncond['autoencoder_params']
@@ -137,7 +143,8 @@ def main():
     print(f"vqvae_decode: oracle-vs-ref {e_or:.2e}  ref bf16-autocast-vs-fp32 {e_bf:.2e}")
     ok &= e_or < 1e-5
     torch.save({"config": acfg, "seed": 1111, "inputs": {"z": z}, "output": ref.to(torch.float16),
-                "ref_bf16_autocast_relerr": e_bf}, os.path.join(GOLD, "vqvae_decode.pt"))
+                "ref_bf16_autocast_relerr": e_bf, "ref_bf16_autocast_l2err": l2err(ref_bf16, ref)},
+               os.path.join(GOLD, "vqvae_decode.pt"))
 
     # scheduler: outputs of the reference class itself
     sys.path.insert(0, REF)

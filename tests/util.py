@@ -10,6 +10,10 @@ def relerr(a, b):
     return ((a.float() - b.float()).abs().max() / b.float().abs().max().clamp_min(1e-30)).item()
 
 
+def l2err(a, b):
+    return ((a.float() - b.float()).norm() / b.float().norm().clamp_min(1e-30)).item()
+
+
 def load_golden(name):
     return torch.load(os.path.join(GOLD, name + ".pt"), weights_only=False)
 
