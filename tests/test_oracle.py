@@ -1,0 +1,57 @@
+"""The oracle restatements against the committed outputs of the REAL reference (tests/golden, made by
+oracle/gen_golden.py in the build container). CPU only."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import scheduler_np as onp
+from oracle import unet_torch as O
+from util import GOLD, cond_of, load_golden, relerr
+
+
+def test_scheduler_oracle_bit_exact_vs_reference_outputs():
+    fx = np.load(os.path.join(GOLD, "scheduler.npz"))
+    for T, b0, b1 in [(1000, 0.00085, 0.012), (1000, 0.0015, 0.0195)]:
+        key = f"T{T}_b{b0}"
+        tb = onp.make_tables(T, b0, b1)
+        assert np.array_equal(tb["betas"], fx[key + "_betas"])
+        assert np.array_equal(tb["alpha_cum_prod"], fx[key + "_acp"])
+        x, n, t = fx[key + "_x"], fx[key + "_n"], fx[key + "_t"]
+        assert np.array_equal(onp.add_noise(tb, x, n, t), fx[key + "_add_noise"])
+        for step in [T - 1, 500, 1, 0]:
+            xp, x0 = onp.sample_prev_timestep(tb, x, n, step, fx[f"{key}_prev{step}_z"])
+            assert np.array_equal(xp, fx[f"{key}_prev{step}_xp"]), step
+            assert np.array_equal(x0, fx[f"{key}_prev{step}_x0"]), step
+
+
+def _product_cls(name, relu):
+    if "uncond" in name:
+        from models.unet_base import Unet
+    elif relu:
+        from models.unet_cond_base_relu import Unet
+    else:
+        from models.unet_cond_base import Unet
+    return Unet
+
+
+@pytest.mark.parametrize("name", ["unet_small_cond", "unet_small_uncond", "unet_small_cond_relu", "unet_full_cond"])
+def test_unet_oracle_vs_reference_golden(name):
+    """Weights come from constructing the PRODUCT module under the fixture seed — so this also proves the product's
+    parameter creation order equals the reference's (any difference would change every weight)."""
+    fx = load_golden(name)
+    torch.manual_seed(fx["seed"])
+    model = _product_cls(name, fx["relu"])(4, fx["config"])
+    inp = fx["inputs"]
+    with torch.no_grad():
+        out = O.unet_forward(model.state_dict(), fx["config"], inp["x"], inp["t"], cond_of(inp, fx["config"]),
+                             relu=fx["relu"])
+    assert relerr(out, fx["output"]) < 1e-5  # fp32 vs fp32: summation-order noise only
+
+
+def test_time_embedding_oracles_agree():
+    t = torch.tensor([0, 3, 999])
+    a = O.time_embedding(t, 512).numpy()
+    b = onp.time_embedding(t.numpy(), 512)
+    assert np.abs(a - b).max() < 1e-4
