@@ -1,0 +1,414 @@
+"""bench.py — DDPM sampling throughput of the text+mask conditioned LDM UNet (BASELINE.json configs[1]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--cfg S] [--impl ours|reference]
+
+Workload: the reference's `config/celebhq_text_image_cond.yaml` UNet (118.5 M parameters,
+random init, seed 1111), batch 64 latents (4x32x32) per GPU, synthetic CLIP-shaped text context (B,77,512) and one-hot
+mask (B,18,512,512); ancestral DDPM sampling over T=1000 timesteps followed by one VQVAE decode to 3x256x256.
+
+A *step* is one DDPM timestep of the whole per-GPU batch: UNet forward (+ a second, unconditional forward when
+--cfg > 1) -> sample_prev_timestep. K steps are timed with CUDA events; with the default K = 1000 the timed region is
+literally the whole job (t = 999..0 and the VQVAE decode). For other K the images/s figure is
+B / (1000 * t_step + t_decode) with both terms measured in the same run (stated in config.extrapolated).
+
+    value : inputs resident in HBM, the device-resident loop (one CUDA-graph replay per timestep)
+    e2e   : the reference-facing drop-in calls `model(xt, t, cond_input)` + `scheduler.sample_prev_timestep(...)`
+            + `vae.decode(xt)` from pinned HOST buffers (H2D of latents/text/mask, per-step D2H of the x0 preview the
+            reference script saves every step, D2H of the decoded images) inside the timed region
+
+Multi-GPU (torchrun): the latent batch is sharded, B per rank, no collective on the data path (weak scaling);
+time = max over ranks.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+T_STEPS = 1000
+SEED = 1111
+# algorithmic forward FLOPs per sample (FlopCounterMode on the reference modules)
+UNET_GFLOP = 40.59
+VQVAE_DECODE_GFLOP = 99.2
+
+
+def load_cfg():
+    """Model configs come from the committed golden fixtures (they embed the reference YAML sections), because
+    /root/reference does not exist on the GPU box."""
+    g = os.path.join(ROOT, "tests", "golden")
+    unet = torch.load(os.path.join(g, "unet_full_cond.pt"), weights_only=False)["config"]
+    vae = torch.load(os.path.join(g, "vqvae_decode.pt"), weights_only=False)["config"]
+    return unet, vae
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "tf_burst": d["bf16_tflops"], "tf_sustained": d["bf16_tflops_sustained"],
+                "src": "measured"}
+    return {"hbm_gbs": 6650.0, "tf_burst": 1590.0, "tf_sustained": 1400.0, "src": "fallback"}
+
+
+def synth_inputs(batch, ucfg, rank=0, pin=True):
+    """Seeded synthetic inputs on the HOST (pinned): x_T, text context, one-hot mask."""
+    g = torch.Generator().manual_seed(SEED + 17 * rank)
+    cc = ucfg["condition_config"]
+    xt = torch.randn(batch, 4, 32, 32, generator=g)
+    text = torch.randn(batch, 77, cc["text_condition_config"]["text_embed_dim"], generator=g)
+    ic = cc["image_condition_config"]
+    ch, mh, mw = ic["image_condition_input_channels"], ic["image_condition_h"], ic["image_condition_w"]
+    cls = torch.randint(0, ch + 1, (batch, mh // 16, mw // 16), generator=g)  # blocky class map, 16x16 cells
+    cls = cls.repeat_interleave(16, 1).repeat_interleave(16, 2)
+    mask = torch.zeros(batch, ch, mh, mw)
+    for c in range(ch):
+        mask[:, c] = (cls == c + 1).float()
+    if pin and torch.cuda.is_available():
+        xt, text, mask = xt.pin_memory(), text.pin_memory(), mask.pin_memory()
+    return xt, text, mask
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled every 200 ms while the timed region runs (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc is not None:
+            time.sleep(0.25)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+            self.th.join(timeout=2)
+
+    def summary(self):
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for nm, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        # "under load": the upper half of the samples (idle samples before/after the region sit at low clocks)
+        med = sm[len(sm) // 2] if sm else None
+        return {"sm_mhz": med, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------- CPU baseline
+def cpu_reference_run(ucfg, vcfg, steps, warmup, budget_s, cfg_scale=1.0, sample_batch=2):
+    """The reference's CPU path for this workload: oracle/unet_torch.py + oracle/scheduler_np.py are the fp32 CPU
+    restatement of models/unet_cond_base.py, scheduler/linear_noise_scheduler.py and models/vqvae.py:decode, pinned
+    to the real reference by oracle/gen_golden.py (the reference itself is Python and cannot travel to the GPU box).
+    Each step is one DDPM timestep on a BOUNDED sample of the workload (`sample_batch` images of the 64); the loop
+    stops early when `budget_s` is spent. Returns per-image seconds for a timestep and for the decode."""
+    import numpy as np
+    from oracle import scheduler_np as onp
+    from oracle import unet_torch as O
+    from models.unet_cond_base import Unet
+    from models.vqvae import VQVAE
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(SEED)
+    usd = {k: v.clone() for k, v in Unet(4, ucfg).state_dict().items()}
+    vsd = {k: v.clone() for k, v in VQVAE(3, vcfg).state_dict().items()}
+    xt, text, mask = synth_inputs(sample_batch, ucfg, pin=False)
+    cond = {"text": text, "image": mask}
+    uncond = {"text": torch.zeros_like(text), "image": torch.zeros_like(mask)}
+    tb = onp.make_tables(T_STEPS, 0.00085, 0.012)
+    rng = np.random.default_rng(SEED)
+    x = xt.clone()
+    done, t_spent, t0_all = 0, 0.0, time.perf_counter()
+    with torch.no_grad():
+        for k in range(warmup + steps):
+            i = max(T_STEPS - 1 - k, 0)
+            t0 = time.perf_counter()
+            tt = torch.full((sample_batch,), i, dtype=torch.long)
+            eps = O.unet_forward(usd, ucfg, x, tt, cond)
+            if cfg_scale > 1:
+                eu = O.unet_forward(usd, ucfg, x, tt, uncond)
+                eps = eu + cfg_scale * (eps - eu)
+            z = rng.standard_normal(x.shape, dtype=np.float32)
+            xp, _ = onp.sample_prev_timestep(tb, x.numpy(), eps.numpy(), i, z)
+            x = torch.from_numpy(np.ascontiguousarray(xp))
+            dt = time.perf_counter() - t0
+            if k >= warmup:
+                done += 1
+                t_spent += dt
+            if time.perf_counter() - t0_all > budget_s and done >= 1:
+                break
+        t0 = time.perf_counter()
+        O.vqvae_decode(vsd, vcfg, x[:1].clamp(-1, 1))
+        t_dec = time.perf_counter() - t0
+    return {"t_step_img": t_spent / done / sample_batch, "t_dec_img": t_dec, "steps_done": done, "cores": cores,
+            "sample_batch": sample_batch}
+
+
+def images_per_s(batch, t_step_s, t_dec_s, t_in_s=0.0):
+    return batch / (T_STEPS * t_step_s + t_dec_s + t_in_s)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    ucfg, vcfg = load_cfg()
+    r = cpu_reference_run(ucfg, vcfg, args.steps, min(args.warmup, 1), budget_s=args.cpu_budget, cfg_scale=args.cfg)
+    ips = images_per_s(1, r["t_step_img"], r["t_dec_img"])
+    sample = (f"{r['steps_done']} timed DDPM timesteps (of {args.steps} requested; stops at {args.cpu_budget:.0f} s) on "
+              f"{r['sample_batch']} of the {args.batch} images + VQVAE decode of 1 image, fp32, oracle port of the "
+              f"reference on {r['cores']} host threads; images/s = 1 / (1000 * s_per_image_step + s_per_image_decode)")
+    line = {
+        "impl": "reference", "metric": "ddpm_sampling_images_per_s", "value": ips, "unit": "images/s",
+        "n_gpus": args.gpus, "steps": r["steps_done"], "warmup": min(args.warmup, 1),
+        "ms_per_step": 1e3 * r["t_step_img"] * args.batch, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, ucfg),
+        "cpu_baseline": {"value": ips, "unit": "images/s", "cores": r["cores"], "kind": "port", "sample": sample},
+        "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(args, ucfg):
+    return {
+        "workload": "configs[1]: text+mask conditioned LDM UNet (config/celebhq_text_image_cond.yaml), 1000-step DDPM "
+                    "ancestral sampling + VQVAE decode, batch 64 per GPU",
+        "batch_per_gpu": args.batch, "timesteps": T_STEPS, "cf_guidance_scale": args.cfg,
+        "latent": [4, 32, 32], "text_ctx": [77, 512], "mask": [18, 512, 512], "image": [3, 256, 256],
+        "unet_params": 118513466, "parallelism": f"batch-sharded x{args.gpus}, no collective",
+        "l2": "inputs larger than L2: 237 MB of bf16 weights + >1 GB of activations are touched per step (L2 = 126 MB)",
+    }
+
+
+# ---------------------------------------------------------------------------------------------- our arm
+def run_ours(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (this package has no CPU path; use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    import torch.distributed as dist
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(vals):
+        t = torch.tensor(vals, device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.tolist()
+
+    import __graft_entry__ as ge
+    ge.build()
+    import sdb200  # noqa: F401
+    from sdb200 import runtime as rt
+    from sdb200.graphs import SamplingPipeline
+    from models.unet_cond_base import Unet
+    from models.vqvae import VQVAE
+    from scheduler.linear_noise_scheduler import LinearNoiseScheduler
+
+    ucfg, vcfg = load_cfg()
+    B, K, W = args.batch, args.steps, max(args.warmup, 3)
+    torch.manual_seed(SEED)
+    model = Unet(4, ucfg).eval().to(dev)
+    vae = VQVAE(3, vcfg).eval().to(dev)
+    sched = LinearNoiseScheduler(T_STEPS, 0.00085, 0.012)
+    sched.seed = SEED + rank
+    xt_h, text_h, mask_h = synth_inputs(B, ucfg, rank)
+    xt_d, text_d, mask_d = xt_h.to(dev), text_h.to(dev), mask_h.to(dev)
+    cond = {"text": text_d, "image": mask_d}
+    uncond = {"text": torch.zeros_like(text_d), "image": torch.zeros_like(mask_d)} if args.cfg > 1 else None
+
+    # ------------------------------------------------------------------ value: device-resident loop
+    pipe = SamplingPipeline(model, sched, vae, use_graph=not args.no_graph)
+    with torch.no_grad():
+        P = pipe.plan(xt_d, cond, uncond, args.cfg)
+        P.xt.copy_(xt_d)
+        P.t.fill_(T_STEPS - 1)
+        for _ in range(W):
+            pipe.step(P)
+        vae.decode(P.xt.clamp(-1, 1))
+        l0 = rt.launch_count()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        P.xt.copy_(xt_d)
+        t_first = min(K, T_STEPS) - 1
+        P.t.fill_(t_first)
+        barrier()
+        with ClockSampler(local) as clk:
+            ev[0].record()
+            for k in range(K):
+                if k and k % T_STEPS == 0:
+                    P.t.fill_(T_STEPS - 1)
+                pipe.step(P)
+            ev[1].record()
+            ims = vae.decode(P.xt)
+            ev[2].record()
+            barrier()
+        launches = rt.launch_count() - l0
+        ms_steps, ms_dec = max_over_ranks([ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2])])
+        finite = bool(torch.isfinite(ims).all().item())
+    t_step, t_dec = ms_steps / K / 1e3, ms_dec / 1e3
+    value = world * images_per_s(B, t_step, t_dec)
+
+    # ------------------------------------------------------------------ e2e: drop-in API from host buffers
+    x0_host = torch.empty(B, 4, 32, 32).pin_memory()
+    ims_host = torch.empty(B, 3, 256, 256).pin_memory()
+    Ke = min(K, args.e2e_steps) if args.e2e_steps > 0 else K
+
+    def e2e_job(nsteps, events=None):
+        rec = (lambda i: events[i].record()) if events else (lambda i: None)
+        with torch.no_grad():
+            rec(0)
+            xt = xt_h.to(dev, non_blocking=True)
+            c = {"text": text_h.to(dev, non_blocking=True), "image": mask_h.to(dev, non_blocking=True)}
+            u = {"text": torch.zeros_like(c["text"]), "image": torch.zeros_like(c["image"])} if args.cfg > 1 else None
+            rec(1)
+            for i in reversed(range(nsteps)):
+                t = torch.full((B,), i, device=dev, dtype=torch.long)
+                eps = model(xt, t, c)
+                if u is not None:
+                    eps_u = model(xt, t, u)
+                    xt, x0 = sched.sample_prev_timestep(xt, eps, torch.as_tensor(i), noise_pred_uncond=eps_u,
+                                                        cf_guidance_scale=args.cfg)
+                else:
+                    xt, x0 = sched.sample_prev_timestep(xt, eps, torch.as_tensor(i))
+                x0_host.copy_(x0, non_blocking=True)  # the per-step preview the reference script pulls to the host
+            rec(2)
+            out = vae.decode(xt)
+            ims_host.copy_(out, non_blocking=True)
+            rec(3)
+
+    e2e_job(W)
+    ee = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+    barrier()
+    wall0 = time.perf_counter()
+    e2e_job(Ke, ee)
+    barrier()
+    wall = time.perf_counter() - wall0
+    ms_in, ms_loop, ms_out = max_over_ranks([ee[0].elapsed_time(ee[1]), ee[1].elapsed_time(ee[2]),
+                                             ee[2].elapsed_time(ee[3])])
+    e2e_value = world * images_per_s(B, ms_loop / Ke / 1e3, ms_out / 1e3, ms_in / 1e3)
+    h2d = (xt_h.numel() + text_h.numel() + mask_h.numel()) * 4 / T_STEPS
+    d2h = x0_host.numel() * 4 + ims_host.numel() * 4 / T_STEPS
+
+    # ------------------------------------------------------------------ roofline of the dominant kernel
+    with torch.no_grad():
+        P.xt.copy_(xt_d)
+        P.t.fill_(500)
+        P.body()
+        with rt.KernelTimer() as kt:
+            P.body()
+        ksum = kt.summary()
+        rows = kt.rows()
+    pk = peaks()
+    ig = ksum.get("igemm", {"launches": 0, "ms": 1e-9, "work": 0.0})
+    ach = ig["work"] / (ig["ms"] * 1e-3) / 1e12
+    eager_ms = sum(v["ms"] for v in ksum.values())
+    roofline = {
+        "kernel": "igemm_kernel (tcgen05 implicit GEMM: every conv / linear of the step)", "bound": "tensor",
+        "achieved": ach, "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": ach / pk["tf_sustained"],
+        "peak_source": f"{pk['src']} MEASURED_PEAKS.json bf16_tflops_sustained (kernel timed inside a long step)",
+        "traffic": None, "launches_per_step": ig["launches"], "avg_launch_us": 1e3 * ig["ms"] / max(ig["launches"], 1),
+        "algorithmic_gflop_per_step": ig["work"] / 1e9,
+    }
+    kernels = {k: {"launches": v["launches"], "ms": round(v["ms"], 4), "share": round(v["ms"] / eager_ms, 4),
+                   "achieved": (round(v["work"] / (v["ms"] * 1e-3) / 1e12, 2) if k in ("igemm", "attention")
+                                else round(v["work"] / (v["ms"] * 1e-3) / 1e9, 1)),
+                   "unit": "TFLOP/s" if k in ("igemm", "attention") else "GB/s"} for k, v in ksum.items()}
+    if rank == 0 and args.dump:
+        os.makedirs(os.path.dirname(os.path.abspath(args.dump)) or ".", exist_ok=True)
+        with open(args.dump, "w") as f:
+            json.dump({"per_launch": [{"kernel": n, "work": w, "us": round(ms * 1e3, 2), "shape": d}
+                                      for n, w, ms, d in rows], "summary": kernels}, f)
+
+    step_flops = B * UNET_GFLOP * 1e9 * (2 if args.cfg > 1 else 1)
+    line = {
+        "metric": "ddpm_sampling_images_per_s", "value": value, "unit": "images/s", "n_gpus": world, "steps": K,
+        "warmup": W, "ms_per_step": 1e3 * t_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic",
+        "config": dict(workload_config(args, ucfg), extrapolated=(K != T_STEPS), decode_ms=ms_dec,
+                       cuda_graph=not args.no_graph, outputs_finite=finite),
+        "step_tflops": step_flops / t_step / 1e12, "step_frac_of_bf16_sustained": step_flops / t_step / 1e12 / pk["tf_sustained"],
+        "decode_tflops": B * VQVAE_DECODE_GFLOP * 1e9 / t_dec / 1e12,
+        "roofline": roofline, "kernels": kernels,
+        "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "steps": Ke, "ms_per_step": ms_loop / Ke, "inputs_h2d_ms": ms_in, "decode_d2h_ms": ms_out,
+                "wall_s": wall, "api": "models.unet_cond_base.Unet.forward + LinearNoiseScheduler.sample_prev_timestep "
+                                        "+ VQVAE.decode (drop-in module calls, pinned host buffers)"},
+        "gpu_launches": launches, "clocks": clk.summary(),
+    }
+    if rank == 0 and world == 1 and not args.no_cpu:
+        r = cpu_reference_run(ucfg, vcfg, 3, 1, budget_s=args.cpu_budget, cfg_scale=args.cfg)
+        ips = images_per_s(1, r["t_step_img"], r["t_dec_img"])
+        line["cpu_baseline"] = {
+            "value": ips, "unit": "images/s", "cores": r["cores"], "kind": "port",
+            "sample": f"{r['steps_done']} DDPM timesteps on {r['sample_batch']} of the {B} images + VQVAE decode of 1 "
+                      f"image, fp32 oracle port on {r['cores']} host threads, extrapolated to 1000 steps per image"}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=T_STEPS)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--cfg", type=float, default=1.0, help="classifier-free guidance scale (>1: two forwards per step)")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cpu-budget", type=float, default=90.0, help="seconds the CPU legs may spend")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="cap on the e2e leg's timesteps (0 = same as --steps)")
+    ap.add_argument("--dump", default="", help="write the per-launch kernel timing of one eager step to this JSON file")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

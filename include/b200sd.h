@@ -63,6 +63,10 @@ int b200sd_sched_prev_step(const float* xt, const float* eps, const float* eps_u
                            const float* alphas, const float* acp, const float* sqrt_1m_acp, int num_timesteps,
                            float* x_prev, float* x0, int64_t n, uint64_t seed, uint64_t offset, void* stream);
 
+/* t[i] += delta on device: the `for i in reversed(range(T))` loop counter of tools/sample_ddpm_text_image_cond.py:79-81
+ * kept on the device so a whole sampling step (UNet forward + ancestral update + counter) replays as one CUDA graph. */
+int b200sd_advance_t(int64_t* t, int64_t t_len, int64_t delta, void* stream);
+
 /* get_time_embedding — models/blocks.py:5-24 (and models/transformer.py:18-40).
  * out[b, j] = sin(t[b]/f_j), out[b, half+j] = cos(t[b]/f_j), f_j = 10000^(j/half); t int64 (t_len = batch or 1).
  * out is bf16 or fp32 [batch, dim]. */

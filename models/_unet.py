@@ -7,6 +7,7 @@ from einops import einsum  # noqa: F401  (kept importable for callers that star-
 
 import sdb200  # noqa: F401
 from sdb200 import engine as E
+from sdb200 import graphs as G
 from sdb200 import runtime as rt
 
 
@@ -138,51 +139,127 @@ class UnetCore(nn.Module):
         self.conv_out = nn.Conv2d(self.conv_out_channels, im_channels, kernel_size=3, padding=1)
 
     # ------------------------------------------------------------------------------------------------ forward
+    def _cond_params(self):
+        """Parameters the hoisted conditioning work depends on (mask 1x1 conv, context_proj, cross-attn in_proj)."""
+        ps = []
+        if self.image_cond:
+            ps.append(self.cond_conv_in.weight)
+        if self.text_cond:
+            for blk in list(self.downs) + list(self.mids) + list(self.ups):
+                if getattr(blk, "cross_attn", False):
+                    for m in list(blk.context_proj) + list(blk.cross_attentions):
+                        ps.extend(m.parameters())
+        return ps
+
+    def prepare_cond(self, cond_input, x_shape, device):
+        """Everything in the forward that depends only on `cond_input` and the weights, not on (x, t): the mask
+        branch (nearest resize + 1x1 conv, unet_cond_base.py:134-138) written once into the mask channels of the
+        conv_in input buffer, and the bf16 text context whose per-site K/V projections are filled in lazily by
+        the first forward that uses this state. The reference recomputes all of it on each of the 1000 sampling
+        steps (tools/sample_ddpm_text_image_cond.py:82)."""
+        n, c, h, w = x_shape
+        st = E.CondState()
+        if self.image_cond:
+            assert 'image' in cond_input, \
+                "Model initialized with image conditioning but cond_input has no image information"
+            mask = cond_input['image']
+            assert mask.shape[0] == n, "Batch size mismatch of image condition and input"
+            assert mask.shape[2] % h == 0, "Height/Width of image condition must be divisible by latent input"
+            cin = c + self.im_cond_output_ch
+            ld = (cin + 7) // 8 * 8
+            buf = torch.zeros(n * h * w, ld, device=device, dtype=torch.bfloat16)
+            if type(self.cond_conv_in) is not nn.Conv2d:
+                raise rt.B200Error("cond_conv_in: quantised leaf on the mask path is not supported yet")
+            rt.mask_cond(mask.float(), self.cond_conv_in.weight.detach().float().reshape(self.im_cond_output_ch, -1),
+                         buf, c, h, w)
+            st.inbuf, st.cin = buf, cin
+        if self.text_cond:
+            assert 'text' in cond_input, \
+                "Model initialized with text conditioning but cond_input has no text information"
+            text = cond_input['text']
+            assert text.shape[0] == n and text.shape[-1] == self.text_embed_dim
+            st.ctx = E.prepare_context(text)
+        if self.class_cond:
+            validate_class_conditional_input(cond_input, torch.empty(x_shape, device='meta'), self.num_classes)
+            st.class_onehot = cond_input['class'].float()
+        return st
+
+    def _cached_cond(self, cond_input, x):
+        """In inference (no grad) reuse the CondState while the caller keeps passing the same, unmodified condition
+        tensors and the conditioning weights are untouched — which is what every sampling loop does."""
+        if isinstance(cond_input, E.CondState):
+            return cond_input
+        if torch.is_grad_enabled() or not E.HOIST_CONDITIONING:
+            return self.prepare_cond(cond_input, x.shape, x.device)
+        key = (tuple(x.shape),) + tuple((k, v.data_ptr(), v._version, tuple(v.shape))
+                                        for k, v in sorted(cond_input.items()) if isinstance(v, torch.Tensor))
+        key += tuple((p.data_ptr(), p._version) for p in self._cond_params())
+        cache = self.__dict__.setdefault("_cond_cache", {})
+        st = cache.get(key)
+        if st is None:
+            st = self.prepare_cond(cond_input, x.shape, x.device)
+            if st.ctx is not None:
+                st.ctx.persistent = True
+            if len(cache) >= 4:  # conditional + unconditional (CFG) and a little slack
+                cache.pop(next(iter(cache)))
+            cache[key] = st
+        return st
+
     def forward(self, x, t, cond_input=None):
         if not x.is_cuda:
             raise rt.B200Error("Unet.forward: CUDA tensors required (this package has no CPU implementation; "
                                "the reference itself is the CPU path)")
         if self.cond:
             assert cond_input is not None, "Model initialized with conditioning so cond_input cannot be None"
+        st = self._cached_cond(cond_input, x) if self.cond else E.CondState()
+        tt = torch.as_tensor(t).to(device=x.device, dtype=torch.int64).reshape(-1)
+        if tt.numel() not in (1, x.shape[0]):
+            raise RuntimeError(f"t has {tt.numel()} entries for batch size {x.shape[0]}")
+        if G.ENABLE_FORWARD_GRAPHS and not torch.is_grad_enabled() and not torch.cuda.is_current_stream_capturing():
+            graphs = self.__dict__.setdefault("_graphed", {})
+            key = (tuple(x.shape), tt.numel(), id(st))
+            gf = graphs.get(key)
+            if gf is None or not gf.valid(st):
+                if len(graphs) >= 4:
+                    graphs.pop(next(iter(graphs)))
+                gf = graphs[key] = G.GraphedForward(self, x, tt, st)
+            return gf(x, tt)
+        return self.run(x, tt, st).to_nchw()
+
+    def invalidate_plan(self):
+        """Drop captured graphs / hoisted conditioning (call after swapping sub-modules in place)."""
+        self.__dict__.pop("_graphed", None)
+        self.__dict__.pop("_cond_cache", None)
+
+    def train(self, mode=True):
+        self.invalidate_plan()
+        return super().train(mode)
+
+    def _apply(self, fn, *a, **k):
+        self.invalidate_plan()
+        return super()._apply(fn, *a, **k)
+
+    def run(self, x, tt, st):
+        """Engine-level forward: x fp32 NCHW, tt int64 on device, st a CondState; returns the fp32 NHWC Act of the
+        noise prediction. Pure kernel enqueues on the current stream (CUDA-graph capturable)."""
         n, c, h, w = x.shape
         dev = x.device
-
-        # ---- input assembly: latent (+ mask conditioning) -> NHWC bf16, then conv_in
+        # ---- input assembly: latent (+ cached mask channels) -> NHWC bf16, then conv_in
         if self.image_cond:
-            validate_image_conditional_input(cond_input, x)
-            mask = cond_input['image']
-            cin = c + self.im_cond_output_ch
-            ld = (cin + 7) // 8 * 8
-            buf = torch.empty(n * h * w, ld, device=dev, dtype=torch.bfloat16)
-            rt.nchw_to_nhwc(x.float(), buf, 0)
-            if type(self.cond_conv_in) is not nn.Conv2d:
-                raise rt.B200Error("cond_conv_in: quantised leaf on the mask path is not supported yet")
-            rt.mask_cond(mask.float(), self.cond_conv_in.weight.detach().reshape(self.im_cond_output_ch, -1), buf, c,
-                         h, w)
-            out = E.conv2d(E.Act(buf, n, h, w, cin), self.conv_in_concat)
+            rt.nchw_to_nhwc(x.float(), st.inbuf, 0)
+            out = E.conv2d(E.Act(st.inbuf, n, h, w, st.cin), self.conv_in_concat)
         else:
             out = E.conv2d(E.Act.from_nchw(x), self.conv_in)
 
         # ---- time embedding: sinusoid -> t_proj; every block then applies act + its own Linear
-        tt = torch.as_tensor(t).to(device=dev, dtype=torch.int64).reshape(-1)
-        if tt.numel() not in (1, n):
-            raise RuntimeError(f"t has {tt.numel()} entries for batch size {n}")
         emb = rt.time_embedding(tt, n, self.t_emb_dim, dtype=torch.bfloat16)
         emb = E.linear(emb, self.t_proj[0], act=E._act_name(self.t_proj[1]))
         emb = E.linear(emb, self.t_proj[2], out_dtype=torch.float32 if self.class_cond else torch.bfloat16)
         if self.class_cond:
-            validate_class_conditional_input(cond_input, x, self.num_classes)
-            emb = emb + cond_input['class'].float() @ self.class_emb.weight.detach()
+            emb = emb + st.class_onehot @ self.class_emb.weight.detach()
         temb_act = E.activate_temb(emb, self.ACT)
 
-        ctx = None
-        if self.text_cond:
-            assert 'text' in cond_input, \
-                "Model initialized with text conditioning but cond_input has no text information"
-            text = cond_input['text']
-            assert text.shape[0] == n and text.shape[-1] == self.text_embed_dim
-            ctx = E.prepare_context(text)
-
+        ctx = st.ctx
         skips = []
         for down in self.downs:
             skips.append(out)
@@ -194,5 +271,4 @@ class UnetCore(nn.Module):
             out = up.run(out, skip, temb_act, ctx) if self.CONDITIONED else up.run(out, skip, temb_act)
 
         out = E.group_norm(out, self.norm_out, act=E._act_name(self.ACT()))
-        out = E.conv2d(out, self.conv_out, out_dtype=torch.float32)
-        return out.to_nchw()
+        return E.conv2d(out, self.conv_out, out_dtype=torch.float32)

@@ -72,7 +72,7 @@ class _Stack(nn.Module):
         ctx_t, lk, dim = ctx
         assert dim == self.context_dim, "Context shape does not match B,_,CONTEXT_DIM"
         return E.cross_attention(a, self.cross_attention_norms[i], self.cross_attentions[i], self.context_proj[i],
-                                 ctx_t, lk)
+                                 ctx_t, lk, cache=ctx)
 
     # --- NCHW boundary helpers -----------------------------------------------------------------------------
     def _prep_temb(self, t_emb):

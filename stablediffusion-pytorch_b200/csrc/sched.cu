@@ -88,7 +88,13 @@ __global__ void __launch_bounds__(256)
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
     curandStatePhilox4_32_10_t rng;
     const bool draw = (z == nullptr) && c.t > 0;
-    if (draw) curand_init(seed, gid, offset, &rng);
+    if (draw) {
+        // when t is read from the device the launch arguments are frozen inside a CUDA graph, so the stream position
+        // is derived from the timestep: every replay draws a fresh, non-overlapping block of the Philox sequence
+        const uint64_t per_call = 4ull * static_cast<uint64_t>((n / 4 + stride - 1) / stride + 1);
+        const uint64_t step = t_dev ? static_cast<uint64_t>(T - 1 - c.t) : 0ull;
+        curand_init(seed, gid, offset + step * per_call, &rng);
+    }
     if (VEC) {
         const int64_t nv = n >> 2;
         for (int64_t i = gid; i < nv; i += stride) {
@@ -142,6 +148,11 @@ __global__ void time_embedding_kernel(const int64_t* __restrict__ t, int64_t t_l
         out[b * dim + j] = static_cast<OutT>(sinf(arg));
         out[b * dim + half + j] = static_cast<OutT>(cosf(arg));
     }
+}
+
+__global__ void advance_t_kernel(int64_t* t, int64_t n, int64_t delta) {
+    const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) t[i] += delta;
 }
 
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
@@ -224,5 +235,13 @@ extern "C" int b200sd_time_embedding(const int64_t* t, int64_t t_len, void* out,
         return B200SD_ERR_ARG;
     }
     B200_CHECK_LAUNCH("time_embedding");
+    return B200SD_OK;
+}
+
+extern "C" int b200sd_advance_t(int64_t* t, int64_t t_len, int64_t delta, void* stream) {
+    B200_REQUIRE(t && t_len >= 0, "advance_t: bad arguments");
+    if (t_len == 0) return B200SD_OK;
+    advance_t_kernel<<<static_cast<int>((t_len + 127) / 128), 128, 0, as_stream(stream)>>>(t, t_len, delta);
+    B200_CHECK_LAUNCH("advance_t");
     return B200SD_OK;
 }

@@ -211,14 +211,44 @@ def self_attention(a, norm, mha):
     return Act(out, a.n, a.h, a.w, C)
 
 
-def cross_attention(a, norm, mha, ctx_proj_mod, ctx, lk):
-    """x + out_proj(MHA(q=GN(x), k=v=context_proj(ctx))) — blocks.py:133-145. ctx: bf16 [n*lk, ctx_dim]."""
+class Context:
+    """Text context of one forward: bf16 [n*lk, dim] rows plus, per cross-attention site, the projected K/V
+    (context_proj -> in_proj[k,v]). The K/V of a site depend only on the context and that site's weights, not on
+    x or t, so a Context that outlives one forward (the 1000-step sampling loop keeps `cond_input` fixed,
+    tools/sample_ddpm_text_image_cond.py:64-82) computes them once instead of once per step."""
+    __slots__ = ("t", "lk", "dim", "kv", "persistent")
+
+    def __init__(self, t, lk, dim, persistent=False):
+        self.t, self.lk, self.dim, self.kv, self.persistent = t, lk, dim, {}, persistent
+
+    def __iter__(self):  # (ctx_t, lk, dim) unpacking used by the block classes
+        return iter((self.t, self.lk, self.dim))
+
+
+class CondState:
+    """The (x, t)-independent part of a conditioned forward; built by Unet.prepare_cond."""
+    __slots__ = ("inbuf", "cin", "ctx", "class_onehot")
+
+    def __init__(self):
+        self.inbuf = self.cin = self.ctx = self.class_onehot = None
+
+
+HOIST_CONDITIONING = True  # tests flip this to compare hoisted and per-call conditioning
+
+
+def cross_attention(a, norm, mha, ctx_proj_mod, ctx, lk, cache=None):
+    """x + out_proj(MHA(q=GN(x), k=v=context_proj(ctx))) — blocks.py:133-145. ctx: bf16 [n*lk, ctx_dim].
+    `cache`: a persistent Context whose per-site K/V are reused across forwards."""
     C, heads = a.c, mha.num_heads
     xn = group_norm(a, norm)
     pk = _mha_weights(mha)
     q = rt.linear(xn.t, pk["q"], bias=pk["b_q"])
-    cp = linear(ctx, ctx_proj_mod)
-    kv = rt.linear(cp, pk["kv"], bias=pk["b_kv"])
+    kv = cache.kv.get(id(mha)) if cache is not None else None
+    if kv is None:
+        cp = linear(ctx, ctx_proj_mod)
+        kv = rt.linear(cp, pk["kv"], bias=pk["b_kv"])
+        if cache is not None and cache.persistent:
+            cache.kv[id(mha)] = kv
     o = rt.attention(q, kv[:, :C], kv[:, C:], a.n, heads, a.hw, lk, C // heads)
     out = linear(o, mha.out_proj, residual=a.t)
     return Act(out, a.n, a.h, a.w, C)
@@ -264,7 +294,7 @@ def prepare_context(context):
     if d % 8:
         raise rt.B200Error("context dimension must be a multiple of 8")
     t = context if context.dtype == torch.bfloat16 else rt.cast_bf16(context.float())
-    return t.reshape(b * l, d), l, d
+    return Context(t.reshape(b * l, d), l, d)
 
 
 def upsample_concat(a, up_conv, skip):

@@ -17,7 +17,7 @@ _ACT = {None: 0, "none": 0, "silu": 1, "relu": 2}
 
 EXPORTS = [
     "b200sd_last_error", "b200sd_version", "b200sd_launch_count", "b200sd_sched_add_noise",
-    "b200sd_sched_prev_step", "b200sd_time_embedding", "b200sd_igemm", "b200sd_groupnorm", "b200sd_attention",
+    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_groupnorm", "b200sd_attention",
     "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16",
 ]
 
@@ -64,6 +64,7 @@ def lib():
         vp, i64, i32, f32, u64 = C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_uint64
         L.b200sd_sched_add_noise.argtypes = [vp, vp, vp, i64, vp, vp, i32, vp, i64, i64, vp]
         L.b200sd_sched_prev_step.argtypes = [vp, vp, vp, f32, vp, vp, i64, vp, vp, vp, vp, i32, vp, vp, i64, u64, u64, vp]
+        L.b200sd_advance_t.argtypes = [vp, i64, i64, vp]
         L.b200sd_time_embedding.argtypes = [vp, i64, vp, i32, i64, i32, vp]
         L.b200sd_igemm.argtypes = [C.POINTER(IgemmParams), vp]
         L.b200sd_groupnorm.argtypes = [vp, i64, vp, i64, vp, vp, i64, i64, i32, i32, f32, i32, vp]
@@ -85,8 +86,70 @@ def check(rc, what=""):
         raise B200Error(f"{what}: {kind}: {msg}")
 
 
+_replayed = 0
+_prof = None
+
+
+class KernelTimer:
+    """Per-launch CUDA-event timing of every C-ABI call made while active (eager mode only): bench.py uses it to
+    attribute a step's device time to kernel families and to compute the roofline of the dominant one.
+    `with KernelTimer() as kt: ...; kt.summary()` -> {name: {"launches", "ms", "work"}} (work = algorithmic flops
+    for igemm/attention, algorithmic bytes for the HBM-bound kernels)."""
+
+    def __init__(self):
+        self.rec = []
+
+    def __enter__(self):
+        global _prof
+        _prof = self
+        return self
+
+    def __exit__(self, *a):
+        global _prof
+        _prof = None
+
+    def begin(self):
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        return e
+
+    def end(self, e0, name, work, detail=None):
+        e1 = torch.cuda.Event(enable_timing=True)
+        e1.record()
+        self.rec.append((name, work, e0, e1, detail))
+
+    def rows(self):
+        torch.cuda.synchronize()
+        return [(n, w, a.elapsed_time(b), d) for n, w, a, b, d in self.rec]
+
+    def summary(self):
+        out = {}
+        for n, w, ms, _ in self.rows():
+            r = out.setdefault(n, {"launches": 0, "ms": 0.0, "work": 0.0})
+            r["launches"] += 1
+            r["ms"] += ms
+            r["work"] += w
+        return out
+
+
+def _pb():
+    return _prof.begin() if _prof is not None else None
+
+
+def _pe(tok, name, work, detail=None):
+    if tok is not None:
+        _prof.end(tok, name, work, detail)
+
+
+def count_external(n):
+    """Kernels of this library launched by replaying a captured CUDA graph (the C-side counter only sees direct
+    launches)."""
+    global _replayed
+    _replayed += int(n)
+
+
 def launch_count():
-    return int(lib().b200sd_launch_count())
+    return int(lib().b200sd_launch_count()) + _replayed
 
 
 def stream_ptr():
@@ -137,6 +200,12 @@ def sched_prev_step(xt, eps, t, tables, z=None, eps_uncond=None, cfg_scale=1.0, 
     return x_prev, x0
 
 
+def advance_t(t, delta):
+    _cuda(t, torch.int64, "t")
+    check(lib().b200sd_advance_t(_p(t), t.numel(), int(delta), stream_ptr()), "advance_t")
+    return t
+
+
 def time_embedding(t, batch, dim, dtype=torch.bfloat16):
     _cuda(t, torch.int64, "t")
     out = torch.empty(batch, dim, device=t.device, dtype=dtype)
@@ -182,7 +251,11 @@ def igemm(srcs, segs, weight, n_out, on, oh, ow, out, out_strides, bias=None, ro
         p.residual = residual.data_ptr()
         p.res_sn, p.res_sy, p.res_sx = res_strides
     p.act = _ACT[act] if not isinstance(act, int) else act
+    tok = _pb()
     check(lib().b200sd_igemm(C.byref(p), stream_ptr()), "igemm")
+    if tok is not None:
+        k_alg = sum(max(0, min(nch * 64, srcs[si].dims[0] - c0)) for si, _, _, c0, nch in segs)
+        _pe(tok, "igemm", 2.0 * on * oh * ow * n_out * k_alg, (on * oh * ow, n_out, k_alg))
     return out
 
 
@@ -219,8 +292,10 @@ def groupnorm(x, n, hw, c, groups, gamma, beta, eps=1e-5, act=None, out=None, ld
         out = torch.empty(n * hw, c, device=x.device, dtype=torch.bfloat16)
         ld_y = c
     ld_y = c if ld_y is None else ld_y
+    tok = _pb()
     check(lib().b200sd_groupnorm(_p(x), ld_x, _p(out), ld_y, _p(gamma), _p(beta), n, hw, c, groups, float(eps),
                                   _ACT[act], stream_ptr()), "groupnorm")
+    _pe(tok, "groupnorm", 4.0 * n * hw * c, (n, hw, c))
     return out
 
 
@@ -231,8 +306,10 @@ def attention(q, k, v, batch, heads, lq, lk, d, scale=None, out=None):
     if out is None:
         out = torch.empty(batch * lq, heads * d, device=q.device, dtype=torch.bfloat16)
     scale = d ** -0.5 if scale is None else scale
+    tok = _pb()
     check(lib().b200sd_attention(_p(q), q.stride(0), _p(k), k.stride(0), _p(v), v.stride(0), _p(out), out.stride(0),
                                   batch, heads, lq, lk, d, float(scale), stream_ptr()), "attention")
+    _pe(tok, "attention", 4.0 * batch * heads * lq * lk * d, (batch, heads, lq, lk, d))
     return out
 
 
