@@ -128,7 +128,8 @@ def conv2d(a, mod, rowbias=None, extra=None, act=None, out=None, c_off=0, out_dt
                 (mod.bias if mod.bias is not None else 0) + (xm.bias if xm.bias is not None else 0)).float().contiguous())
             ex = (xa.t, xa.c, xa.ld)
         if out is None:
-            o = torch.empty(a.n * a.hw, cout, device=a.t.device, dtype=out_dtype)
+            # row pitch padded to 16 B so the next layer's TMA view of this tensor is legal (z_channels = 4)
+            o = torch.empty(a.n * a.hw, (cout + 7) // 8 * 8, device=a.t.device, dtype=out_dtype)
         else:
             o = out.t
         ops.conv_same(a.t, a.n, a.h, a.w, a.c, wmat, cout, k[0], bias=bias, ld_x=a.ld, out=o, c_off=c_off,
