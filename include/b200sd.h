@@ -118,12 +118,17 @@ typedef struct {
     const void* residual; /* bf16, same pixel geometry as out, or NULL */
     int64_t res_sn, res_sy, res_sx;
     int32_t act;
-    /* optional per-(image, channel) sum / sum-of-squares of the bf16-rounded output, fp32 [on, n_out, 2],
-       accumulated with atomics: the GroupNorm statistics of the next layer without re-reading the tensor */
+    /* optional partial GroupNorm statistics of the bf16-rounded output: fp32 [on, stats_p, stats_ld, 2] holding, per
+       image and per tile slot, each channel's (sum, sum of squares) over the tile's pixels. This call writes slots
+       [stats_slot0, stats_slot0 + b200sd_igemm_stats_slots(oh, ow)) at channels [0, n_out); every element it owns
+       is written exactly once (no atomics, no zero-initialisation needed, bit-reproducible). The consumer
+       (b200sd_groupnorm_apply) sums the slots in order. */
     float* stats;
+    int32_t stats_p, stats_slot0, stats_ld;
 } b200sd_igemm_params;
 
 int b200sd_igemm(const b200sd_igemm_params* p, void* stream);
+int b200sd_igemm_stats_slots(int oh, int ow);
 
 /* ------------------------------------------------------------------------------------------- normalisation
  * nn.GroupNorm(G, C) (+ SiLU / ReLU) — models/blocks.py:48-49,67-68,126,136; unet_cond_base.py:179-180.
@@ -131,6 +136,15 @@ int b200sd_igemm(const b200sd_igemm_params* p, void* stream);
  * eps inside the sqrt, fp32 arithmetic; y = act((x-mean)*rstd*gamma + beta) written as bf16 [n, hw, ld_y]. */
 int b200sd_groupnorm(const void* x, int64_t ld_x, void* y, int64_t ld_y, const float* gamma, const float* beta,
                      int64_t n, int64_t hw, int c, int groups, float eps, int act, void* stream);
+
+/* The same normalisation when the producer of x already left partial statistics (b200sd_igemm `stats`): x is read
+ * once and written once. Channels [0, c_split) take their statistics from stats0 ([n, p0, ld_s0, 2]) and channels
+ * [c_split, c) from stats1 ([n, p1, ld_s1, 2]; the skip-connection concat of models/blocks.py:464, whose halves were
+ * produced by different kernels); pass c_split = c and stats1 = NULL for a single producer. */
+int b200sd_groupnorm_apply(const void* x, int64_t ld_x, void* y, int64_t ld_y, const float* stats0, int p0, int ld_s0,
+                           int c_split, const float* stats1, int p1, int ld_s1, const float* gamma,
+                           const float* beta, int64_t n, int64_t hw, int c, int groups, float eps, int act,
+                           void* stream);
 
 /* ----------------------------------------------------------------------------------------------- attention
  * softmax(Q K^T / sqrt(d)) V per (batch, head) — nn.MultiheadAttention call sites models/blocks.py:128,140,242,

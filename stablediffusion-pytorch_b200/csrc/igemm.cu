@@ -1,14 +1,19 @@
 // Implicit-GEMM core on tcgen05 / TMEM / TMA (SURVEY K1-K4, K6, K9-K13 projections).
 //
-// One CTA computes a 128 (output pixels) x BN (output channels) tile:
-//   warp 0      : TMA producer — per 64-channel K chunk, one 4-D box load of the activation tile (the tap shift is
-//                 a coordinate offset; image borders are TMA out-of-bounds zero fill = conv padding) and one 2-D
-//                 box load of the weight tile, both landing 128B-swizzled, K-major in shared memory
-//   warp 1      : MMA issuer — lane 0 issues 4 x tcgen05.mma (M=128, N=BN, K=16) per chunk, accumulating fp32 in
-//                 TMEM, and releases the smem stage with tcgen05.commit
-//   warps 2..5  : epilogue — tcgen05.ld the accumulator (one TMEM lane = one output pixel per thread), add bias /
-//                 time-embedding row bias, activation, gate, residual, convert and store
-// smem ring: STAGES x (16 KB A + BN*128 B B); full/empty mbarriers; one accumulator-ready mbarrier.
+// Persistent kernel, one CTA per SM, each CTA walks output tiles of 128 (pixels) x BN (channels):
+//   warp 0      : TMA producer — per 64-channel K chunk one 4-D box load of the activation tile (the conv tap is a
+//                 coordinate offset; image borders are TMA out-of-bounds zero fill = conv padding) and one 2-D box
+//                 load of the weight tile, both landing 128B-swizzled, K-major in a STAGES-deep smem ring
+//   warp 1      : MMA issuer — lane 0 issues 4 x tcgen05.mma (M=128, N=BN, K=16) per chunk into one of TWO TMEM
+//                 accumulators, releases ring stages with tcgen05.commit and hands the accumulator to the epilogue
+//   warps 2..5  : epilogue — tcgen05.ld the accumulator (one TMEM lane = one output pixel per thread), bias /
+//                 time-embedding row bias / activation / gate / residual, bf16 convert into a swizzled smem staging
+//                 tile, optional per-channel sum / sum-of-squares of the tile (the next GroupNorm's statistics), then
+//                 ONE thread issues TMA tensor stores. The residual tile is TMA-loaded into the same staging buffer
+//                 ahead of time. While the epilogue drains accumulator A the MMA warp fills accumulator B.
+// The epilogue's global traffic is therefore all bulk-async (TMA): a handful of threads keep tens of KB in flight,
+// which per-thread 16-byte loads/stores from 128 threads cannot (r1a profile: 5 % tensor-pipe on K=384 GEMMs).
+// Outputs TMA cannot address (fp32, row pitch not a multiple of 16 B, fewer than 64 columns) take a direct path.
 #include "host.h"
 #include "ptx.cuh"
 #include <cudaTypedefs.h>
@@ -20,6 +25,8 @@ constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int IGEMM_THREADS = 192;
 constexpr int MAX_SEG = 20;
+constexpr int EPI_THREADS = 128;
+constexpr int PANEL_BYTES = BM * 128;  // 128 rows x 64 bf16
 
 struct SegDev {
     int src, dy, dx, c0, nchunk;
@@ -28,12 +35,16 @@ struct SegDev {
 struct alignas(64) IgemmArgs {
     CUtensorMap a_map[4];
     CUtensorMap b_map;
+    CUtensorMap out_map;
+    CUtensorMap res_map;
     SegDev seg[MAX_SEG];
     int n_seg, total_chunks;
     int n_out;
     int on, oh, ow;  // output pixel grid
     int bw, bh, bn;  // tile box (bw*bh*bn == 128)
-    int tiles_x, tiles_y, tiles_img, tiles_col;
+    int tiles_x, tiles_y, tiles_img, tiles_col, num_tiles;
+    int tma_out;     // 1: staged TMA-store epilogue, 0: direct global stores
+    int tma_res;     // 1: residual arrives by TMA into the staging buffer
     void* out;
     int out_f32;
     long long out_sn, out_sy, out_sx;
@@ -45,7 +56,28 @@ struct alignas(64) IgemmArgs {
     const __nv_bfloat16* residual;
     long long res_sn, res_sy, res_sx;
     int act;
+    float* stats;  // [on][stats_p][stats_ld][2] partial sums, or null
+    int stats_p, stats_slot0, stats_ld;
 };
+
+struct Tile {
+    int col_t, x0, y0, n0, slot;
+};
+
+__device__ __forceinline__ Tile decode_tile(const IgemmArgs& a, int tile) {
+    // column tiles vary fastest so CTAs that run together share activation tiles in L2
+    Tile t;
+    t.col_t = tile % a.tiles_col;
+    int m = tile / a.tiles_col;
+    const int tx = m % a.tiles_x;
+    m /= a.tiles_x;
+    const int ty = m % a.tiles_y;
+    t.x0 = tx * a.bw;
+    t.y0 = ty * a.bh;
+    t.n0 = (m / a.tiles_y) * a.bn;
+    t.slot = ty * a.tiles_x + tx;
+    return t;
+}
 
 __device__ __forceinline__ float apply_act(float v, int act) {
     if (act == B200SD_ACT_SILU) return v / (1.f + __expf(-v));
@@ -62,50 +94,105 @@ __device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
         f[2 * i + 1] = t.y;
     }
 }
+__device__ __forceinline__ uint4 pack8(const float (&v)[8]) {
+    uint4 pk;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+    return pk;
+}
+
+// 8 consecutive bf16 / fp32 values starting at p[col], masked to nv valid entries (vector path when aligned)
+__device__ __forceinline__ void load8_bf16(const __nv_bfloat16* p, int nv, float (&f)[8]) {
+    if (nv == 8 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+        unpack8(__ldg(reinterpret_cast<const uint4*>(p)), f);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = j < nv ? __bfloat162float(p[j]) : 0.f;
+    }
+}
+__device__ __forceinline__ void load8_f32(const float* p, int nv, float (&f)[8]) {
+    if (nv == 8 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+        f[0] = a.x, f[1] = a.y, f[2] = a.z, f[3] = a.w, f[4] = b.x, f[5] = b.y, f[6] = b.z, f[7] = b.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = j < nv ? __ldg(p + j) : 0.f;
+    }
+}
 
 template <int BN, int STAGES>
 struct IgemmSmem {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
-    static constexpr int TOTAL = BAR_OFF + (2 * STAGES + 1) * 8 + 16 + 1024;  // +1024: manual alignment slack
+    static constexpr int STAGING_OFF = STAGES * STAGE_BYTES;
+    static constexpr int STAGING_BYTES = BN >= 64 ? (BN / 64) * PANEL_BYTES : 0;
+    static constexpr int BAR_OFF = STAGING_OFF + STAGING_BYTES;
+    static constexpr int NBAR = 2 * STAGES + 5;  // full[S], empty[S], tmem_full[2], tmem_empty[2], res_full
+    static constexpr int RED_OFF = BAR_OFF + NBAR * 8 + 16;  // 64 x 2 floats: half-tile statistics exchange
+    static constexpr int TOTAL = RED_OFF + 512 + 1024;       // +1024: manual alignment slack
 };
 
-template <int BN, int STAGES, int MIN_CTAS>
-__global__ void __launch_bounds__(IGEMM_THREADS, MIN_CTAS) igemm_kernel(const __grid_constant__ IgemmArgs args) {
+// Epilogue arithmetic on 8 consecutive output columns of one row.
+__device__ __forceinline__ void epilogue8(const IgemmArgs& args, float (&v)[8], int col, int nv, int pn) {
+    float f[8];
+    if (args.bias) {
+        load8_f32(args.bias + col, nv, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] += f[j];
+    }
+    if (args.rowbias) {
+        load8_bf16(args.rowbias + pn * args.rowbias_ld + col, nv, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] += f[j];
+    }
+    if (args.act != B200SD_ACT_NONE) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = apply_act(v[j], args.act);
+    }
+    if (args.gate) {
+        load8_bf16(args.gate + pn * args.gate_ld + col, nv, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] *= f[j];
+    }
+}
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_constant__ IgemmArgs args) {
     using L = IgemmSmem<BN, STAGES>;
-    constexpr uint32_t TMEM_COLS = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
+    constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;  // two accumulators; 64..512, a power of two
+    constexpr int PANELS = BN / 64;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* staging = smem + L::STAGING_OFF;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
     uint64_t* empty_bar = full_bar + STAGES;
-    uint64_t* accum_bar = empty_bar + STAGES;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+    uint64_t* tfull_bar = empty_bar + STAGES;
+    uint64_t* tempty_bar = tfull_bar + 2;
+    uint64_t* res_bar = tempty_bar + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + 1);
+    float* red = reinterpret_cast<float*>(smem + L::RED_OFF);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
-    // tile coordinates: column tiles vary fastest so CTAs that share an activation tile are co-scheduled (L2 reuse)
-    const int tile = blockIdx.x;
-    const int col_t = tile % args.tiles_col;
-    int m_t = tile / args.tiles_col;
-    const int tx = m_t % args.tiles_x;
-    m_t /= args.tiles_x;
-    const int ty = m_t % args.tiles_y;
-    const int tn = m_t / args.tiles_y;
-    const int x0 = tx * args.bw, y0 = ty * args.bh, n0 = tn * args.bn;
-
     if (warp == 0 && lane == 0) {
         for (int i = 0; i < 4; ++i) tma_prefetch_desc(&args.a_map[i]);
         tma_prefetch_desc(&args.b_map);
+        if (args.tma_out) tma_prefetch_desc(&args.out_map);
+        if (args.tma_res) tma_prefetch_desc(&args.res_map);
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
-        mbar_init(accum_bar, 1);
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&tfull_bar[b], 1);
+            mbar_init(&tempty_bar[b], EPI_THREADS);
+        }
+        mbar_init(res_bar, 1);
         fence_barrier_init();
     }
     if (warp == 2) {
@@ -121,130 +208,212 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MIN_CTAS) igemm_kernel(const __
         // ------------------------------------------------------------------ TMA producer
         if (lane == 0) {
             int it = 0;
-            for (int s = 0; s < args.n_seg; ++s) {
-                const SegDev sg = args.seg[s];
-                for (int ch = 0; ch < sg.nchunk; ++ch, ++it) {
-                    const int stage = it % STAGES;
-                    const uint32_t phase = (it / STAGES) & 1;
-                    mbar_wait(&empty_bar[stage], phase ^ 1);
-                    uint8_t* sa = smem + stage * L::STAGE_BYTES;
-                    uint8_t* sb = sa + L::A_BYTES;
-                    mbar_expect_tx(&full_bar[stage], L::STAGE_BYTES);
-                    tma_load_4d(sa, &args.a_map[sg.src], &full_bar[stage], sg.c0 + ch * BK, x0 + sg.dx, y0 + sg.dy,
-                                n0);
-                    tma_load_2d(sb, &args.b_map, &full_bar[stage], it * BK, col_t * BN);
+            for (int tile = blockIdx.x; tile < args.num_tiles; tile += gridDim.x) {
+                const Tile t = decode_tile(args, tile);
+                int kc = 0;
+                for (int s = 0; s < args.n_seg; ++s) {
+                    const SegDev sg = args.seg[s];
+                    for (int ch = 0; ch < sg.nchunk; ++ch, ++it, ++kc) {
+                        const int stage = it % STAGES;
+                        const uint32_t phase = (it / STAGES) & 1;
+                        mbar_wait(&empty_bar[stage], phase ^ 1);
+                        uint8_t* sa = smem + stage * L::STAGE_BYTES;
+                        mbar_expect_tx(&full_bar[stage], L::STAGE_BYTES);
+                        tma_load_4d(sa, &args.a_map[sg.src], &full_bar[stage], sg.c0 + ch * BK, t.x0 + sg.dx,
+                                    t.y0 + sg.dy, t.n0);
+                        tma_load_2d(sa + L::A_BYTES, &args.b_map, &full_bar[stage], kc * BK, t.col_t * BN);
+                    }
                 }
             }
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer
         constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
-        for (int it = 0; it < args.total_chunks; ++it) {
-            const int stage = it % STAGES;
-            const uint32_t phase = (it / STAGES) & 1;
-            mbar_wait(&full_bar[stage], phase);
+        int it = 0, lt = 0;
+        for (int tile = blockIdx.x; tile < args.num_tiles; tile += gridDim.x, ++lt) {
+            const int buf = lt & 1;
+            mbar_wait(&tempty_bar[buf], ((lt >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
             tc_fence_after();
-            if (lane == 0) {
-                const uint32_t sa = smem_u32(smem + stage * L::STAGE_BYTES);
-                const uint64_t da = umma_desc_k128(sa);
-                const uint64_t db = umma_desc_k128(sa + L::A_BYTES);
+            const uint32_t tacc = tmem_base + buf * BN;
+            for (int kc = 0; kc < args.total_chunks; ++kc, ++it) {
+                const int stage = it % STAGES;
+                mbar_wait(&full_bar[stage], (it / STAGES) & 1);
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint32_t sa = smem_u32(smem + stage * L::STAGE_BYTES);
+                    const uint64_t da = umma_desc_k128(sa);
+                    const uint64_t db = umma_desc_k128(sa + L::A_BYTES);
 #pragma unroll
-                for (int k = 0; k < BK / 16; ++k) {
-                    // +32 B per K=16 step inside the 128 B swizzle atom: +2 in the (>>4) start-address field
-                    umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc, (it | k) != 0);
+                    for (int k = 0; k < BK / 16; ++k) {
+                        // +32 B per K=16 step inside the 128 B swizzle atom: +2 in the (>>4) start-address field
+                        umma_bf16(tacc, da + 2 * k, db + 2 * k, idesc, (kc | k) != 0);
+                    }
+                    umma_commit(&empty_bar[stage]);
                 }
-                umma_commit(&empty_bar[stage]);
+                __syncwarp();
             }
+            if (lane == 0) umma_commit(&tfull_bar[buf]);
             __syncwarp();
         }
-        if (lane == 0) umma_commit(accum_bar);
-        __syncwarp();
     } else {
         // ------------------------------------------------------------------ epilogue (warps 2..5)
         const int q = warp & 3;  // TMEM lane quarter this warp may read
         const int r = q * 32 + lane;
-        const int lx = r % args.bw;
-        const int ly = (r / args.bw) % args.bh;
-        const int ln = r / (args.bw * args.bh);
-        const int px = x0 + lx, py = y0 + ly, pn = n0 + ln;
-        const bool row_ok = (px < args.ow) && (py < args.oh) && (pn < args.on);
-        const long long o_off = pn * args.out_sn + py * args.out_sy + px * args.out_sx;
-        const long long r_off = pn * args.res_sn + py * args.res_sy + px * args.res_sx;
+        const int et = threadIdx.x - 64;
+        const int rpi = args.bw * args.bh;  // tile rows per image
+        const int lx = r % args.bw, ly = (r / args.bw) % args.bh, ln = r / rpi;
+        auto load_residual = [&](const Tile& t) {
+            int np = 0;
+#pragma unroll
+            for (int p = 0; p < PANELS; ++p)
+                if (t.col_t * BN + p * 64 < args.n_out) ++np;
+            mbar_expect_tx(res_bar, np * PANEL_BYTES);
+#pragma unroll
+            for (int p = 0; p < PANELS; ++p)
+                if (t.col_t * BN + p * 64 < args.n_out)
+                    tma_load_4d(staging + p * PANEL_BYTES, &args.res_map, res_bar, t.col_t * BN + p * 64, t.x0, t.y0,
+                                t.n0);
+        };
+        if (args.tma_res && et == 0 && blockIdx.x < args.num_tiles) load_residual(decode_tile(args, blockIdx.x));
 
-        mbar_wait(accum_bar, 0);
-        tc_fence_after();
+        int lt = 0;
+        for (int tile = blockIdx.x; tile < args.num_tiles; tile += gridDim.x, ++lt) {
+            const Tile t = decode_tile(args, tile);
+            const int buf = lt & 1;
+            const int px = t.x0 + lx, py = t.y0 + ly, pn = t.n0 + ln;
+            const bool row_ok = (px < args.ow) && (py < args.oh) && (pn < args.on);
+            const int pnc = pn < args.on ? pn : args.on - 1;  // clamped image index for per-image operand reads
+            const long long o_off = pn * args.out_sn + py * args.out_sy + px * args.out_sx;
+            const long long r_off = pn * args.res_sn + py * args.res_sy + px * args.res_sx;
+
+            mbar_wait(&tfull_bar[buf], (lt >> 1) & 1);
+            tc_fence_after();
+            if (args.tma_res) mbar_wait(res_bar, lt & 1);
 #pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
-            const int col0 = col_t * BN + c * 32;
-            if (col0 >= args.n_out) break;  // warp-uniform
-            uint32_t acc[32];
-            tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c * 32, acc);
-            tmem_ld_wait();
-            if (!row_ok) continue;
+            for (int c = 0; c < BN / 32; ++c) {
+                const int col0 = t.col_t * BN + c * 32;
+                if (col0 >= args.n_out) break;  // warp-uniform
+                uint32_t acc[32];
+                tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + c * 32, acc);
+                tmem_ld_wait();
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
-                const int col = col0 + g * 8;
-                if (col >= args.n_out) break;
-                const int nv = min(8, args.n_out - col);
-                float v[8];
+                for (int g = 0; g < 4; ++g) {
+                    const int col = col0 + g * 8;
+                    if (col >= args.n_out) break;
+                    const int nv = min(8, args.n_out - col);
+                    float v[8];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(acc[g * 8 + j]);
-                if (args.bias) {
+                    for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(acc[g * 8 + j]);
+                    epilogue8(args, v, col, nv, pnc);
+                    if (BN >= 64 && args.tma_out) {
+                        const int jj = c * 4 + g;  // 16-byte chunk index within the tile row
+                        uint4* sp = reinterpret_cast<uint4*>(staging + (jj >> 3) * PANEL_BYTES + r * 128 +
+                                                             (((jj & 7) ^ (r & 7)) << 4));
+                        if (args.tma_res) {
+                            float f[8];
+                            unpack8(*sp, f);
 #pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        if (j < nv) v[j] += __ldg(args.bias + col + j);
-                }
-                if (args.rowbias) {
-                    const __nv_bfloat16* rb = args.rowbias + pn * args.rowbias_ld + col;
+                            for (int j = 0; j < 8; ++j) v[j] += f[j];
+                        } else if (args.residual && row_ok) {
+                            float f[8];
+                            load8_bf16(args.residual + r_off + col, nv, f);
 #pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        if (j < nv) v[j] += __bfloat162float(rb[j]);
-                }
+                            for (int j = 0; j < 8; ++j) v[j] += f[j];
+                        }
+                        *sp = pack8(v);
+                    } else if (row_ok) {
+                        if (args.residual) {
+                            float f[8];
+                            load8_bf16(args.residual + r_off + col, nv, f);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] = apply_act(v[j], args.act);
-                if (args.gate) {
-                    const __nv_bfloat16* gp = args.gate + pn * args.gate_ld + col;
+                            for (int j = 0; j < 8; ++j) v[j] += f[j];
+                        }
+                        if (args.out_f32) {
+                            float* op = static_cast<float*>(args.out) + o_off + col;
+                            if (nv == 8 && ((reinterpret_cast<uintptr_t>(op) & 15) == 0)) {
+                                reinterpret_cast<float4*>(op)[0] = make_float4(v[0], v[1], v[2], v[3]);
+                                reinterpret_cast<float4*>(op)[1] = make_float4(v[4], v[5], v[6], v[7]);
+                            } else {
 #pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        if (j < nv) v[j] *= __bfloat162float(gp[j]);
-                }
-                if (args.residual) {
-                    const __nv_bfloat16* rp = args.residual + r_off + col;
-                    if (nv == 8 && ((reinterpret_cast<uintptr_t>(rp) & 15) == 0)) {
-                        float f[8];
-                        unpack8(*reinterpret_cast<const uint4*>(rp), f);
+                                for (int j = 0; j < 8; ++j)
+                                    if (j < nv) op[j] = v[j];
+                            }
+                        } else {
+                            __nv_bfloat16* op = static_cast<__nv_bfloat16*>(args.out) + o_off + col;
+                            if (nv == 8 && ((reinterpret_cast<uintptr_t>(op) & 15) == 0)) {
+                                *reinterpret_cast<uint4*>(op) = pack8(v);
+                            } else {
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) v[j] += f[j];
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j)
-                            if (j < nv) v[j] += __bfloat162float(rp[j]);
+                                for (int j = 0; j < 8; ++j)
+                                    if (j < nv) op[j] = __float2bfloat16_rn(v[j]);
+                            }
+                        }
                     }
                 }
-                if (args.out_f32) {
-                    float* op = static_cast<float*>(args.out) + o_off + col;
-                    if (nv == 8 && ((reinterpret_cast<uintptr_t>(op) & 15) == 0)) {
-                        reinterpret_cast<float4*>(op)[0] = make_float4(v[0], v[1], v[2], v[3]);
-                        reinterpret_cast<float4*>(op)[1] = make_float4(v[4], v[5], v[6], v[7]);
-                    } else {
+            }
+            tc_fence_before();
+            mbar_arrive(&tempty_bar[buf]);  // accumulator free: the MMA warp may start tile lt+2 in it
+
+            if (BN >= 64 && args.tma_out) {
+                fence_proxy_async();  // staging writes (generic proxy) -> visible to the TMA store (async proxy)
+                named_bar_sync(1, EPI_THREADS);
+                if (et == 0) {
 #pragma unroll
-                        for (int j = 0; j < 8; ++j)
-                            if (j < nv) op[j] = v[j];
-                    }
-                } else {
-                    __nv_bfloat16* op = static_cast<__nv_bfloat16*>(args.out) + o_off + col;
-                    if (nv == 8 && ((reinterpret_cast<uintptr_t>(op) & 15) == 0)) {
-                        uint4 pk;
-                        __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
-                        *reinterpret_cast<uint4*>(op) = pk;
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j)
-                            if (j < nv) op[j] = __float2bfloat16_rn(v[j]);
+                    for (int p = 0; p < PANELS; ++p)
+                        if (t.col_t * BN + p * 64 < args.n_out)
+                            tma_store_4d(&args.out_map, staging + p * PANEL_BYTES, t.col_t * BN + p * 64, t.x0, t.y0,
+                                         t.n0);
+                    tma_store_commit();
+                }
+                if (args.stats) {
+                    // per-channel sum / sum of squares of the bf16-rounded tile, one partial per (image, tile slot):
+                    // thread -> (column c of a 64-column panel, row half); deterministic (no atomics)
+                    const int c = et & 63, half = et >> 6;
+#pragma unroll 1
+                    for (int p = 0; p < PANELS; ++p) {
+                        const int col = t.col_t * BN + p * 64 + c;
+                        const uint8_t* pb = staging + p * PANEL_BYTES + (c & 7) * 2;
+                        float s = 0.f, ss = 0.f;
+                        int cur = -1;
+                        auto flush = [&](int img_l) {
+                            const int img = t.n0 + img_l;
+                            if (col < args.n_out && img < args.on) {
+                                float* dst = args.stats +
+                                             ((static_cast<long long>(img) * args.stats_p + args.stats_slot0 + t.slot) *
+                                                  args.stats_ld + col) * 2;
+                                dst[0] = s, dst[1] = ss;
+                            }
+                        };
+                        for (int rr = half * 64; rr < half * 64 + 64; ++rr) {
+                            const int il = rr / rpi;
+                            if (rpi < 128 && il != cur) {
+                                if (cur >= 0) flush(cur);
+                                cur = il, s = 0.f, ss = 0.f;
+                            }
+                            const int x = rr % args.bw, y = (rr / args.bw) % args.bh;
+                            if (t.x0 + x < args.ow && t.y0 + y < args.oh) {
+                                const float f = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(
+                                    pb + rr * 128 + (((c >> 3) ^ (rr & 7)) << 4)));
+                                s += f, ss += f * f;
+                            }
+                        }
+                        if (rpi < 128) {
+                            flush(cur);
+                        } else {  // the tile lies in one image: combine the two row halves
+                            if (half == 1) red[c * 2] = s, red[c * 2 + 1] = ss;
+                            named_bar_sync(2, EPI_THREADS);
+                            if (half == 0) {
+                                s += red[c * 2], ss += red[c * 2 + 1];
+                                flush(0);
+                            }
+                            named_bar_sync(2, EPI_THREADS);
+                        }
                     }
                 }
+                if (et == 0) tma_store_wait_read();
+                named_bar_sync(1, EPI_THREADS);  // staging may be overwritten
+                if (args.tma_res && et == 0 && tile + gridDim.x < args.num_tiles)
+                    load_residual(decode_tile(args, tile + gridDim.x));
             }
         }
         tc_fence_before();
@@ -294,20 +463,35 @@ static int encode_map(CUtensorMap* m, const void* base, int rank, const uint64_t
     return B200SD_OK;
 }
 
-template <int BN, int STAGES, int MIN_CTAS>
+// (columns, ow, oh, on) view of a pixel-strided bf16 tensor for the epilogue's TMA store / residual load
+static bool pixel_view_ok(const void* base, long long sn, long long sy, long long sx) {
+    if (reinterpret_cast<uintptr_t>(base) & 15) return false;
+    for (long long s : {sn, sy, sx})
+        if (s < 0 || (s * 2) % 16 != 0) return false;
+    return true;
+}
+static int encode_pixel_view(CUtensorMap* m, const void* base, int cols, int ow, int oh, int on, long long sn,
+                             long long sy, long long sx, const uint32_t* box) {
+    auto fix = [](long long s) { return (uint64_t)(s > 0 ? s * 2 : 16); };  // extent-1 dims may carry stride 0
+    uint64_t dims[4] = {(uint64_t)cols, (uint64_t)ow, (uint64_t)oh, (uint64_t)on};
+    uint64_t str[3] = {fix(sx), fix(sy), fix(sn)};
+    return encode_map(m, base, 4, dims, str, box);
+}
+
+template <int BN, int STAGES>
 static int launch_igemm(const IgemmArgs& a, int grid, cudaStream_t st) {
     using L = IgemmSmem<BN, STAGES>;
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(igemm_kernel<BN, STAGES, MIN_CTAS>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL);
+        cudaError_t e = cudaFuncSetAttribute(igemm_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             L::TOTAL);
         if (e != cudaSuccess) {
             set_error("igemm: cannot set %d B dynamic smem: %s", L::TOTAL, cudaGetErrorString(e));
             return B200SD_ERR_CUDA;
         }
         configured = true;
     }
-    igemm_kernel<BN, STAGES, MIN_CTAS><<<grid, IGEMM_THREADS, L::TOTAL, st>>>(a);
+    igemm_kernel<BN, STAGES><<<grid, IGEMM_THREADS, L::TOTAL, st>>>(a);
     B200_CHECK_LAUNCH("igemm");
     return B200SD_OK;
 }
@@ -324,8 +508,6 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
     B200_REQUIRE(p->n_out >= 1, "igemm: n_out=%d", p->n_out);
     B200_REQUIRE(p->on >= 1 && p->oh >= 1 && p->ow >= 1, "igemm: empty output grid %dx%dx%d", p->on, p->oh, p->ow);
     B200_REQUIRE(p->out_dtype == B200SD_DT_BF16 || p->out_dtype == B200SD_DT_F32, "igemm: bad out dtype");
-    B200_REQUIRE(p->stats == nullptr, "igemm: fused statistics are not built in this version");
-    if (p->stats) return B200SD_ERR_UNSUPPORTED;
 
     IgemmArgs a;
     memset(&a, 0, sizeof(a));
@@ -351,6 +533,7 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
     a.n_seg = p->n_seg;
     a.total_chunks = total;
 
+    const uint32_t abox[4] = {(uint32_t)BK, (uint32_t)bw, (uint32_t)bh, (uint32_t)bn};
     for (int i = 0; i < p->n_src; ++i) {
         const b200sd_src& s = p->srcs[i];
         B200_REQUIRE(s.base && (reinterpret_cast<uintptr_t>(s.base) & 15) == 0, "igemm: source %d base unaligned", i);
@@ -360,25 +543,29 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
                          (long long)s.strides[d]);
         uint64_t dims[4] = {(uint64_t)s.dims[0], (uint64_t)s.dims[1], (uint64_t)s.dims[2], (uint64_t)s.dims[3]};
         uint64_t str[3] = {(uint64_t)s.strides[0], (uint64_t)s.strides[1], (uint64_t)s.strides[2]};
-        uint32_t box[4] = {(uint32_t)BK, (uint32_t)bw, (uint32_t)bh, (uint32_t)bn};
-        int rc = encode_map(&a.a_map[i], s.base, 4, dims, str, box);
+        int rc = encode_map(&a.a_map[i], s.base, 4, dims, str, abox);
         if (rc) return rc;
     }
     for (int i = p->n_src; i < 4; ++i) a.a_map[i] = a.a_map[0];
 
-    // column tile: largest of {256,192,128,96,64,32} that divides n_out, else by size
+    // column tile: the persistent grid runs ceil(tiles / SMs) waves of tiles whose cost grows like BN + const
     const int n = p->n_out;
-    int BNsel;
     const long long m_tiles = (long long)a.tiles_x * a.tiles_y * a.tiles_img;
-    if (n % 256 == 0 && m_tiles * (n / 256) >= 2 * sm_count()) BNsel = 256;
-    else if (n % 192 == 0 && m_tiles * (n / 192) >= 2 * sm_count()) BNsel = 192;
-    else if (n % 128 == 0 && m_tiles * (n / 128) >= sm_count()) BNsel = 128;
-    else if (n % 96 == 0 && n % 64 != 0) BNsel = 96;
-    else if (n >= 64 && m_tiles * ((n + 63) / 64) >= sm_count() / 2) BNsel = 64;
-    else if (n > 32 && n % 64 == 0) BNsel = 64;
-    else BNsel = n > 64 ? 64 : 32;
-    if (n <= 32) BNsel = 32;
+    const int sms = sm_count();
+    int BNsel = 32;
+    if (n > 32) {
+        long long best = -1;
+        for (int bnc : {256, 128, 64}) {
+            if (bnc > 64 && n <= bnc / 2) continue;
+            const long long tiles = m_tiles * ((n + bnc - 1) / bnc);
+            const long long cost = ((tiles + sms - 1) / sms) * (bnc + 64);
+            if (best < 0 || cost < best) best = cost, BNsel = bnc;
+        }
+    }
     a.tiles_col = (n + BNsel - 1) / BNsel;
+    const long long tiles_ll = m_tiles * a.tiles_col;
+    B200_REQUIRE(tiles_ll < (1ll << 31), "igemm: too many tiles");
+    a.num_tiles = (int)tiles_ll;
 
     {
         B200_REQUIRE((reinterpret_cast<uintptr_t>(p->weight) & 15) == 0, "igemm: weight unaligned");
@@ -402,16 +589,47 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
     a.res_sn = p->res_sn, a.res_sy = p->res_sy, a.res_sx = p->res_sx;
     a.act = p->act;
 
-    const long long grid_ll = m_tiles * a.tiles_col;
-    B200_REQUIRE(grid_ll < (1ll << 31), "igemm: grid too large");
-    const int grid = (int)grid_ll;
+    // epilogue route: TMA tensor store from a staged bf16 tile when the output is addressable that way
+    a.tma_out = BNsel >= 64 && !a.out_f32 && pixel_view_ok(p->out, p->out_sn, p->out_sy, p->out_sx);
+    if (a.tma_out) {
+        int rc = encode_pixel_view(&a.out_map, p->out, n, p->ow, p->oh, p->on, p->out_sn, p->out_sy, p->out_sx, abox);
+        if (rc) return rc;
+        a.tma_res = p->residual && pixel_view_ok(p->residual, p->res_sn, p->res_sy, p->res_sx);
+        if (a.tma_res) {
+            rc = encode_pixel_view(&a.res_map, p->residual, n, p->ow, p->oh, p->on, p->res_sn, p->res_sy, p->res_sx,
+                                   abox);
+            if (rc) return rc;
+        }
+    }
+    if (p->stats) {
+        if (!a.tma_out) {
+            set_error("igemm: fused statistics need the staged bf16 epilogue (bf16 output, 16-byte aligned pitch, "
+                      "more than 32 output channels)");
+            return B200SD_ERR_UNSUPPORTED;
+        }
+        const int per_img = bn > 1 ? 1 : a.tiles_x * a.tiles_y;
+        B200_REQUIRE(p->stats_slot0 >= 0 && p->stats_slot0 + per_img <= p->stats_p && p->stats_ld >= n,
+                     "igemm: statistics buffer has %d slots (need %d from slot %d) and pitch %d (need %d)", p->stats_p,
+                     per_img, p->stats_slot0, p->stats_ld, n);
+        a.stats = p->stats, a.stats_p = p->stats_p, a.stats_slot0 = p->stats_slot0, a.stats_ld = p->stats_ld;
+    }
+
+    const int grid = a.num_tiles < sms ? a.num_tiles : sms;
     cudaStream_t st = as_stream(stream);
     switch (BNsel) {
-        case 256: return launch_igemm<256, 4, 1>(a, grid, st);
-        case 192: return launch_igemm<192, 4, 1>(a, grid, st);
-        case 128: return launch_igemm<128, 3, 2>(a, grid, st);
-        case 96: return launch_igemm<96, 3, 2>(a, grid, st);
-        case 64: return launch_igemm<64, 4, 2>(a, grid, st);
-        default: return launch_igemm<32, 4, 2>(a, grid, st);
+        case 256: return launch_igemm<256, 3>(a, grid, st);
+        case 128: return launch_igemm<128, 5>(a, grid, st);
+        case 64: return launch_igemm<64, 6>(a, grid, st);
+        default: return launch_igemm<32, 6>(a, grid, st);
     }
+}
+
+/* Number of per-image partial-statistics slots one b200sd_igemm call with this output grid writes. */
+extern "C" int b200sd_igemm_stats_slots(int oh, int ow) {
+    int bw = ow >= BM ? BM : 1;
+    while (bw < ow && bw < BM) bw <<= 1;
+    int bh = 1;
+    while (bw * bh < BM && bh < oh) bh <<= 1;
+    if (bw * bh < BM) return 1;
+    return ((ow + bw - 1) / bw) * ((oh + bh - 1) / bh);
 }

@@ -113,6 +113,86 @@ __global__ void __launch_bounds__(512)
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// GroupNorm APPLY on precomputed partial statistics (written by the producing igemm's epilogue, b200sd.h `stats`):
+// the tensor is read once and written once, fully coalesced 16-byte accesses, any number of CTAs per image.
+// Prologue per CTA: fold the P partial (sum, sumsq) slots of every channel in fixed order (bit-reproducible), reduce
+// channels to groups, turn (mean, rstd, gamma, beta) into a per-channel scale/shift held in registers.
+struct StatSeg {
+    const float* ptr;
+    int p, ld;
+};
+
+__global__ void __launch_bounds__(256)
+    gn_apply_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, __nv_bfloat16* __restrict__ y, long long ld_y,
+                    StatSeg s0, int c_split, StatSeg s1, const float* __restrict__ gamma,
+                    const float* __restrict__ beta, long long hw, int c, int groups, float eps, int act,
+                    int rows_per_block, int rpp) {
+    extern __shared__ float gn_sm[];
+    float* sc = gn_sm;          // [c]  channel sums, then scale
+    float* sh = gn_sm + c;      // [c]  channel sums of squares, then shift
+    float* gs = gn_sm + 2 * c;  // [groups][2] mean, rstd
+    const int img = blockIdx.y;
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const int cpg = c / groups;
+    for (int ch = tid; ch < c; ch += nt) {
+        const bool first = ch < c_split;
+        const StatSeg sg = first ? s0 : s1;
+        const int cc = first ? ch : ch - c_split;
+        const float* p = sg.ptr + (static_cast<long long>(img) * sg.p * sg.ld + cc) * 2;
+        float a = 0.f, b = 0.f;
+        for (int k = 0; k < sg.p; ++k) {
+            const float2 v = *reinterpret_cast<const float2*>(p + static_cast<long long>(k) * sg.ld * 2);
+            a += v.x, b += v.y;
+        }
+        sc[ch] = a, sh[ch] = b;
+    }
+    __syncthreads();
+    const float inv_cnt = 1.f / (static_cast<float>(hw) * cpg);
+    for (int g = tid; g < groups; g += nt) {
+        float a = 0.f, b = 0.f;
+        for (int k = 0; k < cpg; ++k) a += sc[g * cpg + k], b += sh[g * cpg + k];
+        const float mean = a * inv_cnt;
+        const float var = fmaxf(b * inv_cnt - mean * mean, 0.f);
+        gs[2 * g] = mean, gs[2 * g + 1] = rsqrtf(var + eps);
+    }
+    __syncthreads();
+    for (int ch = tid; ch < c; ch += nt) {
+        const int g = ch / cpg;
+        const float ga = gamma ? gamma[ch] : 1.f, be = beta ? beta[ch] : 0.f;
+        const float scale = gs[2 * g + 1] * ga;
+        sc[ch] = scale, sh[ch] = be - gs[2 * g] * scale;
+    }
+    __syncthreads();
+    const int cv = c >> 3;
+    const int v = tid % cv, r0 = tid / cv;
+    if (r0 >= rpp) return;
+    float scl[8], sft[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) scl[j] = sc[v * 8 + j], sft[j] = sh[v * 8 + j];
+    const long long row_begin = static_cast<long long>(blockIdx.x) * rows_per_block;
+    long long row_end = row_begin + rows_per_block;
+    if (row_end > hw) row_end = hw;
+    const __nv_bfloat16* xs = x + static_cast<long long>(img) * hw * ld_x + v * 8;
+    __nv_bfloat16* ys = y + static_cast<long long>(img) * hw * ld_y + v * 8;
+#pragma unroll 4
+    for (long long r = row_begin + r0; r < row_end; r += rpp) {
+        const uint4 u = *reinterpret_cast<const uint4*>(xs + r * ld_x);
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+        uint4 o;
+        __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float2 f = __bfloat1622float2(h[j]);
+            f.x = act_apply(f.x * scl[2 * j] + sft[2 * j], act);
+            f.y = act_apply(f.y * scl[2 * j + 1] + sft[2 * j + 1], act);
+            oh[j] = __floats2bfloat162_rn(f.x, f.y);
+        }
+        *reinterpret_cast<uint4*>(ys + r * ld_y) = o;
+    }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -171,5 +251,43 @@ extern "C" int b200sd_groupnorm(const void* x, int64_t ld_x, void* y, int64_t ld
             static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y, gamma, beta, hw, c, cpg,
             gpc, eps, act, cached, rows_per_pass);
     B200_CHECK_LAUNCH("groupnorm");
+    return B200SD_OK;
+}
+
+extern "C" int b200sd_groupnorm_apply(const void* x, int64_t ld_x, void* y, int64_t ld_y, const float* stats0, int p0,
+                                      int ld_s0, int c_split, const float* stats1, int p1, int ld_s1,
+                                      const float* gamma, const float* beta, int64_t n, int64_t hw, int c, int groups,
+                                      float eps, int act, void* stream) {
+    B200_REQUIRE(x && y && stats0, "groupnorm_apply: null pointer");
+    B200_REQUIRE(groups > 0 && c > 0 && c % groups == 0, "groupnorm_apply: %d channels not divisible by %d groups", c,
+                 groups);
+    B200_REQUIRE(c % 8 == 0 && c <= 2048 && ld_x % 8 == 0 && ld_y % 8 == 0 && ld_x >= c && ld_y >= c,
+                 "groupnorm_apply: needs channels %% 8 == 0, <= 2048 and 16-byte aligned row pitches");
+    B200_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15) == 0,
+                 "groupnorm_apply: pointers unaligned");
+    B200_REQUIRE(c_split >= 0 && c_split <= c && (c_split == c || stats1), "groupnorm_apply: bad statistics split");
+    B200_REQUIRE(p0 >= 1 && ld_s0 >= c_split && (c_split == c || (p1 >= 1 && ld_s1 >= c - c_split)),
+                 "groupnorm_apply: bad statistics geometry");
+    B200_REQUIRE(n <= 65535, "groupnorm_apply: batch exceeds grid limit");
+    if (n == 0 || hw == 0) return B200SD_OK;
+    const int cv = c / 8;
+    int rpp = 256 / cv;  // rows a CTA covers per pass
+    if (rpp > hw) rpp = (int)hw;
+    const int threads = ((cv * rpp + 31) / 32) * 32;
+    // ~4 CTAs per SM overall, each at least 8 passes deep so the statistics prologue is amortised
+    long long blocks_per_img = (4ll * sm_count() + n - 1) / n;
+    long long max_bpi = (hw + 8ll * rpp - 1) / (8ll * rpp);
+    if (blocks_per_img > max_bpi) blocks_per_img = max_bpi;
+    if (blocks_per_img < 1) blocks_per_img = 1;
+    long long rows_per_block = (hw + blocks_per_img - 1) / blocks_per_img;
+    rows_per_block = (rows_per_block + rpp - 1) / rpp * rpp;
+    blocks_per_img = (hw + rows_per_block - 1) / rows_per_block;
+    const size_t smem = (size_t)(2 * c + 2 * groups) * sizeof(float);
+    StatSeg s0{stats0, p0, ld_s0}, s1{stats1, p1, ld_s1};
+    dim3 grid((unsigned)blocks_per_img, (unsigned)n);
+    gn_apply_kernel<<<grid, threads, smem, as_stream(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y, s0, c_split, s1, gamma, beta,
+        hw, c, groups, eps, act, (int)rows_per_block, rpp);
+    B200_CHECK_LAUNCH("groupnorm_apply");
     return B200SD_OK;
 }

@@ -19,11 +19,16 @@ from . import ops
 from . import runtime as rt
 
 
-class Act:
-    __slots__ = ("t", "n", "h", "w", "c")
+FUSE_GN_STATS = True  # producers leave partial GroupNorm statistics for their consumer (tests flip this)
 
-    def __init__(self, t, n, h, w, c):
-        self.t, self.n, self.h, self.w, self.c = t, n, h, w, c
+
+class Act:
+    """stats: None, or a list of (fp32 [n, P, ld, 2] partial sums, P, ld, channels) segments covering the channels in
+    order — written by the igemm epilogue(s) that produced this tensor, consumed by the next GroupNorm."""
+    __slots__ = ("t", "n", "h", "w", "c", "stats")
+
+    def __init__(self, t, n, h, w, c, stats=None):
+        self.t, self.n, self.h, self.w, self.c, self.stats = t, n, h, w, c, stats
 
     @property
     def ld(self):
@@ -94,15 +99,28 @@ def _act_name(m):
 
 
 # ------------------------------------------------------------------------------------------ leaf operators
+def _new_stats(n, oh, ow, c, device, phases=1):
+    """Statistics buffer for an igemm writing an (n, oh, ow, c) bf16 tensor, or None when the staged epilogue that
+    computes them does not apply (fewer than 33 channels / pitch not 16-byte aligned)."""
+    if not FUSE_GN_STATS or c <= 32 or c % 8:
+        return None
+    p = rt.stats_slots(oh, ow) * phases
+    return (torch.empty(n, p, c, 2, device=device, dtype=torch.float32), p, c)
+
+
 def group_norm(a, mod, act=None):
     _require_leaf(mod, (nn.GroupNorm,), "GroupNorm")
     out = Act.empty(a.n, a.h, a.w, a.c, a.t.device)
+    if a.stats is not None and len(a.stats) <= 2 and a.c % 8 == 0 and a.ld % 8 == 0 and a.c <= 2048:
+        rt.groupnorm_apply(a.t, a.n, a.hw, a.c, mod.num_groups, _f32(mod.weight), _f32(mod.bias), a.stats, mod.eps,
+                           act=act, out=out.t, ld_x=a.ld, ld_y=a.c)
+        return out
     rt.groupnorm(a.t, a.n, a.hw, a.c, mod.num_groups, _f32(mod.weight), _f32(mod.bias), mod.eps, act=act, out=out.t,
                  ld_x=a.ld, ld_y=a.c)
     return out
 
 
-def conv2d(a, mod, rowbias=None, extra=None, act=None, out=None, c_off=0, out_dtype=torch.bfloat16):
+def conv2d(a, mod, rowbias=None, extra=None, act=None, out=None, c_off=0, out_dtype=torch.bfloat16, stats=True):
     """nn.Conv2d leaf on an Act. `extra` = (Act, 1x1 nn.Conv2d) fuses a second 1x1 convolution of another tensor
     into the same accumulator (ResNet shortcut)."""
     if hasattr(mod, "forward_act") and extra is None and rowbias is None:
@@ -132,15 +150,21 @@ def conv2d(a, mod, rowbias=None, extra=None, act=None, out=None, c_off=0, out_dt
             o = torch.empty(a.n * a.hw, (cout + 7) // 8 * 8, device=a.t.device, dtype=out_dtype)
         else:
             o = out.t
+        st = _new_stats(a.n, a.h, a.w, cout, a.t.device) if (stats and out is None and o.dtype == torch.bfloat16) \
+            else None
         ops.conv_same(a.t, a.n, a.h, a.w, a.c, wmat, cout, k[0], bias=bias, ld_x=a.ld, out=o, c_off=c_off,
-                      rowbias=rowbias, act=act, extra=ex)
-        return out if out is not None else Act(o, a.n, a.h, a.w, cout)
+                      rowbias=rowbias, act=act, extra=ex, stats=None if st is None else (st[0], st[1], 0, st[2]))
+        return out if out is not None else Act(o, a.n, a.h, a.w, cout, None if st is None else [st + (cout,)])
     if k == (4, 4) and s == (2, 2) and p == (1, 1) and extra is None and rowbias is None:
         if a.h % 2 or a.w % 2:
             raise rt.B200Error("4x4 stride-2 convolution needs even spatial size")
         wmat = CACHE.get(mod, "w", (mod.weight,), lambda: ops.pack_conv_weight(mod.weight))
         o = Act.empty(a.n, a.h // 2, a.w // 2, cout, a.t.device) if out is None else out
-        ops.conv_down4x4(a.t, a.n, a.h, a.w, a.c, wmat, cout, bias=_f32(mod.bias), ld_x=a.ld, out=o.t)
+        st = _new_stats(a.n, a.h // 2, a.w // 2, cout, a.t.device) if (stats and out is None) else None
+        ops.conv_down4x4(a.t, a.n, a.h, a.w, a.c, wmat, cout, bias=_f32(mod.bias), ld_x=a.ld, out=o.t,
+                         stats=None if st is None else (st[0], st[1], 0, st[2]))
+        if st is not None:
+            o.stats = [st + (cout,)]
         return o
     raise rt.B200Error(f"Conv2d: kernel {k} stride {s} padding {p} has no CUDA path")
 
@@ -152,18 +176,23 @@ def conv_transpose2d(a, mod, out=None, c_off=0):
     phases = CACHE.get(mod, "w", (mod.weight,), lambda: ops.pack_convT_weight(mod.weight))
     cout = mod.out_channels
     o = Act.empty(a.n, 2 * a.h, 2 * a.w, cout, a.t.device) if out is None else out
-    ops.conv_up4x4(a.t, a.n, a.h, a.w, a.c, phases, cout, bias=_f32(mod.bias), ld_x=a.ld, out=o.t, c_off=c_off)
-    return o
+    st = _new_stats(a.n, a.h, a.w, cout, a.t.device, phases=4)
+    ops.conv_up4x4(a.t, a.n, a.h, a.w, a.c, phases, cout, bias=_f32(mod.bias), ld_x=a.ld, out=o.t, c_off=c_off,
+                   stats=st)
+    if out is None and st is not None:
+        o.stats = [st + (cout,)]
+    return o, (None if st is None else st + (cout,))
 
 
-def linear(x, mod, act=None, residual=None, out_dtype=torch.bfloat16, rows_per_img=None, rowbias=None, gate=None):
+def linear(x, mod, act=None, residual=None, out_dtype=torch.bfloat16, rows_per_img=None, rowbias=None, gate=None,
+           stats=None):
     """nn.Linear leaf on a 2-D bf16 matrix."""
     if hasattr(mod, "forward_rows") and residual is None and gate is None and rowbias is None:
         return mod.forward_rows(x, act=act)
     _require_leaf(mod, (nn.Linear, nn.modules.linear.NonDynamicallyQuantizableLinear), "Linear")
     wmat = CACHE.get(mod, "w", (mod.weight,), lambda: ops.pack_linear_weight(mod.weight))
     return rt.linear(x, wmat, bias=_f32(mod.bias), act=act, residual=residual, out_dtype=out_dtype,
-                     rows_per_img=rows_per_img, rowbias=rowbias, gate=gate)
+                     rows_per_img=rows_per_img, rowbias=rowbias, gate=gate, stats=stats)
 
 
 def _mha_weights(mha):
@@ -200,6 +229,17 @@ def _mha_weights(mha):
     return CACHE.get(mha, "in_proj", srcs, build)
 
 
+def _out_proj(o, mha, a):
+    """out_proj GEMM with the residual add (and the next GroupNorm's statistics) in its epilogue."""
+    C = a.c
+    proj = mha.out_proj
+    if hasattr(proj, "forward_rows"):
+        return add(Act(linear(o, proj), a.n, a.h, a.w, C), a)
+    st = _new_stats(a.n, 1, a.hw, C, a.t.device)
+    out = linear(o, proj, residual=a.t, rows_per_img=a.hw, stats=None if st is None else (st[0], st[1], 0, st[2]))
+    return Act(out, a.n, a.h, a.w, C, None if st is None else [st + (C,)])
+
+
 def self_attention(a, norm, mha):
     """x + out_proj(MHA(GN(x))) — blocks.py:122-131. One QKV GEMM, flash attention, out-proj GEMM with the residual
     add in its epilogue."""
@@ -208,8 +248,7 @@ def self_attention(a, norm, mha):
     pk = _mha_weights(mha)
     qkv = rt.linear(xn.t, pk["qkv"], bias=pk["b_qkv"])
     o = rt.attention(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], a.n, heads, a.hw, a.hw, C // heads)
-    out = linear(o, mha.out_proj, residual=a.t)
-    return Act(out, a.n, a.h, a.w, C)
+    return _out_proj(o, mha, a)
 
 
 class Context:
@@ -251,8 +290,7 @@ def cross_attention(a, norm, mha, ctx_proj_mod, ctx, lk, cache=None):
         if cache is not None and cache.persistent:
             cache.kv[id(mha)] = kv
     o = rt.attention(q, kv[:, :C], kv[:, C:], a.n, heads, a.hw, lk, C // heads)
-    out = linear(o, mha.out_proj, residual=a.t)
-    return Act(out, a.n, a.h, a.w, C)
+    return _out_proj(o, mha, a)
 
 
 def resnet(a, first, temb_layer, second, shortcut, temb_act):
@@ -310,9 +348,14 @@ def upsample_concat(a, up_conv, skip):
         raise rt.B200Error("skip tensor shape does not match the upsampled tensor")
     out = Act.empty(a.n, h, w, c_tot, a.t.device)
     if up_conv is not None:
-        conv_transpose2d(a, up_conv, out=out, c_off=0)
+        _, st_up = conv_transpose2d(a, up_conv, out=out, c_off=0)
     else:
         rt.copy_act(a.t, out.t, 0)
+        st_up = a.stats[0] if a.stats is not None and len(a.stats) == 1 else None
+    segs = [st_up]
     if skip is not None:
         rt.copy_act(skip.t[:, :skip.c] if skip.ld != skip.c else skip.t, out.t, c_up)
+        segs.append(skip.stats[0] if skip.stats is not None and len(skip.stats) == 1 else None)
+    if all(sg is not None for sg in segs):
+        out.stats = segs  # channel-concat of tensors whose producers each left their own partial statistics
     return out

@@ -52,7 +52,7 @@ def pack_convT_weight(w):
 
 
 def conv_same(x, n, h, w, cin, wmat, cout, k, bias=None, ld_x=None, out=None, ld_out=None, c_off=0, rowbias=None,
-              residual=None, ld_res=None, act=None, extra=None, out_dtype=torch.bfloat16):
+              residual=None, ld_res=None, act=None, extra=None, out_dtype=torch.bfloat16, stats=None):
     """k x k stride-1 'same' convolution (k in {1, 3}). `extra` = (x2, cin2, ld2): a second source read with a
     1x1 tap whose weights are appended along K (the fused residual_input_conv, blocks.py:104,119)."""
     pad = k // 2
@@ -74,11 +74,11 @@ def conv_same(x, n, h, w, cin, wmat, cout, k, bias=None, ld_x=None, out=None, ld
         ld_res = residual.stride(0) if ld_res is None else ld_res
         rs = (h * w * ld_res, w * ld_res, ld_res)
     rt.igemm(srcs, segs, wmat, cout, n, h, w, o, (h * w * ld_out, w * ld_out, ld_out), bias=bias, rowbias=rowbias,
-             residual=residual, res_strides=rs, act=act)
+             residual=residual, res_strides=rs, act=act, stats=stats)
     return out
 
 
-def conv_down4x4(x, n, h, w, cin, wmat, cout, bias=None, ld_x=None, out=None):
+def conv_down4x4(x, n, h, w, cin, wmat, cout, bias=None, ld_x=None, out=None, stats=None):
     """nn.Conv2d(C, C, 4, 2, 1) (blocks.py:108): iy = 2*oy + ky - 1. The input is read through four stride-2 parity
     views; tap ky uses row parity (ky+1)%2 at coarse row oy + {-1, 0, 0, +1}[ky]."""
     cp = _pad64(cin)
@@ -95,11 +95,11 @@ def conv_down4x4(x, n, h, w, cin, wmat, cout, bias=None, ld_x=None, out=None):
     if out is None:
         out = torch.empty(n * oh * ow, cout, device=x.device, dtype=torch.bfloat16)
     ld = out.stride(0)
-    rt.igemm(srcs, segs, wmat, cout, n, oh, ow, out, (oh * ow * ld, ow * ld, ld), bias=bias)
+    rt.igemm(srcs, segs, wmat, cout, n, oh, ow, out, (oh * ow * ld, ow * ld, ld), bias=bias, stats=stats)
     return out
 
 
-def conv_up4x4(x, n, h, w, cin, phases, cout, bias=None, ld_x=None, out=None, c_off=0):
+def conv_up4x4(x, n, h, w, cin, phases, cout, bias=None, ld_x=None, out=None, c_off=0, stats=None):
     """nn.ConvTranspose2d(C, C, 4, 2, 1) (blocks.py:339,457) as four sub-pixel phase GEMMs writing the interleaved
     (2h, 2w) output directly (optionally into a channel slice of a wider concat buffer)."""
     ld_x = cin if ld_x is None else ld_x
@@ -111,5 +111,8 @@ def conv_up4x4(x, n, h, w, cin, phases, cout, bias=None, ld_x=None, out=None, c_
     for idx, (wmat, segs) in enumerate(phases):
         py, px = idx // 2, idx % 2
         o = flat[(py * 2 * w + px) * ld + c_off:]
-        rt.igemm([src], segs, wmat, cout, n, h, w, o, (4 * h * w * ld, 4 * w * ld, 2 * ld), bias=bias)
+        st = None
+        if stats is not None:  # (tensor, P, ld): each sub-pixel phase owns a quarter of the slots
+            st = (stats[0], stats[1], idx * (stats[1] // 4), stats[2])
+        rt.igemm([src], segs, wmat, cout, n, h, w, o, (4 * h * w * ld, 4 * w * ld, 2 * ld), bias=bias, stats=st)
     return out

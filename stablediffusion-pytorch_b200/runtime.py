@@ -17,7 +17,7 @@ _ACT = {None: 0, "none": 0, "silu": 1, "relu": 2}
 
 EXPORTS = [
     "b200sd_last_error", "b200sd_version", "b200sd_launch_count", "b200sd_sched_add_noise",
-    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_groupnorm", "b200sd_attention",
+    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_attention",
     "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16",
 ]
 
@@ -42,6 +42,7 @@ class IgemmParams(C.Structure):
         ("gate", C.c_void_p), ("gate_ld", C.c_int64),
         ("residual", C.c_void_p), ("res_sn", C.c_int64), ("res_sy", C.c_int64), ("res_sx", C.c_int64),
         ("act", C.c_int32), ("stats", C.c_void_p),
+        ("stats_p", C.c_int32), ("stats_slot0", C.c_int32), ("stats_ld", C.c_int32),
     ]
 
 
@@ -67,7 +68,10 @@ def lib():
         L.b200sd_advance_t.argtypes = [vp, i64, i64, vp]
         L.b200sd_time_embedding.argtypes = [vp, i64, vp, i32, i64, i32, vp]
         L.b200sd_igemm.argtypes = [C.POINTER(IgemmParams), vp]
+        L.b200sd_igemm_stats_slots.argtypes = [i32, i32]
         L.b200sd_groupnorm.argtypes = [vp, i64, vp, i64, vp, vp, i64, i64, i32, i32, f32, i32, vp]
+        L.b200sd_groupnorm_apply.argtypes = [vp, i64, vp, i64, vp, i32, i32, i32, vp, i32, i32, vp, vp, i64, i64, i32, i32,
+                                             f32, i32, vp]
         L.b200sd_attention.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, i64, i32, i32, i32, i32, f32, vp]
         L.b200sd_nchw_to_nhwc.argtypes = [vp, vp, i64, i32, i64, i32, i64, vp]
         L.b200sd_nhwc_to_nchw.argtypes = [vp, i32, i64, vp, i64, i32, i64, vp]
@@ -228,9 +232,14 @@ def make_src(t, n, h, w, c, ld=None, sy=1, sx=1, oy=0, ox=0, hh=None, ww=None):
     return s
 
 
+def stats_slots(oh, ow):
+    return int(lib().b200sd_igemm_stats_slots(int(oh), int(ow)))
+
+
 def igemm(srcs, segs, weight, n_out, on, oh, ow, out, out_strides, bias=None, rowbias=None, gate=None,
-          residual=None, res_strides=None, act=None):
-    """Raw launcher. srcs: list[Src]; segs: list of (src, dy, dx, c0, nchunk); out_strides=(sn, sy, sx) elements."""
+          residual=None, res_strides=None, act=None, stats=None):
+    """Raw launcher. srcs: list[Src]; segs: list of (src, dy, dx, c0, nchunk); out_strides=(sn, sy, sx) elements.
+    stats = (fp32 tensor [on, P, ld, 2], P, slot0, ld[, channel offset]): partial GroupNorm statistics of the output."""
     p = IgemmParams()
     p.n_src, p.n_seg = len(srcs), len(segs)
     for i, s in enumerate(srcs):
@@ -251,6 +260,10 @@ def igemm(srcs, segs, weight, n_out, on, oh, ow, out, out_strides, bias=None, ro
         p.residual = residual.data_ptr()
         p.res_sn, p.res_sy, p.res_sx = res_strides
     p.act = _ACT[act] if not isinstance(act, int) else act
+    if stats is not None:
+        st, sp, s0, sld = stats[:4]
+        coff = stats[4] if len(stats) > 4 else 0
+        p.stats, p.stats_p, p.stats_slot0, p.stats_ld = st.data_ptr() + 8 * coff, sp, s0, sld - coff
     tok = _pb()
     check(lib().b200sd_igemm(C.byref(p), stream_ptr()), "igemm")
     if tok is not None:
@@ -260,7 +273,7 @@ def igemm(srcs, segs, weight, n_out, on, oh, ow, out, out_strides, bias=None, ro
 
 
 def linear(a, weight, bias=None, act=None, residual=None, out=None, out_dtype=torch.bfloat16, rows_per_img=None,
-           rowbias=None, gate=None):
+           rowbias=None, gate=None, stats=None):
     """out[M, N] = act(a[M, K] @ weight[N, Kp]^T + bias) (+ residual). a: bf16 rows with stride a.stride(0) (mult. of
     8), weight: bf16 [N, Kp] with Kp = K rounded up to 64 (zero padded). rows_per_img groups rows into images for the
     per-image rowbias/gate operands."""
@@ -281,10 +294,27 @@ def linear(a, weight, bias=None, act=None, residual=None, out=None, out_dtype=to
     if residual is not None:
         rs = (ow * residual.stride(0), 0, residual.stride(0))
     return igemm([src], [(0, 0, 0, 0, Kp // 64)], weight, N, on, 1, ow, out, (ow * ldo, 0, ldo), bias=bias,
-                 rowbias=rowbias, gate=gate, residual=residual, res_strides=rs, act=act)
+                 rowbias=rowbias, gate=gate, residual=residual, res_strides=rs, act=act, stats=stats)
 
 
 # ------------------------------------------------------------------------------------------------ others
+def groupnorm_apply(x, n, hw, c, groups, gamma, beta, segs, eps=1e-5, act=None, out=None, ld_x=None, ld_y=None):
+    """GroupNorm from partial statistics left by the producing igemm(s). segs: [(stats, P, ld, channels)], 1 or 2."""
+    _cuda(x, torch.bfloat16, "x")
+    ld_x = c if ld_x is None else ld_x
+    if out is None:
+        out = torch.empty(n * hw, c, device=x.device, dtype=torch.bfloat16)
+        ld_y = c
+    ld_y = c if ld_y is None else ld_y
+    (s0, p0, l0, c0) = segs[0]
+    s1, p1, l1 = (segs[1][0], segs[1][1], segs[1][2]) if len(segs) > 1 else (None, 0, 0)
+    tok = _pb()
+    check(lib().b200sd_groupnorm_apply(_p(x), ld_x, _p(out), ld_y, _p(s0), p0, l0, c0 if len(segs) > 1 else c,
+                                        _p(s1), p1, l1, _p(gamma), _p(beta), n, hw, c, groups, float(eps), _ACT[act],
+                                        stream_ptr()), "groupnorm_apply")
+    _pe(tok, "groupnorm", 4.0 * n * hw * c, (n, hw, c))
+    return out
+
 def groupnorm(x, n, hw, c, groups, gamma, beta, eps=1e-5, act=None, out=None, ld_x=None, ld_y=None):
     _cuda(x, torch.bfloat16, "x")
     ld_x = c if ld_x is None else ld_x

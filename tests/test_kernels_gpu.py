@@ -213,3 +213,81 @@ def test_time_embedding(rt):
     assert (out.cpu() - ref).abs().max().item() < 2e-4  # fp32 sin/cos of arguments up to 999 (ulp of arg ~6e-5)
     out1 = rt.time_embedding(t[2:3].to(dev), 4, 512, dtype=torch.float32)  # (1,) t broadcast over the batch
     assert torch.equal(out1.cpu(), out.cpu()[2:3].expand(4, -1))
+
+
+# ------------------------------------------------------------------------- fused GroupNorm statistics (igemm v2)
+STAT_CASES = [  # n, h, w, cin, cout, k, groups
+    (3, 32, 32, 64, 128, 3, 32), (5, 8, 8, 128, 192, 3, 16), (9, 4, 4, 64, 256, 3, 32), (2, 16, 16, 96, 64, 1, 16),
+    (2, 24, 20, 64, 96, 3, 8), (70, 4, 4, 64, 512, 1, 32),
+]
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout,k,groups", STAT_CASES)
+def test_conv_stats_then_groupnorm_apply(rt, n, h, w, cin, cout, k, groups):
+    """The igemm epilogue's partial statistics + groupnorm_apply reproduce F.group_norm of the conv output."""
+    dev = _dev()
+    from sdb200 import ops
+    g = torch.Generator().manual_seed(n + h + cin + cout)
+    x = bf(torch.randn(n, cin, h, w, generator=g))
+    wt = torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5
+    b = torch.randn(cout, generator=g)
+    gamma, beta = torch.randn(cout, generator=g), torch.randn(cout, generator=g)
+    xd = x.permute(0, 2, 3, 1).reshape(n * h * w, cin).contiguous().to(dev)
+    P = rt.stats_slots(h, w)
+    stats = torch.full((n, P, cout, 2), float("nan"), device=dev)  # every element must be overwritten
+    y = ops.conv_same(xd, n, h, w, cin, ops.pack_conv_weight(wt.to(dev)), cout, k, bias=b.to(dev),
+                      stats=(stats, P, 0, cout))
+    out = rt.groupnorm_apply(y, n, h * w, cout, groups, gamma.to(dev), beta.to(dev), [(stats, P, cout, cout)],
+                             act="silu")
+    torch.cuda.synchronize()
+    assert torch.isfinite(stats).all()
+    yref = y.float().cpu().reshape(n, h, w, cout).permute(0, 3, 1, 2)  # GroupNorm of the bf16 tensor we produced
+    ref = F.silu(F.group_norm(yref, groups, gamma, beta, 1e-5))
+    got = out.float().cpu().reshape(n, h, w, cout).permute(0, 3, 1, 2)
+    assert relerr(got, ref) < 6e-3  # one bf16 rounding at the output
+    # statistics themselves: sum over slots equals the per-(image, channel) sums of the bf16 output
+    s = stats.sum(1).cpu()
+    assert torch.allclose(s[..., 0], yref.sum((2, 3)), rtol=1e-3, atol=1e-2)
+    assert torch.allclose(s[..., 1], (yref ** 2).sum((2, 3)), rtol=1e-3, atol=1e-2)
+    # bit-reproducible: no atomics anywhere
+    stats2 = torch.empty_like(stats)
+    y2 = ops.conv_same(xd, n, h, w, cin, ops.pack_conv_weight(wt.to(dev)), cout, k, bias=b.to(dev),
+                       stats=(stats2, P, 0, cout))
+    assert torch.equal(stats, stats2) and torch.equal(y, y2)
+
+
+def test_groupnorm_apply_two_segments(rt):
+    """Channel concat of two producers (up-block skip connection): statistics come from two buffers."""
+    dev = _dev()
+    g = torch.Generator().manual_seed(4)
+    n, hw, c0, c1, groups = 3, 256, 64, 128, 16
+    x = bf(torch.randn(n, hw, c0 + c1, generator=g) * 2 + 0.5)
+    xf = x.float()
+
+    def mk(part, P):
+        st = torch.zeros(n, P, part.shape[-1], 2)
+        chunks = part.chunk(P, dim=1)
+        for i, ch in enumerate(chunks):
+            st[:, i, :, 0], st[:, i, :, 1] = ch.sum(1), (ch ** 2).sum(1)
+        return st.to(dev)
+
+    s0, s1 = mk(xf[..., :c0], 2), mk(xf[..., c0:], 4)
+    gamma, beta = torch.randn(c0 + c1, generator=g), torch.randn(c0 + c1, generator=g)
+    out = rt.groupnorm_apply(x.reshape(n * hw, -1).to(dev), n, hw, c0 + c1, groups, gamma.to(dev), beta.to(dev),
+                             [(s0, 2, c0, c0), (s1, 4, c1, c1)], act=None)
+    ref = F.group_norm(xf.permute(0, 2, 1), groups, gamma, beta, 1e-5).permute(0, 2, 1)
+    assert relerr(out.float().cpu().reshape(n, hw, -1), ref) < 6e-3
+
+
+def test_linear_residual_tma_epilogue_large(rt):
+    """The attention out-projection shape (K = N = 384, residual) at many tiles per CTA: exercises the persistent
+    loop, both TMEM accumulators, the residual prefetch and the staged TMA store."""
+    dev = _dev()
+    from sdb200 import ops
+    g = torch.Generator().manual_seed(8)
+    M, K, N = 40000, 384, 384
+    a, res = bf(torch.randn(M, K, generator=g)), bf(torch.randn(M, N, generator=g))
+    w, b = torch.randn(N, K, generator=g) / K ** 0.5, torch.randn(N, generator=g)
+    out = rt.linear(a.to(dev), ops.pack_linear_weight(w.to(dev)), bias=b.to(dev), residual=res.to(dev))
+    ref = a.float() @ bf(w).float().t() + b + res.float()
+    assert relerr(out.cpu(), ref) < 6e-3
