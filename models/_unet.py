@@ -258,6 +258,9 @@ class UnetCore(nn.Module):
         if self.class_cond:
             emb = emb + st.class_onehot @ self.class_emb.weight.detach()
         temb_act = E.activate_temb(emb, self.ACT)
+        if E.BATCH_TEMB:
+            temb_act = E.TembBank.build(self, temb_act, [tl[1] for blk in list(self.downs) + list(self.mids) +
+                                                         list(self.ups) for tl in blk.t_emb_layers])
 
         ctx = st.ctx
         skips = []

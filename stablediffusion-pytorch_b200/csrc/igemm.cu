@@ -23,9 +23,9 @@ namespace b200 {
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int IGEMM_THREADS = 192;
+constexpr int IGEMM_THREADS = 320;  // TMA warp, MMA warp, 8 epilogue warps
 constexpr int MAX_SEG = 20;
-constexpr int EPI_THREADS = 128;
+constexpr int EPI_THREADS = 256;
 constexpr int PANEL_BYTES = BM * 128;  // 128 rows x 64 bf16
 
 struct SegDev {
@@ -127,17 +127,22 @@ struct IgemmSmem {
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int STAGING_OFF = STAGES * STAGE_BYTES;
-    static constexpr int STAGING_BYTES = BN >= 64 ? (BN / 64) * PANEL_BYTES : 0;
-    static constexpr int BAR_OFF = STAGING_OFF + STAGING_BYTES;
-    static constexpr int NBAR = 2 * STAGES + 5;  // full[S], empty[S], tmem_full[2], tmem_empty[2], res_full
-    static constexpr int RED_OFF = BAR_OFF + NBAR * 8 + 16;  // 64 x 2 floats: half-tile statistics exchange
-    static constexpr int TOTAL = RED_OFF + 512 + 1024;       // +1024: manual alignment slack
+    static constexpr int STAGING_ONE = BN >= 64 ? (BN / 64) * PANEL_BYTES : 0;
+    static constexpr int NSTG = BN >= 64 && BN <= 128 ? 2 : 1;  // staging tiles (two when shared memory allows)
+    static constexpr int STAGING_BYTES = NSTG * STAGING_ONE;
+    static constexpr int BIAS_MAX = 2560;                       // floats of bias kept in shared memory
+    static constexpr int BIAS_OFF = STAGING_OFF + STAGING_BYTES;
+    static constexpr int BAR_OFF = BIAS_OFF + BIAS_MAX * 4;
+    static constexpr int NBAR = 2 * STAGES + 6;  // full[S], empty[S], tmem_full[2], tmem_empty[2], res_full[2]
+    static constexpr int RED_OFF = BAR_OFF + (NBAR * 8 + 16 + 15) / 16 * 16;  // 8 warps x 32 float4: statistics exchange
+    static constexpr int TOTAL = RED_OFF + 4096 + 1024;      // +1024: manual alignment slack
 };
 
 // Epilogue arithmetic on 8 consecutive output columns of one row.
-__device__ __forceinline__ void epilogue8(const IgemmArgs& args, float (&v)[8], int col, int nv, int pn) {
+__device__ __forceinline__ void epilogue8(const IgemmArgs& args, float (&v)[8], int col, int nv, int pn,
+                                          bool bias_from_global) {
     float f[8];
-    if (args.bias) {
+    if (args.bias && bias_from_global) {
         load8_f32(args.bias + col, nv, f);
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[j] += f[j];
@@ -163,6 +168,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_co
     using L = IgemmSmem<BN, STAGES>;
     constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;  // two accumulators; 64..512, a power of two
     constexpr int PANELS = BN / 64;
+    constexpr int NSTG = L::NSTG;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* staging = smem + L::STAGING_OFF;
@@ -171,7 +177,8 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_co
     uint64_t* tfull_bar = empty_bar + STAGES;
     uint64_t* tempty_bar = tfull_bar + 2;
     uint64_t* res_bar = tempty_bar + 2;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + 1);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + 2);
+    float* sbias = reinterpret_cast<float*>(smem + L::BIAS_OFF);
     float* red = reinterpret_cast<float*>(smem + L::RED_OFF);
 
     const int warp = threadIdx.x >> 5;
@@ -192,7 +199,8 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_co
             mbar_init(&tfull_bar[b], 1);
             mbar_init(&tempty_bar[b], EPI_THREADS);
         }
-        mbar_init(res_bar, 1);
+        mbar_init(&res_bar[0], 1);
+        mbar_init(&res_bar[1], 1);
         fence_barrier_init();
     }
     if (warp == 2) {
@@ -256,30 +264,39 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_co
             __syncwarp();
         }
     } else {
-        // ------------------------------------------------------------------ epilogue (warps 2..5)
+        // ------------------------------------------------------------------ epilogue (warps 2..9)
+        const int e = warp - 2;  // 0..7
         const int q = warp & 3;  // TMEM lane quarter this warp may read
+        const int cg = e >> 2;   // column group: this warp handles 32-column chunks cg, cg+2, ...
         const int r = q * 32 + lane;
         const int et = threadIdx.x - 64;
         const int rpi = args.bw * args.bh;  // tile rows per image
         const int lx = r % args.bw, ly = (r / args.bw) % args.bh, ln = r / rpi;
-        auto load_residual = [&](const Tile& t) {
+        const bool bias_sm = args.bias && args.n_out <= L::BIAS_MAX;
+        if (bias_sm) {
+            for (int i = et; i < args.n_out; i += EPI_THREADS) sbias[i] = __ldg(args.bias + i);
+            named_bar_sync(1, EPI_THREADS);
+        }
+        auto load_residual = [&](const Tile& t, uint8_t* dst, uint64_t* bar) {
             int np = 0;
 #pragma unroll
             for (int p = 0; p < PANELS; ++p)
                 if (t.col_t * BN + p * 64 < args.n_out) ++np;
-            mbar_expect_tx(res_bar, np * PANEL_BYTES);
+            mbar_expect_tx(bar, np * PANEL_BYTES);
 #pragma unroll
             for (int p = 0; p < PANELS; ++p)
                 if (t.col_t * BN + p * 64 < args.n_out)
-                    tma_load_4d(staging + p * PANEL_BYTES, &args.res_map, res_bar, t.col_t * BN + p * 64, t.x0, t.y0,
-                                t.n0);
+                    tma_load_4d(dst + p * PANEL_BYTES, &args.res_map, bar, t.col_t * BN + p * 64, t.x0, t.y0, t.n0);
         };
-        if (args.tma_res && et == 0 && blockIdx.x < args.num_tiles) load_residual(decode_tile(args, blockIdx.x));
+        if (args.tma_res && et == 0 && blockIdx.x < args.num_tiles)
+            load_residual(decode_tile(args, blockIdx.x), staging, &res_bar[0]);
 
         int lt = 0;
         for (int tile = blockIdx.x; tile < args.num_tiles; tile += gridDim.x, ++lt) {
             const Tile t = decode_tile(args, tile);
             const int buf = lt & 1;
+            const int sb = NSTG == 2 ? (lt & 1) : 0;
+            uint8_t* stg = staging + sb * L::STAGING_ONE;
             const int px = t.x0 + lx, py = t.y0 + ly, pn = t.n0 + ln;
             const bool row_ok = (px < args.ow) && (py < args.oh) && (pn < args.on);
             const int pnc = pn < args.on ? pn : args.on - 1;  // clamped image index for per-image operand reads
@@ -288,9 +305,9 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_co
 
             mbar_wait(&tfull_bar[buf], (lt >> 1) & 1);
             tc_fence_after();
-            if (args.tma_res) mbar_wait(res_bar, lt & 1);
+            if (args.tma_res) mbar_wait(&res_bar[sb], NSTG == 2 ? (lt >> 1) & 1 : lt & 1);
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
+            for (int c = cg; c < BN / 32; c += 2) {
                 const int col0 = t.col_t * BN + c * 32;
                 if (col0 >= args.n_out) break;  // warp-uniform
                 uint32_t acc[32];
@@ -304,10 +321,22 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_co
                     float v[8];
 #pragma unroll
                     for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(acc[g * 8 + j]);
-                    epilogue8(args, v, col, nv, pnc);
+                    if (bias_sm) {
+                        if (nv == 8) {
+                            const float4 b0 = *reinterpret_cast<const float4*>(sbias + col);
+                            const float4 b1 = *reinterpret_cast<const float4*>(sbias + col + 4);
+                            v[0] += b0.x, v[1] += b0.y, v[2] += b0.z, v[3] += b0.w;
+                            v[4] += b1.x, v[5] += b1.y, v[6] += b1.z, v[7] += b1.w;
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                if (j < nv) v[j] += sbias[col + j];
+                        }
+                    }
+                    epilogue8(args, v, col, nv, pnc, !bias_sm);
                     if (BN >= 64 && args.tma_out) {
                         const int jj = c * 4 + g;  // 16-byte chunk index within the tile row
-                        uint4* sp = reinterpret_cast<uint4*>(staging + (jj >> 3) * PANEL_BYTES + r * 128 +
+                        uint4* sp = reinterpret_cast<uint4*>(stg + (jj >> 3) * PANEL_BYTES + r * 128 +
                                                              (((jj & 7) ^ (r & 7)) << 4));
                         if (args.tma_res) {
                             float f[8];
@@ -356,66 +385,90 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_co
 
             if (BN >= 64 && args.tma_out) {
                 fence_proxy_async();  // staging writes (generic proxy) -> visible to the TMA store (async proxy)
+                const bool has_next = tile + gridDim.x < args.num_tiles;
+                if (NSTG == 2 && et == 0) {
+                    tma_store_wait_read();  // the previous tile's store has finished reading the other buffer
+                    if (args.tma_res && has_next)
+                        load_residual(decode_tile(args, tile + gridDim.x), staging + (sb ^ 1) * L::STAGING_ONE,
+                                      &res_bar[sb ^ 1]);
+                }
                 named_bar_sync(1, EPI_THREADS);
                 if (et == 0) {
 #pragma unroll
                     for (int p = 0; p < PANELS; ++p)
                         if (t.col_t * BN + p * 64 < args.n_out)
-                            tma_store_4d(&args.out_map, staging + p * PANEL_BYTES, t.col_t * BN + p * 64, t.x0, t.y0,
-                                         t.n0);
+                            tma_store_4d(&args.out_map, stg + p * PANEL_BYTES, t.col_t * BN + p * 64, t.x0, t.y0, t.n0);
                     tma_store_commit();
                 }
                 if (args.stats) {
-                    // per-channel sum / sum of squares of the bf16-rounded tile, one partial per (image, tile slot):
-                    // thread -> (column c of a 64-column panel, row half); deterministic (no atomics)
-                    const int c = et & 63, half = et >> 6;
+                    // per-channel sum / sum of squares of the bf16-rounded tile, one partial per (image, tile slot),
+                    // deterministic (no atomics). Warp e owns rows [16e, 16e+16), lane l owns columns 2l, 2l+1 of a
+                    // 64-column panel: one conflict-free 4-byte smem read per row.
+                    const bool full = (t.x0 + args.bw <= args.ow) && (t.y0 + args.bh <= args.oh);
+                    const int rbase = e * 16;
 #pragma unroll 1
                     for (int p = 0; p < PANELS; ++p) {
-                        const int col = t.col_t * BN + p * 64 + c;
-                        const uint8_t* pb = staging + p * PANEL_BYTES + (c & 7) * 2;
-                        float s = 0.f, ss = 0.f;
-                        int cur = -1;
-                        auto flush = [&](int img_l) {
+                        const int col = t.col_t * BN + p * 64 + 2 * lane;
+                        const uint8_t* pb = stg + p * PANEL_BYTES + (lane & 3) * 4;
+                        const int chunk = lane >> 2;
+                        auto put = [&](int img_l, float s0, float s1, float q0, float q1) {
                             const int img = t.n0 + img_l;
                             if (col < args.n_out && img < args.on) {
                                 float* dst = args.stats +
                                              ((static_cast<long long>(img) * args.stats_p + args.stats_slot0 + t.slot) *
                                                   args.stats_ld + col) * 2;
-                                dst[0] = s, dst[1] = ss;
+                                *reinterpret_cast<float2*>(dst) = make_float2(s0, q0);
+                                if (col + 1 < args.n_out) *reinterpret_cast<float2*>(dst + 2) = make_float2(s1, q1);
                             }
                         };
-                        for (int rr = half * 64; rr < half * 64 + 64; ++rr) {
-                            const int il = rr / rpi;
-                            if (rpi < 128 && il != cur) {
-                                if (cur >= 0) flush(cur);
-                                cur = il, s = 0.f, ss = 0.f;
+                        const int seg = rpi < 16 ? rpi : 16;  // rows of one image inside this warp's 16 rows
+                        float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll 4
+                        for (int rr = 0; rr < 16; ++rr) {
+                            const int row = rbase + rr;
+                            bool ok = true;
+                            if (!full) ok = (t.x0 + row % args.bw < args.ow) && (t.y0 + (row / args.bw) % args.bh < args.oh);
+                            if (ok) {
+                                const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(
+                                    pb + row * 128 + ((chunk ^ (row & 7)) << 4)));
+                                s0 += f.x, s1 += f.y, q0 += f.x * f.x, q1 += f.y * f.y;
                             }
-                            const int x = rr % args.bw, y = (rr / args.bw) % args.bh;
-                            if (t.x0 + x < args.ow && t.y0 + y < args.oh) {
-                                const float f = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(
-                                    pb + rr * 128 + (((c >> 3) ^ (rr & 7)) << 4)));
-                                s += f, ss += f * f;
+                            if (seg < 16 && ((rr + 1) & (seg - 1)) == 0) {  // image boundary inside the warp's rows
+                                put(row / rpi, s0, s1, q0, q1);
+                                s0 = s1 = q0 = q1 = 0.f;
                             }
                         }
-                        if (rpi < 128) {
-                            flush(cur);
-                        } else {  // the tile lies in one image: combine the two row halves
-                            if (half == 1) red[c * 2] = s, red[c * 2 + 1] = ss;
-                            named_bar_sync(2, EPI_THREADS);
-                            if (half == 0) {
-                                s += red[c * 2], ss += red[c * 2 + 1];
-                                flush(0);
+                        if (rpi >= 16) {
+                            if (rpi == 16) {
+                                put(e, s0, s1, q0, q1);
+                            } else {  // 2, 4 or 8 warps share an image: combine through smem
+                                float4* rd = reinterpret_cast<float4*>(red);
+                                rd[e * 32 + lane] = make_float4(s0, s1, q0, q1);
+                                named_bar_sync(2, EPI_THREADS);
+                                const int wpi = rpi >> 4;  // warps per image
+                                if ((e & (wpi - 1)) == 0) {
+                                    for (int k = 1; k < wpi; ++k) {
+                                        const float4 o = rd[(e + k) * 32 + lane];
+                                        s0 += o.x, s1 += o.y, q0 += o.z, q1 += o.w;
+                                    }
+                                    put(rbase / rpi, s0, s1, q0, q1);
+                                }
+                                named_bar_sync(2, EPI_THREADS);
                             }
-                            named_bar_sync(2, EPI_THREADS);
                         }
                     }
                 }
-                if (et == 0) tma_store_wait_read();
-                named_bar_sync(1, EPI_THREADS);  // staging may be overwritten
-                if (args.tma_res && et == 0 && tile + gridDim.x < args.num_tiles)
-                    load_residual(decode_tile(args, tile + gridDim.x));
+                if (NSTG == 1) {
+                    if (et == 0) tma_store_wait_read();
+                    named_bar_sync(1, EPI_THREADS);  // staging may be overwritten
+                    if (args.tma_res && et == 0 && has_next)
+                        load_residual(decode_tile(args, tile + gridDim.x), staging, &res_bar[0]);
+                } else if (args.stats) {
+                    named_bar_sync(1, EPI_THREADS);  // all statistics reads done before this buffer is refilled
+                }
             }
         }
+        if (et == 0) tma_store_wait_read();  // smem must outlive the last store's reads
         tc_fence_before();
     }
     __syncthreads();
@@ -618,7 +671,7 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
     cudaStream_t st = as_stream(stream);
     switch (BNsel) {
         case 256: return launch_igemm<256, 3>(a, grid, st);
-        case 128: return launch_igemm<128, 5>(a, grid, st);
+        case 128: return launch_igemm<128, 4>(a, grid, st);
         case 64: return launch_igemm<64, 6>(a, grid, st);
         default: return launch_igemm<32, 6>(a, grid, st);
     }

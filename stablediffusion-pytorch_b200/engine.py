@@ -273,7 +273,8 @@ class CondState:
         self.inbuf = self.cin = self.ctx = self.class_onehot = None
 
 
-HOIST_CONDITIONING = True  # tests flip this to compare hoisted and per-call conditioning
+HOIST_CONDITIONING = True
+BATCH_TEMB = True  # one GEMM for all per-block time-embedding projections  # tests flip this to compare hoisted and per-call conditioning
 
 
 def cross_attention(a, norm, mha, ctx_proj_mod, ctx, lk, cache=None):
@@ -293,6 +294,36 @@ def cross_attention(a, norm, mha, ctx_proj_mod, ctx, lk, cache=None):
     return _out_proj(o, mha, a)
 
 
+class TembBank:
+    """All per-block time-embedding projections `Linear(t_emb_dim -> C_out)` of one forward (22 in the full UNet,
+    blocks.py:57-62) depend only on t, so they run as ONE GEMM against the row-concatenated weights at the top of the
+    forward; each ResNet unit then picks its [n, C_out] slice as the conv epilogue's row bias."""
+
+    def __init__(self, act, slices):
+        self.act, self.slices = act, slices
+
+    @staticmethod
+    def build(owner, temb_act, linears):
+        mods = [m for m in linears if type(m) is nn.Linear and m.out_features % 8 == 0]
+        if len(mods) < 2:
+            return TembBank(temb_act, {})
+        params = tuple(m.weight for m in mods) + tuple(m.bias for m in mods)
+
+        def pack():
+            w = ops.pack_linear_weight(torch.cat([m.weight for m in mods], 0))
+            b = torch.cat([m.bias if m.bias is not None else torch.zeros(m.out_features, device=m.weight.device)
+                           for m in mods], 0).float().contiguous()
+            return w, b
+
+        w, b = CACHE.get(owner, "temb_bank", params, pack)
+        big = rt.linear(temb_act, w, bias=b)
+        slices, off = {}, 0
+        for m in mods:
+            slices[id(m)] = big[:, off:off + m.out_features]
+            off += m.out_features
+        return TembBank(temb_act, slices)
+
+
 def resnet(a, first, temb_layer, second, shortcut, temb_act):
     """GN-act-conv3x3 (+ time-embedding row bias) -> GN-act-conv3x3 + 1x1 shortcut of the block input, the shortcut
     fused into the second conv's accumulator — blocks.py:113-119. `first`/`second` are the reference's
@@ -301,7 +332,12 @@ def resnet(a, first, temb_layer, second, shortcut, temb_act):
     h = group_norm(a, first[0], act=act)
     rowbias = None
     if temb_layer is not None:
-        rowbias = linear(temb_act, temb_layer[1])
+        if isinstance(temb_act, TembBank):
+            rowbias = temb_act.slices.get(id(temb_layer[1]))
+            if rowbias is None:
+                rowbias = linear(temb_act.act, temb_layer[1])
+        else:
+            rowbias = linear(temb_act, temb_layer[1])
     h = conv2d(h, first[2], rowbias=rowbias)
     h = group_norm(h, second[0], act=_act_name(second[1]))
     if type(second[2]) is nn.Conv2d and type(shortcut) is nn.Conv2d:
