@@ -207,6 +207,243 @@ __global__ void __launch_bounds__(ATT_THREADS)
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Resident-KV variant (every attention inside the UNet / DiT: lk <= 1024 with d <= 32, or lk <= 256 with d <= 64).
+// With head dims this small the kernel is bound by the softmax arithmetic (one exp + ~6 fp32 ops per score against
+// 4*d tensor flops), so the structure removes everything else from the inner loop:
+//   * K and V of the whole (batch, head) are staged ONCE in shared memory; after one barrier each warp streams
+//     through all keys on its own — no per-tile barriers, no per-tile global loads
+//   * the head dim is a template parameter in units of 8 and is NOT padded to 16: the odd 8 columns use
+//     mma.m16n8k8 (d = 8 -> one k8 MMA, d = 24 -> k16 + k8), rows are 16-byte chunks at an odd 16-byte pitch so
+//     every ldmatrix is bank-conflict free without padding columns to zero
+//   * exp2 via ex2.approx.ftz with the softmax scale folded into one FFMA; key masking only in the last tile, and
+//     the last tile only touches the 8-key groups that exist (lk = 77 costs 64 + 16 keys, not 128)
+template <int D8>
+struct AttRes {
+    static constexpr int P16 = (D8 & 1) ? D8 : D8 + 1;  // row pitch in 16-byte units (odd)
+    static constexpr int PITCH = P16 * 8;               // elements
+};
+
+__device__ __forceinline__ void ldsm_x2(uint32_t (&r)[2], const void* p) {
+    uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(p));
+    asm volatile("ldmatrix.sync.aligned.m8n8.x2.shared.b16 {%0,%1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(a));
+}
+__device__ __forceinline__ void ldsm_x2_t(uint32_t (&r)[2], const void* p) {
+    uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(p));
+    asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0,%1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(a));
+}
+__device__ __forceinline__ void mma1688(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k8.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a0), "r"(a1), "r"(b0));
+}
+__device__ __forceinline__ float ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+template <int D8>
+__global__ void __launch_bounds__(256)
+    attention_resident_kernel(const __nv_bfloat16* __restrict__ q, long long ld_q, const __nv_bfloat16* __restrict__ k,
+                              long long ld_k, const __nv_bfloat16* __restrict__ v, long long ld_v,
+                              __nv_bfloat16* __restrict__ out, long long ld_o, int lq, int lk, float scale_log2) {
+    constexpr int PITCH = AttRes<D8>::PITCH;
+    constexpr int K16 = D8 / 2;        // k16 chunks of the head dim
+    constexpr bool TAIL = (D8 & 1);    // one trailing k8 chunk
+    extern __shared__ __align__(16) uint8_t att_smem[];
+    const int nthreads = blockDim.x, bq = (nthreads >> 5) * 16;
+    const int lk_pad = (lk + 63) & ~63;
+    __nv_bfloat16* sK = reinterpret_cast<__nv_bfloat16*>(att_smem);
+    __nv_bfloat16* sV = sK + lk_pad * PITCH;
+    __nv_bfloat16* sQ = sV + lk_pad * PITCH;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int q0 = blockIdx.x * bq;
+    const int head = blockIdx.y;
+    const long long b = blockIdx.z;
+    const __nv_bfloat16* qg = q + (b * lq) * ld_q + head * (D8 * 8);
+    const __nv_bfloat16* kg = k + (b * lk) * ld_k + head * (D8 * 8);
+    const __nv_bfloat16* vg = v + (b * lk) * ld_v + head * (D8 * 8);
+
+    for (int i = tid; i < lk_pad * D8; i += nthreads) {
+        const int r = i / D8, c = i - r * D8;
+        const bool ok = r < lk;
+        const long long ro = ok ? r : 0;
+        cp_async16(sK + r * PITCH + c * 8, kg + ro * ld_k + c * 8, ok ? 16 : 0);
+        cp_async16(sV + r * PITCH + c * 8, vg + ro * ld_v + c * 8, ok ? 16 : 0);
+    }
+    for (int i = tid; i < bq * D8; i += nthreads) {
+        const int r = i / D8, c = i - r * D8;
+        const bool ok = (q0 + r) < lq;
+        cp_async16(sQ + r * PITCH + c * 8, qg + (long long)(ok ? q0 + r : 0) * ld_q + c * 8, ok ? 16 : 0);
+    }
+    cp_async_commit();
+    cp_async_wait<0>();
+    __syncthreads();
+    if (q0 + warp * 16 >= lq) return;  // no barriers below
+
+    uint32_t qf[K16 > 0 ? K16 : 1][4];
+    uint32_t qt[2] = {0u, 0u};
+    const __nv_bfloat16* qrow = sQ + (warp * 16 + (lane & 7) + 8 * ((lane >> 3) & 1)) * PITCH;
+#pragma unroll
+    for (int kb = 0; kb < K16; ++kb) ldsm_x4(qf[kb], qrow + kb * 16 + 8 * (lane >> 4));
+    if (TAIL) ldsm_x2(qt, qrow + K16 * 16);
+
+    float o[D8][4];
+#pragma unroll
+    for (int i = 0; i < D8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+    const int ntiles = lk_pad >> 6;
+
+    for (int t = 0; t < ntiles; ++t) {
+        const __nv_bfloat16* tK = sK + t * 64 * PITCH;
+        const __nv_bfloat16* tV = sV + t * 64 * PITCH;
+        const int rem = lk - t * 64;                     // keys left (>= 1)
+        const int nb_valid = rem >= 64 ? 8 : (rem + 7) >> 3;  // 8-key groups to touch in this tile
+        float s[8][4];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f;
+#pragma unroll
+        for (int np = 0; np < 4; ++np) {
+            if (2 * np < nb_valid) {
+#pragma unroll
+                for (int kb = 0; kb < K16; ++kb) {
+                    uint32_t bf[4];
+                    ldsm_x4(bf, tK + (np * 16 + (lane & 7) + 8 * (lane >> 4)) * PITCH + kb * 16 + 8 * ((lane >> 3) & 1));
+                    mma16816(s[2 * np], qf[kb], bf[0], bf[1]);
+                    mma16816(s[2 * np + 1], qf[kb], bf[2], bf[3]);
+                }
+            }
+        }
+        if (TAIL) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                if (4 * h < nb_valid) {
+                    uint32_t bf[4];
+                    ldsm_x4(bf, tK + (h * 32 + lane) * PITCH + K16 * 16);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) mma1688(s[4 * h + i], qt[0], qt[1], bf[i]);
+                }
+            }
+        }
+        if (rem < 64) {  // last, partial tile: mask keys beyond lk
+            const int kbase = (lane & 3) * 2;
+#pragma unroll
+            for (int nb = 0; nb < 8; ++nb) {
+                const int key = kbase + nb * 8;
+                if (key >= rem) s[nb][0] = s[nb][2] = -INFINITY;
+                if (key + 1 >= rem) s[nb][1] = s[nb][3] = -INFINITY;
+            }
+        }
+        float mx0 = m0, mx1 = m1;
+#pragma unroll
+        for (int nb = 0; nb < 8; ++nb) {
+            if (nb < nb_valid) {
+                mx0 = fmaxf(mx0, fmaxf(s[nb][0], s[nb][1]));
+                mx1 = fmaxf(mx1, fmaxf(s[nb][2], s[nb][3]));
+            }
+        }
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        const float a0 = ex2((m0 - mx0) * scale_log2), a1 = ex2((m1 - mx1) * scale_log2);
+        m0 = mx0, m1 = mx1;
+        const float ms0 = mx0 * scale_log2, ms1 = mx1 * scale_log2;
+        float rs0 = 0.f, rs1 = 0.f;
+#pragma unroll
+        for (int nb = 0; nb < 8; ++nb) {
+            if (nb < nb_valid) {
+                s[nb][0] = ex2(fmaf(s[nb][0], scale_log2, -ms0));
+                s[nb][1] = ex2(fmaf(s[nb][1], scale_log2, -ms0));
+                s[nb][2] = ex2(fmaf(s[nb][2], scale_log2, -ms1));
+                s[nb][3] = ex2(fmaf(s[nb][3], scale_log2, -ms1));
+                rs0 += s[nb][0] + s[nb][1];
+                rs1 += s[nb][2] + s[nb][3];
+            } else {
+                s[nb][0] = s[nb][1] = s[nb][2] = s[nb][3] = 0.f;  // untouched 8-key groups contribute nothing to P V
+            }
+        }
+        l0 = l0 * a0 + rs0;
+        l1 = l1 * a1 + rs1;
+#pragma unroll
+        for (int i = 0; i < D8; ++i) {
+            o[i][0] *= a0, o[i][1] *= a0;
+            o[i][2] *= a1, o[i][3] *= a1;
+        }
+        // O += P V (16 keys per step; V fragments transposed on load)
+#pragma unroll
+        for (int kb = 0; kb < 4; ++kb) {
+            if (2 * kb < nb_valid) {
+                uint32_t pf[4];
+                pf[0] = pack_bf16(s[2 * kb][0], s[2 * kb][1]);
+                pf[1] = pack_bf16(s[2 * kb][2], s[2 * kb][3]);
+                pf[2] = pack_bf16(s[2 * kb + 1][0], s[2 * kb + 1][1]);
+                pf[3] = pack_bf16(s[2 * kb + 1][2], s[2 * kb + 1][3]);
+                const __nv_bfloat16* vrow = tV + (kb * 16 + (lane & 7) + 8 * ((lane >> 3) & 1)) * PITCH;
+#pragma unroll
+                for (int dp = 0; dp < K16; ++dp) {
+                    uint32_t bf[4];
+                    ldsm_x4_t(bf, vrow + dp * 16 + 8 * (lane >> 4));
+                    mma16816(o[2 * dp], pf, bf[0], bf[1]);
+                    mma16816(o[2 * dp + 1], pf, bf[2], bf[3]);
+                }
+                if (TAIL) {
+                    uint32_t bf[2];
+                    ldsm_x2_t(bf, vrow + K16 * 16);
+                    mma16816(o[D8 - 1], pf, bf[0], bf[1]);
+                }
+            }
+        }
+    }
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    const float i0 = 1.f / l0, i1 = 1.f / l1;
+    const int r0 = q0 + warp * 16 + (lane >> 2), r1 = r0 + 8;
+    __nv_bfloat16* og = out + (b * lq) * ld_o + head * (D8 * 8);
+#pragma unroll
+    for (int nb = 0; nb < D8; ++nb) {
+        const int col = nb * 8 + (lane & 3) * 2;
+        if (r0 < lq)
+            *reinterpret_cast<__nv_bfloat162*>(og + (long long)r0 * ld_o + col) =
+                __floats2bfloat162_rn(o[nb][0] * i0, o[nb][1] * i0);
+        if (r1 < lq)
+            *reinterpret_cast<__nv_bfloat162*>(og + (long long)r1 * ld_o + col) =
+                __floats2bfloat162_rn(o[nb][2] * i1, o[nb][3] * i1);
+    }
+}
+
+static size_t resident_smem(int d8, int lk, int bq) {
+    const int p16 = (d8 & 1) ? d8 : d8 + 1;
+    const size_t lk_pad = (size_t)((lk + 63) & ~63);
+    return (2 * lk_pad + bq) * p16 * 16;
+}
+
+template <int D8>
+static int launch_resident(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v,
+                           void* out, int64_t ld_o, int64_t batch, int heads, int lq, int lk, float scale,
+                           cudaStream_t st) {
+    const int warps = lq >= 128 ? 8 : lq > 32 ? 4 : lq > 16 ? 2 : 1;
+    const int bq = warps * 16;
+    const size_t smem = resident_smem(D8, lk, bq);
+    static bool configured = false;
+    if (!configured) {
+        cudaFuncSetAttribute(attention_resident_kernel<D8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        configured = true;
+    }
+    dim3 grid((lq + bq - 1) / bq, heads, (unsigned)batch);
+    attention_resident_kernel<D8><<<grid, warps * 32, smem, st>>>(
+        static_cast<const __nv_bfloat16*>(q), ld_q, static_cast<const __nv_bfloat16*>(k), ld_k,
+        static_cast<const __nv_bfloat16*>(v), ld_v, static_cast<__nv_bfloat16*>(out), ld_o, lq, lk,
+        scale * 1.4426950408889634f);
+    B200_CHECK_LAUNCH("attention_resident");
+    return B200SD_OK;
+}
+
 template <int DP>
 static int launch_attention(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v,
                             void* out, int64_t ld_o, int64_t batch, int heads, int lq, int lk, int d, float scale,
@@ -247,6 +484,18 @@ extern "C" int b200sd_attention(const void* q, int64_t ld_q, const void* k, int6
                  "attention: pointers unaligned");
     if (batch == 0) return B200SD_OK;
     cudaStream_t st = as_stream(stream);
+    if (resident_smem(d / 8, lk, 128) <= 112 * 1024) {  // two CTAs per SM still fit
+        switch (d / 8) {
+            case 1: return launch_resident<1>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, st);
+            case 2: return launch_resident<2>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, st);
+            case 3: return launch_resident<3>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, st);
+            case 4: return launch_resident<4>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, st);
+            case 5: return launch_resident<5>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, st);
+            case 6: return launch_resident<6>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, st);
+            case 7: return launch_resident<7>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, st);
+            default: return launch_resident<8>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, st);
+        }
+    }
     const int dp = (d + 15) / 16 * 16;
     switch (dp) {
         case 16: return launch_attention<16>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, d, scale, st);

@@ -153,7 +153,9 @@ def test_groupnorm(rt, n, hw, c, groups, act):
 
 @pytest.mark.parametrize("b,heads,lq,lk,d", [(2, 16, 1024, 1024, 24), (3, 16, 256, 256, 32), (2, 16, 64, 64, 48),
                                              (5, 16, 16, 16, 32), (2, 16, 1024, 77, 8), (2, 16, 256, 77, 16),
-                                             (1, 4, 1024, 1024, 64), (2, 9, 256, 256, 32), (3, 16, 16, 77, 32)])
+                                             (1, 4, 1024, 1024, 64), (2, 9, 256, 256, 32), (3, 16, 16, 77, 32),
+                                             (2, 16, 1024, 1024, 8), (2, 8, 100, 90, 40), (2, 4, 130, 17, 56),
+                                             (1, 2, 48, 200, 64), (2, 16, 64, 77, 24), (1, 16, 1000, 1000, 16)])
 def test_attention(rt, b, heads, lq, lk, d):
     dev = _dev()
     g = torch.Generator().manual_seed(lq + lk + d)
