@@ -11,6 +11,7 @@
 // CTA = 4 warps = 64 queries of one (batch, head); KV streamed in 64-key tiles, double-buffered with cp.async.
 #include "host.h"
 #include <cuda_bf16.h>
+#include <type_traits>
 
 namespace b200 {
 
@@ -297,17 +298,18 @@ __global__ void __launch_bounds__(256)
     float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
     const int ntiles = lk_pad >> 6;
 
-    for (int t = 0; t < ntiles; ++t) {
+    auto tile = [&](int t, auto full_tag) {
+        constexpr bool FULL = decltype(full_tag)::value;
         const __nv_bfloat16* tK = sK + t * 64 * PITCH;
         const __nv_bfloat16* tV = sV + t * 64 * PITCH;
         const int rem = lk - t * 64;                     // keys left (>= 1)
-        const int nb_valid = rem >= 64 ? 8 : (rem + 7) >> 3;  // 8-key groups to touch in this tile
+        const int nb_valid = FULL ? 8 : (rem + 7) >> 3;  // 8-key groups to touch in this tile
         float s[8][4];
 #pragma unroll
         for (int i = 0; i < 8; ++i) s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f;
 #pragma unroll
         for (int np = 0; np < 4; ++np) {
-            if (2 * np < nb_valid) {
+            if (FULL || 2 * np < nb_valid) {
 #pragma unroll
                 for (int kb = 0; kb < K16; ++kb) {
                     uint32_t bf[4];
@@ -320,7 +322,7 @@ __global__ void __launch_bounds__(256)
         if (TAIL) {
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                if (4 * h < nb_valid) {
+                if (FULL || 4 * h < nb_valid) {
                     uint32_t bf[4];
                     ldsm_x4(bf, tK + (h * 32 + lane) * PITCH + K16 * 16);
 #pragma unroll
@@ -328,7 +330,7 @@ __global__ void __launch_bounds__(256)
                 }
             }
         }
-        if (rem < 64) {  // last, partial tile: mask keys beyond lk
+        if (!FULL) {  // last, partial tile: mask keys beyond lk
             const int kbase = (lane & 3) * 2;
 #pragma unroll
             for (int nb = 0; nb < 8; ++nb) {
@@ -340,7 +342,7 @@ __global__ void __launch_bounds__(256)
         float mx0 = m0, mx1 = m1;
 #pragma unroll
         for (int nb = 0; nb < 8; ++nb) {
-            if (nb < nb_valid) {
+            if (FULL || nb < nb_valid) {
                 mx0 = fmaxf(mx0, fmaxf(s[nb][0], s[nb][1]));
                 mx1 = fmaxf(mx1, fmaxf(s[nb][2], s[nb][3]));
             }
@@ -355,7 +357,7 @@ __global__ void __launch_bounds__(256)
         float rs0 = 0.f, rs1 = 0.f;
 #pragma unroll
         for (int nb = 0; nb < 8; ++nb) {
-            if (nb < nb_valid) {
+            if (FULL || nb < nb_valid) {
                 s[nb][0] = ex2(fmaf(s[nb][0], scale_log2, -ms0));
                 s[nb][1] = ex2(fmaf(s[nb][1], scale_log2, -ms0));
                 s[nb][2] = ex2(fmaf(s[nb][2], scale_log2, -ms1));
@@ -376,7 +378,7 @@ __global__ void __launch_bounds__(256)
         // O += P V (16 keys per step; V fragments transposed on load)
 #pragma unroll
         for (int kb = 0; kb < 4; ++kb) {
-            if (2 * kb < nb_valid) {
+            if (FULL || 2 * kb < nb_valid) {
                 uint32_t pf[4];
                 pf[0] = pack_bf16(s[2 * kb][0], s[2 * kb][1]);
                 pf[1] = pack_bf16(s[2 * kb][2], s[2 * kb][3]);
@@ -397,7 +399,10 @@ __global__ void __launch_bounds__(256)
                 }
             }
         }
-    }
+    };
+    const int nfull = lk >> 6;
+    for (int t = 0; t < nfull; ++t) tile(t, std::true_type{});
+    if (nfull < ntiles) tile(nfull, std::false_type{});
     l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
     l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
     l1 += __shfl_xor_sync(0xffffffffu, l1, 1);

@@ -18,6 +18,7 @@
 #include "ptx.cuh"
 #include <cudaTypedefs.h>
 #include <mutex>
+#include <stdlib.h>
 
 namespace b200 {
 
@@ -611,9 +612,16 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
         for (int bnc : {256, 128, 64}) {
             if (bnc > 64 && n <= bnc / 2) continue;
             const long long tiles = m_tiles * ((n + bnc - 1) / bnc);
-            const long long cost = ((tiles + sms - 1) / sms) * (bnc + 64);
+            long long cost = ((tiles + sms - 1) / sms) * (bnc + 64);
+            // BN = 256 has a single staging tile (its epilogue store is not overlapped with the next tile's
+            // epilogue): with a short K loop there is no mainloop to hide that behind
+            if (bnc == 256 && total <= 16) cost = cost * 3 / 2;
             if (best < 0 || cost < best) best = cost, BNsel = bnc;
         }
+    }
+    if (const char* f = getenv("B200SD_FORCE_BN")) {  // tuning aid (tools/kernel_bench.py); not used by the product path
+        const int v = atoi(f);
+        if ((v == 256 || v == 128 || v == 64) && n > 32) BNsel = v;
     }
     a.tiles_col = (n + BNsel - 1) / BNsel;
     const long long tiles_ll = m_tiles * a.tiles_col;
