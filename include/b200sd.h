@@ -130,6 +130,27 @@ typedef struct {
 int b200sd_igemm(const b200sd_igemm_params* p, void* stream);
 int b200sd_igemm_stats_slots(int oh, int ow);
 
+/* ------------------------------------------------------------------------------------------- weight gradient
+ * Backward of the same leaves w.r.t. their weights (loss.backward(), train_ddpm_cond_celebhq_multi_gpu.py:362):
+ *   dWp[co, k(s, c)] = sum over output pixels p: dY[p, co] * A_s[p shifted by (dy_s, dx_s), c0_s + c]
+ * in the packed [n_out, k_total] layout b200sd_igemm reads (srcs/segs exactly as in the forward call). dY is a
+ * (C = n_out, W, H, N) bf16 view like the sources. The pixel reduction is split into `splits` ranges (use
+ * b200sd_wgrad_splits); each range stores fp32 partial[split][n_out][k_total] and b200sd_wgrad_reduce sums them in
+ * order into `out` (packed fp32; accumulate != 0 adds to what is there). No atomics: bit-reproducible. */
+typedef struct {
+    int32_t n_src, n_seg;
+    b200sd_src srcs[4];
+    b200sd_seg segs[20];
+    b200sd_src dy;
+    int32_t n_out;
+    int32_t on, oh, ow;
+    float* partial;
+    int32_t splits;
+} b200sd_wgrad_params;
+int b200sd_wgrad_splits(int n_out, int k_total, int on, int oh, int ow);
+int b200sd_wgrad(const b200sd_wgrad_params* p, void* stream);
+int b200sd_wgrad_reduce(const float* partial, int splits, int64_t elems, float* out, int accumulate, void* stream);
+
 /* ------------------------------------------------------------------------------------------- normalisation
  * nn.GroupNorm(G, C) (+ SiLU / ReLU) — models/blocks.py:48-49,67-68,126,136; unet_cond_base.py:179-180.
  * x: NHWC bf16 [n, hw, ld_x] (C contiguous); statistics over (hw, C/G) per image and group, biased variance,

@@ -17,7 +17,7 @@ _ACT = {None: 0, "none": 0, "silu": 1, "relu": 2}
 
 EXPORTS = [
     "b200sd_last_error", "b200sd_version", "b200sd_launch_count", "b200sd_sched_add_noise",
-    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_attention",
+    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_attention",
     "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16",
 ]
 
@@ -46,6 +46,15 @@ class IgemmParams(C.Structure):
     ]
 
 
+class WgradParams(C.Structure):
+    _fields_ = [
+        ("n_src", C.c_int32), ("n_seg", C.c_int32),
+        ("srcs", Src * 4), ("segs", Seg * 20), ("dy", Src),
+        ("n_out", C.c_int32), ("on", C.c_int32), ("oh", C.c_int32), ("ow", C.c_int32),
+        ("partial", C.c_void_p), ("splits", C.c_int32),
+    ]
+
+
 _lib = None
 
 
@@ -69,6 +78,9 @@ def lib():
         L.b200sd_time_embedding.argtypes = [vp, i64, vp, i32, i64, i32, vp]
         L.b200sd_igemm.argtypes = [C.POINTER(IgemmParams), vp]
         L.b200sd_igemm_stats_slots.argtypes = [i32, i32]
+        L.b200sd_wgrad.argtypes = [C.POINTER(WgradParams), vp]
+        L.b200sd_wgrad_splits.argtypes = [i32, i32, i32, i32, i32]
+        L.b200sd_wgrad_reduce.argtypes = [vp, i32, i64, vp, i32, vp]
         L.b200sd_groupnorm.argtypes = [vp, i64, vp, i64, vp, vp, i64, i64, i32, i32, f32, i32, vp]
         L.b200sd_groupnorm_apply.argtypes = [vp, i64, vp, i64, vp, i32, i32, i32, vp, i32, i32, vp, vp, i64, i64, i32, i32,
                                              f32, i32, vp]
@@ -295,6 +307,35 @@ def linear(a, weight, bias=None, act=None, residual=None, out=None, out_dtype=to
         rs = (ow * residual.stride(0), 0, residual.stride(0))
     return igemm([src], [(0, 0, 0, 0, Kp // 64)], weight, N, on, 1, ow, out, (ow * ldo, 0, ldo), bias=bias,
                  rowbias=rowbias, gate=gate, residual=residual, res_strides=rs, act=act, stats=stats)
+
+
+def wgrad(srcs, segs, dy_src, n_out, on, oh, ow, out=None, accumulate=False):
+    """Packed weight gradient fp32 [n_out, 64 * sum(nchunk)] of an igemm leaf: srcs/segs as in the forward call,
+    dy_src a (C = n_out, W, H, N) Src view of the bf16 output gradient."""
+    k_total = 64 * sum(sg[4] for sg in segs)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    splits = int(lib().b200sd_wgrad_splits(n_out, k_total, on, oh, ow))
+    partial = torch.empty(splits, n_out, k_total, device=dev, dtype=torch.float32)
+    p = WgradParams()
+    p.n_src, p.n_seg = len(srcs), len(segs)
+    for i, s in enumerate(srcs):
+        p.srcs[i] = s
+    for i, sg in enumerate(segs):
+        p.segs[i] = Seg(*sg)
+    p.dy = dy_src
+    p.n_out, p.on, p.oh, p.ow = n_out, on, oh, ow
+    p.partial, p.splits = partial.data_ptr(), splits
+    tok = _pb()
+    check(lib().b200sd_wgrad(C.byref(p), stream_ptr()), "wgrad")
+    k_alg = sum(max(0, min(nch * 64, srcs[si].dims[0] - c0)) for si, _, _, c0, nch in segs)
+    _pe(tok, "wgrad", 2.0 * on * oh * ow * n_out * k_alg, (on * oh * ow, n_out, k_alg))
+    if splits == 1 and not accumulate and out is None:
+        return partial[0]
+    if out is None:
+        out = torch.empty(n_out, k_total, device=dev, dtype=torch.float32)
+    check(lib().b200sd_wgrad_reduce(_p(partial), splits, n_out * k_total, _p(out), 1 if accumulate else 0,
+                                     stream_ptr()), "wgrad_reduce")
+    return out
 
 
 # ------------------------------------------------------------------------------------------------ others

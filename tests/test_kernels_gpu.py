@@ -293,3 +293,35 @@ def test_linear_residual_tma_epilogue_large(rt):
     out = rt.linear(a.to(dev), ops.pack_linear_weight(w.to(dev)), bias=b.to(dev), residual=res.to(dev))
     ref = a.float() @ bf(w).float().t() + b + res.float()
     assert relerr(out.cpu(), ref) < 6e-3
+
+
+# ------------------------------------------------------------------------------------------- weight gradient
+@pytest.mark.parametrize("n,h,w,cin,cout,k", [(2, 32, 32, 64, 128, 3), (4, 16, 16, 128, 192, 3), (5, 8, 8, 192, 256, 3),
+                                              (9, 4, 4, 256, 64, 3), (2, 32, 32, 7, 64, 3), (3, 16, 16, 320, 96, 1),
+                                              (2, 24, 20, 72, 40, 3), (16, 32, 32, 128, 128, 3)])
+def test_wgrad_conv(rt, n, h, w, cin, cout, k):
+    """MN-major tcgen05 wgrad vs torch autograd of F.conv2d on the same bf16-rounded operands."""
+    dev = _dev()
+    from sdb200 import ops
+    g = torch.Generator().manual_seed(n + h + cin + cout)
+    x = bf(torch.randn(n, cin, h, w, generator=g))
+    dy = bf(torch.randn(n, cout, h, w, generator=g))
+    wt = torch.zeros(cout, cin, k, k, requires_grad=True)
+    F.conv2d(x.float(), wt, padding=k // 2).backward(dy.float())
+    ldx, ldy = (cin + 7) // 8 * 8, (cout + 7) // 8 * 8
+    xd = torch.zeros(n * h * w, ldx, dtype=torch.bfloat16)
+    xd[:, :cin] = x.permute(0, 2, 3, 1).reshape(-1, cin)
+    dyd = torch.zeros(n * h * w, ldy, dtype=torch.bfloat16)
+    dyd[:, :cout] = dy.permute(0, 2, 3, 1).reshape(-1, cout)
+    xd, dyd = xd.to(dev), dyd.to(dev)
+    pad = k // 2
+    cp = (cin + 63) // 64 * 64
+    srcs = [rt.make_src(xd, n, h, w, cin, ld=ldx)]
+    segs = [(0, ky - pad, kx - pad, 0, cp // 64) for ky in range(k) for kx in range(k)]
+    dwp = rt.wgrad(srcs, segs, rt.make_src(dyd, n, h, w, cout, ld=ldy), cout, n, h, w)
+    torch.cuda.synchronize()
+    got = dwp.cpu().reshape(cout, k * k, cp)[:, :, :cin].permute(0, 2, 1).reshape(cout, cin, k, k)
+    assert torch.all(dwp.cpu().reshape(cout, k * k, cp)[:, :, cin:] == 0)  # padded columns read zero-filled channels
+    assert relerr(got, wt.grad) < 2e-3  # bf16 products, fp32 accumulation over n*h*w pixels, fp32 output
+    dwp2 = rt.wgrad(srcs, segs, rt.make_src(dyd, n, h, w, cout, ld=ldy), cout, n, h, w)
+    assert torch.equal(dwp, dwp2)  # split-K partials are reduced in fixed order
