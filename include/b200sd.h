@@ -167,6 +167,22 @@ int b200sd_groupnorm_apply(const void* x, int64_t ld_x, void* y, int64_t ld_y, c
                            const float* beta, int64_t n, int64_t hw, int c, int groups, float eps, int act,
                            void* stream);
 
+/* Backward of GroupNorm (+activation), given the forward's partial statistics (same stats0/stats1 as
+ * b200sd_groupnorm_apply), x, and dy = dL/d act(GN(x)):  dx = dL/dx (+ add, an optional extra gradient of x with the
+ * same geometry, e.g. the ResNet shortcut's). part: fp32 scratch [n, b200sd_rowblocks(n, hw, c), c, 2]; ab (optional):
+ * fp32 [n, c, 2] receiving per-image (sum dz, sum dz*xhat), whose sums over n are dbeta and dgamma. */
+int b200sd_rowblocks(int64_t n, int64_t hw, int c);
+int b200sd_groupnorm_bwd(const void* x, int64_t ld_x, const void* dy, int64_t ld_dy, const void* add, int64_t ld_add,
+                         void* dx, int64_t ld_dx, const float* stats0, int p0, int ld_s0, int c_split,
+                         const float* stats1, int p1, int ld_s1, const float* gamma, const float* beta, int64_t n,
+                         int64_t hw, int c, int groups, float eps, int act, float* part, float* ab, void* stream);
+/* Per-(image, row block) column sums of a bf16 [n, hw, ld_x] tensor: part fp32 [n, b200sd_rowblocks(n, hw, c), c]
+ * (bias gradients; the per-image time-embedding gradient of models/blocks.py:118). */
+int b200sd_colsum(const void* x, int64_t ld_x, int64_t n, int64_t hw, int c, float* part, void* stream);
+/* out[b, j] (+)= sum_r in[(b*rows + r)*cols*col_stride + j*col_stride], fp32, fixed order. */
+int b200sd_reduce_f32(const float* in, int64_t batch, int64_t rows, int64_t cols, int64_t col_stride, float* out,
+                      int accumulate, void* stream);
+
 /* ----------------------------------------------------------------------------------------------- attention
  * softmax(Q K^T / sqrt(d)) V per (batch, head) — nn.MultiheadAttention call sites models/blocks.py:128,140,242,
  * 254,480,495; CustomMultiheadAttention models/multihead_attention.py:41-80; DiT Attention models/attention.py:33-78.
@@ -175,6 +191,18 @@ int b200sd_groupnorm_apply(const void* x, int64_t ld_x, void* y, int64_t ld_y, c
 int b200sd_attention(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v,
                      void* out, int64_t ld_o, int64_t batch, int heads, int lq, int lk, int d, float scale,
                      void* stream);
+
+/* Training variants. b200sd_attention_lse also writes lse: fp32 [batch, heads, lq], the log2-domain log-sum-exp of the
+ * scaled scores. b200sd_attention_bwd recomputes the scores tile by tile from q, k, v and lse and returns dq / dk / dv
+ * (bf16, same layout as q / k / v); o and d_o are the forward output and its gradient; dvec is fp32 scratch
+ * [batch, heads, lq]. Needs K/V (and Q/dO) of one (batch, head) to fit shared memory: B200SD_ERR_UNSUPPORTED otherwise. */
+int b200sd_attention_lse(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v,
+                         void* out, int64_t ld_o, float* lse, int64_t batch, int heads, int lq, int lk, int d,
+                         float scale, void* stream);
+int b200sd_attention_bwd(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v,
+                         const void* o, int64_t ld_o, const void* d_o, int64_t ld_do, const float* lse, float* dvec,
+                         void* dq, int64_t ld_dq, void* dk, int64_t ld_dk, void* dv, int64_t ld_dv, int64_t batch,
+                         int heads, int lq, int lk, int d, float scale, void* stream);
 
 /* ------------------------------------------------------------------------------------- layout / glue
  * NCHW fp32 -> NHWC bf16 channel slice: dst[n, p, c_off + c] = bf16(src[n, c, p]), c < c. */

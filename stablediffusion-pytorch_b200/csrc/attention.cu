@@ -249,7 +249,8 @@ template <int D8>
 __global__ void __launch_bounds__(256)
     attention_resident_kernel(const __nv_bfloat16* __restrict__ q, long long ld_q, const __nv_bfloat16* __restrict__ k,
                               long long ld_k, const __nv_bfloat16* __restrict__ v, long long ld_v,
-                              __nv_bfloat16* __restrict__ out, long long ld_o, int lq, int lk, float scale_log2) {
+                              __nv_bfloat16* __restrict__ out, long long ld_o, int lq, int lk, float scale_log2,
+                              float* __restrict__ lse) {
     constexpr int PITCH = AttRes<D8>::PITCH;
     constexpr int K16 = D8 / 2;        // k16 chunks of the head dim
     constexpr bool TAIL = (D8 & 1);    // one trailing k8 chunk
@@ -409,6 +410,11 @@ __global__ void __launch_bounds__(256)
     l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
     const float i0 = 1.f / l0, i1 = 1.f / l1;
     const int r0 = q0 + warp * 16 + (lane >> 2), r1 = r0 + 8;
+    if (lse && (lane & 3) == 0) {  // log2-domain log-sum-exp of the scaled scores, for the backward pass
+        float* lp = lse + (b * gridDim.y + head) * lq;
+        if (r0 < lq) lp[r0] = m0 * scale_log2 + log2f(l0);
+        if (r1 < lq) lp[r1] = m1 * scale_log2 + log2f(l1);
+    }
     __nv_bfloat16* og = out + (b * lq) * ld_o + head * (D8 * 8);
 #pragma unroll
     for (int nb = 0; nb < D8; ++nb) {
@@ -431,7 +437,7 @@ static size_t resident_smem(int d8, int lk, int bq) {
 template <int D8>
 static int launch_resident(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v,
                            void* out, int64_t ld_o, int64_t batch, int heads, int lq, int lk, float scale,
-                           cudaStream_t st) {
+                           float* lse, cudaStream_t st) {
     const int warps = lq >= 128 ? 8 : lq > 32 ? 4 : lq > 16 ? 2 : 1;
     const int bq = warps * 16;
     const size_t smem = resident_smem(D8, lk, bq);
@@ -444,7 +450,7 @@ static int launch_resident(const void* q, int64_t ld_q, const void* k, int64_t l
     attention_resident_kernel<D8><<<grid, warps * 32, smem, st>>>(
         static_cast<const __nv_bfloat16*>(q), ld_q, static_cast<const __nv_bfloat16*>(k), ld_k,
         static_cast<const __nv_bfloat16*>(v), ld_v, static_cast<__nv_bfloat16*>(out), ld_o, lq, lk,
-        scale * 1.4426950408889634f);
+        scale * 1.4426950408889634f, lse);
     B200_CHECK_LAUNCH("attention_resident");
     return B200SD_OK;
 }
@@ -469,13 +475,302 @@ static int launch_attention(const void* q, int64_t ld_q, const void* k, int64_t 
     return B200SD_OK;
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// Attention BACKWARD (resident operands, same structure as the forward). One kernel, two roles:
+//   DKV = false ("dQ"):   rows = queries.  R1 = Q, R2 = dO, resident C1 = K, C2 = V.   outB = dQ = dS K
+//   DKV = true  ("dK,dV"): rows = keys.    R1 = K, R2 = V,  resident C1 = Q, C2 = dO.  outB = dK = dS^T Q, outA = dV = P^T dO
+// Per 64-column tile: S = R1 C1^T, dP = R2 C2^T, P = exp2(S*scale_log2 - L), dS = P o (dP - D) * scale, where L (the
+// forward's log-sum-exp) and D = rowsum(dO o O) belong to the query: per ROW in the dQ role, per COLUMN in the dK/dV
+// role. Scores are recomputed, never stored (the reference materialises B*H*L*L weights, multihead_attention.py:58-61).
+template <int D8, bool DKV>
+__global__ void __launch_bounds__(256)
+    attention_bwd_kernel(const __nv_bfloat16* __restrict__ r1, long long ld_r1, const __nv_bfloat16* __restrict__ r2,
+                         long long ld_r2, const __nv_bfloat16* __restrict__ c1, long long ld_c1,
+                         const __nv_bfloat16* __restrict__ c2, long long ld_c2, const float* __restrict__ lse,
+                         const float* __restrict__ dvec, __nv_bfloat16* __restrict__ out_b, long long ld_ob,
+                         __nv_bfloat16* __restrict__ out_a, long long ld_oa, int lr, int lc, int lq, float scale,
+                         float scale_log2) {
+    constexpr int PITCH = AttRes<D8>::PITCH;
+    constexpr int K16 = D8 / 2;
+    constexpr bool TAIL = (D8 & 1);
+    extern __shared__ __align__(16) uint8_t att_smem[];
+    const int nthreads = blockDim.x, bq = (nthreads >> 5) * 16;
+    const int lc_pad = (lc + 63) & ~63;
+    __nv_bfloat16* sC1 = reinterpret_cast<__nv_bfloat16*>(att_smem);
+    __nv_bfloat16* sC2 = sC1 + lc_pad * PITCH;
+    __nv_bfloat16* sR1 = sC2 + lc_pad * PITCH;
+    __nv_bfloat16* sR2 = sR1 + bq * PITCH;
+    float* sL = reinterpret_cast<float*>(sR2 + bq * PITCH);  // [lc_pad] (DKV only)
+    float* sD = sL + lc_pad;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int row0 = blockIdx.x * bq;
+    const int head = blockIdx.y;
+    const long long b = blockIdx.z;
+    const int hoff = head * (D8 * 8);
+    const __nv_bfloat16* r1g = r1 + (b * lr) * ld_r1 + hoff;
+    const __nv_bfloat16* r2g = r2 + (b * lr) * ld_r2 + hoff;
+    const __nv_bfloat16* c1g = c1 + (b * lc) * ld_c1 + hoff;
+    const __nv_bfloat16* c2g = c2 + (b * lc) * ld_c2 + hoff;
+    const float* lg = lse + (b * gridDim.y + head) * lq;
+    const float* dg = dvec + (b * gridDim.y + head) * lq;
+
+    for (int i = tid; i < lc_pad * D8; i += nthreads) {
+        const int r = i / D8, c = i - r * D8;
+        const bool ok = r < lc;
+        const long long ro = ok ? r : 0;
+        cp_async16(sC1 + r * PITCH + c * 8, c1g + ro * ld_c1 + c * 8, ok ? 16 : 0);
+        cp_async16(sC2 + r * PITCH + c * 8, c2g + ro * ld_c2 + c * 8, ok ? 16 : 0);
+    }
+    for (int i = tid; i < bq * D8; i += nthreads) {
+        const int r = i / D8, c = i - r * D8;
+        const bool ok = (row0 + r) < lr;
+        const long long ro = ok ? row0 + r : 0;
+        cp_async16(sR1 + r * PITCH + c * 8, r1g + ro * ld_r1 + c * 8, ok ? 16 : 0);
+        cp_async16(sR2 + r * PITCH + c * 8, r2g + ro * ld_r2 + c * 8, ok ? 16 : 0);
+    }
+    cp_async_commit();
+    if (DKV) {
+        for (int i = tid; i < lc_pad; i += nthreads) {
+            sL[i] = i < lc ? lg[i] : 0.f;
+            sD[i] = i < lc ? dg[i] : 0.f;
+        }
+    }
+    cp_async_wait<0>();
+    __syncthreads();
+    if (row0 + warp * 16 >= lr) return;
+
+    uint32_t f1[K16 > 0 ? K16 : 1][4], f2[K16 > 0 ? K16 : 1][4];
+    uint32_t t1[2] = {0u, 0u}, t2[2] = {0u, 0u};
+    {
+        const int ro = (warp * 16 + (lane & 7) + 8 * ((lane >> 3) & 1)) * PITCH;
+#pragma unroll
+        for (int kb = 0; kb < K16; ++kb) {
+            ldsm_x4(f1[kb], sR1 + ro + kb * 16 + 8 * (lane >> 4));
+            ldsm_x4(f2[kb], sR2 + ro + kb * 16 + 8 * (lane >> 4));
+        }
+        if (TAIL) {
+            ldsm_x2(t1, sR1 + ro + K16 * 16);
+            ldsm_x2(t2, sR2 + ro + K16 * 16);
+        }
+    }
+    const int rr0 = row0 + warp * 16 + (lane >> 2), rr1 = rr0 + 8;
+    float L0 = 0.f, L1 = 0.f, D0 = 0.f, D1 = 0.f;
+    if (!DKV) {
+        if (rr0 < lr) L0 = lg[rr0], D0 = dg[rr0];
+        if (rr1 < lr) L1 = lg[rr1], D1 = dg[rr1];
+    }
+    float acc_b[D8][4], acc_a[DKV ? D8 : 1][4];
+#pragma unroll
+    for (int i = 0; i < D8; ++i) acc_b[i][0] = acc_b[i][1] = acc_b[i][2] = acc_b[i][3] = 0.f;
+#pragma unroll
+    for (int i = 0; i < (DKV ? D8 : 1); ++i) acc_a[i][0] = acc_a[i][1] = acc_a[i][2] = acc_a[i][3] = 0.f;
+
+    const int ntiles = lc_pad >> 6;
+    for (int t = 0; t < ntiles; ++t) {
+        const __nv_bfloat16* tC1 = sC1 + t * 64 * PITCH;
+        const __nv_bfloat16* tC2 = sC2 + t * 64 * PITCH;
+        const int rem = lc - t * 64;
+        const int nb_valid = rem >= 64 ? 8 : (rem + 7) >> 3;
+        float s[8][4], dp[8][4];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f;
+            dp[i][0] = dp[i][1] = dp[i][2] = dp[i][3] = 0.f;
+        }
+#pragma unroll
+        for (int np = 0; np < 4; ++np) {
+            if (2 * np < nb_valid) {
+                const int off = (np * 16 + (lane & 7) + 8 * (lane >> 4)) * PITCH + 8 * ((lane >> 3) & 1);
+#pragma unroll
+                for (int kb = 0; kb < K16; ++kb) {
+                    uint32_t bf[4];
+                    ldsm_x4(bf, tC1 + off + kb * 16);
+                    mma16816(s[2 * np], f1[kb], bf[0], bf[1]);
+                    mma16816(s[2 * np + 1], f1[kb], bf[2], bf[3]);
+                    ldsm_x4(bf, tC2 + off + kb * 16);
+                    mma16816(dp[2 * np], f2[kb], bf[0], bf[1]);
+                    mma16816(dp[2 * np + 1], f2[kb], bf[2], bf[3]);
+                }
+            }
+        }
+        if (TAIL) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                if (4 * h < nb_valid) {
+                    uint32_t bf[4];
+                    ldsm_x4(bf, tC1 + (h * 32 + lane) * PITCH + K16 * 16);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) mma1688(s[4 * h + i], t1[0], t1[1], bf[i]);
+                    ldsm_x4(bf, tC2 + (h * 32 + lane) * PITCH + K16 * 16);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) mma1688(dp[4 * h + i], t2[0], t2[1], bf[i]);
+                }
+            }
+        }
+        // P and dS (dS overwrites dp)
+        const int cbase = t * 64 + (lane & 3) * 2;
+#pragma unroll
+        for (int nb = 0; nb < 8; ++nb) {
+            if (nb < nb_valid) {
+                const int col = cbase + nb * 8;
+                float la0 = L0, la1 = L0, lb0 = L1, lb1 = L1, da0 = D0, da1 = D0, db0 = D1, db1 = D1;
+                if (DKV) {
+                    la0 = lb0 = sL[col], la1 = lb1 = sL[col + 1];
+                    da0 = db0 = sD[col], da1 = db1 = sD[col + 1];
+                }
+                const bool v0 = col < lc, v1 = col + 1 < lc;
+                const float p0 = v0 ? ex2(fmaf(s[nb][0], scale_log2, -la0)) : 0.f;
+                const float p1 = v1 ? ex2(fmaf(s[nb][1], scale_log2, -la1)) : 0.f;
+                const float p2 = v0 ? ex2(fmaf(s[nb][2], scale_log2, -lb0)) : 0.f;
+                const float p3 = v1 ? ex2(fmaf(s[nb][3], scale_log2, -lb1)) : 0.f;
+                s[nb][0] = p0, s[nb][1] = p1, s[nb][2] = p2, s[nb][3] = p3;
+                dp[nb][0] = p0 * (dp[nb][0] - da0) * scale;
+                dp[nb][1] = p1 * (dp[nb][1] - da1) * scale;
+                dp[nb][2] = p2 * (dp[nb][2] - db0) * scale;
+                dp[nb][3] = p3 * (dp[nb][3] - db1) * scale;
+            } else {
+                s[nb][0] = s[nb][1] = s[nb][2] = s[nb][3] = 0.f;
+                dp[nb][0] = dp[nb][1] = dp[nb][2] = dp[nb][3] = 0.f;
+            }
+        }
+#pragma unroll
+        for (int kb = 0; kb < 4; ++kb) {
+            if (2 * kb < nb_valid) {
+                uint32_t pf[4], df[4];
+                df[0] = pack_bf16(dp[2 * kb][0], dp[2 * kb][1]);
+                df[1] = pack_bf16(dp[2 * kb][2], dp[2 * kb][3]);
+                df[2] = pack_bf16(dp[2 * kb + 1][0], dp[2 * kb + 1][1]);
+                df[3] = pack_bf16(dp[2 * kb + 1][2], dp[2 * kb + 1][3]);
+                if (DKV) {
+                    pf[0] = pack_bf16(s[2 * kb][0], s[2 * kb][1]);
+                    pf[1] = pack_bf16(s[2 * kb][2], s[2 * kb][3]);
+                    pf[2] = pack_bf16(s[2 * kb + 1][0], s[2 * kb + 1][1]);
+                    pf[3] = pack_bf16(s[2 * kb + 1][2], s[2 * kb + 1][3]);
+                }
+                const int off = (kb * 16 + (lane & 7) + 8 * ((lane >> 3) & 1)) * PITCH;
+#pragma unroll
+                for (int d2 = 0; d2 < K16; ++d2) {
+                    uint32_t bf[4];
+                    ldsm_x4_t(bf, tC1 + off + d2 * 16 + 8 * (lane >> 4));
+                    mma16816(acc_b[2 * d2], df, bf[0], bf[1]);
+                    mma16816(acc_b[2 * d2 + 1], df, bf[2], bf[3]);
+                    if (DKV) {
+                        ldsm_x4_t(bf, tC2 + off + d2 * 16 + 8 * (lane >> 4));
+                        mma16816(acc_a[2 * d2], pf, bf[0], bf[1]);
+                        mma16816(acc_a[2 * d2 + 1], pf, bf[2], bf[3]);
+                    }
+                }
+                if (TAIL) {
+                    uint32_t bf[2];
+                    ldsm_x2_t(bf, tC1 + off + K16 * 16);
+                    mma16816(acc_b[D8 - 1], df, bf[0], bf[1]);
+                    if (DKV) {
+                        ldsm_x2_t(bf, tC2 + off + K16 * 16);
+                        mma16816(acc_a[D8 - 1], pf, bf[0], bf[1]);
+                    }
+                }
+            }
+        }
+    }
+    __nv_bfloat16* ob = out_b + (b * lr) * ld_ob + hoff;
+    __nv_bfloat16* oa = DKV ? out_a + (b * lr) * ld_oa + hoff : nullptr;
+#pragma unroll
+    for (int nb = 0; nb < D8; ++nb) {
+        const int col = nb * 8 + (lane & 3) * 2;
+        if (rr0 < lr) {
+            *reinterpret_cast<__nv_bfloat162*>(ob + (long long)rr0 * ld_ob + col) =
+                __floats2bfloat162_rn(acc_b[nb][0], acc_b[nb][1]);
+            if (DKV)
+                *reinterpret_cast<__nv_bfloat162*>(oa + (long long)rr0 * ld_oa + col) =
+                    __floats2bfloat162_rn(acc_a[nb][0], acc_a[nb][1]);
+        }
+        if (rr1 < lr) {
+            *reinterpret_cast<__nv_bfloat162*>(ob + (long long)rr1 * ld_ob + col) =
+                __floats2bfloat162_rn(acc_b[nb][2], acc_b[nb][3]);
+            if (DKV)
+                *reinterpret_cast<__nv_bfloat162*>(oa + (long long)rr1 * ld_oa + col) =
+                    __floats2bfloat162_rn(acc_a[nb][2], acc_a[nb][3]);
+        }
+    }
+}
+
+// D[b, h, i] = sum_d dO[i, h*d + j] * O[i, h*d + j]
+__global__ void attn_dot_kernel(const __nv_bfloat16* __restrict__ o, long long ld_o, const __nv_bfloat16* __restrict__ d_o,
+                                long long ld_do, float* __restrict__ dvec, long long batch, int heads, int lq, int d) {
+    const long long total = batch * heads * lq;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int row = static_cast<int>(i % lq);
+        const long long bh = i / lq;
+        const int h = static_cast<int>(bh % heads);
+        const long long b = bh / heads;
+        const __nv_bfloat16* po = o + (b * lq + row) * ld_o + h * d;
+        const __nv_bfloat16* pd = d_o + (b * lq + row) * ld_do + h * d;
+        float acc = 0.f;
+        for (int j = 0; j < d; j += 8) {
+            const uint4 uo = *reinterpret_cast<const uint4*>(po + j), ud = *reinterpret_cast<const uint4*>(pd + j);
+            const __nv_bfloat162* ho = reinterpret_cast<const __nv_bfloat162*>(&uo);
+            const __nv_bfloat162* hd = reinterpret_cast<const __nv_bfloat162*>(&ud);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 a = __bfloat1622float2(ho[e]), c = __bfloat1622float2(hd[e]);
+                acc += a.x * c.x + a.y * c.y;
+            }
+        }
+        dvec[i] = acc;
+    }
+}
+
+static size_t bwd_smem(int d8, int lc, int bq) {
+    const int p16 = (d8 & 1) ? d8 : d8 + 1;
+    const size_t lc_pad = (size_t)((lc + 63) & ~63);
+    return (2 * lc_pad + 2 * bq) * p16 * 16 + 2 * lc_pad * sizeof(float);
+}
+
+template <int D8, bool DKV>
+static int launch_bwd(const void* r1, int64_t ld_r1, const void* r2, int64_t ld_r2, const void* c1, int64_t ld_c1,
+                      const void* c2, int64_t ld_c2, const float* lse, const float* dvec, void* out_b, int64_t ld_ob,
+                      void* out_a, int64_t ld_oa, int64_t batch, int heads, int lr, int lc, int lq, float scale,
+                      cudaStream_t st) {
+    const int warps = lr >= 128 ? 8 : lr > 32 ? 4 : lr > 16 ? 2 : 1;
+    const int bq = warps * 16;
+    const size_t smem = bwd_smem(D8, lc, bq);
+    static bool configured = false;
+    if (!configured) {
+        cudaFuncSetAttribute(attention_bwd_kernel<D8, DKV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        configured = true;
+    }
+    dim3 grid((lr + bq - 1) / bq, heads, (unsigned)batch);
+    attention_bwd_kernel<D8, DKV><<<grid, warps * 32, smem, st>>>(
+        static_cast<const __nv_bfloat16*>(r1), ld_r1, static_cast<const __nv_bfloat16*>(r2), ld_r2,
+        static_cast<const __nv_bfloat16*>(c1), ld_c1, static_cast<const __nv_bfloat16*>(c2), ld_c2, lse, dvec,
+        static_cast<__nv_bfloat16*>(out_b), ld_ob, static_cast<__nv_bfloat16*>(out_a), ld_oa, lr, lc, lq, scale,
+        scale * 1.4426950408889634f);
+    B200_CHECK_LAUNCH("attention_bwd");
+    return B200SD_OK;
+}
+
+template <int D8>
+static int attention_bwd_d8(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v,
+                            const void* d_o, int64_t ld_do, const float* lse, const float* dvec, void* dq, int64_t ld_dq,
+                            void* dk, int64_t ld_dk, void* dv, int64_t ld_dv, int64_t batch, int heads, int lq, int lk,
+                            float scale, cudaStream_t st) {
+    int rc = launch_bwd<D8, false>(q, ld_q, d_o, ld_do, k, ld_k, v, ld_v, lse, dvec, dq, ld_dq, nullptr, 0, batch, heads,
+                                   lq, lk, lq, scale, st);
+    if (rc) return rc;
+    return launch_bwd<D8, true>(k, ld_k, v, ld_v, q, ld_q, d_o, ld_do, lse, dvec, dk, ld_dk, dv, ld_dv, batch, heads, lk,
+                                lq, lq, scale, st);
+}
+
 }  // namespace b200
 
 using namespace b200;
 
-extern "C" int b200sd_attention(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v,
-                                void* out, int64_t ld_o, int64_t batch, int heads, int lq, int lk, int d, float scale,
-                                void* stream) {
+static int attention_fwd(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v,
+                         void* out, int64_t ld_o, int64_t batch, int heads, int lq, int lk, int d, float scale,
+                         float* lse, void* stream) {
     B200_REQUIRE(q && k && v && out, "attention: null pointer");
     B200_REQUIRE(batch >= 0 && heads >= 1 && lq >= 1 && lk >= 1, "attention: bad sizes");
     B200_REQUIRE(batch <= 65535 && heads <= 65535, "attention: batch/heads exceed grid limits");
@@ -491,15 +786,19 @@ extern "C" int b200sd_attention(const void* q, int64_t ld_q, const void* k, int6
     cudaStream_t st = as_stream(stream);
     if (resident_smem(d / 8, lk, 128) <= 112 * 1024) {  // two CTAs per SM still fit
         switch (d / 8) {
-            case 1: return launch_resident<1>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, st);
-            case 2: return launch_resident<2>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, st);
-            case 3: return launch_resident<3>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, st);
-            case 4: return launch_resident<4>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, st);
-            case 5: return launch_resident<5>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, st);
-            case 6: return launch_resident<6>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, st);
-            case 7: return launch_resident<7>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, st);
-            default: return launch_resident<8>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, st);
+            case 1: return launch_resident<1>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, lse, st);
+            case 2: return launch_resident<2>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, lse, st);
+            case 3: return launch_resident<3>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, lse, st);
+            case 4: return launch_resident<4>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, lse, st);
+            case 5: return launch_resident<5>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, lse, st);
+            case 6: return launch_resident<6>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, lse, st);
+            case 7: return launch_resident<7>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, lse, st);
+            default: return launch_resident<8>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, lse, st);
         }
+    }
+    if (lse) {
+        set_error("attention: log-sum-exp output needs the resident-KV kernel (lk=%d, d=%d do not fit)", lk, d);
+        return B200SD_ERR_UNSUPPORTED;
     }
     const int dp = (d + 15) / 16 * 16;
     switch (dp) {
@@ -508,4 +807,59 @@ extern "C" int b200sd_attention(const void* q, int64_t ld_q, const void* k, int6
         case 48: return launch_attention<48>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, d, scale, st);
         default: return launch_attention<64>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, d, scale, st);
     }
+}
+
+extern "C" int b200sd_attention(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v,
+                                void* out, int64_t ld_o, int64_t batch, int heads, int lq, int lk, int d, float scale,
+                                void* stream) {
+    return attention_fwd(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, d, scale, nullptr, stream);
+}
+
+extern "C" int b200sd_attention_lse(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v,
+                                    int64_t ld_v, void* out, int64_t ld_o, float* lse, int64_t batch, int heads, int lq,
+                                    int lk, int d, float scale, void* stream) {
+    B200_REQUIRE(lse, "attention_lse: null lse");
+    return attention_fwd(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, d, scale, lse, stream);
+}
+
+/* Backward of softmax(Q K^T * scale) V: dq/dk/dv (bf16, same row/head layout as q/k/v) from d_o, the forward output
+ * `o` and the forward's log-sum-exp `lse` (b200sd_attention_lse). dvec: fp32 scratch [batch, heads, lq]. */
+extern "C" int b200sd_attention_bwd(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v,
+                                    int64_t ld_v, const void* o, int64_t ld_o, const void* d_o, int64_t ld_do,
+                                    const float* lse, float* dvec, void* dq, int64_t ld_dq, void* dk, int64_t ld_dk,
+                                    void* dv, int64_t ld_dv, int64_t batch, int heads, int lq, int lk, int d,
+                                    float scale, void* stream) {
+    B200_REQUIRE(q && k && v && o && d_o && lse && dvec && dq && dk && dv, "attention_bwd: null pointer");
+    B200_REQUIRE(batch >= 0 && heads >= 1 && lq >= 1 && lk >= 1 && batch <= 65535 && heads <= 65535,
+                 "attention_bwd: bad sizes");
+    if (d % 8 != 0 || d < 8 || d > 64) {
+        set_error("attention_bwd: head dim %d unsupported (need a multiple of 8 in [8, 64])", d);
+        return B200SD_ERR_UNSUPPORTED;
+    }
+    for (int64_t ld : {ld_q, ld_k, ld_v, ld_o, ld_do, ld_dq, ld_dk, ld_dv})
+        B200_REQUIRE(ld % 8 == 0, "attention_bwd: leading dims must be multiples of 8");
+    if (batch == 0) return B200SD_OK;
+    const int lmax = lq > lk ? lq : lk;
+    if (bwd_smem(d / 8, lmax, 128) > 220 * 1024) {
+        set_error("attention_bwd: lq=%d lk=%d d=%d do not fit the resident kernel", lq, lk, d);
+        return B200SD_ERR_UNSUPPORTED;
+    }
+    cudaStream_t st = as_stream(stream);
+    {
+        const long long total = batch * heads * (long long)lq;
+        long long blocks = (total + 255) / 256;
+        if (blocks > 8ll * sm_count()) blocks = 8ll * sm_count();
+        attn_dot_kernel<<<(int)blocks, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(o), ld_o,
+                                                     static_cast<const __nv_bfloat16*>(d_o), ld_do, dvec, batch, heads, lq, d);
+        B200_CHECK_LAUNCH("attention_dot");
+    }
+#define B200_BWD(N) \
+    case N: return attention_bwd_d8<N>(q, ld_q, k, ld_k, v, ld_v, d_o, ld_do, lse, dvec, dq, ld_dq, dk, ld_dk, dv, ld_dv, \
+                                       batch, heads, lq, lk, scale, st);
+    switch (d / 8) {
+        B200_BWD(1) B200_BWD(2) B200_BWD(3) B200_BWD(4) B200_BWD(5) B200_BWD(6) B200_BWD(7)
+        default: return attention_bwd_d8<8>(q, ld_q, k, ld_k, v, ld_v, d_o, ld_do, lse, dvec, dq, ld_dq, dk, ld_dk, dv,
+                                            ld_dv, batch, heads, lq, lk, scale, st);
+    }
+#undef B200_BWD
 }

@@ -193,6 +193,245 @@ __global__ void __launch_bounds__(256)
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// GroupNorm (+activation) BACKWARD. With xhat = (x - mean) * rstd, z = xhat * gamma + beta, y = act(z):
+//   dz = dy * act'(z);   A[c] = sum_rows dz,  B[c] = sum_rows dz * xhat   (per image; dbeta = sum_n A, dgamma = sum_n B)
+//   S1[g] = sum_{c in g} gamma[c] A[c],  S2[g] = sum_{c in g} gamma[c] B[c]
+//   dx = rstd * (gamma * dz - (S1 + xhat * S2) / (hw * cpg))  (+ an optional extra gradient of x, e.g. the shortcut's)
+// Pass 1 (gn_bwd_reduce) writes per-(image, row block) partial A/B; pass 2 (gn_bwd_apply) folds them in fixed order
+// and streams dx. Mean / rstd are rebuilt from the forward's partial statistics exactly as gn_apply does.
+__device__ __forceinline__ float act_grad(float z, int act) {
+    if (act == B200SD_ACT_SILU) {
+        const float s = 1.f / (1.f + __expf(-z));
+        return s * (1.f + z * (1.f - s));
+    }
+    if (act == B200SD_ACT_RELU) return z > 0.f ? 1.f : 0.f;
+    return 1.f;
+}
+
+// shared prologue: per-channel mean/rstd-derived (scale = rstd*gamma, shift = beta - mean*scale) plus per-channel
+// mean and rstd themselves, from the forward's partial statistics
+__device__ __forceinline__ void gn_channel_params(float* sc, float* sh, float* mu, float* rs, float* gs, StatSeg s0,
+                                                  int c_split, StatSeg s1, const float* gamma, const float* beta,
+                                                  long long hw, int c, int groups, float eps, int img) {
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const int cpg = c / groups;
+    for (int ch = tid; ch < c; ch += nt) {
+        const bool first = ch < c_split;
+        const StatSeg sg = first ? s0 : s1;
+        const int cc = first ? ch : ch - c_split;
+        const float* p = sg.ptr + (static_cast<long long>(img) * sg.p * sg.ld + cc) * 2;
+        float a = 0.f, b = 0.f;
+        for (int k = 0; k < sg.p; ++k) {
+            const float2 v = *reinterpret_cast<const float2*>(p + static_cast<long long>(k) * sg.ld * 2);
+            a += v.x, b += v.y;
+        }
+        sc[ch] = a, sh[ch] = b;
+    }
+    __syncthreads();
+    const float inv_cnt = 1.f / (static_cast<float>(hw) * cpg);
+    for (int g = tid; g < groups; g += nt) {
+        float a = 0.f, b = 0.f;
+        for (int k = 0; k < cpg; ++k) a += sc[g * cpg + k], b += sh[g * cpg + k];
+        const float mean = a * inv_cnt;
+        const float var = fmaxf(b * inv_cnt - mean * mean, 0.f);
+        gs[2 * g] = mean, gs[2 * g + 1] = rsqrtf(var + eps);
+    }
+    __syncthreads();
+    for (int ch = tid; ch < c; ch += nt) {
+        const int g = ch / cpg;
+        const float ga = gamma ? gamma[ch] : 1.f, be = beta ? beta[ch] : 0.f;
+        const float scale = gs[2 * g + 1] * ga;
+        sc[ch] = scale, sh[ch] = be - gs[2 * g] * scale;
+        mu[ch] = gs[2 * g], rs[ch] = gs[2 * g + 1];
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(256)
+    gn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, const __nv_bfloat16* __restrict__ dy,
+                         long long ld_dy, StatSeg s0, int c_split, StatSeg s1, const float* __restrict__ gamma,
+                         const float* __restrict__ beta, long long hw, int c, int groups, float eps, int act,
+                         int rows_per_block, int rpp, float* __restrict__ part /* [n][gridDim.x][c][2] */) {
+    extern __shared__ float gn_sm[];
+    float* sc = gn_sm;
+    float* sh = sc + c;
+    float* mu = sh + c;
+    float* rs = mu + c;
+    float* gs = rs + c;                 // [groups][2]
+    float* red = gs + 2 * groups;       // [rpp][c][2]
+    const int img = blockIdx.y, tid = threadIdx.x;
+    gn_channel_params(sc, sh, mu, rs, gs, s0, c_split, s1, gamma, beta, hw, c, groups, eps, img);
+    const int cv = c >> 3;
+    const int v = tid % cv, r0 = tid / cv;
+    float a[8], b[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = b[j] = 0.f;
+    if (r0 < rpp) {
+        float scl[8], sft[8], m[8], r[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) scl[j] = sc[v * 8 + j], sft[j] = sh[v * 8 + j], m[j] = mu[v * 8 + j], r[j] = rs[v * 8 + j];
+        const long long row_begin = static_cast<long long>(blockIdx.x) * rows_per_block;
+        long long row_end = row_begin + rows_per_block;
+        if (row_end > hw) row_end = hw;
+        const __nv_bfloat16* xs = x + static_cast<long long>(img) * hw * ld_x + v * 8;
+        const __nv_bfloat16* ds = dy + static_cast<long long>(img) * hw * ld_dy + v * 8;
+        for (long long rr = row_begin + r0; rr < row_end; rr += rpp) {
+            const uint4 ux = *reinterpret_cast<const uint4*>(xs + rr * ld_x);
+            const uint4 ud = *reinterpret_cast<const uint4*>(ds + rr * ld_dy);
+            const __nv_bfloat162* hx = reinterpret_cast<const __nv_bfloat162*>(&ux);
+            const __nv_bfloat162* hd = reinterpret_cast<const __nv_bfloat162*>(&ud);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 fx = __bfloat1622float2(hx[j]), fd = __bfloat1622float2(hd[j]);
+                const float z0 = fx.x * scl[2 * j] + sft[2 * j], z1 = fx.y * scl[2 * j + 1] + sft[2 * j + 1];
+                const float d0 = fd.x * act_grad(z0, act), d1 = fd.y * act_grad(z1, act);
+                a[2 * j] += d0, a[2 * j + 1] += d1;
+                b[2 * j] += d0 * (fx.x - m[2 * j]) * r[2 * j], b[2 * j + 1] += d1 * (fx.y - m[2 * j + 1]) * r[2 * j + 1];
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) red[(r0 * c + v * 8 + j) * 2] = a[j], red[(r0 * c + v * 8 + j) * 2 + 1] = b[j];
+    }
+    __syncthreads();
+    float* dst = part + (static_cast<long long>(img) * gridDim.x + blockIdx.x) * c * 2;
+    for (int i = tid; i < 2 * c; i += blockDim.x) {
+        float s = 0.f;
+        for (int k = 0; k < rpp; ++k) s += red[k * c * 2 + i];
+        dst[i] = s;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+    gn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, const __nv_bfloat16* __restrict__ dy,
+                        long long ld_dy, const __nv_bfloat16* __restrict__ add, long long ld_add,
+                        __nv_bfloat16* __restrict__ dx, long long ld_dx, StatSeg s0, int c_split, StatSeg s1,
+                        const float* __restrict__ gamma, const float* __restrict__ beta, long long hw, int c, int groups,
+                        float eps, int act, int rows_per_block, int rpp, const float* __restrict__ part, int pb,
+                        float* __restrict__ ab /* [n][c][2] or null */) {
+    extern __shared__ float gn_sm[];
+    float* sc = gn_sm;
+    float* sh = sc + c;
+    float* mu = sh + c;
+    float* rs = mu + c;
+    float* gs = rs + c;               // [groups][2]
+    float* ca = gs + 2 * groups;      // [c] gamma*A then unused
+    float* cb = ca + c;               // [c] gamma*B
+    float* g12 = cb + c;              // [groups][2] S1, S2 scaled by 1/(hw*cpg)
+    const int img = blockIdx.y, tid = threadIdx.x, nt = blockDim.x;
+    const int cpg = c / groups;
+    gn_channel_params(sc, sh, mu, rs, gs, s0, c_split, s1, gamma, beta, hw, c, groups, eps, img);
+    for (int ch = tid; ch < c; ch += nt) {
+        const float* p = part + (static_cast<long long>(img) * pb * c + ch) * 2;
+        float a = 0.f, b = 0.f;
+        for (int k = 0; k < pb; ++k) a += p[static_cast<long long>(k) * c * 2], b += p[static_cast<long long>(k) * c * 2 + 1];
+        if (ab && blockIdx.x == 0) ab[(static_cast<long long>(img) * c + ch) * 2] = a, ab[(static_cast<long long>(img) * c + ch) * 2 + 1] = b;
+        const float ga = gamma ? gamma[ch] : 1.f;
+        ca[ch] = ga * a, cb[ch] = ga * b;
+    }
+    __syncthreads();
+    const float inv_cnt = 1.f / (static_cast<float>(hw) * cpg);
+    for (int g = tid; g < groups; g += nt) {
+        float a = 0.f, b = 0.f;
+        for (int k = 0; k < cpg; ++k) a += ca[g * cpg + k], b += cb[g * cpg + k];
+        g12[2 * g] = a * inv_cnt, g12[2 * g + 1] = b * inv_cnt;
+    }
+    __syncthreads();
+    const int cv = c >> 3;
+    const int v = tid % cv, r0 = tid / cv;
+    if (r0 >= rpp) return;
+    float scl[8], sft[8], m[8], r[8], t1[8], t2[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int ch = v * 8 + j, g = ch / cpg;
+        scl[j] = sc[ch], sft[j] = sh[ch], m[j] = mu[ch], r[j] = rs[ch], t1[j] = g12[2 * g], t2[j] = g12[2 * g + 1];
+    }
+    const long long row_begin = static_cast<long long>(blockIdx.x) * rows_per_block;
+    long long row_end = row_begin + rows_per_block;
+    if (row_end > hw) row_end = hw;
+    const long long base = static_cast<long long>(img) * hw;
+    for (long long rr = row_begin + r0; rr < row_end; rr += rpp) {
+        const uint4 ux = *reinterpret_cast<const uint4*>(x + (base + rr) * ld_x + v * 8);
+        const uint4 ud = *reinterpret_cast<const uint4*>(dy + (base + rr) * ld_dy + v * 8);
+        uint4 ua = make_uint4(0u, 0u, 0u, 0u);
+        if (add) ua = *reinterpret_cast<const uint4*>(add + (base + rr) * ld_add + v * 8);
+        const __nv_bfloat162* hx = reinterpret_cast<const __nv_bfloat162*>(&ux);
+        const __nv_bfloat162* hd = reinterpret_cast<const __nv_bfloat162*>(&ud);
+        const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&ua);
+        uint4 o;
+        __nv_bfloat162* ho = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 fx = __bfloat1622float2(hx[j]), fd = __bfloat1622float2(hd[j]), fa = __bfloat1622float2(ha[j]);
+            float res[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int jj = 2 * j + e;
+                const float xv = e ? fx.y : fx.x, dv = e ? fd.y : fd.x, av = e ? fa.y : fa.x;
+                const float z = xv * scl[jj] + sft[jj];
+                const float dz = dv * act_grad(z, act);
+                const float xh = (xv - m[jj]) * r[jj];
+                const float gam = scl[jj] / r[jj];  // gamma = scale / rstd
+                res[e] = r[jj] * (gam * dz - t1[jj] - xh * t2[jj]) + av;
+            }
+            ho[j] = __floats2bfloat162_rn(res[0], res[1]);
+        }
+        *reinterpret_cast<uint4*>(dx + (base + rr) * ld_dx + v * 8) = o;
+    }
+}
+
+// out[b][c] (+)= sum over r of in[b][r][c]  (fp32; bias / GroupNorm-affine / time-embedding gradients)
+__global__ void reduce_f32_kernel(const float* __restrict__ in, long long batch, long long rows, long long cols,
+                                  long long col_stride, float* __restrict__ out, int accumulate) {
+    const long long total = batch * cols;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const long long b = i / cols, cidx = i - b * cols;
+        const float* p = in + b * rows * cols * col_stride + cidx * col_stride;
+        float s = 0.f;
+        for (long long r = 0; r < rows; ++r) s += p[r * cols * col_stride];
+        out[i] = accumulate ? out[i] + s : s;
+    }
+}
+
+// per-(image, row block) column sums of a bf16 [n, hw, ld] tensor -> fp32 part[n][gridDim.x][c]
+__global__ void __launch_bounds__(256)
+    colsum_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, long long hw, int c, int rows_per_block, int rpp,
+                  float* __restrict__ part) {
+    extern __shared__ float gn_sm[];  // [rpp][c]
+    const int img = blockIdx.y, tid = threadIdx.x;
+    const int cv = c >> 3;
+    const int v = tid % cv, r0 = tid / cv;
+    if (r0 < rpp) {
+        float a[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] = 0.f;
+        const long long row_begin = static_cast<long long>(blockIdx.x) * rows_per_block;
+        long long row_end = row_begin + rows_per_block;
+        if (row_end > hw) row_end = hw;
+        const __nv_bfloat16* xs = x + static_cast<long long>(img) * hw * ld_x + v * 8;
+        for (long long rr = row_begin + r0; rr < row_end; rr += rpp) {
+            const uint4 u = *reinterpret_cast<const uint4*>(xs + rr * ld_x);
+            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 f = __bfloat1622float2(h[j]);
+                a[2 * j] += f.x, a[2 * j + 1] += f.y;
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) gn_sm[r0 * c + v * 8 + j] = a[j];
+    }
+    __syncthreads();
+    float* dst = part + (static_cast<long long>(img) * gridDim.x + blockIdx.x) * c;
+    for (int i = tid; i < c; i += blockDim.x) {
+        float s = 0.f;
+        for (int k = 0; k < rpp; ++k) s += gn_sm[k * c + i];
+        dst[i] = s;
+    }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -289,5 +528,97 @@ extern "C" int b200sd_groupnorm_apply(const void* x, int64_t ld_x, void* y, int6
         static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y, s0, c_split, s1, gamma, beta,
         hw, c, groups, eps, act, (int)rows_per_block, rpp);
     B200_CHECK_LAUNCH("groupnorm_apply");
+    return B200SD_OK;
+}
+
+// row-block geometry shared by the backward / column-sum kernels
+struct RowGeom {
+    int cv, rpp, threads, rows_per_block, blocks_per_img;
+};
+static RowGeom row_geom(int64_t n, int64_t hw, int c) {
+    RowGeom g;
+    g.cv = c / 8;
+    g.rpp = 256 / g.cv;
+    if (g.rpp > hw) g.rpp = (int)hw;
+    if (g.rpp < 1) g.rpp = 1;
+    g.threads = ((g.cv * g.rpp + 31) / 32) * 32;
+    long long bpi = (4ll * sm_count() + n - 1) / n;
+    long long max_bpi = (hw + 8ll * g.rpp - 1) / (8ll * g.rpp);
+    if (bpi > max_bpi) bpi = max_bpi;
+    if (bpi < 1) bpi = 1;
+    long long rpb = (hw + bpi - 1) / bpi;
+    rpb = (rpb + g.rpp - 1) / g.rpp * g.rpp;
+    g.rows_per_block = (int)rpb;
+    g.blocks_per_img = (int)((hw + rpb - 1) / rpb);
+    return g;
+}
+
+extern "C" int b200sd_rowblocks(int64_t n, int64_t hw, int c) {
+    if (n <= 0 || hw <= 0 || c <= 0 || c % 8) return 0;
+    return row_geom(n, hw, c).blocks_per_img;
+}
+
+extern "C" int b200sd_groupnorm_bwd(const void* x, int64_t ld_x, const void* dy, int64_t ld_dy, const void* add,
+                                    int64_t ld_add, void* dx, int64_t ld_dx, const float* stats0, int p0, int ld_s0,
+                                    int c_split, const float* stats1, int p1, int ld_s1, const float* gamma,
+                                    const float* beta, int64_t n, int64_t hw, int c, int groups, float eps, int act,
+                                    float* part, float* ab, void* stream) {
+    B200_REQUIRE(x && dy && dx && stats0 && part, "groupnorm_bwd: null pointer");
+    B200_REQUIRE(groups > 0 && c > 0 && c % groups == 0 && c % 8 == 0 && c <= 2048,
+                 "groupnorm_bwd: channels must be divisible by groups and by 8, <= 2048");
+    B200_REQUIRE(ld_x % 8 == 0 && ld_dy % 8 == 0 && ld_dx % 8 == 0 && (!add || ld_add % 8 == 0),
+                 "groupnorm_bwd: row pitches must be multiples of 8 elements");
+    B200_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dx) |
+                   reinterpret_cast<uintptr_t>(add)) & 15) == 0, "groupnorm_bwd: pointers unaligned");
+    B200_REQUIRE(c_split >= 0 && c_split <= c && (c_split == c || stats1), "groupnorm_bwd: bad statistics split");
+    B200_REQUIRE(n <= 65535, "groupnorm_bwd: batch exceeds grid limit");
+    if (n == 0 || hw == 0) return B200SD_OK;
+    const RowGeom g = row_geom(n, hw, c);
+    StatSeg s0{stats0, p0, ld_s0}, s1{stats1, p1, ld_s1};
+    dim3 grid((unsigned)g.blocks_per_img, (unsigned)n);
+    cudaStream_t st = as_stream(stream);
+    const size_t sm1 = (size_t)(4 * c + 2 * groups + 2 * g.rpp * c) * sizeof(float);
+    const size_t sm2 = (size_t)(6 * c + 4 * groups) * sizeof(float);
+    static bool configured = false;
+    if (!configured) {
+        cudaFuncSetAttribute(gn_bwd_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+        cudaFuncSetAttribute(gn_bwd_apply_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        configured = true;
+    }
+    B200_REQUIRE(sm1 <= 160 * 1024, "groupnorm_bwd: reduction scratch too large");
+    gn_bwd_reduce_kernel<<<grid, g.threads, sm1, st>>>(
+        static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<const __nv_bfloat16*>(dy), ld_dy, s0, c_split, s1, gamma,
+        beta, hw, c, groups, eps, act, g.rows_per_block, g.rpp, part);
+    B200_CHECK_LAUNCH("groupnorm_bwd_reduce");
+    gn_bwd_apply_kernel<<<grid, g.threads, sm2, st>>>(
+        static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<const __nv_bfloat16*>(dy), ld_dy,
+        static_cast<const __nv_bfloat16*>(add), ld_add, static_cast<__nv_bfloat16*>(dx), ld_dx, s0, c_split, s1, gamma,
+        beta, hw, c, groups, eps, act, g.rows_per_block, g.rpp, part, g.blocks_per_img, ab);
+    B200_CHECK_LAUNCH("groupnorm_bwd_apply");
+    return B200SD_OK;
+}
+
+extern "C" int b200sd_colsum(const void* x, int64_t ld_x, int64_t n, int64_t hw, int c, float* part, void* stream) {
+    B200_REQUIRE(x && part, "colsum: null pointer");
+    B200_REQUIRE(c > 0 && c % 8 == 0 && c <= 2048 && ld_x % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0,
+                 "colsum: needs channels %% 8 == 0 (<= 2048) and 16-byte aligned rows");
+    B200_REQUIRE(n <= 65535, "colsum: batch exceeds grid limit");
+    if (n == 0 || hw == 0) return B200SD_OK;
+    const RowGeom g = row_geom(n, hw, c);
+    dim3 grid((unsigned)g.blocks_per_img, (unsigned)n);
+    colsum_kernel<<<grid, g.threads, (size_t)g.rpp * c * sizeof(float), as_stream(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), ld_x, hw, c, g.rows_per_block, g.rpp, part);
+    B200_CHECK_LAUNCH("colsum");
+    return B200SD_OK;
+}
+
+extern "C" int b200sd_reduce_f32(const float* in, int64_t batch, int64_t rows, int64_t cols, int64_t col_stride,
+                                 float* out, int accumulate, void* stream) {
+    B200_REQUIRE(in && out && batch >= 0 && rows >= 0 && cols >= 0 && col_stride >= 1, "reduce_f32: bad arguments");
+    if (batch * cols == 0) return B200SD_OK;
+    long long blocks = (batch * cols + 127) / 128;
+    if (blocks > 4ll * sm_count()) blocks = 4ll * sm_count();
+    reduce_f32_kernel<<<(int)blocks, 128, 0, as_stream(stream)>>>(in, batch, rows, cols, col_stride, out, accumulate);
+    B200_CHECK_LAUNCH("reduce_f32");
     return B200SD_OK;
 }

@@ -17,7 +17,8 @@ _ACT = {None: 0, "none": 0, "silu": 1, "relu": 2}
 
 EXPORTS = [
     "b200sd_last_error", "b200sd_version", "b200sd_launch_count", "b200sd_sched_add_noise",
-    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_attention",
+    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_attention_lse", "b200sd_attention_bwd", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_rowblocks", "b200sd_groupnorm_bwd", "b200sd_colsum",
+    "b200sd_reduce_f32", "b200sd_attention",
     "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16",
 ]
 
@@ -84,7 +85,15 @@ def lib():
         L.b200sd_groupnorm.argtypes = [vp, i64, vp, i64, vp, vp, i64, i64, i32, i32, f32, i32, vp]
         L.b200sd_groupnorm_apply.argtypes = [vp, i64, vp, i64, vp, i32, i32, i32, vp, i32, i32, vp, vp, i64, i64, i32, i32,
                                              f32, i32, vp]
+        L.b200sd_rowblocks.argtypes = [i64, i64, i32]
+        L.b200sd_groupnorm_bwd.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, vp, i32, i32, i32, vp, i32, i32, vp, vp, i64,
+                                           i64, i32, i32, f32, i32, vp, vp, vp]
+        L.b200sd_colsum.argtypes = [vp, i64, i64, i64, i32, vp, vp]
+        L.b200sd_reduce_f32.argtypes = [vp, i64, i64, i64, i64, vp, i32, vp]
         L.b200sd_attention.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, i64, i32, i32, i32, i32, f32, vp]
+        L.b200sd_attention_lse.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, vp, i64, i32, i32, i32, i32, f32, vp]
+        L.b200sd_attention_bwd.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, vp, i64, vp, vp, vp, i64, vp, i64, vp, i64,
+                                           i64, i32, i32, i32, i32, f32, vp]
         L.b200sd_nchw_to_nhwc.argtypes = [vp, vp, i64, i32, i64, i32, i64, vp]
         L.b200sd_nhwc_to_nchw.argtypes = [vp, i32, i64, vp, i64, i32, i64, vp]
         L.b200sd_mask_cond.argtypes = [vp, vp, vp, i64, i32, i64, i32, i32, i32, i32, i32, i32, vp]
@@ -370,6 +379,49 @@ def groupnorm(x, n, hw, c, groups, gamma, beta, eps=1e-5, act=None, out=None, ld
     return out
 
 
+def groupnorm_bwd(x, dy, n, hw, c, groups, gamma, beta, segs, eps=1e-5, act=None, add=None, ld_x=None, ld_dy=None):
+    """-> (dx bf16 [n*hw, c], dgamma fp32 [c], dbeta fp32 [c])."""
+    dev = x.device
+    ld_x = x.stride(0) if ld_x is None else ld_x
+    ld_dy = dy.stride(0) if ld_dy is None else ld_dy
+    pb = int(lib().b200sd_rowblocks(n, hw, c))
+    part = torch.empty(n, pb, c, 2, device=dev, dtype=torch.float32)
+    ab = torch.empty(n, c, 2, device=dev, dtype=torch.float32)
+    dx = torch.empty(n * hw, c, device=dev, dtype=torch.bfloat16)
+    (s0, p0, l0, c0) = segs[0]
+    s1, p1, l1 = (segs[1][0], segs[1][1], segs[1][2]) if len(segs) > 1 else (None, 0, 0)
+    tok = _pb()
+    check(lib().b200sd_groupnorm_bwd(_p(x), ld_x, _p(dy), ld_dy, _p(add), 0 if add is None else add.stride(0), _p(dx), c,
+                                      _p(s0), p0, l0, c0 if len(segs) > 1 else c, _p(s1), p1, l1, _p(gamma), _p(beta), n,
+                                      hw, c, groups, float(eps), _ACT[act], _p(part), _p(ab), stream_ptr()),
+          "groupnorm_bwd")
+    _pe(tok, "groupnorm_bwd", (10.0 + (2.0 if add is not None else 0.0)) * n * hw * c, (n, hw, c))
+    dgamma = torch.empty(c, device=dev, dtype=torch.float32)
+    dbeta = torch.empty(c, device=dev, dtype=torch.float32)
+    reduce_f32(ab.view(-1)[1:], 1, n, c, 2, dgamma)
+    reduce_f32(ab, 1, n, c, 2, dbeta)
+    return dx, dgamma, dbeta
+
+
+def reduce_f32(src, batch, rows, cols, col_stride, out, accumulate=False):
+    check(lib().b200sd_reduce_f32(_p(src), batch, rows, cols, col_stride, _p(out), 1 if accumulate else 0, stream_ptr()),
+          "reduce_f32")
+    return out
+
+
+def colsum(x, n, hw, c, ld_x=None, per_image=False):
+    """Column sums of a bf16 [n*hw, ld] tensor: fp32 [c] (bias gradient) or [n, c] (per-image)."""
+    ld_x = x.stride(0) if ld_x is None else ld_x
+    pb = int(lib().b200sd_rowblocks(n, hw, c))
+    part = torch.empty(n, pb, c, device=x.device, dtype=torch.float32)
+    tok = _pb()
+    check(lib().b200sd_colsum(_p(x), ld_x, n, hw, c, _p(part), stream_ptr()), "colsum")
+    _pe(tok, "colsum", 2.0 * n * hw * c, (n, hw, c))
+    if per_image:
+        return reduce_f32(part, n, pb, c, 1, torch.empty(n, c, device=x.device, dtype=torch.float32))
+    return reduce_f32(part, 1, n * pb, c, 1, torch.empty(c, device=x.device, dtype=torch.float32))
+
+
 def attention(q, k, v, batch, heads, lq, lk, d, scale=None, out=None):
     """q/k/v: 2-D bf16 views [batch*L, >=heads*d] (may be column slices of one fused projection)."""
     for t, nm in ((q, "q"), (k, "k"), (v, "v")):
@@ -382,6 +434,31 @@ def attention(q, k, v, batch, heads, lq, lk, d, scale=None, out=None):
                                   batch, heads, lq, lk, d, float(scale), stream_ptr()), "attention")
     _pe(tok, "attention", 4.0 * batch * heads * lq * lk * d, (batch, heads, lq, lk, d))
     return out
+
+
+def attention_lse(q, k, v, batch, heads, lq, lk, d, scale=None):
+    """Forward for training: -> (out bf16 [batch*lq, heads*d], lse fp32 [batch, heads, lq])."""
+    out = torch.empty(batch * lq, heads * d, device=q.device, dtype=torch.bfloat16)
+    lse = torch.empty(batch, heads, lq, device=q.device, dtype=torch.float32)
+    scale = d ** -0.5 if scale is None else scale
+    tok = _pb()
+    check(lib().b200sd_attention_lse(_p(q), q.stride(0), _p(k), k.stride(0), _p(v), v.stride(0), _p(out), out.stride(0),
+                                      _p(lse), batch, heads, lq, lk, d, float(scale), stream_ptr()), "attention_lse")
+    _pe(tok, "attention", 4.0 * batch * heads * lq * lk * d, (batch, heads, lq, lk, d))
+    return out, lse
+
+
+def attention_bwd(q, k, v, o, d_o, lse, batch, heads, lq, lk, d, dq, dk, dv, scale=None):
+    """dq/dk/dv: preallocated bf16 2-D views (may be column slices of one packed gradient buffer)."""
+    scale = d ** -0.5 if scale is None else scale
+    dvec = torch.empty(batch, heads, lq, device=q.device, dtype=torch.float32)
+    tok = _pb()
+    check(lib().b200sd_attention_bwd(_p(q), q.stride(0), _p(k), k.stride(0), _p(v), v.stride(0), _p(o), o.stride(0),
+                                      _p(d_o), d_o.stride(0), _p(lse), _p(dvec), _p(dq), dq.stride(0), _p(dk),
+                                      dk.stride(0), _p(dv), dv.stride(0), batch, heads, lq, lk, d, float(scale),
+                                      stream_ptr()), "attention_bwd")
+    _pe(tok, "attention_bwd", 10.0 * batch * heads * lq * lk * d, (batch, heads, lq, lk, d))
+    return dq, dk, dv
 
 
 def nchw_to_nhwc(src, dst, c_off=0):

@@ -325,3 +325,75 @@ def test_wgrad_conv(rt, n, h, w, cin, cout, k):
     assert relerr(got, wt.grad) < 2e-3  # bf16 products, fp32 accumulation over n*h*w pixels, fp32 output
     dwp2 = rt.wgrad(srcs, segs, rt.make_src(dyd, n, h, w, cout, ld=ldy), cout, n, h, w)
     assert torch.equal(dwp, dwp2)  # split-K partials are reduced in fixed order
+
+
+# ------------------------------------------------------------------------------------- GroupNorm backward, colsum
+@pytest.mark.parametrize("n,hw,c,groups,act", [(3, 1024, 128, 32, "silu"), (5, 64, 384, 32, "silu"),
+                                               (4, 16, 512, 32, "relu"), (2, 256, 96, 8, None), (16, 1024, 256, 32, "silu")])
+def test_groupnorm_backward(rt, n, hw, c, groups, act):
+    dev = _dev()
+    g = torch.Generator().manual_seed(n + hw + c)
+    x = bf(torch.randn(n, hw, c, generator=g) * 1.5 + 0.3)
+    dy = bf(torch.randn(n, hw, c, generator=g))
+    extra = bf(torch.randn(n, hw, c, generator=g))
+    gamma = (torch.randn(c, generator=g) * 0.5 + 1).requires_grad_()
+    beta = torch.randn(c, generator=g).requires_grad_()
+    xr = x.float().requires_grad_()
+    y = F.group_norm(xr.permute(0, 2, 1), groups, gamma, beta, 1e-5).permute(0, 2, 1)
+    y = {"silu": F.silu, "relu": F.relu, None: lambda t: t}[act](y)
+    y.backward(dy.float())
+    # forward statistics in the layout the igemm epilogue writes: 2 partial slots per image
+    st = torch.zeros(n, 2, c, 2)
+    for i, part in enumerate(x.float().chunk(2, dim=1)):
+        st[:, i, :, 0], st[:, i, :, 1] = part.sum(1), (part ** 2).sum(1)
+    dx, dgamma, dbeta = rt.groupnorm_bwd(x.reshape(n * hw, c).to(dev), dy.reshape(n * hw, c).to(dev), n, hw, c, groups,
+                                         gamma.detach().to(dev), beta.detach().to(dev), [(st.to(dev), 2, c, c)], act=act,
+                                         add=extra.reshape(n * hw, c).to(dev))
+    torch.cuda.synchronize()
+    ref_dx = xr.grad + extra.float()
+    assert relerr(dx.float().cpu().reshape(n, hw, c), ref_dx) < 6e-3   # bf16 output
+    assert relerr(dgamma.cpu(), gamma.grad) < 2e-3
+    assert relerr(dbeta.cpu(), beta.grad) < 2e-3
+
+
+def test_colsum(rt):
+    dev = _dev()
+    g = torch.Generator().manual_seed(2)
+    n, hw, c = 7, 300, 192
+    x = bf(torch.randn(n, hw, c, generator=g))
+    xd = x.reshape(n * hw, c).to(dev)
+    per = rt.colsum(xd, n, hw, c, per_image=True)
+    tot = rt.colsum(xd, n, hw, c)
+    assert torch.allclose(per.cpu(), x.float().sum(1), rtol=1e-4, atol=1e-3)
+    assert torch.allclose(tot.cpu(), x.float().sum((0, 1)), rtol=1e-4, atol=1e-3)
+
+
+# --------------------------------------------------------------------------------------------- attention backward
+@pytest.mark.parametrize("b,heads,lq,lk,d", [(2, 16, 1024, 1024, 24), (2, 16, 1024, 1024, 8), (3, 16, 256, 256, 32),
+                                             (2, 16, 64, 64, 48), (5, 16, 16, 16, 32), (2, 16, 1024, 77, 8),
+                                             (2, 16, 256, 77, 16), (2, 9, 256, 256, 32), (2, 4, 100, 90, 40)])
+def test_attention_backward(rt, b, heads, lq, lk, d):
+    dev = _dev()
+    g = torch.Generator().manual_seed(lq + lk + d)
+    C = heads * d
+    q = bf(torch.randn(b * lq, C, generator=g))
+    kv = bf(torch.randn(b * lk, 2 * C, generator=g))
+    d_o = bf(torch.randn(b * lq, C, generator=g))
+    sh = lambda t, L: t.float().reshape(b, L, heads, d).transpose(1, 2)
+    qr, kr, vr = (t.clone().requires_grad_() for t in (sh(q, lq), sh(kv[:, :C], lk), sh(kv[:, C:], lk)))
+    ref = F.scaled_dot_product_attention(qr, kr, vr)
+    ref.backward(sh(d_o, lq))
+    un = lambda t, L: t.transpose(1, 2).reshape(b * L, C)
+    qd, kvd, dod = q.to(dev), kv.to(dev), d_o.to(dev)
+    out, lse = rt.attention_lse(qd, kvd[:, :C], kvd[:, C:], b, heads, lq, lk, d)
+    assert relerr(out.cpu(), un(ref.detach(), lq)) < 1e-2
+    ref_lse = torch.logsumexp((qr.detach() @ kr.detach().transpose(-1, -2)) * d ** -0.5, -1) * 1.4426950408889634
+    assert torch.allclose(lse.cpu(), ref_lse, atol=2e-3, rtol=1e-4)
+    dq = torch.empty_like(qd)
+    dkv = torch.empty_like(kvd)
+    rt.attention_bwd(qd, kvd[:, :C], kvd[:, C:], out, dod, lse, b, heads, lq, lk, d, dq, dkv[:, :C], dkv[:, C:])
+    torch.cuda.synchronize()
+    # P and dS are rounded to bf16 before the second GEMMs; outputs are bf16
+    assert relerr(dq.cpu(), un(qr.grad, lq)) < 1.5e-2
+    assert relerr(dkv[:, :C].cpu(), un(kr.grad, lk)) < 1.5e-2
+    assert relerr(dkv[:, C:].cpu(), un(vr.grad, lk)) < 1.5e-2
