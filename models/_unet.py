@@ -6,6 +6,7 @@ import torch.nn as nn
 from einops import einsum  # noqa: F401  (kept importable for callers that star-import like the reference)
 
 import sdb200  # noqa: F401
+from sdb200 import autograd as AG
 from sdb200 import engine as E
 from sdb200 import graphs as G
 from sdb200 import runtime as rt
@@ -170,8 +171,11 @@ class UnetCore(nn.Module):
             buf = torch.zeros(n * h * w, ld, device=device, dtype=torch.bfloat16)
             if type(self.cond_conv_in) is not nn.Conv2d:
                 raise rt.B200Error("cond_conv_in: quantised leaf on the mask path is not supported yet")
-            rt.mask_cond(mask.float(), self.cond_conv_in.weight.detach().float().reshape(self.im_cond_output_ch, -1),
-                         buf, c, h, w)
+            if E.training() and self.cond_conv_in.weight.requires_grad:
+                buf = AG.MaskCondFn.apply(self.cond_conv_in.weight, mask, buf, c, h, w)
+            else:
+                rt.mask_cond(mask.float(), self.cond_conv_in.weight.detach().float().reshape(self.im_cond_output_ch, -1),
+                             buf, c, h, w)
             st.inbuf, st.cin = buf, cin
         if self.text_cond:
             assert 'text' in cond_input, \
@@ -253,10 +257,16 @@ class UnetCore(nn.Module):
 
         # ---- time embedding: sinusoid -> t_proj; every block then applies act + its own Linear
         emb = rt.time_embedding(tt, n, self.t_emb_dim, dtype=torch.bfloat16)
-        emb = E.linear(emb, self.t_proj[0], act=E._act_name(self.t_proj[1]))
-        emb = E.linear(emb, self.t_proj[2], out_dtype=torch.float32 if self.class_cond else torch.bfloat16)
-        if self.class_cond:
-            emb = emb + st.class_onehot @ self.class_emb.weight.detach()
+        if E.training():
+            emb = self.t_proj[1](E.linear(emb, self.t_proj[0]))  # (B, t_emb_dim) activation: tiny, on torch
+            emb = E.linear(emb, self.t_proj[2])
+            if self.class_cond:
+                emb = emb.float() + st.class_onehot @ self.class_emb.weight
+        else:
+            emb = E.linear(emb, self.t_proj[0], act=E._act_name(self.t_proj[1]))
+            emb = E.linear(emb, self.t_proj[2], out_dtype=torch.float32 if self.class_cond else torch.bfloat16)
+            if self.class_cond:
+                emb = emb + st.class_onehot @ self.class_emb.weight.detach()
         temb_act = E.activate_temb(emb, self.ACT)
         if E.BATCH_TEMB:
             temb_act = E.TembBank.build(self, temb_act, [tl[1] for blk in list(self.downs) + list(self.mids) +

@@ -15,8 +15,22 @@ import weakref
 import torch
 import torch.nn as nn
 
+from . import autograd as AG
 from . import ops
 from . import runtime as rt
+
+
+def training():
+    """Autograd is recording: leaves run through the autograd.Function wrappers (autograd.py), whose backward is
+    also on the sm_100a kernels. Inference (torch.no_grad) takes the direct path with cached packed weights."""
+    return torch.is_grad_enabled()
+
+
+def _st(stats_t, p_c):
+    """(stats tensor from an autograd Function, or empty) -> Act.stats list."""
+    if stats_t is None or stats_t.numel() == 0:
+        return None
+    return [(stats_t, stats_t.shape[1], stats_t.shape[2], p_c)]
 
 
 FUSE_GN_STATS = True  # producers leave partial GroupNorm statistics for their consumer (tests flip this)
@@ -49,10 +63,15 @@ class Act:
         a = Act(torch.empty(n * h * w, ld, device=x.device, dtype=torch.bfloat16), n, h, w, c)
         if ld != c:
             a.t.zero_()
+        if training() and x.requires_grad:
+            a.t = AG.FromNchwFn.apply(x, ld)
+            return a
         rt.nchw_to_nhwc(x.float(), a.t, 0)
         return a
 
     def to_nchw(self):
+        if training() and self.t.requires_grad:
+            return AG.ToNchwFn.apply(self.t, (self.n, self.c, self.h, self.w))
         return rt.nhwc_to_nchw(self.t, self.n, self.c, self.h, self.w, ld=self.ld)
 
 
@@ -110,6 +129,13 @@ def _new_stats(n, oh, ow, c, device, phases=1):
 
 def group_norm(a, mod, act=None):
     _require_leaf(mod, (nn.GroupNorm,), "GroupNorm")
+    if training():
+        segs = a.stats if (a.stats is not None and len(a.stats) <= 2) else [AG.tensor_stats(a.t, a.n, a.hw, a.c) + (a.c,)]
+        if a.c % 8 or a.ld % 8 or a.c > 2048:
+            raise rt.B200Error("GroupNorm backward needs channels % 8 == 0 and <= 2048")
+        meta = (a.n, a.hw, a.c, mod.num_groups, mod.eps, act, [sg[1:] for sg in segs])
+        out = AG.GroupNormFn.apply(a.t, mod.weight, mod.bias, segs[0][0], segs[1][0] if len(segs) > 1 else None, meta)
+        return Act(out, a.n, a.h, a.w, a.c)
     out = Act.empty(a.n, a.h, a.w, a.c, a.t.device)
     if a.stats is not None and len(a.stats) <= 2 and a.c % 8 == 0 and a.ld % 8 == 0 and a.c <= 2048:
         rt.groupnorm_apply(a.t, a.n, a.hw, a.c, mod.num_groups, _f32(mod.weight), _f32(mod.bias), a.stats, mod.eps,
@@ -130,6 +156,21 @@ def conv2d(a, mod, rowbias=None, extra=None, act=None, out=None, c_off=0, out_dt
     if mod.groups != 1 or mod.dilation != (1, 1):
         raise rt.B200Error("Conv2d: groups/dilation are not supported")
     cout = mod.out_channels
+    if training() and out is None:
+        if k in ((3, 3), (1, 1)) and s == (1, 1) and p == (k[0] // 2, k[0] // 2) and act is None:
+            x2 = w2 = b2 = None
+            cin2 = 0
+            if extra is not None:
+                xa, xm = extra
+                _require_leaf(xm, (nn.Conv2d,), "Conv2d(shortcut)")
+                x2, w2, b2, cin2 = xa.t, xm.weight, xm.bias, xa.c
+            o, st = AG.ConvSameFn.apply(a.t, mod.weight, mod.bias, rowbias, x2, w2, b2, (a.n, a.h, a.w, a.c, cin2), stats,
+                                        out_dtype == torch.float32)
+            return Act(o, a.n, a.h, a.w, cout, _st(st, cout))
+        if k == (4, 4) and s == (2, 2) and p == (1, 1) and extra is None and rowbias is None:
+            o, st = AG.ConvDownFn.apply(a.t, mod.weight, mod.bias, (a.n, a.h, a.w, a.c), stats)
+            return Act(o, a.n, a.h // 2, a.w // 2, cout, _st(st, cout))
+        raise rt.B200Error(f"Conv2d: kernel {k} stride {s} padding {p} has no training path")
     if k in ((3, 3), (1, 1)) and s == (1, 1) and p == (k[0] // 2, k[0] // 2):
         if extra is None:
             wmat = CACHE.get(mod, "w", (mod.weight,), lambda: ops.pack_conv_weight(mod.weight))
@@ -173,8 +214,15 @@ def conv_transpose2d(a, mod, out=None, c_off=0):
     _require_leaf(mod, (nn.ConvTranspose2d,), "ConvTranspose2d")
     if mod.kernel_size != (4, 4) or mod.stride != (2, 2) or mod.padding != (1, 1) or mod.output_padding != (0, 0):
         raise rt.B200Error("ConvTranspose2d: only kernel 4 stride 2 padding 1 has a CUDA path")
-    phases = CACHE.get(mod, "w", (mod.weight,), lambda: ops.pack_convT_weight(mod.weight))
     cout = mod.out_channels
+    if training():
+        if out is not None:
+            raise rt.B200Error("conv_transpose2d: in-place concat target is an inference-only optimisation")
+        o, st = AG.ConvUpFn.apply(a.t, mod.weight, mod.bias, (a.n, a.h, a.w, a.c), True)
+        segs = _st(st, cout)
+        act_o = Act(o, a.n, 2 * a.h, 2 * a.w, cout, segs)
+        return act_o, (None if segs is None else segs[0])
+    phases = CACHE.get(mod, "w", (mod.weight,), lambda: ops.pack_convT_weight(mod.weight))
     o = Act.empty(a.n, 2 * a.h, 2 * a.w, cout, a.t.device) if out is None else out
     st = _new_stats(a.n, a.h, a.w, cout, a.t.device, phases=4)
     ops.conv_up4x4(a.t, a.n, a.h, a.w, a.c, phases, cout, bias=_f32(mod.bias), ld_x=a.ld, out=o.t, c_off=c_off,
@@ -190,9 +238,30 @@ def linear(x, mod, act=None, residual=None, out_dtype=torch.bfloat16, rows_per_i
     if hasattr(mod, "forward_rows") and residual is None and gate is None and rowbias is None:
         return mod.forward_rows(x, act=act)
     _require_leaf(mod, (nn.Linear, nn.modules.linear.NonDynamicallyQuantizableLinear), "Linear")
+    if training() and act is None and gate is None and rowbias is None and out_dtype == torch.bfloat16:
+        o, st = AG.LinearFn.apply(x, mod.weight, mod.bias, residual, rows_per_img, stats is not None)
+        return (o, st) if stats is not None else o
+    if training():
+        raise rt.B200Error("Linear: this epilogue combination has no training path")
     wmat = CACHE.get(mod, "w", (mod.weight,), lambda: ops.pack_linear_weight(mod.weight))
     return rt.linear(x, wmat, bias=_f32(mod.bias), act=act, residual=residual, out_dtype=out_dtype,
                      rows_per_img=rows_per_img, rowbias=rowbias, gate=gate, stats=stats)
+
+
+def _mha_params(mha):
+    """(in_proj weight [3C, C], bias [3C] or None) as differentiable tensors (packed parameter of nn.MultiheadAttention, or
+    the concatenation of CustomMultiheadAttention's q/k/v Linear parameters)."""
+    if isinstance(mha, nn.MultiheadAttention):
+        if mha.in_proj_weight is None:
+            raise rt.B200Error("MultiheadAttention with kdim/vdim != embed_dim has no CUDA path")
+        return mha.in_proj_weight, mha.in_proj_bias
+    if all(hasattr(mha, k) for k in ("q_proj", "k_proj", "v_proj", "out_proj")):
+        for k in ("q_proj", "k_proj", "v_proj"):
+            _require_leaf(getattr(mha, k), (nn.Linear,), f"attention {k}")
+        w = torch.cat([mha.q_proj.weight, mha.k_proj.weight, mha.v_proj.weight], 0)
+        b = None if mha.q_proj.bias is None else torch.cat([mha.q_proj.bias, mha.k_proj.bias, mha.v_proj.bias], 0)
+        return w, b
+    raise rt.B200Error(f"attention module {type(mha).__name__} has no CUDA path")
 
 
 def _mha_weights(mha):
@@ -235,6 +304,10 @@ def _out_proj(o, mha, a):
     proj = mha.out_proj
     if hasattr(proj, "forward_rows"):
         return add(Act(linear(o, proj), a.n, a.h, a.w, C), a)
+    if training():
+        _require_leaf(proj, (nn.Linear, nn.modules.linear.NonDynamicallyQuantizableLinear), "Linear")
+        out, stt = AG.LinearFn.apply(o, proj.weight, proj.bias, a.t, a.hw, True)
+        return Act(out, a.n, a.h, a.w, C, _st(stt, C))
     st = _new_stats(a.n, 1, a.hw, C, a.t.device)
     out = linear(o, proj, residual=a.t, rows_per_img=a.hw, stats=None if st is None else (st[0], st[1], 0, st[2]))
     return Act(out, a.n, a.h, a.w, C, None if st is None else [st + (C,)])
@@ -245,6 +318,11 @@ def self_attention(a, norm, mha):
     add in its epilogue."""
     C, heads = a.c, mha.num_heads
     xn = group_norm(a, norm)
+    if training():
+        w, b = _mha_params(mha)
+        qkv, _ = AG.LinearFn.apply(xn.t, w, b, None, None, False)
+        o = AG.AttentionFn.apply(None, qkv, (a.n, heads, a.hw, a.hw, C // heads))
+        return _out_proj(o, mha, a)
     pk = _mha_weights(mha)
     qkv = rt.linear(xn.t, pk["qkv"], bias=pk["b_qkv"])
     o = rt.attention(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], a.n, heads, a.hw, a.hw, C // heads)
@@ -282,6 +360,14 @@ def cross_attention(a, norm, mha, ctx_proj_mod, ctx, lk, cache=None):
     `cache`: a persistent Context whose per-site K/V are reused across forwards."""
     C, heads = a.c, mha.num_heads
     xn = group_norm(a, norm)
+    if training():
+        w, b = _mha_params(mha)
+        q, _ = AG.LinearFn.apply(xn.t, w[:C], None if b is None else b[:C], None, None, False)
+        _require_leaf(ctx_proj_mod, (nn.Linear,), "Linear")
+        cp, _ = AG.LinearFn.apply(ctx, ctx_proj_mod.weight, ctx_proj_mod.bias, None, None, False)
+        kv, _ = AG.LinearFn.apply(cp, w[C:], None if b is None else b[C:], None, None, False)
+        o = AG.AttentionFn.apply(q, kv, (a.n, heads, a.hw, lk, C // heads))
+        return _out_proj(o, mha, a)
     pk = _mha_weights(mha)
     q = rt.linear(xn.t, pk["q"], bias=pk["b_q"])
     kv = cache.kv.get(id(mha)) if cache is not None else None
@@ -307,6 +393,16 @@ class TembBank:
         mods = [m for m in linears if type(m) is nn.Linear and m.out_features % 8 == 0]
         if len(mods) < 2:
             return TembBank(temb_act, {})
+        if training():
+            w = torch.cat([m.weight for m in mods], 0)
+            b = torch.cat([m.bias if m.bias is not None else torch.zeros(m.out_features, device=m.weight.device)
+                           for m in mods], 0)
+            big, _ = AG.LinearFn.apply(temb_act, w, b, None, None, False)
+            slices, off = {}, 0
+            for m in mods:
+                slices[id(m)] = big[:, off:off + m.out_features]
+                off += m.out_features
+            return TembBank(temb_act, slices)
         params = tuple(m.weight for m in mods) + tuple(m.bias for m in mods)
 
         def pack():
@@ -349,6 +445,8 @@ def resnet(a, first, temb_layer, second, shortcut, temb_act):
 
 
 def add(a, b):
+    if training():
+        return Act(a.t[:, :a.c] + b.t[:, :b.c], a.n, a.h, a.w, a.c)
     out = Act.empty(a.n, a.h, a.w, a.c, a.t.device)
     rt.add_bf16(a.t, b.t, out.t)
     return out
@@ -356,6 +454,9 @@ def add(a, b):
 
 def activate_temb(t_emb, act_cls):
     """act(t_emb) as bf16 [B, D]: the shared first half of every block's t_emb_layers (blocks.py:57-62)."""
+    if training() and t_emb.requires_grad:
+        fn = {"silu": torch.nn.functional.silu, "relu": torch.relu, None: lambda v: v}[_act_name(act_cls())]
+        return fn(t_emb.to(torch.bfloat16))  # (B, t_emb_dim): tiny
     src = t_emb if t_emb.dtype == torch.bfloat16 else rt.cast_bf16(t_emb.float())
     out = torch.empty_like(src)
     rt.copy_act(src, out, 0, act=_act_name(act_cls()))
@@ -382,6 +483,15 @@ def upsample_concat(a, up_conv, skip):
     c_tot = c_up + (skip.c if skip is not None else 0)
     if skip is not None and (skip.h, skip.w, skip.n) != (h, w, a.n):
         raise rt.B200Error("skip tensor shape does not match the upsampled tensor")
+    if training():
+        up = conv_transpose2d(a, up_conv)[0] if up_conv is not None else a
+        if skip is None:
+            return up
+        out = Act(torch.cat([up.t[:, :up.c], skip.t[:, :skip.c]], dim=1), a.n, h, w, c_tot)
+        segs = [x.stats[0] if x.stats is not None and len(x.stats) == 1 else None for x in (up, skip)]
+        if all(sg is not None for sg in segs):
+            out.stats = segs
+        return out
     out = Act.empty(a.n, h, w, c_tot, a.t.device)
     if up_conv is not None:
         _, st_up = conv_transpose2d(a, up_conv, out=out, c_off=0)
