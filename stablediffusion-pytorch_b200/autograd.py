@@ -38,6 +38,13 @@ def _rows(t, c):
     return t
 
 
+def _grad_buf(x, c):
+    """Gradient buffer for an activation whose row matrix may carry padding columns beyond its c channels."""
+    if x.shape[1] == c:
+        return torch.empty(x.shape[0], _pad8(c), device=x.device, dtype=torch.bfloat16)
+    return torch.zeros(x.shape[0], x.shape[1], device=x.device, dtype=torch.bfloat16)
+
+
 def _stats_arg(st):
     return None if st is None else (st[0], st[1], 0, st[2])
 
@@ -132,12 +139,16 @@ class ConvSameFn(Function):
         if ctx.needs_input_grad[0]:
             # dgrad of a stride-1 'same' conv = the same conv with taps flipped and in/out channels swapped
             wd = ops.pack_conv_weight(weight.detach().flip(2, 3).transpose(0, 1))
-            dx = torch.empty(P, _pad8(cin), device=x.device, dtype=torch.bfloat16)[:, :cin]
+            full = _grad_buf(x, cin)
+            dx = full[:, :cin]
             ops.conv_same(dy, n, h, w, cout, wd, cin, k, ld_x=dy.stride(0), out=dx)
+            dx = full if full.shape[1] == x.shape[1] else dx
         if x2 is not None and ctx.needs_input_grad[4]:
             wt = ops.pack_linear_weight(w2.detach().reshape(cout, cin2).t())
-            dx2 = torch.empty(P, _pad8(cin2), device=x.device, dtype=torch.bfloat16)[:, :cin2]
+            full = _grad_buf(x2, cin2)
+            dx2 = full[:, :cin2]
             rt.linear(dy, wt, out=dx2)
+            dx2 = full if full.shape[1] == x2.shape[1] else dx2
         if ctx.needs_input_grad[1] or (w2 is not None and ctx.needs_input_grad[5]):
             pad, cp = k // 2, ops._pad64(cin)
             srcs = [rt.make_src(x, n, h, w, cin, ld=x.stride(0))]

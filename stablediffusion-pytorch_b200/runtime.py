@@ -412,6 +412,10 @@ def reduce_f32(src, batch, rows, cols, col_stride, out, accumulate=False):
 def colsum(x, n, hw, c, ld_x=None, per_image=False):
     """Column sums of a bf16 [n*hw, ld] tensor: fp32 [c] (bias gradient) or [n, c] (per-image)."""
     ld_x = x.stride(0) if ld_x is None else ld_x
+    if c > 2048:  # wide matrices (packed QKV, the batched time-embedding bank): column slabs of 2048
+        parts = [colsum(x[:, j:min(j + 2048, c)], n, hw, min(2048, c - j), ld_x=ld_x, per_image=per_image)
+                 for j in range(0, c, 2048)]
+        return torch.cat(parts, dim=-1)
     pb = int(lib().b200sd_rowblocks(n, hw, c))
     part = torch.empty(n, pb, c, device=x.device, dtype=torch.float32)
     tok = _pb()
