@@ -384,10 +384,88 @@ def run_ours(args):
             "value": ips, "unit": "images/s", "cores": r["cores"], "kind": "port",
             "sample": f"{r['steps_done']} DDPM timesteps on {r['sample_batch']} of the {B} images + VQVAE decode of 1 "
                       f"image, fp32 oracle port on {r['cores']} host threads, extrapolated to 1000 steps per image"}
+    if args.train_steps > 0:
+        del pipe, P, model, vae
+        torch.cuda.empty_cache()
+        line["train"] = train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks)
     if rank == 0:
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks):
+    """BASELINE.json configs[2]: data-parallel training of the same conditioned UNet as
+    train_ddpm_cond_celebhq_multi_gpu.py:341-378 does it — add_noise, bf16-autocast forward, MSE, backward (DDP's
+    bucketed NCCL all-reduce overlapped with it when world > 1), clip_grad_norm_(1.0), Adam, EMA — per-GPU batch 16
+    (config/celebhq_text_image_cond.py:76). Forward and backward of every heavy op run on libb200sd.so.
+    value: inputs resident on the device. e2e: latents / text / mask copied from pinned host memory every step and
+    loss.item() read back every step, as the reference loop does (:327-354)."""
+    import copy
+    import torch.distributed as dist
+    from sdb200 import runtime as rt
+    from models.unet_cond_base import Unet
+    from scheduler.linear_noise_scheduler import LinearNoiseScheduler
+    B, K, W = args.train_batch, args.train_steps, 3
+    torch.manual_seed(SEED)
+    model = Unet(4, ucfg).train().to(dev)
+    ema = copy.deepcopy(model).eval()
+    net = model
+    if world > 1:
+        net = torch.nn.parallel.DistributedDataParallel(model, device_ids=[dev.index], broadcast_buffers=False)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-5)
+    sched = LinearNoiseScheduler(T_STEPS, 0.00085, 0.012)
+    x_h, text_h, mask_h = synth_inputs(B, ucfg, rank)
+    g = torch.Generator().manual_seed(SEED + 5 + rank)
+    noise_h = torch.randn(x_h.shape, generator=g).pin_memory()
+    t_h = torch.randint(0, T_STEPS, (B,), generator=g).pin_memory()
+    res = {"x": x_h.to(dev), "text": text_h.to(dev), "mask": mask_h.to(dev), "noise": noise_h.to(dev), "t": t_h.to(dev)}
+
+    def step(from_host):
+        if from_host:
+            x0, text, mask = (v.to(dev, non_blocking=True) for v in (x_h, text_h, mask_h))
+            noise, t = noise_h.to(dev, non_blocking=True), t_h.to(dev, non_blocking=True)
+        else:
+            x0, text, mask, noise, t = res["x"], res["text"], res["mask"], res["noise"], res["t"]
+        noisy = sched.add_noise(x0, noise, t)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            pred = net(noisy, t, {"text": text, "image": mask})
+            loss = torch.nn.functional.mse_loss(pred, noise)
+        opt.zero_grad(set_to_none=True)
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+        opt.step()
+        with torch.no_grad():
+            torch._foreach_mul_(list(ema.parameters()), 0.999)
+            torch._foreach_add_(list(ema.parameters()), list(model.parameters()), alpha=0.001)
+        return loss.item() if from_host else loss
+
+    out = {}
+    for name, from_host in (("value", False), ("e2e", True)):
+        for _ in range(W):
+            step(from_host)
+        l0 = rt.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for _ in range(K):
+            last = step(from_host)
+        e1.record()
+        barrier()
+        (ms,) = max_over_ranks([e0.elapsed_time(e1)])
+        out[name] = (world * B * K / (ms / 1e3), ms / K, rt.launch_count() - l0, float(last))
+    h2d = (x_h.numel() + text_h.numel() + mask_h.numel() + noise_h.numel()) * 4 + t_h.numel() * 8
+    del net, model, ema, opt
+    return {
+        "metric": "ddp_train_samples_per_s", "value": out["value"][0], "unit": "samples/s", "ms_per_step": out["value"][1],
+        "steps": K, "warmup": W, "batch_per_gpu": B, "global_batch": B * world, "dtype": "bf16",
+        "algorithmic_tflops": 3 * UNET_GFLOP * 1e9 * B / (out["value"][1] / 1e3) / 1e12,
+        "optimizer": "Adam + clip_grad_norm_(1.0) + EMA (torch foreach)", "gpu_launches": out["value"][2],
+        "grad_allreduce": "torch DistributedDataParallel, 25 MB NCCL buckets overlapped with backward" if world > 1 else None,
+        "loss_finite": bool(out["value"][3] == out["value"][3]),
+        "e2e": {"value": out["e2e"][0], "unit": "samples/s", "ms_per_step": out["e2e"][1], "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": 4},
+    }
 
 
 def main():
@@ -402,6 +480,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-budget", type=float, default=90.0, help="seconds the CPU legs may spend")
     ap.add_argument("--e2e-steps", type=int, default=0, help="cap on the e2e leg's timesteps (0 = same as --steps)")
+    ap.add_argument("--train-steps", type=int, default=20, help="timed steps of the training leg (0 = skip it)")
+    ap.add_argument("--train-batch", type=int, default=16, help="per-GPU training batch (reference: 16)")
     ap.add_argument("--dump", default="", help="write the per-launch kernel timing of one eager step to this JSON file")
     args = ap.parse_args()
     if args.impl == "reference":

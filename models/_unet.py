@@ -215,10 +215,33 @@ class UnetCore(nn.Module):
                                "the reference itself is the CPU path)")
         if self.cond:
             assert cond_input is not None, "Model initialized with conditioning so cond_input cannot be None"
-        st = self._cached_cond(cond_input, x) if self.cond else E.CondState()
         tt = torch.as_tensor(t).to(device=x.device, dtype=torch.int64).reshape(-1)
         if tt.numel() not in (1, x.shape[0]):
             raise RuntimeError(f"t has {tt.numel()} entries for batch size {x.shape[0]}")
+        if torch.is_grad_enabled() and G.ENABLE_TRAIN_GRAPHS and not torch.cuda.is_current_stream_capturing() \
+                and not self.class_cond and not isinstance(cond_input, E.CondState):
+            return self._forward_train_graphed(x, tt, cond_input)
+        with torch.autocast("cuda", enabled=False):
+            return self._forward_eager(x, tt, cond_input)
+
+    def _forward_train_graphed(self, x, tt, cond_input):
+        cond_t = []
+        if self.text_cond:
+            assert 'text' in cond_input, \
+                "Model initialized with text conditioning but cond_input has no text information"
+            cond_t.append(cond_input['text'].float().contiguous())
+        if self.image_cond:
+            validate_image_conditional_input(cond_input, x)
+            cond_t.append(cond_input['image'].float().contiguous())
+        x = x.float().contiguous()
+        tg = self.__dict__.get("_train_graph")
+        if tg is None or tg.key != G.TrainGraph.make_key(self, x, tt, cond_t):
+            tg = G.TrainGraph(self, x, tt, cond_t, self.text_cond, self.image_cond)
+            self.__dict__["_train_graph"] = tg
+        return tg(x, tt, cond_t)
+
+    def _forward_eager(self, x, tt, cond_input):
+        st = self._cached_cond(cond_input, x) if self.cond else E.CondState()
         if G.ENABLE_FORWARD_GRAPHS and not torch.is_grad_enabled() and not torch.cuda.is_current_stream_capturing():
             graphs = self.__dict__.setdefault("_graphed", {})
             key = (tuple(x.shape), tt.numel(), id(st))
@@ -234,6 +257,7 @@ class UnetCore(nn.Module):
         """Drop captured graphs / hoisted conditioning (call after swapping sub-modules in place)."""
         self.__dict__.pop("_graphed", None)
         self.__dict__.pop("_cond_cache", None)
+        self.__dict__.pop("_train_graph", None)
 
     def train(self, mode=True):
         self.invalidate_plan()

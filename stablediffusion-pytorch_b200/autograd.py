@@ -167,7 +167,7 @@ class ConvSameFn(Function):
                 per = dy.float().reshape(n, h * w, cout).sum(1)
             tot = per.sum(0) if (has_b or has_b2) else None
             db = tot if has_b else None
-            db2 = tot if has_b2 else None
+            db2 = (tot.clone() if has_b else tot) if has_b2 else None   # never hand one buffer to two parameters
             drb = per.to(torch.bfloat16) if has_rb else None
         return dx, dw, db, drb, dx2, dw2, db2, None, None, None
 

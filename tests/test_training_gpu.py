@@ -122,3 +122,27 @@ def test_training_step_reduces_loss_and_is_deterministic():
     a, b = run(), run()
     assert a == b, "training is not bit-reproducible"
     assert a[-1] < a[0]
+
+
+@pytest.mark.parametrize("graphs", [True, False])
+def test_parameter_gradients_do_not_share_memory(graphs):
+    """In-place consumers of .grad (clip_grad_norm_, DDP buckets) race when two parameters are handed one buffer —
+    the fused conv + 1x1 shortcut once returned its shared bias column sum to both biases."""
+    dev = _dev()
+    from models.unet_cond_base import Unet
+    from sdb200 import graphs as G
+    fx = load_golden("unet_small_cond")
+    inp, cfg = fx["inputs"], fx["config"]
+    old = G.ENABLE_TRAIN_GRAPHS
+    G.ENABLE_TRAIN_GRAPHS = graphs
+    try:
+        torch.manual_seed(0)
+        model = Unet(4, cfg).train().to(dev)
+        x, t = inp["x"].to(dev), inp["t"].to(dev)
+        model(x, t, cond_of(inp, cfg, dev)).square().mean().backward()
+    finally:
+        G.ENABLE_TRAIN_GRAPHS = old
+    spans = sorted((p.grad.untyped_storage().data_ptr() + p.grad.storage_offset() * p.grad.element_size(),
+                    p.grad.numel() * p.grad.element_size(), n) for n, p in model.named_parameters())
+    for (a, la, na), (b, _, nb) in zip(spans, spans[1:]):
+        assert a + la <= b, f"{na} and {nb} gradients overlap"
