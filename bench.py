@@ -412,7 +412,11 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks):
     ema = copy.deepcopy(model).eval()
     net = model
     if world > 1:
-        net = torch.nn.parallel.DistributedDataParallel(model, device_ids=[dev.index], broadcast_buffers=False)
+        if args.train_ddp == "torch":
+            net = torch.nn.parallel.DistributedDataParallel(model, device_ids=[dev.index], broadcast_buffers=False)
+        else:
+            from sdb200.parallel import DataParallel
+            net = DataParallel(model, device_ids=[dev.index], broadcast_buffers=False)
     opt = torch.optim.Adam(model.parameters(), lr=1e-5)
     sched = LinearNoiseScheduler(T_STEPS, 0.00085, 0.012)
     x_h, text_h, mask_h = synth_inputs(B, ucfg, rank)
@@ -438,7 +442,7 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks):
         with torch.no_grad():
             torch._foreach_mul_(list(ema.parameters()), 0.999)
             torch._foreach_add_(list(ema.parameters()), list(model.parameters()), alpha=0.001)
-        return loss.item() if from_host else loss
+        return loss.item() if from_host else loss.detach()
 
     out = {}
     for name, from_host in (("value", False), ("e2e", True)):
@@ -461,7 +465,11 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks):
         "steps": K, "warmup": W, "batch_per_gpu": B, "global_batch": B * world, "dtype": "bf16",
         "algorithmic_tflops": 3 * UNET_GFLOP * 1e9 * B / (out["value"][1] / 1e3) / 1e12,
         "optimizer": "Adam + clip_grad_norm_(1.0) + EMA (torch foreach)", "gpu_launches": out["value"][2],
-        "grad_allreduce": "torch DistributedDataParallel, 25 MB NCCL buckets overlapped with backward" if world > 1 else None,
+        "grad_allreduce": None if world == 1 else (
+            "torch DistributedDataParallel: 25 MB NCCL buckets, reduced after the backward graph has replayed"
+            if args.train_ddp == "torch" else
+            "sdb200.parallel.DataParallel: one in-place NCCL AVG all-reduce of the flat fp32 gradient buffer "
+            "(474 MB) after the backward graph"),
         "loss_finite": bool(out["value"][3] == out["value"][3]),
         "e2e": {"value": out["e2e"][0], "unit": "samples/s", "ms_per_step": out["e2e"][1], "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 4},
@@ -482,6 +490,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=0, help="cap on the e2e leg's timesteps (0 = same as --steps)")
     ap.add_argument("--train-steps", type=int, default=20, help="timed steps of the training leg (0 = skip it)")
     ap.add_argument("--train-batch", type=int, default=16, help="per-GPU training batch (reference: 16)")
+    ap.add_argument("--train-ddp", choices=["ours", "torch"], default="ours",
+                    help="N>1 gradient mean: sdb200.parallel.DataParallel (flat buffer) or torch DistributedDataParallel")
     ap.add_argument("--dump", default="", help="write the per-launch kernel timing of one eager step to this JSON file")
     args = ap.parse_args()
     if args.impl == "reference":

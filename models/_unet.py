@@ -219,7 +219,8 @@ class UnetCore(nn.Module):
         if tt.numel() not in (1, x.shape[0]):
             raise RuntimeError(f"t has {tt.numel()} entries for batch size {x.shape[0]}")
         if torch.is_grad_enabled() and G.ENABLE_TRAIN_GRAPHS and not torch.cuda.is_current_stream_capturing() \
-                and not self.class_cond and not isinstance(cond_input, E.CondState):
+                and not self.class_cond and not isinstance(cond_input, E.CondState) \
+                and (x.requires_grad or any(p.requires_grad for p in self.parameters())):
             return self._forward_train_graphed(x, tt, cond_input)
         with torch.autocast("cuda", enabled=False):
             return self._forward_eager(x, tt, cond_input)
@@ -238,6 +239,7 @@ class UnetCore(nn.Module):
         if tg is None or tg.key != G.TrainGraph.make_key(self, x, tt, cond_t):
             tg = G.TrainGraph(self, x, tt, cond_t, self.text_cond, self.image_cond)
             self.__dict__["_train_graph"] = tg
+        tg.grad_sync = self.__dict__.get("_grad_sync")   # set by sdb200.parallel.DataParallel
         return tg(x, tt, cond_t)
 
     def _forward_eager(self, x, tt, cond_input):

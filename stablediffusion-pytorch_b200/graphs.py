@@ -149,50 +149,134 @@ class SamplingPipeline:
         return P.xt.clone(), P.x0.clone(), ims
 
 
-class _TensorArgs(torch.nn.Module):
-    """Tensor-only calling convention over Unet.run for torch.cuda.make_graphed_callables (which needs an nn.Module
-    whose parameters it can differentiate and whose arguments are all tensors). The wrapped model is kept out of
-    this module's registered children on purpose (it is reached through a plain attribute)."""
+class _ParamSwap:
+    """Temporarily binds every `module._parameters[name]` slot of a model to a stand-in tensor (same storage, fresh
+    autograd leaf). Capture differentiates the stand-ins, never the real Parameters: their AccumulateGrad nodes (which
+    DistributedDataParallel keeps alive, tied to the stream it was built on) stay out of the captured region."""
 
-    def __init__(self, core, has_text, has_mask):
-        super().__init__()
-        object.__setattr__(self, "_core", core)
-        self.has_text, self.has_mask = has_text, has_mask
-        # same Parameter objects, registered here so make_graphed_callables sees them
-        for i, p in enumerate(core.parameters()):
-            self.register_parameter(f"p{i}", p)
+    def __init__(self, core, params):
+        index = {id(p): i for i, p in enumerate(params)}
+        self.slots = [(m, k, index[id(p)]) for m in core.modules() for k, p in m._parameters.items() if p is not None]
+        self.standins = [p.detach().requires_grad_(p.requires_grad) for p in params]
 
-    def forward(self, x, tt, *cond):
-        core = self._core
-        ci = {}
-        k = 0
-        if self.has_text:
-            ci["text"] = cond[k]
-            k += 1
-        if self.has_mask:
-            ci["image"] = cond[k]
-        st = core.prepare_cond(ci, x.shape, x.device) if core.cond else E.CondState()
-        return core.run(x, tt, st).to_nchw()
+    def __enter__(self):
+        self.saved = [m._parameters[k] for m, k, _ in self.slots]
+        for m, k, i in self.slots:
+            m._parameters[k] = self.standins[i]
+
+    def __exit__(self, *exc):
+        for (m, k, _), p in zip(self.slots, self.saved):
+            m._parameters[k] = p
+
+
+class _ReplayFn(torch.autograd.Function):
+    """forward = replay of the captured forward graph; backward = replay of the captured backward graph. Parameters are
+    arguments only so that autograd routes the gradients to them (the graphs read the parameter storage in place)."""
+
+    @staticmethod
+    def forward(ctx, tg, x, *params):
+        ctx.tg = tg
+        tg.x.copy_(x)
+        tg.fwd_graph.replay()
+        rt.count_external(tg.fwd_launches)
+        return tg.out.detach().clone()
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g):
+        tg = ctx.tg
+        tg.gout.copy_(g)
+        tg.bwd_graph.replay()
+        rt.count_external(tg.bwd_launches)
+        return (None, tg.dx.clone() if tg.dx is not None else None) + tg.take_grads()
 
 
 class TrainGraph:
-    """One training step's forward and backward as two CUDA graphs (torch.cuda.make_graphed_callables over the
-    model's kernel sequence): ~1200 kernel launches + ~1000 small torch ops per step cost ~55 ms of host time when
-    issued one by one, several times the device time at the reference's per-GPU batch of 16. Parameters are read in
-    place on every replay (weight packing is inside the graph), so optimizer steps need no re-capture. Parameter
-    gradients surface when the backward graph finishes; DistributedDataParallel's hooks fire then."""
+    """One training step's forward and backward as two CUDA graphs: ~1200 kernel launches + ~1000 small torch ops per
+    step cost ~55 ms of host time when issued one by one, several times the device time at the reference's per-GPU
+    batch of 16 (train_ddpm_cond_celebhq_multi_gpu.py:341-362). Parameters are read in place on every replay (weight
+    packing is inside the graph), so optimizer steps need no re-capture.
+
+    The backward graph ends by gathering every parameter gradient into ONE flat fp32 buffer (`flat`, 256-byte aligned
+    slots in parameter order). Each backward hands out views of a fresh copy of it, so `.grad` accumulation,
+    in-place clipping and DistributedDataParallel's bucket copies see ordinary tensors; `grad_sync`, when set, is called
+    with that flat copy before the views are handed out (one collective for the whole model, see parallel.py)."""
+
+    WARMUP = 2
 
     def __init__(self, core, x, tt, cond_tensors, has_text, has_mask):
         self.params = list(core.parameters())
         self.key = self.make_key(core, x, tt, cond_tensors)
-        mod = _TensorArgs(core, has_text, has_mask)
-        sample = (x.detach().clone().requires_grad_(x.requires_grad), tt.clone()) + tuple(
-            c.detach().clone() for c in cond_tensors)
-        before = rt.launch_count()
-        with torch.autocast("cuda", enabled=False):
-            self.fn = torch.cuda.make_graphed_callables(mod, sample, allow_unused_input=True)
-        # make_graphed_callables runs 3 warm-up forward+backward passes and captures one more
-        self.launches = (rt.launch_count() - before) // 4
+        self.grad_sync = None
+        dev = x.device
+        swap = _ParamSwap(core, self.params)
+        self.x = x.detach().clone().requires_grad_(x.requires_grad)
+        self.tt = tt.clone()
+        self.cond = [c.detach().clone() for c in cond_tensors]
+        wrt = [t for t in [self.x] + swap.standins if t.requires_grad]
+        if not wrt:
+            raise rt.B200Error("training graph requested but nothing requires grad")
+
+        def forward():
+            ci, k = {}, 0
+            if has_text:
+                ci["text"], k = self.cond[k], k + 1
+            if has_mask:
+                ci["image"] = self.cond[k]
+            with swap:
+                st = core.prepare_cond(ci, self.x.shape, dev) if core.cond else E.CondState()
+                return core.run(self.x, self.tt, st).to_nchw()
+
+        # slots of the flat gradient buffer
+        self.slots, off = [], 0
+        for p in self.params:
+            self.slots.append((off, p.numel(), tuple(p.shape)) if p.requires_grad else None)
+            if p.requires_grad:
+                off += (p.numel() + 63) // 64 * 64
+        self.flat = torch.zeros(max(off, 64), device=dev, dtype=torch.float32)
+
+        with torch.autocast("cuda", enabled=False), torch.enable_grad():
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(self.WARMUP):  # lazy kernel attributes, allocator warm-up
+                    out = forward()
+                    torch.autograd.grad((out,), wrt, (torch.ones_like(out),), allow_unused=True)
+                del out
+            torch.cuda.current_stream().wait_stream(side)
+            pool = torch.cuda.graph_pool_handle()
+            self.fwd_graph, self.bwd_graph = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+            before = rt.launch_count()
+            with torch.cuda.graph(self.fwd_graph, pool=pool):
+                self.out = forward()
+            self.fwd_launches = rt.launch_count() - before
+            self.gout = torch.empty_like(self.out)
+            before = rt.launch_count()
+            with torch.cuda.graph(self.bwd_graph, pool=pool):
+                grads = list(torch.autograd.grad((self.out,), wrt, (self.gout,), allow_unused=True))
+                self.dx = grads.pop(0) if self.x.requires_grad else None
+                views, srcs, self.unused = [], [], set()
+                it = iter(grads)
+                for i, sl in enumerate(self.slots):
+                    if sl is None:
+                        continue
+                    g = next(it)
+                    if g is None:
+                        self.unused.add(i)
+                        continue
+                    views.append(self.flat[sl[0]:sl[0] + sl[1]].view(sl[2]))
+                    srcs.append(g if g.dtype == torch.float32 else g.float())
+                if views:
+                    torch._foreach_copy_(views, srcs)
+            self.bwd_launches = rt.launch_count() - before
+        self.launches = self.fwd_launches + self.bwd_launches
+
+    def take_grads(self):
+        flat = self.flat.clone()
+        if self.grad_sync is not None:
+            self.grad_sync(flat)
+        return tuple(None if sl is None or i in self.unused else flat[sl[0]:sl[0] + sl[1]].view(sl[2])
+                     for i, sl in enumerate(self.slots))
 
     @staticmethod
     def make_key(core, x, tt, cond_tensors):
@@ -200,5 +284,7 @@ class TrainGraph:
             + tuple((p.data_ptr(), p.requires_grad) for p in core.parameters())
 
     def __call__(self, x, tt, cond_tensors):
-        rt.count_external(self.launches)   # library kernels replayed by the forward graph and, later, the backward graph
-        return self.fn(x, tt, *cond_tensors)
+        self.tt.copy_(tt)
+        for s, c in zip(self.cond, cond_tensors):
+            s.copy_(c)
+        return _ReplayFn.apply(self, x, *self.params)

@@ -1,0 +1,83 @@
+"""Host-side logic of the N>1 training path on CPU: two gloo ranks (SURVEY.md §8 row e / a15). The device path is
+the same code over NCCL."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from sdb200.parallel import DataParallel, _mean_
+        torch.manual_seed(100 + rank)                       # ranks start from different weights
+        net = torch.nn.Sequential(torch.nn.Linear(5, 7), torch.nn.ReLU(), torch.nn.Linear(7, 3))
+        dp = DataParallel(net, bucket_cap_mb=None)
+        w0 = torch.cat([p.detach().flatten() for p in net.parameters()])
+        gathered = [torch.empty_like(w0) for _ in range(world)]
+        dist.all_gather(gathered, w0)
+        same_init = all(torch.equal(g, gathered[0]) for g in gathered)
+
+        # eager path: hooks reduce once the last gradient has landed; two backward passes to check the latch resets
+        ok_grad = True
+        for it in range(2):
+            g = torch.Generator().manual_seed(7 * it + rank)
+            x = torch.randn(4, 5, generator=g)
+            net.zero_grad()
+            dp(x).square().sum().backward()
+            mine = torch.cat([p.grad.flatten() for p in net.parameters()])
+            # the same thing by hand: local gradients of every rank's batch, averaged
+            ref = torch.zeros_like(mine)
+            for r in range(world):
+                xr = torch.randn(4, 5, generator=torch.Generator().manual_seed(7 * it + r))
+                net2 = torch.nn.Sequential(torch.nn.Linear(5, 7), torch.nn.ReLU(), torch.nn.Linear(7, 3))
+                net2.load_state_dict(net.state_dict())
+                net2(xr).square().sum().backward()
+                ref += torch.cat([p.grad.flatten() for p in net2.parameters()]) / world
+            ok_grad &= torch.allclose(mine, ref, rtol=1e-6, atol=1e-7)
+
+        # flat-buffer path (what a captured step calls), bucketed and unbucketed give the same mean
+        flat = torch.arange(1000, dtype=torch.float32) * (rank + 1)
+        a = _mean_(flat.clone(), None, None)
+        b = _mean_(flat.clone(), None, 96)
+        want = torch.arange(1000, dtype=torch.float32) * (sum(range(1, world + 1)) / world)
+        ok_flat = torch.equal(a, b) and torch.allclose(a, want)
+        dp._sync_flat(flat.clone())
+        latch = dp._graph_synced
+        q.put((rank, same_init, bool(ok_grad), bool(ok_flat), latch))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_data_parallel_two_ranks_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29600 + os.getpid() % 300
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    for rank, same_init, ok_grad, ok_flat, latch in res:
+        assert same_init, f"rank {rank}: parameters not broadcast from rank 0"
+        assert ok_grad, f"rank {rank}: eager-path gradients are not the mean over ranks"
+        assert ok_flat, f"rank {rank}: flat-buffer mean wrong"
+        assert latch
+
+
+def test_bench_batch_sharding_is_disjoint():
+    """Sampling shards by batch with no collective: every rank draws its own latents / conditions."""
+    sys.path.insert(0, ROOT)
+    import bench
+    cfg = bench.load_cfg()[0]
+    a = bench.synth_inputs(2, cfg, rank=0, pin=False)
+    b = bench.synth_inputs(2, cfg, rank=1, pin=False)
+    assert a[0].shape == b[0].shape and not torch.equal(a[0], b[0])
