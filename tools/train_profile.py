@@ -20,6 +20,10 @@ from scheduler.linear_noise_scheduler import LinearNoiseScheduler  # noqa: E402
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--batch", type=int, default=16)
+    ap.add_argument("--ncu-steps", type=int, default=0,
+                    help="run N captured steps (forward, backward, clip, Adam), each preceded by an advance_t_kernel "
+                         "marker, and exit: the launch list for `ncu --metrics gpu__time_duration.sum`; "
+                         "tools/summarize_launches.py --step k then cuts out one step")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     ucfg, _ = bench.load_cfg()
@@ -37,6 +41,21 @@ def main():
         model.zero_grad(set_to_none=True)
         loss.backward()
 
+    if a.ncu_steps:
+        opt = torch.optim.Adam(model.parameters(), lr=1e-5)
+        mark = torch.zeros(1, device=dev, dtype=torch.int64)
+        for i in range(a.ncu_steps + 1):
+            rt.advance_t(mark, 1)
+            if i == a.ncu_steps:
+                break
+            step()
+            torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+            opt.step()
+        torch.cuda.synchronize()
+        print("done", a.ncu_steps, "steps")
+        return
+    from sdb200 import graphs as G
+    G.ENABLE_TRAIN_GRAPHS = False   # per-launch events need eager launches
     for _ in range(3):
         step()
     torch.cuda.synchronize()
