@@ -227,6 +227,48 @@ int b200sd_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
 /* out[i] = a[i] + b[i] on contiguous bf16 (residual add when a quantised leaf prevents epilogue fusion). */
 int b200sd_add_bf16(const void* a, const void* b, void* out, int64_t n, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * DiT token-row operators (csrc/rows.cu). Rows are bf16 [rows, ld] with `c` valid channels (c % 8 == 0, c <= 1024,
+ * pitches multiples of 8); rows are grouped into images of `rows_per_img` tokens; per-image operands (shift, scale,
+ * gate) are bf16 [n, ld_m] row vectors, typically column slices of the adaLN projection output.
+ * ------------------------------------------------------------------------------------------------------------- */
+
+/* y = LayerNorm(x, eps, no affine) * (1 + scale[img]) + shift[img]  — models/transformer_layer.py:88-89,103-104 and
+ * models/transformer.py:196-197; shift = scale = NULL gives the un-modulated cross_attn_norm (:94).
+ * stats (optional) receives fp32 (mean, rstd) per row for the backward. */
+int b200sd_layernorm_mod(const void* x, int64_t ld_x, void* y, int64_t ld_y, const void* shift, const void* scale,
+                         int64_t ld_m, int64_t rows, int64_t rows_per_img, int32_t c, float eps, float* stats,
+                         void* stream);
+
+/* Backward of b200sd_layernorm_mod: dx (+ dres, the gradient of a second consumer of x, optional). part (optional,
+ * required when scale != NULL gradients are wanted) = fp32 [n, slots, 2, c] partial sums over
+ * b200sd_rows_per_slot() rows of (dy, dy * xhat) = the gradients of (shift, scale); fold with b200sd_reduce_f32. */
+int b200sd_layernorm_mod_bwd(const void* dy, int64_t ld_dy, const void* x, int64_t ld_x, const float* stats,
+                             const void* scale, int64_t ld_m, const void* dres, int64_t ld_r, void* dx, int64_t ld_dx,
+                             int64_t n, int64_t rows_per_img, int32_t c, float* part, void* stream);
+int b200sd_rows_per_slot(void);
+
+/* y = x + gate[img] * h — the adaLN-Zero gated residual (transformer_layer.py:90,105) as a stand-alone kernel for
+ * training (inference fuses it into b200sd_igemm's epilogue), and its backward: dh = gate * dy,
+ * part = fp32 [n, slots, c] partial sums of dy * h (= d gate); dx = dy needs no kernel. */
+int b200sd_gate_residual(const void* x, int64_t ld_x, const void* h, int64_t ld_h, const void* gate, int64_t ld_g,
+                         void* y, int64_t ld_y, int64_t rows, int64_t rows_per_img, int32_t c, void* stream);
+int b200sd_gate_residual_bwd(const void* dy, int64_t ld_dy, const void* h, int64_t ld_h, const void* gate,
+                             int64_t ld_g, void* dh, int64_t ld_dh, int64_t n, int64_t rows_per_img, int32_t c,
+                             float* part, void* stream);
+
+/* dx = dy where y > 0 (nn.ReLU of the MLP block, transformer_layer.py:34-38; y is the saved forward output). */
+int b200sd_relu_bwd(const void* dy, int64_t ld_dy, const void* y, int64_t ld_y, void* dx, int64_t ld_dx, int64_t rows,
+                    int32_t c, void* stream);
+
+/* tokens [(img, gy, gx)][(py, px, ch)] (bf16, or fp32 when tokens_f32) -> image fp32 NCHW [n, ch, gh*ph, gw*pw]
+ * (einops 'b (nh nw) (ph pw c) -> b c (nh ph) (nw pw)', models/transformer.py:207-211) and its adjoint
+ * (models/patch_embed.py:84-86), which zero-fills token columns beyond ph*pw*ch. */
+int b200sd_unpatchify(const void* tokens, int32_t tokens_f32, int64_t ld, float* image, int64_t n, int32_t channels,
+                      int32_t grid_h, int32_t grid_w, int32_t patch_h, int32_t patch_w, void* stream);
+int b200sd_patchify(const float* image, void* tokens, int64_t ld, int64_t n, int32_t channels, int32_t grid_h,
+                    int32_t grid_w, int32_t patch_h, int32_t patch_w, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

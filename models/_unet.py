@@ -10,6 +10,7 @@ from sdb200 import autograd as AG
 from sdb200 import engine as E
 from sdb200 import graphs as G
 from sdb200 import runtime as rt
+from models._denoiser import Denoiser
 
 
 def get_config_value(config, key, default_value):
@@ -46,7 +47,7 @@ def validate_class_conditional_input(cond_input, x, num_classes):
         "Shape of class condition input must match (Batch Size, )"
 
 
-class UnetCore(nn.Module):
+class UnetCore(Denoiser):
     """conv_in -> DownBlocks (skips pushed before each) -> MidBlocks -> UpBlockUnets (skips popped) ->
     GroupNorm/act/conv_out, with optional text (cross-attention), mask-image (concat) and class (time-embedding
     add) conditioning — reference models/unet_cond_base.py:15-183 and models/unet_base.py:13-100."""
@@ -187,87 +188,6 @@ class UnetCore(nn.Module):
             validate_class_conditional_input(cond_input, torch.empty(x_shape, device='meta'), self.num_classes)
             st.class_onehot = cond_input['class'].float()
         return st
-
-    def _cached_cond(self, cond_input, x):
-        """In inference (no grad) reuse the CondState while the caller keeps passing the same, unmodified condition
-        tensors and the conditioning weights are untouched — which is what every sampling loop does."""
-        if isinstance(cond_input, E.CondState):
-            return cond_input
-        if torch.is_grad_enabled() or not E.HOIST_CONDITIONING:
-            return self.prepare_cond(cond_input, x.shape, x.device)
-        key = (tuple(x.shape),) + tuple((k, v.data_ptr(), v._version, tuple(v.shape))
-                                        for k, v in sorted(cond_input.items()) if isinstance(v, torch.Tensor))
-        key += tuple((p.data_ptr(), p._version) for p in self._cond_params())
-        cache = self.__dict__.setdefault("_cond_cache", {})
-        st = cache.get(key)
-        if st is None:
-            st = self.prepare_cond(cond_input, x.shape, x.device)
-            if st.ctx is not None:
-                st.ctx.persistent = True
-            if len(cache) >= 4:  # conditional + unconditional (CFG) and a little slack
-                cache.pop(next(iter(cache)))
-            cache[key] = st
-        return st
-
-    def forward(self, x, t, cond_input=None):
-        if not x.is_cuda:
-            raise rt.B200Error("Unet.forward: CUDA tensors required (this package has no CPU implementation; "
-                               "the reference itself is the CPU path)")
-        if self.cond:
-            assert cond_input is not None, "Model initialized with conditioning so cond_input cannot be None"
-        tt = torch.as_tensor(t).to(device=x.device, dtype=torch.int64).reshape(-1)
-        if tt.numel() not in (1, x.shape[0]):
-            raise RuntimeError(f"t has {tt.numel()} entries for batch size {x.shape[0]}")
-        if torch.is_grad_enabled() and G.ENABLE_TRAIN_GRAPHS and not torch.cuda.is_current_stream_capturing() \
-                and not self.class_cond and not isinstance(cond_input, E.CondState) \
-                and (x.requires_grad or any(p.requires_grad for p in self.parameters())):
-            return self._forward_train_graphed(x, tt, cond_input)
-        with torch.autocast("cuda", enabled=False):
-            return self._forward_eager(x, tt, cond_input)
-
-    def _forward_train_graphed(self, x, tt, cond_input):
-        cond_t = []
-        if self.text_cond:
-            assert 'text' in cond_input, \
-                "Model initialized with text conditioning but cond_input has no text information"
-            cond_t.append(cond_input['text'].float().contiguous())
-        if self.image_cond:
-            validate_image_conditional_input(cond_input, x)
-            cond_t.append(cond_input['image'].float().contiguous())
-        x = x.float().contiguous()
-        tg = self.__dict__.get("_train_graph")
-        if tg is None or tg.key != G.TrainGraph.make_key(self, x, tt, cond_t):
-            tg = G.TrainGraph(self, x, tt, cond_t, self.text_cond, self.image_cond)
-            self.__dict__["_train_graph"] = tg
-        tg.grad_sync = self.__dict__.get("_grad_sync")   # set by sdb200.parallel.DataParallel
-        return tg(x, tt, cond_t)
-
-    def _forward_eager(self, x, tt, cond_input):
-        st = self._cached_cond(cond_input, x) if self.cond else E.CondState()
-        if G.ENABLE_FORWARD_GRAPHS and not torch.is_grad_enabled() and not torch.cuda.is_current_stream_capturing():
-            graphs = self.__dict__.setdefault("_graphed", {})
-            key = (tuple(x.shape), tt.numel(), id(st))
-            gf = graphs.get(key)
-            if gf is None or not gf.valid(st):
-                if len(graphs) >= 4:
-                    graphs.pop(next(iter(graphs)))
-                gf = graphs[key] = G.GraphedForward(self, x, tt, st)
-            return gf(x, tt)
-        return self.run(x, tt, st).to_nchw()
-
-    def invalidate_plan(self):
-        """Drop captured graphs / hoisted conditioning (call after swapping sub-modules in place)."""
-        self.__dict__.pop("_graphed", None)
-        self.__dict__.pop("_cond_cache", None)
-        self.__dict__.pop("_train_graph", None)
-
-    def train(self, mode=True):
-        self.invalidate_plan()
-        return super().train(mode)
-
-    def _apply(self, fn, *a, **k):
-        self.invalidate_plan()
-        return super()._apply(fn, *a, **k)
 
     def run(self, x, tt, st):
         """Engine-level forward: x fp32 NCHW, tt int64 on device, st a CondState; returns the fp32 NHWC Act of the

@@ -87,7 +87,77 @@ def cond_of(inp, cfg):
     return c
 
 
+def _cond(types, text_dim=512, mask_hw=512):
+    cc = {'condition_types': types}
+    if 'text' in types:
+        cc['text_condition_config'] = {'text_embed_model': 'clip', 'train_text_embed_model': False,
+                                       'text_embed_dim': text_dim, 'cond_drop_prob': 0.9}
+    if 'image' in types:
+        cc['image_condition_config'] = {'image_condition_input_channels': 18, 'image_condition_output_channels': 3,
+                                        'image_condition_h': mask_hw, 'image_condition_w': mask_hw,
+                                        'cond_drop_prob': 0.9}
+    return cc
+
+
+# Model_DiT_9L_config.py:139-148 / Model_DiT_12L_config.py:125-133 (timestep_emb_dim = ldm_scaling(2.58) = 192)
+DIT_9L = {'hidden_size': 288, 'patch_size': 2, 'timestep_emb_dim': 192, 'num_layers': 9, 'num_heads': 9,
+          'head_dim': 32, 'condition_config': _cond(['text', 'image'])}
+DIT_12L = dict(DIT_9L, num_layers=12, condition_config=_cond(['image']))
+DIT_SMALL = {'hidden_size': 96, 'patch_size': 2, 'timestep_emb_dim': 64, 'num_layers': 2, 'num_heads': 3,
+             'head_dim': 32, 'condition_config': _cond(['text', 'image'], text_dim=128, mask_hw=64)}
+DIT_SMALL_PLAIN = {k: v for k, v in DIT_SMALL.items() if k != 'condition_config'}
+
+
+def randomise_zero_init(model, seed):
+    """SURVEY §8c trap (i): adaLN projections and proj_out are zero-initialised (transformer.py:147-151,
+    transformer_layer.py:73-74) — a default-init DiT returns exactly 0 and every gate is closed. Fixtures draw those
+    parameters from N(0, 0.02) (biases too) so the whole network is exercised."""
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for name, p in model.named_parameters():
+            if "adaptive_norm_layer" in name or name.startswith("proj_out"):
+                p.copy_(torch.randn(p.shape, generator=g) * 0.02)
+
+
+def gen_dit():
+    sys.path.insert(0, REF)
+    from models.transformer import DIT as RefDIT
+    sys.path.pop(0)
+    O = _load(os.path.join(ROOT, "oracle", "dit_torch.py"), "oracle_dit_torch")
+    ok = True
+    for name, cfg, batch, hw in [("dit_small_cond", DIT_SMALL, 3, 16), ("dit_small_plain", DIT_SMALL_PLAIN, 2, 16),
+                                 ("dit_9l_text_image", DIT_9L, 2, 32), ("dit_12l_image", DIT_12L, 2, 32)]:
+        seed = 1111
+        torch.manual_seed(seed)
+        model = RefDIT(4, cfg).eval()
+        randomise_zero_init(model, seed + 7)
+        inp = make_inputs(seed + 1, batch, cfg, hw=hw)
+        cond = cond_of(inp, cfg)
+        with torch.no_grad():
+            args = (inp["x"], inp["t"]) + ((cond,) if cond is not None else ())
+            ref = model(*args)
+            ref_scalar_t = model(inp["x"], torch.as_tensor(int(inp["t"][0])), *args[2:])
+            with torch.autocast("cpu", dtype=torch.bfloat16):
+                ref_bf16 = model(*args).float()
+            orc = O.dit_forward(model.state_dict(), cfg, inp["x"], inp["t"], cond)
+            orc_scalar = O.dit_forward(model.state_dict(), cfg, inp["x"], torch.as_tensor(int(inp["t"][0])), cond)
+        e_or, e_sc, e_bf = relerr(orc, ref), relerr(orc_scalar, ref_scalar_t), relerr(ref_bf16, ref)
+        print(f"{name}: oracle-vs-ref {e_or:.2e} (scalar t {e_sc:.2e})  ref bf16-autocast-vs-fp32 {e_bf:.2e} "
+              f"rel-L2 {l2err(ref_bf16, ref):.2e}  |out|max {ref.abs().max():.3f}")
+        ok &= e_or < 1e-5 and e_sc < 1e-5
+        torch.save({"config": cfg, "seed": seed, "rand_seed": seed + 7, "inputs": inp, "output": ref,
+                    "output_scalar_t": ref_scalar_t,
+                    "ref_bf16_autocast_relerr": e_bf, "ref_bf16_autocast_l2err": l2err(ref_bf16, ref)},
+                   os.path.join(GOLD, name + ".pt"))
+    return ok
+
+
 def main():
+    if "--only-dit" in sys.argv:
+        if not gen_dit():
+            print("ORACLE DISAGREES WITH THE REFERENCE")
+            sys.exit(1)
+        return
     sys.path.insert(0, REF)
     from models.unet_cond_base import Unet as RefCond
     from models.unet_base import Unet as RefUncond
@@ -171,6 +241,7 @@ def main():
         fx[key + "_acp"] = s.alpha_cum_prod.numpy()
     np.savez_compressed(os.path.join(GOLD, "scheduler.npz"), **fx)
     print("scheduler fixtures written")
+    ok &= gen_dit()
     if not ok:
         print("ORACLE DISAGREES WITH THE REFERENCE")
         sys.exit(1)

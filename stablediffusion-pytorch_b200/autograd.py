@@ -61,7 +61,7 @@ class LinearFn(Function):
     """y = x @ W^T + b (+ residual); x bf16 [M, K] rows, W fp32 [N, K]. Returns (y, stats or empty)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, residual, rows_per_img, want_stats):
+    def forward(ctx, x, weight, bias, residual, rows_per_img, want_stats, act=None):
         M, K = x.shape
         N = weight.shape[0]
         wp = ops.pack_linear_weight(weight)
@@ -69,9 +69,11 @@ class LinearFn(Function):
         if want_stats and rows_per_img:
             st = _new_stats(M // rows_per_img, 1, rows_per_img, N, x.device)
         out = torch.empty(M, _pad8(N), device=x.device, dtype=torch.bfloat16)[:, :N]
-        rt.linear(x, wp, bias=None if bias is None else bias.detach().float(), residual=residual, out=out,
+        if act not in (None, "relu") or (act and residual is not None):
+            raise rt.B200Error("LinearFn: only a ReLU epilogue (without residual) has a backward")
+        rt.linear(x, wp, bias=None if bias is None else bias.detach().float(), residual=residual, out=out, act=act,
                   rows_per_img=rows_per_img if st is not None else None, stats=_stats_arg(st))
-        ctx.save_for_backward(x, weight)
+        ctx.save_for_backward(x, weight, out if act else None)
         ctx.has_bias, ctx.has_res = bias is not None, residual is not None
         stats_t = st[0] if st is not None else torch.empty(0, device=x.device)
         ctx.mark_non_differentiable(stats_t)
@@ -79,10 +81,12 @@ class LinearFn(Function):
 
     @staticmethod
     def backward(ctx, dy, _):
-        x, weight = ctx.saved_tensors
+        x, weight, y_act = ctx.saved_tensors
         M, K = x.shape
         N = weight.shape[0]
         dy = _rows(dy, N)
+        if y_act is not None:
+            dy = rt.relu_bwd(dy, y_act)
         dx = dw = db = dres = None
         if ctx.needs_input_grad[0]:
             wt = ops.pack_linear_weight(weight.detach().t())  # [K, N_pad64]
@@ -97,7 +101,7 @@ class LinearFn(Function):
             db = rt.colsum(dy, 1, M, N) if N % 8 == 0 else dy.float().sum(0)
         if ctx.has_res and ctx.needs_input_grad[3]:
             dres = dy
-        return dx, dw, db, dres, None, None
+        return dx, dw, db, dres, None, None, None
 
 
 # ---------------------------------------------------------------------------------------------------- Conv 3x3 / 1x1
@@ -411,3 +415,108 @@ class MaskCondFn(Function):
         ms = mask[:, :, ::sy, ::sx][:, :, :h, :w].float().permute(0, 2, 3, 1).reshape(n * h * w, cin)
         dw = g[:, c_off:c_off + cout].float().t() @ ms
         return dw.reshape(cout, cin, 1, 1), None, g, None, None, None
+
+
+# ---------------------------------------------------------------------------------------------------- DiT rows
+class LayerNormModFn(Function):
+    """LayerNorm(no affine, eps) * (1 + scale[img]) + shift[img] on bf16 token rows (transformer_layer.py:88-89,
+    103-104; transformer.py:196-197); shift = scale = None is the plain cross_attn_norm (:94)."""
+
+    @staticmethod
+    def forward(ctx, x, shift, scale, meta):
+        n, rows_per_img, c, eps = meta
+        y, stats = rt.layernorm_mod(x, n, rows_per_img, c, shift=shift, scale=scale, eps=eps, want_stats=True)
+        ctx.save_for_backward(x, stats, scale)
+        ctx.meta = meta
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, stats, scale = ctx.saved_tensors
+        n, rows_per_img, c, _ = ctx.meta
+        dy = _rows(dy, c)
+        dx, dshift, dscale = rt.layernorm_mod_bwd(dy, x, stats, n, rows_per_img, c, scale=scale)
+        if scale is None:
+            return dx, None, None, None
+        return dx, dshift.to(torch.bfloat16), dscale.to(torch.bfloat16), None
+
+
+class GateResidualFn(Function):
+    """y = x + gate[img] * h (adaLN-Zero gate, transformer_layer.py:90,105). Inference fuses this into the igemm
+    epilogue; training keeps h, which the gate gradient needs."""
+
+    @staticmethod
+    def forward(ctx, x, h, gate, meta):
+        n, rows_per_img, c = meta
+        ctx.save_for_backward(h, gate)
+        ctx.meta = meta
+        return rt.gate_residual(x, h, gate, n, rows_per_img, c)
+
+    @staticmethod
+    def backward(ctx, dy):
+        h, gate = ctx.saved_tensors
+        n, rows_per_img, c = ctx.meta
+        dy = _rows(dy, c)
+        dh, dgate = rt.gate_residual_bwd(dy, h, gate, n, rows_per_img, c)
+        return dy, dh, dgate.to(torch.bfloat16), None
+
+
+class PatchEmbedFn(Function):
+    """PatchEmbedding (patch_embed.py:75-96) on the NHWC input buffer: the (ph pw c) fold + Linear is a p x p stride-p
+    convolution, run as one implicit GEMM over p*p strided views of the buffer, with the position embedding as the
+    epilogue's (batch-broadcast) residual. xbuf: bf16 [n*H*W, ld]; weight fp32 [hidden, p*p*cin]; pos bf16 [gh*gw, hidden]."""
+
+    @staticmethod
+    def forward(ctx, xbuf, weight, bias, pos, geom):
+        n, H, W, cin, p = geom
+        out = ops.patch_embed(xbuf, n, H, W, cin, p, ops.pack_patch_weight(weight, p, cin), weight.shape[0],
+                              bias=None if bias is None else bias.detach().float(), pos=pos)
+        ctx.save_for_backward(xbuf, weight)
+        ctx.geom, ctx.has_bias = geom, bias is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        xbuf, weight = ctx.saved_tensors
+        n, H, W, cin, p = ctx.geom
+        hidden = weight.shape[0]
+        gh, gw = H // p, W // p
+        dy = _rows(dy, hidden)
+        dx = dw = db = None
+        ld = xbuf.stride(0)
+        if ctx.needs_input_grad[0]:
+            # adjoint: each (py, px) phase of the input grid is a GEMM against that tap's [cin, hidden] weights
+            dx = torch.zeros_like(xbuf)
+            wv = weight.detach().reshape(hidden, p * p, cin)
+            flat = dx.view(-1)
+            for t in range(p * p):
+                py, px = t // p, t % p
+                wt = ops.pack_linear_weight(wv[:, t, :].t())           # [cin, hidden_pad64]
+                o = flat[(py * W + px) * ld:]
+                src = rt.make_src(dy, n, gh, gw, hidden, ld=dy.stride(0))
+                rt.igemm([src], [(0, 0, 0, 0, wt.shape[1] // 64)], wt, cin, n, gh, gw, o, (H * W * ld, p * W * ld, p * ld))
+        if ctx.needs_input_grad[1]:
+            srcs = [rt.make_src(xbuf, n, gh, gw, cin, ld=ld, sy=p, sx=p, oy=t // p, ox=t % p, hh=H, ww=W)
+                    for t in range(p * p)]
+            segs = [(t, 0, 0, 0, 1) for t in range(p * p)]
+            dwp = rt.wgrad(srcs, segs, rt.make_src(dy, n, gh, gw, hidden, ld=dy.stride(0)), hidden, n, gh, gw)
+            dw = dwp.reshape(hidden, p * p, 64)[:, :, :cin].reshape(hidden, p * p * cin)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = rt.colsum(dy, 1, n * gh * gw, hidden)
+        return dx, dw, db, None, None
+
+
+class UnpatchifyFn(Function):
+    """Token rows -> fp32 NCHW model output (transformer.py:203-211); the NCHW gradient folds back into token rows."""
+
+    @staticmethod
+    def forward(ctx, tokens, geom):
+        n, ch, gh, gw, p = geom
+        ctx.geom, ctx.ld = geom, tokens.shape[1]
+        return rt.unpatchify(tokens, n, ch, gh, gw, p, p)
+
+    @staticmethod
+    def backward(ctx, g):
+        n, ch, gh, gw, p = ctx.geom
+        tok = rt.patchify(g.float(), p, p, ld=(ctx.ld + 7) // 8 * 8)
+        return tok[:, :ctx.ld], None

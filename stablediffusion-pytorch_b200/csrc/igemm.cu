@@ -655,7 +655,11 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
     if (a.tma_out) {
         int rc = encode_pixel_view(&a.out_map, p->out, n, p->ow, p->oh, p->on, p->out_sn, p->out_sy, p->out_sx, abox);
         if (rc) return rc;
-        a.tma_res = p->residual && pixel_view_ok(p->residual, p->res_sn, p->res_sy, p->res_sx);
+        // a zero stride over an extent > 1 is a broadcast (position embedding shared by all images): TMA cannot
+        // express it, the epilogue's direct loads can
+        const bool res_bcast = (p->res_sn == 0 && p->on > 1) || (p->res_sy == 0 && p->oh > 1) ||
+                               (p->res_sx == 0 && p->ow > 1);
+        a.tma_res = p->residual && !res_bcast && pixel_view_ok(p->residual, p->res_sn, p->res_sy, p->res_sx);
         if (a.tma_res) {
             rc = encode_pixel_view(&a.res_map, p->residual, n, p->ow, p->oh, p->on, p->res_sn, p->res_sy, p->res_sx,
                                    abox);

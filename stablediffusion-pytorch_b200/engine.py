@@ -238,8 +238,8 @@ def linear(x, mod, act=None, residual=None, out_dtype=torch.bfloat16, rows_per_i
     if hasattr(mod, "forward_rows") and residual is None and gate is None and rowbias is None:
         return mod.forward_rows(x, act=act)
     _require_leaf(mod, (nn.Linear, nn.modules.linear.NonDynamicallyQuantizableLinear), "Linear")
-    if training() and act is None and gate is None and rowbias is None and out_dtype == torch.bfloat16:
-        o, st = AG.LinearFn.apply(x, mod.weight, mod.bias, residual, rows_per_img, stats is not None)
+    if training() and act in (None, "relu") and gate is None and rowbias is None and out_dtype == torch.bfloat16:
+        o, st = AG.LinearFn.apply(x, mod.weight, mod.bias, residual, rows_per_img, stats is not None, act)
         return (o, st) if stats is not None else o
     if training():
         raise rt.B200Error("Linear: this epilogue combination has no training path")
@@ -505,3 +505,80 @@ def upsample_concat(a, up_conv, skip):
     if all(sg is not None for sg in segs):
         out.stats = segs  # channel-concat of tensors whose producers each left their own partial statistics
     return out
+
+
+# ------------------------------------------------------------------------------------------ DiT token-row operators
+# The DiT residual stream is a bf16 [n*L, hidden] row matrix (L tokens per image); per-image adaLN operands are
+# [n, hidden] column slices of ONE batched projection of relu(t_emb) (TembBank over every layer's
+# adaptive_norm_layer[1], transformer_layer.py:62-65 + transformer.py:126-129).
+def layer_norm_mod(x, norm, n, L, shift=None, scale=None):
+    """LayerNorm(elementwise_affine=False) * (1 + scale) + shift — transformer_layer.py:88-89,94,103-104."""
+    _require_leaf(norm, (nn.LayerNorm,), "LayerNorm")
+    if norm.elementwise_affine or len(norm.normalized_shape) != 1:
+        raise rt.B200Error("LayerNorm: only the affine-free last-dimension form has a CUDA path")
+    c = norm.normalized_shape[0]
+    if training() and (x.requires_grad or (scale is not None and scale.requires_grad)):
+        return AG.LayerNormModFn.apply(x, shift, scale, (n, L, c, norm.eps))
+    return rt.layernorm_mod(x, n, L, c, shift=shift, scale=scale, eps=norm.eps)
+
+
+def gated_linear(h_in, mod, x, gate, n, L):
+    """x + gate[img] * Linear(h_in) — the adaLN-Zero residual (transformer_layer.py:90,105): one GEMM with the gate
+    and the residual in its epilogue; in training the un-gated product is kept for the gate gradient."""
+    if training():
+        h = linear(h_in, mod)
+        return AG.GateResidualFn.apply(x, h, gate, (n, L, x.shape[1]))
+    return linear(h_in, mod, residual=x, gate=gate, rows_per_img=L)
+
+
+def dit_self_attention(xn, attn, n, L):
+    """models/attention.py:33-78 up to (not including) output_proj: packed QKV GEMM + flash attention."""
+    A, heads, d = attn.att_dim, attn.n_heads, attn.head_dim
+    qkv = linear(xn, attn.qkv_proj)
+    if training():
+        return AG.AttentionFn.apply(None, qkv, (n, heads, L, L, d))
+    return rt.attention(qkv[:, :A], qkv[:, A:2 * A], qkv[:, 2 * A:], n, heads, L, L, d)
+
+
+def dit_cross_attention(x, norm, mha, ctx_proj_mod, ctx, n, L):
+    """x + out_proj(MHA(q = LN(x), k = v = context_proj(context))) — transformer_layer.py:92-101 (un-gated). The K/V of
+    a site depend only on the context and the weights: a persistent Context keeps them across sampling steps."""
+    C, heads = mha.embed_dim, mha.num_heads
+    xn = layer_norm_mod(x, norm, n, L)
+    if training():
+        w, b = _mha_params(mha)
+        q, _ = AG.LinearFn.apply(xn, w[:C], None if b is None else b[:C], None, None, False)
+        _require_leaf(ctx_proj_mod, (nn.Linear,), "Linear")
+        cp, _ = AG.LinearFn.apply(ctx.t, ctx_proj_mod.weight, ctx_proj_mod.bias, None, None, False)
+        kv, _ = AG.LinearFn.apply(cp, w[C:], None if b is None else b[C:], None, None, False)
+        o = AG.AttentionFn.apply(q, kv, (n, heads, L, ctx.lk, C // heads))
+        out, _ = AG.LinearFn.apply(o, mha.out_proj.weight, mha.out_proj.bias, x, None, False)
+        return out
+    pk = _mha_weights(mha)
+    q = rt.linear(xn, pk["q"], bias=pk["b_q"])
+    kv = ctx.kv.get(id(mha))
+    if kv is None:
+        kv = rt.linear(linear(ctx.t, ctx_proj_mod), pk["kv"], bias=pk["b_kv"])
+        if ctx.persistent:
+            ctx.kv[id(mha)] = kv
+    o = rt.attention(q, kv[:, :C], kv[:, C:], n, heads, L, ctx.lk, C // heads)
+    return linear(o, mha.out_proj, residual=x)
+
+
+def patch_embed(xbuf, n, H, W, cin, p, mod, pos):
+    """PatchEmbedding.patch_embed[0] on the NHWC input buffer (+ position embedding) — patch_embed.py:84-95."""
+    _require_leaf(mod, (nn.Linear,), "Linear(patch_embed)")
+    if p * p > 4:
+        raise rt.B200Error("patch embedding: patch sizes above 2 are not supported")
+    if mod.in_features != p * p * cin:
+        raise rt.B200Error("patch embedding: Linear.in_features does not match patch_size^2 * channels")
+    if training():
+        return AG.PatchEmbedFn.apply(xbuf, mod.weight, mod.bias, pos, (n, H, W, cin, p))
+    wmat = CACHE.get(mod, "patch", (mod.weight,), lambda: ops.pack_patch_weight(mod.weight, p, cin))
+    return ops.patch_embed(xbuf, n, H, W, cin, p, wmat, mod.out_features, bias=_f32(mod.bias), pos=pos)
+
+
+def unpatchify(tokens, n, ch, gh, gw, p):
+    if training() and tokens.requires_grad:
+        return AG.UnpatchifyFn.apply(tokens, (n, ch, gh, gw, p))
+    return rt.unpatchify(tokens, n, ch, gh, gw, p, p)

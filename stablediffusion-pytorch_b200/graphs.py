@@ -17,6 +17,11 @@ ENABLE_FORWARD_GRAPHS = True
 ENABLE_TRAIN_GRAPHS = True   # forward AND backward of a training step replay captured graphs (see TrainGraph)
 
 
+def as_nchw(out):
+    """A model's `run` returns either an NHWC Act (UNet) or the fp32 NCHW tensor itself (DiT un-patchifies)."""
+    return out.to_nchw() if hasattr(out, "to_nchw") else out
+
+
 def _param_stamp(params):
     return tuple((p.data_ptr(), p._version) for p in params)
 
@@ -40,7 +45,7 @@ class GraphedForward:
         self.graph = torch.cuda.CUDAGraph()
         before = rt.launch_count()
         with torch.cuda.graph(self.graph), torch.no_grad():
-            self.out = model.run(self.x, self.t, st).to_nchw()
+            self.out = as_nchw(model.run(self.x, self.t, st))
         self.launches = rt.launch_count() - before
 
     def valid(self, st):
@@ -85,8 +90,8 @@ class SamplingPipeline:
         seed = self.scheduler.seed
 
         def body():
-            eps = m.run(P.xt, P.t, P.st).to_nchw()
-            eps_u = m.run(P.xt, P.t, P.st_u).to_nchw() if P.st_u is not None else None
+            eps = as_nchw(m.run(P.xt, P.t, P.st))
+            eps_u = as_nchw(m.run(P.xt, P.t, P.st_u)) if P.st_u is not None else None
             rt.sched_prev_step(P.xt, eps, P.t[:1], tables, z=P.z, eps_uncond=eps_u, cfg_scale=cfg_scale,
                                seed=seed, offset=0, x_prev=P.xt, x0=P.x0)
             rt.advance_t(P.t, -1)
@@ -225,7 +230,7 @@ class TrainGraph:
                 ci["image"] = self.cond[k]
             with swap:
                 st = core.prepare_cond(ci, self.x.shape, dev) if core.cond else E.CondState()
-                return core.run(self.x, self.tt, st).to_nchw()
+                return as_nchw(core.run(self.x, self.tt, st))
 
         # slots of the flat gradient buffer
         self.slots, off = [], 0

@@ -116,3 +116,31 @@ def conv_up4x4(x, n, h, w, cin, phases, cout, bias=None, ld_x=None, out=None, c_
             st = (stats[0], stats[1], idx * (stats[1] // 4), stats[2])
         rt.igemm([src], segs, wmat, cout, n, h, w, o, (4 * h * w * ld, 4 * w * ld, 2 * ld), bias=bias, stats=st)
     return out
+
+
+def pack_patch_weight(w, p, cin):
+    """PatchEmbedding Linear weight [hidden, (py px c)] -> bf16 [hidden, p*p*64]: one 64-wide K chunk per tap."""
+    hidden = w.shape[0]
+    if cin > 64:
+        raise rt.B200Error("patch embedding: more than 64 input channels per tap is not supported")
+    m = torch.zeros(hidden, p * p, 64, device=w.device, dtype=torch.bfloat16)
+    m[:, :, :cin] = w.detach().reshape(hidden, p * p, cin).to(torch.bfloat16)
+    return m.reshape(hidden, p * p * 64)
+
+
+def patch_embed(xbuf, n, H, W, cin, p, wmat, hidden, bias=None, pos=None):
+    """tokens[(img, gy, gx)] = W . fold_{p x p}(x)[gy, gx] + bias + pos[(gy, gx)] (models/patch_embed.py:84-95) as an
+    implicit GEMM over p*p strided views of the NHWC buffer xbuf [n*H*W, ld]."""
+    if H % p or W % p:
+        raise rt.B200Error("patch embedding: image size must be divisible by the patch size")
+    gh, gw = H // p, W // p
+    ld = xbuf.stride(0)
+    srcs = [rt.make_src(xbuf, n, gh, gw, cin, ld=ld, sy=p, sx=p, oy=t // p, ox=t % p, hh=H, ww=W) for t in range(p * p)]
+    segs = [(t, 0, 0, 0, 1) for t in range(p * p)]
+    out = torch.empty(n * gh * gw, hidden, device=xbuf.device, dtype=torch.bfloat16)
+    rs = None
+    if pos is not None:
+        rs = (0, gw * pos.stride(0), pos.stride(0))   # the same position rows for every image
+    rt.igemm(srcs, segs, wmat, hidden, n, gh, gw, out, (gh * gw * hidden, gw * hidden, hidden), bias=bias, residual=pos,
+             res_strides=rs)
+    return out

@@ -20,6 +20,8 @@ EXPORTS = [
     "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_attention_lse", "b200sd_attention_bwd", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_rowblocks", "b200sd_groupnorm_bwd", "b200sd_colsum",
     "b200sd_reduce_f32", "b200sd_attention",
     "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16",
+    "b200sd_layernorm_mod", "b200sd_layernorm_mod_bwd", "b200sd_rows_per_slot", "b200sd_gate_residual",
+    "b200sd_gate_residual_bwd", "b200sd_relu_bwd", "b200sd_unpatchify", "b200sd_patchify",
 ]
 
 
@@ -100,6 +102,14 @@ def lib():
         L.b200sd_copy_act.argtypes = [vp, i64, vp, i64, i32, i64, i32, i32, vp]
         L.b200sd_cast_f32_bf16.argtypes = [vp, vp, i64, vp]
         L.b200sd_add_bf16.argtypes = [vp, vp, vp, i64, vp]
+        L.b200sd_layernorm_mod.argtypes = [vp, i64, vp, i64, vp, vp, i64, i64, i64, i32, f32, vp, vp]
+        L.b200sd_layernorm_mod_bwd.argtypes = [vp, i64, vp, i64, vp, vp, i64, vp, i64, vp, i64, i64, i64, i32, vp, vp]
+        L.b200sd_rows_per_slot.argtypes = []
+        L.b200sd_gate_residual.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, i64, i64, i32, vp]
+        L.b200sd_gate_residual_bwd.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, i64, i64, i32, vp, vp]
+        L.b200sd_relu_bwd.argtypes = [vp, i64, vp, i64, vp, i64, i64, i32, vp]
+        L.b200sd_unpatchify.argtypes = [vp, i32, i64, vp, i64, i32, i32, i32, i32, i32, vp]
+        L.b200sd_patchify.argtypes = [vp, vp, i64, i64, i32, i32, i32, i32, i32, vp]
         _lib = L
     return _lib
 
@@ -510,3 +520,97 @@ def cast_bf16(src):
 def add_bf16(a, b, out):
     check(lib().b200sd_add_bf16(_p(a), _p(b), _p(out), a.numel(), stream_ptr()), "add_bf16")
     return out
+
+
+# ------------------------------------------------------------------------------------------------ DiT token rows
+def _slots(rows_per_img):
+    r = int(lib().b200sd_rows_per_slot())
+    return (rows_per_img + r - 1) // r
+
+
+def layernorm_mod(x, n, rows_per_img, c, shift=None, scale=None, eps=1e-6, want_stats=False):
+    """LayerNorm(no affine) * (1 + scale[img]) + shift[img] on bf16 rows; shift/scale: bf16 [n, >=c] views of a common
+    parent (same row pitch) or None. Returns y (and fp32 [rows, 2] (mean, rstd) when want_stats)."""
+    _cuda(x, torch.bfloat16, "x")
+    rows = n * rows_per_img
+    y = torch.empty(rows, c, device=x.device, dtype=torch.bfloat16)
+    stats = torch.empty(rows, 2, device=x.device, dtype=torch.float32) if want_stats else None
+    ld_m = 0
+    if scale is not None:
+        _cuda(scale, torch.bfloat16, "scale"), _cuda(shift, torch.bfloat16, "shift")
+        if scale.stride(0) != shift.stride(0) or scale.stride(1) != 1 or shift.stride(1) != 1:
+            raise B200Error("layernorm_mod: shift and scale must be unit-stride rows with one pitch")
+        ld_m = scale.stride(0)
+    tok = _pb()
+    check(lib().b200sd_layernorm_mod(_p(x), x.stride(0), _p(y), c, _p(shift), _p(scale), ld_m, rows, rows_per_img, c,
+                                     float(eps), _p(stats), stream_ptr()), "layernorm_mod")
+    _pe(tok, "layernorm", 4.0 * rows * c, (rows, c))
+    return (y, stats) if want_stats else y
+
+
+def layernorm_mod_bwd(dy, x, stats, n, rows_per_img, c, scale=None, dres=None):
+    """-> (dx bf16, dshift fp32 [n, c] or None, dscale fp32 [n, c] or None)."""
+    rows = n * rows_per_img
+    dx = torch.empty(rows, c, device=x.device, dtype=torch.bfloat16)
+    part = None
+    slots = _slots(rows_per_img)
+    if scale is not None:
+        part = torch.empty(n, slots, 2, c, device=x.device, dtype=torch.float32)
+    tok = _pb()
+    check(lib().b200sd_layernorm_mod_bwd(_p(dy), dy.stride(0), _p(x), x.stride(0), _p(stats), _p(scale),
+                                         0 if scale is None else scale.stride(0), _p(dres),
+                                         0 if dres is None else dres.stride(0), _p(dx), c, n, rows_per_img, c, _p(part),
+                                         stream_ptr()), "layernorm_mod_bwd")
+    _pe(tok, "layernorm_bwd", 6.0 * rows * c, (rows, c))
+    if part is None:
+        return dx, None, None
+    both = reduce_f32(part, n, slots, 2 * c, 1, torch.empty(n, 2, c, device=x.device, dtype=torch.float32))
+    return dx, both[:, 0], both[:, 1]
+
+
+def gate_residual(x, h, gate, n, rows_per_img, c):
+    y = torch.empty(n * rows_per_img, c, device=x.device, dtype=torch.bfloat16)
+    check(lib().b200sd_gate_residual(_p(x), x.stride(0), _p(h), h.stride(0), _p(gate), gate.stride(0), _p(y), c,
+                                     n * rows_per_img, rows_per_img, c, stream_ptr()), "gate_residual")
+    return y
+
+
+def gate_residual_bwd(dy, h, gate, n, rows_per_img, c):
+    """-> (dh bf16, dgate fp32 [n, c])."""
+    dh = torch.empty(n * rows_per_img, c, device=dy.device, dtype=torch.bfloat16)
+    slots = _slots(rows_per_img)
+    part = torch.empty(n, slots, c, device=dy.device, dtype=torch.float32)
+    check(lib().b200sd_gate_residual_bwd(_p(dy), dy.stride(0), _p(h), h.stride(0), _p(gate), gate.stride(0), _p(dh), c, n,
+                                         rows_per_img, c, _p(part), stream_ptr()), "gate_residual_bwd")
+    dgate = reduce_f32(part, n, slots, c, 1, torch.empty(n, c, device=dy.device, dtype=torch.float32))
+    return dh, dgate
+
+
+def relu_bwd(dy, y):
+    rows, c = y.shape
+    dx = torch.empty(rows, c, device=y.device, dtype=torch.bfloat16)
+    check(lib().b200sd_relu_bwd(_p(dy), dy.stride(0), _p(y), y.stride(0), _p(dx), c, rows, c, stream_ptr()), "relu_bwd")
+    return dx
+
+
+def unpatchify(tokens, n, channels, gh, gw, ph, pw):
+    """token rows [(n, gh, gw), >= ph*pw*channels] (bf16 / fp32) -> fp32 NCHW [n, channels, gh*ph, gw*pw]."""
+    if tokens.dtype not in (torch.bfloat16, torch.float32) or not tokens.is_cuda:
+        raise B200Error("unpatchify: CUDA bf16/fp32 token rows required")
+    img = torch.empty(n, channels, gh * ph, gw * pw, device=tokens.device, dtype=torch.float32)
+    check(lib().b200sd_unpatchify(_p(tokens), 1 if tokens.dtype == torch.float32 else 0, tokens.stride(0), _p(img), n,
+                                  channels, gh, gw, ph, pw, stream_ptr()), "unpatchify")
+    return img
+
+
+def patchify(img, ph, pw, ld=None):
+    """fp32 NCHW -> bf16 token rows [(n, gh, gw), ld] with columns (py, px, ch), zero beyond ph*pw*ch."""
+    _cuda(img, torch.float32, "image")
+    img = img.contiguous()
+    n, ch, H, W = img.shape
+    gh, gw = H // ph, W // pw
+    width = ph * pw * ch
+    ld = (width + 7) // 8 * 8 if ld is None else ld
+    tok = torch.empty(n * gh * gw, ld, device=img.device, dtype=torch.bfloat16)
+    check(lib().b200sd_patchify(_p(img), _p(tok), ld, n, ch, gh, gw, ph, pw, stream_ptr()), "patchify")
+    return tok

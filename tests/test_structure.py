@@ -28,6 +28,20 @@ def test_state_dict_matches_reference_manifest(name):
     assert [n for n, _ in m.named_parameters()] == [k for k, _ in entry["state_dict"]]
 
 
+@pytest.mark.parametrize("name", ["dit_9l_text_image", "dit_12l_image"])
+def test_dit_state_dict_matches_reference_manifest(name):
+    from models.transformer import DIT
+    entry = MAN[name]
+    with torch.device("meta"):
+        m = DIT(4, entry["config"])
+    got = [[k, list(v.shape)] for k, v in m.state_dict().items()]
+    assert got == entry["state_dict"]
+    assert [n for n, _ in m.named_parameters()] == [k for k, _ in entry["state_dict"]]
+    # cim_qn_train's module surgery matches exact leaf types: every projection must be a plain nn.Linear
+    assert sum(1 for x in m.modules() if type(x) is nn.Linear) == sum(
+        1 for k, shp in entry["state_dict"] if k.endswith(".weight") and len(shp) == 2)
+
+
 def test_leaves_are_exact_torch_types_for_module_surgery():
     """cim_qn_train/progressive_qn_train.py:614 matches `type(m) in (nn.Conv2d, nn.Linear)` exactly."""
     with torch.device("meta"):

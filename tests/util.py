@@ -35,3 +35,12 @@ def cond_of(inp, cfg, device=None):
     if device is not None:
         c = {k: v.to(device) for k, v in c.items()}
     return c
+
+
+def randomise_zero_init(model, seed):
+    """Same draw as oracle/gen_golden.py: the DiT's zero-initialised adaLN / proj_out parameters from N(0, 0.02)."""
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for name, p in model.named_parameters():
+            if "adaptive_norm_layer" in name or name.startswith("proj_out"):
+                p.copy_(torch.randn(p.shape, generator=g) * 0.02)
