@@ -1,0 +1,178 @@
+"""Drop-in for the reference's cim_layers/layers_qn_lsq.py: `Conv2d_qn_lsq` / `Linear_qn_lsq` —
+    y = Q_out( conv_or_linear( Q_in(x), W_q + noise, bias ) )
+with LSQ (learned step size) quantisers, weight noise proportional to the quantised weight range, a `use_FP` bypass
+and `update_para` bit-width changes. Same constructor keywords, parameter names (`step_size_input/output/weight`,
+checkpoints interchange) and lazy step-size initialisation as the reference (:17-121,126-216); activations are
+quantised by CUDA kernels, the product runs on the tcgen05 implicit GEMM, backward included."""
+import torch
+import torch.nn as nn
+
+import sdb200  # noqa: F401
+from sdb200 import autograd as AG
+from sdb200 import engine as E
+from sdb200 import ops
+from sdb200 import quant as Q
+from sdb200 import runtime as rt
+
+
+class _LsqMixin:
+    def _init_lsq(self, weight_bit, input_bit, output_bit, noise_scale, input_quant, output_quant, weight_quant,
+                  gain_noise_scale, offset_noise_scale):
+        self.use_FP = False
+        self.weight_bit = weight_bit
+        self.input_bit = input_bit
+        self.output_bit = output_bit
+        self.noise_scale = noise_scale
+        self.gain_noise_scale = gain_noise_scale
+        self.offset_noise_scale = offset_noise_scale
+        self.input_quant = input_quant
+        self.output_quant = output_quant
+        self.weight_quant = weight_quant
+        self.step_size_input = nn.Parameter(torch.tensor(1.0))
+        self.step_size_output = nn.Parameter(torch.tensor(1.0))
+        self.step_size_weight = nn.Parameter(torch.tensor(1.0))
+        self.weight_noise_unit = None   # tests inject the N(0,1) draw of the weight noise here
+
+    def update_para(self, use_FP=False, weight_bit=None, input_bit=None, output_bit=None, noise_scale=None,
+                    gain_noise_scale=0, offset_noise_scale=0):
+        old = (self.weight_bit, self.input_bit, self.output_bit)
+        self.use_FP = use_FP
+        if weight_bit is not None:
+            self.weight_bit = weight_bit
+        if input_bit is not None:
+            self.input_bit = input_bit
+        if output_bit is not None:
+            self.output_bit = output_bit
+        if noise_scale is not None:
+            self.noise_scale = noise_scale
+        if gain_noise_scale is not None:
+            self.gain_noise_scale = gain_noise_scale
+        if offset_noise_scale is not None:
+            self.offset_noise_scale = offset_noise_scale
+        Q.rescale_step_sizes(self, *old)
+
+    def _linear(self, rows, w, act=None):
+        """rows @ w^T + bias with an explicit (already quantised) weight tensor."""
+        if E.training():
+            o, _ = AG.LinearFn.apply(rows, w, self.bias, None, None, False, act)
+            return o
+        return rt.linear(rows, ops.pack_linear_weight(w), bias=None if self.bias is None else self.bias.detach().float(),
+                         act=act)
+
+    # ---- the three quantisers ---------------------------------------------------------------------------------
+    def _q_in(self, rows, numel, isint=False):
+        if not self.input_quant:
+            return rows
+        return Q.quantize_rows(rows, self.step_size_input, self.input_bit, codes=isint, numel=numel)
+
+    def _q_out(self, rows, numel):
+        if not self.output_quant:
+            return rows
+        return Q.quantize_rows(rows, self.step_size_output, self.output_bit, numel=numel)
+
+    def _w_qn(self, isint=False):
+        """(quantised + noisy weight as a differentiable fp32 tensor, w_scale)."""
+        w, scale = self.weight, 1.0
+        if self.weight_quant:
+            Q.init_weight_step_(self.step_size_weight, self.weight, self.weight_bit)
+            w, scale = Q.quantize_weight(self.weight, self.step_size_weight, self.weight_bit, isint)
+        return Q.add_weight_noise(w, self.noise_scale, self.weight_noise_unit), scale
+
+
+class Conv2d_qn_lsq(nn.Conv2d, _LsqMixin):
+    def __init__(self, in_channels, out_channels, kernel_size, stride, padding, groups, weight_bit, input_bit,
+                 output_bit, noise_scale, input_quant=True, output_quant=True, weight_quant=True, gain_noise_scale=0,
+                 offset_noise_scale=0, bias=True):
+        super().__init__(in_channels=in_channels, out_channels=out_channels, kernel_size=kernel_size, stride=stride,
+                         padding=padding, groups=groups, bias=bias)
+        self._init_lsq(weight_bit, input_bit, output_bit, noise_scale, input_quant, output_quant, weight_quant,
+                       gain_noise_scale, offset_noise_scale)
+
+    def _conv(self, a, x_rows, w):
+        """Convolution of NHWC rows with an explicit (already quantised) weight tensor -> Act."""
+        k, s, p = self.kernel_size, self.stride, self.padding
+        if self.groups != 1 or self.dilation != (1, 1):
+            raise rt.B200Error("Conv2d_qn_lsq: groups/dilation are not supported")
+        cout = self.out_channels
+        same = k in ((3, 3), (1, 1)) and s == (1, 1) and p == (k[0] // 2, k[0] // 2)
+        down = k == (4, 4) and s == (2, 2) and p == (1, 1)
+        if not (same or down):
+            raise rt.B200Error(f"Conv2d_qn_lsq: kernel {k} stride {s} padding {p} has no CUDA path")
+        if E.training():
+            if same:
+                o, _ = AG.ConvSameFn.apply(x_rows, w, self.bias, None, None, None, None, (a.n, a.h, a.w, a.c, 0), False,
+                                           False)
+                return E.Act(o, a.n, a.h, a.w, cout)
+            o, _ = AG.ConvDownFn.apply(x_rows, w, self.bias, (a.n, a.h, a.w, a.c), False)
+            return E.Act(o, a.n, a.h // 2, a.w // 2, cout)
+        wmat = ops.pack_conv_weight(w)
+        bias = None if self.bias is None else self.bias.detach().float()
+        if same:
+            o = torch.empty(a.n * a.hw, (cout + 7) // 8 * 8, device=x_rows.device, dtype=torch.bfloat16)
+            ops.conv_same(x_rows, a.n, a.h, a.w, a.c, wmat, cout, k[0], bias=bias, ld_x=x_rows.stride(0), out=o)
+            return E.Act(o, a.n, a.h, a.w, cout)
+        o = E.Act.empty(a.n, a.h // 2, a.w // 2, cout, x_rows.device)
+        ops.conv_down4x4(x_rows, a.n, a.h, a.w, a.c, wmat, cout, bias=bias, ld_x=x_rows.stride(0), out=o.t)
+        return o
+
+    def forward_act(self, a):
+        """Engine entry: NHWC bf16 Act -> Act."""
+        if self.use_FP:
+            return self._conv(a, a.t, self.weight)
+        if a.c % 8 or a.t.shape[1] != a.c:
+            raise rt.B200Error("Conv2d_qn_lsq: input channels must be a multiple of 8 and densely packed")
+        xq = self._q_in(a.t, a.n * a.hw * a.c)
+        w, _ = self._w_qn()
+        y = self._conv(a, xq, w)
+        if y.t.shape[1] != y.c:  # padded pitch: padding columns hold zeros after the conv; quantise the dense view
+            dense = y.t[:, :y.c]
+            if y.c % 8:
+                raise rt.B200Error("Conv2d_qn_lsq: output channels must be a multiple of 8")
+            y = E.Act(dense.contiguous(), y.n, y.h, y.w, y.c)
+        y.t = self._q_out(y.t, y.n * y.hw * y.c)
+        return y
+
+    def forward(self, x):
+        if not x.is_cuda:
+            raise rt.B200Error("Conv2d_qn_lsq.forward: CUDA tensors required (no CPU implementation in this package)")
+        with torch.autocast("cuda", enabled=False):
+            out = self.forward_act(E.Act.from_nchw(x)).to_nchw()
+        return out.to(x.dtype)
+
+
+class Linear_qn_lsq(nn.Linear, _LsqMixin):
+    def __init__(self, in_features, out_features, weight_bit, input_bit, output_bit, noise_scale, input_quant=True,
+                 output_quant=True, weight_quant=True, gain_noise_scale=0, offset_noise_scale=0, bias=False):
+        super().__init__(in_features, out_features, bias)
+        self._init_lsq(weight_bit, input_bit, output_bit, noise_scale, input_quant, output_quant, weight_quant,
+                       gain_noise_scale, offset_noise_scale)
+
+    def forward_rows(self, rows, act=None):
+        """Engine entry: bf16 rows [M, >= in_features] -> bf16 rows [M, out_features] (act applied after Q_out)."""
+        K, N = self.in_features, self.out_features
+        if self.use_FP:
+            return self._linear(rows, self.weight, act)
+        if K % 8 or N % 8:
+            raise rt.B200Error("Linear_qn_lsq: in/out features must be multiples of 8")
+        x = rows if rows.shape[1] == K else rows[:, :K].contiguous()
+        xq = self._q_in(x, x.shape[0] * K)
+        w, _ = self._w_qn()
+        y = self._linear(xq, w)
+        y = self._q_out(y if y.is_contiguous() else y.contiguous(), y.shape[0] * N)
+        if act is not None:
+            if act != "relu":
+                raise rt.B200Error("Linear_qn_lsq: only ReLU may follow a quantised Linear")
+            y = torch.relu(y) if E.training() else rt.copy_act(y, torch.empty_like(y), 0, act="relu")
+        return y
+
+    def forward(self, x):
+        if not x.is_cuda:
+            raise rt.B200Error("Linear_qn_lsq.forward: CUDA tensors required (no CPU implementation in this package)")
+        lead = x.shape[:-1]
+        with torch.autocast("cuda", enabled=False):
+            rows = x.reshape(-1, x.shape[-1])
+            rows = rows.to(torch.bfloat16) if rows.dtype != torch.bfloat16 else rows
+            if rows.shape[1] % 8:
+                raise rt.B200Error("Linear_qn_lsq: in_features must be a multiple of 8")
+            out = self.forward_rows(rows.contiguous())
+        return out.reshape(*lead, self.out_features).to(x.dtype)

@@ -1,0 +1,229 @@
+"""Drop-in for the reference's cim_layers/layers_qn_lsq_adda_cim.py: `Linear_lsq_adda_cim` / `Conv2d_lsq_adda_cim`,
+the compute-in-memory model of a layer (reference :25-522):
+
+  input  -> LSQ integer codes -> DAC bit slices (signed digits of dac_bit-1 bits)
+  weight -> LSQ integer codes (+ noise proportional to the code range)
+  for every mapped weight block (rows <= array height, `module.weight_mapping_info`):
+      analogue partial sum of each bit slice against the block  ->  ADC: scale, (gain/offset noise), clamp to
+      [-R-1, R], round  ->  slices recombined with weights 2^(k*slice_bit)  ->  accumulated into the output columns
+  output -> / (w_scale * in_scale * adc_scale) + bias -> LSQ output quantiser
+
+Here the digits and weight codes are exact in bf16 and every block product runs on the tcgen05 GEMM with fp32
+accumulation (partial sums are integers < 2^24: exact), so the ADC codes are bit-exact with the reference's fp32
+arithmetic when no weight noise is injected. Step sizes, the ADC gain and its lazy initialisation stay on the device.
+
+Not available yet: the backward pass (progressive quant-noise *training* through ADDA layers) and convolutions other
+than 1x1 (the reference maps k x k kernels through nn.Unfold's (c, ky, kx) row order)."""
+import math
+
+import torch
+import torch.nn as nn
+
+import sdb200  # noqa: F401
+from sdb200 import engine as E
+from sdb200 import ops
+from sdb200 import quant as Q
+from sdb200 import runtime as rt
+from cim_layers.layers_qn_lsq import _LsqMixin
+
+
+def gen_weight_split_dict(module, weight_block_size):
+    """Block list of a layer for an array of `weight_block_size` = [rows, cols] — same keys and fields as the
+    reference mapper produces (cim_weight_mapper/weight_process.py:10-40), for callers that do not run the mapper."""
+    max_rows, max_cols = weight_block_size
+    cols = module.weight.shape[0]
+    rows = module.weight.numel() // cols
+    info = {}
+    for rb in range(rows // max_rows + 1):
+        for cb in range(cols // max_cols + 1):
+            r0, c0 = rb * max_rows, cb * max_cols
+            rn, cn = min(max_rows, rows - r0), min(max_cols, cols - c0)
+            if rn > 0 and cn > 0:
+                info[f"{rb}_{cb}"] = {"start_row": r0, "start_col": c0, "row_num": rn, "col_num": cn}
+    return info
+
+
+class _AddaMixin(_LsqMixin):
+    def _init_adda(self, dac_bit, adc_bit, adc_gain_1_scale, adc_gain_range, adc_adjust_mode, seed):
+        self.dac_bit = dac_bit
+        self.adc_bit = adc_bit
+        self.adc_gain_1_scale = adc_gain_1_scale
+        self.slice_bit = dac_bit - 1
+        self.bit_slices = int(math.ceil((self.input_bit - 1) / self.slice_bit))
+        self.adc_gain_min = float(adc_gain_range[0])
+        self.adc_gain_max = float(adc_gain_range[1])
+        self.adc_gain = nn.Parameter(torch.tensor(self.adc_gain_min))
+        self.adc_adjust_mode = adc_adjust_mode
+        self.seed = seed
+        self._gen_adc_noise()
+
+    def _gen_adc_noise(self):
+        """gen_adc_noise (layers_utils_adda.py:100-105): 1000 gain and offset draws per layer from a generator seeded
+        with `seed` (the reference reseeds the GLOBAL generator here — oracle trap (v); a private generator gives the
+        same numbers without that side effect)."""
+        g = torch.Generator(device=self.weight.device).manual_seed(self.seed)
+        self.gain_noise = torch.randn(1000, device=self.weight.device, generator=g) * self.gain_noise_scale
+        self.offset_noise = torch.randn(1000, device=self.weight.device, generator=g) * self.offset_noise_scale
+
+    def update_para(self, use_FP=False, weight_bit=None, input_bit=None, output_bit=None, noise_scale=None, adc_bit=None,
+                    dac_bit=None, gain_noise_scale=None, offset_noise_scale=None, seed=None):
+        old = (self.weight_bit, self.input_bit, self.output_bit)
+        adc_old, dac_old = self.adc_bit, self.dac_bit
+        self.use_FP = use_FP
+        for name, val in (("weight_bit", weight_bit), ("input_bit", input_bit), ("output_bit", output_bit),
+                          ("adc_bit", adc_bit), ("dac_bit", dac_bit), ("noise_scale", noise_scale),
+                          ("gain_noise_scale", gain_noise_scale), ("offset_noise_scale", offset_noise_scale),
+                          ("seed", seed)):
+            if val is not None:
+                setattr(self, name, val)
+        self._gen_adc_noise()
+        # update_adc_gain (layers_utils_adda.py:52-73): keep the analogue range matched to the new bit widths
+        gain = self.adc_gain.data
+        if adc_old != self.adc_bit:
+            gain = gain * 2 ** (self.adc_bit - adc_old)
+        if dac_old != self.dac_bit:
+            gain = gain / 2 ** (self.dac_bit - dac_old)
+        if old[0] != self.weight_bit:
+            gain = gain / 2 ** (self.weight_bit - old[0])
+        self.adc_gain.data = torch.clamp(gain, min=0.8 * self.adc_gain_min, max=1.2 * self.adc_gain_max)
+        Q.rescale_step_sizes(self, *old)
+        self.slice_bit = self.dac_bit - 1
+        self.bit_slices = int(math.ceil((self.input_bit - 1) / self.slice_bit))
+
+    # ---- ADC parameters -----------------------------------------------------------------------------------------
+    def _adc_scale(self):
+        """get_adc_scale (layers_utils_adda.py:40-49) on the device: clamp (straight-through), round the gain ('gain')
+        or the range 1/gain (other modes), times the scale of gain 1."""
+        g = self.adc_gain
+        gc = torch.clamp(g, self.adc_gain_min, self.adc_gain_max)
+        g = (gc - g).detach() + g
+        if self.adc_adjust_mode == 'gain':
+            g = (torch.round(g) - g).detach() + g
+        else:
+            r = 1 / g
+            g = 1 / ((torch.round(r) - r).detach() + r)
+        return g * self.adc_gain_1_scale
+
+    def _maybe_init_gain(self, partial):
+        """init_adc_gain (layers_utils_adda.py:12-20), fired while adc_gain still equals adc_gain_min and the block
+        product is not all zero — evaluated on the device (the reference compares on the host per block)."""
+        with torch.no_grad():
+            amax = partial.abs().max()
+            ideal = (2 ** (self.adc_bit - 1) - 1) / amax / self.adc_gain_1_scale
+            ideal = torch.clamp(ideal, min=0.8 * self.adc_gain_min, max=1.2 * self.adc_gain_max)
+            fire = (self.adc_gain == self.adc_gain_min) & (amax != 0)
+            self.adc_gain.copy_(torch.where(fire, ideal.to(self.adc_gain.dtype), self.adc_gain))
+
+    def _cim_rows(self, x, w2d, bias, numel_in):
+        """x: bf16 rows [M, K]; w2d: fp32 parameter view [N, K]. Returns bf16 rows [M, N]."""
+        if E.training():
+            raise rt.B200Error("ADDA layers: the backward pass is not available yet (inference / evaluation only)")
+        M, K = x.shape
+        N = w2d.shape[0]
+        R = float(2 ** (self.adc_bit - 1) - 1)
+        if self.input_bit > 9 or self.bit_slices * self.slice_bit > 24:
+            raise rt.B200Error("ADDA layers: input codes wider than 9 bits are not supported")
+        if not self.input_quant:
+            raise rt.B200Error("ADDA layers: the DAC needs quantised inputs (input_quant=True)")
+        qp_in = Q.qp_of(self.input_bit)
+        rt.lsq_init_step(x, self.step_size_input, qp_in)
+        # LSQ codes and their DAC digits in one pass over the activations
+        digits = rt.bit_split(x, self.bit_slices, self.slice_bit, self.input_bit, step=self.step_size_input.detach(),
+                              qp=qp_in, numel=numel_in)
+        w, w_scale = self._w_qn(isint=True)
+        w = w.detach().reshape(N, K)
+        mapping = getattr(self, "weight_mapping_info", None) or {"0_0": {"start_row": 0, "start_col": 0, "row_num": K,
+                                                                          "col_num": N}}
+        noisy = self.gain_noise_scale != 0 or self.offset_noise_scale != 0
+        out = torch.zeros(M, N, device=x.device, dtype=torch.float32)
+        pending = self.__dict__.get("_gain_init_pending", True)
+        for info in mapping.values():
+            r0, rn, c0, cn = info["start_row"], info["row_num"], info["start_col"], info["col_num"]
+            if r0 % 8:
+                raise rt.B200Error("ADDA layers: weight blocks must start at a row multiple of 8")
+            wb = ops.pack_linear_weight(w[c0:c0 + cn, r0:r0 + rn])
+            part = rt.linear(digits[:, r0:r0 + rn], wb, out_dtype=torch.float32)
+            if pending:
+                self._maybe_init_gain(part)
+            alpha = self._adc_scale().detach().float().reshape(1)
+            if noisy and c0 + cn > 1000:
+                raise rt.B200Error("ADDA layers: ADC noise tables hold 1000 columns (layers_utils_adda.py:100-105)")
+            rt.adc_combine(part, out, M, cn, c0, self.bit_slices, self.slice_bit, alpha, R,
+                           self.gain_noise.to(x.device, torch.float32) if noisy else None,
+                           self.offset_noise.to(x.device, torch.float32) if noisy else None)
+        self.__dict__["_gain_init_pending"] = False
+        alpha = self._adc_scale().detach()
+        in_scale = (1.0 / self.step_size_input).detach() if self.input_quant else 1.0
+        y = out / w_scale / in_scale / alpha
+        if bias is not None:
+            y = y + bias.detach().view(1, -1)
+        if self.output_quant:
+            return Q.quantize_rows(y, self.step_size_output, self.output_bit, numel=M * N)
+        return y.to(torch.bfloat16)
+
+    def _load_from_state_dict(self, *a, **k):
+        self.__dict__["_gain_init_pending"] = True
+        return super()._load_from_state_dict(*a, **k)
+
+
+class Linear_lsq_adda_cim(nn.Linear, _AddaMixin):
+    def __init__(self, in_features, out_features, weight_bit, input_bit, output_bit, noise_scale, dac_bit, adc_bit,
+                 adc_gain_1_scale, adc_gain_range, adc_adjust_mode='gain', input_quant=True, output_quant=True,
+                 weight_quant=True, gain_noise_scale=0, offset_noise_scale=0, seed=0, bias=True):
+        super().__init__(in_features, out_features, bias)
+        self._init_lsq(weight_bit, input_bit, output_bit, noise_scale, input_quant, output_quant, weight_quant,
+                       gain_noise_scale, offset_noise_scale)
+        self._init_adda(dac_bit, adc_bit, adc_gain_1_scale, adc_gain_range, adc_adjust_mode, seed)
+
+    def forward_rows(self, rows, act=None):
+        K, N = self.in_features, self.out_features
+        if self.use_FP:
+            return self._linear(rows, self.weight, act)
+        if K % 8 or N % 8:
+            raise rt.B200Error("Linear_lsq_adda_cim: in/out features must be multiples of 8")
+        x = rows if rows.shape[1] == K else rows[:, :K].contiguous()
+        y = self._cim_rows(x, self.weight, self.bias, x.shape[0] * K)
+        if act is not None:
+            if act != "relu":
+                raise rt.B200Error("Linear_lsq_adda_cim: only ReLU may follow a quantised Linear")
+            y = rt.copy_act(y, torch.empty_like(y), 0, act="relu")
+        return y
+
+    def forward(self, x):
+        if not x.is_cuda:
+            raise rt.B200Error("Linear_lsq_adda_cim.forward: CUDA tensors required (no CPU implementation in this package)")
+        lead = x.shape[:-1]
+        with torch.autocast("cuda", enabled=False):
+            rows = x.reshape(-1, x.shape[-1])
+            rows = rows.to(torch.bfloat16) if rows.dtype != torch.bfloat16 else rows
+            out = self.forward_rows(rows.contiguous())
+        return out.reshape(*lead, self.out_features).to(x.dtype)
+
+
+class Conv2d_lsq_adda_cim(nn.Conv2d, _AddaMixin):
+    def __init__(self, in_channels, out_channels, kernel_size, stride, padding, groups, weight_bit, input_bit,
+                 output_bit, noise_scale, dac_bit, adc_bit, adc_gain_1_scale, adc_gain_range, adc_adjust_mode='gain',
+                 input_quant=True, output_quant=True, weight_quant=True, gain_noise_scale=0, offset_noise_scale=0,
+                 seed=0, bias=True):
+        super().__init__(in_channels=in_channels, out_channels=out_channels, kernel_size=kernel_size, stride=stride,
+                         padding=padding, groups=groups, bias=bias)
+        self._init_lsq(weight_bit, input_bit, output_bit, noise_scale, input_quant, output_quant, weight_quant,
+                       gain_noise_scale, offset_noise_scale)
+        self._init_adda(dac_bit, adc_bit, adc_gain_1_scale, adc_gain_range, adc_adjust_mode, seed)
+
+    def forward_act(self, a):
+        if self.use_FP:
+            raise rt.B200Error("Conv2d_lsq_adda_cim: use_FP bypass is served by Conv2d_qn_lsq / nn.Conv2d")
+        if self.kernel_size != (1, 1) or self.stride != (1, 1) or self.padding != (0, 0) or self.groups != 1:
+            raise rt.B200Error("Conv2d_lsq_adda_cim: only 1x1 convolutions have a CUDA path (see module docstring)")
+        if a.c % 8 or a.t.shape[1] != a.c or self.out_channels % 8:
+            raise rt.B200Error("Conv2d_lsq_adda_cim: channels must be multiples of 8 and densely packed")
+        y = self._cim_rows(a.t, self.weight.reshape(self.out_channels, -1), self.bias, a.n * a.hw * a.c)
+        return E.Act(y, a.n, a.h, a.w, self.out_channels)
+
+    def forward(self, x):
+        if not x.is_cuda:
+            raise rt.B200Error("Conv2d_lsq_adda_cim.forward: CUDA tensors required (no CPU implementation in this package)")
+        with torch.autocast("cuda", enabled=False):
+            out = self.forward_act(E.Act.from_nchw(x)).to_nchw()
+        return out.to(x.dtype)

@@ -269,6 +269,46 @@ int b200sd_unpatchify(const void* tokens, int32_t tokens_f32, int64_t ld, float*
 int b200sd_patchify(const float* image, void* tokens, int64_t ld, int64_t n, int32_t channels, int32_t grid_h,
                     int32_t grid_w, int32_t patch_h, int32_t patch_w, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * cim_layers quantisers on activations (csrc/quant.cu). Step sizes / ADC scale are read through device pointers
+ * (they are nn.Parameters): no host synchronisation. Tensors are [rows, c] with pitch ld (c, ld multiples of 8),
+ * bf16 or fp32 as flagged. Codes are bit-exact with the reference's fp32 torch ops on identical inputs.
+ * ------------------------------------------------------------------------------------------------------------- */
+
+/* Lazy LSQ step-size initialisation (cim_layers/layers_utils_lsq.py:31-34,40-42,57-59,74-76): while *step == 1.0,
+ * *step = 1 / (1 / max|x| * qp). scratch: one uint32 of device memory. */
+int b200sd_lsq_init_step(const void* x, int32_t x_f32, int64_t ld_x, int64_t rows, int32_t c, float* step, float qp,
+                         uint32_t* scratch, void* stream);
+
+/* data_quant_lsq (cim_layers/quant_noise_utils.py:101-120) with s' = the VALUE of grad_scale(s, grad_scale) =
+ * fl(fl(s - s*g) + s*g), g = 1/sqrt(qp * numel) (:51-58): mode 0 -> round(clamp(x / s', -qp, qp)) * s' (isint=False),
+ * mode 1 -> that code times s' / s' (isint=True, :117-118 — an integer up to the reference's own final rounding). */
+int b200sd_lsq_quant(const void* x, int32_t x_f32, int64_t ld_x, void* y, int32_t y_f32, int64_t ld_y, int64_t rows,
+                     int32_t c, const float* step, float qp, float grad_scale, int32_t mode, void* stream);
+
+/* Its backward (straight-through round, clamp mask, LSQ step-size gradient): dx bf16; part[b200sd_lsq_quant_bwd_blocks()]
+ * = fp32 partial sums of d(step) before the 1/sqrt(qp * numel) gradient scale (quant_noise_utils.py:51-58). */
+int b200sd_lsq_quant_bwd(const void* dy, int64_t ld_dy, const void* x, int32_t x_f32, int64_t ld_x, void* dx,
+                         int64_t ld_dx, int64_t rows, int32_t c, const float* step, float qp, float grad_scale,
+                         int32_t mode, float* part, void* stream);
+int b200sd_lsq_quant_bwd_blocks(int64_t rows, int32_t c);
+
+/* bit_split_tensor (cim_layers/layers_utils_adda.py:161-185): codes [rows, c] -> `slices` signed digits of slice_bit
+ * bits stacked along rows, bf16 [slices * rows, c] — the DAC input slices. step == NULL: x holds the codes (bf16 or
+ * fp32); step != NULL: x holds activations and the LSQ code (mode 1 above, with qp / grad_scale) is computed in the
+ * same pass, so the fp32 codes never travel through HBM. */
+int b200sd_bit_split(const void* x, int32_t x_f32, int64_t ld_x, void* digits, int64_t ld_o, int64_t rows, int32_t c,
+                     int32_t slices, int32_t slice_bit, int32_t x_bit, const float* step, float qp, float grad_scale,
+                     void* stream);
+
+/* ADC + bit_concat of one mapped weight block (cim_layers/layers_qn_lsq_adda_cim.py:464-480,
+ * layers_utils_adda.py:108-116,144-159): partial = fp32 [slices * rows, ncol] analogue sums of the block;
+ * out[r, col0 + j] (+)= sum_k 2^(k * slice_bit) * round(clamp(scale * partial_k * (1 + gain[col0 + j])
+ *                                                          + range * offset[col0 + j], -range - 1, range)). */
+int b200sd_adc_combine(const float* partial, int64_t ld_p, float* out, int64_t ld_o, int64_t rows, int32_t ncol,
+                       int32_t col0, int32_t slices, int32_t slice_bit, const float* adc_scale, float adc_range,
+                       const float* gain_noise, const float* offset_noise, int32_t accumulate, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

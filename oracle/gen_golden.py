@@ -152,7 +152,119 @@ def gen_dit():
     return ok
 
 
+LSQ_CFG = dict(weight_bit=4, input_bit=8, output_bit=8, noise_scale=0.08)                       # Model_DiT_9L_train.py:541-548
+ADDA_CFG = dict(LSQ_CFG, dac_bit=5, adc_bit=8, adc_gain_1_scale=9.071428571, adc_gain_range=[1 / 64, 1 / 64],
+                adc_adjust_mode='current')                                                       # :578-590
+
+
+def gen_cim():
+    """cim_layers fixtures: the real reference layers on seeded inputs, weight noise injected (trap iv)."""
+    from unittest.mock import MagicMock
+    for mod in ("onnx", "onnx.shape_inference", "onnx.numpy_helper", "matplotlib", "matplotlib.pyplot"):
+        sys.modules.setdefault(mod, MagicMock())   # absent here; only plotting / export helpers of the mapper use them
+    sys.path.insert(0, REF)
+    from cim_layers.layers_qn_lsq import Conv2d_qn_lsq as RConv, Linear_qn_lsq as RLin
+    from cim_layers.layers_qn_lsq_adda_cim import Linear_lsq_adda_cim as RAdda
+    from cim_weight_mapper.weight_process import gen_weight_split_dict
+    sys.path.pop(0)
+    O = _load(os.path.join(ROOT, "oracle", "cim_torch.py"), "oracle_cim_torch")
+    ok = True
+    out = {}
+    real_randn_like = torch.randn_like
+
+    def run(layer, x, unit):
+        torch.randn_like = lambda t, **k: unit.to(t)       # the ONLY randn_like on the path is the weight noise
+        try:
+            return layer(x)
+        finally:
+            torch.randn_like = real_randn_like
+
+    def params_of(layer):
+        return {k: v.detach().clone() for k, v in layer.state_dict().items()}
+
+    g = torch.Generator().manual_seed(1111)
+    # ---- Linear_qn_lsq: DiT MLP shape, two forwards (first one initialises the step sizes)
+    for name, mk, x, conv in [
+        ("lsq_linear", lambda: RLin(288, 192, bias=True, **LSQ_CFG), torch.randn(2, 32, 288, generator=g), None),
+        ("lsq_linear_clean", lambda: RLin(96, 64, bias=False, **dict(LSQ_CFG, noise_scale=0)),
+         torch.randn(48, 96, generator=g) * 3, None),
+        ("lsq_conv3x3", lambda: RConv(32, 64, 3, 1, 1, 1, bias=True, **LSQ_CFG), torch.randn(2, 32, 16, 16, generator=g),
+         dict(stride=1, padding=1)),
+        ("lsq_conv1x1", lambda: RConv(64, 32, 1, 1, 0, 1, bias=True, **dict(LSQ_CFG, weight_bit=8)),
+         torch.randn(2, 64, 8, 8, generator=g), dict(stride=1, padding=0)),
+    ]:
+        torch.manual_seed(5)
+        layer = mk()
+        init = params_of(layer)
+        unit = torch.randn(layer.weight.shape, generator=g).to(torch.float16).float()   # stored as fp16: keep it exact
+        x2 = torch.randn(x.shape, generator=g) * 1.3
+        with torch.no_grad():
+            y1 = run(layer, x, unit)
+        after = params_of(layer)
+        layer.zero_grad()
+        y2 = run(layer, x2, unit)
+        tgt = torch.randn(y2.shape, generator=g)
+        ((y2 - tgt) ** 2).mean().backward()
+        grads = {k: v.grad.detach().clone() for k, v in layer.named_parameters() if v.grad is not None}
+        cfg = dict(LSQ_CFG, weight_bit=layer.weight_bit, noise_scale=layer.noise_scale)
+        p = {k: v.clone() for k, v in init.items()}
+        with torch.no_grad():
+            o1 = O.lsq_layer(p, cfg, x, unit, conv)
+        e1 = (o1 - y1).abs().max().item()
+        ep = max((p[k] - after[k]).abs().max().item() for k in after)
+        p2 = {k: v.clone().requires_grad_(True) for k, v in after.items()}
+        assert all(torch.equal(after[k], init[k]) for k in after if after[k].dim() > 0)
+        o2 = O.lsq_layer(p2, cfg, x2, unit, conv)
+        ((o2 - tgt) ** 2).mean().backward()
+        eg = max(((p2[k].grad - grads[k]).abs().max() / grads[k].abs().max().clamp_min(1e-20)).item() for k in grads)
+        print(f"cim {name}: oracle-vs-ref out {e1:.1e} lazy-init params {ep:.1e} second forward {(o2 - y2).abs().max().item():.1e} grads {eg:.1e}")
+        ok &= e1 == 0 and ep == 0 and (o2 - y2).abs().max().item() == 0 and eg < 1e-5
+        out[name] = {"cfg": cfg, "conv": conv, "init": init, "after": {k: v for k, v in after.items() if v.dim() == 0},
+                     "x": x, "x2": x2, "unit": unit.to(torch.float16), "y1": y1, "y2": y2.detach(), "target": tgt,
+                     "grads": grads}
+
+    # ---- Linear_lsq_adda_cim: one and two row blocks (array height 576), with and without ADC noise
+    for name, (K, N), extra, block in [("adda_linear_288", (288, 160), {}, [576, 2048]),
+                                       ("adda_linear_1152", (1152, 96), {}, [576, 2048]),
+                                       ("adda_linear_noise", (192, 96), dict(gain_noise_scale=0.02, offset_noise_scale=0.01,
+                                                                             noise_scale=0.0), [64, 40])]:
+        cfgk = dict(ADDA_CFG, **extra)
+        torch.manual_seed(9)
+        layer = RAdda(K, N, bias=True, **cfgk)
+        layer.weight_mapping_info = gen_weight_split_dict(layer, block)
+        init = params_of(layer)
+        unit = torch.randn(layer.weight.shape, generator=g).to(torch.float16).float()
+        x = torch.randn(2, 32, K, generator=g)
+        x2 = torch.randn(2, 32, K, generator=g) * 0.7
+        with torch.no_grad():
+            y1 = run(layer, x, unit)
+            after = params_of(layer)
+            y2 = run(layer, x2, unit)
+        c = dict(cfgk, adc_gain_min=layer.adc_gain_min, adc_gain_max=layer.adc_gain_max)
+        p = {k: v.clone() for k, v in init.items()}
+        noise = dict(gain_noise=layer.gain_noise, offset_noise=layer.offset_noise) if extra else {}
+        with torch.no_grad():
+            o1 = O.adda_linear(p, c, x, layer.weight_mapping_info, unit, **noise)
+            ep = max((p[k] - after[k]).abs().max().item() for k in after)
+            o2 = O.adda_linear(p, c, x2, layer.weight_mapping_info, unit, **noise)
+        e1, e2 = (o1 - y1).abs().max().item(), (o2 - y2).abs().max().item()
+        print(f"cim {name}: oracle-vs-ref out {e1:.1e} lazy-init params {ep:.1e} second forward {e2:.1e} "
+              f"blocks {len(layer.weight_mapping_info)} adc_gain {after['adc_gain'].item():.6f}")
+        ok &= e1 == 0 and ep == 0 and e2 == 0
+        out[name] = {"cfg": {k: v for k, v in c.items()}, "mapping": layer.weight_mapping_info, "init": init,
+                     "after": {k: v for k, v in after.items() if v.dim() == 0}, "x": x, "x2": x2,
+                     "unit": unit.to(torch.float16), "y1": y1, "y2": y2,
+                     "gain_noise": layer.gain_noise.clone(), "offset_noise": layer.offset_noise.clone()}
+    torch.save(out, os.path.join(GOLD, "cim_layers.pt"))
+    return ok
+
+
 def main():
+    if "--only-cim" in sys.argv:
+        if not gen_cim():
+            print("ORACLE DISAGREES WITH THE REFERENCE")
+            sys.exit(1)
+        return
     if "--only-dit" in sys.argv:
         if not gen_dit():
             print("ORACLE DISAGREES WITH THE REFERENCE")
@@ -242,6 +354,7 @@ def main():
     np.savez_compressed(os.path.join(GOLD, "scheduler.npz"), **fx)
     print("scheduler fixtures written")
     ok &= gen_dit()
+    ok &= gen_cim()
     if not ok:
         print("ORACLE DISAGREES WITH THE REFERENCE")
         sys.exit(1)

@@ -235,8 +235,26 @@ def conv_transpose2d(a, mod, out=None, c_off=0):
 def linear(x, mod, act=None, residual=None, out_dtype=torch.bfloat16, rows_per_img=None, rowbias=None, gate=None,
            stats=None):
     """nn.Linear leaf on a 2-D bf16 matrix."""
-    if hasattr(mod, "forward_rows") and residual is None and gate is None and rowbias is None:
-        return mod.forward_rows(x, act=act)
+    if hasattr(mod, "forward_rows"):
+        # quantised leaf (cim_layers drop-ins): its own CUDA path produces the layer output; what the float path fuses
+        # into the GEMM epilogue is applied afterwards
+        if rowbias is not None or stats is not None or out_dtype != torch.bfloat16:
+            raise rt.B200Error("Linear: this epilogue combination is not available around a quantised leaf")
+        y = mod.forward_rows(x, act=act)
+        if gate is not None:
+            if residual is None or rows_per_img is None:
+                raise rt.B200Error("Linear: a gate needs its residual and rows_per_img")
+            n = y.shape[0] // rows_per_img
+            if training():
+                return AG.GateResidualFn.apply(residual, y, gate, (n, rows_per_img, y.shape[1]))
+            return rt.gate_residual(residual, y, gate, n, rows_per_img, y.shape[1])
+        if residual is not None:
+            if training():
+                return residual[:, :y.shape[1]] + y
+            out = torch.empty_like(y)
+            rt.add_bf16(residual if residual.shape[1] == y.shape[1] else residual[:, :y.shape[1]].contiguous(), y, out)
+            return out
+        return y
     _require_leaf(mod, (nn.Linear, nn.modules.linear.NonDynamicallyQuantizableLinear), "Linear")
     if training() and act in (None, "relu") and gate is None and rowbias is None and out_dtype == torch.bfloat16:
         o, st = AG.LinearFn.apply(x, mod.weight, mod.bias, residual, rows_per_img, stats is not None, act)
@@ -540,11 +558,32 @@ def dit_self_attention(xn, attn, n, L):
     return rt.attention(qkv[:, :A], qkv[:, A:2 * A], qkv[:, 2 * A:], n, heads, L, L, d)
 
 
+def _plain_projections(mha):
+    return all(type(getattr(mha, k, None)) is nn.Linear for k in ("q_proj", "k_proj", "v_proj", "out_proj")) \
+        or isinstance(mha, nn.MultiheadAttention)
+
+
+def _cross_attention_leafwise(xn, x, mha, ctx_proj_mod, ctx, n, L):
+    """Cross-attention whose projections are separate (possibly quantised) leaves — CustomMultiheadAttention exists for
+    exactly this (models/multihead_attention.py:34-37): each projection runs through its own leaf."""
+    C, heads = mha.embed_dim, mha.num_heads
+    q = linear(xn, mha.q_proj)
+    cp = linear(ctx.t, ctx_proj_mod)
+    kv = torch.cat([linear(cp, mha.k_proj), linear(cp, mha.v_proj)], dim=1)
+    if training():
+        o = AG.AttentionFn.apply(q, kv, (n, heads, L, ctx.lk, C // heads))
+    else:
+        o = rt.attention(q, kv[:, :C], kv[:, C:], n, heads, L, ctx.lk, C // heads)
+    return linear(o, mha.out_proj, residual=x)
+
+
 def dit_cross_attention(x, norm, mha, ctx_proj_mod, ctx, n, L):
     """x + out_proj(MHA(q = LN(x), k = v = context_proj(context))) — transformer_layer.py:92-101 (un-gated). The K/V of
     a site depend only on the context and the weights: a persistent Context keeps them across sampling steps."""
     C, heads = mha.embed_dim, mha.num_heads
     xn = layer_norm_mod(x, norm, n, L)
+    if not _plain_projections(mha) or type(ctx_proj_mod) is not nn.Linear:
+        return _cross_attention_leafwise(xn, x, mha, ctx_proj_mod, ctx, n, L)
     if training():
         w, b = _mha_params(mha)
         q, _ = AG.LinearFn.apply(xn, w[:C], None if b is None else b[:C], None, None, False)

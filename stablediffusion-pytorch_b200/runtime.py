@@ -22,6 +22,8 @@ EXPORTS = [
     "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16",
     "b200sd_layernorm_mod", "b200sd_layernorm_mod_bwd", "b200sd_rows_per_slot", "b200sd_gate_residual",
     "b200sd_gate_residual_bwd", "b200sd_relu_bwd", "b200sd_unpatchify", "b200sd_patchify",
+    "b200sd_lsq_init_step", "b200sd_lsq_quant", "b200sd_lsq_quant_bwd", "b200sd_lsq_quant_bwd_blocks", "b200sd_bit_split",
+    "b200sd_adc_combine",
 ]
 
 
@@ -110,6 +112,12 @@ def lib():
         L.b200sd_relu_bwd.argtypes = [vp, i64, vp, i64, vp, i64, i64, i32, vp]
         L.b200sd_unpatchify.argtypes = [vp, i32, i64, vp, i64, i32, i32, i32, i32, i32, vp]
         L.b200sd_patchify.argtypes = [vp, vp, i64, i64, i32, i32, i32, i32, i32, vp]
+        L.b200sd_lsq_init_step.argtypes = [vp, i32, i64, i64, i32, vp, f32, vp, vp]
+        L.b200sd_lsq_quant.argtypes = [vp, i32, i64, vp, i32, i64, i64, i32, vp, f32, f32, i32, vp]
+        L.b200sd_lsq_quant_bwd.argtypes = [vp, i64, vp, i32, i64, vp, i64, i64, i32, vp, f32, f32, i32, vp, vp]
+        L.b200sd_lsq_quant_bwd_blocks.argtypes = [i64, i32]
+        L.b200sd_bit_split.argtypes = [vp, i32, i64, vp, i64, i64, i32, i32, i32, i32, vp, f32, f32, vp]
+        L.b200sd_adc_combine.argtypes = [vp, i64, vp, i64, i64, i32, i32, i32, i32, vp, f32, vp, vp, i32, vp]
         _lib = L
     return _lib
 
@@ -614,3 +622,73 @@ def patchify(img, ph, pw, ld=None):
     tok = torch.empty(n * gh * gw, ld, device=img.device, dtype=torch.bfloat16)
     check(lib().b200sd_patchify(_p(img), _p(tok), ld, n, ch, gh, gw, ph, pw, stream_ptr()), "patchify")
     return tok
+
+
+# ------------------------------------------------------------------------------------------------ cim_layers quantisers
+def _rows2d(x):
+    if x.dim() != 2 or x.stride(1) != 1 or x.shape[1] % 8 or x.stride(0) % 8 or x.dtype not in (torch.bfloat16, torch.float32):
+        raise B200Error("quantiser: [rows, c] bf16/fp32 rows with c and pitch multiples of 8 required")
+    if not x.is_cuda:
+        raise B200Error("quantiser: CUDA tensors required (this path has no CPU implementation)")
+    return x
+
+
+def lsq_init_step(x, step, qp):
+    """Device-side `if step_size == 1: step_size = init_step_size(x, bit)` (layers_utils_lsq.py:40-42)."""
+    _rows2d(x)
+    scratch = torch.empty(1, device=x.device, dtype=torch.int32)
+    check(lib().b200sd_lsq_init_step(_p(x), int(x.dtype == torch.float32), x.stride(0), x.shape[0], x.shape[1],
+                                     step.data_ptr(), float(qp), _p(scratch), stream_ptr()), "lsq_init_step")
+
+
+def lsq_grad_scale(qp, numel):
+    """grad_scale_factor (quant_noise_utils.py:57-58); also fixes the value of the step the reference quantises with."""
+    return 1.0 / ((qp * numel) ** 0.5)
+
+
+def lsq_quant(x, step, qp, codes=False, out_dtype=torch.bfloat16, numel=None):
+    """Fake-quantised values (codes=False) or codes (codes=True) of [rows, c] activations; numel = element count of the
+    reference tensor (padding columns excluded) — it enters the effective step through the LSQ gradient scale."""
+    _rows2d(x)
+    numel = x.shape[0] * x.shape[1] if numel is None else numel
+    y = torch.empty(x.shape[0], x.shape[1], device=x.device, dtype=out_dtype)
+    check(lib().b200sd_lsq_quant(_p(x), int(x.dtype == torch.float32), x.stride(0), _p(y), int(out_dtype == torch.float32),
+                                 y.stride(0), x.shape[0], x.shape[1], step.data_ptr(), float(qp),
+                                 lsq_grad_scale(qp, numel), 1 if codes else 0, stream_ptr()), "lsq_quant")
+    return y
+
+
+def lsq_quant_bwd(dy, x, step, qp, codes=False, numel=None):
+    """-> (dx bf16, d(step) fp32 0-dim, already multiplied by the LSQ gradient scale 1/sqrt(qp * numel))."""
+    _rows2d(x)
+    rows, c = x.shape
+    numel = rows * c if numel is None else numel
+    g = lsq_grad_scale(qp, numel)
+    dx = torch.empty(rows, c, device=x.device, dtype=torch.bfloat16)
+    nb = int(lib().b200sd_lsq_quant_bwd_blocks(rows, c))
+    part = torch.empty(nb, device=x.device, dtype=torch.float32)
+    check(lib().b200sd_lsq_quant_bwd(_p(dy), dy.stride(0), _p(x), int(x.dtype == torch.float32), x.stride(0), _p(dx), c,
+                                     rows, c, step.data_ptr(), float(qp), g, 1 if codes else 0, _p(part), stream_ptr()),
+          "lsq_quant_bwd")
+    ds = reduce_f32(part, 1, nb, 1, 1, torch.empty(1, device=x.device, dtype=torch.float32))
+    return dx, (ds * g).reshape(())
+
+
+def bit_split(x, slices, slice_bit, x_bit, step=None, qp=0.0, numel=None):
+    """DAC digits bf16 [slices * rows, c] of codes `x` (step None) or of activations `x` quantised on the fly."""
+    _rows2d(x)
+    rows, c = x.shape
+    out = torch.empty(slices * rows, c, device=x.device, dtype=torch.bfloat16)
+    g = 0.0 if step is None else lsq_grad_scale(qp, rows * c if numel is None else numel)
+    check(lib().b200sd_bit_split(_p(x), int(x.dtype == torch.float32), x.stride(0), _p(out), c, rows, c, slices, slice_bit,
+                                 x_bit, None if step is None else step.data_ptr(), float(qp), g, stream_ptr()),
+          "bit_split")
+    return out
+
+
+def adc_combine(partial, out, rows, ncol, col0, slices, slice_bit, adc_scale, adc_range, gain_noise=None,
+                offset_noise=None, accumulate=True):
+    check(lib().b200sd_adc_combine(_p(partial), partial.stride(0), _p(out), out.stride(0), rows, ncol, col0, slices,
+                                   slice_bit, adc_scale.data_ptr(), float(adc_range), _p(gain_noise), _p(offset_noise),
+                                   1 if accumulate else 0, stream_ptr()), "adc_combine")
+    return out

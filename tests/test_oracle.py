@@ -76,3 +76,35 @@ def test_dit_oracle_vs_reference_golden(name):
     assert relerr(out, fx["output"]) < 1e-5
     assert relerr(out_s, fx["output_scalar_t"]) < 1e-5
     assert fx["output"].abs().max() > 0.1  # not the vacuous all-zero default-init output
+
+
+def test_cim_oracle_vs_reference_golden():
+    """cim_layers restatement against the committed outputs of the real reference layers: outputs of two forwards,
+    the lazily initialised step sizes / ADC gain, and (LSQ layers) the parameter gradients — all exactly."""
+    from oracle import cim_torch as OC
+    fx = load_golden("cim_layers")
+    for name, f in fx.items():
+        unit = f["unit"].float()
+        p = {k: v.clone() for k, v in f["init"].items()}
+        if name.startswith("lsq"):
+            with torch.no_grad():
+                y1 = OC.lsq_layer(p, f["cfg"], f["x"], unit, f["conv"])
+            assert torch.equal(y1, f["y1"]), name
+            for k, v in f["after"].items():
+                assert torch.equal(p[k], v), (name, k)
+            p2 = {k: v.clone().requires_grad_(True) for k, v in p.items()}
+            y2 = OC.lsq_layer(p2, f["cfg"], f["x2"], unit, f["conv"])
+            assert torch.equal(y2.detach(), f["y2"]), name
+            ((y2 - f["target"]) ** 2).mean().backward()
+            for k, g in f["grads"].items():
+                assert relerr(p2[k].grad, g) < 1e-5, (name, k)
+        else:
+            noise = {}
+            if f["cfg"].get("gain_noise_scale"):
+                noise = dict(gain_noise=f["gain_noise"], offset_noise=f["offset_noise"])
+            with torch.no_grad():
+                y1 = OC.adda_linear(p, f["cfg"], f["x"], f["mapping"], unit, **noise)
+                for k, v in f["after"].items():
+                    assert torch.equal(p[k], v), (name, k)
+                y2 = OC.adda_linear(p, f["cfg"], f["x2"], f["mapping"], unit, **noise)
+            assert torch.equal(y1, f["y1"]) and torch.equal(y2, f["y2"]), name
