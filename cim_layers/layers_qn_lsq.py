@@ -116,20 +116,23 @@ class Conv2d_qn_lsq(nn.Conv2d, _LsqMixin):
         return o
 
     def forward_act(self, a):
-        """Engine entry: NHWC bf16 Act -> Act."""
+        """Engine entry: NHWC bf16 Act -> Act. Channel counts that are not multiples of 8 (the DiT mask conv: 18 -> 3)
+        travel in zero-padded rows; zeros quantise to code 0 and do not move the lazily initialised step sizes."""
         if self.use_FP:
             return self._conv(a, a.t, self.weight)
-        if a.c % 8 or a.t.shape[1] != a.c:
-            raise rt.B200Error("Conv2d_qn_lsq: input channels must be a multiple of 8 and densely packed")
+        cp = (a.c + 7) // 8 * 8
+        if a.t.shape[1] != cp:
+            raise rt.B200Error("Conv2d_qn_lsq: input rows must be packed to the channel count rounded up to 8")
         xq = self._q_in(a.t, a.n * a.hw * a.c)
         w, _ = self._w_qn()
         y = self._conv(a, xq, w)
-        if y.t.shape[1] != y.c:  # padded pitch: padding columns hold zeros after the conv; quantise the dense view
-            dense = y.t[:, :y.c]
-            if y.c % 8:
-                raise rt.B200Error("Conv2d_qn_lsq: output channels must be a multiple of 8")
-            y = E.Act(dense.contiguous(), y.n, y.h, y.w, y.c)
-        y.t = self._q_out(y.t, y.n * y.hw * y.c)
+        op = (y.c + 7) // 8 * 8
+        t = y.t
+        if y.c % 8:  # the GEMM leaves the padding columns of its output unwritten: make them zeros
+            t = torch.nn.functional.pad(t[:, :y.c], (0, op - y.c))
+        elif t.shape[1] != op or not t.is_contiguous():
+            t = t[:, :op].contiguous()
+        y = E.Act(self._q_out(t, y.n * y.hw * y.c), y.n, y.h, y.w, y.c)
         return y
 
     def forward(self, x):
@@ -148,22 +151,31 @@ class Linear_qn_lsq(nn.Linear, _LsqMixin):
                        gain_noise_scale, offset_noise_scale)
 
     def forward_rows(self, rows, act=None):
-        """Engine entry: bf16 rows [M, >= in_features] -> bf16 rows [M, out_features] (act applied after Q_out)."""
+        """Engine entry: bf16 rows [M, >= in_features] -> bf16 rows [M, out_features] (act applied after Q_out).
+        in_features that are not a multiple of 8 (the DiT patch embedding: 28) are served on rows zero-padded to the
+        next multiple of 8: zeros quantise to code 0 and meet zero weight columns."""
         K, N = self.in_features, self.out_features
         if self.use_FP:
-            return self._linear(rows, self.weight, act)
-        if K % 8 or N % 8:
-            raise rt.B200Error("Linear_qn_lsq: in/out features must be multiples of 8")
-        x = rows if rows.shape[1] == K else rows[:, :K].contiguous()
+            return self._linear(rows if rows.shape[1] == K or K % 8 else rows[:, :K].contiguous(), self._pad_k(self.weight), act)
+        if N % 8:
+            raise rt.B200Error("Linear_qn_lsq: out_features must be a multiple of 8")
+        Kp = (K + 7) // 8 * 8
+        if rows.shape[1] < Kp:
+            raise rt.B200Error("Linear_qn_lsq: input rows narrower than in_features rounded up to 8")
+        x = rows if rows.shape[1] == Kp else rows[:, :Kp].contiguous()
         xq = self._q_in(x, x.shape[0] * K)
         w, _ = self._w_qn()
-        y = self._linear(xq, w)
+        y = self._linear(xq, self._pad_k(w))
         y = self._q_out(y if y.is_contiguous() else y.contiguous(), y.shape[0] * N)
         if act is not None:
             if act != "relu":
                 raise rt.B200Error("Linear_qn_lsq: only ReLU may follow a quantised Linear")
             y = torch.relu(y) if E.training() else rt.copy_act(y, torch.empty_like(y), 0, act="relu")
         return y
+
+    def _pad_k(self, w):
+        K = self.in_features
+        return w if K % 8 == 0 else torch.nn.functional.pad(w, (0, (K + 7) // 8 * 8 - K))
 
     def forward(self, x):
         if not x.is_cuda:
@@ -173,6 +185,6 @@ class Linear_qn_lsq(nn.Linear, _LsqMixin):
             rows = x.reshape(-1, x.shape[-1])
             rows = rows.to(torch.bfloat16) if rows.dtype != torch.bfloat16 else rows
             if rows.shape[1] % 8:
-                raise rt.B200Error("Linear_qn_lsq: in_features must be a multiple of 8")
+                rows = torch.nn.functional.pad(rows, (0, 8 - rows.shape[1] % 8))
             out = self.forward_rows(rows.contiguous())
         return out.reshape(*lead, self.out_features).to(x.dtype)

@@ -120,9 +120,20 @@ class DIT(Denoiser):
             mask = cond_input['image']
             assert mask.shape[0] == n, "Batch size mismatch of image condition and input"
             assert mask.shape[2] % h == 0, "Height/Width of image condition must be divisible by latent input"
-            if type(self.cond_conv_in) is not nn.Conv2d:
-                raise rt.B200Error("cond_conv_in: quantised leaf on the mask path is not supported yet")
-            if E.training() and self.cond_conv_in.weight.requires_grad:
+            if hasattr(self.cond_conv_in, "forward_act"):
+                # quantised mask conv (cim_layers drop-in): nearest resize by index (F.interpolate 'nearest' picks
+                # floor(dst * in / out)), the leaf's own CUDA path, then the result goes into the trailing channels
+                mh, mw = mask.shape[2], mask.shape[3]
+                iy = torch.clamp((torch.arange(h, device=device, dtype=torch.float32) * (mh / h)).floor().long(), max=mh - 1)
+                ix = torch.clamp((torch.arange(w, device=device, dtype=torch.float32) * (mw / w)).floor().long(), max=mw - 1)
+                small = mask.float()[:, :, iy][:, :, :, ix]
+                im = self.cond_conv_in.forward_act(E.Act.from_nchw(small))
+                pad = torch.nn.functional.pad(im.t[:, :self.im_cond_output_ch],
+                                              (c, ld - c - self.im_cond_output_ch))
+                buf = buf + pad if E.training() else buf.add_(pad)
+            elif type(self.cond_conv_in) is not nn.Conv2d:
+                raise rt.B200Error(f"cond_conv_in: no CUDA path for leaf of type {type(self.cond_conv_in).__name__}")
+            elif E.training() and self.cond_conv_in.weight.requires_grad:
                 buf = AG.MaskCondFn.apply(self.cond_conv_in.weight, mask, buf, c, h, w)
             else:
                 rt.mask_cond(mask.float(), self.cond_conv_in.weight.detach().float().reshape(self.im_cond_output_ch, -1),

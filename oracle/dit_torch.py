@@ -34,7 +34,14 @@ def position_embedding(dim, gh, gw):
     return torch.cat([torch.sin(ey), torch.cos(ey), torch.sin(ex), torch.cos(ex)], dim=-1)
 
 
+# Optional leaf hook: LEAF(name, x, weight, bias, conv) -> y replaces every nn.Linear / the mask nn.Conv2d — how the
+# reference's module surgery (cim_qn_train/progressive_qn_train.py:576-651) swaps in cim_layers drop-ins.
+LEAF = None
+
+
 def _lin(sd, name, x):
+    if LEAF is not None:
+        return LEAF(name, x, sd[name + ".weight"], sd.get(name + ".bias"), None)
     return F.linear(x, sd[name + ".weight"], sd.get(name + ".bias"))
 
 
@@ -80,7 +87,11 @@ def dit_forward(state_dict, cfg, x, t, cond_input=None):
     src = x
     if "cond_conv_in.weight" in sd:
         im = F.interpolate(cond_input['image'].to(x.dtype), size=(H, W))
-        src = torch.cat([x, F.conv2d(im, sd["cond_conv_in.weight"])], dim=1)
+        if LEAF is not None:
+            imc = LEAF("cond_conv_in", im, sd["cond_conv_in.weight"], None, dict(stride=1, padding=0))
+        else:
+            imc = F.conv2d(im, sd["cond_conv_in.weight"])
+        src = torch.cat([x, imc], dim=1)
     gh, gw = H // p, W // p
     cin = src.shape[1]
     tok = src.reshape(b, cin, gh, p, gw, p).permute(0, 2, 4, 3, 5, 1).reshape(b, gh * gw, p * p * cin)

@@ -606,6 +606,19 @@ def dit_cross_attention(x, norm, mha, ctx_proj_mod, ctx, n, L):
 
 def patch_embed(xbuf, n, H, W, cin, p, mod, pos):
     """PatchEmbedding.patch_embed[0] on the NHWC input buffer (+ position embedding) — patch_embed.py:84-95."""
+    if hasattr(mod, "forward_rows"):
+        # quantised leaf: its input quantiser needs the folded patches as rows (layout glue on an 8-channel tensor)
+        gh, gw, ld = H // p, W // p, xbuf.stride(0)
+        tok = xbuf.reshape(n, gh, p, gw, p, ld)[..., :cin].permute(0, 1, 3, 2, 4, 5).reshape(n * gh * gw, p * p * cin)
+        kp = (p * p * cin + 7) // 8 * 8
+        tok = torch.nn.functional.pad(tok, (0, kp - p * p * cin))
+        y = mod.forward_rows(tok)
+        pos_all = pos.repeat(n, 1)
+        if training():
+            return y + pos_all
+        out = torch.empty_like(y)
+        rt.add_bf16(y, pos_all, out)
+        return out
     _require_leaf(mod, (nn.Linear,), "Linear(patch_embed)")
     if p * p > 4:
         raise rt.B200Error("patch embedding: patch sizes above 2 are not supported")

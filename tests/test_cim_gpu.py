@@ -253,3 +253,94 @@ def test_adda_linear_vs_oracle(name):
             # by one on some boundaries and the upper DAC slice carries weight 16
             assert dcode.max().item() <= 3 and same > 0.7
     assert relerr(out1.cpu(), f["y1"]) < 5e-2                            # vs the reference on the un-rounded inputs
+
+
+# --------------------------------------------------------------------------------------------------- inside the DiT
+def _convert(model, lin_cls, conv_cls, **kw):
+    """What cim_qn_train/progressive_qn_train.py:576-651 does: every leaf of EXACT type nn.Linear / nn.Conv2d is
+    replaced by the quantised class sharing its weight / bias Parameters."""
+    import torch.nn as nn
+    for parent in list(model.modules()):
+        for name, m in list(parent.named_children()):
+            new = None
+            if type(m) is nn.Linear:
+                new = lin_cls(m.in_features, m.out_features, bias=m.bias is not None, **kw)
+            elif type(m) is nn.Conv2d:
+                new = conv_cls(m.in_channels, m.out_channels, m.kernel_size, m.stride, m.padding, m.groups,
+                               bias=m.bias is not None, **kw)
+            if new is not None:
+                new.weight = m.weight
+                if m.bias is not None:
+                    new.bias = m.bias
+                setattr(parent, name, new.to(m.weight.device))
+    return model
+
+
+def test_dit_with_lsq_leaves_vs_oracle():
+    """The drop-in DiT after the reference's module surgery (all 25 Linear + the mask Conv2d of the small config
+    become LSQ layers, 8-bit activations / 4-bit weights): forward against the oracle DiT with the oracle LSQ layer in
+    every leaf, lazily initialised step sizes copied from the oracle's warm-up (SURVEY §8c trap iii); then one captured
+    training step must produce finite gradients for every parameter including the step sizes."""
+    dev = _dev()
+    from oracle import cim_torch as OC
+    from oracle import dit_torch as OD
+    from cim_layers.layers_qn_lsq import Conv2d_qn_lsq, Linear_qn_lsq
+    from models.transformer import DIT
+    from util import cond_of, l2err, randomise_zero_init
+    fx = load_golden("dit_small_cond")
+    cfg, inp = fx["config"], fx["inputs"]
+    torch.manual_seed(fx["seed"])
+    model = DIT(4, cfg)
+    randomise_zero_init(model, fx["rand_seed"])
+    qcfg = dict(weight_bit=4, input_bit=8, output_bit=8, noise_scale=0.0)
+    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    states = {}
+
+    def leaf(name, x, w, b, conv):
+        p = states.setdefault(name, {"step_size_input": torch.tensor(1.0), "step_size_output": torch.tensor(1.0),
+                                     "step_size_weight": torch.tensor(1.0)})
+        p["weight"] = w
+        if b is not None:
+            p["bias"] = b
+        return OC.lsq_layer(p, qcfg, x, None, conv)
+
+    cond = cond_of(inp, cfg)
+    OD.LEAF = leaf
+    try:
+        with torch.no_grad():
+            OD.dit_forward(sd, cfg, inp["x"], inp["t"], cond)                    # warm-up: initialises every step size
+            ref = OD.dit_forward(sd, cfg, inp["x"], inp["t"], cond)
+            with torch.autocast("cpu", dtype=torch.bfloat16):
+                ref16 = OD.dit_forward(sd, cfg, inp["x"], inp["t"], cond).float()
+    finally:
+        OD.LEAF = None
+    model = _convert(model, Linear_qn_lsq, Conv2d_qn_lsq, **qcfg).to(dev).eval()
+    n_q = sum(1 for m in model.modules() if isinstance(m, (Linear_qn_lsq, Conv2d_qn_lsq)))
+    # mask conv + patch embed + t_proj (2) + 2 layers x (qkv, out, mlp x2, q/k/v/out, context_proj, adaLN) + adaLN + proj_out
+    assert n_q == len(states) == 1 + 1 + 2 + 2 * 10 + 2                         # every leaf went through the hook
+    with torch.no_grad():
+        for name, m in model.named_modules():
+            if name in states:
+                for k in ("step_size_input", "step_size_output", "step_size_weight"):
+                    getattr(m, k).copy_(states[name][k])
+        condd = cond_of(inp, cfg, dev)
+        out = model(inp["x"].to(dev), inp["t"].to(dev), condd)
+        out_again = model(inp["x"].to(dev), inp["t"].to(dev), condd)             # captured-graph replay
+    torch.cuda.synchronize()
+    err, yard = l2err(out.cpu(), ref), l2err(ref16, ref)
+    print(f"DiT with LSQ leaves: ours-vs-oracle rel-L2 {err:.3e}; oracle bf16-autocast-vs-fp32 {yard:.3e}")
+    assert torch.equal(out, out_again)
+    assert err < max(5e-2, 1.5 * yard)
+    # one training step through the quantised network
+    model.train()
+    x, t = inp["x"].to(dev), inp["t"].to(dev)
+    tgt = torch.randn(x.shape, generator=torch.Generator().manual_seed(1)).to(dev)
+    for _ in range(2):                                                            # second pass replays the graphs
+        model.zero_grad()
+        loss = torch.nn.functional.mse_loss(model(x, t, condd), tgt)
+        loss.backward()
+    torch.cuda.synchronize()
+    missing = [k for k, p in model.named_parameters() if p.grad is None or not torch.isfinite(p.grad).all()]
+    assert not missing, missing[:6]
+    steps = [p.grad.abs().item() for k, p in model.named_parameters() if "step_size" in k]
+    assert sum(1 for s in steps if s > 0) > 0.9 * len(steps)
