@@ -388,13 +388,121 @@ def run_ours(args):
         del pipe, P, model, vae
         torch.cuda.empty_cache()
         line["train"] = train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks)
+    if args.dit_steps > 0:
+        line["dit"] = dit_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, t_dec)
     if rank == 0:
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
 
-def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks):
+# Model_DiT_12L_config.py:125-133 (image-conditioned, 12 layers) and Model_DiT_9L_config.py:139-148 (text + image, 9 layers)
+def dit_config(layers, kinds):
+    cc = {"condition_types": kinds}
+    if "text" in kinds:
+        cc["text_condition_config"] = {"text_embed_model": "clip", "train_text_embed_model": False, "text_embed_dim": 512,
+                                       "cond_drop_prob": 0.9}
+    if "image" in kinds:
+        cc["image_condition_config"] = {"image_condition_input_channels": 18, "image_condition_output_channels": 3,
+                                        "image_condition_h": 512, "image_condition_w": 512, "cond_drop_prob": 0.9}
+    return {"hidden_size": 288, "patch_size": 2, "timestep_emb_dim": 192, "num_layers": layers, "num_heads": 9,
+            "head_dim": 32, "condition_config": cc}
+
+
+DIT12_GFLOP, DIT9_GFLOP = 7.04, 6.69     # forward per sample, SURVEY §8d [probed]
+
+
+def dit_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, t_dec):
+    """BASELINE.json configs[3] (DiT-12L, image-conditioned: sampling + data-parallel training, batch sharded) and the
+    LSQ half of configs[4] (DiT-9L text+image with every Linear / the mask conv replaced by cim_layers LSQ drop-ins,
+    8-bit activations, 4-bit weights, weight noise 0.08: one quant-noise training step). Same step definitions as the
+    UNet legs; the VQVAE decode time of the main leg is reused for images/s."""
+    import torch.nn as nn
+    from sdb200 import runtime as rt
+    from sdb200.graphs import SamplingPipeline
+    from models.transformer import DIT
+    from scheduler.linear_noise_scheduler import LinearNoiseScheduler
+    from cim_layers.layers_qn_lsq import Conv2d_qn_lsq, Linear_qn_lsq
+
+    def fresh(layers, kinds):
+        torch.manual_seed(SEED)
+        m = DIT(4, dit_config(layers, kinds))
+        g = torch.Generator().manual_seed(SEED + 7)
+        with torch.no_grad():   # the adaLN / proj_out parameters are zero-initialised: a default-init DiT outputs 0
+            for name, p in m.named_parameters():
+                if "adaptive_norm_layer" in name or name.startswith("proj_out"):
+                    p.copy_(torch.randn(p.shape, generator=g) * 0.02)
+        return m
+
+    B, K, W = args.batch, args.dit_steps, 5
+    model = fresh(12, ["image"]).eval().to(dev)
+    sched = LinearNoiseScheduler(T_STEPS, 0.00085, 0.012)
+    sched.seed = SEED + rank
+    xt_h, text_h, mask_h = synth_inputs(B, ucfg, rank)
+    xt_d, mask_d = xt_h.to(dev), mask_h.to(dev)
+    pipe = SamplingPipeline(model, sched, None)
+    with torch.no_grad():
+        P = pipe.plan(xt_d, {"image": mask_d}, None, 1.0)
+        P.xt.copy_(xt_d)
+        P.t.fill_(T_STEPS - 1)
+        for _ in range(W):
+            pipe.step(P)
+        with rt.KernelTimer() as kt:
+            P.body()
+        ksum = kt.summary()
+        if rank == 0 and args.dump:
+            with open(args.dump.replace(".json", "") + "_dit.json", "w") as f:
+                json.dump({"per_launch": [{"kernel": n, "work": w, "us": round(ms_ * 1e3, 2), "shape": d}
+                                          for n, w, ms_, d in kt.rows()]}, f)
+        l0 = rt.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        P.t.fill_(min(K, T_STEPS) - 1)
+        barrier()
+        e0.record()
+        for _ in range(K):
+            pipe.step(P)
+        e1.record()
+        barrier()
+        (ms,) = max_over_ranks([e0.elapsed_time(e1)])
+        launches = rt.launch_count() - l0
+    t_step = ms / K / 1e3
+    tot = sum(v["ms"] for v in ksum.values())
+    kernels = {k: {"launches": v["launches"], "ms": round(v["ms"], 4), "share": round(v["ms"] / tot, 4)}
+               for k, v in sorted(ksum.items(), key=lambda kv: -kv[1]["ms"])}
+    ln = ksum.get("layernorm")
+    out = {
+        "sampling": {"model": "DiT-12L image-conditioned (Model_DiT_12L_config)", "metric": "ddpm_sampling_images_per_s",
+                     "value": world * images_per_s(B, t_step, t_dec), "unit": "images/s", "ms_per_step": ms / K,
+                     "steps": K, "batch_per_gpu": B, "step_tflops": DIT12_GFLOP * 1e9 * B / t_step / 1e12,
+                     "gpu_launches": launches, "kernels": kernels,
+                     "layernorm_gbps": None if ln is None else ln["work"] / (ln["ms"] * 1e-3) / 1e9},
+    }
+    del pipe, P, model
+    out["train"] = train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=lambda: fresh(12, ["image"]),
+                             gflop_fwd=DIT12_GFLOP, tag="DiT-12L image-conditioned")
+
+    def lsq_model():
+        m = fresh(9, ["text", "image"])
+        kw = dict(weight_bit=4, input_bit=8, output_bit=8, noise_scale=0.08)      # Model_DiT_9L_train.py:541-548
+        for parent in list(m.modules()):
+            for name, c in list(parent.named_children()):
+                new = None
+                if type(c) is nn.Linear:
+                    new = Linear_qn_lsq(c.in_features, c.out_features, bias=c.bias is not None, **kw)
+                elif type(c) is nn.Conv2d:
+                    new = Conv2d_qn_lsq(c.in_channels, c.out_channels, c.kernel_size, c.stride, c.padding, c.groups,
+                                        bias=c.bias is not None, **kw)
+                if new is not None:
+                    new.weight, new.bias = c.weight, c.bias
+                    setattr(parent, name, new)
+        return m
+
+    out["cim_lsq_train"] = train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=lsq_model,
+                                     gflop_fwd=DIT9_GFLOP, tag="DiT-9L text+image, all 95 Linear + mask conv as LSQ layers")
+    return out
+
+
+def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=None, gflop_fwd=None, tag="unet"):
     """BASELINE.json configs[2]: data-parallel training of the same conditioned UNet as
     train_ddpm_cond_celebhq_multi_gpu.py:341-378 does it — add_noise, bf16-autocast forward, MSE, backward (DDP's
     bucketed NCCL all-reduce overlapped with it when world > 1), clip_grad_norm_(1.0), Adam, EMA — per-GPU batch 16
@@ -408,7 +516,9 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks):
     from scheduler.linear_noise_scheduler import LinearNoiseScheduler
     B, K, W = args.train_batch, args.train_steps, 3
     torch.manual_seed(SEED)
-    model = Unet(4, ucfg).train().to(dev)
+    model = (make_model() if make_model is not None else Unet(4, ucfg)).train().to(dev)
+    gflop_fwd = UNET_GFLOP if gflop_fwd is None else gflop_fwd
+    cond_keys = [k for k, on in (("text", model.text_cond), ("image", model.image_cond)) if on]
     ema = copy.deepcopy(model).eval()
     net = model
     if world > 1:
@@ -433,7 +543,7 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks):
             x0, text, mask, noise, t = res["x"], res["text"], res["mask"], res["noise"], res["t"]
         noisy = sched.add_noise(x0, noise, t)
         with torch.autocast("cuda", dtype=torch.bfloat16):
-            pred = net(noisy, t, {"text": text, "image": mask})
+            pred = net(noisy, t, {k: v for k, v in (("text", text), ("image", mask)) if k in cond_keys})
             loss = torch.nn.functional.mse_loss(pred, noise)
         opt.zero_grad(set_to_none=True)
         loss.backward()
@@ -459,11 +569,13 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks):
         (ms,) = max_over_ranks([e0.elapsed_time(e1)])
         out[name] = (world * B * K / (ms / 1e3), ms / K, rt.launch_count() - l0, float(last))
     h2d = (x_h.numel() + text_h.numel() + mask_h.numel() + noise_h.numel()) * 4 + t_h.numel() * 8
-    del net, model, ema, opt
+    ema_params = list(ema.parameters())
+    del net, model, opt
     return {
         "metric": "ddp_train_samples_per_s", "value": out["value"][0], "unit": "samples/s", "ms_per_step": out["value"][1],
         "steps": K, "warmup": W, "batch_per_gpu": B, "global_batch": B * world, "dtype": "bf16",
-        "algorithmic_tflops": 3 * UNET_GFLOP * 1e9 * B / (out["value"][1] / 1e3) / 1e12,
+        "model": tag, "params": sum(p.numel() for p in ema_params),
+        "algorithmic_tflops": 3 * gflop_fwd * 1e9 * B / (out["value"][1] / 1e3) / 1e12,
         "optimizer": "Adam + clip_grad_norm_(1.0) + EMA (torch foreach)", "gpu_launches": out["value"][2],
         "grad_allreduce": None if world == 1 else (
             "torch DistributedDataParallel: 25 MB NCCL buckets, reduced after the backward graph has replayed"
@@ -490,6 +602,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=0, help="cap on the e2e leg's timesteps (0 = same as --steps)")
     ap.add_argument("--train-steps", type=int, default=20, help="timed steps of the training leg (0 = skip it)")
     ap.add_argument("--train-batch", type=int, default=16, help="per-GPU training batch (reference: 16)")
+    ap.add_argument("--dit-steps", type=int, default=200,
+                    help="DiT legs (configs[3], LSQ half of configs[4]): timed sampling steps; 0 disables them")
     ap.add_argument("--train-ddp", choices=["ours", "torch"], default="ours",
                     help="N>1 gradient mean: sdb200.parallel.DataParallel (flat buffer) or torch DistributedDataParallel")
     ap.add_argument("--dump", default="", help="write the per-launch kernel timing of one eager step to this JSON file")

@@ -57,6 +57,7 @@ struct alignas(64) IgemmArgs {
     const __nv_bfloat16* residual;
     long long res_sn, res_sy, res_sx;
     int act;
+    int vec_ok;    // every optional epilogue operand (and a directly stored output) is 16-byte addressable
     float* stats;  // [on][stats_p][stats_ld][2] partial sums, or null
     int stats_p, stats_slot0, stats_ld;
 };
@@ -292,6 +293,10 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_co
         if (args.tma_res && et == 0 && blockIdx.x < args.num_tiles)
             load_residual(decode_tile(args, blockIdx.x), staging, &res_bar[0]);
 
+        const bool fast = args.vec_ok != 0;
+        const bool has_bias = args.bias != nullptr, has_rowbias = args.rowbias != nullptr;
+        const bool has_gate = args.gate != nullptr, has_res = args.residual != nullptr;
+        const int act = args.act;
         int lt = 0;
         for (int tile = blockIdx.x; tile < args.num_tiles; tile += gridDim.x, ++lt) {
             const Tile t = decode_tile(args, tile);
@@ -314,6 +319,96 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_co
                 uint32_t acc[32];
                 tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + c * 32, acc);
                 tmem_ld_wait();
+                if (fast && col0 + 32 <= args.n_out) {
+                    // full 32-column chunk with 16-byte addressable operands: straight-line code, one uniform branch
+                    // per optional operand per chunk (the general path below pays them per 8 columns, with scalar
+                    // fall-backs inlined each time — its instruction footprint stalls short-K tiles on fetch)
+                    float v[4][8];
+#pragma unroll
+                    for (int g = 0; g < 4; ++g)
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) v[g][j] = __uint_as_float(acc[g * 8 + j]);
+                    if (has_bias) {
+                        const float4* bp = bias_sm ? reinterpret_cast<const float4*>(sbias + col0)
+                                                   : reinterpret_cast<const float4*>(args.bias + col0);
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            const float4 b0 = bp[2 * g], b1 = bp[2 * g + 1];
+                            v[g][0] += b0.x, v[g][1] += b0.y, v[g][2] += b0.z, v[g][3] += b0.w;
+                            v[g][4] += b1.x, v[g][5] += b1.y, v[g][6] += b1.z, v[g][7] += b1.w;
+                        }
+                    }
+                    if (has_rowbias) {
+                        const uint4* rp = reinterpret_cast<const uint4*>(args.rowbias + pnc * args.rowbias_ld + col0);
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            float f[8];
+                            unpack8(__ldg(rp + g), f);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) v[g][j] += f[j];
+                        }
+                    }
+                    if (act == B200SD_ACT_RELU) {
+#pragma unroll
+                        for (int g = 0; g < 4; ++g)
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) v[g][j] = fmaxf(v[g][j], 0.f);
+                    } else if (act == B200SD_ACT_SILU) {
+#pragma unroll
+                        for (int g = 0; g < 4; ++g)
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) v[g][j] = v[g][j] / (1.f + __expf(-v[g][j]));
+                    }
+                    if (has_gate) {
+                        const uint4* gp = reinterpret_cast<const uint4*>(args.gate + pnc * args.gate_ld + col0);
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            float f[8];
+                            unpack8(__ldg(gp + g), f);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) v[g][j] *= f[j];
+                        }
+                    }
+                    if (has_res && !args.tma_res && row_ok) {
+                        const uint4* rp = reinterpret_cast<const uint4*>(args.residual + r_off + col0);
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            float f[8];
+                            unpack8(__ldg(rp + g), f);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) v[g][j] += f[j];
+                        }
+                    }
+                    if (BN >= 64 && args.tma_out) {
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            const int jj = c * 4 + g;  // 16-byte chunk index within the tile row
+                            uint4* sp = reinterpret_cast<uint4*>(stg + (jj >> 3) * PANEL_BYTES + r * 128 +
+                                                                 (((jj & 7) ^ (r & 7)) << 4));
+                            if (args.tma_res) {
+                                float f[8];
+                                unpack8(*sp, f);
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) v[g][j] += f[j];
+                            }
+                            *sp = pack8(v[g]);
+                        }
+                    } else if (row_ok) {
+                        if (args.out_f32) {
+                            float4* op = reinterpret_cast<float4*>(static_cast<float*>(args.out) + o_off + col0);
+#pragma unroll
+                            for (int g = 0; g < 4; ++g) {
+                                op[2 * g] = make_float4(v[g][0], v[g][1], v[g][2], v[g][3]);
+                                op[2 * g + 1] = make_float4(v[g][4], v[g][5], v[g][6], v[g][7]);
+                            }
+                        } else {
+                            uint4* op = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(args.out) + o_off + col0);
+#pragma unroll
+                            for (int g = 0; g < 4; ++g) op[g] = pack8(v[g]);
+                        }
+                    }
+                    continue;
+                }
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
                     const int col = col0 + g * 8;
@@ -602,7 +697,7 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
     }
     for (int i = p->n_src; i < 4; ++i) a.a_map[i] = a.a_map[0];
 
-    // column tile: the persistent grid runs ceil(tiles / SMs) waves of tiles whose cost grows like BN + const
+    // column tile: the persistent grid runs ceil(tiles / SMs) waves of tiles
     const int n = p->n_out;
     const long long m_tiles = (long long)a.tiles_x * a.tiles_y * a.tiles_img;
     const int sms = sm_count();
@@ -612,10 +707,10 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
         for (int bnc : {256, 128, 64}) {
             if (bnc > 64 && n <= bnc / 2) continue;
             const long long tiles = m_tiles * ((n + bnc - 1) / bnc);
-            long long cost = ((tiles + sms - 1) / sms) * (bnc + 64);
-            // BN = 256 has a single staging tile (its epilogue store is not overlapped with the next tile's
-            // epilogue): with a short K loop there is no mainloop to hide that behind
-            if (bnc == 256 && total <= 16) cost = cost * 3 / 2;
+            // per-tile time ~ max(mainloop, epilogue) + fixed: the mainloop is operand-feed bound (128 + BN rows of 128
+            // bytes per K chunk), the epilogue is proportional to BN; constants fitted to tools/gemm_sweep.py on B200
+            const long long main_c = (long long)total * (128 + bnc), epi_c = 10ll * bnc;
+            long long cost = ((tiles + sms - 1) / sms) * ((main_c > epi_c ? main_c : epi_c) + 120);
             if (best < 0 || cost < best) best = cost, BNsel = bnc;
         }
     }
@@ -650,6 +745,16 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
     a.res_sn = p->res_sn, a.res_sy = p->res_sy, a.res_sx = p->res_sx;
     a.act = p->act;
 
+    {
+        auto al = [](const void* ptr, long long bytes_a, long long bytes_b = 16, long long bytes_c = 16) {
+            return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && bytes_a % 16 == 0 && bytes_b % 16 == 0 && bytes_c % 16 == 0;
+        };
+        const long long ob = a.out_f32 ? 4 : 2;
+        a.vec_ok = (!p->bias || al(p->bias, 16)) && (!p->rowbias || al(p->rowbias, p->rowbias_ld * 2)) &&
+                   (!p->gate || al(p->gate, p->gate_ld * 2)) &&
+                   (!p->residual || al(p->residual, p->res_sn * 2, p->res_sy * 2, p->res_sx * 2)) &&
+                   al(p->out, p->out_sn * ob, p->out_sy * ob, p->out_sx * ob);
+    }
     // epilogue route: TMA tensor store from a staged bf16 tile when the output is addressable that way
     a.tma_out = BNsel >= 64 && !a.out_f32 && pixel_view_ok(p->out, p->out_sn, p->out_sy, p->out_sx);
     if (a.tma_out) {
