@@ -478,6 +478,8 @@ def dit_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, t_dec):
                      "layernorm_gbps": None if ln is None else ln["work"] / (ln["ms"] * 1e-3) / 1e9},
     }
     del pipe, P, model
+    if args.train_steps <= 0:
+        return out
     out["train"] = train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=lambda: fresh(12, ["image"]),
                              gflop_fwd=DIT12_GFLOP, tag="DiT-12L image-conditioned")
 

@@ -329,11 +329,18 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_co
 #pragma unroll
                         for (int j = 0; j < 8; ++j) v[g][j] = __uint_as_float(acc[g * 8 + j]);
                     if (has_bias) {
-                        const float4* bp = bias_sm ? reinterpret_cast<const float4*>(sbias + col0)
-                                                   : reinterpret_cast<const float4*>(args.bias + col0);
+                        const uint32_t bs = smem_u32(sbias + col0);
+                        const float4* bp = reinterpret_cast<const float4*>(args.bias + col0);
 #pragma unroll
                         for (int g = 0; g < 4; ++g) {
-                            const float4 b0 = bp[2 * g], b1 = bp[2 * g + 1];
+                            float4 b0, b1;
+                            if (bias_sm) {
+                                const uint4 u0 = lds128(bs + 32 * g), u1 = lds128(bs + 32 * g + 16);
+                                b0 = make_float4(__uint_as_float(u0.x), __uint_as_float(u0.y), __uint_as_float(u0.z), __uint_as_float(u0.w));
+                                b1 = make_float4(__uint_as_float(u1.x), __uint_as_float(u1.y), __uint_as_float(u1.z), __uint_as_float(u1.w));
+                            } else {
+                                b0 = __ldg(bp + 2 * g), b1 = __ldg(bp + 2 * g + 1);
+                            }
                             v[g][0] += b0.x, v[g][1] += b0.y, v[g][2] += b0.z, v[g][3] += b0.w;
                             v[g][4] += b1.x, v[g][5] += b1.y, v[g][6] += b1.z, v[g][7] += b1.w;
                         }
@@ -380,18 +387,18 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_co
                         }
                     }
                     if (BN >= 64 && args.tma_out) {
+                        const uint32_t row_s = smem_u32(stg) + r * 128;
 #pragma unroll
                         for (int g = 0; g < 4; ++g) {
                             const int jj = c * 4 + g;  // 16-byte chunk index within the tile row
-                            uint4* sp = reinterpret_cast<uint4*>(stg + (jj >> 3) * PANEL_BYTES + r * 128 +
-                                                                 (((jj & 7) ^ (r & 7)) << 4));
+                            const uint32_t sa = row_s + (jj >> 3) * PANEL_BYTES + (((jj & 7) ^ (r & 7)) << 4);
                             if (args.tma_res) {
                                 float f[8];
-                                unpack8(*sp, f);
+                                unpack8(lds128(sa), f);
 #pragma unroll
                                 for (int j = 0; j < 8; ++j) v[g][j] += f[j];
                             }
-                            *sp = pack8(v[g]);
+                            sts128(sa, pack8(v[g]));
                         }
                     } else if (row_ok) {
                         if (args.out_f32) {
