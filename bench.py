@@ -413,9 +413,10 @@ DIT12_GFLOP, DIT9_GFLOP = 7.04, 6.69     # forward per sample, SURVEY §8d [prob
 
 
 def dit_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, t_dec):
-    """BASELINE.json configs[3] (DiT-12L, image-conditioned: sampling + data-parallel training, batch sharded) and the
-    LSQ half of configs[4] (DiT-9L text+image with every Linear / the mask conv replaced by cim_layers LSQ drop-ins,
-    8-bit activations, 4-bit weights, weight noise 0.08: one quant-noise training step). Same step definitions as the
+    """BASELINE.json configs[3] (DiT-12L, image-conditioned: sampling + data-parallel training, batch sharded) and
+    configs[4] (DiT-9L text+image with every Linear / the mask conv replaced by the cim_layers drop-ins — first the LSQ
+    layers, then the ADDA compute-in-memory layers — 8-bit activations, 4-bit weights, weight noise 0.08: one
+    quant-noise training step; the Enhance wrappers and PercentOptimizerFP of that pipeline are not part of it). Same step definitions as the
     UNet legs; the VQVAE decode time of the main leg is reused for images/s."""
     import torch.nn as nn
     from sdb200 import runtime as rt
@@ -483,24 +484,37 @@ def dit_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, t_dec):
     out["train"] = train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=lambda: fresh(12, ["image"]),
                              gflop_fwd=DIT12_GFLOP, tag="DiT-12L image-conditioned")
 
-    def lsq_model():
+    def cim_model(kind):
+        from cim_layers.layers_qn_lsq_adda_cim import Conv2d_lsq_adda_cim, Linear_lsq_adda_cim, gen_weight_split_dict
         m = fresh(9, ["text", "image"])
         kw = dict(weight_bit=4, input_bit=8, output_bit=8, noise_scale=0.08)      # Model_DiT_9L_train.py:541-548
+        lin_cls, conv_cls = Linear_qn_lsq, Conv2d_qn_lsq
+        if kind == "adda":                                                          # :578-590
+            kw.update(dac_bit=5, adc_bit=8, adc_gain_1_scale=9.071428571, adc_gain_range=[1 / 64, 1 / 64],
+                      adc_adjust_mode="current")
+            lin_cls, conv_cls = Linear_lsq_adda_cim, Conv2d_lsq_adda_cim
         for parent in list(m.modules()):
             for name, c in list(parent.named_children()):
                 new = None
                 if type(c) is nn.Linear:
-                    new = Linear_qn_lsq(c.in_features, c.out_features, bias=c.bias is not None, **kw)
+                    new = lin_cls(c.in_features, c.out_features, bias=c.bias is not None, **kw)
                 elif type(c) is nn.Conv2d:
-                    new = Conv2d_qn_lsq(c.in_channels, c.out_channels, c.kernel_size, c.stride, c.padding, c.groups,
-                                        bias=c.bias is not None, **kw)
+                    new = conv_cls(c.in_channels, c.out_channels, c.kernel_size, c.stride, c.padding, c.groups,
+                                   bias=c.bias is not None, **kw)
                 if new is not None:
                     new.weight, new.bias = c.weight, c.bias
+                    if kind == "adda":                                              # array [576, 2048], :594-600
+                        new.weight_mapping_info = gen_weight_split_dict(new, [576, 2048])
                     setattr(parent, name, new)
         return m
 
-    out["cim_lsq_train"] = train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=lsq_model,
-                                     gflop_fwd=DIT9_GFLOP, tag="DiT-9L text+image, all 95 Linear + mask conv as LSQ layers")
+    out["cim_lsq_train"] = train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks,
+                                     make_model=lambda: cim_model("lsq"), gflop_fwd=DIT9_GFLOP,
+                                     tag="DiT-9L text+image, all 95 Linear + mask conv as LSQ layers")
+    out["cim_adda_train"] = train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks,
+                                      make_model=lambda: cim_model("adda"), gflop_fwd=DIT9_GFLOP,
+                                      tag="DiT-9L text+image, all 95 Linear + mask conv as ADDA compute-in-memory layers "
+                                          "(2 DAC slices, 8-bit ADC, array 576 x 2048)")
     return out
 
 

@@ -12,8 +12,12 @@ Here the digits and weight codes are exact in bf16 and every block product runs 
 accumulation (partial sums are integers < 2^24: exact), so the ADC codes are bit-exact with the reference's fp32
 arithmetic when no weight noise is injected. Step sizes, the ADC gain and its lazy initialisation stay on the device.
 
-Not available yet: the backward pass (progressive quant-noise *training* through ADDA layers) and convolutions other
-than 1x1 (the reference maps k x k kernels through nn.Unfold's (c, ky, kx) row order)."""
+The backward pass (progressive quant-noise training, Model_DiT_9L_train.py:610-623) follows the reference's autograd
+graph: straight-through rounds, the ADC clamp mask, bit-split gradient 1/(slices * 2^lsb), LSQ step-size gradients,
+and the ADC-gain gradient through both the scale and the final division (sdb200/quant.py: AddaFn).
+
+Not available yet: convolutions other than 1x1 (the reference maps k x k kernels through nn.Unfold's (c, ky, kx) row
+order)."""
 import math
 
 import torch
@@ -115,51 +119,65 @@ class _AddaMixin(_LsqMixin):
             self.adc_gain.copy_(torch.where(fire, ideal.to(self.adc_gain.dtype), self.adc_gain))
 
     def _cim_rows(self, x, w2d, bias, numel_in):
-        """x: bf16 rows [M, K]; w2d: fp32 parameter view [N, K]. Returns bf16 rows [M, N]."""
-        if E.training():
-            raise rt.B200Error("ADDA layers: the backward pass is not available yet (inference / evaluation only)")
-        M, K = x.shape
-        N = w2d.shape[0]
-        R = float(2 ** (self.adc_bit - 1) - 1)
+        """x: bf16 rows [M, Kp] (Kp = in-features rounded up to 8, padding columns zero); w2d: fp32 parameter view
+        [N, K] (shape only: the quantised weight is rebuilt from self.weight). Returns bf16 rows [M, Np] with
+        Np = N rounded up to 8 (padding columns zero)."""
+        M, Kp = x.shape
+        N, K = w2d.shape
+        Np = (N + 7) // 8 * 8
+        if Kp != (K + 7) // 8 * 8:
+            raise rt.B200Error("ADDA layers: input rows must be packed to in_features rounded up to 8")
         if self.input_bit > 9 or self.bit_slices * self.slice_bit > 24:
             raise rt.B200Error("ADDA layers: input codes wider than 9 bits are not supported")
         if not self.input_quant:
             raise rt.B200Error("ADDA layers: the DAC needs quantised inputs (input_quant=True)")
         qp_in = Q.qp_of(self.input_bit)
         rt.lsq_init_step(x, self.step_size_input, qp_in)
-        # LSQ codes and their DAC digits in one pass over the activations
-        digits = rt.bit_split(x, self.bit_slices, self.slice_bit, self.input_bit, step=self.step_size_input.detach(),
-                              qp=qp_in, numel=numel_in)
         w, w_scale = self._w_qn(isint=True)
-        w = w.detach().reshape(N, K)
+        w = w.reshape(N, K)
+        if Kp != K or Np != N:
+            w = torch.nn.functional.pad(w, (0, Kp - K, 0, Np - N))   # zero codes meet zero digits / unused columns
+            if bias is not None:
+                bias = torch.nn.functional.pad(bias, (0, Np - N))
         mapping = getattr(self, "weight_mapping_info", None) or {"0_0": {"start_row": 0, "start_col": 0, "row_num": K,
                                                                           "col_num": N}}
+        blocks = [(i["start_row"], i["row_num"], i["start_col"], i["col_num"]) for i in mapping.values()]
+        if any(r0 % 8 for r0, _, _, _ in blocks):
+            raise rt.B200Error("ADDA layers: weight blocks must start at a row multiple of 8")
         noisy = self.gain_noise_scale != 0 or self.offset_noise_scale != 0
-        out = torch.zeros(M, N, device=x.device, dtype=torch.float32)
-        pending = self.__dict__.get("_gain_init_pending", True)
-        for info in mapping.values():
-            r0, rn, c0, cn = info["start_row"], info["row_num"], info["start_col"], info["col_num"]
-            if r0 % 8:
-                raise rt.B200Error("ADDA layers: weight blocks must start at a row multiple of 8")
-            wb = ops.pack_linear_weight(w[c0:c0 + cn, r0:r0 + rn])
-            part = rt.linear(digits[:, r0:r0 + rn], wb, out_dtype=torch.float32)
-            if pending:
-                self._maybe_init_gain(part)
-            alpha = self._adc_scale().detach().float().reshape(1)
-            if noisy and c0 + cn > 1000:
-                raise rt.B200Error("ADDA layers: ADC noise tables hold 1000 columns (layers_utils_adda.py:100-105)")
-            rt.adc_combine(part, out, M, cn, c0, self.bit_slices, self.slice_bit, alpha, R,
-                           self.gain_noise.to(x.device, torch.float32) if noisy else None,
-                           self.offset_noise.to(x.device, torch.float32) if noisy else None)
-        self.__dict__["_gain_init_pending"] = False
-        alpha = self._adc_scale().detach()
-        in_scale = (1.0 / self.step_size_input).detach() if self.input_quant else 1.0
-        y = out / w_scale / in_scale / alpha
+        if noisy and max(c0 + cn for _, _, c0, cn in blocks) > 1000:
+            raise rt.B200Error("ADDA layers: ADC noise tables hold 1000 columns (layers_utils_adda.py:100-105)")
+        cfg = {"slices": self.bit_slices, "slice_bit": self.slice_bit, "input_bit": self.input_bit, "qp_in": qp_in,
+               "numel_in": numel_in, "R": float(2 ** (self.adc_bit - 1) - 1), "blocks": blocks,
+               "gain_noise": self.gain_noise.to(x.device, torch.float32) if noisy else None,
+               "offset_noise": self.offset_noise.to(x.device, torch.float32) if noisy else None}
+        if self.__dict__.get("_gain_init_pending", True):
+            # first forward: the analogue range of the first block decides the ADC gain (init_adc_gain)
+            with torch.no_grad():
+                r0, rn, c0, cn = blocks[0]
+                digits = Q.AddaFn._digits(x, self.step_size_input.detach(), cfg)
+                first = rt.linear(digits[:, r0:r0 + rn], ops.pack_linear_weight(w.detach()[c0:c0 + cn, r0:r0 + rn]),
+                                  out_dtype=torch.float32)
+                self._maybe_init_gain(first)
+            self.__dict__["_gain_init_pending"] = False
+        alpha = self._adc_scale()
+        if torch.is_grad_enabled() and any(t.requires_grad for t in (x, w, alpha, self.step_size_input)):
+            acc = Q.AddaFn.apply(x, self.step_size_input, w, alpha, cfg)
+        else:
+            acc = Q.AddaFn._run(x, self.step_size_input.detach(), w.detach(), alpha.detach(), cfg)
+        in_scale = (1.0 / self.step_size_input).detach()
+        y = acc / w_scale / in_scale / alpha
         if bias is not None:
-            y = y + bias.detach().view(1, -1)
+            y = y + bias.view(1, -1)
         if self.output_quant:
             return Q.quantize_rows(y, self.step_size_output, self.output_bit, numel=M * N)
         return y.to(torch.bfloat16)
+
+    def _rows_in(self, rows, K):
+        Kp = (K + 7) // 8 * 8
+        if rows.shape[1] < Kp:
+            raise rt.B200Error("ADDA layers: input rows narrower than in_features rounded up to 8")
+        return rows if rows.shape[1] == Kp else rows[:, :Kp].contiguous()
 
     def _load_from_state_dict(self, *a, **k):
         self.__dict__["_gain_init_pending"] = True
@@ -179,14 +197,14 @@ class Linear_lsq_adda_cim(nn.Linear, _AddaMixin):
         K, N = self.in_features, self.out_features
         if self.use_FP:
             return self._linear(rows, self.weight, act)
-        if K % 8 or N % 8:
-            raise rt.B200Error("Linear_lsq_adda_cim: in/out features must be multiples of 8")
-        x = rows if rows.shape[1] == K else rows[:, :K].contiguous()
+        if N % 8:
+            raise rt.B200Error("Linear_lsq_adda_cim: out_features must be a multiple of 8")
+        x = self._rows_in(rows, K)
         y = self._cim_rows(x, self.weight, self.bias, x.shape[0] * K)
         if act is not None:
             if act != "relu":
                 raise rt.B200Error("Linear_lsq_adda_cim: only ReLU may follow a quantised Linear")
-            y = rt.copy_act(y, torch.empty_like(y), 0, act="relu")
+            y = torch.relu(y) if E.training() else rt.copy_act(y, torch.empty_like(y), 0, act="relu")
         return y
 
     def forward(self, x):
@@ -196,6 +214,8 @@ class Linear_lsq_adda_cim(nn.Linear, _AddaMixin):
         with torch.autocast("cuda", enabled=False):
             rows = x.reshape(-1, x.shape[-1])
             rows = rows.to(torch.bfloat16) if rows.dtype != torch.bfloat16 else rows
+            if rows.shape[1] % 8:
+                rows = torch.nn.functional.pad(rows, (0, 8 - rows.shape[1] % 8))
             out = self.forward_rows(rows.contiguous())
         return out.reshape(*lead, self.out_features).to(x.dtype)
 
@@ -216,9 +236,8 @@ class Conv2d_lsq_adda_cim(nn.Conv2d, _AddaMixin):
             raise rt.B200Error("Conv2d_lsq_adda_cim: use_FP bypass is served by Conv2d_qn_lsq / nn.Conv2d")
         if self.kernel_size != (1, 1) or self.stride != (1, 1) or self.padding != (0, 0) or self.groups != 1:
             raise rt.B200Error("Conv2d_lsq_adda_cim: only 1x1 convolutions have a CUDA path (see module docstring)")
-        if a.c % 8 or a.t.shape[1] != a.c or self.out_channels % 8:
-            raise rt.B200Error("Conv2d_lsq_adda_cim: channels must be multiples of 8 and densely packed")
-        y = self._cim_rows(a.t, self.weight.reshape(self.out_channels, -1), self.bias, a.n * a.hw * a.c)
+        y = self._cim_rows(self._rows_in(a.t, a.c), self.weight.reshape(self.out_channels, -1), self.bias,
+                           a.n * a.hw * a.c)
         return E.Act(y, a.n, a.h, a.w, self.out_channels)
 
     def forward(self, x):

@@ -309,6 +309,18 @@ int b200sd_adc_combine(const float* partial, int64_t ld_p, float* out, int64_t l
                        int32_t col0, int32_t slices, int32_t slice_bit, const float* adc_scale, float adc_range,
                        const float* gain_noise, const float* offset_noise, int32_t accumulate, void* stream);
 
+/* Backward of b200sd_adc_combine for one block (straight-through round, clamp mask on the noisy scaled value):
+ * dpartial bf16 [slices * rows, ld_d] = adc_scale * 2^(k*slice_bit) * dacc[r, col0 + j] * [in range] (the operand of
+ * the block's dgrad / wgrad GEMMs); part[b200sd_adc_bwd_blocks()] = fp32 partial sums of d(adc_scale). */
+int b200sd_adc_bwd(const float* partial, int64_t ld_p, const float* dacc, int64_t ld_g, void* dpartial, int64_t ld_d,
+                   int64_t rows, int32_t ncol, int32_t col0, int32_t slices, int32_t slice_bit, const float* adc_scale,
+                   float adc_range, const float* gain_noise, const float* offset_noise, float* part, void* stream);
+int b200sd_adc_bwd_blocks(int64_t rows, int32_t ncol);
+
+/* Backward of b200sd_bit_split (layers_utils_adda.py:178-183): dcodes = sum_k ddigits_k / (slices * 2^(k*slice_bit)). */
+int b200sd_bit_split_bwd(const void* ddigits, int64_t ld_d, void* dcodes, int64_t ld_q, int64_t rows, int32_t c,
+                         int32_t slices, int32_t slice_bit, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -239,21 +239,34 @@ def gen_cim():
         with torch.no_grad():
             y1 = run(layer, x, unit)
             after = params_of(layer)
-            y2 = run(layer, x2, unit)
+        layer.zero_grad()
+        x2r = x2.clone().requires_grad_(True)
+        y2 = run(layer, x2r, unit)
+        tgt = torch.randn(y2.shape, generator=g)
+        ((y2 - tgt) ** 2).mean().backward()
+        grads = {k: v.grad.detach().clone() for k, v in layer.named_parameters() if v.grad is not None}
+        grads["x"] = x2r.grad.detach().clone()
+        y2 = y2.detach()
         c = dict(cfgk, adc_gain_min=layer.adc_gain_min, adc_gain_max=layer.adc_gain_max)
         p = {k: v.clone() for k, v in init.items()}
         noise = dict(gain_noise=layer.gain_noise, offset_noise=layer.offset_noise) if extra else {}
         with torch.no_grad():
             o1 = O.adda_linear(p, c, x, layer.weight_mapping_info, unit, **noise)
             ep = max((p[k] - after[k]).abs().max().item() for k in after)
-            o2 = O.adda_linear(p, c, x2, layer.weight_mapping_info, unit, **noise)
-        e1, e2 = (o1 - y1).abs().max().item(), (o2 - y2).abs().max().item()
-        print(f"cim {name}: oracle-vs-ref out {e1:.1e} lazy-init params {ep:.1e} second forward {e2:.1e} "
+        p2 = {k: v.clone().requires_grad_(True) for k, v in p.items()}
+        x2o = x2.clone().requires_grad_(True)
+        o2 = O.adda_linear(p2, c, x2o, layer.weight_mapping_info, unit, **noise)
+        ((o2 - tgt) ** 2).mean().backward()
+        og = {k: v.grad for k, v in p2.items()}
+        og["x"] = x2o.grad
+        eg = max(((og[k] - grads[k]).abs().max() / grads[k].abs().max().clamp_min(1e-20)).item() for k in grads)
+        e1, e2 = (o1 - y1).abs().max().item(), (o2.detach() - y2).abs().max().item()
+        print(f"cim {name}: oracle-vs-ref out {e1:.1e} lazy-init params {ep:.1e} second forward {e2:.1e} grads {eg:.1e} "
               f"blocks {len(layer.weight_mapping_info)} adc_gain {after['adc_gain'].item():.6f}")
-        ok &= e1 == 0 and ep == 0 and e2 == 0
+        ok &= e1 == 0 and ep == 0 and e2 == 0 and eg < 1e-5
         out[name] = {"cfg": {k: v for k, v in c.items()}, "mapping": layer.weight_mapping_info, "init": init,
                      "after": {k: v for k, v in after.items() if v.dim() == 0}, "x": x, "x2": x2,
-                     "unit": unit.to(torch.float16), "y1": y1, "y2": y2,
+                     "unit": unit.to(torch.float16), "y1": y1, "y2": y2, "target": tgt, "grads": grads,
                      "gain_noise": layer.gain_noise.clone(), "offset_noise": layer.offset_noise.clone()}
     torch.save(out, os.path.join(GOLD, "cim_layers.pt"))
     return ok

@@ -219,6 +219,73 @@ __global__ void adc_combine_kernel(const float* __restrict__ p, long long ld_p, 
     }
 }
 
+// Backward of the ADC of one mapped block. Forward: a_k = alpha * P_k (+ noise), code_k = round(clamp(a_k, -R-1, R)),
+// acc += sum_k 2^(k*slice_bit) * code_k. With g = d acc (per output element) the straight-through gradients are
+//   d P_k = alpha * 2^(k*slice_bit) * g * [a_k in range]          (bf16 [slices * rows, ld_d], GEMM operand)
+//   d alpha += sum 2^(k*slice_bit) * g * P_k * [a_k in range]     (fixed-order partial per CTA)
+__global__ void __launch_bounds__(256)
+    adc_bwd_kernel(const float* __restrict__ p, long long ld_p, const float* __restrict__ dacc, long long ld_g,
+                   __nv_bfloat16* __restrict__ dp, long long ld_d, long long rows, int ncol, int col0, int slices,
+                   int slice_bit, const float* __restrict__ alpha_p, float R, const float* __restrict__ gain_noise,
+                   const float* __restrict__ offset_noise, float* __restrict__ part) {
+    __shared__ float wsum[8];
+    const float alpha = *alpha_p;
+    const long long total = rows * ncol;
+    float acc = 0.f;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const long long r = i / ncol;
+        const int col = static_cast<int>(i - r * ncol);
+        const float g = dacc[r * ld_g + col0 + col];
+        for (int k = 0; k < slices; ++k) {
+            const float pv = p[(static_cast<long long>(k) * rows + r) * ld_p + col];
+            float v = __fmul_rn(alpha, pv);
+            if (gain_noise) {
+                v = __fmul_rn(v, __fadd_rn(1.0f, gain_noise[col0 + col]));
+                v = __fadd_rn(v, __fmul_rn(R, offset_noise[col0 + col]));
+            }
+            const bool in = (v >= -R - 1.0f) && (v <= R);
+            const float gk = in ? g * static_cast<float>(1 << (k * slice_bit)) : 0.f;
+            acc += gk * pv;
+            dp[(static_cast<long long>(k) * rows + r) * ld_d + col] = __float2bfloat16_rn(alpha * gk);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+        for (int w = 0; w < 8; ++w) t += wsum[w];
+        part[blockIdx.x] = t;
+    }
+}
+
+// Backward of bit_split_tensor: d code = sum_k d digit_k / (slices * 2^(k*slice_bit)) (layers_utils_adda.py:178-183:
+// every slice passes the gradient of shift / slices, shift = floor_pass(code / 2^lsb)).
+__global__ void bit_split_bwd_kernel(const __nv_bfloat16* __restrict__ dd, long long ld_d, __nv_bfloat16* __restrict__ dq,
+                                     long long ld_q, long long rows, int c, int slices, int slice_bit) {
+    const int nchunk = c >> 3;
+    const long long total = rows * nchunk;
+    const float inv = 1.f / static_cast<float>(slices);
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const long long r = i / nchunk;
+        const int ch = static_cast<int>(i - r * nchunk);
+        float s[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s[j] = 0.f;
+        for (int k = 0; k < slices; ++k) {
+            float f[8];
+            q_ld8(dd + (static_cast<long long>(k) * rows + r) * ld_d + ch * 8, f);
+            const float w = inv / static_cast<float>(1 << (k * slice_bit));
+#pragma unroll
+            for (int j = 0; j < 8; ++j) s[j] += f[j] * w;
+        }
+        q_st8(dq + r * ld_q + ch * 8, s);
+    }
+}
+
 static int q_grid(long long items, int per_block, int cap_mult = 16) {
     long long b = (items + per_block - 1) / per_block;
     const long long cap = static_cast<long long>(cap_mult) * sm_count();
@@ -325,5 +392,34 @@ extern "C" int b200sd_adc_combine(const float* partial, int64_t ld_p, float* out
         partial, ld_p, out, ld_o, rows, ncol, col0, slices, slice_bit, adc_scale, adc_range, gain_noise, offset_noise,
         accumulate);
     B200_CHECK_LAUNCH("adc_combine");
+    return B200SD_OK;
+}
+
+extern "C" int b200sd_adc_bwd_blocks(int64_t rows, int32_t ncol) { return q_grid(rows * ncol, 256, 4); }
+
+extern "C" int b200sd_adc_bwd(const float* partial, int64_t ld_p, const float* dacc, int64_t ld_g, void* dpartial,
+                              int64_t ld_d, int64_t rows, int32_t ncol, int32_t col0, int32_t slices, int32_t slice_bit,
+                              const float* adc_scale, float adc_range, const float* gain_noise, const float* offset_noise,
+                              float* part, void* stream) {
+    B200_REQUIRE(partial && dacc && dpartial && adc_scale && part && rows > 0 && ncol > 0 && col0 >= 0 && slices >= 1 &&
+                     slice_bit >= 1, "adc_bwd: bad arguments");
+    B200_REQUIRE((gain_noise == nullptr) == (offset_noise == nullptr), "adc_bwd: gain and offset noise come together");
+    B200_REQUIRE(ld_d >= ncol, "adc_bwd: gradient pitch too small");
+    adc_bwd_kernel<<<q_grid(rows * ncol, 256, 4), 256, 0, as_stream(stream)>>>(
+        partial, ld_p, dacc, ld_g, static_cast<__nv_bfloat16*>(dpartial), ld_d, rows, ncol, col0, slices, slice_bit,
+        adc_scale, adc_range, gain_noise, offset_noise, part);
+    B200_CHECK_LAUNCH("adc_bwd");
+    return B200SD_OK;
+}
+
+extern "C" int b200sd_bit_split_bwd(const void* ddigits, int64_t ld_d, void* dcodes, int64_t ld_q, int64_t rows, int32_t c,
+                                    int32_t slices, int32_t slice_bit, void* stream) {
+    B200_REQUIRE(ddigits && dcodes && rows >= 0 && slices >= 1 && slice_bit >= 1, "bit_split_bwd: bad arguments");
+    B200_REQUIRE(Q_SHAPE_OK(c, ld_d) && Q_SHAPE_OK(c, ld_q), "bit_split_bwd: channels and pitches must be multiples of 8");
+    if (rows == 0) return B200SD_OK;
+    bit_split_bwd_kernel<<<q_grid(rows * (c / 8), 256), 256, 0, as_stream(stream)>>>(
+        static_cast<const __nv_bfloat16*>(ddigits), ld_d, static_cast<__nv_bfloat16*>(dcodes), ld_q, rows, c, slices,
+        slice_bit);
+    B200_CHECK_LAUNCH("bit_split_bwd");
     return B200SD_OK;
 }

@@ -96,3 +96,71 @@ def rescale_step_sizes(module, weight_bit_old, input_bit_old, output_bit_old):
                            ("output", module.output_bit, output_bit_old)):
         if new != old:
             getattr(module, f"step_size_{name}").data /= 2 ** (new - old)
+
+
+# ---------------------------------------------------------------------------------------------- ADDA block products
+from . import ops  # noqa: E402
+
+
+class AddaFn(Function):
+    """Integer accumulation of a compute-in-memory layer (cim_layers/layers_qn_lsq_adda_cim.py:430-480):
+    acc[M, N] = sum over mapped blocks and DAC slices of 2^(k*slice_bit) * ADC(alpha * digits_k[:, rows] @ W[cols, rows]^T).
+    x: bf16 activation rows; w: fp32 [N, K] weight codes (+ noise), differentiable; alpha: 0-dim ADC scale.
+    Backward recomputes digits and block products (no fp32 block products are kept between forward and backward):
+    per block one ADC-backward kernel, a dgrad GEMM (accumulated over column blocks through the residual epilogue) and a
+    wgrad GEMM; then bit-split and LSQ-code backward."""
+
+    @staticmethod
+    def forward(ctx, x, step_in, w, alpha, cfg):
+        ctx.save_for_backward(x, step_in, w, alpha)
+        ctx.cfg = cfg
+        return AddaFn._run(x, step_in.detach(), w.detach(), alpha.detach(), cfg)
+
+    @staticmethod
+    def _digits(x, step_in, cfg):
+        return rt.bit_split(x, cfg["slices"], cfg["slice_bit"], cfg["input_bit"], step=step_in, qp=cfg["qp_in"],
+                            numel=cfg["numel_in"])
+
+    @staticmethod
+    def _run(x, step_in, w, alpha, cfg):
+        M, N = x.shape[0], w.shape[0]
+        digits = AddaFn._digits(x, step_in, cfg)
+        a1 = alpha.reshape(1).float()
+        out = torch.zeros(M, N, device=x.device, dtype=torch.float32)
+        for r0, rn, c0, cn in cfg["blocks"]:
+            part = rt.linear(digits[:, r0:r0 + rn], ops.pack_linear_weight(w[c0:c0 + cn, r0:r0 + rn]), out_dtype=torch.float32)
+            rt.adc_combine(part, out, M, cn, c0, cfg["slices"], cfg["slice_bit"], a1, cfg["R"], cfg["gain_noise"],
+                           cfg["offset_noise"])
+        return out
+
+    @staticmethod
+    def backward(ctx, dacc):
+        x, step_in, w, alpha = ctx.saved_tensors
+        cfg = ctx.cfg
+        M, K = x.shape
+        N = w.shape[0]
+        S, sb = cfg["slices"], cfg["slice_bit"]
+        dacc = dacc.float().contiguous()
+        wd = w.detach()
+        a1 = alpha.detach().reshape(1).float()
+        digits = AddaFn._digits(x, step_in.detach(), cfg)
+        ddigits = torch.zeros(S * M, K, device=x.device, dtype=torch.bfloat16)
+        dw = torch.zeros(N, K, device=x.device, dtype=torch.float32)
+        dalpha = torch.zeros(1, device=x.device, dtype=torch.float32)
+        seen = set()
+        for r0, rn, c0, cn in cfg["blocks"]:
+            wb = wd[c0:c0 + cn, r0:r0 + rn]
+            part = rt.linear(digits[:, r0:r0 + rn], ops.pack_linear_weight(wb), out_dtype=torch.float32)
+            dp, da = rt.adc_bwd(part, dacc, M, cn, c0, S, sb, a1, cfg["R"], cfg["gain_noise"], cfg["offset_noise"])
+            dalpha = dalpha + da
+            view = ddigits[:, r0:r0 + rn]
+            rt.linear(dp[:, :cn], ops.pack_linear_weight(wb.t()), out=view, residual=view if r0 in seen else None)
+            seen.add(r0)
+            kp = (rn + 63) // 64 * 64
+            dwp = rt.wgrad([rt.make_src(digits[:, r0:r0 + rn], 1, 1, S * M, rn, ld=K)], [(0, 0, 0, 0, kp // 64)],
+                           rt.make_src(dp, 1, 1, S * M, cn, ld=dp.stride(0)), cn, 1, 1, S * M)
+            dw[c0:c0 + cn, r0:r0 + rn] = dwp[:, :rn]
+        dxq = rt.bit_split_bwd(ddigits, M, K, S, sb)
+        dx, ds = rt.lsq_quant_bwd(dxq, x, step_in.detach(), cfg["qp_in"], codes=True, numel=cfg["numel_in"])
+        return (dx if ctx.needs_input_grad[0] else None), ds.reshape(step_in.shape), dw, \
+            dalpha.reshape(alpha.shape).to(alpha.dtype), None

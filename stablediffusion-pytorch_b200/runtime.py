@@ -23,7 +23,7 @@ EXPORTS = [
     "b200sd_layernorm_mod", "b200sd_layernorm_mod_bwd", "b200sd_rows_per_slot", "b200sd_gate_residual",
     "b200sd_gate_residual_bwd", "b200sd_relu_bwd", "b200sd_unpatchify", "b200sd_patchify",
     "b200sd_lsq_init_step", "b200sd_lsq_quant", "b200sd_lsq_quant_bwd", "b200sd_lsq_quant_bwd_blocks", "b200sd_bit_split",
-    "b200sd_adc_combine",
+    "b200sd_adc_combine", "b200sd_adc_bwd", "b200sd_adc_bwd_blocks", "b200sd_bit_split_bwd",
 ]
 
 
@@ -118,6 +118,9 @@ def lib():
         L.b200sd_lsq_quant_bwd_blocks.argtypes = [i64, i32]
         L.b200sd_bit_split.argtypes = [vp, i32, i64, vp, i64, i64, i32, i32, i32, i32, vp, f32, f32, vp]
         L.b200sd_adc_combine.argtypes = [vp, i64, vp, i64, i64, i32, i32, i32, i32, vp, f32, vp, vp, i32, vp]
+        L.b200sd_adc_bwd.argtypes = [vp, i64, vp, i64, vp, i64, i64, i32, i32, i32, i32, vp, f32, vp, vp, vp, vp]
+        L.b200sd_adc_bwd_blocks.argtypes = [i64, i32]
+        L.b200sd_bit_split_bwd.argtypes = [vp, i64, vp, i64, i64, i32, i32, i32, vp]
         _lib = L
     return _lib
 
@@ -692,3 +695,22 @@ def adc_combine(partial, out, rows, ncol, col0, slices, slice_bit, adc_scale, ad
                                    slice_bit, adc_scale.data_ptr(), float(adc_range), _p(gain_noise), _p(offset_noise),
                                    1 if accumulate else 0, stream_ptr()), "adc_combine")
     return out
+
+
+def adc_bwd(partial, dacc, rows, ncol, col0, slices, slice_bit, adc_scale, adc_range, gain_noise=None, offset_noise=None):
+    """-> (d partial bf16 [slices * rows, pad8(ncol)] (padding columns zero), d(adc_scale) fp32 [1])."""
+    ld = (ncol + 7) // 8 * 8
+    dp = (torch.zeros if ld != ncol else torch.empty)(slices * rows, ld, device=partial.device, dtype=torch.bfloat16)
+    nb = int(lib().b200sd_adc_bwd_blocks(rows, ncol))
+    part = torch.empty(nb, device=partial.device, dtype=torch.float32)
+    check(lib().b200sd_adc_bwd(_p(partial), partial.stride(0), _p(dacc), dacc.stride(0), _p(dp), ld, rows, ncol, col0,
+                               slices, slice_bit, adc_scale.data_ptr(), float(adc_range), _p(gain_noise), _p(offset_noise),
+                               _p(part), stream_ptr()), "adc_bwd")
+    return dp, reduce_f32(part, 1, nb, 1, 1, torch.empty(1, device=partial.device, dtype=torch.float32))
+
+
+def bit_split_bwd(ddigits, rows, c, slices, slice_bit):
+    dq = torch.empty(rows, c, device=ddigits.device, dtype=torch.bfloat16)
+    check(lib().b200sd_bit_split_bwd(_p(ddigits), ddigits.stride(0), _p(dq), c, rows, c, slices, slice_bit, stream_ptr()),
+          "bit_split_bwd")
+    return dq

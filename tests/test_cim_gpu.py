@@ -344,3 +344,137 @@ def test_dit_with_lsq_leaves_vs_oracle():
     assert not missing, missing[:6]
     steps = [p.grad.abs().item() for k, p in model.named_parameters() if "step_size" in k]
     assert sum(1 for s in steps if s > 0) > 0.9 * len(steps)
+
+
+@pytest.mark.parametrize("name", ["adda_linear_288", "adda_linear_1152", "adda_linear_noise"])
+def test_adda_linear_backward_vs_oracle(name):
+    """Gradients of the ADDA layer (input, weight, bias, the three LSQ step sizes and the ADC gain) against autograd
+    through the oracle (itself pinned to the reference's gradients exactly, tests/test_oracle.py)."""
+    dev = _dev()
+    from oracle import cim_torch as OC
+    from cim_layers.layers_qn_lsq_adda_cim import Linear_lsq_adda_cim
+    f = load_golden("cim_layers")[name]
+    cfg = f["cfg"]
+    w = f["init"]["weight"]
+    layer = Linear_lsq_adda_cim(w.shape[1], w.shape[0], weight_bit=cfg["weight_bit"], input_bit=cfg["input_bit"],
+                                output_bit=cfg["output_bit"], noise_scale=cfg["noise_scale"], dac_bit=cfg["dac_bit"],
+                                adc_bit=cfg["adc_bit"], adc_gain_1_scale=cfg["adc_gain_1_scale"],
+                                adc_gain_range=cfg["adc_gain_range"], adc_adjust_mode=cfg["adc_adjust_mode"],
+                                gain_noise_scale=cfg.get("gain_noise_scale", 0),
+                                offset_noise_scale=cfg.get("offset_noise_scale", 0), bias=True)
+    # start from the state AFTER the reference's first forward (step sizes and ADC gain initialised)
+    state = dict(f["init"])
+    state.update(f["after"])
+    layer.load_state_dict(state)
+    layer = layer.to(dev).train()
+    layer.__dict__["_gain_init_pending"] = False
+    layer.weight_noise_unit = f["unit"].float().to(dev)
+    layer.weight_mapping_info = f["mapping"]
+    noise = {}
+    if cfg.get("gain_noise_scale"):
+        layer.gain_noise, layer.offset_noise = f["gain_noise"].to(dev), f["offset_noise"].to(dev)
+        noise = dict(gain_noise=f["gain_noise"], offset_noise=f["offset_noise"])
+    x2 = _bfr(f["x2"])
+    tgt = f["target"]
+    p = {k: v.clone().requires_grad_(True) for k, v in state.items()}
+    xo = x2.clone().requires_grad_(True)
+    ref = OC.adda_linear(p, cfg, xo, f["mapping"], f["unit"].float(), **noise)
+    ((ref - tgt) ** 2).mean().backward()
+    p16 = {k: v.clone().requires_grad_(True) for k, v in state.items()}
+    with torch.autocast("cpu", dtype=torch.bfloat16):
+        ref16 = OC.adda_linear(p16, cfg, x2, f["mapping"], f["unit"].float(), **noise)
+    ((ref16.float() - tgt) ** 2).mean().backward()
+    xd = x2.to(dev).requires_grad_(True)
+    out = layer(xd)
+    ((out - tgt.to(dev)) ** 2).mean().backward()
+    torch.cuda.synchronize()
+    got = {k: v.grad.cpu() for k, v in layer.named_parameters()}
+    got["x"] = xd.grad.cpu()
+    want = {k: v.grad for k, v in p.items()}
+    want["x"] = xo.grad
+    for k in want:
+        err = ((got[k] - want[k]).norm() / want[k].norm().clamp_min(1e-20)).item()
+        yard = ((p16[k].grad - want[k]).norm() / want[k].norm().clamp_min(1e-20)).item() if k in p16 else 0.0
+        print(f"   {name} grad {k}: rel-L2 {err:.3e} (oracle under bf16 autocast: {yard:.3e})")
+        # scalar gradients (step sizes, ADC gain) are ill-conditioned sums; everything is gated on the reference's own
+        # bf16-autocast error like the LSQ layers
+        assert err < max(8e-2 if want[k].dim() == 0 else 4e-2, 1.5 * yard), k
+
+
+def test_dit_with_adda_leaves_vs_oracle_and_trains():
+    """configs[4] structure: every Linear and the mask conv of the DiT as ADDA compute-in-memory layers (8-bit inputs in
+    two 4-bit DAC slices, 4-bit weights, 8-bit ADC, array height 576) — forward against the oracle DiT with the oracle
+    ADDA layer in every leaf (lazily initialised parameters copied from the oracle's warm-up), then a captured training
+    step with finite gradients for every parameter including step sizes and ADC gains."""
+    dev = _dev()
+    from oracle import cim_torch as OC
+    from oracle import dit_torch as OD
+    from cim_layers.layers_qn_lsq_adda_cim import Conv2d_lsq_adda_cim, Linear_lsq_adda_cim, gen_weight_split_dict
+    from models.transformer import DIT
+    from util import cond_of, l2err, randomise_zero_init
+    fx = load_golden("dit_small_cond")
+    cfg, inp = fx["config"], fx["inputs"]
+    torch.manual_seed(fx["seed"])
+    model = DIT(4, cfg)
+    randomise_zero_init(model, fx["rand_seed"])
+    acfg = dict(weight_bit=4, input_bit=8, output_bit=8, noise_scale=0.0, dac_bit=5, adc_bit=8,
+                adc_gain_1_scale=9.071428571, adc_gain_range=[1 / 64, 1 / 64], adc_adjust_mode='current')
+    ocfg = dict(acfg, adc_gain_min=1 / 64, adc_gain_max=1 / 64)
+    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    states, maps = {}, {}
+
+    class _W:   # the mapper only looks at module.weight
+        def __init__(self, w):
+            self.weight = w
+
+    def leaf(name, x, w, b, conv):
+        p = states.setdefault(name, {"step_size_input": torch.tensor(1.0), "step_size_output": torch.tensor(1.0),
+                                     "step_size_weight": torch.tensor(1.0), "adc_gain": torch.tensor(1 / 64)})
+        p["weight"] = w.reshape(w.shape[0], -1)
+        if b is not None:
+            p["bias"] = b
+        maps.setdefault(name, gen_weight_split_dict(_W(p["weight"]), [576, 2048]))
+        if conv is not None:   # 1x1 convolution = the linear layer applied per pixel (Unfold order (c, 1, 1))
+            y = OC.adda_linear(p, ocfg, x.permute(0, 2, 3, 1).contiguous(), maps[name], None)
+            return y.permute(0, 3, 1, 2).contiguous()
+        return OC.adda_linear(p, ocfg, x, maps[name], None)
+
+    cond = cond_of(inp, cfg)
+    OD.LEAF = leaf
+    try:
+        with torch.no_grad():
+            OD.dit_forward(sd, cfg, inp["x"], inp["t"], cond)
+            ref = OD.dit_forward(sd, cfg, inp["x"], inp["t"], cond)
+            with torch.autocast("cpu", dtype=torch.bfloat16):
+                ref16 = OD.dit_forward(sd, cfg, inp["x"], inp["t"], cond).float()
+    finally:
+        OD.LEAF = None
+    model = _convert(model, Linear_lsq_adda_cim, Conv2d_lsq_adda_cim, **acfg).to(dev).eval()
+    with torch.no_grad():
+        for name, m in model.named_modules():
+            if name in states:
+                for k in ("step_size_input", "step_size_output", "step_size_weight", "adc_gain"):
+                    getattr(m, k).copy_(states[name][k])
+                m.__dict__["_gain_init_pending"] = False
+                m.weight_mapping_info = gen_weight_split_dict(m, [576, 2048])
+        condd = cond_of(inp, cfg, dev)
+        out = model(inp["x"].to(dev), inp["t"].to(dev), condd)
+        out_again = model(inp["x"].to(dev), inp["t"].to(dev), condd)
+    torch.cuda.synchronize()
+    err, yard = l2err(out.cpu(), ref), l2err(ref16, ref)
+    print(f"DiT with ADDA leaves: ours-vs-oracle rel-L2 {err:.3e}; oracle bf16-autocast-vs-fp32 {yard:.3e}")
+    assert torch.equal(out, out_again)
+    assert err < max(5e-2, 1.5 * yard)
+    model.train()
+    x, t = inp["x"].to(dev), inp["t"].to(dev)
+    tgt = torch.randn(x.shape, generator=torch.Generator().manual_seed(1)).to(dev)
+    for _ in range(2):
+        model.zero_grad()
+        loss = torch.nn.functional.mse_loss(model(x, t, condd), tgt)
+        loss.backward()
+    torch.cuda.synchronize()
+    missing = [(k, "none" if p.grad is None else "nonfinite") for k, p in model.named_parameters()
+               if p.grad is None or not torch.isfinite(p.grad).all()]
+    assert not missing, (len(missing), missing[:40])
+    gains = [p.grad.abs().item() for k, p in model.named_parameters() if k.endswith("adc_gain")]
+    assert len(gains) == 26

@@ -106,5 +106,13 @@ def test_cim_oracle_vs_reference_golden():
                 y1 = OC.adda_linear(p, f["cfg"], f["x"], f["mapping"], unit, **noise)
                 for k, v in f["after"].items():
                     assert torch.equal(p[k], v), (name, k)
-                y2 = OC.adda_linear(p, f["cfg"], f["x2"], f["mapping"], unit, **noise)
-            assert torch.equal(y1, f["y1"]) and torch.equal(y2, f["y2"]), name
+            assert torch.equal(y1, f["y1"]), name
+            p2 = {k: v.clone().requires_grad_(True) for k, v in p.items()}
+            x2 = f["x2"].clone().requires_grad_(True)
+            y2 = OC.adda_linear(p2, f["cfg"], x2, f["mapping"], unit, **noise)
+            assert torch.equal(y2.detach(), f["y2"]), name
+            ((y2 - f["target"]) ** 2).mean().backward()
+            got = {k: v.grad for k, v in p2.items()}
+            got["x"] = x2.grad
+            for k, g in f["grads"].items():
+                assert relerr(got[k], g) < 1e-5, (name, k)
