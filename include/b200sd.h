@@ -170,15 +170,22 @@ int b200sd_groupnorm_apply(const void* x, int64_t ld_x, void* y, int64_t ld_y, c
 /* Backward of GroupNorm (+activation), given the forward's partial statistics (same stats0/stats1 as
  * b200sd_groupnorm_apply), x, and dy = dL/d act(GN(x)):  dx = dL/dx (+ add, an optional extra gradient of x with the
  * same geometry, e.g. the ResNet shortcut's). part: fp32 scratch [n, b200sd_rowblocks(n, hw, c), c, 2]; ab (optional):
- * fp32 [n, c, 2] receiving per-image (sum dz, sum dz*xhat), whose sums over n are dbeta and dgamma. */
+ * fp32 [n, c, 2] receiving per-image (sum dz, sum dz*xhat), whose sums over n are dbeta and dgamma.
+ * counter (optional): one zero-initialised uint32 in device memory, not shared with a concurrently running launch.
+ * With it the last CTA to finish folds ab over the batch into dgamma[c] / dbeta[c] (fixed order) and leaves the
+ * counter at 0 again — no second kernel. */
 int b200sd_rowblocks(int64_t n, int64_t hw, int c);
 int b200sd_groupnorm_bwd(const void* x, int64_t ld_x, const void* dy, int64_t ld_dy, const void* add, int64_t ld_add,
                          void* dx, int64_t ld_dx, const float* stats0, int p0, int ld_s0, int c_split,
                          const float* stats1, int p1, int ld_s1, const float* gamma, const float* beta, int64_t n,
-                         int64_t hw, int c, int groups, float eps, int act, float* part, float* ab, void* stream);
+                         int64_t hw, int c, int groups, float eps, int act, float* part, float* ab, float* dgamma,
+                         float* dbeta, uint32_t* counter, void* stream);
 /* Per-(image, row block) column sums of a bf16 [n, hw, ld_x] tensor: part fp32 [n, b200sd_rowblocks(n, hw, c), c]
- * (bias gradients; the per-image time-embedding gradient of models/blocks.py:118). */
-int b200sd_colsum(const void* x, int64_t ld_x, int64_t n, int64_t hw, int c, float* part, void* stream);
+ * (bias gradients; the per-image time-embedding gradient of models/blocks.py:118). With `counter` (as in
+ * b200sd_groupnorm_bwd) the last CTA also folds the partials in fixed order into out: fp32 [n, c] if per_image
+ * else [c]. */
+int b200sd_colsum(const void* x, int64_t ld_x, int64_t n, int64_t hw, int c, float* part, float* out, int per_image,
+                  uint32_t* counter, void* stream);
 /* out[b, j] (+)= sum_r in[(b*rows + r)*cols*col_stride + j*col_stride], fp32, fixed order. */
 int b200sd_reduce_f32(const float* in, int64_t batch, int64_t rows, int64_t cols, int64_t col_stride, float* out,
                       int accumulate, void* stream);
@@ -320,6 +327,34 @@ int b200sd_adc_bwd_blocks(int64_t rows, int32_t ncol);
 /* Backward of b200sd_bit_split (layers_utils_adda.py:178-183): dcodes = sum_k ddigits_k / (slices * 2^(k*slice_bit)). */
 int b200sd_bit_split_bwd(const void* ddigits, int64_t ld_d, void* dcodes, int64_t ld_q, int64_t rows, int32_t c,
                          int32_t slices, int32_t slice_bit, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Weight-side data movement of a training step (csrc/pack.cu).
+ * ------------------------------------------------------------------------------------------------------------- */
+
+/* One job: packed[r, t * cp + c] = bf16(src[r * s_r + c * s_c + tap_off[t]]) for c < cin, 0 for cin <= c < cp; the
+ * K-major matrices b200sd_igemm / b200sd_wgrad read, from parameters in the reference layouts (nn.Conv2d
+ * [Cout, Cin, kh, kw], nn.ConvTranspose2d [Cin, Cout, 4, 4], nn.Linear [N, K]); forward, transposed and
+ * flipped-tap (dgrad) forms differ only in strides. tile0 / tiles_c are the launch geometry: a job owns
+ * ceil(rows / 32) * (cp / 32) consecutive tiles starting at tile0, tiles_c = cp / 32. */
+typedef struct {
+    const float* src;
+    void* dst;               /* bf16, already offset to the job's first column */
+    int64_t s_r, s_c, dst_ld;
+    int32_t rows, cin, cp, taps;
+    int32_t tap_off[16];
+    int32_t tile0, tiles_c;
+} b200sd_pack_job;
+
+/* jobs_dev: DEVICE array of n_jobs jobs sorted by tile0; n_tiles = total tiles. Every weight of a model in one launch. */
+int b200sd_pack_weights(const void* jobs_dev, int32_t n_jobs, int32_t n_tiles, void* stream);
+int b200sd_pack_job_size(void);
+
+/* Split-K partials of b200sd_wgrad ([splits, n_out, k_total], columns col0 + t * cp + c) -> the gradient in the
+ * parameter's own layout: out[co * s_co + c * s_ci + tap_off[t]] (+)= sum over splits (fixed order). */
+int b200sd_wgrad_scatter(const float* partial, int32_t splits, int32_t n_out, int32_t k_total, int32_t col0, int32_t cin,
+                         int32_t cp, int32_t taps, const int32_t* tap_off, float* out, int64_t s_co, int64_t s_ci,
+                         int32_t accumulate, void* stream);
 
 #ifdef __cplusplus
 }

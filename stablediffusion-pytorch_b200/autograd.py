@@ -18,8 +18,32 @@ has two consumers, SiLU on the (B, 512) time embedding, and un-packing weight gr
 import torch
 from torch.autograd import Function
 
+from . import bank as BK
 from . import ops
 from . import runtime as rt
+
+
+def _bank(*ws):
+    """The active weight bank if every given weight is parameter storage it knows (captured training step), else None."""
+    b = BK.ACTIVE
+    if b is None or not all(b.knows(w) for w in ws):
+        return None
+    return b
+
+
+def _phase_taps(cp):
+    """Sub-pixel phases of ConvTranspose2d(4, 2, 1): ([(ky, kx)] taps, igemm segments) per output parity (py, px)."""
+    taps = {0: ((1, 0), (3, -1)), 1: ((0, 1), (2, 0))}
+    out = []
+    for py in (0, 1):
+        for px in (0, 1):
+            tl, segs = [], []
+            for ky, dy in taps[py]:
+                for kx, dx in taps[px]:
+                    tl.append((ky, kx))
+                    segs.append((0, dy, dx, 0, cp // 64))
+            out.append((tl, segs))
+    return out
 
 
 def _pad8(c):
@@ -64,7 +88,8 @@ class LinearFn(Function):
     def forward(ctx, x, weight, bias, residual, rows_per_img, want_stats, act=None):
         M, K = x.shape
         N = weight.shape[0]
-        wp = ops.pack_linear_weight(weight)
+        b = _bank(weight)
+        wp = b.linear(weight) if b else ops.pack_linear_weight(weight)
         st = None
         if want_stats and rows_per_img:
             st = _new_stats(M // rows_per_img, 1, rows_per_img, N, x.device)
@@ -77,6 +102,7 @@ class LinearFn(Function):
         ctx.has_bias, ctx.has_res = bias is not None, residual is not None
         stats_t = st[0] if st is not None else torch.empty(0, device=x.device)
         ctx.mark_non_differentiable(stats_t)
+        ctx.set_materialize_grads(False)   # no zero-filled gradient tensor for the statistics output
         return out, stats_t
 
     @staticmethod
@@ -89,19 +115,90 @@ class LinearFn(Function):
             dy = rt.relu_bwd(dy, y_act)
         dx = dw = db = dres = None
         if ctx.needs_input_grad[0]:
-            wt = ops.pack_linear_weight(weight.detach().t())  # [K, N_pad64]
+            b = _bank(weight)
+            wt = b.linear_t(weight) if b else ops.pack_linear_weight(weight.detach().t())  # [K, N_pad64]
             dx = torch.empty(M, _pad8(K), device=x.device, dtype=torch.bfloat16)[:, :K]
             rt.linear(dy, wt, out=dx)
         if ctx.needs_input_grad[1]:
             kp = (K + 63) // 64 * 64
             src = rt.make_src(x, 1, 1, M, K, ld=x.stride(0))
-            dwp = rt.wgrad([src], [(0, 0, 0, 0, kp // 64)], rt.make_src(dy, 1, 1, M, N, ld=dy.stride(0)), N, 1, 1, M)
-            dw = dwp[:, :K]
+            b = _bank(weight)
+            gv = b.grad_view(weight) if b else None
+            dwp = rt.wgrad([src], [(0, 0, 0, 0, kp // 64)], rt.make_src(dy, 1, 1, M, N, ld=dy.stride(0)), N, 1, 1, M,
+                           scatter=None if gv is None else [(gv, 0, K, kp, 1, K, 1, [0])])
+            dw = gv if gv is not None else dwp[:, :K]
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = rt.colsum(dy, 1, M, N) if N % 8 == 0 else dy.float().sum(0)
         if ctx.has_res and ctx.needs_input_grad[3]:
             dres = dy
         return dx, dw, db, dres, None, None, None
+
+
+class CrossProjFn(Function):
+    """The two input projections of a cross-attention site from ONE packed in_proj parameter (nn.MultiheadAttention,
+    blocks.py:138-141): q = xq @ W[:C]^T + b[:C];  kv = xkv @ W[C:]^T + b[C:]. One autograd node for the parameter:
+    its gradient is assembled in place (row ranges of one [3C, C] tensor) instead of two sliced gradients that
+    autograd would zero-pad and add."""
+
+    @staticmethod
+    def forward(ctx, xq, xkv, weight, bias, C):
+        bk = _bank(weight)
+        wd = weight.detach()
+        wq = bk.linear(weight, 0, C) if bk else ops.pack_linear_weight(wd[:C])
+        wkv = bk.linear(weight, C, 2 * C) if bk else ops.pack_linear_weight(wd[C:])
+        bf = None if bias is None else bias.detach().float()
+        q = torch.empty(xq.shape[0], C, device=xq.device, dtype=torch.bfloat16)
+        kv = torch.empty(xkv.shape[0], 2 * C, device=xq.device, dtype=torch.bfloat16)
+        rt.linear(xq, wq, bias=None if bf is None else bf[:C], out=q)
+        rt.linear(xkv, wkv, bias=None if bf is None else bf[C:], out=kv)
+        ctx.save_for_backward(xq, xkv, weight)
+        ctx.C, ctx.has_bias = C, bias is not None
+        ctx.set_materialize_grads(False)
+        return q, kv
+
+    @staticmethod
+    def backward(ctx, dq, dkv):
+        xq, xkv, weight = ctx.saved_tensors
+        C = ctx.C
+        K = weight.shape[1]
+        kp = (K + 63) // 64 * 64
+        dev = xq.device
+        bk = _bank(weight)
+        wd = weight.detach()
+        dxq = dxkv = dw = db = None
+        parts = ((dq, xq, 0, C, 0), (dkv, xkv, C, 2 * C, 1))
+        if ctx.needs_input_grad[2]:
+            gv = bk.grad_view(weight) if bk else None
+            dw = gv if gv is not None else torch.zeros(3 * C, K, device=dev, dtype=torch.float32)
+            if gv is not None and (dq is None or dkv is None):
+                (dw[:C] if dq is None else dw[C:]).zero_()
+        if ctx.has_bias and ctx.needs_input_grad[3]:
+            db = torch.empty(3 * C, device=dev, dtype=torch.float32)
+            if dq is None or dkv is None or C % 8:
+                db.zero_()
+        for dy, x, r0, rn, slot in parts:
+            if dy is None:
+                continue
+            dy = _rows(dy, rn)
+            M = x.shape[0]
+            if ctx.needs_input_grad[slot]:
+                wt = bk.linear_t(weight, r0, rn) if bk else ops.pack_linear_weight(wd[r0:r0 + rn].t())
+                dx = torch.empty(M, _pad8(K), device=dev, dtype=torch.bfloat16)[:, :K]
+                rt.linear(dy, wt, out=dx)
+                if slot == 0:
+                    dxq = dx
+                else:
+                    dxkv = dx
+            if dw is not None:
+                rt.wgrad([rt.make_src(x, 1, 1, M, K, ld=x.stride(0))], [(0, 0, 0, 0, kp // 64)],
+                         rt.make_src(dy, 1, 1, M, rn, ld=dy.stride(0)), rn, 1, 1, M,
+                         scatter=[(dw[r0:r0 + rn], 0, K, kp, 1, K, 1, [0])])
+            if db is not None:
+                if rn % 8 == 0:
+                    rt.colsum(dy, 1, M, rn, out=db[r0:r0 + rn])
+                else:
+                    db[r0:r0 + rn] = dy.float().sum(0)
+        return dxq, dxkv, dw, db, None
 
 
 # ---------------------------------------------------------------------------------------------------- Conv 3x3 / 1x1
@@ -113,12 +210,15 @@ class ConvSameFn(Function):
     def forward(ctx, x, weight, bias, rowbias, x2, w2, b2, geom, want_stats, out_f32):
         n, h, w, cin, cin2 = geom
         cout, k = weight.shape[0], weight.shape[2]
-        wmat = ops.pack_conv_weight(weight)
+        bk = _bank(weight) if x2 is None else _bank(weight, w2)
+        wmat = bk.conv(weight, w2) if bk else ops.pack_conv_weight(weight)
         b = None if bias is None else bias.detach().float()
         extra = None
         if x2 is not None:
-            wmat = torch.cat([wmat, ops.pack_conv_weight(w2)], dim=1).contiguous()
-            b = (b if b is not None else 0) + (b2.detach().float() if b2 is not None else 0)
+            if not bk:
+                wmat = torch.cat([wmat, ops.pack_conv_weight(w2)], dim=1).contiguous()
+            if b2 is not None:
+                b = b2.detach().float() if b is None else b + b2.detach().float()
             extra = (x2, cin2, x2.stride(0))
         st = _new_stats(n, h, w, cout, x.device) if (want_stats and not out_f32) else None
         out = torch.empty(n * h * w, _pad8(cout), device=x.device,
@@ -129,6 +229,7 @@ class ConvSameFn(Function):
         ctx.geom, ctx.flags = geom, (bias is not None, rowbias is not None, b2 is not None)
         stats_t = st[0] if st is not None else torch.empty(0, device=x.device)
         ctx.mark_non_differentiable(stats_t)
+        ctx.set_materialize_grads(False)   # no zero-filled gradient tensor for the statistics output
         return out, stats_t
 
     @staticmethod
@@ -142,13 +243,15 @@ class ConvSameFn(Function):
         dx = dw = db = drb = dx2 = dw2 = db2 = None
         if ctx.needs_input_grad[0]:
             # dgrad of a stride-1 'same' conv = the same conv with taps flipped and in/out channels swapped
-            wd = ops.pack_conv_weight(weight.detach().flip(2, 3).transpose(0, 1))
+            bk = _bank(weight)
+            wd = bk.conv_dgrad(weight) if bk else ops.pack_conv_weight(weight.detach().flip(2, 3).transpose(0, 1))
             full = _grad_buf(x, cin)
             dx = full[:, :cin]
             ops.conv_same(dy, n, h, w, cout, wd, cin, k, ld_x=dy.stride(0), out=dx)
             dx = full if full.shape[1] == x.shape[1] else dx
         if x2 is not None and ctx.needs_input_grad[4]:
-            wt = ops.pack_linear_weight(w2.detach().reshape(cout, cin2).t())
+            bk = _bank(w2)
+            wt = bk.linear_t(w2) if bk else ops.pack_linear_weight(w2.detach().reshape(cout, cin2).t())
             full = _grad_buf(x2, cin2)
             dx2 = full[:, :cin2]
             rt.linear(dy, wt, out=dx2)
@@ -160,10 +263,22 @@ class ConvSameFn(Function):
             if x2 is not None:
                 srcs.append(rt.make_src(x2, n, h, w, cin2, ld=x2.stride(0)))
                 segs.append((1, 0, 0, 0, ops._pad64(cin2) // 64))
-            dwp = rt.wgrad(srcs, segs, rt.make_src(dy, n, h, w, cout, ld=dy.stride(0)), cout, n, h, w)
-            dw = dwp[:, :k * k * cp].reshape(cout, k * k, cp)[:, :, :cin].permute(0, 2, 1).reshape(cout, cin, k, k)
-            if x2 is not None:
-                dw2 = dwp[:, k * k * cp:k * k * cp + cin2].reshape(cout, cin2, 1, 1)
+            bk = _bank(weight) if x2 is None else _bank(weight, w2)
+            gv = bk.grad_view(weight) if bk else None
+            gv2 = bk.grad_view(w2) if (bk and x2 is not None) else None
+            sc = None
+            if gv is not None and (x2 is None or gv2 is not None):
+                kk = k * k
+                sc = [(gv, 0, cin, cp, kk, cin * kk, kk, list(range(kk)))]
+                if x2 is not None:
+                    sc.append((gv2, kk * cp, cin2, ops._pad64(cin2), 1, cin2, 1, [0]))
+            dwp = rt.wgrad(srcs, segs, rt.make_src(dy, n, h, w, cout, ld=dy.stride(0)), cout, n, h, w, scatter=sc)
+            if sc is not None:
+                dw, dw2 = gv, gv2
+            else:
+                dw = dwp[:, :k * k * cp].reshape(cout, k * k, cp)[:, :, :cin].permute(0, 2, 1).reshape(cout, cin, k, k)
+                if x2 is not None:
+                    dw2 = dwp[:, k * k * cp:k * k * cp + cin2].reshape(cout, cin2, 1, 1)
         if (has_b and ctx.needs_input_grad[2]) or (has_b2 and ctx.needs_input_grad[6]) or has_rb:
             if cout % 8 == 0:
                 per = rt.colsum(dy, n, h * w, cout, per_image=True)  # fp32 [n, cout]
@@ -196,13 +311,15 @@ class ConvDownFn(Function):
         cout = weight.shape[0]
         st = _new_stats(n, h // 2, w // 2, cout, x.device) if want_stats else None
         out = torch.empty(n * (h // 2) * (w // 2), cout, device=x.device, dtype=torch.bfloat16)
-        ops.conv_down4x4(x, n, h, w, cin, ops.pack_conv_weight(weight), cout,
+        bk = _bank(weight)
+        ops.conv_down4x4(x, n, h, w, cin, bk.conv(weight) if bk else ops.pack_conv_weight(weight), cout,
                          bias=None if bias is None else bias.detach().float(), ld_x=x.stride(0), out=out,
                          stats=_stats_arg(st))
         ctx.save_for_backward(x, weight)
         ctx.geom, ctx.has_bias = geom, bias is not None
         stats_t = st[0] if st is not None else torch.empty(0, device=x.device)
         ctx.mark_non_differentiable(stats_t)
+        ctx.set_materialize_grads(False)   # no zero-filled gradient tensor for the statistics output
         return out, stats_t
 
     @staticmethod
@@ -215,7 +332,8 @@ class ConvDownFn(Function):
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
             # adjoint of Conv2d(4, 2, 1) with weight [co, ci] = ConvTranspose2d(4, 2, 1) with the same tensor as [in=co, out=ci]
-            phases = ops.pack_convT_weight(weight.detach())
+            bk = _bank(weight)
+            phases = bk.convT_phases(weight, _phase_taps(ops._pad64(cout))) if bk else ops.pack_convT_weight(weight.detach())
             dx = torch.empty(n * h * w, cin, device=x.device, dtype=torch.bfloat16)
             ops.conv_up4x4(dy, n, oh, ow, cout, phases, cin, ld_x=dy.stride(0), out=dx)
         if ctx.needs_input_grad[1]:
@@ -223,8 +341,11 @@ class ConvDownFn(Function):
             ld = x.stride(0)
             srcs = [rt.make_src(x, n, oh, ow, cin, ld=ld, sy=2, sx=2, oy=py, ox=px, hh=h, ww=w) for py in (0, 1)
                     for px in (0, 1)]
-            dwp = rt.wgrad(srcs, _down_segs(cp), rt.make_src(dy, n, oh, ow, cout, ld=dy.stride(0)), cout, n, oh, ow)
-            dw = dwp.reshape(cout, 16, cp)[:, :, :cin].permute(0, 2, 1).reshape(cout, cin, 4, 4)
+            bk = _bank(weight)
+            gv = bk.grad_view(weight) if bk else None
+            dwp = rt.wgrad(srcs, _down_segs(cp), rt.make_src(dy, n, oh, ow, cout, ld=dy.stride(0)), cout, n, oh, ow,
+                           scatter=None if gv is None else [(gv, 0, cin, cp, 16, cin * 16, 16, list(range(16)))])
+            dw = gv if gv is not None else dwp.reshape(cout, 16, cp)[:, :, :cin].permute(0, 2, 1).reshape(cout, cin, 4, 4)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = rt.colsum(dy, n, oh * ow, cout)
         return dx, dw, db, None, None
@@ -243,12 +364,15 @@ class ConvUpFn(Function):
         cout = weight.shape[1]
         st = _new_stats(n, h, w, cout, x.device, phases=4) if want_stats else None
         out = torch.empty(n * 4 * h * w, cout, device=x.device, dtype=torch.bfloat16)
-        ops.conv_up4x4(x, n, h, w, cin, ops.pack_convT_weight(weight), cout,
+        bk = _bank(weight)
+        phases = bk.convT_phases(weight, _phase_taps(ops._pad64(cin))) if bk else ops.pack_convT_weight(weight)
+        ops.conv_up4x4(x, n, h, w, cin, phases, cout,
                        bias=None if bias is None else bias.detach().float(), ld_x=x.stride(0), out=out, stats=st)
         ctx.save_for_backward(x, weight)
         ctx.geom, ctx.has_bias = geom, bias is not None
         stats_t = st[0] if st is not None else torch.empty(0, device=x.device)
         ctx.mark_non_differentiable(stats_t)
+        ctx.set_materialize_grads(False)   # no zero-filled gradient tensor for the statistics output
         return out, stats_t
 
     @staticmethod
@@ -261,12 +385,15 @@ class ConvUpFn(Function):
         if ctx.needs_input_grad[0]:
             # adjoint of ConvTranspose2d(4, 2, 1) with weight [ci, co] = Conv2d(4, 2, 1) with the same tensor as [out=ci, in=co]
             dx = torch.empty(n * h * w, cin, device=x.device, dtype=torch.bfloat16)
-            ops.conv_down4x4(dy, n, 2 * h, 2 * w, cout, ops.pack_conv_weight(weight.detach()), cin, ld_x=dy.stride(0),
-                             out=dx)
+            bk = _bank(weight)
+            ops.conv_down4x4(dy, n, 2 * h, 2 * w, cout, bk.conv(weight) if bk else ops.pack_conv_weight(weight.detach()),
+                             cin, ld_x=dy.stride(0), out=dx)
         if ctx.needs_input_grad[1]:
             cp = ops._pad64(cin)
             src = rt.make_src(x, n, h, w, cin, ld=x.stride(0))
-            dw = torch.empty_like(weight)
+            bk = _bank(weight)
+            gv = bk.grad_view(weight) if bk else None
+            dw = gv if gv is not None else torch.empty_like(weight)
             ld = dy.stride(0)
             for py in (0, 1):
                 for px in (0, 1):
@@ -276,6 +403,10 @@ class ConvUpFn(Function):
                             segs.append((0, ddy, ddx, 0, cp // 64))
                             taps.append((ky, kx))
                     dyv = rt.make_src(dy, n, h, w, cout, ld=ld, sy=2, sx=2, oy=py, ox=px, hh=2 * h, ww=2 * w)
+                    if gv is not None:   # dw[ci, co, ky, kx]: rows of the GEMM are co, channels ci
+                        rt.wgrad([src], segs, dyv, cout, n, h, w,
+                                 scatter=[(gv, 0, cin, cp, 4, 16, cout * 16, [ky * 4 + kx for ky, kx in taps])])
+                        continue
                     dwp = rt.wgrad([src], segs, dyv, cout, n, h, w).reshape(cout, 4, cp)
                     for i, (ky, kx) in enumerate(taps):
                         dw[:, :, ky, kx] = dwp[:, i, :cin].t()

@@ -303,13 +303,50 @@ __global__ void __launch_bounds__(256)
     }
 }
 
+// Fixed-order tail reduction by the LAST CTA of a launch (no second kernel, no atomics on the data): every CTA
+// publishes its partials, bumps `counter`; whichever CTA sees total-1 owns the tail and leaves the counter at 0 for the
+// next launch. The summation order does not depend on which CTA that is.
+__device__ __forceinline__ bool last_cta_arrives(unsigned int* counter, unsigned int total) {
+    __shared__ unsigned int s_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int t = atomicAdd(counter, 1u);
+        s_last = (t == total - 1u) ? 1u : 0u;
+        if (s_last) *counter = 0u;
+    }
+    __syncthreads();
+    if (s_last) __threadfence();
+    return s_last != 0u;
+}
+
+// out[b][c] = sum over r of in[b][r][c * col_stride], r ascending in four interleaved chains (fixed order)
+__device__ __forceinline__ void tail_reduce(const float* in, long long batch, long long rows, long long cols,
+                                            long long col_stride, float* __restrict__ out) {
+    const long long total = batch * cols;
+    for (long long i = threadIdx.x; i < total; i += blockDim.x) {
+        const long long b = i / cols, cidx = i - b * cols;
+        const float* p = in + b * rows * cols * col_stride + cidx * col_stride;
+        const long long step = cols * col_stride;
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        long long r = 0;
+        for (; r + 4 <= rows; r += 4) {
+            s0 += __ldcg(p + r * step), s1 += __ldcg(p + (r + 1) * step);
+            s2 += __ldcg(p + (r + 2) * step), s3 += __ldcg(p + (r + 3) * step);
+        }
+        for (; r < rows; ++r) s0 += __ldcg(p + r * step);
+        out[i] = (s0 + s1) + (s2 + s3);
+    }
+}
+
 __global__ void __launch_bounds__(256)
     gn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, const __nv_bfloat16* __restrict__ dy,
                         long long ld_dy, const __nv_bfloat16* __restrict__ add, long long ld_add,
                         __nv_bfloat16* __restrict__ dx, long long ld_dx, StatSeg s0, int c_split, StatSeg s1,
                         const float* __restrict__ gamma, const float* __restrict__ beta, long long hw, int c, int groups,
                         float eps, int act, int rows_per_block, int rpp, const float* __restrict__ part, int pb,
-                        float* __restrict__ ab /* [n][c][2] or null */) {
+                        float* __restrict__ ab /* [n][c][2] or null */, float* __restrict__ dgamma,
+                        float* __restrict__ dbeta, unsigned int* counter) {
     extern __shared__ float gn_sm[];
     float* sc = gn_sm;
     float* sh = sc + c;
@@ -338,6 +375,10 @@ __global__ void __launch_bounds__(256)
         g12[2 * g] = a * inv_cnt, g12[2 * g + 1] = b * inv_cnt;
     }
     __syncthreads();
+    if (counter && blockIdx.x == 0 && last_cta_arrives(counter, gridDim.y)) {   // dgamma / dbeta over the batch
+        tail_reduce(ab + 1, 1, gridDim.y, c, 2, dgamma);
+        tail_reduce(ab, 1, gridDim.y, c, 2, dbeta);
+    }
     const int cv = c >> 3;
     const int v = tid % cv, r0 = tid / cv;
     if (r0 >= rpp) return;
@@ -398,7 +439,7 @@ __global__ void reduce_f32_kernel(const float* __restrict__ in, long long batch,
 // per-(image, row block) column sums of a bf16 [n, hw, ld] tensor -> fp32 part[n][gridDim.x][c]
 __global__ void __launch_bounds__(256)
     colsum_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, long long hw, int c, int rows_per_block, int rpp,
-                  float* __restrict__ part) {
+                  float* __restrict__ part, float* __restrict__ out, int per_image, unsigned int* counter) {
     extern __shared__ float gn_sm[];  // [rpp][c]
     const int img = blockIdx.y, tid = threadIdx.x;
     const int cv = c >> 3;
@@ -429,6 +470,10 @@ __global__ void __launch_bounds__(256)
         float s = 0.f;
         for (int k = 0; k < rpp; ++k) s += gn_sm[k * c + i];
         dst[i] = s;
+    }
+    if (counter && last_cta_arrives(counter, gridDim.x * gridDim.y)) {
+        if (per_image) tail_reduce(part, gridDim.y, gridDim.x, c, 1, out);
+        else tail_reduce(part, 1, static_cast<long long>(gridDim.x) * gridDim.y, c, 1, out);
     }
 }
 
@@ -562,8 +607,10 @@ extern "C" int b200sd_groupnorm_bwd(const void* x, int64_t ld_x, const void* dy,
                                     int64_t ld_add, void* dx, int64_t ld_dx, const float* stats0, int p0, int ld_s0,
                                     int c_split, const float* stats1, int p1, int ld_s1, const float* gamma,
                                     const float* beta, int64_t n, int64_t hw, int c, int groups, float eps, int act,
-                                    float* part, float* ab, void* stream) {
+                                    float* part, float* ab, float* dgamma, float* dbeta, uint32_t* counter,
+                                    void* stream) {
     B200_REQUIRE(x && dy && dx && stats0 && part, "groupnorm_bwd: null pointer");
+    B200_REQUIRE(!counter || (ab && dgamma && dbeta), "groupnorm_bwd: fused dgamma/dbeta needs ab, dgamma and dbeta");
     B200_REQUIRE(groups > 0 && c > 0 && c % groups == 0 && c % 8 == 0 && c <= 2048,
                  "groupnorm_bwd: channels must be divisible by groups and by 8, <= 2048");
     B200_REQUIRE(ld_x % 8 == 0 && ld_dy % 8 == 0 && ld_dx % 8 == 0 && (!add || ld_add % 8 == 0),
@@ -593,13 +640,15 @@ extern "C" int b200sd_groupnorm_bwd(const void* x, int64_t ld_x, const void* dy,
     gn_bwd_apply_kernel<<<grid, g.threads, sm2, st>>>(
         static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<const __nv_bfloat16*>(dy), ld_dy,
         static_cast<const __nv_bfloat16*>(add), ld_add, static_cast<__nv_bfloat16*>(dx), ld_dx, s0, c_split, s1, gamma,
-        beta, hw, c, groups, eps, act, g.rows_per_block, g.rpp, part, g.blocks_per_img, ab);
+        beta, hw, c, groups, eps, act, g.rows_per_block, g.rpp, part, g.blocks_per_img, ab, dgamma, dbeta, counter);
     B200_CHECK_LAUNCH("groupnorm_bwd_apply");
     return B200SD_OK;
 }
 
-extern "C" int b200sd_colsum(const void* x, int64_t ld_x, int64_t n, int64_t hw, int c, float* part, void* stream) {
+extern "C" int b200sd_colsum(const void* x, int64_t ld_x, int64_t n, int64_t hw, int c, float* part, float* out,
+                             int per_image, uint32_t* counter, void* stream) {
     B200_REQUIRE(x && part, "colsum: null pointer");
+    B200_REQUIRE(!counter || out, "colsum: fused total needs an output");
     B200_REQUIRE(c > 0 && c % 8 == 0 && c <= 2048 && ld_x % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0,
                  "colsum: needs channels %% 8 == 0 (<= 2048) and 16-byte aligned rows");
     B200_REQUIRE(n <= 65535, "colsum: batch exceeds grid limit");
@@ -607,7 +656,7 @@ extern "C" int b200sd_colsum(const void* x, int64_t ld_x, int64_t n, int64_t hw,
     const RowGeom g = row_geom(n, hw, c);
     dim3 grid((unsigned)g.blocks_per_img, (unsigned)n);
     colsum_kernel<<<grid, g.threads, (size_t)g.rpp * c * sizeof(float), as_stream(stream)>>>(
-        static_cast<const __nv_bfloat16*>(x), ld_x, hw, c, g.rows_per_block, g.rpp, part);
+        static_cast<const __nv_bfloat16*>(x), ld_x, hw, c, g.rows_per_block, g.rpp, part, out, per_image, counter);
     B200_CHECK_LAUNCH("colsum");
     return B200SD_OK;
 }

@@ -380,10 +380,9 @@ def cross_attention(a, norm, mha, ctx_proj_mod, ctx, lk, cache=None):
     xn = group_norm(a, norm)
     if training():
         w, b = _mha_params(mha)
-        q, _ = AG.LinearFn.apply(xn.t, w[:C], None if b is None else b[:C], None, None, False)
         _require_leaf(ctx_proj_mod, (nn.Linear,), "Linear")
         cp, _ = AG.LinearFn.apply(ctx, ctx_proj_mod.weight, ctx_proj_mod.bias, None, None, False)
-        kv, _ = AG.LinearFn.apply(cp, w[C:], None if b is None else b[C:], None, None, False)
+        q, kv = AG.CrossProjFn.apply(xn.t, cp, w, b, C)
         o = AG.AttentionFn.apply(q, kv, (a.n, heads, a.hw, lk, C // heads))
         return _out_proj(o, mha, a)
     pk = _mha_weights(mha)

@@ -11,6 +11,7 @@ sequence once and replay it:
 import torch
 
 from . import engine as E
+from . import bank as BK
 from . import runtime as rt
 
 ENABLE_FORWARD_GRAPHS = True
@@ -223,6 +224,7 @@ class TrainGraph:
             raise rt.B200Error("training graph requested but nothing requires grad")
 
         def forward():
+            self.bank.refresh()
             ci, k = {}, 0
             if has_text:
                 ci["text"], k = self.cond[k], k + 1
@@ -239,15 +241,26 @@ class TrainGraph:
             if p.requires_grad:
                 off += (p.numel() + 63) // 64 * 64
         self.flat = torch.zeros(max(off, 64), device=dev, dtype=torch.float32)
+        # packed bf16 forms of every parameter in one launch per step; weight gradients written straight into `flat`
+        self.bank = BK.WeightBank(swap.standins, self.flat, self.slots)
+        BK.ACTIVE = self.bank
+        try:
+            self._build(forward, wrt, dev)
+        finally:
+            BK.ACTIVE = None
 
+    def _build(self, forward, wrt, dev):
         with torch.autocast("cuda", enabled=False), torch.enable_grad():
             side = torch.cuda.Stream(device=dev)
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
-                for _ in range(self.WARMUP):  # lazy kernel attributes, allocator warm-up
+                for _ in range(self.WARMUP):  # lazy kernel attributes, allocator warm-up, weight-bank discovery
+                    self.bank.begin_pass()
                     out = forward()
                     torch.autograd.grad((out,), wrt, (torch.ones_like(out),), allow_unused=True)
+                    self.bank.finalize()
                 del out
+            self.bank.begin_pass()
             torch.cuda.current_stream().wait_stream(side)
             pool = torch.cuda.graph_pool_handle()
             self.fwd_graph, self.bwd_graph = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
@@ -269,7 +282,10 @@ class TrainGraph:
                     if g is None:
                         self.unused.add(i)
                         continue
-                    views.append(self.flat[sl[0]:sl[0] + sl[1]].view(sl[2]))
+                    v = self.flat[sl[0]:sl[0] + sl[1]].view(sl[2])
+                    if g.dtype == torch.float32 and g.data_ptr() == v.data_ptr():
+                        continue   # the weight-gradient kernel wrote it in place
+                    views.append(v)
                     srcs.append(g if g.dtype == torch.float32 else g.float())
                 if views:
                     torch._foreach_copy_(views, srcs)

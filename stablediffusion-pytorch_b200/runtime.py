@@ -24,11 +24,18 @@ EXPORTS = [
     "b200sd_gate_residual_bwd", "b200sd_relu_bwd", "b200sd_unpatchify", "b200sd_patchify",
     "b200sd_lsq_init_step", "b200sd_lsq_quant", "b200sd_lsq_quant_bwd", "b200sd_lsq_quant_bwd_blocks", "b200sd_bit_split",
     "b200sd_adc_combine", "b200sd_adc_bwd", "b200sd_adc_bwd_blocks", "b200sd_bit_split_bwd",
+    "b200sd_pack_weights", "b200sd_pack_job_size", "b200sd_wgrad_scatter",
 ]
 
 
 class Src(C.Structure):
     _fields_ = [("base", C.c_void_p), ("dims", C.c_int32 * 4), ("strides", C.c_int64 * 3)]
+
+
+class PackJob(C.Structure):
+    _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("s_r", C.c_int64), ("s_c", C.c_int64), ("dst_ld", C.c_int64),
+                ("rows", C.c_int32), ("cin", C.c_int32), ("cp", C.c_int32), ("taps", C.c_int32),
+                ("tap_off", C.c_int32 * 16), ("tile0", C.c_int32), ("tiles_c", C.c_int32)]
 
 
 class Seg(C.Structure):
@@ -91,8 +98,8 @@ def lib():
                                              f32, i32, vp]
         L.b200sd_rowblocks.argtypes = [i64, i64, i32]
         L.b200sd_groupnorm_bwd.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, vp, i32, i32, i32, vp, i32, i32, vp, vp, i64,
-                                           i64, i32, i32, f32, i32, vp, vp, vp]
-        L.b200sd_colsum.argtypes = [vp, i64, i64, i64, i32, vp, vp]
+                                           i64, i32, i32, f32, i32, vp, vp, vp, vp, vp, vp]
+        L.b200sd_colsum.argtypes = [vp, i64, i64, i64, i32, vp, vp, i32, vp, vp]
         L.b200sd_reduce_f32.argtypes = [vp, i64, i64, i64, i64, vp, i32, vp]
         L.b200sd_attention.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, i64, i32, i32, i32, i32, f32, vp]
         L.b200sd_attention_lse.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, vp, i64, i32, i32, i32, i32, f32, vp]
@@ -121,6 +128,9 @@ def lib():
         L.b200sd_adc_bwd.argtypes = [vp, i64, vp, i64, vp, i64, i64, i32, i32, i32, i32, vp, f32, vp, vp, vp, vp]
         L.b200sd_adc_bwd_blocks.argtypes = [i64, i32]
         L.b200sd_bit_split_bwd.argtypes = [vp, i64, vp, i64, i64, i32, i32, i32, vp]
+        L.b200sd_pack_weights.argtypes = [vp, i32, i32, vp]
+        L.b200sd_pack_job_size.argtypes = []
+        L.b200sd_wgrad_scatter.argtypes = [vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, i64, i64, i32, vp]
         _lib = L
     return _lib
 
@@ -339,9 +349,11 @@ def linear(a, weight, bias=None, act=None, residual=None, out=None, out_dtype=to
                  rowbias=rowbias, gate=gate, residual=residual, res_strides=rs, act=act, stats=stats)
 
 
-def wgrad(srcs, segs, dy_src, n_out, on, oh, ow, out=None, accumulate=False):
+def wgrad(srcs, segs, dy_src, n_out, on, oh, ow, out=None, accumulate=False, scatter=None):
     """Packed weight gradient fp32 [n_out, 64 * sum(nchunk)] of an igemm leaf: srcs/segs as in the forward call,
-    dy_src a (C = n_out, W, H, N) Src view of the bf16 output gradient."""
+    dy_src a (C = n_out, W, H, N) Src view of the bf16 output gradient.
+    scatter = [(out_tensor, col0, cin, cp, taps, s_co, s_ci, tap_off), ...]: instead of the packed matrix, write each
+    column range straight into a parameter-layout gradient tensor (fixed-order sum over the split-K partials)."""
     k_total = 64 * sum(sg[4] for sg in segs)
     dev = torch.device("cuda", torch.cuda.current_device())
     splits = int(lib().b200sd_wgrad_splits(n_out, k_total, on, oh, ow))
@@ -359,6 +371,12 @@ def wgrad(srcs, segs, dy_src, n_out, on, oh, ow, out=None, accumulate=False):
     check(lib().b200sd_wgrad(C.byref(p), stream_ptr()), "wgrad")
     k_alg = sum(max(0, min(nch * 64, srcs[si].dims[0] - c0)) for si, _, _, c0, nch in segs)
     _pe(tok, "wgrad", 2.0 * on * oh * ow * n_out * k_alg, (on * oh * ow, n_out, k_alg))
+    if scatter is not None:
+        for dst, col0, cin, cp, taps, s_co, s_ci, tap_off in scatter:
+            offs = (C.c_int32 * 16)(*(list(tap_off) + [0] * (16 - len(tap_off))))
+            check(lib().b200sd_wgrad_scatter(_p(partial), splits, n_out, k_total, col0, cin, cp, taps, offs, _p(dst),
+                                             s_co, s_ci, 1 if accumulate else 0, stream_ptr()), "wgrad_scatter")
+        return None
     if splits == 1 and not accumulate and out is None:
         return partial[0]
     if out is None:
@@ -409,19 +427,33 @@ def groupnorm_bwd(x, dy, n, hw, c, groups, gamma, beta, segs, eps=1e-5, act=None
     part = torch.empty(n, pb, c, 2, device=dev, dtype=torch.float32)
     ab = torch.empty(n, c, 2, device=dev, dtype=torch.float32)
     dx = torch.empty(n * hw, c, device=dev, dtype=torch.bfloat16)
+    dgamma = torch.empty(c, device=dev, dtype=torch.float32)
+    dbeta = torch.empty(c, device=dev, dtype=torch.float32)
     (s0, p0, l0, c0) = segs[0]
     s1, p1, l1 = (segs[1][0], segs[1][1], segs[1][2]) if len(segs) > 1 else (None, 0, 0)
     tok = _pb()
     check(lib().b200sd_groupnorm_bwd(_p(x), ld_x, _p(dy), ld_dy, _p(add), 0 if add is None else add.stride(0), _p(dx), c,
                                       _p(s0), p0, l0, c0 if len(segs) > 1 else c, _p(s1), p1, l1, _p(gamma), _p(beta), n,
-                                      hw, c, groups, float(eps), _ACT[act], _p(part), _p(ab), stream_ptr()),
+                                      hw, c, groups, float(eps), _ACT[act], _p(part), _p(ab), _p(dgamma), _p(dbeta),
+                                      tail_counter(dev), stream_ptr()),
           "groupnorm_bwd")
     _pe(tok, "groupnorm_bwd", (10.0 + (2.0 if add is not None else 0.0)) * n * hw * c, (n, hw, c))
-    dgamma = torch.empty(c, device=dev, dtype=torch.float32)
-    dbeta = torch.empty(c, device=dev, dtype=torch.float32)
-    reduce_f32(ab.view(-1)[1:], 1, n, c, 2, dgamma)
-    reduce_f32(ab, 1, n, c, 2, dbeta)
     return dx, dgamma, dbeta
+
+
+_TAIL = {}
+
+
+def tail_counter(dev):
+    """Address of a zeroed uint32 for a kernel whose last CTA folds the launch's partials (csrc/norm.cu
+    last_cta_arrives). Every such kernel returns its counter to 0, so a counter can be reused by any later launch; the
+    pool hands them out round robin so that launches close together in time (other streams) never share one."""
+    key = dev.index if dev.index is not None else torch.cuda.current_device()
+    ent = _TAIL.get(key)
+    if ent is None:
+        ent = _TAIL[key] = [torch.zeros(4096, device=dev, dtype=torch.int32), 0]
+    ent[1] = (ent[1] + 1) % 4096
+    return ent[0].data_ptr() + 4 * ent[1]
 
 
 def reduce_f32(src, batch, rows, cols, col_stride, out, accumulate=False):
@@ -430,21 +462,29 @@ def reduce_f32(src, batch, rows, cols, col_stride, out, accumulate=False):
     return out
 
 
-def colsum(x, n, hw, c, ld_x=None, per_image=False):
-    """Column sums of a bf16 [n*hw, ld] tensor: fp32 [c] (bias gradient) or [n, c] (per-image)."""
+def colsum(x, n, hw, c, ld_x=None, per_image=False, out=None):
+    """Column sums of a bf16 [n*hw, ld] tensor: fp32 [c] (bias gradient) or [n, c] (per-image). `out`: a contiguous
+    fp32 destination (e.g. a slice of a larger bias gradient)."""
     ld_x = x.stride(0) if ld_x is None else ld_x
     if c > 2048:  # wide matrices (packed QKV, the batched time-embedding bank): column slabs of 2048
+        if out is not None and not per_image:
+            for j in range(0, c, 2048):
+                colsum(x[:, j:min(j + 2048, c)], n, hw, min(2048, c - j), ld_x=ld_x, out=out[j:min(j + 2048, c)])
+            return out
         parts = [colsum(x[:, j:min(j + 2048, c)], n, hw, min(2048, c - j), ld_x=ld_x, per_image=per_image)
                  for j in range(0, c, 2048)]
-        return torch.cat(parts, dim=-1)
+        res = torch.cat(parts, dim=-1)
+        return res if out is None else out.copy_(res)
     pb = int(lib().b200sd_rowblocks(n, hw, c))
     part = torch.empty(n, pb, c, device=x.device, dtype=torch.float32)
+    if out is None:
+        out = torch.empty((n, c) if per_image else (c,), device=x.device, dtype=torch.float32)
+    assert out.is_contiguous() and out.dtype == torch.float32 and out.numel() == (n * c if per_image else c)
     tok = _pb()
-    check(lib().b200sd_colsum(_p(x), ld_x, n, hw, c, _p(part), stream_ptr()), "colsum")
+    check(lib().b200sd_colsum(_p(x), ld_x, n, hw, c, _p(part), _p(out), 1 if per_image else 0, tail_counter(x.device),
+                              stream_ptr()), "colsum")
     _pe(tok, "colsum", 2.0 * n * hw * c, (n, hw, c))
-    if per_image:
-        return reduce_f32(part, n, pb, c, 1, torch.empty(n, c, device=x.device, dtype=torch.float32))
-    return reduce_f32(part, 1, n * pb, c, 1, torch.empty(c, device=x.device, dtype=torch.float32))
+    return out
 
 
 def attention(q, k, v, batch, heads, lq, lk, d, scale=None, out=None):
@@ -714,3 +754,8 @@ def bit_split_bwd(ddigits, rows, c, slices, slice_bit):
     check(lib().b200sd_bit_split_bwd(_p(ddigits), ddigits.stride(0), _p(dq), c, rows, c, slices, slice_bit, stream_ptr()),
           "bit_split_bwd")
     return dq
+
+
+def pack_weights(table, n_jobs, n_tiles):
+    """table: uint8 device tensor holding n_jobs PackJob structs sorted by tile0."""
+    check(lib().b200sd_pack_weights(table.data_ptr(), n_jobs, n_tiles, stream_ptr()), "pack_weights")
