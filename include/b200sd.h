@@ -180,10 +180,11 @@ int b200sd_groupnorm_bwd(const void* x, int64_t ld_x, const void* dy, int64_t ld
                          const float* stats1, int p1, int ld_s1, const float* gamma, const float* beta, int64_t n,
                          int64_t hw, int c, int groups, float eps, int act, float* part, float* ab, float* dgamma,
                          float* dbeta, uint32_t* counter, void* stream);
-/* Per-(image, row block) column sums of a bf16 [n, hw, ld_x] tensor: part fp32 [n, b200sd_rowblocks(n, hw, c), c]
- * (bias gradients; the per-image time-embedding gradient of models/blocks.py:118). With `counter` (as in
- * b200sd_groupnorm_bwd) the last CTA also folds the partials in fixed order into out: fp32 [n, c] if per_image
- * else [c]. */
+/* Per-(image, row block) column sums of a bf16 [n, hw, ld_x] tensor: part fp32 [n, b200sd_colsum_blocks(n, hw, c), c]
+ * (bias gradients; the per-image time-embedding gradient of models/blocks.py:118). With `counter` — here
+ * ceil(c / 64) zero-initialised uint32, one per 64-channel slab — the last CTA of each slab also folds that slab's
+ * partials in fixed order into out: fp32 [n, c] if per_image else [c], and leaves the counters at 0. */
+int b200sd_colsum_blocks(int64_t n, int64_t hw, int c);
 int b200sd_colsum(const void* x, int64_t ld_x, int64_t n, int64_t hw, int c, float* part, float* out, int per_image,
                   uint32_t* counter, void* stream);
 /* out[b, j] (+)= sum_r in[(b*rows + r)*cols*col_stride + j*col_stride], fp32, fixed order. */

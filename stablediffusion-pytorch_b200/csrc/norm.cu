@@ -436,23 +436,26 @@ __global__ void reduce_f32_kernel(const float* __restrict__ in, long long batch,
     }
 }
 
-// per-(image, row block) column sums of a bf16 [n, hw, ld] tensor -> fp32 part[n][gridDim.x][c]
+// Column sums of a bf16 [n, hw, ld] tensor. CTA = (64-channel slab, row block, image): 8 lanes x 16 B cover the
+// slab's 128 B of a row, 32 row lanes stride down the block. part[n][pb][c] holds the per-block sums; with `counter`
+// (one zeroed uint32 PER SLAB) the last CTA of each slab folds its 64 columns over the row blocks, so the tails of a
+// launch run in parallel, one per slab, each over a few dozen partial rows.
 __global__ void __launch_bounds__(256)
-    colsum_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, long long hw, int c, int rows_per_block, int rpp,
+    colsum_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, long long hw, int c, int rows_per_block,
                   float* __restrict__ part, float* __restrict__ out, int per_image, unsigned int* counter) {
-    extern __shared__ float gn_sm[];  // [rpp][c]
-    const int img = blockIdx.y, tid = threadIdx.x;
-    const int cv = c >> 3;
-    const int v = tid % cv, r0 = tid / cv;
-    if (r0 < rpp) {
-        float a[8];
+    __shared__ float red[32][65];
+    const int slab = blockIdx.x, rb = blockIdx.y, img = blockIdx.z, pb = gridDim.y;
+    const int tid = threadIdx.x, v = tid & 7, lane_r = tid >> 3;
+    const int ch = slab * 64 + v * 8;
+    float a[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) a[j] = 0.f;
-        const long long row_begin = static_cast<long long>(blockIdx.x) * rows_per_block;
+    for (int j = 0; j < 8; ++j) a[j] = 0.f;
+    if (ch < c) {
+        const long long row_begin = static_cast<long long>(rb) * rows_per_block;
         long long row_end = row_begin + rows_per_block;
         if (row_end > hw) row_end = hw;
-        const __nv_bfloat16* xs = x + static_cast<long long>(img) * hw * ld_x + v * 8;
-        for (long long rr = row_begin + r0; rr < row_end; rr += rpp) {
+        const __nv_bfloat16* xs = x + static_cast<long long>(img) * hw * ld_x + ch;
+        for (long long rr = row_begin + lane_r; rr < row_end; rr += 32) {
             const uint4 u = *reinterpret_cast<const uint4*>(xs + rr * ld_x);
             const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
 #pragma unroll
@@ -461,19 +464,38 @@ __global__ void __launch_bounds__(256)
                 a[2 * j] += f.x, a[2 * j + 1] += f.y;
             }
         }
+    }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) gn_sm[r0 * c + v * 8 + j] = a[j];
-    }
+    for (int j = 0; j < 8; ++j) red[lane_r][v * 8 + j] = a[j];
     __syncthreads();
-    float* dst = part + (static_cast<long long>(img) * gridDim.x + blockIdx.x) * c;
-    for (int i = tid; i < c; i += blockDim.x) {
+    const int ncol = min(64, c - slab * 64);
+    if (tid < ncol) {
         float s = 0.f;
-        for (int k = 0; k < rpp; ++k) s += gn_sm[k * c + i];
-        dst[i] = s;
+#pragma unroll 8
+        for (int k = 0; k < 32; ++k) s += red[k][tid];
+        part[(static_cast<long long>(img) * pb + rb) * c + slab * 64 + tid] = s;
     }
-    if (counter && last_cta_arrives(counter, gridDim.x * gridDim.y)) {
-        if (per_image) tail_reduce(part, gridDim.y, gridDim.x, c, 1, out);
-        else tail_reduce(part, 1, static_cast<long long>(gridDim.x) * gridDim.y, c, 1, out);
+    if (counter && last_cta_arrives(counter + slab, gridDim.y * gridDim.z)) {
+        const float* p0 = part + slab * 64;
+        if (per_image) {
+            for (int i = tid; i < static_cast<int>(gridDim.z) * ncol; i += 256) {
+                const int im = i / ncol, col = i - im * ncol;
+                const float* p = p0 + static_cast<long long>(im) * pb * c + col;
+                float s = 0.f;
+                for (int k = 0; k < pb; ++k) s += __ldcg(p + static_cast<long long>(k) * c);
+                out[static_cast<long long>(im) * c + slab * 64 + col] = s;
+            }
+        } else {
+            // 4 row-block lanes per column, folded in fixed order
+            const int col = tid & 63, q = tid >> 6;
+            const long long rows = static_cast<long long>(pb) * gridDim.z;
+            float s = 0.f;
+            if (col < ncol)
+                for (long long k = q; k < rows; k += 4) s += __ldcg(p0 + k * c + col);
+            red[q][col] = s;
+            __syncthreads();
+            if (tid < ncol) out[slab * 64 + tid] = (red[0][tid] + red[1][tid]) + (red[2][tid] + red[3][tid]);
+        }
     }
 }
 
@@ -645,18 +667,34 @@ extern "C" int b200sd_groupnorm_bwd(const void* x, int64_t ld_x, const void* dy,
     return B200SD_OK;
 }
 
+static int colsum_blocks(int64_t n, int64_t hw, int c) {
+    const long long slabs = (c + 63) / 64;
+    long long pb = (3ll * sm_count() + n * slabs - 1) / (n * slabs);
+    const long long max_pb = (hw + 63) / 64;          // at least two passes of the 32 row lanes per CTA
+    if (pb > max_pb) pb = max_pb;
+    if (pb > 65535) pb = 65535;
+    if (pb < 1) pb = 1;
+    return static_cast<int>(pb);
+}
+
+extern "C" int b200sd_colsum_blocks(int64_t n, int64_t hw, int c) {
+    if (n <= 0 || hw <= 0 || c <= 0 || c % 8) return 0;
+    return colsum_blocks(n, hw, c);
+}
+
 extern "C" int b200sd_colsum(const void* x, int64_t ld_x, int64_t n, int64_t hw, int c, float* part, float* out,
                              int per_image, uint32_t* counter, void* stream) {
     B200_REQUIRE(x && part, "colsum: null pointer");
     B200_REQUIRE(!counter || out, "colsum: fused total needs an output");
-    B200_REQUIRE(c > 0 && c % 8 == 0 && c <= 2048 && ld_x % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0,
-                 "colsum: needs channels %% 8 == 0 (<= 2048) and 16-byte aligned rows");
+    B200_REQUIRE(c > 0 && c % 8 == 0 && c <= 4096 && ld_x % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0,
+                 "colsum: needs channels %% 8 == 0 (<= 4096) and 16-byte aligned rows");
     B200_REQUIRE(n <= 65535, "colsum: batch exceeds grid limit");
     if (n == 0 || hw == 0) return B200SD_OK;
-    const RowGeom g = row_geom(n, hw, c);
-    dim3 grid((unsigned)g.blocks_per_img, (unsigned)n);
-    colsum_kernel<<<grid, g.threads, (size_t)g.rpp * c * sizeof(float), as_stream(stream)>>>(
-        static_cast<const __nv_bfloat16*>(x), ld_x, hw, c, g.rows_per_block, g.rpp, part, out, per_image, counter);
+    const int pb = colsum_blocks(n, hw, c);
+    const long long rpb = (hw + pb - 1) / pb;
+    dim3 grid((unsigned)((c + 63) / 64), (unsigned)pb, (unsigned)n);
+    colsum_kernel<<<grid, 256, 0, as_stream(stream)>>>(static_cast<const __nv_bfloat16*>(x), ld_x, hw, c, (int)rpb, part,
+                                                       out, per_image, counter);
     B200_CHECK_LAUNCH("colsum");
     return B200SD_OK;
 }

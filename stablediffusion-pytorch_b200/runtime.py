@@ -17,7 +17,7 @@ _ACT = {None: 0, "none": 0, "silu": 1, "relu": 2}
 
 EXPORTS = [
     "b200sd_last_error", "b200sd_version", "b200sd_launch_count", "b200sd_sched_add_noise",
-    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_attention_lse", "b200sd_attention_bwd", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_rowblocks", "b200sd_groupnorm_bwd", "b200sd_colsum",
+    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_attention_lse", "b200sd_attention_bwd", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_rowblocks", "b200sd_groupnorm_bwd", "b200sd_colsum", "b200sd_colsum_blocks",
     "b200sd_reduce_f32", "b200sd_attention",
     "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16",
     "b200sd_layernorm_mod", "b200sd_layernorm_mod_bwd", "b200sd_rows_per_slot", "b200sd_gate_residual",
@@ -99,6 +99,7 @@ def lib():
         L.b200sd_rowblocks.argtypes = [i64, i64, i32]
         L.b200sd_groupnorm_bwd.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, vp, i32, i32, i32, vp, i32, i32, vp, vp, i64,
                                            i64, i32, i32, f32, i32, vp, vp, vp, vp, vp, vp]
+        L.b200sd_colsum_blocks.argtypes = [i64, i64, i32]
         L.b200sd_colsum.argtypes = [vp, i64, i64, i64, i32, vp, vp, i32, vp, vp]
         L.b200sd_reduce_f32.argtypes = [vp, i64, i64, i64, i64, vp, i32, vp]
         L.b200sd_attention.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, i64, i32, i32, i32, i32, f32, vp]
@@ -451,9 +452,9 @@ def tail_counter(dev):
     key = dev.index if dev.index is not None else torch.cuda.current_device()
     ent = _TAIL.get(key)
     if ent is None:
-        ent = _TAIL[key] = [torch.zeros(4096, device=dev, dtype=torch.int32), 0]
+        ent = _TAIL[key] = [torch.zeros(4096 * 64, device=dev, dtype=torch.int32), 0]
     ent[1] = (ent[1] + 1) % 4096
-    return ent[0].data_ptr() + 4 * ent[1]
+    return ent[0].data_ptr() + 256 * ent[1]      # a run of 64 counters (colsum: one per 64-channel slab)
 
 
 def reduce_f32(src, batch, rows, cols, col_stride, out, accumulate=False):
@@ -466,16 +467,17 @@ def colsum(x, n, hw, c, ld_x=None, per_image=False, out=None):
     """Column sums of a bf16 [n*hw, ld] tensor: fp32 [c] (bias gradient) or [n, c] (per-image). `out`: a contiguous
     fp32 destination (e.g. a slice of a larger bias gradient)."""
     ld_x = x.stride(0) if ld_x is None else ld_x
-    if c > 2048:  # wide matrices (packed QKV, the batched time-embedding bank): column slabs of 2048
+    W = 4096
+    if c > W:  # very wide matrices (the batched time-embedding bank): column slabs
         if out is not None and not per_image:
-            for j in range(0, c, 2048):
-                colsum(x[:, j:min(j + 2048, c)], n, hw, min(2048, c - j), ld_x=ld_x, out=out[j:min(j + 2048, c)])
+            for j in range(0, c, W):
+                colsum(x[:, j:min(j + W, c)], n, hw, min(W, c - j), ld_x=ld_x, out=out[j:min(j + W, c)])
             return out
-        parts = [colsum(x[:, j:min(j + 2048, c)], n, hw, min(2048, c - j), ld_x=ld_x, per_image=per_image)
-                 for j in range(0, c, 2048)]
+        parts = [colsum(x[:, j:min(j + W, c)], n, hw, min(W, c - j), ld_x=ld_x, per_image=per_image)
+                 for j in range(0, c, W)]
         res = torch.cat(parts, dim=-1)
         return res if out is None else out.copy_(res)
-    pb = int(lib().b200sd_rowblocks(n, hw, c))
+    pb = int(lib().b200sd_colsum_blocks(n, hw, c))
     part = torch.empty(n, pb, c, device=x.device, dtype=torch.float32)
     if out is None:
         out = torch.empty((n, c) if per_image else (c,), device=x.device, dtype=torch.float32)
