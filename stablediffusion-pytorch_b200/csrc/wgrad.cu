@@ -316,10 +316,22 @@ extern "C" int b200sd_wgrad_splits(int n_out, int k_total, int on, int oh, int o
     const int k_blocks = (k_total + 63) / 64;
     const int BN = wg_bn(k_blocks);
     const long long base = (long long)((n_out + 127) / 128) * ((k_blocks * 64 + BN - 1) / BN);
-    long long s = (2ll * sm_count() + base - 1) / base;
-    if (s > chunks) s = chunks;
-    if (s > 64) s = 64;
-    if (s < 1) s = 1;
+    // Split-K depth by a small cost model (microseconds, fitted to the batch-16 UNet shapes on B200): each split adds a
+    // full fp32 copy of the gradient to write (here) and to read back (wgrad_scatter / wgrad_reduce), which costs more
+    // than the tensor-core time it saves once one wave of CTAs is busy:
+    //   rounds(s) * (chunks/s * t_chunk + t_tile_store) + s * tiles * t_tile_load
+    const double f = BN / 256.0;
+    const double t_chunk = 0.4 * f, t_store = 6.5 * f, t_load = 0.055 * f;
+    const int nsm = sm_count();
+    long long smax = chunks < 64 ? chunks : 64;
+    if (smax < 1) smax = 1;
+    long long s = 1;
+    double best = 1e30;
+    for (long long c = 1; c <= smax; ++c) {
+        const double rounds = (double)((base * c + nsm - 1) / nsm);
+        const double cost = rounds * ((double)((chunks + c - 1) / c) * t_chunk + t_store) + (double)(c * base) * t_load;
+        if (cost < best - 1e-9) best = cost, s = c;
+    }
     return (int)s;
 }
 

@@ -373,10 +373,12 @@ def wgrad(srcs, segs, dy_src, n_out, on, oh, ow, out=None, accumulate=False, sca
     k_alg = sum(max(0, min(nch * 64, srcs[si].dims[0] - c0)) for si, _, _, c0, nch in segs)
     _pe(tok, "wgrad", 2.0 * on * oh * ow * n_out * k_alg, (on * oh * ow, n_out, k_alg))
     if scatter is not None:
+        tok = _pb()
         for dst, col0, cin, cp, taps, s_co, s_ci, tap_off in scatter:
             offs = (C.c_int32 * 16)(*(list(tap_off) + [0] * (16 - len(tap_off))))
             check(lib().b200sd_wgrad_scatter(_p(partial), splits, n_out, k_total, col0, cin, cp, taps, offs, _p(dst),
                                              s_co, s_ci, 1 if accumulate else 0, stream_ptr()), "wgrad_scatter")
+        _pe(tok, "wgrad_scatter", 4.0 * (splits + 1) * n_out * k_total, (splits, n_out, k_total))
         return None
     if splits == 1 and not accumulate and out is None:
         return partial[0]
