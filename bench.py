@@ -543,7 +543,12 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=
         else:
             from sdb200.parallel import DataParallel
             net = DataParallel(model, device_ids=[dev.index], broadcast_buffers=False)
-    opt = torch.optim.Adam(model.parameters(), lr=1e-5)
+    fused = args.train_opt == "fused"
+    if fused:
+        from sdb200.optim import FusedAdam
+        opt = FusedAdam(model.parameters(), lr=1e-5, max_grad_norm=1.0, ema_params=ema.parameters(), ema_decay=0.999)
+    else:
+        opt = torch.optim.Adam(model.parameters(), lr=1e-5)
     sched = LinearNoiseScheduler(T_STEPS, 0.00085, 0.012)
     x_h, text_h, mask_h = synth_inputs(B, ucfg, rank)
     g = torch.Generator().manual_seed(SEED + 5 + rank)
@@ -563,11 +568,14 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=
             loss = torch.nn.functional.mse_loss(pred, noise)
         opt.zero_grad(set_to_none=True)
         loss.backward()
-        torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
-        opt.step()
-        with torch.no_grad():
-            torch._foreach_mul_(list(ema.parameters()), 0.999)
-            torch._foreach_add_(list(ema.parameters()), list(model.parameters()), alpha=0.001)
+        if fused:
+            opt.step()      # clip_grad_norm_(1.0) + finite check + Adam + EMA: two launches (sdb200/optim.py)
+        else:
+            torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+            opt.step()
+            with torch.no_grad():
+                torch._foreach_mul_(list(ema.parameters()), 0.999)
+                torch._foreach_add_(list(ema.parameters()), list(model.parameters()), alpha=0.001)
         return loss.item() if from_host else loss.detach()
 
     out = {}
@@ -592,7 +600,8 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=
         "steps": K, "warmup": W, "batch_per_gpu": B, "global_batch": B * world, "dtype": "bf16",
         "model": tag, "params": sum(p.numel() for p in ema_params),
         "algorithmic_tflops": 3 * gflop_fwd * 1e9 * B / (out["value"][1] / 1e3) / 1e12,
-        "optimizer": "Adam + clip_grad_norm_(1.0) + EMA (torch foreach)", "gpu_launches": out["value"][2],
+        "optimizer": ("sdb200.optim.FusedAdam: clip_grad_norm_(1.0) + finite check + Adam + EMA in two launches" if fused
+                      else "Adam + clip_grad_norm_(1.0) + EMA (torch foreach)"), "gpu_launches": out["value"][2],
         "grad_allreduce": None if world == 1 else (
             "torch DistributedDataParallel: 25 MB NCCL buckets, reduced after the backward graph has replayed"
             if args.train_ddp == "torch" else
@@ -620,6 +629,8 @@ def main():
     ap.add_argument("--train-batch", type=int, default=16, help="per-GPU training batch (reference: 16)")
     ap.add_argument("--dit-steps", type=int, default=200,
                     help="DiT legs (configs[3], LSQ half of configs[4]): timed sampling steps; 0 disables them")
+    ap.add_argument("--train-opt", choices=["fused", "torch"], default="fused",
+                    help="optimizer side of the training legs: sdb200.optim.FusedAdam or torch Adam + clip + EMA")
     ap.add_argument("--train-ddp", choices=["ours", "torch"], default="ours",
                     help="N>1 gradient mean: sdb200.parallel.DataParallel (flat buffer) or torch DistributedDataParallel")
     ap.add_argument("--dump", default="", help="write the per-launch kernel timing of one eager step to this JSON file")

@@ -357,6 +357,32 @@ int b200sd_wgrad_scatter(const float* partial, int32_t splits, int32_t n_out, in
                          int32_t cp, int32_t taps, const int32_t* tap_off, float* out, int64_t s_co, int64_t s_ci,
                          int32_t accumulate, void* stream);
 
+/* ------------------------------------------------------------------------------------------ optimizer step
+ * Replaces, for one training step, torch.nn.utils.clip_grad_norm_ + the isfinite(grad_norm) check + Adam.step + the
+ * per-parameter EMA loop of train_ddpm_cond_celebhq_multi_gpu.py:362-378 (same code in Model_DiT_9L_train.py).
+ * Gradients, exp_avg and exp_avg_sq are flat fp32 buffers sharing one slot layout; a chunk names a run of <=
+ * b200sd_opt_chunk_elems() consecutive elements of one parameter: its address, its EMA shadow's (or NULL), the run's
+ * offset in the flat buffers and its length. vec = 1 when p (and ema) are 16-byte aligned. */
+typedef struct {
+    float* p;
+    float* ema;
+    int64_t off;
+    int32_t n;
+    int32_t vec;
+} b200sd_opt_chunk;
+int b200sd_opt_chunk_size(void);
+int b200sd_opt_chunk_elems(void);
+/* scalars (device fp32[4]): [0] total L2 norm of the gradients, [1] clip coefficient min(1, max_norm / (norm + 1e-6))
+ * (1 when max_norm <= 0), [2] 1 if the norm is finite (or check_finite == 0) else 0, [3] step counter, incremented here
+ * when [2] is 1. partial: fp32 scratch [n_chunks]; counter: one zeroed uint32 (left at 0). chunks: DEVICE array. */
+int b200sd_grad_sqnorm(const void* chunks, int32_t n_chunks, const float* g_base, float max_norm, int32_t check_finite,
+                       float* partial, float* scalars, uint32_t* counter, void* stream);
+/* Adam (torch.optim.Adam semantics: L2 weight decay, bias correction from scalars[3]) on the clipped gradient, then
+ * ema = ema_decay * ema + (1 - ema_decay) * p. Does nothing when scalars[2] == 0. */
+int b200sd_adam_ema_step(const void* chunks, int32_t n_chunks, const float* g_base, float* m_base, float* v_base,
+                         const float* scalars, float lr, float beta1, float beta2, float eps, float weight_decay,
+                         float ema_decay, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -57,6 +57,7 @@ __global__ void __launch_bounds__(ATT_THREADS)
     attention_kernel(const __nv_bfloat16* __restrict__ q, long long ld_q, const __nv_bfloat16* __restrict__ k,
                      long long ld_k, const __nv_bfloat16* __restrict__ v, long long ld_v,
                      __nv_bfloat16* __restrict__ out, long long ld_o, int lq, int lk, int d, float scale_log2) {
+    pdl_enter();
     constexpr int PITCH = DP + 8;  // elements
     extern __shared__ __align__(16) uint8_t att_smem[];
     __nv_bfloat16* sQ = reinterpret_cast<__nv_bfloat16*>(att_smem);
@@ -251,6 +252,7 @@ __global__ void __launch_bounds__(256)
                               long long ld_k, const __nv_bfloat16* __restrict__ v, long long ld_v,
                               __nv_bfloat16* __restrict__ out, long long ld_o, int lq, int lk, float scale_log2,
                               float* __restrict__ lse) {
+    pdl_enter();
     constexpr int PITCH = AttRes<D8>::PITCH;
     constexpr int K16 = D8 / 2;        // k16 chunks of the head dim
     constexpr bool TAIL = (D8 & 1);    // one trailing k8 chunk
@@ -447,7 +449,7 @@ static int launch_resident(const void* q, int64_t ld_q, const void* k, int64_t l
         configured = true;
     }
     dim3 grid((lq + bq - 1) / bq, heads, (unsigned)batch);
-    attention_resident_kernel<D8><<<grid, warps * 32, smem, st>>>(
+    launch_k(attention_resident_kernel<D8>, grid, warps * 32, smem, st, 
         static_cast<const __nv_bfloat16*>(q), ld_q, static_cast<const __nv_bfloat16*>(k), ld_k,
         static_cast<const __nv_bfloat16*>(v), ld_v, static_cast<__nv_bfloat16*>(out), ld_o, lq, lk,
         scale * 1.4426950408889634f, lse);
@@ -467,7 +469,7 @@ static int launch_attention(const void* q, int64_t ld_q, const void* k, int64_t 
         configured = true;
     }
     dim3 grid((lq + ATT_BQ - 1) / ATT_BQ, heads, (unsigned)batch);
-    attention_kernel<DP><<<grid, ATT_THREADS, smem, st>>>(
+    launch_k(attention_kernel<DP>, grid, ATT_THREADS, smem, st, 
         static_cast<const __nv_bfloat16*>(q), ld_q, static_cast<const __nv_bfloat16*>(k), ld_k,
         static_cast<const __nv_bfloat16*>(v), ld_v, static_cast<__nv_bfloat16*>(out), ld_o, lq, lk, d,
         scale * 1.4426950408889634f);
@@ -491,6 +493,7 @@ __global__ void __launch_bounds__(256)
                          const float* __restrict__ dvec, __nv_bfloat16* __restrict__ out_b, long long ld_ob,
                          __nv_bfloat16* __restrict__ out_a, long long ld_oa, int lr, int lc, int lq, float scale,
                          float scale_log2) {
+    pdl_enter();
     constexpr int PITCH = AttRes<D8>::PITCH;
     constexpr int K16 = D8 / 2;
     constexpr bool TAIL = (D8 & 1);
@@ -699,6 +702,7 @@ __global__ void __launch_bounds__(256)
 // D[b, h, i] = sum_d dO[i, h*d + j] * O[i, h*d + j]
 __global__ void attn_dot_kernel(const __nv_bfloat16* __restrict__ o, long long ld_o, const __nv_bfloat16* __restrict__ d_o,
                                 long long ld_do, float* __restrict__ dvec, long long batch, int heads, int lq, int d) {
+    pdl_enter();
     const long long total = batch * heads * lq;
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
          i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -743,7 +747,7 @@ static int launch_bwd(const void* r1, int64_t ld_r1, const void* r2, int64_t ld_
         configured = true;
     }
     dim3 grid((lr + bq - 1) / bq, heads, (unsigned)batch);
-    attention_bwd_kernel<D8, DKV><<<grid, warps * 32, smem, st>>>(
+    launch_k(attention_bwd_kernel<D8, DKV>, grid, warps * 32, smem, st, 
         static_cast<const __nv_bfloat16*>(r1), ld_r1, static_cast<const __nv_bfloat16*>(r2), ld_r2,
         static_cast<const __nv_bfloat16*>(c1), ld_c1, static_cast<const __nv_bfloat16*>(c2), ld_c2, lse, dvec,
         static_cast<__nv_bfloat16*>(out_b), ld_ob, static_cast<__nv_bfloat16*>(out_a), ld_oa, lr, lc, lq, scale,
@@ -849,7 +853,7 @@ extern "C" int b200sd_attention_bwd(const void* q, int64_t ld_q, const void* k, 
         const long long total = batch * heads * (long long)lq;
         long long blocks = (total + 255) / 256;
         if (blocks > 8ll * sm_count()) blocks = 8ll * sm_count();
-        attn_dot_kernel<<<(int)blocks, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(o), ld_o,
+        launch_k(attn_dot_kernel, (int)blocks, 256, 0, st, static_cast<const __nv_bfloat16*>(o), ld_o,
                                                      static_cast<const __nv_bfloat16*>(d_o), ld_do, dvec, batch, heads, lq, d);
         B200_CHECK_LAUNCH("attention_dot");
     }

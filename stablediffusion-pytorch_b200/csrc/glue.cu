@@ -14,6 +14,7 @@ __device__ __forceinline__ float glue_act(float v, int act) {
 // src NCHW fp32 -> dst NHWC bf16 slice. Thread per (n, p): reads are coalesced over p for each c.
 __global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long ld,
                                     int c_off, long long n, int c, long long hw) {
+    pdl_enter();
     const long long total = n * hw;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
@@ -27,6 +28,7 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, __nv_bfloat16
 template <typename T>
 __global__ void nhwc_to_nchw_kernel(const T* __restrict__ src, long long ld, float* __restrict__ dst, long long n,
                                     int c, long long hw) {
+    pdl_enter();
     const long long total = n * hw;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
@@ -42,6 +44,7 @@ __global__ void nhwc_to_nchw_kernel(const T* __restrict__ src, long long ld, flo
 __global__ void mask_cond_kernel(const float* __restrict__ mask, const float* __restrict__ w,
                                  __nv_bfloat16* __restrict__ dst, long long ld, int c_off, long long n, int cin,
                                  int cout, int mh, int mw, int h, int wd) {
+    pdl_enter();
     extern __shared__ float sw[];  // [cout, cin]
     for (int i = threadIdx.x; i < cout * cin; i += blockDim.x) sw[i] = w[i];
     __syncthreads();
@@ -71,6 +74,7 @@ __global__ void mask_cond_kernel(const float* __restrict__ mask, const float* __
 __global__ void copy_act_kernel(const __nv_bfloat16* __restrict__ src, long long ld_src,
                                 __nv_bfloat16* __restrict__ dst, long long ld_dst, int c_off, long long rows, int c,
                                 int act, int vec) {
+    pdl_enter();
     if (vec) {  // 8 channels (16 B) per thread
         const int vpr = c >> 3;
         const long long total = rows * vpr;
@@ -103,6 +107,7 @@ __global__ void copy_act_kernel(const __nv_bfloat16* __restrict__ src, long long
 
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n4,
                                      long long n) {
+    pdl_enter();
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4;
          i += (long long)gridDim.x * blockDim.x) {
         float4 f = reinterpret_cast<const float4*>(src)[i];
@@ -119,6 +124,7 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat1
 
 __global__ void add_bf16_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ o,
                                 long long n8) {
+    pdl_enter();
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8;
          i += (long long)gridDim.x * blockDim.x) {
         uint4 x = a[i], y = b[i], r;
@@ -150,7 +156,7 @@ extern "C" int b200sd_nchw_to_nhwc(const float* src, void* dst, int64_t ld_dst, 
     B200_REQUIRE(c_off >= 0 && c_off + c <= ld_dst, "nchw_to_nhwc: channel slice [%d,%d) exceeds ld %lld", c_off,
                  c_off + c, (long long)ld_dst);
     if (n * hw == 0) return B200SD_OK;
-    nchw_to_nhwc_kernel<<<glue_grid(n * hw, 256), 256, 0, as_stream(stream)>>>(
+    launch_k(nchw_to_nhwc_kernel, glue_grid(n * hw, 256), 256, 0, as_stream(stream), 
         src, static_cast<__nv_bfloat16*>(dst), ld_dst, c_off, n, c, hw);
     B200_CHECK_LAUNCH("nchw_to_nhwc");
     return B200SD_OK;
@@ -163,10 +169,9 @@ extern "C" int b200sd_nhwc_to_nchw(const void* src, int src_dtype, int64_t ld_sr
     if (n * hw == 0) return B200SD_OK;
     const int grid = glue_grid(n * hw, 256);
     if (src_dtype == B200SD_DT_BF16)
-        nhwc_to_nchw_kernel<__nv_bfloat16>
-            <<<grid, 256, 0, as_stream(stream)>>>(static_cast<const __nv_bfloat16*>(src), ld_src, dst, n, c, hw);
+        launch_k(nhwc_to_nchw_kernel<__nv_bfloat16>, grid, 256, 0, as_stream(stream), static_cast<const __nv_bfloat16*>(src), ld_src, dst, n, c, hw);
     else if (src_dtype == B200SD_DT_F32)
-        nhwc_to_nchw_kernel<float><<<grid, 256, 0, as_stream(stream)>>>(static_cast<const float*>(src), ld_src, dst, n, c, hw);
+        launch_k(nhwc_to_nchw_kernel<float>, grid, 256, 0, as_stream(stream), static_cast<const float*>(src), ld_src, dst, n, c, hw);
     else {
         set_error("nhwc_to_nchw: bad dtype %d", src_dtype);
         return B200SD_ERR_ARG;
@@ -182,7 +187,7 @@ extern "C" int b200sd_mask_cond(const float* mask, const float* w, void* dst, in
     B200_REQUIRE(c_off >= 0 && c_off + cout <= ld_dst, "mask_cond: channel slice exceeds ld");
     B200_REQUIRE(cin >= 1 && cin * cout * 4 <= 48 * 1024, "mask_cond: weight too large for shared memory");
     if (n == 0) return B200SD_OK;
-    mask_cond_kernel<<<glue_grid(n * h * wd, 128), 128, cin * cout * sizeof(float), as_stream(stream)>>>(
+    launch_k(mask_cond_kernel, glue_grid(n * h * wd, 128), 128, cin * cout * sizeof(float), as_stream(stream), 
         mask, w, static_cast<__nv_bfloat16*>(dst), ld_dst, c_off, n, cin, cout, mh, mw, h, wd);
     B200_CHECK_LAUNCH("mask_cond");
     return B200SD_OK;
@@ -196,7 +201,7 @@ extern "C" int b200sd_copy_act(const void* src, int64_t ld_src, void* dst, int64
     const int vec = (c % 8 == 0) && (ld_src % 8 == 0) && (ld_dst % 8 == 0) && (c_off % 8 == 0) &&
                     ((reinterpret_cast<uintptr_t>(src) & 15) == 0) && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0);
     const long long items = vec ? rows * (c / 8) : rows * c;
-    copy_act_kernel<<<glue_grid(items, 256), 256, 0, as_stream(stream)>>>(
+    launch_k(copy_act_kernel, glue_grid(items, 256), 256, 0, as_stream(stream), 
         static_cast<const __nv_bfloat16*>(src), ld_src, static_cast<__nv_bfloat16*>(dst), ld_dst, c_off, rows, c, act,
         vec);
     B200_CHECK_LAUNCH("copy_act");
@@ -208,7 +213,7 @@ extern "C" int b200sd_cast_f32_bf16(const float* src, void* dst, int64_t n, void
     B200_REQUIRE(((reinterpret_cast<uintptr_t>(src) & 15) == 0) && ((reinterpret_cast<uintptr_t>(dst) & 7) == 0),
                  "cast: pointers unaligned");
     if (n == 0) return B200SD_OK;
-    cast_f32_bf16_kernel<<<glue_grid((n + 3) / 4, 256), 256, 0, as_stream(stream)>>>(
+    launch_k(cast_f32_bf16_kernel, glue_grid((n + 3) / 4, 256), 256, 0, as_stream(stream), 
         src, static_cast<__nv_bfloat16*>(dst), n / 4, n);
     B200_CHECK_LAUNCH("cast_f32_bf16");
     return B200SD_OK;
@@ -220,7 +225,7 @@ extern "C" int b200sd_add_bf16(const void* a, const void* b, void* out, int64_t 
     B200_REQUIRE(((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(out)) & 15) == 0,
                  "add: pointers unaligned");
     if (n == 0) return B200SD_OK;
-    add_bf16_kernel<<<glue_grid(n / 8, 256), 256, 0, as_stream(stream)>>>(
+    launch_k(add_bf16_kernel, glue_grid(n / 8, 256), 256, 0, as_stream(stream), 
         static_cast<const uint4*>(a), static_cast<const uint4*>(b), static_cast<uint4*>(out), n / 8);
     B200_CHECK_LAUNCH("add_bf16");
     return B200SD_OK;

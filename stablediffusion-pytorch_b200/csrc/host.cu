@@ -1,5 +1,6 @@
 #include "host.h"
 #include <atomic>
+#include <stdlib.h>
 #include <string.h>
 
 namespace b200 {
@@ -26,6 +27,15 @@ int sm_count() {
             cached = 148;
     }
     return cached;
+}
+
+bool pdl_enabled() {
+    static int cached = -1;
+    if (cached < 0) {
+        const char* e = getenv("B200SD_PDL");
+        cached = (e && e[0] == '1') ? 1 : 0;   // measured on B200: no gain inside CUDA graphs, so opt-in
+    }
+    return cached == 1;
 }
 
 }  // namespace b200

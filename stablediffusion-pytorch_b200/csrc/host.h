@@ -14,6 +14,38 @@ int sm_count();
 
 inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
+// Programmatic dependent launch (opt-in: B200SD_PDL=1). With it every kernel of this library is launched with
+// programmatic stream serialisation:
+// the next kernel in the stream (or captured graph) may become resident as soon as every CTA of this one has started,
+// sets up its barriers / TMEM / descriptor prefetches, and blocks in pdl_wait() until this grid has completed and its
+// memory is visible. The gap between two dependent kernels shrinks from a full drain + launch to the wait itself.
+// Rule for kernels: no global-memory access (read OR write) before pdl_wait().
+bool pdl_enabled();
+
+template <typename... P, typename... A>
+inline cudaError_t launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<P>(args)...);
+}
+
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_enter() {
+    pdl_trigger();
+    pdl_wait();
+}
+#endif
+
 #define B200_REQUIRE(cond, ...)              \
     do {                                     \
         if (!(cond)) {                       \

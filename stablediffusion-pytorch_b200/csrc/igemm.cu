@@ -186,6 +186,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_co
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
+    pdl_trigger();
     if (warp == 0 && lane == 0) {
         for (int i = 0; i < 4; ++i) tma_prefetch_desc(&args.a_map[i]);
         tma_prefetch_desc(&args.b_map);
@@ -213,6 +214,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_co
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();   // everything above overlapped the previous kernel's tail; from here on its results are read
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
@@ -647,7 +649,7 @@ static int launch_igemm(const IgemmArgs& a, int grid, cudaStream_t st) {
         }
         configured = true;
     }
-    igemm_kernel<BN, STAGES><<<grid, IGEMM_THREADS, L::TOTAL, st>>>(a);
+    launch_k(igemm_kernel<BN, STAGES>, grid, IGEMM_THREADS, L::TOTAL, st, a);
     B200_CHECK_LAUNCH("igemm");
     return B200SD_OK;
 }

@@ -19,6 +19,7 @@ __global__ void __launch_bounds__(512)
     groupnorm_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, __nv_bfloat16* __restrict__ y,
                      long long ld_y, const float* __restrict__ gamma, const float* __restrict__ beta, long long hw,
                      int c, int cpg, int gpc, float eps, int act, int cached, int rows_per_pass) {
+    pdl_enter();
     extern __shared__ __align__(16) uint8_t gn_smem[];
     __shared__ float s_sum[64];
     __shared__ float s_mean[64];
@@ -129,6 +130,7 @@ __global__ void __launch_bounds__(256)
                     StatSeg s0, int c_split, StatSeg s1, const float* __restrict__ gamma,
                     const float* __restrict__ beta, long long hw, int c, int groups, float eps, int act,
                     int rows_per_block, int rpp) {
+    pdl_enter();
     extern __shared__ float gn_sm[];
     float* sc = gn_sm;          // [c]  channel sums, then scale
     float* sh = gn_sm + c;      // [c]  channel sums of squares, then shift
@@ -254,6 +256,7 @@ __global__ void __launch_bounds__(256)
                          long long ld_dy, StatSeg s0, int c_split, StatSeg s1, const float* __restrict__ gamma,
                          const float* __restrict__ beta, long long hw, int c, int groups, float eps, int act,
                          int rows_per_block, int rpp, float* __restrict__ part /* [n][gridDim.x][c][2] */) {
+    pdl_enter();
     extern __shared__ float gn_sm[];
     float* sc = gn_sm;
     float* sh = sc + c;
@@ -347,6 +350,7 @@ __global__ void __launch_bounds__(256)
                         float eps, int act, int rows_per_block, int rpp, const float* __restrict__ part, int pb,
                         float* __restrict__ ab /* [n][c][2] or null */, float* __restrict__ dgamma,
                         float* __restrict__ dbeta, unsigned int* counter) {
+    pdl_enter();
     extern __shared__ float gn_sm[];
     float* sc = gn_sm;
     float* sh = sc + c;
@@ -425,6 +429,7 @@ __global__ void __launch_bounds__(256)
 // out[b][c] (+)= sum over r of in[b][r][c]  (fp32; bias / GroupNorm-affine / time-embedding gradients)
 __global__ void reduce_f32_kernel(const float* __restrict__ in, long long batch, long long rows, long long cols,
                                   long long col_stride, float* __restrict__ out, int accumulate) {
+    pdl_enter();
     const long long total = batch * cols;
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
          i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -443,6 +448,7 @@ __global__ void reduce_f32_kernel(const float* __restrict__ in, long long batch,
 __global__ void __launch_bounds__(256)
     colsum_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, long long hw, int c, int rows_per_block,
                   float* __restrict__ part, float* __restrict__ out, int per_image, unsigned int* counter) {
+    pdl_enter();
     __shared__ float red[32][65];
     const int slab = blockIdx.x, rb = blockIdx.y, img = blockIdx.z, pb = gridDim.y;
     const int tid = threadIdx.x, v = tid & 7, lane_r = tid >> 3;
@@ -549,11 +555,11 @@ extern "C" int b200sd_groupnorm(const void* x, int64_t ld_x, void* y, int64_t ld
         configured = true;
     }
     if (VEC == 2)
-        groupnorm_kernel<2><<<(int)grid, threads, smem, st>>>(
+        launch_k(groupnorm_kernel<2>, (int)grid, threads, smem, st, 
             static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y, gamma, beta, hw, c, cpg,
             gpc, eps, act, cached, rows_per_pass);
     else
-        groupnorm_kernel<1><<<(int)grid, threads, smem, st>>>(
+        launch_k(groupnorm_kernel<1>, (int)grid, threads, smem, st, 
             static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y, gamma, beta, hw, c, cpg,
             gpc, eps, act, cached, rows_per_pass);
     B200_CHECK_LAUNCH("groupnorm");
@@ -591,7 +597,7 @@ extern "C" int b200sd_groupnorm_apply(const void* x, int64_t ld_x, void* y, int6
     const size_t smem = (size_t)(2 * c + 2 * groups) * sizeof(float);
     StatSeg s0{stats0, p0, ld_s0}, s1{stats1, p1, ld_s1};
     dim3 grid((unsigned)blocks_per_img, (unsigned)n);
-    gn_apply_kernel<<<grid, threads, smem, as_stream(stream)>>>(
+    launch_k(gn_apply_kernel, grid, threads, smem, as_stream(stream), 
         static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y, s0, c_split, s1, gamma, beta,
         hw, c, groups, eps, act, (int)rows_per_block, rpp);
     B200_CHECK_LAUNCH("groupnorm_apply");
@@ -655,11 +661,11 @@ extern "C" int b200sd_groupnorm_bwd(const void* x, int64_t ld_x, const void* dy,
         configured = true;
     }
     B200_REQUIRE(sm1 <= 160 * 1024, "groupnorm_bwd: reduction scratch too large");
-    gn_bwd_reduce_kernel<<<grid, g.threads, sm1, st>>>(
+    launch_k(gn_bwd_reduce_kernel, grid, g.threads, sm1, st, 
         static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<const __nv_bfloat16*>(dy), ld_dy, s0, c_split, s1, gamma,
         beta, hw, c, groups, eps, act, g.rows_per_block, g.rpp, part);
     B200_CHECK_LAUNCH("groupnorm_bwd_reduce");
-    gn_bwd_apply_kernel<<<grid, g.threads, sm2, st>>>(
+    launch_k(gn_bwd_apply_kernel, grid, g.threads, sm2, st, 
         static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<const __nv_bfloat16*>(dy), ld_dy,
         static_cast<const __nv_bfloat16*>(add), ld_add, static_cast<__nv_bfloat16*>(dx), ld_dx, s0, c_split, s1, gamma,
         beta, hw, c, groups, eps, act, g.rows_per_block, g.rpp, part, g.blocks_per_img, ab, dgamma, dbeta, counter);
@@ -693,7 +699,7 @@ extern "C" int b200sd_colsum(const void* x, int64_t ld_x, int64_t n, int64_t hw,
     const int pb = colsum_blocks(n, hw, c);
     const long long rpb = (hw + pb - 1) / pb;
     dim3 grid((unsigned)((c + 63) / 64), (unsigned)pb, (unsigned)n);
-    colsum_kernel<<<grid, 256, 0, as_stream(stream)>>>(static_cast<const __nv_bfloat16*>(x), ld_x, hw, c, (int)rpb, part,
+    launch_k(colsum_kernel, grid, 256, 0, as_stream(stream), static_cast<const __nv_bfloat16*>(x), ld_x, hw, c, (int)rpb, part,
                                                        out, per_image, counter);
     B200_CHECK_LAUNCH("colsum");
     return B200SD_OK;
@@ -705,7 +711,7 @@ extern "C" int b200sd_reduce_f32(const float* in, int64_t batch, int64_t rows, i
     if (batch * cols == 0) return B200SD_OK;
     long long blocks = (batch * cols + 127) / 128;
     if (blocks > 4ll * sm_count()) blocks = 4ll * sm_count();
-    reduce_f32_kernel<<<(int)blocks, 128, 0, as_stream(stream)>>>(in, batch, rows, cols, col_stride, out, accumulate);
+    launch_k(reduce_f32_kernel, (int)blocks, 128, 0, as_stream(stream), in, batch, rows, cols, col_stride, out, accumulate);
     B200_CHECK_LAUNCH("reduce_f32");
     return B200SD_OK;
 }

@@ -31,6 +31,7 @@ static_assert(sizeof(PackJob) == sizeof(b200sd_pack_job), "PackJob must match th
 
 // tile = 32 packed rows x 32 channels x all taps
 __global__ void __launch_bounds__(256) pack_weights_kernel(const PackJob* __restrict__ jobs, int n_jobs) {
+    pdl_enter();
     __shared__ __nv_bfloat16 tile[PK_ROWS][PK_MAX_TAPS * PK_CH + 2];
     // binary search: last job with tile0 <= blockIdx.x
     int lo = 0, hi = n_jobs - 1;
@@ -78,6 +79,7 @@ struct ScatterArgs {
 constexpr int SC_CH = 128;
 
 __global__ void __launch_bounds__(256) wgrad_scatter_kernel(const ScatterArgs a) {
+    pdl_enter();
     __shared__ float tile[SC_CH * (PK_MAX_TAPS + 1)];
     const int ts = a.taps | 1;   // odd row stride: conflict-free turn-around
     const int co = blockIdx.y, c0 = blockIdx.x * SC_CH;
@@ -110,7 +112,7 @@ extern "C" int b200sd_pack_job_size(void) { return static_cast<int>(sizeof(PackJ
 
 extern "C" int b200sd_pack_weights(const void* jobs_dev, int32_t n_jobs, int32_t n_tiles, void* stream) {
     B200_REQUIRE(jobs_dev && n_jobs > 0 && n_tiles > 0, "pack_weights: bad arguments");
-    pack_weights_kernel<<<n_tiles, 256, 0, as_stream(stream)>>>(static_cast<const PackJob*>(jobs_dev), n_jobs);
+    launch_k(pack_weights_kernel, n_tiles, 256, 0, as_stream(stream), static_cast<const PackJob*>(jobs_dev), n_jobs);
     B200_CHECK_LAUNCH("pack_weights");
     return B200SD_OK;
 }
@@ -127,7 +129,7 @@ extern "C" int b200sd_wgrad_scatter(const float* partial, int32_t splits, int32_
     a.splits = splits, a.n_out = n_out, a.k_total = k_total, a.col0 = col0, a.cin = cin, a.cp = cp, a.taps = taps;
     a.accumulate = accumulate;
     for (int t = 0; t < PK_MAX_TAPS; ++t) a.tap_off[t] = t < taps ? tap_off[t] : 0;
-    wgrad_scatter_kernel<<<dim3((cin + SC_CH - 1) / SC_CH, n_out), 256, 0, as_stream(stream)>>>(a);
+    launch_k(wgrad_scatter_kernel, dim3((cin + SC_CH - 1) / SC_CH, n_out), 256, 0, as_stream(stream), a);
     B200_CHECK_LAUNCH("wgrad_scatter");
     return B200SD_OK;
 }

@@ -47,6 +47,7 @@ __device__ __forceinline__ float effective_step(float s, float g) {
 // ---- max |x| over a [rows, c] tensor (pitch ld) into *slot as float bits (non-negative floats order like uints)
 template <typename T>
 __global__ void absmax_kernel(const T* __restrict__ x, long long ld, long long rows, int c, unsigned int* slot) {
+    pdl_enter();
     const int nchunk = c >> 3;
     const long long total = rows * nchunk;
     float m = 0.f;
@@ -67,6 +68,7 @@ __global__ void absmax_kernel(const T* __restrict__ x, long long ld, long long r
 // init_step_size (layers_utils_lsq.py:31-34 via data_quant(isint=True), quant_noise_utils.py:8-28): while the
 // parameter still holds its construction value 1.0, step = 1 / (1 / max|x| * Qp); an all-zero tensor leaves it at 1.
 __global__ void lsq_init_step_kernel(float* step, const unsigned int* slot, float qp) {
+    pdl_enter();
     if (*step != 1.0f) return;
     const float range = __uint_as_float(*slot);
     if (range == 0.f) return;
@@ -80,6 +82,7 @@ __global__ void lsq_init_step_kernel(float* step, const unsigned int* slot, floa
 template <typename TI, typename TO>
 __global__ void lsq_quant_kernel(const TI* __restrict__ x, long long ld_x, TO* __restrict__ y, long long ld_y,
                                  long long rows, int c, const float* __restrict__ step, float qp, float g, int mode) {
+    pdl_enter();
     const float s = effective_step(*step, g);
     const int nchunk = c >> 3;
     const long long total = rows * nchunk;
@@ -109,6 +112,7 @@ __global__ void __launch_bounds__(256)
     lsq_quant_bwd_kernel(const __nv_bfloat16* __restrict__ dy, long long ld_dy, const TI* __restrict__ x, long long ld_x,
                          __nv_bfloat16* __restrict__ dx, long long ld_dx, long long rows, int c,
                          const float* __restrict__ step, float qp, float g, int mode, float* __restrict__ part) {
+    pdl_enter();
     __shared__ float wsum[8];
     const float s = effective_step(*step, g);
     const float inv_s = __fdiv_rn(1.0f, s);
@@ -163,6 +167,7 @@ template <typename TI>
 __global__ void bit_split_kernel(const TI* __restrict__ q, long long ld_q, __nv_bfloat16* __restrict__ out,
                                  long long ld_o, long long rows, int c, int slices, int slice_bit, int x_bit,
                                  int quantise, const float* __restrict__ step, float qp, float g) {
+    pdl_enter();
     const float s = quantise ? effective_step(*step, g) : 1.f;
     const int nchunk = c >> 3;
     const long long total = rows * nchunk;
@@ -198,6 +203,7 @@ __global__ void adc_combine_kernel(const float* __restrict__ p, long long ld_p, 
                                    long long rows, int ncol, int col0, int slices, int slice_bit,
                                    const float* __restrict__ alpha_p, float R, const float* __restrict__ gain_noise,
                                    const float* __restrict__ offset_noise, int accumulate) {
+    pdl_enter();
     const float alpha = *alpha_p;
     const long long total = rows * ncol;
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -228,6 +234,7 @@ __global__ void __launch_bounds__(256)
                    __nv_bfloat16* __restrict__ dp, long long ld_d, long long rows, int ncol, int col0, int slices,
                    int slice_bit, const float* __restrict__ alpha_p, float R, const float* __restrict__ gain_noise,
                    const float* __restrict__ offset_noise, float* __restrict__ part) {
+    pdl_enter();
     __shared__ float wsum[8];
     const float alpha = *alpha_p;
     const long long total = rows * ncol;
@@ -265,6 +272,7 @@ __global__ void __launch_bounds__(256)
 // every slice passes the gradient of shift / slices, shift = floor_pass(code / 2^lsb)).
 __global__ void bit_split_bwd_kernel(const __nv_bfloat16* __restrict__ dd, long long ld_d, __nv_bfloat16* __restrict__ dq,
                                      long long ld_q, long long rows, int c, int slices, int slice_bit) {
+    pdl_enter();
     const int nchunk = c >> 3;
     const long long total = rows * nchunk;
     const float inv = 1.f / static_cast<float>(slices);
@@ -309,12 +317,12 @@ extern "C" int b200sd_lsq_init_step(const void* x, int32_t x_f32, int64_t ld_x, 
     if (rows > 0) {
         const int grid = q_grid(rows * (c / 8), 256, 4);
         if (x_f32)
-            absmax_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(x), ld_x, rows, c, scratch);
+            launch_k(absmax_kernel<float>, grid, 256, 0, st, static_cast<const float*>(x), ld_x, rows, c, scratch);
         else
-            absmax_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), ld_x, rows, c, scratch);
+            launch_k(absmax_kernel<__nv_bfloat16>, grid, 256, 0, st, static_cast<const __nv_bfloat16*>(x), ld_x, rows, c, scratch);
         B200_CHECK_LAUNCH("lsq_init_step(absmax)");
     }
-    lsq_init_step_kernel<<<1, 1, 0, st>>>(step, scratch, qp);
+    launch_k(lsq_init_step_kernel, 1, 1, 0, st, step, scratch, qp);
     B200_CHECK_LAUNCH("lsq_init_step");
     return B200SD_OK;
 }
@@ -328,13 +336,13 @@ extern "C" int b200sd_lsq_quant(const void* x, int32_t x_f32, int64_t ld_x, void
     const int grid = q_grid(rows * (c / 8), 256);
     cudaStream_t st = as_stream(stream);
     if (x_f32 && y_f32)
-        lsq_quant_kernel<float, float><<<grid, 256, 0, st>>>(static_cast<const float*>(x), ld_x, static_cast<float*>(y), ld_y, rows, c, step, qp, g, mode);
+        launch_k(lsq_quant_kernel<float, float>, grid, 256, 0, st, static_cast<const float*>(x), ld_x, static_cast<float*>(y), ld_y, rows, c, step, qp, g, mode);
     else if (x_f32)
-        lsq_quant_kernel<float, __nv_bfloat16><<<grid, 256, 0, st>>>(static_cast<const float*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y, rows, c, step, qp, g, mode);
+        launch_k(lsq_quant_kernel<float, __nv_bfloat16>, grid, 256, 0, st, static_cast<const float*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y, rows, c, step, qp, g, mode);
     else if (y_f32)
-        lsq_quant_kernel<__nv_bfloat16, float><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<float*>(y), ld_y, rows, c, step, qp, g, mode);
+        launch_k(lsq_quant_kernel<__nv_bfloat16, float>, grid, 256, 0, st, static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<float*>(y), ld_y, rows, c, step, qp, g, mode);
     else
-        lsq_quant_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y, rows, c, step, qp, g, mode);
+        launch_k(lsq_quant_kernel<__nv_bfloat16, __nv_bfloat16>, grid, 256, 0, st, static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y, rows, c, step, qp, g, mode);
     B200_CHECK_LAUNCH("lsq_quant");
     return B200SD_OK;
 }
@@ -350,10 +358,10 @@ extern "C" int b200sd_lsq_quant_bwd(const void* dy, int64_t ld_dy, const void* x
     const int grid = q_grid(rows * (c / 8), 256, 4);
     cudaStream_t st = as_stream(stream);
     if (x_f32)
-        lsq_quant_bwd_kernel<float><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(dy), ld_dy, static_cast<const float*>(x), ld_x,
+        launch_k(lsq_quant_bwd_kernel<float>, grid, 256, 0, st, static_cast<const __nv_bfloat16*>(dy), ld_dy, static_cast<const float*>(x), ld_x,
                                                           static_cast<__nv_bfloat16*>(dx), ld_dx, rows, c, step, qp, g, mode, part);
     else
-        lsq_quant_bwd_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(dy), ld_dy, static_cast<const __nv_bfloat16*>(x), ld_x,
+        launch_k(lsq_quant_bwd_kernel<__nv_bfloat16>, grid, 256, 0, st, static_cast<const __nv_bfloat16*>(dy), ld_dy, static_cast<const __nv_bfloat16*>(x), ld_x,
                                                                   static_cast<__nv_bfloat16*>(dx), ld_dx, rows, c, step, qp, g, mode, part);
     B200_CHECK_LAUNCH("lsq_quant_bwd");
     return B200SD_OK;
@@ -370,10 +378,10 @@ extern "C" int b200sd_bit_split(const void* x, int32_t x_f32, int64_t ld_x, void
     const int grid = q_grid(rows * (c / 8), 256);
     cudaStream_t st = as_stream(stream);
     if (x_f32)
-        bit_split_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(x), ld_x, static_cast<__nv_bfloat16*>(digits), ld_o,
+        launch_k(bit_split_kernel<float>, grid, 256, 0, st, static_cast<const float*>(x), ld_x, static_cast<__nv_bfloat16*>(digits), ld_o,
                                                       rows, c, slices, slice_bit, x_bit, step != nullptr, step, qp, g);
     else
-        bit_split_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(digits),
+        launch_k(bit_split_kernel<__nv_bfloat16>, grid, 256, 0, st, static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(digits),
                                                               ld_o, rows, c, slices, slice_bit, x_bit, step != nullptr, step, qp, g);
     B200_CHECK_LAUNCH("bit_split");
     return B200SD_OK;
@@ -388,7 +396,7 @@ extern "C" int b200sd_adc_combine(const float* partial, int64_t ld_p, float* out
     B200_REQUIRE((gain_noise == nullptr) == (offset_noise == nullptr), "adc_combine: gain and offset noise come together");
     B200_REQUIRE(slices * slice_bit <= 24, "adc_combine: digit weights beyond 2^24 are not exact in fp32");
     if (rows == 0) return B200SD_OK;
-    adc_combine_kernel<<<q_grid(rows * ncol, 256), 256, 0, as_stream(stream)>>>(
+    launch_k(adc_combine_kernel, q_grid(rows * ncol, 256), 256, 0, as_stream(stream), 
         partial, ld_p, out, ld_o, rows, ncol, col0, slices, slice_bit, adc_scale, adc_range, gain_noise, offset_noise,
         accumulate);
     B200_CHECK_LAUNCH("adc_combine");
@@ -405,7 +413,7 @@ extern "C" int b200sd_adc_bwd(const float* partial, int64_t ld_p, const float* d
                      slice_bit >= 1, "adc_bwd: bad arguments");
     B200_REQUIRE((gain_noise == nullptr) == (offset_noise == nullptr), "adc_bwd: gain and offset noise come together");
     B200_REQUIRE(ld_d >= ncol, "adc_bwd: gradient pitch too small");
-    adc_bwd_kernel<<<q_grid(rows * ncol, 256, 4), 256, 0, as_stream(stream)>>>(
+    launch_k(adc_bwd_kernel, q_grid(rows * ncol, 256, 4), 256, 0, as_stream(stream), 
         partial, ld_p, dacc, ld_g, static_cast<__nv_bfloat16*>(dpartial), ld_d, rows, ncol, col0, slices, slice_bit,
         adc_scale, adc_range, gain_noise, offset_noise, part);
     B200_CHECK_LAUNCH("adc_bwd");
@@ -417,7 +425,7 @@ extern "C" int b200sd_bit_split_bwd(const void* ddigits, int64_t ld_d, void* dco
     B200_REQUIRE(ddigits && dcodes && rows >= 0 && slices >= 1 && slice_bit >= 1, "bit_split_bwd: bad arguments");
     B200_REQUIRE(Q_SHAPE_OK(c, ld_d) && Q_SHAPE_OK(c, ld_q), "bit_split_bwd: channels and pitches must be multiples of 8");
     if (rows == 0) return B200SD_OK;
-    bit_split_bwd_kernel<<<q_grid(rows * (c / 8), 256), 256, 0, as_stream(stream)>>>(
+    launch_k(bit_split_bwd_kernel, q_grid(rows * (c / 8), 256), 256, 0, as_stream(stream), 
         static_cast<const __nv_bfloat16*>(ddigits), ld_d, static_cast<__nv_bfloat16*>(dcodes), ld_q, rows, c, slices,
         slice_bit);
     B200_CHECK_LAUNCH("bit_split_bwd");

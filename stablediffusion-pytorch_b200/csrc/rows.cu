@@ -45,6 +45,7 @@ __global__ void __launch_bounds__(ROW_WARPS * 32)
     ln_mod_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, __nv_bfloat16* __restrict__ y, long long ld_y,
                   const __nv_bfloat16* __restrict__ shift, const __nv_bfloat16* __restrict__ scale, long long ld_m,
                   long long rows, long long rows_per_img, int c, float eps, float* __restrict__ stats) {
+    pdl_enter();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nchunk = c >> 3;
     const float inv_c = 1.f / static_cast<float>(c);
@@ -105,6 +106,7 @@ __global__ void __launch_bounds__(ROW_WARPS * 32)
                       long long ld_m, const __nv_bfloat16* __restrict__ dres, long long ld_r,
                       __nv_bfloat16* __restrict__ dx, long long ld_dx, long long rows_per_img, int c, int slots,
                       float* __restrict__ part) {
+    pdl_enter();
     extern __shared__ float row_sm[];  // [ROW_WARPS][2][c]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nchunk = c >> 3;
@@ -188,6 +190,7 @@ __global__ void gate_residual_kernel(const __nv_bfloat16* __restrict__ x, long l
                                      const __nv_bfloat16* __restrict__ gate, long long ld_g,
                                      __nv_bfloat16* __restrict__ y, long long ld_y, long long rows,
                                      long long rows_per_img, int c) {
+    pdl_enter();
     const int nchunk = c >> 3;
     const long long total = rows * nchunk;
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -210,6 +213,7 @@ __global__ void __launch_bounds__(ROW_WARPS * 32)
                              const __nv_bfloat16* __restrict__ h, long long ld_h,
                              const __nv_bfloat16* __restrict__ gate, long long ld_g, __nv_bfloat16* __restrict__ dh,
                              long long ld_dh, long long rows_per_img, int c, int slots, float* __restrict__ part) {
+    pdl_enter();
     extern __shared__ float row_sm[];  // [ROW_WARPS][c]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nchunk = c >> 3;
@@ -263,6 +267,7 @@ __global__ void __launch_bounds__(ROW_WARPS * 32)
 __global__ void relu_bwd_kernel(const __nv_bfloat16* __restrict__ dy, long long ld_dy,
                                 const __nv_bfloat16* __restrict__ y, long long ld_y, __nv_bfloat16* __restrict__ dx,
                                 long long ld_dx, long long rows, int c) {
+    pdl_enter();
     const int nchunk = c >> 3;
     const long long total = rows * nchunk;
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -283,6 +288,7 @@ __global__ void relu_bwd_kernel(const __nv_bfloat16* __restrict__ dy, long long 
 template <typename T>
 __global__ void unpatchify_kernel(const T* __restrict__ tok, long long ld, float* __restrict__ img, long long n, int ch,
                                   int gh, int gw, int ph, int pw) {
+    pdl_enter();
     const int H = gh * ph, W = gw * pw;
     const long long total = n * ch * H * W;
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -298,6 +304,7 @@ __global__ void unpatchify_kernel(const T* __restrict__ tok, long long ld, float
 
 __global__ void patchify_kernel(const float* __restrict__ img, __nv_bfloat16* __restrict__ tok, long long ld,
                                 long long n, int ch, int gh, int gw, int ph, int pw) {
+    pdl_enter();
     const int H = gh * ph, W = gw * pw;
     const long long total = n * gh * gw * ld;
     const int width = ph * pw * ch;
@@ -340,7 +347,7 @@ extern "C" int b200sd_layernorm_mod(const void* x, int64_t ld_x, void* y, int64_
     B200_REQUIRE((shift == nullptr) == (scale == nullptr), "layernorm_mod: shift and scale come together");
     B200_REQUIRE(!scale || (ld_m % 8 == 0 && rows % rows_per_img == 0), "layernorm_mod: modulation pitch / rows_per_img");
     if (rows == 0) return B200SD_OK;
-    ln_mod_kernel<<<grid_for(rows, ROW_WARPS), ROW_WARPS * 32, 0, as_stream(stream)>>>(
+    launch_k(ln_mod_kernel, grid_for(rows, ROW_WARPS), ROW_WARPS * 32, 0, as_stream(stream), 
         static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y,
         static_cast<const __nv_bfloat16*>(shift), static_cast<const __nv_bfloat16*>(scale), ld_m, rows, rows_per_img, c,
         eps, stats);
@@ -364,7 +371,7 @@ extern "C" int b200sd_layernorm_mod_bwd(const void* dy, int64_t ld_dy, const voi
         cudaFuncSetAttribute(ln_mod_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2 * 1024 * 4);
         attr = true;
     }
-    ln_mod_bwd_kernel<<<dim3(slots, static_cast<unsigned>(n)), ROW_WARPS * 32, smem, as_stream(stream)>>>(
+    launch_k(ln_mod_bwd_kernel, dim3(slots, static_cast<unsigned>(n)), ROW_WARPS * 32, smem, as_stream(stream), 
         static_cast<const __nv_bfloat16*>(dy), ld_dy, static_cast<const __nv_bfloat16*>(x), ld_x, stats,
         static_cast<const __nv_bfloat16*>(scale), ld_m, static_cast<const __nv_bfloat16*>(dres), ld_r,
         static_cast<__nv_bfloat16*>(dx), ld_dx, rows_per_img, c, slots, part);
@@ -378,7 +385,7 @@ extern "C" int b200sd_gate_residual(const void* x, int64_t ld_x, const void* h, 
     B200_REQUIRE(x && h && gate && y && rows >= 0 && rows_per_img > 0, "gate_residual: bad arguments");
     B200_REQUIRE(row_ok(c, ld_x) && row_ok(c, ld_h) && row_ok(c, ld_y) && ld_g % 8 == 0, "gate_residual: channels / pitches");
     if (rows == 0) return B200SD_OK;
-    gate_residual_kernel<<<grid_for(rows * (c / 8), 256), 256, 0, as_stream(stream)>>>(
+    launch_k(gate_residual_kernel, grid_for(rows * (c / 8), 256), 256, 0, as_stream(stream), 
         static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<const __nv_bfloat16*>(h), ld_h,
         static_cast<const __nv_bfloat16*>(gate), ld_g, static_cast<__nv_bfloat16*>(y), ld_y, rows, rows_per_img, c);
     B200_CHECK_LAUNCH("gate_residual");
@@ -392,8 +399,7 @@ extern "C" int b200sd_gate_residual_bwd(const void* dy, int64_t ld_dy, const voi
     B200_REQUIRE(row_ok(c, ld_dy) && row_ok(c, ld_h) && row_ok(c, ld_dh) && ld_g % 8 == 0, "gate_residual_bwd: channels / pitches");
     if (n == 0) return B200SD_OK;
     const int slots = static_cast<int>((rows_per_img + ROWS_PER_CTA - 1) / ROWS_PER_CTA);
-    gate_residual_bwd_kernel<<<dim3(slots, static_cast<unsigned>(n)), ROW_WARPS * 32, sizeof(float) * ROW_WARPS * c,
-                               as_stream(stream)>>>(
+    launch_k(gate_residual_bwd_kernel, dim3(slots, static_cast<unsigned>(n)), ROW_WARPS * 32, sizeof(float) * ROW_WARPS * c, as_stream(stream), 
         static_cast<const __nv_bfloat16*>(dy), ld_dy, static_cast<const __nv_bfloat16*>(h), ld_h,
         static_cast<const __nv_bfloat16*>(gate), ld_g, static_cast<__nv_bfloat16*>(dh), ld_dh, rows_per_img, c, slots,
         part);
@@ -406,7 +412,7 @@ extern "C" int b200sd_relu_bwd(const void* dy, int64_t ld_dy, const void* y, int
     B200_REQUIRE(dy && y && dx && rows >= 0 && c > 0 && c % 8 == 0, "relu_bwd: bad arguments");
     B200_REQUIRE(ld_dy % 8 == 0 && ld_y % 8 == 0 && ld_dx % 8 == 0, "relu_bwd: pitches must be multiples of 8");
     if (rows == 0) return B200SD_OK;
-    relu_bwd_kernel<<<grid_for(rows * (c / 8), 256), 256, 0, as_stream(stream)>>>(
+    launch_k(relu_bwd_kernel, grid_for(rows * (c / 8), 256), 256, 0, as_stream(stream), 
         static_cast<const __nv_bfloat16*>(dy), ld_dy, static_cast<const __nv_bfloat16*>(y), ld_y,
         static_cast<__nv_bfloat16*>(dx), ld_dx, rows, c);
     B200_CHECK_LAUNCH("relu_bwd");
@@ -422,10 +428,10 @@ extern "C" int b200sd_unpatchify(const void* tokens, int32_t tokens_f32, int64_t
     const long long total = n * channels * grid_h * patch_h * static_cast<long long>(grid_w) * patch_w;
     if (total == 0) return B200SD_OK;
     if (tokens_f32)
-        unpatchify_kernel<float><<<grid_for(total, 256), 256, 0, as_stream(stream)>>>(
+        launch_k(unpatchify_kernel<float>, grid_for(total, 256), 256, 0, as_stream(stream), 
             static_cast<const float*>(tokens), ld, image, n, channels, grid_h, grid_w, patch_h, patch_w);
     else
-        unpatchify_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, as_stream(stream)>>>(
+        launch_k(unpatchify_kernel<__nv_bfloat16>, grid_for(total, 256), 256, 0, as_stream(stream), 
             static_cast<const __nv_bfloat16*>(tokens), ld, image, n, channels, grid_h, grid_w, patch_h, patch_w);
     B200_CHECK_LAUNCH("unpatchify");
     return B200SD_OK;
@@ -438,7 +444,7 @@ extern "C" int b200sd_patchify(const float* image, void* tokens, int64_t ld, int
     B200_REQUIRE(ld >= static_cast<int64_t>(patch_h) * patch_w * channels, "patchify: token pitch too small");
     const long long total = n * grid_h * static_cast<long long>(grid_w) * ld;
     if (total == 0) return B200SD_OK;
-    patchify_kernel<<<grid_for(total, 256), 256, 0, as_stream(stream)>>>(
+    launch_k(patchify_kernel, grid_for(total, 256), 256, 0, as_stream(stream), 
         image, static_cast<__nv_bfloat16*>(tokens), ld, n, channels, grid_h, grid_w, patch_h, patch_w);
     B200_CHECK_LAUNCH("patchify");
     return B200SD_OK;

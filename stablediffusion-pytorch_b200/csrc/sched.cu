@@ -45,6 +45,7 @@ __global__ void __launch_bounds__(256) add_noise_kernel(const float* __restrict_
                                                         const float* __restrict__ sa, const float* __restrict__ sb,
                                                         int T, float* __restrict__ out, int64_t batch,
                                                         int64_t per_sample) {
+    pdl_enter();
     const int64_t total = batch * per_sample;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
     if (VEC) {
@@ -81,6 +82,7 @@ __global__ void __launch_bounds__(256)
                      const float* __restrict__ acp, const float* __restrict__ s1m, int T,
                      float* __restrict__ x_prev, float* __restrict__ x0, int64_t n, uint64_t seed,
                      uint64_t offset) {
+    pdl_enter();
     int64_t tt = t_dev ? *t_dev : t_host;
     tt = tt < 0 ? tt + T : tt;
     const PrevCoef c = prev_coef(betas, alphas, acp, s1m, static_cast<int>(tt));
@@ -136,6 +138,7 @@ __global__ void __launch_bounds__(256)
 template <typename OutT>
 __global__ void time_embedding_kernel(const int64_t* __restrict__ t, int64_t t_len, OutT* __restrict__ out,
                                       int64_t batch, int dim) {
+    pdl_enter();
     const int half = dim >> 1;
     const int64_t total = batch * half;
     for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -151,6 +154,7 @@ __global__ void time_embedding_kernel(const int64_t* __restrict__ t, int64_t t_l
 }
 
 __global__ void advance_t_kernel(int64_t* t, int64_t n, int64_t delta) {
+    pdl_enter();
     const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i < n) t[i] += delta;
 }
@@ -181,10 +185,10 @@ extern "C" int b200sd_sched_add_noise(const float* x0, const float* noise, const
     const int64_t items = vec ? batch * per_sample / 4 : batch * per_sample;
     const int grid = ew_grid(items, 256);
     if (vec)
-        add_noise_kernel<true><<<grid, 256, 0, as_stream(stream)>>>(x0, noise, t, t_len, sqrt_acp, sqrt_1m_acp,
+        launch_k(add_noise_kernel<true>, grid, 256, 0, as_stream(stream), x0, noise, t, t_len, sqrt_acp, sqrt_1m_acp,
                                                                       num_timesteps, out, batch, per_sample);
     else
-        add_noise_kernel<false><<<grid, 256, 0, as_stream(stream)>>>(x0, noise, t, t_len, sqrt_acp, sqrt_1m_acp,
+        launch_k(add_noise_kernel<false>, grid, 256, 0, as_stream(stream), x0, noise, t, t_len, sqrt_acp, sqrt_1m_acp,
                                                                        num_timesteps, out, batch, per_sample);
     B200_CHECK_LAUNCH("add_noise");
     return B200SD_OK;
@@ -206,11 +210,11 @@ extern "C" int b200sd_sched_prev_step(const float* xt, const float* eps, const f
     const int64_t items = vec ? n / 4 : n;
     const int grid = ew_grid(items, 256);
     if (vec)
-        prev_step_kernel<true><<<grid, 256, 0, as_stream(stream)>>>(xt, eps, eps_uncond, cfg_scale, z, t_dev, t_host,
+        launch_k(prev_step_kernel<true>, grid, 256, 0, as_stream(stream), xt, eps, eps_uncond, cfg_scale, z, t_dev, t_host,
                                                                       betas, alphas, acp, sqrt_1m_acp, num_timesteps,
                                                                       x_prev, x0, n, seed, offset);
     else
-        prev_step_kernel<false><<<grid, 256, 0, as_stream(stream)>>>(xt, eps, eps_uncond, cfg_scale, z, t_dev,
+        launch_k(prev_step_kernel<false>, grid, 256, 0, as_stream(stream), xt, eps, eps_uncond, cfg_scale, z, t_dev,
                                                                        t_host, betas, alphas, acp, sqrt_1m_acp,
                                                                        num_timesteps, x_prev, x0, n, seed, offset);
     B200_CHECK_LAUNCH("prev_step");
@@ -226,10 +230,9 @@ extern "C" int b200sd_time_embedding(const int64_t* t, int64_t t_len, void* out,
     if (batch == 0) return B200SD_OK;
     const int grid = ew_grid(batch * (dim / 2), 128);
     if (out_dtype == B200SD_DT_BF16)
-        time_embedding_kernel<__nv_bfloat16>
-            <<<grid, 128, 0, as_stream(stream)>>>(t, t_len, static_cast<__nv_bfloat16*>(out), batch, dim);
+        launch_k(time_embedding_kernel<__nv_bfloat16>, grid, 128, 0, as_stream(stream), t, t_len, static_cast<__nv_bfloat16*>(out), batch, dim);
     else if (out_dtype == B200SD_DT_F32)
-        time_embedding_kernel<float><<<grid, 128, 0, as_stream(stream)>>>(t, t_len, static_cast<float*>(out), batch, dim);
+        launch_k(time_embedding_kernel<float>, grid, 128, 0, as_stream(stream), t, t_len, static_cast<float*>(out), batch, dim);
     else {
         set_error("time_embedding: bad dtype %d", out_dtype);
         return B200SD_ERR_ARG;
@@ -241,7 +244,7 @@ extern "C" int b200sd_time_embedding(const int64_t* t, int64_t t_len, void* out,
 extern "C" int b200sd_advance_t(int64_t* t, int64_t t_len, int64_t delta, void* stream) {
     B200_REQUIRE(t && t_len >= 0, "advance_t: bad arguments");
     if (t_len == 0) return B200SD_OK;
-    advance_t_kernel<<<static_cast<int>((t_len + 127) / 128), 128, 0, as_stream(stream)>>>(t, t_len, delta);
+    launch_k(advance_t_kernel, static_cast<int>((t_len + 127) / 128), 128, 0, as_stream(stream), t, t_len, delta);
     B200_CHECK_LAUNCH("advance_t");
     return B200SD_OK;
 }

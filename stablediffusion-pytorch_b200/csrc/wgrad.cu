@@ -91,6 +91,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
+    pdl_trigger();
     if (warp == 0 && lane == 0) {
         for (int i = 0; i < 4; ++i) tma_prefetch_desc(&args.x_map[i]);
         tma_prefetch_desc(&args.dy_map);
@@ -114,6 +115,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -219,6 +221,7 @@ __global__ void __launch_bounds__(WG_THREADS, 1) wgrad_kernel(const __grid_const
 
 __global__ void wgrad_reduce_kernel(const float* __restrict__ partial, int splits, long long elems,
                                     float* __restrict__ out, int accumulate) {
+    pdl_enter();
     const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
     for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < (elems >> 2); i += stride) {
         float4 s = reinterpret_cast<const float4*>(partial)[i];
@@ -298,7 +301,7 @@ static int launch_wgrad(const WgradArgs& a, int grid, cudaStream_t st) {
         }
         configured = true;
     }
-    wgrad_kernel<BN, STAGES><<<grid, WG_THREADS, L::TOTAL, st>>>(a);
+    launch_k(wgrad_kernel<BN, STAGES>, grid, WG_THREADS, L::TOTAL, st, a);
     B200_CHECK_LAUNCH("wgrad");
     return B200SD_OK;
 }
@@ -391,7 +394,7 @@ extern "C" int b200sd_wgrad_reduce(const float* partial, int splits, int64_t ele
     long long blocks = (elems / 4 + 255) / 256;
     const long long cap = 8ll * sm_count();
     if (blocks > cap) blocks = cap;
-    wgrad_reduce_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(partial, splits, elems, out, accumulate);
+    launch_k(wgrad_reduce_kernel, (int)blocks, 256, 0, as_stream(stream), partial, splits, elems, out, accumulate);
     B200_CHECK_LAUNCH("wgrad_reduce");
     return B200SD_OK;
 }

@@ -1,0 +1,125 @@
+"""FusedAdam (clip + finite check + Adam + EMA in two launches) against the reference trainers' sequence
+(train_ddpm_cond_celebhq_multi_gpu.py:362-378): torch clip_grad_norm_ -> torch.optim.Adam.step -> per-parameter EMA.
+Tolerance: fp32 element-wise math in a different fusion order (fma contraction): rtol 1e-5 over 6 steps."""
+import copy
+import importlib
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+OPT = importlib.import_module("stablediffusion-pytorch_b200.optim")
+RTOL, ATOL = 1e-5, 5e-7   # parameters are O(1): 5e-7 absolute = a few ulp of the value, ~1e-4 of one update
+SHAPES = [(7,), (33, 65), (96, 40, 3, 3), (), (1000, 257), (3,)]
+DECAY = 0.9999
+
+
+def _params(seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return [torch.randn(s, device="cuda", generator=g).requires_grad_() for s in SHAPES]
+
+
+def _grads(step, scale=1.0):
+    g = torch.Generator(device="cuda").manual_seed(100 + step)
+    return [torch.randn(s, device="cuda", generator=g) * scale for s in SHAPES]
+
+
+def _reference_step(params, ema, opt, grads, max_norm):
+    for p, g in zip(params, grads):
+        p.grad = g.clone()
+    norm = None
+    if max_norm is not None:
+        norm = torch.nn.utils.clip_grad_norm_(params, max_norm)
+        if not torch.isfinite(norm):
+            opt.zero_grad(set_to_none=True)
+            return norm
+    opt.step()
+    if ema is not None:
+        with torch.no_grad():
+            for e, p in zip(ema, params):
+                e.data.mul_(DECAY).add_(p.data, alpha=1 - DECAY)
+    return norm
+
+
+def _close(a, b):
+    for u, v in zip(a, b):
+        torch.testing.assert_close(u.detach(), v.detach(), rtol=RTOL, atol=ATOL)
+
+
+@pytest.mark.parametrize("max_norm,wd,with_ema", [(1.0, 0.0, True), (None, 0.0, True), (0.5, 0.01, False)])
+def test_matches_clip_adam_ema(max_norm, wd, with_ema):
+    pr, po = _params(), _params()
+    er = [p.detach().clone() for p in pr] if with_ema else None
+    eo = [p.detach().clone() for p in po] if with_ema else None
+    ref = torch.optim.Adam(pr, lr=3e-3, betas=(0.9, 0.99), eps=1e-8, weight_decay=wd)
+    ours = OPT.FusedAdam(po, lr=3e-3, betas=(0.9, 0.99), eps=1e-8, weight_decay=wd, max_grad_norm=max_norm,
+                         ema_params=eo, ema_decay=DECAY)
+    for step in range(6):
+        grads = _grads(step, scale=0.3 if step % 2 else 3.0)   # below and above the clip threshold
+        norm = _reference_step(pr, er, ref, grads, max_norm)
+        for p, g in zip(po, grads):
+            p.grad = g.clone()
+        ours.step()
+        if norm is not None:
+            torch.testing.assert_close(ours.grad_norm, norm, rtol=1e-5, atol=0)
+        _close(po, pr)
+        if with_ema:
+            _close(eo, er)
+        _close([ours.state[p]["exp_avg"] for p in po], [ref.state[p]["exp_avg"] for p in pr])
+        _close([ours.state[p]["exp_avg_sq"] for p in po], [ref.state[p]["exp_avg_sq"] for p in pr])
+    assert ours._g is not None      # scattered gradients went through the private flat buffer
+
+
+def test_flat_gradient_views_are_read_in_place_and_nonfinite_steps_are_skipped():
+    po, pr = _params(1), _params(1)
+    ref = torch.optim.Adam(pr, lr=1e-3)
+    ours = OPT.FusedAdam(po, lr=1e-3, max_grad_norm=1.0)
+    flat = torch.zeros(ours._total, device="cuda")
+    views = [flat[o:o + p.numel()].view(p.shape) for p, o in zip(po, ours._off)]
+    for step in range(3):
+        grads = _grads(step)
+        if step == 1:
+            grads[2][0, 0, 0, 0] = float("inf")
+        for v, g, p in zip(views, grads, po):
+            v.copy_(g)
+            p.grad = v
+        before = [p.detach().clone() for p in po]
+        ours.step()
+        norm = _reference_step(pr, None, ref, grads, 1.0)
+        if step == 1:
+            assert not torch.isfinite(norm) and ours.last_step_applied.item() == 0.0
+            for b, p in zip(before, po):
+                assert torch.equal(b, p.detach())
+        else:
+            assert ours.last_step_applied.item() == 1.0
+        _close(po, pr)
+    assert ours._g is None
+    assert ours._scalars[3].item() == 2.0     # the skipped step did not advance the bias correction
+
+
+def test_state_dict_interchanges_with_torch_adam():
+    po, pr = _params(2), _params(2)
+    ours = OPT.FusedAdam(po, lr=2e-3, max_grad_norm=1.0)
+    for step in range(2):
+        for p, g in zip(po, _grads(step)):
+            p.grad = g
+        ours.step()
+    sd = copy.deepcopy(ours.state_dict())
+    with torch.no_grad():
+        for a, b in zip(pr, po):
+            a.copy_(b)
+    ref = torch.optim.Adam(pr, lr=2e-3)
+    ref.load_state_dict(sd)
+    again = OPT.FusedAdam(_params(2), lr=2e-3, max_grad_norm=1.0)
+    with torch.no_grad():
+        for a, b in zip(again._all, po):
+            a.copy_(b)
+    again.load_state_dict(sd)
+    grads = _grads(7, scale=1e-4)     # norm ~0.05, below the threshold: clipping is the identity, torch Adam alone is the reference
+    for opt, ps in ((ref, pr), (ours, po), (again, again._all)):
+        for p, g in zip(ps, grads):
+            p.grad = g.clone()
+        opt.step()
+    _close(po, pr)
+    _close(again._all, pr)
