@@ -67,6 +67,14 @@ int b200sd_sched_prev_step(const float* xt, const float* eps, const float* eps_u
  * kept on the device so a whole sampling step (UNet forward + ancestral update + counter) replays as one CUDA graph. */
 int b200sd_advance_t(int64_t* t, int64_t t_len, int64_t delta, void* stream);
 
+/* One update of DDPMSampler.sample_one_step (scheduler/linear_noise_scheduler.py:106-131: c1 = coeff_1[t],
+ * c2 = -coeff_2[t], sigma = sqrt(posterior_variance[t])) or DDIMSampler.sample_one_step (:185-204: c1 =
+ * sqrt(a_prev / a_t), c2 = sqrt(1 - a_prev - sigma^2) - sqrt(a_prev (1 - a_t) / a_t)), coefficients computed by the
+ * caller: out = (c1 * x + c2 * eps) + sigma * z, each operation rounded separately in that order. z may be NULL
+ * (term dropped). out may alias x. fp32, n elements. */
+int b200sd_sampler_step(const float* x, const float* eps, const float* z, float c1, float c2, float sigma, float* out,
+                        int64_t n, void* stream);
+
 /* get_time_embedding — models/blocks.py:5-24 (and models/transformer.py:18-40).
  * out[b, j] = sin(t[b]/f_j), out[b, half+j] = cos(t[b]/f_j), f_j = 10000^(j/half); t int64 (t_len = batch or 1).
  * out is bf16 or fp32 [batch, dim]. */

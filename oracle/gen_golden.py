@@ -272,7 +272,84 @@ def gen_cim():
     return ok
 
 
+def sampler_model(x, t, cond=None):
+    """Deterministic stand-in denoiser whose arithmetic (*, +, / on fp32) is bit-reproducible on any device."""
+    s = (t.float() * 0.001).view(-1, 1, 1, 1)   # (not "/ 1000": CUDA divides by a scalar through its reciprocal)
+    out = x * 0.5 + s * x.flip(-1)
+    if cond is not None:
+        out = out + cond["image"]
+    return out
+
+
+def gen_samplers():
+    """DDPMSampler / DDIMSampler of the real reference on a stand-in model with every randn_like draw recorded."""
+    sys.path.insert(0, REF)
+    import scheduler.linear_noise_scheduler as ref_sched
+    sys.path.pop(0)
+    import numpy as np
+    S = _load(os.path.join(ROOT, "oracle", "scheduler_np.py"), "oracle_scheduler_np")
+    os.makedirs(GOLD, exist_ok=True)
+    g = torch.Generator().manual_seed(77)
+    draws = []
+    real_randn_like = torch.randn_like
+
+    def recording_randn_like(x, *a, **k):
+        z = torch.randn(x.shape, generator=g)
+        draws.append(z)
+        return z
+
+    out, ok = {}, True
+    x_T = torch.randn(3, 4, 8, 8, generator=g)
+    cond = {"image": torch.randn(3, 4, 8, 8, generator=g) * 0.1}
+    torch.randn_like = recording_randn_like
+    try:
+        for name, kw in (("ddim_linear_eta0", dict(steps=10, method="linear", eta=0.0)),
+                         ("ddim_quadratic_eta05", dict(steps=7, method="quadratic", eta=0.5)),
+                         ("ddim_linear_eta1_trace", dict(steps=20, method="linear", eta=1.0, only_return_x_0=False,
+                                                         interval=4))):
+            draws.clear()
+            smp = ref_sched.DDIMSampler(sampler_model, (0.0015, 0.0195), 1000)
+            res = smp.forward(x_T.clone(), cond, None, **kw)
+            out[name] = {"kw": kw, "beta": (0.0015, 0.0195), "T": 1000, "out": res.clone(), "z": [z.clone() for z in draws]}
+            # oracle restatement against the reference
+            bar = S.sampler_alpha_bar((0.0015, 0.0195), 1000)[2]
+            ts, tp = S.ddim_timesteps(1000, kw["steps"], kw["method"])
+            x = x_T.numpy()
+            for k, i in enumerate(reversed(range(kw["steps"]))):
+                t = torch.full((3,), int(ts[i]), dtype=torch.long)
+                x = S.ddim_step(bar, x, sampler_model(torch.from_numpy(x), t, cond).numpy(), draws[k].numpy(), int(ts[i]),
+                                int(tp[i]), kw["eta"])
+            final = res if res.dim() == 4 else res[:, -1]
+            want = final.numpy() if res.dim() == 4 else np.clip(x, -1, 1)
+            same = np.array_equal(x if res.dim() == 4 else want, final.numpy())
+            print(f"{name}: oracle == reference: {same}")
+            ok &= bool(same)
+        draws.clear()
+        smp = ref_sched.DDPMSampler(sampler_model, (1e-4, 0.02), 40)
+        res = smp.forward(x_T.clone())
+        out["ddpm_T40"] = {"beta": (1e-4, 0.02), "T": 40, "out": res.clone(), "z": [z.clone() for z in draws],
+                           "state_keys": list(smp.state_dict().keys())}
+        x = x_T.numpy()
+        for k, ts_ in enumerate(reversed(range(40))):
+            t = torch.full((3,), ts_, dtype=torch.long)
+            z = draws[k].numpy() if ts_ > 0 else None
+            x = S.ddpm_step((1e-4, 0.02), 40, x, sampler_model(torch.from_numpy(x), t).numpy(), z, ts_)
+        same = np.array_equal(x, res.numpy())
+        print(f"ddpm_T40: oracle == reference: {same}")
+        ok &= bool(same)
+    finally:
+        torch.randn_like = real_randn_like
+    out["x_T"], out["cond_image"] = x_T, cond["image"]
+    torch.save(out, os.path.join(GOLD, "samplers.pt"))
+    return ok
+
+
 def main():
+    if "--only-samplers" in sys.argv:
+        if not gen_samplers():
+            print("ORACLE DISAGREES WITH THE REFERENCE")
+            sys.exit(1)
+        return
     if "--only-cim" in sys.argv:
         if not gen_cim():
             print("ORACLE DISAGREES WITH THE REFERENCE")
@@ -368,6 +445,7 @@ def main():
     print("scheduler fixtures written")
     ok &= gen_dit()
     ok &= gen_cim()
+    ok &= gen_samplers()
     if not ok:
         print("ORACLE DISAGREES WITH THE REFERENCE")
         sys.exit(1)

@@ -72,3 +72,63 @@ def time_embedding(t, dim):
     factor = np.power(f32(10000.0), (np.arange(half, dtype=f32) / f32(half)).astype(f32)).astype(f32)
     arg = (np.asarray(t, dtype=np.int64).reshape(-1, 1).astype(f32) / factor[None, :]).astype(f32)
     return np.concatenate([np.sin(arg), np.cos(arg)], axis=-1).astype(f32)
+
+
+# ------------------------------------------------------------------------------------------------ samplers
+def sampler_alpha_bar(beta, T):
+    """DDPMSampler / DDIMSampler tables — scheduler/linear_noise_scheduler.py:101-112,181-185 (torch builds them, as in
+    make_tables above)."""
+    import torch
+    beta_t = torch.linspace(*beta, T, dtype=torch.float32)
+    alpha_t = 1.0 - beta_t
+    return beta_t.numpy(), alpha_t.numpy(), torch.cumprod(alpha_t, dim=0).numpy()
+
+
+def ddim_timesteps(T, steps, method):
+    """DDIMSampler.forward — :229-241."""
+    if method == "linear":
+        ts = np.asarray(list(range(0, T, T // steps)))
+    elif method == "quadratic":
+        ts = (np.linspace(0, np.sqrt(T * 0.8), steps) ** 2).astype(np.int32)
+    else:
+        raise NotImplementedError(f"sampling method {method} is not implemented!")
+    ts = ts + 1
+    return ts, np.concatenate([[0], ts[:-1]])
+
+
+def ddim_coeffs(alpha_bar, time_step, prev_time_step, eta):
+    """(c1, c2, sigma) of DDIMSampler.sample_one_step — :186-203. The coefficient arithmetic is torch's, evaluated with
+    torch on the host as the reference run that produced the golden vectors did: this build's ATen CPU sqrt is NOT
+    correctly rounded for every input (measured: sqrt(0.61737615...) comes out 1 ulp below numpy's / CUDA's IEEE
+    result), so a numpy restatement of these five scalar operations cannot be pinned bit-exactly."""
+    import torch
+    a = torch.from_numpy(np.asarray(alpha_bar, dtype=f32))
+    alpha_t, alpha_t_prev = a[int(time_step)], a[int(prev_time_step)]
+    sigma_t = eta * torch.sqrt((1 - alpha_t_prev) / (1 - alpha_t) * (1 - alpha_t / alpha_t_prev))
+    c1 = torch.sqrt(alpha_t_prev / alpha_t)
+    c2 = torch.sqrt(1 - alpha_t_prev - sigma_t ** 2) - torch.sqrt((alpha_t_prev * (1 - alpha_t)) / alpha_t)
+    return f32(c1.item()), f32(c2.item()), f32(sigma_t.item())
+
+
+def ddim_step(alpha_bar, x_t, eps, z, time_step, prev_time_step, eta):
+    """DDIMSampler.sample_one_step — :185-204; the update itself float32 op by op in numpy."""
+    c1, c2, sigma = ddim_coeffs(alpha_bar, time_step, prev_time_step, eta)
+    return (c1 * x_t.astype(f32) + c2 * eps.astype(f32)) + sigma * z.astype(f32)
+
+
+def ddpm_step(beta, T, x_t, eps, z, time_step):
+    """DDPMSampler.sample_one_step — :106-139 (z ignored at time_step 0)."""
+    import torch
+    import torch.nn.functional as F
+    beta_t = torch.linspace(*beta, T, dtype=torch.float32)
+    alpha_t = 1.0 - beta_t
+    bar = torch.cumprod(alpha_t, dim=0)
+    prev = F.pad(bar[:-1], (1, 0), value=1.0)
+    coeff_1 = torch.sqrt(1.0 / alpha_t)
+    coeff_2 = coeff_1 * (1.0 - alpha_t) / torch.sqrt(1.0 - bar)
+    var = beta_t * (1.0 - prev) / (1.0 - bar)
+    c1, c2 = f32(coeff_1[time_step].item()), f32(coeff_2[time_step].item())
+    mean = c1 * x_t.astype(f32) - c2 * eps.astype(f32)
+    if time_step == 0:
+        return mean
+    return mean + np.sqrt(f32(var[time_step].item()), dtype=f32) * z.astype(f32)

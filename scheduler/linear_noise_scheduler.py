@@ -71,3 +71,152 @@ class LinearNoiseScheduler:
         return _rt.sched_prev_step(xt.float(), noise_pred.float(), t, (betas, alphas, acp, s1m), z=z,
                                    eps_uncond=noise_pred_uncond, cfg_scale=cf_guidance_scale, seed=self.seed,
                                    offset=off)
+
+
+# --------------------------------------------------------------------------------------------------------------
+# DDPMSampler / DDIMSampler — reference scheduler/linear_noise_scheduler.py:80-256 (the samplers the GUIs and
+# batch_condition_image_generator.py:323 drive, usually through a classifier-free-guidance wrapper as `model`).
+# Same constructors, buffers, forward() signatures and return values. Per step the reference uploads the alpha table,
+# gathers two (B,1,1,1) coefficient tensors and runs ~15 elementwise kernels; here the coefficients of the step are
+# computed once on the host with the same fp32 torch operations (so they are the same numbers) and the update is one
+# kernel, bit-identical to the reference's result for the same model output and the same z.
+import numpy as np
+import torch.nn as nn
+import torch.nn.functional as F
+from tqdm import tqdm
+
+
+def extract(v, i, shape):
+    """v[i] reshaped to (batch, 1, 1, ...) — reference :80-91."""
+    out = torch.gather(v, index=i, dim=0)
+    out = out.to(device=i.device, dtype=torch.float32)
+    return out.view([i.shape[0]] + [1] * (len(shape) - 1))
+
+
+def _require_cuda(x_t, who):
+    if not x_t.is_cuda:
+        raise _rt.B200Error(f"{who}: CUDA tensors required (no CPU implementation in this package)")
+
+
+class DDPMSampler(nn.Module):
+    """Ancestral sampler over all T steps with an unconditional `model(x_t, t)` — reference :94-170."""
+
+    NAN_CHECK_EVERY = 50   # the reference syncs the host on every step for its NaN check (:136); NaNs do not heal,
+                           # so checking every 50th step and the last raises the same error without the 1000 syncs
+
+    def __init__(self, model, beta, T):
+        super().__init__()
+        self.model = model
+        self.T = T
+        self.register_buffer("beta_t", torch.linspace(*beta, T, dtype=torch.float32))
+        alpha_t = 1.0 - self.beta_t
+        alpha_t_bar = torch.cumprod(alpha_t, dim=0)
+        alpha_t_bar_prev = F.pad(alpha_t_bar[:-1], (1, 0), value=1.0)
+        self.register_buffer("coeff_1", torch.sqrt(1.0 / alpha_t))
+        self.register_buffer("coeff_2", self.coeff_1 * (1.0 - alpha_t) / torch.sqrt(1.0 - alpha_t_bar))
+        self.register_buffer("posterior_variance", self.beta_t * (1.0 - alpha_t_bar_prev) / (1.0 - alpha_t_bar))
+        self._host = None
+
+    def _coeffs(self, time_step):
+        if self._host is None or self._host[0] is not self.coeff_1:
+            self._host = (self.coeff_1, self.coeff_1.detach().float().cpu(), self.coeff_2.detach().float().cpu(),
+                          torch.sqrt(self.posterior_variance.detach().float().cpu()))
+        _, c1, c2, sd = self._host
+        return c1[time_step].item(), c2[time_step].item(), sd[time_step].item()
+
+    @torch.no_grad()
+    def cal_mean_variance(self, x_t, t):
+        epsilon_theta = self.model(x_t, t)
+        ts = int(t.reshape(-1)[0].item())
+        c1, c2, _ = self._coeffs(ts)
+        mean = _rt.sampler_step(x_t.float().contiguous(), epsilon_theta.float().contiguous(), None, c1, -c2, 0.0)
+        return mean, extract(self.posterior_variance.to(x_t.device), t, x_t.shape)
+
+    @torch.no_grad()
+    def sample_one_step(self, x_t, time_step, z=None):
+        _require_cuda(x_t, "DDPMSampler")
+        t = torch.full((x_t.shape[0],), time_step, device=x_t.device, dtype=torch.long)
+        epsilon_theta = self.model(x_t, t)
+        c1, c2, sd = self._coeffs(int(time_step))
+        if time_step > 0 and z is None:
+            z = torch.randn_like(x_t)
+        x_prev = _rt.sampler_step(x_t.float().contiguous(), epsilon_theta.float().contiguous(),
+                                  z if time_step > 0 else None, c1, -c2, sd)
+        if time_step % self.NAN_CHECK_EVERY == 0 and torch.isnan(x_prev).any().item():
+            raise ValueError("nan in tensor!")
+        return x_prev
+
+    @torch.no_grad()
+    def forward(self, x_t, only_return_x_0=True, interval=1, **kwargs):
+        x = [x_t]
+        with tqdm(reversed(range(self.T)), colour="#6565b5", total=self.T) as sampling_steps:
+            for time_step in sampling_steps:
+                x_t = self.sample_one_step(x_t, time_step)
+                if not only_return_x_0 and ((self.T - time_step) % interval == 0 or time_step == 0):
+                    x.append(torch.clip(x_t, -1.0, 1.0))
+                sampling_steps.set_postfix(ordered_dict={"step": time_step + 1, "sample": len(x)})
+        if only_return_x_0:
+            return x_t
+        return torch.stack(x, dim=1)
+
+
+class DDIMSampler(nn.Module):
+    """DDIM sampler (eta = 0) .. DDPM-like (eta = 1) over a linear or quadratic sub-sequence of the T timesteps, with a
+    conditional `model(x_t, t, cond_input)` — reference :174-256. `uncond_input` is stored, as in the reference; the
+    classifier-free-guidance combine is the job of whatever module is passed as `model`
+    (batch_condition_image_generator.py:241-254)."""
+
+    draw_noise_when_eta_is_zero = True   # the reference draws randn_like(x_t) every step even when sigma = 0 (:194);
+                                         # keeping the draw keeps torch's CUDA generator in the reference's state
+
+    def __init__(self, model, beta, T):
+        super().__init__()
+        self.model = model
+        self.T = T
+        beta_t = torch.linspace(*beta, T, dtype=torch.float32)
+        alpha_t = 1.0 - beta_t
+        self.alpha_t_bar = torch.cumprod(alpha_t, dim=0)
+
+    def step_coefficients(self, time_step, prev_time_step, eta):
+        """(c1, c2, sigma) of x_{t-1} = c1 x_t + c2 eps + sigma z, with the reference's fp32 operations (:186-203)."""
+        a = self.alpha_t_bar.detach().float().cpu()
+        alpha_t, alpha_t_prev = a[int(time_step)], a[int(prev_time_step)]
+        sigma_t = eta * torch.sqrt((1 - alpha_t_prev) / (1 - alpha_t) * (1 - alpha_t / alpha_t_prev))
+        c1 = torch.sqrt(alpha_t_prev / alpha_t)
+        c2 = torch.sqrt(1 - alpha_t_prev - sigma_t ** 2) - torch.sqrt((alpha_t_prev * (1 - alpha_t)) / alpha_t)
+        return c1.item(), c2.item(), sigma_t.item()
+
+    @torch.no_grad()
+    def sample_one_step(self, x_t, time_step, prev_time_step, eta, z=None):
+        _require_cuda(x_t, "DDIMSampler")
+        t = torch.full((x_t.shape[0],), int(time_step), device=x_t.device, dtype=torch.long)
+        c1, c2, sigma = self.step_coefficients(time_step, prev_time_step, eta)
+        epsilon_theta_t = self.model(x_t, t, self.cond_input)
+        if z is None and (sigma != 0.0 or self.draw_noise_when_eta_is_zero):
+            z = torch.randn_like(x_t)
+        return _rt.sampler_step(x_t.float().contiguous(), epsilon_theta_t.float().contiguous(), z, c1, c2, sigma)
+
+    @torch.no_grad()
+    def forward(self, x_t, cond_input, uncond_input, steps=1, method="linear", eta=0.0, only_return_x_0=True,
+                interval=1):
+        self.cond_input = cond_input
+        self.uncond_input = uncond_input
+        if method == "linear":
+            a = self.T // steps
+            time_steps = np.asarray(list(range(0, self.T, a)))
+        elif method == "quadratic":
+            time_steps = (np.linspace(0, np.sqrt(self.T * 0.8), steps) ** 2).astype(np.int32)
+        else:
+            raise NotImplementedError(f"sampling method {method} is not implemented!")
+        time_steps = time_steps + 1
+        time_steps_prev = np.concatenate([[0], time_steps[:-1]])
+        x = [x_t]
+        with tqdm(reversed(range(0, steps)), colour="#6565b5", total=steps) as sampling_steps:
+            for i in sampling_steps:
+                x_t = self.sample_one_step(x_t, time_steps[i], time_steps_prev[i], eta)
+                if not only_return_x_0 and ((steps - i) % interval == 0 or i == 0):
+                    x.append(torch.clip(x_t, -1.0, 1.0))
+                sampling_steps.set_postfix(ordered_dict={"step": i + 1, "sample": len(x)})
+        if only_return_x_0:
+            return x_t
+        return torch.stack(x, dim=1)

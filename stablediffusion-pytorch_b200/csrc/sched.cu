@@ -169,6 +169,21 @@ static inline int ew_grid(int64_t work_items, int threads) {
     return static_cast<int>(blocks);
 }
 
+// DDIM / DDPM sampler update (scheduler/linear_noise_scheduler.py:106-131 DDPMSampler, :185-204 DDIMSampler):
+// out = (c1 * x + c2 * eps) + sigma * z, every product and sum rounded separately in the reference's order (no fma),
+// so that the result is bit-identical to the reference's chain of elementwise torch kernels.
+__global__ void sampler_step_kernel(const float* __restrict__ x, const float* __restrict__ eps,
+                                    const float* __restrict__ z, float c1, float c2, float sigma,
+                                    float* __restrict__ out, long long n) {
+    pdl_enter();
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+        float r = __fadd_rn(__fmul_rn(c1, x[i]), __fmul_rn(c2, eps[i]));
+        if (z) r = __fadd_rn(r, __fmul_rn(sigma, z[i]));
+        out[i] = r;
+    }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -246,5 +261,15 @@ extern "C" int b200sd_advance_t(int64_t* t, int64_t t_len, int64_t delta, void* 
     if (t_len == 0) return B200SD_OK;
     launch_k(advance_t_kernel, static_cast<int>((t_len + 127) / 128), 128, 0, as_stream(stream), t, t_len, delta);
     B200_CHECK_LAUNCH("advance_t");
+    return B200SD_OK;
+}
+
+extern "C" int b200sd_sampler_step(const float* x, const float* eps, const float* z, float c1, float c2, float sigma,
+                                   float* out, int64_t n, void* stream) {
+    B200_REQUIRE(x && eps && out && n >= 0, "sampler_step: bad arguments");
+    if (n == 0) return B200SD_OK;
+    launch_k(sampler_step_kernel, ew_grid(n, 256), 256, 0, as_stream(stream), x, eps, z, c1, c2, sigma, out,
+             static_cast<long long>(n));
+    B200_CHECK_LAUNCH("sampler_step");
     return B200SD_OK;
 }

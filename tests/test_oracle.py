@@ -116,3 +116,37 @@ def test_cim_oracle_vs_reference_golden():
             got["x"] = x2.grad
             for k, g in f["grads"].items():
                 assert relerr(got[k], g) < 1e-5, (name, k)
+
+
+def _sampler_model(x, t, cond=None):
+    """The stand-in denoiser of oracle/gen_golden.py:gen_samplers (fp32 * and + only: bit-reproducible anywhere)."""
+    s = (t.float() * 0.001).view(-1, 1, 1, 1)   # (not "/ 1000": CUDA divides by a scalar through its reciprocal)
+    out = x * 0.5 + s * x.flip(-1)
+    if cond is not None:
+        out = out + cond["image"]
+    return out
+
+
+def test_sampler_oracle_bit_exact_vs_reference_outputs():
+    fx = torch.load(os.path.join(GOLD, "samplers.pt"), weights_only=False)
+    x_T, cond = fx["x_T"], {"image": fx["cond_image"]}
+    for name in ("ddim_linear_eta0", "ddim_quadratic_eta05", "ddim_linear_eta1_trace"):
+        c = fx[name]
+        kw = c["kw"]
+        bar = onp.sampler_alpha_bar(c["beta"], c["T"])[2]
+        ts, tp = onp.ddim_timesteps(c["T"], kw["steps"], kw["method"])
+        x = x_T.numpy()
+        for k, i in enumerate(reversed(range(kw["steps"]))):
+            t = torch.full((x.shape[0],), int(ts[i]), dtype=torch.long)
+            x = onp.ddim_step(bar, x, _sampler_model(torch.from_numpy(x), t, cond).numpy(), c["z"][k].numpy(),
+                              int(ts[i]), int(tp[i]), kw["eta"])
+        want = c["out"] if c["out"].dim() == 4 else c["out"][:, -1]
+        got = x if c["out"].dim() == 4 else np.clip(x, -1, 1)
+        assert np.array_equal(got, want.numpy()), name
+    c = fx["ddpm_T40"]
+    x = x_T.numpy()
+    for k, ts_ in enumerate(reversed(range(c["T"]))):
+        t = torch.full((x.shape[0],), ts_, dtype=torch.long)
+        x = onp.ddpm_step(c["beta"], c["T"], x, _sampler_model(torch.from_numpy(x), t).numpy(),
+                          c["z"][k].numpy() if ts_ > 0 else None, ts_)
+    assert np.array_equal(x, c["out"].numpy())
