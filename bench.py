@@ -523,7 +523,8 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=
     train_ddpm_cond_celebhq_multi_gpu.py:341-378 does it — add_noise, bf16-autocast forward, MSE, backward (DDP's
     bucketed NCCL all-reduce overlapped with it when world > 1), clip_grad_norm_(1.0), Adam, EMA — per-GPU batch 16
     (config/celebhq_text_image_cond.py:76). Forward and backward of every heavy op run on libb200sd.so.
-    value: inputs resident on the device. e2e: latents / text / mask copied from pinned host memory every step and
+    value: inputs resident on the device. e2e: latents / text / mask copied from pinned host memory every step (on the
+    copy stream of sdb200.data.DevicePrefetcher, one batch ahead) and
     loss.item() read back every step, as the reference loop does (:327-354)."""
     import copy
     import torch.distributed as dist
@@ -556,12 +557,8 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=
     t_h = torch.randint(0, T_STEPS, (B,), generator=g).pin_memory()
     res = {"x": x_h.to(dev), "text": text_h.to(dev), "mask": mask_h.to(dev), "noise": noise_h.to(dev), "t": t_h.to(dev)}
 
-    def step(from_host):
-        if from_host:
-            x0, text, mask = (v.to(dev, non_blocking=True) for v in (x_h, text_h, mask_h))
-            noise, t = noise_h.to(dev, non_blocking=True), t_h.to(dev, non_blocking=True)
-        else:
-            x0, text, mask, noise, t = res["x"], res["text"], res["mask"], res["noise"], res["t"]
+    def step(batch, from_host):
+        x0, text, mask, noise, t = batch
         noisy = sched.add_noise(x0, noise, t)
         with torch.autocast("cuda", dtype=torch.bfloat16):
             pred = net(noisy, t, {k: v for k, v in (("text", text), ("image", mask)) if k in cond_keys})
@@ -578,16 +575,24 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=
                 torch._foreach_add_(list(ema.parameters()), list(model.parameters()), alpha=0.001)
         return loss.item() if from_host else loss.detach()
 
+    def batches(k, from_host):
+        """k batches: device-resident tensors, or the pinned host buffers uploaded every step — batch i+1 on the
+        prefetcher's copy stream while step i computes (sdb200/data.py)."""
+        if not from_host:
+            return ((res["x"], res["text"], res["mask"], res["noise"], res["t"]) for _ in range(k))
+        from sdb200.data import DevicePrefetcher
+        return DevicePrefetcher(((x_h, text_h, mask_h, noise_h, t_h) for _ in range(k)), dev)
+
     out = {}
     for name, from_host in (("value", False), ("e2e", True)):
-        for _ in range(W):
-            step(from_host)
+        for b in batches(W, from_host):
+            step(b, from_host)
         l0 = rt.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         e0.record()
-        for _ in range(K):
-            last = step(from_host)
+        for b in batches(K, from_host):
+            last = step(b, from_host)
         e1.record()
         barrier()
         (ms,) = max_over_ranks([e0.elapsed_time(e1)])
