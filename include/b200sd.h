@@ -365,6 +365,17 @@ int b200sd_wgrad_scatter(const float* partial, int32_t splits, int32_t n_out, in
                          int32_t cp, int32_t taps, const int32_t* tap_off, float* out, int64_t s_co, int64_t s_ci,
                          int32_t accumulate, void* stream);
 
+/* ------------------------------------------------------------------------------------------ VQVAE.quantize
+ * models/vqvae.py:93-128 (called by VQVAE.encode :130-139 when latents are pre-generated,
+ * gen_vqvae_latents_multi_GPU.py:42-188). x: fp32 rows [n*hw, ld_x] (NHWC pixels, c <= 16 channels); codebook fp32
+ * [n_codes, c] (nn.Embedding weight). idx[n*hw]: index of the nearest code (first of equal minima); zq_nchw: fp32
+ * [n, c, hw] = x + (e - x) as the straight-through expression evaluates; loss[0] = mean((e - x)^2), the value of both
+ * codebook_loss and commitment_loss. partial: fp32 scratch [b200sd_vq_blocks(n*hw)]; counter: one zeroed uint32. */
+int b200sd_vq_blocks(int64_t rows);
+int b200sd_vq_nearest(const float* x, int64_t ld_x, const float* codebook, int32_t n_codes, int32_t c, int64_t n,
+                      int64_t hw, int64_t* idx, float* zq_nchw, float* partial, float* loss, uint32_t* counter,
+                      void* stream);
+
 /* ------------------------------------------------------------------------------------------ optimizer step
  * Replaces, for one training step, torch.nn.utils.clip_grad_norm_ + the isfinite(grad_norm) check + Adam.step + the
  * per-parameter EMA loop of train_ddpm_cond_celebhq_multi_gpu.py:362-378 (same code in Model_DiT_9L_train.py).

@@ -344,7 +344,50 @@ def gen_samplers():
     return ok
 
 
+def gen_vqvae_encode():
+    """VQVAE encoder + quantiser (SURVEY f-4): the call that produces the latents the LDM trainers consume."""
+    sys.path.insert(0, REF)
+    from models.vqvae import VQVAE as RefVQVAE
+    sys.path.pop(0)
+    O = _load(os.path.join(ROOT, "oracle", "unet_torch.py"), "oracle_unet_torch")
+    acfg = yaml.safe_load(open(os.path.join(REF, "config/celebhq.yaml")))['autoencoder_params']
+    torch.manual_seed(1111)
+    vae = RefVQVAE(3, acfg).eval()
+    x_im = torch.rand(2, 3, 64, 64, generator=torch.Generator().manual_seed(6)) * 2 - 1
+    feats = {}
+    hook = vae.pre_quant_conv.register_forward_hook(lambda m, i, o: feats.__setitem__("pre", o.detach().float().clone()))
+    with torch.no_grad():
+        with torch.autocast("cpu", dtype=torch.bfloat16):
+            vae.encode(x_im)
+        pre_bf16 = feats["pre"]
+        zq, losses = vae.encode(x_im)
+        pre = feats["pre"]
+        hook.remove()
+        _, _, ref_idx = vae.quantize(pre)
+        o_pre = O.vqvae_encode_latent(vae.state_dict(), acfg, x_im)
+        o_q, o_mse, o_idx, d2 = O.vq_quantize(pre, vae.embedding.weight.detach())
+    e_or, e_bf = relerr(o_pre, pre), relerr(pre_bf16, pre)
+    same = (o_idx == ref_idx).float().mean().item()
+    rows = torch.arange(d2.shape[0])   # where the reference's cdist picked another code it must be a numerical tie
+    best = d2[rows, o_idx.reshape(-1)]
+    gap = ((d2[rows, ref_idx.reshape(-1)] - best) / best.clamp_min(1e-30)).max().item()
+    print(f"vqvae_encode: oracle-vs-ref latent {e_or:.2e}  ref bf16-autocast-vs-fp32 {e_bf:.2e}  indices equal "
+          f"{same:.4f}  worst relative distance gap of a differing index {gap:.2e}  "
+          f"mse {o_mse.item():.6f} vs {losses['codebook_loss'].item():.6f}  quant_out equal {torch.equal(o_q, zq) if same == 1 else 'n/a'}")
+    ok = e_or < 1e-5 and gap < 1e-5 and abs(o_mse.item() - losses['codebook_loss'].item()) < 1e-6
+    torch.save({"config": acfg, "seed": 1111, "inputs": {"x": x_im}, "pre_quant": pre, "quant_out": zq,
+                "indices": ref_idx, "codebook_loss": losses["codebook_loss"], "commitment_loss": losses["commitment_loss"],
+                "ref_bf16_autocast_relerr": e_bf, "ref_bf16_autocast_l2err": l2err(pre_bf16, pre)},
+               os.path.join(GOLD, "vqvae_encode.pt"))
+    return ok
+
+
 def main():
+    if "--only-vqvae-encode" in sys.argv:
+        if not gen_vqvae_encode():
+            print("ORACLE DISAGREES WITH THE REFERENCE")
+            sys.exit(1)
+        return
     if "--only-samplers" in sys.argv:
         if not gen_samplers():
             print("ORACLE DISAGREES WITH THE REFERENCE")
@@ -446,6 +489,7 @@ def main():
     ok &= gen_dit()
     ok &= gen_cim()
     ok &= gen_samplers()
+    ok &= gen_vqvae_encode()
     if not ok:
         print("ORACLE DISAGREES WITH THE REFERENCE")
         sys.exit(1)

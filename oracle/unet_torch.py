@@ -190,3 +190,33 @@ def vqvae_decode(state_dict, cfg, z):
                        cfg["down_sample"][i - 1], False, attn=cfg["attn_down"][i - 1])
     out = F.silu(F.group_norm(out, groups, sd["decoder_norm_out.weight"], sd["decoder_norm_out.bias"], 1e-5))
     return F.conv2d(out, sd["decoder_conv_out.weight"], sd["decoder_conv_out.bias"], padding=1)
+
+
+def vqvae_encode_latent(state_dict, cfg, x):
+    """VQVAE.encode up to the quantiser — models/vqvae.py:130-138: conv_in -> DownBlocks (no time embedding) ->
+    MidBlocks -> GroupNorm / SiLU / conv_out -> pre_quant 1x1."""
+    sd = _SD(state_dict)
+    groups, heads = cfg["norm_channels"], cfg["num_heads"]
+    out = F.conv2d(x.float(), sd["encoder_conv_in.weight"], sd["encoder_conv_in.bias"], padding=1)
+    for i in range(len(cfg["down_channels"]) - 1):
+        out = down_block(sd.sub(f"encoder_layers.{i}"), out, None, None, cfg["num_down_layers"], groups, heads,
+                         cfg["attn_down"][i], cfg["down_sample"][i], False)
+    for i in range(len(cfg["mid_channels"]) - 1):
+        out = mid_block(sd.sub(f"encoder_mids.{i}"), out, None, None, cfg["num_mid_layers"], groups, heads, False)
+    out = F.silu(F.group_norm(out, groups, sd["encoder_norm_out.weight"], sd["encoder_norm_out.bias"], 1e-5))
+    out = F.conv2d(out, sd["encoder_conv_out.weight"], sd["encoder_conv_out.bias"], padding=1)
+    return F.conv2d(out, sd["pre_quant_conv.weight"], sd["pre_quant_conv.bias"])
+
+
+def vq_quantize(x, codebook):
+    """VQVAE.quantize — models/vqvae.py:93-128, with the distances as float64 sums of squared differences (the exact
+    argmin; the reference's cdist picks the same code except between numerically tied ones).
+    -> (quant_out NCHW fp32 as `x + (e - x)` evaluates, mse, indices (B, H, W), squared distances (B*H*W, K) float64)."""
+    B, C, H, W = x.shape
+    rows = x.float().permute(0, 2, 3, 1).reshape(-1, C)
+    d2 = ((rows.double()[:, None, :] - codebook.double()[None, :, :]) ** 2).sum(-1)
+    idx = torch.argmin(d2, dim=-1)
+    e = codebook.float()[idx]
+    mse = torch.mean((e - rows) ** 2)
+    q = rows + (e - rows)
+    return q.reshape(B, H, W, C).permute(0, 3, 1, 2).contiguous(), mse, idx.reshape(B, H, W), d2

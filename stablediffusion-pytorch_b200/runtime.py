@@ -17,7 +17,7 @@ _ACT = {None: 0, "none": 0, "silu": 1, "relu": 2}
 
 EXPORTS = [
     "b200sd_last_error", "b200sd_version", "b200sd_launch_count", "b200sd_sched_add_noise",
-    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_attention_lse", "b200sd_attention_bwd", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_rowblocks", "b200sd_groupnorm_bwd", "b200sd_colsum", "b200sd_colsum_blocks", "b200sd_sampler_step", "b200sd_opt_chunk_size", "b200sd_opt_chunk_elems", "b200sd_grad_sqnorm", "b200sd_adam_ema_step",
+    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_attention_lse", "b200sd_attention_bwd", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_rowblocks", "b200sd_groupnorm_bwd", "b200sd_colsum", "b200sd_colsum_blocks", "b200sd_vq_blocks", "b200sd_vq_nearest", "b200sd_sampler_step", "b200sd_opt_chunk_size", "b200sd_opt_chunk_elems", "b200sd_grad_sqnorm", "b200sd_adam_ema_step",
     "b200sd_reduce_f32", "b200sd_attention",
     "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16",
     "b200sd_layernorm_mod", "b200sd_layernorm_mod_bwd", "b200sd_rows_per_slot", "b200sd_gate_residual",
@@ -100,6 +100,8 @@ def lib():
         L.b200sd_groupnorm_bwd.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, vp, i32, i32, i32, vp, i32, i32, vp, vp, i64,
                                            i64, i32, i32, f32, i32, vp, vp, vp, vp, vp, vp]
         L.b200sd_colsum_blocks.argtypes = [i64, i64, i32]
+        L.b200sd_vq_blocks.argtypes = [i64]
+        L.b200sd_vq_nearest.argtypes = [vp, i64, vp, i32, i32, i64, i64, vp, vp, vp, vp, vp, vp]
         L.b200sd_sampler_step.argtypes = [vp, vp, vp, f32, f32, f32, vp, i64, vp]
         L.b200sd_grad_sqnorm.argtypes = [vp, i32, vp, f32, i32, vp, vp, vp, vp]
         L.b200sd_adam_ema_step.argtypes = [vp, i32, vp, vp, vp, vp, f32, f32, f32, f32, f32, f32, vp]
@@ -801,3 +803,19 @@ def sampler_step(x, eps, z, c1, c2, sigma, out=None):
     check(lib().b200sd_sampler_step(_p(x), _p(eps), _p(z), float(c1), float(c2), float(sigma), _p(out), x.numel(),
                                     stream_ptr()), "sampler_step")
     return out
+
+
+def vq_nearest(x_rows, n, hw, c, codebook):
+    """VQVAE.quantize on fp32 NHWC rows [n*hw, >= c]: -> (zq fp32 NCHW-flat [n, c, hw], indices int64 [n*hw], mse 0-dim)."""
+    _cuda(x_rows, torch.float32, "x")
+    _cuda(codebook, torch.float32, "codebook")
+    if not codebook.is_contiguous() or codebook.shape[1] != c or x_rows.stride(1) != 1:
+        raise B200Error("vq_nearest: codebook must be contiguous [n_codes, c], x rows unit-stride")
+    dev = x_rows.device
+    idx = torch.empty(n * hw, device=dev, dtype=torch.int64)
+    zq = torch.empty(n, c, hw, device=dev, dtype=torch.float32)
+    partial = torch.empty(max(1, int(lib().b200sd_vq_blocks(n * hw))), device=dev, dtype=torch.float32)
+    loss = torch.empty(1, device=dev, dtype=torch.float32)
+    check(lib().b200sd_vq_nearest(_p(x_rows), x_rows.stride(0), _p(codebook), codebook.shape[0], c, n, hw, _p(idx),
+                                  _p(zq), _p(partial), _p(loss), tail_counter(dev), stream_ptr()), "vq_nearest")
+    return zq, idx, loss[0]

@@ -150,3 +150,16 @@ def test_sampler_oracle_bit_exact_vs_reference_outputs():
         x = onp.ddpm_step(c["beta"], c["T"], x, _sampler_model(torch.from_numpy(x), t).numpy(),
                           c["z"][k].numpy() if ts_ > 0 else None, ts_)
     assert np.array_equal(x, c["out"].numpy())
+
+
+def test_vqvae_encode_oracle_vs_reference_golden():
+    from models.vqvae import VQVAE  # only for the seeded weights (same constructor RNG consumption as the reference)
+    fx = load_golden("vqvae_encode")
+    torch.manual_seed(fx["seed"])
+    vae = VQVAE(3, fx["config"])
+    with torch.no_grad():
+        pre = O.vqvae_encode_latent(vae.state_dict(), fx["config"], fx["inputs"]["x"])
+        q, mse, idx, _ = O.vq_quantize(fx["pre_quant"], vae.embedding.weight.detach())
+    assert relerr(pre, fx["pre_quant"]) < 1e-5
+    assert torch.equal(idx, fx["indices"]) and torch.equal(q, fx["quant_out"])
+    torch.testing.assert_close(mse, fx["codebook_loss"], rtol=1e-6, atol=0)

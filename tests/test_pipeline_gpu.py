@@ -35,16 +35,72 @@ def test_vqvae_decode_vs_reference_golden():
     assert l2 <= min(5e-2, fx["ref_bf16_autocast_l2err"])
 
 
-def test_vqvae_train_side_is_out_of_scope():
+def test_vqvae_quantize_vs_reference_golden():
+    """Codebook search on the reference's own pre-quantisation latent: same indices (the reference's cdist may pick
+    another code only between numerically tied ones), bit-identical straight-through output, same loss value."""
+    dev = _dev()
+    from models.vqvae import VQVAE
+    from oracle import unet_torch as O
+    fx = load_golden("vqvae_encode")
+    torch.manual_seed(fx["seed"])
+    vae = VQVAE(3, fx["config"]).eval().to(dev)
+    pre = fx["pre_quant"]
+    with torch.no_grad():
+        zq, losses, idx = vae.quantize(pre.to(dev))
+    assert idx.dtype == torch.int64 and idx.shape == fx["indices"].shape and zq.shape == fx["quant_out"].shape
+    same = idx.cpu() == fx["indices"]
+    if not same.all():
+        _, _, _, d2 = O.vq_quantize(pre, vae.embedding.weight.detach().cpu())
+        rows = torch.arange(d2.shape[0])
+        ours, ref = d2[rows, idx.cpu().reshape(-1)], d2[rows, fx["indices"].reshape(-1)]
+        assert ((ours - ref).abs() / ref.clamp_min(1e-30)).max() < 1e-5
+    assert same.float().mean() > 0.999
+    m = same[:, None].expand_as(zq)
+    assert torch.equal(zq.cpu()[m], fx["quant_out"][m])
+    for k in ("codebook_loss", "commitment_loss"):
+        torch.testing.assert_close(losses[k].cpu(), fx[k], rtol=1e-5, atol=0)
+
+
+def test_vqvae_encode_vs_reference_golden():
+    dev = _dev()
+    from models.vqvae import VQVAE
+    fx = load_golden("vqvae_encode")
+    torch.manual_seed(fx["seed"])
+    vae = VQVAE(3, fx["config"]).eval().to(dev)
+    x = fx["inputs"]["x"].to(dev)
+    with torch.no_grad():
+        lat = vae.encode_latent(x)
+        zq, losses = vae.encode(x)
+        zq2, losses2, idx = vae.quantize(lat)
+        out, z, ql = vae(x)
+    ref = fx["pre_quant"]
+    err, l2 = relerr(lat.cpu(), ref), l2err(lat.cpu(), ref)
+    print(f"vqvae encoder latent: max-norm {err:.3e} L2 {l2:.3e} (reference bf16 autocast "
+          f"{fx['ref_bf16_autocast_relerr']:.3e} / {fx['ref_bf16_autocast_l2err']:.3e})")
+    # gate: never less accurate than the reference's own bf16-autocast encoder on the same image, capped at 5e-2
+    assert err <= min(5e-2, fx["ref_bf16_autocast_relerr"]) and l2 <= min(5e-2, fx["ref_bf16_autocast_l2err"])
+    assert torch.equal(zq, zq2) and torch.equal(losses["codebook_loss"], losses2["codebook_loss"])
+    assert zq.shape == fx["quant_out"].shape and idx.shape == fx["indices"].shape
+    assert out.shape == x.shape and torch.equal(z, zq) and set(ql) == {"codebook_loss", "commitment_loss"}
+    # every output vector is (numerically) a codebook row
+    cb = vae.embedding.weight.detach()
+    pick = cb[idx.reshape(-1)].reshape(*idx.shape, -1).permute(0, 3, 1, 2)
+    torch.testing.assert_close(zq, pick, rtol=1e-6, atol=1e-6)
+
+
+def test_vqvae_has_no_cpu_path_and_no_backward():
     _dev()
     from models.vqvae import VQVAE
     from sdb200.runtime import B200Error
     fx = load_golden("vqvae_decode")
     vae = VQVAE(3, fx["config"])
     with pytest.raises(B200Error):
-        vae.encode(torch.zeros(1, 3, 64, 64))
+        vae.encode(torch.zeros(1, 3, 64, 64))  # CPU tensor
     with pytest.raises(B200Error):
         vae.decode(torch.zeros(1, 4, 8, 8))  # CPU tensor
+    vae = vae.cuda()
+    with pytest.raises(B200Error):
+        vae.encode(torch.zeros(1, 3, 64, 64, device="cuda"))  # autograd recording: stage-1 training is out of scope
 
 
 def _small_cond(dev):
