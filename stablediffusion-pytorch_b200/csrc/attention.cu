@@ -246,12 +246,18 @@ __device__ __forceinline__ float ex2(float x) {
     return y;
 }
 
-template <int D8>
-__global__ void __launch_bounds__(256)
+__device__ __forceinline__ uint32_t ldg32(const __nv_bfloat16* p) { return *reinterpret_cast<const uint32_t*>(p); }
+
+// NT / MINB: launch bounds. <512, 2> (64 registers) puts 32 warps on an SM for the L >= 512 sites, where the kernel
+// was latency-bound at 16 warps (ncu r1j: issue 44 %, MUFU 48 %, tensor 39 %, none saturated).
+// Each CTA stages K/V once and then walks `qiter` query tiles of (warps * 16) rows; the Q fragments come straight
+// from global memory in mma A-operand layout (no shared-memory staging, no barrier per query tile).
+template <int D8, int NT, int MINB>
+__global__ void __launch_bounds__(NT, MINB)
     attention_resident_kernel(const __nv_bfloat16* __restrict__ q, long long ld_q, const __nv_bfloat16* __restrict__ k,
                               long long ld_k, const __nv_bfloat16* __restrict__ v, long long ld_v,
                               __nv_bfloat16* __restrict__ out, long long ld_o, int lq, int lk, float scale_log2,
-                              float* __restrict__ lse) {
+                              float* __restrict__ lse, int qiter) {
     pdl_enter();
     constexpr int PITCH = AttRes<D8>::PITCH;
     constexpr int K16 = D8 / 2;        // k16 chunks of the head dim
@@ -261,10 +267,8 @@ __global__ void __launch_bounds__(256)
     const int lk_pad = (lk + 63) & ~63;
     __nv_bfloat16* sK = reinterpret_cast<__nv_bfloat16*>(att_smem);
     __nv_bfloat16* sV = sK + lk_pad * PITCH;
-    __nv_bfloat16* sQ = sV + lk_pad * PITCH;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int q0 = blockIdx.x * bq;
     const int head = blockIdx.y;
     const long long b = blockIdx.z;
     const __nv_bfloat16* qg = q + (b * lq) * ld_q + head * (D8 * 8);
@@ -278,29 +282,34 @@ __global__ void __launch_bounds__(256)
         cp_async16(sK + r * PITCH + c * 8, kg + ro * ld_k + c * 8, ok ? 16 : 0);
         cp_async16(sV + r * PITCH + c * 8, vg + ro * ld_v + c * 8, ok ? 16 : 0);
     }
-    for (int i = tid; i < bq * D8; i += nthreads) {
-        const int r = i / D8, c = i - r * D8;
-        const bool ok = (q0 + r) < lq;
-        cp_async16(sQ + r * PITCH + c * 8, qg + (long long)(ok ? q0 + r : 0) * ld_q + c * 8, ok ? 16 : 0);
-    }
     cp_async_commit();
     cp_async_wait<0>();
-    __syncthreads();
-    if (q0 + warp * 16 >= lq) return;  // no barriers below
+    __syncthreads();  // the only barrier
 
+    const int ntiles = lk_pad >> 6;
+    const int nfull = lk >> 6;
+#pragma unroll 1
+    for (int it = 0; it < qiter; ++it) {
+    const int qw = (blockIdx.x * qiter + it) * bq + warp * 16;  // this warp's first query row
+    if (qw >= lq) break;
     uint32_t qf[K16 > 0 ? K16 : 1][4];
     uint32_t qt[2] = {0u, 0u};
-    const __nv_bfloat16* qrow = sQ + (warp * 16 + (lane & 7) + 8 * ((lane >> 3) & 1)) * PITCH;
+    {
+        const int ra = qw + (lane >> 2), rb = ra + 8;
+        const __nv_bfloat16* pa = qg + static_cast<long long>(ra < lq ? ra : lq - 1) * ld_q + (lane & 3) * 2;
+        const __nv_bfloat16* pb = qg + static_cast<long long>(rb < lq ? rb : lq - 1) * ld_q + (lane & 3) * 2;
 #pragma unroll
-    for (int kb = 0; kb < K16; ++kb) ldsm_x4(qf[kb], qrow + kb * 16 + 8 * (lane >> 4));
-    if (TAIL) ldsm_x2(qt, qrow + K16 * 16);
+        for (int kb = 0; kb < K16; ++kb) {
+            qf[kb][0] = ldg32(pa + kb * 16), qf[kb][1] = ldg32(pb + kb * 16);
+            qf[kb][2] = ldg32(pa + kb * 16 + 8), qf[kb][3] = ldg32(pb + kb * 16 + 8);
+        }
+        if (TAIL) qt[0] = ldg32(pa + K16 * 16), qt[1] = ldg32(pb + K16 * 16);
+    }
 
     float o[D8][4];
 #pragma unroll
     for (int i = 0; i < D8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
     float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
-    const int ntiles = lk_pad >> 6;
-
     auto tile = [&](int t, auto full_tag) {
         constexpr bool FULL = decltype(full_tag)::value;
         const __nv_bfloat16* tK = sK + t * 64 * PITCH;
@@ -403,7 +412,7 @@ __global__ void __launch_bounds__(256)
             }
         }
     };
-    const int nfull = lk >> 6;
+#pragma unroll 1
     for (int t = 0; t < nfull; ++t) tile(t, std::true_type{});
     if (nfull < ntiles) tile(nfull, std::false_type{});
     l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
@@ -411,7 +420,7 @@ __global__ void __launch_bounds__(256)
     l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
     l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
     const float i0 = 1.f / l0, i1 = 1.f / l1;
-    const int r0 = q0 + warp * 16 + (lane >> 2), r1 = r0 + 8;
+    const int r0 = qw + (lane >> 2), r1 = r0 + 8;
     if (lse && (lane & 3) == 0) {  // log2-domain log-sum-exp of the scaled scores, for the backward pass
         float* lp = lse + (b * gridDim.y + head) * lq;
         if (r0 < lq) lp[r0] = m0 * scale_log2 + log2f(l0);
@@ -428,31 +437,50 @@ __global__ void __launch_bounds__(256)
             *reinterpret_cast<__nv_bfloat162*>(og + (long long)r1 * ld_o + col) =
                 __floats2bfloat162_rn(o[nb][2] * i1, o[nb][3] * i1);
     }
+    }  // query tiles
 }
 
-static size_t resident_smem(int d8, int lk, int bq) {
+static size_t resident_smem(int d8, int lk) {
     const int p16 = (d8 & 1) ? d8 : d8 + 1;
     const size_t lk_pad = (size_t)((lk + 63) & ~63);
-    return (2 * lk_pad + bq) * p16 * 16;
+    return 2 * lk_pad * p16 * 16;
 }
 
 template <int D8>
 static int launch_resident(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v,
                            void* out, int64_t ld_o, int64_t batch, int heads, int lq, int lk, float scale,
                            float* lse, cudaStream_t st) {
-    const int warps = lq >= 128 ? 8 : lq > 32 ? 4 : lq > 16 ? 2 : 1;
+    constexpr int MB256 = D8 <= 4 ? 3 : 0;  // 80 registers -> three 8-warp CTAs per SM for the small head dims
+    const size_t smem = resident_smem(D8, lk);
+    // 16 warps x 2 CTAs per SM where the 64-register budget holds without heavy spilling (head dim <= 32)
+    const bool big = D8 <= 4 && lq >= 512 && smem <= 112 * 1024;
+    const int warps = big ? 16 : lq >= 128 ? 8 : lq > 32 ? 4 : lq > 16 ? 2 : 1;
     const int bq = warps * 16;
-    const size_t smem = resident_smem(D8, lk, bq);
     static bool configured = false;
     if (!configured) {
-        cudaFuncSetAttribute(attention_resident_kernel<D8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(attention_resident_kernel<D8, 256, MB256>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             200 * 1024);
+        cudaFuncSetAttribute(attention_resident_kernel<D8, 512, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             112 * 1024);
         configured = true;
     }
-    dim3 grid((lq + bq - 1) / bq, heads, (unsigned)batch);
-    launch_k(attention_resident_kernel<D8>, grid, warps * 32, smem, st, 
-        static_cast<const __nv_bfloat16*>(q), ld_q, static_cast<const __nv_bfloat16*>(k), ld_k,
-        static_cast<const __nv_bfloat16*>(v), ld_v, static_cast<__nv_bfloat16*>(out), ld_o, lq, lk,
-        scale * 1.4426950408889634f, lse);
+    // query tiles per CTA: as many as leave >= 6 resident waves of CTAs (K/V staging is paid once per CTA)
+    const int qtiles = (lq + bq - 1) / bq;
+    const long long cap = (long long)sm_count() * (big ? 2 : 3);
+    int qiter = 1;
+    while (qiter * 2 <= qtiles && (long long)((qtiles + 2 * qiter - 1) / (2 * qiter)) * heads * batch >= 6 * cap)
+        qiter *= 2;
+    dim3 grid((qtiles + qiter - 1) / qiter, heads, (unsigned)batch);
+    if (big)
+        launch_k(attention_resident_kernel<D8, 512, 2>, grid, warps * 32, smem, st,
+                 static_cast<const __nv_bfloat16*>(q), ld_q, static_cast<const __nv_bfloat16*>(k), ld_k,
+                 static_cast<const __nv_bfloat16*>(v), ld_v, static_cast<__nv_bfloat16*>(out), ld_o, lq, lk,
+                 scale * 1.4426950408889634f, lse, qiter);
+    else
+        launch_k(attention_resident_kernel<D8, 256, MB256>, grid, warps * 32, smem, st,
+                 static_cast<const __nv_bfloat16*>(q), ld_q, static_cast<const __nv_bfloat16*>(k), ld_k,
+                 static_cast<const __nv_bfloat16*>(v), ld_v, static_cast<__nv_bfloat16*>(out), ld_o, lq, lk,
+                 scale * 1.4426950408889634f, lse, qiter);
     B200_CHECK_LAUNCH("attention_resident");
     return B200SD_OK;
 }
@@ -788,7 +816,7 @@ static int attention_fwd(const void* q, int64_t ld_q, const void* k, int64_t ld_
                  "attention: pointers unaligned");
     if (batch == 0) return B200SD_OK;
     cudaStream_t st = as_stream(stream);
-    if (resident_smem(d / 8, lk, 128) <= 112 * 1024) {  // two CTAs per SM still fit
+    if (resident_smem(d / 8, lk) <= 110 * 1024) {  // two CTAs per SM still fit
         switch (d / 8) {
             case 1: return launch_resident<1>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, lse, st);
             case 2: return launch_resident<2>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, lse, st);

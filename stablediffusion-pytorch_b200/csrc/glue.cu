@@ -6,7 +6,7 @@
 namespace b200 {
 
 __device__ __forceinline__ float glue_act(float v, int act) {
-    if (act == B200SD_ACT_SILU) return v / (1.f + __expf(-v));
+    if (act == B200SD_ACT_SILU) return __fdividef(v, 1.f + __expf(-v));
     if (act == B200SD_ACT_RELU) return fmaxf(v, 0.f);
     return v;
 }

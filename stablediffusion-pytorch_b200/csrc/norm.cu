@@ -8,7 +8,7 @@
 namespace b200 {
 
 __device__ __forceinline__ float act_apply(float v, int act) {
-    if (act == B200SD_ACT_SILU) return v / (1.f + __expf(-v));
+    if (act == B200SD_ACT_SILU) return __fdividef(v, 1.f + __expf(-v));
     if (act == B200SD_ACT_RELU) return fmaxf(v, 0.f);
     return v;
 }
@@ -125,10 +125,22 @@ struct StatSeg {
     int p, ld;
 };
 
-__global__ void __launch_bounds__(256)
+// SiLU / ReLU with the activation fixed at compile time. SiLU = v * rcp(1 + ex2(-v log2 e)): two MUFU ops and three
+// FP32 ops per element (an IEEE division here was ~20 instructions per element and made the kernel issue-bound).
+template <int ACT>
+__device__ __forceinline__ float act_fast(float v) {
+    if (ACT == B200SD_ACT_SILU) return __fdividef(v, 1.f + __expf(-v));
+    if (ACT == B200SD_ACT_RELU) return fmaxf(v, 0.f);
+    return v;
+}
+
+constexpr int GN_U = 4;  // 16-byte loads each thread keeps in flight per batch
+
+template <int ACT>
+__global__ void __launch_bounds__(256, 4)
     gn_apply_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, __nv_bfloat16* __restrict__ y, long long ld_y,
                     StatSeg s0, int c_split, StatSeg s1, const float* __restrict__ gamma,
-                    const float* __restrict__ beta, long long hw, int c, int groups, float eps, int act,
+                    const float* __restrict__ beta, long long hw, int c, int groups, float eps,
                     int rows_per_block, int rpp) {
     pdl_enter();
     extern __shared__ float gn_sm[];
@@ -138,15 +150,32 @@ __global__ void __launch_bounds__(256)
     const int img = blockIdx.y;
     const int tid = threadIdx.x, nt = blockDim.x;
     const int cpg = c / groups;
+    const int cv = c >> 3;
+    const int v = tid % cv, r0 = tid / cv;
+    const bool active = r0 < rpp;
+    const long long row_begin = static_cast<long long>(blockIdx.x) * rows_per_block;
+    const int nrows = static_cast<int>(hw - row_begin < rows_per_block ? hw - row_begin : rows_per_block);
+    const __nv_bfloat16* px = x + (static_cast<long long>(img) * hw + row_begin + r0) * ld_x + v * 8;
+    __nv_bfloat16* py = y + (static_cast<long long>(img) * hw + row_begin + r0) * ld_y + v * 8;
+    const long long sx = static_cast<long long>(rpp) * ld_x, sy = static_cast<long long>(rpp) * ld_y;
+
+    // first batch of rows goes in flight before the statistics prologue: its HBM latency hides the fold below
+    uint4 cur[GN_U];
+    int i = r0;  // row inside this CTA's block
+#pragma unroll
+    for (int j = 0; j < GN_U; ++j)
+        if (active && i + j * rpp < nrows) cur[j] = *reinterpret_cast<const uint4*>(px + j * sx);
+
     for (int ch = tid; ch < c; ch += nt) {
         const bool first = ch < c_split;
-        const StatSeg sg = first ? s0 : s1;
+        const float* sp = first ? s0.ptr : s1.ptr;
+        const int np = first ? s0.p : s1.p, sld = first ? s0.ld : s1.ld;
         const int cc = first ? ch : ch - c_split;
-        const float* p = sg.ptr + (static_cast<long long>(img) * sg.p * sg.ld + cc) * 2;
+        const float* p = sp + (static_cast<long long>(img) * np * sld + cc) * 2;
         float a = 0.f, b = 0.f;
-        for (int k = 0; k < sg.p; ++k) {
-            const float2 v = *reinterpret_cast<const float2*>(p + static_cast<long long>(k) * sg.ld * 2);
-            a += v.x, b += v.y;
+        for (int k = 0; k < np; ++k) {
+            const float2 t = *reinterpret_cast<const float2*>(p + static_cast<long long>(k) * sld * 2);
+            a += t.x, b += t.y;
         }
         sc[ch] = a, sh[ch] = b;
     }
@@ -167,31 +196,33 @@ __global__ void __launch_bounds__(256)
         sc[ch] = scale, sh[ch] = be - gs[2 * g] * scale;
     }
     __syncthreads();
-    const int cv = c >> 3;
-    const int v = tid % cv, r0 = tid / cv;
-    if (r0 >= rpp) return;
+    if (!active) return;
     float scl[8], sft[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) scl[j] = sc[v * 8 + j], sft[j] = sh[v * 8 + j];
-    const long long row_begin = static_cast<long long>(blockIdx.x) * rows_per_block;
-    long long row_end = row_begin + rows_per_block;
-    if (row_end > hw) row_end = hw;
-    const __nv_bfloat16* xs = x + static_cast<long long>(img) * hw * ld_x + v * 8;
-    __nv_bfloat16* ys = y + static_cast<long long>(img) * hw * ld_y + v * 8;
-#pragma unroll 4
-    for (long long r = row_begin + r0; r < row_end; r += rpp) {
-        const uint4 u = *reinterpret_cast<const uint4*>(xs + r * ld_x);
-        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
-        uint4 o;
-        __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&o);
+    const int step = GN_U * rpp;
+    for (;;) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            float2 f = __bfloat1622float2(h[j]);
-            f.x = act_apply(f.x * scl[2 * j] + sft[2 * j], act);
-            f.y = act_apply(f.y * scl[2 * j + 1] + sft[2 * j + 1], act);
-            oh[j] = __floats2bfloat162_rn(f.x, f.y);
+        for (int j = 0; j < GN_U; ++j) {
+            if (i + j * rpp < nrows) {
+                const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&cur[j]);
+                uint4 o;
+                __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    float2 f = __bfloat1622float2(h[e]);
+                    f.x = act_fast<ACT>(fmaf(f.x, scl[2 * e], sft[2 * e]));
+                    f.y = act_fast<ACT>(fmaf(f.y, scl[2 * e + 1], sft[2 * e + 1]));
+                    oh[e] = __floats2bfloat162_rn(f.x, f.y);
+                }
+                *reinterpret_cast<uint4*>(py + j * sy) = o;
+            }
         }
-        *reinterpret_cast<uint4*>(ys + r * ld_y) = o;
+        i += step, px += GN_U * sx, py += GN_U * sy;
+        if (i >= nrows) break;
+#pragma unroll
+        for (int j = 0; j < GN_U; ++j)
+            if (i + j * rpp < nrows) cur[j] = *reinterpret_cast<const uint4*>(px + j * sx);
     }
 }
 
@@ -205,7 +236,7 @@ __global__ void __launch_bounds__(256)
 // and streams dx. Mean / rstd are rebuilt from the forward's partial statistics exactly as gn_apply does.
 __device__ __forceinline__ float act_grad(float z, int act) {
     if (act == B200SD_ACT_SILU) {
-        const float s = 1.f / (1.f + __expf(-z));
+        const float s = __fdividef(1.f, 1.f + __expf(-z));
         return s * (1.f + z * (1.f - s));
     }
     if (act == B200SD_ACT_RELU) return z > 0.f ? 1.f : 0.f;
@@ -586,9 +617,10 @@ extern "C" int b200sd_groupnorm_apply(const void* x, int64_t ld_x, void* y, int6
     int rpp = 256 / cv;  // rows a CTA covers per pass
     if (rpp > hw) rpp = (int)hw;
     const int threads = ((cv * rpp + 31) / 32) * 32;
-    // ~4 CTAs per SM overall, each at least 8 passes deep so the statistics prologue is amortised
-    long long blocks_per_img = (4ll * sm_count() + n - 1) / n;
-    long long max_bpi = (hw + 8ll * rpp - 1) / (8ll * rpp);
+    // ~8 CTAs per SM overall = two resident waves of 4 (64 B in flight per thread; other CTAs cover the compute phase), each at least two load batches deep so the statistics
+    // prologue is amortised
+    long long blocks_per_img = (8ll * sm_count() + n - 1) / n;
+    long long max_bpi = (hw + 2ll * GN_U * rpp - 1) / (2ll * GN_U * rpp);
     if (blocks_per_img > max_bpi) blocks_per_img = max_bpi;
     if (blocks_per_img < 1) blocks_per_img = 1;
     long long rows_per_block = (hw + blocks_per_img - 1) / blocks_per_img;
@@ -597,9 +629,14 @@ extern "C" int b200sd_groupnorm_apply(const void* x, int64_t ld_x, void* y, int6
     const size_t smem = (size_t)(2 * c + 2 * groups) * sizeof(float);
     StatSeg s0{stats0, p0, ld_s0}, s1{stats1, p1, ld_s1};
     dim3 grid((unsigned)blocks_per_img, (unsigned)n);
-    launch_k(gn_apply_kernel, grid, threads, smem, as_stream(stream), 
-        static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y, s0, c_split, s1, gamma, beta,
-        hw, c, groups, eps, act, (int)rows_per_block, rpp);
+    auto go = [&](auto kern) {
+        launch_k(kern, grid, threads, smem, as_stream(stream), static_cast<const __nv_bfloat16*>(x), ld_x,
+                 static_cast<__nv_bfloat16*>(y), ld_y, s0, c_split, s1, gamma, beta, hw, c, groups, eps,
+                 (int)rows_per_block, rpp);
+    };
+    if (act == B200SD_ACT_SILU) go(gn_apply_kernel<B200SD_ACT_SILU>);
+    else if (act == B200SD_ACT_RELU) go(gn_apply_kernel<B200SD_ACT_RELU>);
+    else go(gn_apply_kernel<B200SD_ACT_NONE>);
     B200_CHECK_LAUNCH("groupnorm_apply");
     return B200SD_OK;
 }
