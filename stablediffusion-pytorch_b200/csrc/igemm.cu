@@ -123,14 +123,16 @@ __device__ __forceinline__ void load8_f32(const float* p, int nv, float (&f)[8])
     }
 }
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int MINB = 1>
 struct IgemmSmem {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int STAGING_OFF = STAGES * STAGE_BYTES;
     static constexpr int STAGING_ONE = BN >= 64 ? (BN / 64) * PANEL_BYTES : 0;
-    static constexpr int NSTG = BN >= 64 && BN <= 128 ? 2 : 1;  // staging tiles (two when shared memory allows)
+    // staging tiles: two when shared memory allows (one CTA per SM: BN <= 128; two CTAs per SM: within 96 KB)
+    static constexpr int NSTG =
+        BN >= 64 && BN <= 128 && (MINB == 1 || STAGES * STAGE_BYTES + 2 * STAGING_ONE <= 96 * 1024) ? 2 : 1;
     static constexpr int STAGING_BYTES = NSTG * STAGING_ONE;
     static constexpr int BIAS_MAX = 2560;                       // floats of bias kept in shared memory
     static constexpr int BIAS_OFF = STAGING_OFF + STAGING_BYTES;
@@ -165,9 +167,12 @@ __device__ __forceinline__ void epilogue8(const IgemmArgs& args, float (&v)[8], 
     }
 }
 
-template <int BN, int STAGES>
-__global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_constant__ IgemmArgs args) {
-    using L = IgemmSmem<BN, STAGES>;
+// MINB = 2: two CTAs per SM (<= 102 registers, <= 113 KB shared memory, 2 x 2 x BN <= 512 TMEM columns). Short-K
+// GEMMs are bound by the serial latency of one tile's epilogue (TMEM load -> operands -> staging -> barrier -> TMA store
+// -> statistics); a second resident CTA runs its epilogue chain in the gaps of the first.
+template <int BN, int STAGES, int MINB>
+__global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid_constant__ IgemmArgs args) {
+    using L = IgemmSmem<BN, STAGES, MINB>;
     constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;  // two accumulators; 64..512, a power of two
     constexpr int PANELS = BN / 64;
     constexpr int NSTG = L::NSTG;
@@ -441,11 +446,10 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_co
                     epilogue8(args, v, col, nv, pnc, !bias_sm);
                     if (BN >= 64 && args.tma_out) {
                         const int jj = c * 4 + g;  // 16-byte chunk index within the tile row
-                        uint4* sp = reinterpret_cast<uint4*>(stg + (jj >> 3) * PANEL_BYTES + r * 128 +
-                                                             (((jj & 7) ^ (r & 7)) << 4));
+                        const uint32_t sp = smem_u32(stg) + (jj >> 3) * PANEL_BYTES + r * 128 + (((jj & 7) ^ (r & 7)) << 4);
                         if (args.tma_res) {
                             float f[8];
-                            unpack8(*sp, f);
+                            unpack8(lds128(sp), f);
 #pragma unroll
                             for (int j = 0; j < 8; ++j) v[j] += f[j];
                         } else if (args.residual && row_ok) {
@@ -454,7 +458,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_co
 #pragma unroll
                             for (int j = 0; j < 8; ++j) v[j] += f[j];
                         }
-                        *sp = pack8(v);
+                        sts128(sp, pack8(v));
                     } else if (row_ok) {
                         if (args.residual) {
                             float f[8];
@@ -505,10 +509,66 @@ __global__ void __launch_bounds__(IGEMM_THREADS, 1) igemm_kernel(const __grid_co
                             tma_store_4d(&args.out_map, stg + p * PANEL_BYTES, t.col_t * BN + p * 64, t.x0, t.y0, t.n0);
                     tma_store_commit();
                 }
-                if (args.stats) {
+                if (args.stats && rpi >= 8) {
                     // per-channel sum / sum of squares of the bf16-rounded tile, one partial per (image, tile slot),
-                    // deterministic (no atomics). Warp e owns rows [16e, 16e+16), lane l owns columns 2l, 2l+1 of a
-                    // 64-column panel: one conflict-free 4-byte smem read per row.
+                    // deterministic (no atomics). Warp e owns the BN/8 columns [e*W, e*W+W) for ALL 128 rows, so one
+                    // image's partial is complete inside the warp: no shared-memory exchange and no barrier (the
+                    // row-sliced version below spent 2 named barriers per 64-column panel and cost 8 us per 128x256
+                    // tile). Lane = (row lane rl, column pair cp); in every 8-row group a lane reads rows
+                    // rl*RG .. rl*RG+RG-1, which XOR the 128-byte swizzle to different 16-byte chunks for different
+                    // rl: bank-conflict free 4-byte reads.
+                    constexpr int W = BN >= 64 ? BN / 8 : 8, CP = W / 2, RL = 32 / CP, RG = 8 / RL;  // (BN = 32 never gets here)
+                    const int cp = lane % CP, rl = lane / CP;
+                    const int colt = e * W + 2 * cp;  // column inside the tile
+                    const int col = t.col_t * BN + colt;
+                    // explicit ld.shared: through a generic pointer these reads took the L1TEX path (long scoreboard)
+                    const uint32_t pb = smem_u32(stg) + (colt >> 6) * PANEL_BYTES + (colt & 7) * 2;
+                    const int chunk = (colt & 63) >> 3;
+                    const bool full = (t.x0 + args.bw <= args.ow) && (t.y0 + args.bh <= args.oh);
+                    const int seg_i = rpi / RL;  // iterations per image
+                    int i = 0;
+                    for (int im = 0; im < args.bn; ++im) {
+                        float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+                        // branch-free body (staging rows outside the output are readable, just not counted):
+                        // a per-lane `if` here cost a BSSY/BSYNC pair per row and made this pass 5 us per tile
+                        if (full) {
+#pragma unroll 8
+                            for (int k = 0; k < seg_i; ++k, ++i) {
+                                const int row = rl * RG + (i % RG) + 8 * (i / RG);
+                                const uint32_t u = lds32(pb + row * 128 + ((chunk ^ (row & 7)) << 4));
+                                const float fx = __uint_as_float(u << 16), fy = __uint_as_float(u & 0xffff0000u);
+                                s0 += fx, s1 += fy, q0 = fmaf(fx, fx, q0), q1 = fmaf(fy, fy, q1);
+                            }
+                        } else {
+#pragma unroll 2
+                            for (int k = 0; k < seg_i; ++k, ++i) {
+                                const int row = rl * RG + (i % RG) + 8 * (i / RG);
+                                const bool ok = (t.x0 + row % args.bw < args.ow) && (t.y0 + (row / args.bw) % args.bh < args.oh);
+                                const uint32_t u = lds32(pb + row * 128 + ((chunk ^ (row & 7)) << 4));
+                                const float fx = ok ? __uint_as_float(u << 16) : 0.f;
+                                const float fy = ok ? __uint_as_float(u & 0xffff0000u) : 0.f;
+                                s0 += fx, s1 += fy, q0 = fmaf(fx, fx, q0), q1 = fmaf(fy, fy, q1);
+                            }
+                        }
+#pragma unroll
+                        for (int off = CP; off < 32; off <<= 1) {
+                            s0 += __shfl_xor_sync(0xffffffffu, s0, off);
+                            s1 += __shfl_xor_sync(0xffffffffu, s1, off);
+                            q0 += __shfl_xor_sync(0xffffffffu, q0, off);
+                            q1 += __shfl_xor_sync(0xffffffffu, q1, off);
+                        }
+                        const int img = t.n0 + im;
+                        if (rl == 0 && col < args.n_out && img < args.on) {
+                            float* dst = args.stats +
+                                         ((static_cast<long long>(img) * args.stats_p + args.stats_slot0 + t.slot) *
+                                              args.stats_ld + col) * 2;
+                            *reinterpret_cast<float2*>(dst) = make_float2(s0, q0);
+                            if (col + 1 < args.n_out) *reinterpret_cast<float2*>(dst + 2) = make_float2(s1, q1);
+                        }
+                    }
+                } else if (args.stats) {
+                    // images smaller than 8 pixels: row-sliced version. Warp e owns rows [16e, 16e+16), lane l owns
+                    // columns 2l, 2l+1 of a 64-column panel: one conflict-free 4-byte smem read per row.
                     const bool full = (t.x0 + args.bw <= args.ow) && (t.y0 + args.bh <= args.oh);
                     const int rbase = e * 16;
 #pragma unroll 1
@@ -636,20 +696,21 @@ static int encode_pixel_view(CUtensorMap* m, const void* base, int cols, int ow,
     return encode_map(m, base, 4, dims, str, box);
 }
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int MINB = 1>
 static int launch_igemm(const IgemmArgs& a, int grid, cudaStream_t st) {
-    using L = IgemmSmem<BN, STAGES>;
+    using L = IgemmSmem<BN, STAGES, MINB>;
+    static_assert(MINB == 1 || L::TOTAL <= 113 * 1024, "two CTAs per SM need <= 113 KB each");
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(igemm_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             L::TOTAL);
+        cudaError_t e = cudaFuncSetAttribute(igemm_kernel<BN, STAGES, MINB>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL);
         if (e != cudaSuccess) {
             set_error("igemm: cannot set %d B dynamic smem: %s", L::TOTAL, cudaGetErrorString(e));
             return B200SD_ERR_CUDA;
         }
         configured = true;
     }
-    launch_k(igemm_kernel<BN, STAGES>, grid, IGEMM_THREADS, L::TOTAL, st, a);
+    launch_k(igemm_kernel<BN, STAGES, MINB>, grid, IGEMM_THREADS, L::TOTAL, st, a);
     B200_CHECK_LAUNCH("igemm");
     return B200SD_OK;
 }
@@ -793,8 +854,17 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
         a.stats = p->stats, a.stats_p = p->stats_p, a.stats_slot0 = p->stats_slot0, a.stats_ld = p->stats_ld;
     }
 
-    const int grid = a.num_tiles < sms ? a.num_tiles : sms;
     cudaStream_t st = as_stream(stream);
+    // short reductions with more than one wave of tiles: two co-resident CTAs per SM overlap their epilogue chains
+    static const int dual_max = [] {
+        const char* f = getenv("B200SD_DUAL_MAXCHUNKS");
+        return f ? atoi(f) : 12;
+    }();
+    if (total <= dual_max && a.num_tiles > sms && (BNsel == 128 || BNsel == 64)) {
+        const int grid2 = a.num_tiles < 2 * sms ? a.num_tiles : 2 * sms;
+        return BNsel == 128 ? launch_igemm<128, 2, 2>(a, grid2, st) : launch_igemm<64, 2, 2>(a, grid2, st);
+    }
+    const int grid = a.num_tiles < sms ? a.num_tiles : sms;
     switch (BNsel) {
         case 256: return launch_igemm<256, 3>(a, grid, st);
         case 128: return launch_igemm<128, 4>(a, grid, st);
