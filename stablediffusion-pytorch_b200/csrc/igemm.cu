@@ -173,7 +173,7 @@ __device__ __forceinline__ void epilogue8(const IgemmArgs& args, float (&v)[8], 
 template <int BN, int STAGES, int MINB>
 __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid_constant__ IgemmArgs args) {
     using L = IgemmSmem<BN, STAGES, MINB>;
-    constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;  // two accumulators; 64..512, a power of two
+    constexpr uint32_t TMEM_COLS = 2 * BN <= 32 ? 32 : 2 * BN <= 64 ? 64 : 2 * BN <= 128 ? 128 : 2 * BN <= 256 ? 256 : 512;  // two accumulators, rounded up to a power of two
     constexpr int PANELS = BN / 64;
     constexpr int NSTG = L::NSTG;
     extern __shared__ uint8_t smem_raw[];
@@ -517,7 +517,8 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                     // tile). Lane = (row lane rl, column pair cp); in every 8-row group a lane reads rows
                     // rl*RG .. rl*RG+RG-1, which XOR the 128-byte swizzle to different 16-byte chunks for different
                     // rl: bank-conflict free 4-byte reads.
-                    constexpr int W = BN >= 64 ? BN / 8 : 8, CP = W / 2, RL = 32 / CP, RG = 8 / RL;  // (BN = 32 never gets here)
+                    // (BN = 192: six warps take 32 columns each; BN = 32 never gets here)
+                    constexpr int W = BN == 192 ? 32 : BN >= 64 ? BN / 8 : 8, CP = W / 2, RL = 32 / CP, RG = 8 / RL;
                     const int cp = lane % CP, rl = lane / CP;
                     const int colt = e * W + 2 * cp;  // column inside the tile
                     const int col = t.col_t * BN + colt;
@@ -527,7 +528,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                     const bool full = (t.x0 + args.bw <= args.ow) && (t.y0 + args.bh <= args.oh);
                     const int seg_i = rpi / RL;  // iterations per image
                     int i = 0;
-                    for (int im = 0; im < args.bn; ++im) {
+                    for (int im = 0; im < args.bn && e * W < BN; ++im) {
                         float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
                         // branch-free body (staging rows outside the output are readable, just not counted):
                         // a per-lane `if` here cost a BSSY/BSYNC pair per row and made this pass 5 us per tile
@@ -774,8 +775,11 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
     int BNsel = 32;
     if (n > 32) {
         long long best = -1;
-        for (int bnc : {256, 128, 64}) {
+        for (int bnc : {256, 192, 128, 64}) {
             if (bnc > 64 && n <= bnc / 2) continue;
+            // 192 only for long reductions whose width it divides (N = 384, 768 convs: measured +4..5 % over 256, whose
+            // last tile is half empty); short-K GEMMs prefer the two-CTA 128 tile, wide ones the 256 tile
+            if (bnc == 192 && (n % 192 != 0 || n > 768 || total < 24)) continue;
             const long long tiles = m_tiles * ((n + bnc - 1) / bnc);
             // per-tile time ~ max(mainloop, epilogue) + fixed: the mainloop is operand-feed bound (128 + BN rows of 128
             // bytes per K chunk), the epilogue is proportional to BN; constants fitted to tools/gemm_sweep.py on B200
@@ -786,7 +790,7 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
     }
     if (const char* f = getenv("B200SD_FORCE_BN")) {  // tuning aid (tools/kernel_bench.py); not used by the product path
         const int v = atoi(f);
-        if ((v == 256 || v == 128 || v == 64) && n > 32) BNsel = v;
+        if ((v == 256 || v == 192 || v == 128 || v == 64) && n > 32) BNsel = v;
     }
     a.tiles_col = (n + BNsel - 1) / BNsel;
     const long long tiles_ll = m_tiles * a.tiles_col;
@@ -867,6 +871,7 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
     const int grid = a.num_tiles < sms ? a.num_tiles : sms;
     switch (BNsel) {
         case 256: return launch_igemm<256, 3>(a, grid, st);
+        case 192: return launch_igemm<192, 3>(a, grid, st);
         case 128: return launch_igemm<128, 4>(a, grid, st);
         case 64: return launch_igemm<64, 6>(a, grid, st);
         default: return launch_igemm<32, 6>(a, grid, st);
