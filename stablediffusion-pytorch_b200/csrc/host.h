@@ -37,6 +37,27 @@ inline cudaError_t launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t 
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<P>(args)...);
 }
 
+// Same, as thread-block clusters of `cluster` CTAs along x (grid.x must be a multiple of it).
+template <typename... P, typename... A>
+inline cudaError_t launch_k_cluster(void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                    unsigned cluster, A&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    at[1].id = cudaLaunchAttributeClusterDimension;
+    at[1].val.clusterDim.x = cluster;
+    at[1].val.clusterDim.y = 1;
+    at[1].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 2;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<P>(args)...);
+}
+
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }

@@ -36,6 +36,7 @@ struct SegDev {
 struct alignas(64) IgemmArgs {
     CUtensorMap a_map[4];
     CUtensorMap b_map;
+    CUtensorMap b_half_map;  // box of BN/2 rows: each CTA of a pair stages one half of the weight tile (CL2 kernels)
     CUtensorMap out_map;
     CUtensorMap res_map;
     SegDev seg[MAX_SEG];
@@ -44,6 +45,7 @@ struct alignas(64) IgemmArgs {
     int on, oh, ow;  // output pixel grid
     int bw, bh, bn;  // tile box (bw*bh*bn == 128)
     int tiles_x, tiles_y, tiles_img, tiles_col, num_tiles;
+    int m_tiles, num_ptiles;  // row tiles; (row-tile pair, column tile) work items of the CL2 kernels
     int tma_out;     // 1: staged TMA-store epilogue, 0: direct global stores
     int tma_res;     // 1: residual arrives by TMA into the staging buffer
     void* out;
@@ -123,10 +125,10 @@ __device__ __forceinline__ void load8_f32(const float* p, int nv, float (&f)[8])
     }
 }
 
-template <int BN, int STAGES, int MINB = 1>
+template <int BN, int STAGES, int MINB = 1, bool CL2 = false>
 struct IgemmSmem {
     static constexpr int A_BYTES = BM * BK * 2;
-    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int B_BYTES = (CL2 ? BN / 2 : BN) * BK * 2;  // a CTA of a pair stages half of the weight tile's rows
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int STAGING_OFF = STAGES * STAGE_BYTES;
     static constexpr int STAGING_ONE = BN >= 64 ? (BN / 64) * PANEL_BYTES : 0;
@@ -170,9 +172,18 @@ __device__ __forceinline__ void epilogue8(const IgemmArgs& args, float (&v)[8], 
 // MINB = 2: two CTAs per SM (<= 102 registers, <= 113 KB shared memory, 2 x 2 x BN <= 512 TMEM columns). Short-K
 // GEMMs are bound by the serial latency of one tile's epilogue (TMEM load -> operands -> staging -> barrier -> TMA store
 // -> statistics); a second resident CTA runs its epilogue chain in the gaps of the first.
-template <int BN, int STAGES, int MINB>
+//
+// CL2: CTA pairs (thread-block clusters of two, tcgen05 cta_group::2) that compute two adjacent row tiles of the SAME
+// column tile as one 256 x BN MMA. Each CTA stages its own 128 activation rows and HALF of the weight tile's rows; the
+// leader (rank 0) issues the MMAs, which read both CTAs' shared memory and write each CTA's 128 accumulator rows into
+// its own TMEM. Per K chunk a CTA now fills and reads 128 + BN/2 rows of shared memory instead of 128 + BN: the
+// one-CTA 128 x 256 tile was bound by shared-memory bandwidth (TMA fill + MMA operand reads ~ 190 B/clk against 128),
+// which is why it stopped at ~70 % of the tensor pipe. Barriers: every load of a stage completes bytes on the LEADER's
+// full barrier; the leader's tcgen05.commit multicasts the stage release / accumulator-ready arrivals to both CTAs;
+// both CTAs' epilogue threads arrive on the leader's accumulator-empty barrier.
+template <int BN, int STAGES, int MINB, bool CL2 = false>
 __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid_constant__ IgemmArgs args) {
-    using L = IgemmSmem<BN, STAGES, MINB>;
+    using L = IgemmSmem<BN, STAGES, MINB, CL2>;
     constexpr uint32_t TMEM_COLS = 2 * BN <= 32 ? 32 : 2 * BN <= 64 ? 64 : 2 * BN <= 128 ? 128 : 2 * BN <= 256 ? 256 : 512;  // two accumulators, rounded up to a power of two
     constexpr int PANELS = BN / 64;
     constexpr int NSTG = L::NSTG;
@@ -191,10 +202,23 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
+    // this CTA's work list: tile_of(i), i < my_tiles
+    const int crank = CL2 ? static_cast<int>(cluster_ctarank()) : 0;
+    const int unit = CL2 ? blockIdx.x >> 1 : blockIdx.x, nunits = CL2 ? gridDim.x >> 1 : gridDim.x;
+    const int nwork = CL2 ? args.num_ptiles : args.num_tiles;
+    const int my_tiles = unit < nwork ? (nwork - unit + nunits - 1) / nunits : 0;
+    auto tile_of = [&](int i) -> int {
+        const int w = unit + i * nunits;
+        if (!CL2) return w;
+        // (row-tile pair, column tile); a pair's second row tile may lie past the last one: every access of such a
+        // tile is out of bounds for TMA (zero fill / clipped) and masked in the epilogue
+        return (2 * (w / args.tiles_col) + crank) * args.tiles_col + w % args.tiles_col;
+    };
+
     pdl_trigger();
     if (warp == 0 && lane == 0) {
         for (int i = 0; i < 4; ++i) tma_prefetch_desc(&args.a_map[i]);
-        tma_prefetch_desc(&args.b_map);
+        tma_prefetch_desc(CL2 ? &args.b_half_map : &args.b_map);
         if (args.tma_out) tma_prefetch_desc(&args.out_map);
         if (args.tma_res) tma_prefetch_desc(&args.res_map);
     }
@@ -205,18 +229,24 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(&tfull_bar[b], 1);
-            mbar_init(&tempty_bar[b], EPI_THREADS);
+            mbar_init(&tempty_bar[b], CL2 ? 2 * EPI_THREADS : EPI_THREADS);
         }
         mbar_init(&res_bar[0], 1);
         mbar_init(&res_bar[1], 1);
         fence_barrier_init();
     }
     if (warp == 2) {
-        tmem_alloc(tmem_slot, TMEM_COLS);
-        tmem_relinquish();
+        if (CL2) {
+            tmem_alloc_pair(tmem_slot, TMEM_COLS);
+            tmem_relinquish_pair();
+        } else {
+            tmem_alloc(tmem_slot, TMEM_COLS);
+            tmem_relinquish();
+        }
     }
     tc_fence_before();
     __syncthreads();
+    if (CL2) cluster_sync_all();  // both CTAs' barriers exist before any load or arrive that names the peer's
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     pdl_wait();   // everything above overlapped the previous kernel's tail; from here on its results are read
@@ -225,8 +255,8 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
         // ------------------------------------------------------------------ TMA producer
         if (lane == 0) {
             int it = 0;
-            for (int tile = blockIdx.x; tile < args.num_tiles; tile += gridDim.x) {
-                const Tile t = decode_tile(args, tile);
+            for (int lt = 0; lt < my_tiles; ++lt) {
+                const Tile t = decode_tile(args, tile_of(lt));
                 int kc = 0;
                 for (int s = 0; s < args.n_seg; ++s) {
                     const SegDev sg = args.seg[s];
@@ -235,19 +265,29 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                         const uint32_t phase = (it / STAGES) & 1;
                         mbar_wait(&empty_bar[stage], phase ^ 1);
                         uint8_t* sa = smem + stage * L::STAGE_BYTES;
-                        mbar_expect_tx(&full_bar[stage], L::STAGE_BYTES);
-                        tma_load_4d(sa, &args.a_map[sg.src], &full_bar[stage], sg.c0 + ch * BK, t.x0 + sg.dx,
-                                    t.y0 + sg.dy, t.n0);
-                        tma_load_2d(sa + L::A_BYTES, &args.b_map, &full_bar[stage], kc * BK, t.col_t * BN);
+                        if (CL2) {
+                            // both CTAs' bytes complete on the leader's barrier; only the leader's MMA warp waits on it
+                            const uint32_t lbar = mapa_rank(&full_bar[stage], 0);
+                            if (crank == 0) mbar_expect_tx(&full_bar[stage], 2 * L::STAGE_BYTES);
+                            tma_load_4d_pair(sa, &args.a_map[sg.src], lbar, sg.c0 + ch * BK, t.x0 + sg.dx, t.y0 + sg.dy,
+                                             t.n0);
+                            tma_load_2d_pair(sa + L::A_BYTES, &args.b_half_map, lbar, kc * BK,
+                                             t.col_t * BN + crank * (BN / 2));
+                        } else {
+                            mbar_expect_tx(&full_bar[stage], L::STAGE_BYTES);
+                            tma_load_4d(sa, &args.a_map[sg.src], &full_bar[stage], sg.c0 + ch * BK, t.x0 + sg.dx,
+                                        t.y0 + sg.dy, t.n0);
+                            tma_load_2d(sa + L::A_BYTES, &args.b_map, &full_bar[stage], kc * BK, t.col_t * BN);
+                        }
                     }
                 }
             }
         }
-    } else if (warp == 1) {
-        // ------------------------------------------------------------------ MMA issuer
-        constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
-        int it = 0, lt = 0;
-        for (int tile = blockIdx.x; tile < args.num_tiles; tile += gridDim.x, ++lt) {
+    } else if (warp == 1 && (!CL2 || crank == 0)) {
+        // ------------------------------------------------------------------ MMA issuer (the pair's leader only)
+        constexpr uint32_t idesc = umma_idesc_bf16(CL2 ? 2 * BM : BM, BN);
+        int it = 0;
+        for (int lt = 0; lt < my_tiles; ++lt) {
             const int buf = lt & 1;
             mbar_wait(&tempty_bar[buf], ((lt >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
             tc_fence_after();
@@ -263,16 +303,21 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
 #pragma unroll
                     for (int k = 0; k < BK / 16; ++k) {
                         // +32 B per K=16 step inside the 128 B swizzle atom: +2 in the (>>4) start-address field
-                        umma_bf16(tacc, da + 2 * k, db + 2 * k, idesc, (kc | k) != 0);
+                        if (CL2) umma_bf16_pair(tacc, da + 2 * k, db + 2 * k, idesc, (kc | k) != 0);
+                        else umma_bf16(tacc, da + 2 * k, db + 2 * k, idesc, (kc | k) != 0);
                     }
-                    umma_commit(&empty_bar[stage]);
+                    if (CL2) umma_commit_pair(&empty_bar[stage], 3);
+                    else umma_commit(&empty_bar[stage]);
                 }
                 __syncwarp();
             }
-            if (lane == 0) umma_commit(&tfull_bar[buf]);
+            if (lane == 0) {
+                if (CL2) umma_commit_pair(&tfull_bar[buf], 3);
+                else umma_commit(&tfull_bar[buf]);
+            }
             __syncwarp();
         }
-    } else {
+    } else if (warp >= 2) {
         // ------------------------------------------------------------------ epilogue (warps 2..9)
         const int e = warp - 2;  // 0..7
         const int q = warp & 3;  // TMEM lane quarter this warp may read
@@ -297,16 +342,15 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                 if (t.col_t * BN + p * 64 < args.n_out)
                     tma_load_4d(dst + p * PANEL_BYTES, &args.res_map, bar, t.col_t * BN + p * 64, t.x0, t.y0, t.n0);
         };
-        if (args.tma_res && et == 0 && blockIdx.x < args.num_tiles)
-            load_residual(decode_tile(args, blockIdx.x), staging, &res_bar[0]);
+        if (args.tma_res && et == 0 && my_tiles > 0)
+            load_residual(decode_tile(args, tile_of(0)), staging, &res_bar[0]);
 
         const bool fast = args.vec_ok != 0;
         const bool has_bias = args.bias != nullptr, has_rowbias = args.rowbias != nullptr;
         const bool has_gate = args.gate != nullptr, has_res = args.residual != nullptr;
         const int act = args.act;
-        int lt = 0;
-        for (int tile = blockIdx.x; tile < args.num_tiles; tile += gridDim.x, ++lt) {
-            const Tile t = decode_tile(args, tile);
+        for (int lt = 0; lt < my_tiles; ++lt) {
+            const Tile t = decode_tile(args, tile_of(lt));
             const int buf = lt & 1;
             const int sb = NSTG == 2 ? (lt & 1) : 0;
             uint8_t* stg = staging + sb * L::STAGING_ONE;
@@ -490,15 +534,17 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                 }
             }
             tc_fence_before();
-            mbar_arrive(&tempty_bar[buf]);  // accumulator free: the MMA warp may start tile lt+2 in it
+            // accumulator free: the MMA warp may start tile lt+2 in it (CTA pair: the leader's barrier counts both CTAs)
+            if (CL2) mbar_arrive_cluster(mapa_rank(&tempty_bar[buf], 0));
+            else mbar_arrive(&tempty_bar[buf]);
 
             if (BN >= 64 && args.tma_out) {
                 fence_proxy_async();  // staging writes (generic proxy) -> visible to the TMA store (async proxy)
-                const bool has_next = tile + gridDim.x < args.num_tiles;
+                const bool has_next = lt + 1 < my_tiles;
                 if (NSTG == 2 && et == 0) {
                     tma_store_wait_read();  // the previous tile's store has finished reading the other buffer
                     if (args.tma_res && has_next)
-                        load_residual(decode_tile(args, tile + gridDim.x), staging + (sb ^ 1) * L::STAGING_ONE,
+                        load_residual(decode_tile(args, tile_of(lt + 1)), staging + (sb ^ 1) * L::STAGING_ONE,
                                       &res_bar[sb ^ 1]);
                 }
                 named_bar_sync(1, EPI_THREADS);
@@ -628,7 +674,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                     if (et == 0) tma_store_wait_read();
                     named_bar_sync(1, EPI_THREADS);  // staging may be overwritten
                     if (args.tma_res && et == 0 && has_next)
-                        load_residual(decode_tile(args, tile + gridDim.x), staging, &res_bar[0]);
+                        load_residual(decode_tile(args, tile_of(lt + 1)), staging, &res_bar[0]);
                 } else if (args.stats) {
                     named_bar_sync(1, EPI_THREADS);  // all statistics reads done before this buffer is refilled
                 }
@@ -638,9 +684,11 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
         tc_fence_before();
     }
     __syncthreads();
+    if (CL2) cluster_sync_all();  // my shared memory, barriers and TMEM stay valid until the peer has finished too
     if (warp == 2) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, TMEM_COLS);
+        if (CL2) tmem_dealloc_pair(tmem_base, TMEM_COLS);
+        else tmem_dealloc(tmem_base, TMEM_COLS);
     }
 }
 
@@ -697,13 +745,14 @@ static int encode_pixel_view(CUtensorMap* m, const void* base, int cols, int ow,
     return encode_map(m, base, 4, dims, str, box);
 }
 
-template <int BN, int STAGES, int MINB = 1>
+template <int BN, int STAGES, int MINB = 1, bool CL2 = false>
 static int launch_igemm(const IgemmArgs& a, int grid, cudaStream_t st) {
-    using L = IgemmSmem<BN, STAGES, MINB>;
+    using L = IgemmSmem<BN, STAGES, MINB, CL2>;
+    static_assert(L::TOTAL <= 227 * 1024, "shared memory budget");
     static_assert(MINB == 1 || L::TOTAL <= 113 * 1024, "two CTAs per SM need <= 113 KB each");
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(igemm_kernel<BN, STAGES, MINB>,
+        cudaError_t e = cudaFuncSetAttribute(igemm_kernel<BN, STAGES, MINB, CL2>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL);
         if (e != cudaSuccess) {
             set_error("igemm: cannot set %d B dynamic smem: %s", L::TOTAL, cudaGetErrorString(e));
@@ -711,7 +760,10 @@ static int launch_igemm(const IgemmArgs& a, int grid, cudaStream_t st) {
         }
         configured = true;
     }
-    launch_k(igemm_kernel<BN, STAGES, MINB>, grid, IGEMM_THREADS, L::TOTAL, st, a);
+    if (CL2)
+        launch_k_cluster(igemm_kernel<BN, STAGES, MINB, CL2>, grid, IGEMM_THREADS, L::TOTAL, st, 2, a);
+    else
+        launch_k(igemm_kernel<BN, STAGES, MINB, CL2>, grid, IGEMM_THREADS, L::TOTAL, st, a);
     B200_CHECK_LAUNCH("igemm");
     return B200SD_OK;
 }
@@ -796,6 +848,8 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
     const long long tiles_ll = m_tiles * a.tiles_col;
     B200_REQUIRE(tiles_ll < (1ll << 31), "igemm: too many tiles");
     a.num_tiles = (int)tiles_ll;
+    a.m_tiles = (int)m_tiles;
+    a.num_ptiles = (int)((m_tiles + 1) / 2) * a.tiles_col;
 
     {
         B200_REQUIRE((reinterpret_cast<uintptr_t>(p->weight) & 15) == 0, "igemm: weight unaligned");
@@ -803,6 +857,9 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
         uint64_t str[1] = {(uint64_t)total * BK * 2};
         uint32_t box[2] = {(uint32_t)BK, (uint32_t)BNsel};
         int rc = encode_map(&a.b_map, p->weight, 2, dims, str, box);
+        if (rc) return rc;
+        uint32_t hbox[2] = {(uint32_t)BK, (uint32_t)(BNsel / 2)};
+        rc = encode_map(&a.b_half_map, p->weight, 2, dims, str, hbox);
         if (rc) return rc;
     }
     a.n_out = n;
@@ -867,6 +924,15 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
     if (total <= dual_max && a.num_tiles > sms && (BNsel == 128 || BNsel == 64)) {
         const int grid2 = a.num_tiles < 2 * sms ? a.num_tiles : 2 * sms;
         return BNsel == 128 ? launch_igemm<128, 2, 2>(a, grid2, st) : launch_igemm<64, 2, 2>(a, grid2, st);
+    }
+    // long reductions: CTA pairs (cta_group::2), each CTA staging half of the weight tile
+    static const int cl2_min = [] {
+        const char* f = getenv("B200SD_CL2_MINCHUNKS");
+        return f ? atoi(f) : 16;
+    }();
+    if (total >= cl2_min && (BNsel == 256 || BNsel == 192) && m_tiles >= 2) {
+        const int ncl = a.num_ptiles < sms / 2 ? a.num_ptiles : sms / 2;
+        return BNsel == 256 ? launch_igemm<256, 4, 1, true>(a, 2 * ncl, st) : launch_igemm<192, 5, 1, true>(a, 2 * ncl, st);
     }
     const int grid = a.num_tiles < sms ? a.num_tiles : sms;
     switch (BNsel) {
