@@ -336,11 +336,22 @@ def run_ours(args):
         P.xt.copy_(xt_d)
         P.t.fill_(500)
         P.body()
+        torch.cuda.synchronize()
+        # hold the stream busy while the host enqueues the whole step, so that the event pairs bracket kernels that run
+        # back to back as they do inside the captured graph (an idle stream adds the launch latency to every pair)
+        torch.cuda._sleep(int(3.0e7))
         with rt.KernelTimer() as kt:
             P.body()
         ksum = kt.summary()
         rows = kt.rows()
     pk = peaks()
+    traffic = None  # DRAM bytes per igemm launch from the committed ncu pass of one step (profiles/README.md)
+    tpath = os.path.join(ROOT, "profiles", "igemm_traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+        except (OSError, ValueError):
+            traffic = None
     ig = ksum.get("igemm", {"launches": 0, "ms": 1e-9, "work": 0.0})
     ach = ig["work"] / (ig["ms"] * 1e-3) / 1e12
     eager_ms = sum(v["ms"] for v in ksum.values())
@@ -348,7 +359,7 @@ def run_ours(args):
         "kernel": "igemm_kernel (tcgen05 implicit GEMM: every conv / linear of the step)", "bound": "tensor",
         "achieved": ach, "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": ach / pk["tf_sustained"],
         "peak_source": f"{pk['src']} MEASURED_PEAKS.json bf16_tflops_sustained (kernel timed inside a long step)",
-        "traffic": None, "launches_per_step": ig["launches"], "avg_launch_us": 1e3 * ig["ms"] / max(ig["launches"], 1),
+        "traffic": traffic, "launches_per_step": ig["launches"], "avg_launch_us": 1e3 * ig["ms"] / max(ig["launches"], 1),
         "algorithmic_gflop_per_step": ig["work"] / 1e9,
     }
     kernels = {k: {"launches": v["launches"], "ms": round(v["ms"], 4), "share": round(v["ms"] / eager_ms, 4),

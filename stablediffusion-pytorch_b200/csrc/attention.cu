@@ -310,42 +310,44 @@ __global__ void __launch_bounds__(NT, MINB)
 #pragma unroll
     for (int i = 0; i < D8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
     float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
-    auto tile = [&](int t, auto full_tag) {
-        constexpr bool FULL = decltype(full_tag)::value;
+    // One 64-key tile. NPV = 0: a full tile (no masking); NPV = 1..4: the last, partial tile with that many 16-key
+    // pairs present — every loop bound is a compile-time constant (lk = 77 costs 64 + 16 keys of straight-line code).
+    auto tile = [&](int t, auto npv_tag) {
+        constexpr int NPV = decltype(npv_tag)::value;
+        constexpr bool FULL = NPV == 0;
+        constexpr int NPX = FULL ? 4 : NPV;  // 16-key pairs touched
         const __nv_bfloat16* tK = sK + t * 64 * PITCH;
         const __nv_bfloat16* tV = sV + t * 64 * PITCH;
-        const int rem = lk - t * 64;                     // keys left (>= 1)
-        const int nb_valid = FULL ? 8 : (rem + 7) >> 3;  // 8-key groups to touch in this tile
-        float s[8][4];
+        const int rem = lk - t * 64;  // keys left (>= 1)
+        float s[2 * NPX][4];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f;
+        for (int i = 0; i < 2 * NPX; ++i) s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f;
 #pragma unroll
-        for (int np = 0; np < 4; ++np) {
-            if (FULL || 2 * np < nb_valid) {
+        for (int np = 0; np < NPX; ++np) {
 #pragma unroll
-                for (int kb = 0; kb < K16; ++kb) {
-                    uint32_t bf[4];
-                    ldsm_x4(bf, tK + (np * 16 + (lane & 7) + 8 * (lane >> 4)) * PITCH + kb * 16 + 8 * ((lane >> 3) & 1));
-                    mma16816(s[2 * np], qf[kb], bf[0], bf[1]);
-                    mma16816(s[2 * np + 1], qf[kb], bf[2], bf[3]);
-                }
+            for (int kb = 0; kb < K16; ++kb) {
+                uint32_t bf[4];
+                ldsm_x4(bf, tK + (np * 16 + (lane & 7) + 8 * (lane >> 4)) * PITCH + kb * 16 + 8 * ((lane >> 3) & 1));
+                mma16816(s[2 * np], qf[kb], bf[0], bf[1]);
+                mma16816(s[2 * np + 1], qf[kb], bf[2], bf[3]);
             }
         }
         if (TAIL) {
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                if (FULL || 4 * h < nb_valid) {
+                if (4 * h < 2 * NPX) {
                     uint32_t bf[4];
                     ldsm_x4(bf, tK + (h * 32 + lane) * PITCH + K16 * 16);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) mma1688(s[4 * h + i], qt[0], qt[1], bf[i]);
+                    for (int i = 0; i < 4; ++i)
+                        if (4 * h + i < 2 * NPX) mma1688(s[4 * h + i], qt[0], qt[1], bf[i]);
                 }
             }
         }
-        if (!FULL) {  // last, partial tile: mask keys beyond lk
+        if (!FULL) {  // mask keys beyond lk
             const int kbase = (lane & 3) * 2;
 #pragma unroll
-            for (int nb = 0; nb < 8; ++nb) {
+            for (int nb = 0; nb < 2 * NPX; ++nb) {
                 const int key = kbase + nb * 8;
                 if (key >= rem) s[nb][0] = s[nb][2] = -INFINITY;
                 if (key + 1 >= rem) s[nb][1] = s[nb][3] = -INFINITY;
@@ -353,11 +355,9 @@ __global__ void __launch_bounds__(NT, MINB)
         }
         float mx0 = m0, mx1 = m1;
 #pragma unroll
-        for (int nb = 0; nb < 8; ++nb) {
-            if (FULL || nb < nb_valid) {
-                mx0 = fmaxf(mx0, fmaxf(s[nb][0], s[nb][1]));
-                mx1 = fmaxf(mx1, fmaxf(s[nb][2], s[nb][3]));
-            }
+        for (int nb = 0; nb < 2 * NPX; ++nb) {
+            mx0 = fmaxf(mx0, fmaxf(s[nb][0], s[nb][1]));
+            mx1 = fmaxf(mx1, fmaxf(s[nb][2], s[nb][3]));
         }
         mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
         mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
@@ -368,17 +368,13 @@ __global__ void __launch_bounds__(NT, MINB)
         const float ms0 = mx0 * scale_log2, ms1 = mx1 * scale_log2;
         float rs0 = 0.f, rs1 = 0.f;
 #pragma unroll
-        for (int nb = 0; nb < 8; ++nb) {
-            if (FULL || nb < nb_valid) {
-                s[nb][0] = ex2(fmaf(s[nb][0], scale_log2, -ms0));
-                s[nb][1] = ex2(fmaf(s[nb][1], scale_log2, -ms0));
-                s[nb][2] = ex2(fmaf(s[nb][2], scale_log2, -ms1));
-                s[nb][3] = ex2(fmaf(s[nb][3], scale_log2, -ms1));
-                rs0 += s[nb][0] + s[nb][1];
-                rs1 += s[nb][2] + s[nb][3];
-            } else {
-                s[nb][0] = s[nb][1] = s[nb][2] = s[nb][3] = 0.f;  // untouched 8-key groups contribute nothing to P V
-            }
+        for (int nb = 0; nb < 2 * NPX; ++nb) {
+            s[nb][0] = ex2(fmaf(s[nb][0], scale_log2, -ms0));
+            s[nb][1] = ex2(fmaf(s[nb][1], scale_log2, -ms0));
+            s[nb][2] = ex2(fmaf(s[nb][2], scale_log2, -ms1));
+            s[nb][3] = ex2(fmaf(s[nb][3], scale_log2, -ms1));
+            rs0 += s[nb][0] + s[nb][1];
+            rs1 += s[nb][2] + s[nb][3];
         }
         l0 = l0 * a0 + rs0;
         l1 = l1 * a1 + rs1;
@@ -389,32 +385,37 @@ __global__ void __launch_bounds__(NT, MINB)
         }
         // O += P V (16 keys per step; V fragments transposed on load)
 #pragma unroll
-        for (int kb = 0; kb < 4; ++kb) {
-            if (FULL || 2 * kb < nb_valid) {
-                uint32_t pf[4];
-                pf[0] = pack_bf16(s[2 * kb][0], s[2 * kb][1]);
-                pf[1] = pack_bf16(s[2 * kb][2], s[2 * kb][3]);
-                pf[2] = pack_bf16(s[2 * kb + 1][0], s[2 * kb + 1][1]);
-                pf[3] = pack_bf16(s[2 * kb + 1][2], s[2 * kb + 1][3]);
-                const __nv_bfloat16* vrow = tV + (kb * 16 + (lane & 7) + 8 * ((lane >> 3) & 1)) * PITCH;
+        for (int kb = 0; kb < NPX; ++kb) {
+            uint32_t pf[4];
+            pf[0] = pack_bf16(s[2 * kb][0], s[2 * kb][1]);
+            pf[1] = pack_bf16(s[2 * kb][2], s[2 * kb][3]);
+            pf[2] = pack_bf16(s[2 * kb + 1][0], s[2 * kb + 1][1]);
+            pf[3] = pack_bf16(s[2 * kb + 1][2], s[2 * kb + 1][3]);
+            const __nv_bfloat16* vrow = tV + (kb * 16 + (lane & 7) + 8 * ((lane >> 3) & 1)) * PITCH;
 #pragma unroll
-                for (int dp = 0; dp < K16; ++dp) {
-                    uint32_t bf[4];
-                    ldsm_x4_t(bf, vrow + dp * 16 + 8 * (lane >> 4));
-                    mma16816(o[2 * dp], pf, bf[0], bf[1]);
-                    mma16816(o[2 * dp + 1], pf, bf[2], bf[3]);
-                }
-                if (TAIL) {
-                    uint32_t bf[2];
-                    ldsm_x2_t(bf, vrow + K16 * 16);
-                    mma16816(o[D8 - 1], pf, bf[0], bf[1]);
-                }
+            for (int dp = 0; dp < K16; ++dp) {
+                uint32_t bf[4];
+                ldsm_x4_t(bf, vrow + dp * 16 + 8 * (lane >> 4));
+                mma16816(o[2 * dp], pf, bf[0], bf[1]);
+                mma16816(o[2 * dp + 1], pf, bf[2], bf[3]);
+            }
+            if (TAIL) {
+                uint32_t bf[2];
+                ldsm_x2_t(bf, vrow + K16 * 16);
+                mma16816(o[D8 - 1], pf, bf[0], bf[1]);
             }
         }
     };
 #pragma unroll 1
-    for (int t = 0; t < nfull; ++t) tile(t, std::true_type{});
-    if (nfull < ntiles) tile(nfull, std::false_type{});
+    for (int t = 0; t < nfull; ++t) tile(t, std::integral_constant<int, 0>{});
+    if (nfull < ntiles) {
+        switch ((lk - nfull * 64 + 15) >> 4) {  // 16-key pairs in the last tile (warp-uniform)
+            case 1: tile(nfull, std::integral_constant<int, 1>{}); break;
+            case 2: tile(nfull, std::integral_constant<int, 2>{}); break;
+            case 3: tile(nfull, std::integral_constant<int, 3>{}); break;
+            default: tile(nfull, std::integral_constant<int, 4>{}); break;
+        }
+    }
     l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
     l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
     l1 += __shfl_xor_sync(0xffffffffu, l1, 1);

@@ -930,9 +930,13 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
         const char* f = getenv("B200SD_CL2_MINCHUNKS");
         return f ? atoi(f) : 16;
     }();
-    if (total >= cl2_min && (BNsel == 256 || BNsel == 192) && m_tiles >= 2) {
+    if (total >= cl2_min && BNsel >= 128 && m_tiles >= 2) {
         const int ncl = a.num_ptiles < sms / 2 ? a.num_ptiles : sms / 2;
-        return BNsel == 256 ? launch_igemm<256, 4, 1, true>(a, 2 * ncl, st) : launch_igemm<192, 5, 1, true>(a, 2 * ncl, st);
+        switch (BNsel) {
+            case 256: return launch_igemm<256, 4, 1, true>(a, 2 * ncl, st);
+            case 192: return launch_igemm<192, 5, 1, true>(a, 2 * ncl, st);
+            default: return launch_igemm<128, 5, 1, true>(a, 2 * ncl, st);
+        }
     }
     const int grid = a.num_tiles < sms ? a.num_tiles : sms;
     switch (BNsel) {
