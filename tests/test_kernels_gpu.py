@@ -221,6 +221,10 @@ def test_time_embedding(rt):
 STAT_CASES = [  # n, h, w, cin, cout, k, groups
     (3, 32, 32, 64, 128, 3, 32), (5, 8, 8, 128, 192, 3, 16), (9, 4, 4, 64, 256, 3, 32), (2, 16, 16, 96, 64, 1, 16),
     (2, 24, 20, 64, 96, 3, 8), (70, 4, 4, 64, 512, 1, 32),
+    # CTA-pair kernels (>= 16 K-chunks): 192-column tile; an odd number of row tiles (the pair's second tile lies
+    # outside the tensor); more work items than clusters; several images per tile with an odd tile count
+    (3, 16, 16, 192, 384, 3, 32), (5, 8, 8, 192, 384, 3, 32), (24, 32, 32, 128, 256, 3, 32),
+    (17, 4, 4, 256, 512, 3, 32), (5, 16, 16, 128, 128, 3, 32),
 ]
 
 
