@@ -404,7 +404,28 @@ def run_ours(args):
     if rank == 0:
         print(json.dumps(line))
     if world > 1:
-        dist.destroy_process_group()
+        shutdown(dist)
+
+
+def shutdown(dist):
+    """Leave the process group without risking a hang at exit: captured graphs that still hold NCCL nodes (the in-graph
+    gradient buckets of the training legs) can keep destroy_process_group() waiting; give it ten seconds after a
+    collect + barrier, then exit the process."""
+    import gc
+    import threading
+    gc.collect()
+    torch.cuda.synchronize()
+    try:
+        dist.barrier()
+    except Exception:
+        pass
+    sys.stdout.flush()
+    sys.stderr.flush()
+    th = threading.Thread(target=dist.destroy_process_group, daemon=True)
+    th.start()
+    th.join(10.0)
+    if th.is_alive():
+        os._exit(0)
 
 
 # Model_DiT_12L_config.py:125-133 (image-conditioned, 12 layers) and Model_DiT_9L_config.py:139-148 (text + image, 9 layers)
@@ -621,8 +642,8 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=
         "grad_allreduce": None if world == 1 else (
             "torch DistributedDataParallel: 25 MB NCCL buckets, reduced after the backward graph has replayed"
             if args.train_ddp == "torch" else
-            "sdb200.parallel.DataParallel: one in-place NCCL AVG all-reduce of the flat fp32 gradient buffer "
-            "(474 MB) after the backward graph"),
+            "sdb200.parallel.DataParallel: in-place NCCL AVG all-reduces of 64 MB slices of the flat fp32 gradient "
+            "buffer, captured inside the backward graph on a side stream as each bucket's last gradient is produced"),
         "loss_finite": bool(out["value"][3] == out["value"][3]),
         "e2e": {"value": out["e2e"][0], "unit": "samples/s", "ms_per_step": out["e2e"][1], "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 4},

@@ -73,8 +73,9 @@ class Denoiser(nn.Module):
             cond_t.append(cond_input['image'].float().contiguous())
         x = x.float().contiguous()
         tg = self.__dict__.get("_train_graph")
-        if tg is None or tg.key != G.TrainGraph.make_key(self, x, tt, cond_t):
-            tg = G.TrainGraph(self, x, tt, cond_t, self.text_cond, self.image_cond)
+        ov = self.__dict__.get("_grad_overlap")   # (process group, bucket elements): set by sdb200.parallel.DataParallel
+        if tg is None or tg.key != G.TrainGraph.make_key(self, x, tt, cond_t, ov):
+            tg = G.TrainGraph(self, x, tt, cond_t, self.text_cond, self.image_cond, overlap=ov)
             self.__dict__["_train_graph"] = tg
         tg.grad_sync = self.__dict__.get("_grad_sync")   # set by sdb200.parallel.DataParallel
         return tg(x, tt, cond_t)

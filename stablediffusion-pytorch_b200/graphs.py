@@ -197,6 +197,86 @@ class _ReplayFn(torch.autograd.Function):
         return (None, tg.dx.clone() if tg.dx is not None else None) + tg.take_grads()
 
 
+class _BucketReducer:
+    """Gradient mean over ranks, captured inside the backward graph. The flat buffer is cut into contiguous buckets in
+    REVERSE parameter order (the order backward produces gradients); a tensor hook on every stand-in parameter counts its
+    bucket down, and the hook that completes a bucket (i) copies the bucket's gradients that were not written in place
+    into their slots, (ii) forks a side stream off the capturing stream and issues ONE in-place NCCL all-reduce (AVG) on
+    the bucket's slice there. `finish()` reduces whatever is still open and joins the side stream, so the graph ends
+    with every slot holding the mean. Element-wise the result is identical to one all-reduce of the whole buffer."""
+
+    def __init__(self, tg, dev):
+        import torch.distributed as dist
+        self.dist, self.tg = dist, tg
+        self.group, bucket_elems = tg.overlap
+        self.side = torch.cuda.Stream(device=dev)
+        used = sorted(set(tg._fired))
+        self.index_of = {i: k for k, i in enumerate([i for i, sl in enumerate(tg.slots) if sl is not None])}
+        # buckets over parameter indices, walking from the last parameter to the first
+        self.buckets, cur, size = [], [], 0
+        for i in reversed(used):
+            cur.append(i)
+            size += tg.slots[i][1]
+            if size >= bucket_elems:
+                self.buckets.append(cur)
+                cur, size = [], 0
+        if cur:
+            self.buckets.append(cur)
+        self.bucket_of = {i: b for b, idxs in enumerate(self.buckets) for i in idxs}
+        self.pending = [len(b) for b in self.buckets]
+        self.done = [False] * len(self.buckets)
+        self.grads, self.copied, self.handles = {}, set(), []
+
+    def arm(self):
+        for i, k in self.index_of.items():
+            if i in self.bucket_of:
+                self.handles.append(self.tg._standins[k].register_hook(lambda g, i=i: self._landed(i, g)))
+
+    def disarm(self):
+        for h in self.handles:
+            h.remove()
+        self.handles = []
+
+    def _landed(self, i, g):
+        self.grads[i] = g
+        b = self.bucket_of[i]
+        self.pending[b] -= 1
+        if self.pending[b] == 0:
+            self._flush(b)
+
+    def _flush(self, b):
+        tg, idxs = self.tg, self.buckets[b]
+        views, srcs = [], []
+        for i in idxs:
+            g = self.grads.pop(i, None)
+            if g is None:
+                continue
+            off, n, shape = tg.slots[i]
+            v = tg.flat[off:off + n].view(shape)
+            self.copied.add(i)
+            if g.dtype == torch.float32 and g.data_ptr() == v.data_ptr():
+                continue
+            views.append(v)
+            srcs.append(g if g.dtype == torch.float32 else g.float())
+        if views:
+            torch._foreach_copy_(views, srcs)
+        lo = min(tg.slots[i][0] for i in idxs)
+        hi = max(tg.slots[i][0] + (tg.slots[i][1] + 63) // 64 * 64 for i in idxs)
+        main = torch.cuda.current_stream()
+        self.side.wait_stream(main)          # fork: the bucket's producers are ordered before the collective
+        with torch.cuda.stream(self.side):
+            self.dist.all_reduce(tg.flat[lo:min(hi, tg.flat.numel())], op=self.dist.ReduceOp.AVG, group=self.group)
+        self.done[b] = True
+
+    def finish(self):
+        for b in range(len(self.buckets)):
+            if not self.done[b]:
+                for i in self.buckets[b]:   # gradients whose hook did not fire during capture were copied by the caller
+                    self.grads.pop(i, None)
+                self._flush(b)
+        torch.cuda.current_stream().wait_stream(self.side)   # join
+
+
 class TrainGraph:
     """One training step's forward and backward as two CUDA graphs: ~1200 kernel launches + ~1000 small torch ops per
     step cost ~55 ms of host time when issued one by one, several times the device time at the reference's per-GPU
@@ -210,10 +290,17 @@ class TrainGraph:
 
     WARMUP = 2
 
-    def __init__(self, core, x, tt, cond_tensors, has_text, has_mask):
+    def __init__(self, core, x, tt, cond_tensors, has_text, has_mask, overlap=None):
+        """overlap = (process_group, bucket_elems) or None: when given (parallel.DataParallel on NCCL), the gradient mean
+        over ranks is captured INSIDE the backward graph, bucket by bucket on a side stream, as soon as the last
+        gradient of a bucket has been produced (the reference's DDP reducer does the same from autograd hooks,
+        train_ddpm_cond_celebhq_multi_gpu.py:257-263,362) — in place on slices of the flat buffer, no bucket copies."""
         self.params = list(core.parameters())
-        self.key = self.make_key(core, x, tt, cond_tensors)
+        self.key = self.make_key(core, x, tt, cond_tensors, overlap)
         self.grad_sync = None
+        self.overlap = overlap
+        self.reduced_in_graph = False
+        self.n_buckets = 0
         dev = x.device
         swap = _ParamSwap(core, self.params)
         self.x = x.detach().clone().requires_grad_(x.requires_grad)
@@ -254,10 +341,20 @@ class TrainGraph:
             side = torch.cuda.Stream(device=dev)
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
+                self._fired = []   # parameter indices in the order their gradients are produced (last warm-up pass)
+                self._standins = [t for t in wrt if t is not self.x]
                 for _ in range(self.WARMUP):  # lazy kernel attributes, allocator warm-up, weight-bank discovery
                     self.bank.begin_pass()
                     out = forward()
+                    fired, hs = [], []
+                    if self.overlap is not None:
+                        idx = [i for i, sl in enumerate(self.slots) if sl is not None]
+                        for i, t in zip(idx, self._standins):
+                            hs.append(t.register_hook(lambda g, i=i: fired.append(i)))
                     torch.autograd.grad((out,), wrt, (torch.ones_like(out),), allow_unused=True)
+                    for h in hs:
+                        h.remove()
+                    self._fired = fired
                     self.bank.finalize()
                 del out
             self.bank.begin_pass()
@@ -270,8 +367,13 @@ class TrainGraph:
             self.fwd_launches = rt.launch_count() - before
             self.gout = torch.empty_like(self.out)
             before = rt.launch_count()
+            red = _BucketReducer(self, dev) if self.overlap is not None and self._fired else None
             with torch.cuda.graph(self.bwd_graph, pool=pool):
+                if red is not None:
+                    red.arm()
                 grads = list(torch.autograd.grad((self.out,), wrt, (self.gout,), allow_unused=True))
+                if red is not None:
+                    red.disarm()
                 self.dx = grads.pop(0) if self.x.requires_grad else None
                 views, srcs, self.unused = [], [], set()
                 it = iter(grads)
@@ -282,6 +384,8 @@ class TrainGraph:
                     if g is None:
                         self.unused.add(i)
                         continue
+                    if red is not None and i in red.copied:
+                        continue   # already in the flat buffer (and, with its bucket, on its way through NCCL)
                     v = self.flat[sl[0]:sl[0] + sl[1]].view(sl[2])
                     if g.dtype == torch.float32 and g.data_ptr() == v.data_ptr():
                         continue   # the weight-gradient kernel wrote it in place
@@ -289,19 +393,24 @@ class TrainGraph:
                     srcs.append(g if g.dtype == torch.float32 else g.float())
                 if views:
                     torch._foreach_copy_(views, srcs)
+                if red is not None:
+                    red.finish()   # buckets still open (late or unhooked gradients), then join the side stream
+                    self.reduced_in_graph = True
+                    self.n_buckets = len(red.buckets)
             self.bwd_launches = rt.launch_count() - before
         self.launches = self.fwd_launches + self.bwd_launches
 
     def take_grads(self):
         flat = self.flat.clone()
         if self.grad_sync is not None:
-            self.grad_sync(flat)
+            self.grad_sync(flat, reduced=self.reduced_in_graph)
         return tuple(None if sl is None or i in self.unused else flat[sl[0]:sl[0] + sl[1]].view(sl[2])
                      for i, sl in enumerate(self.slots))
 
     @staticmethod
-    def make_key(core, x, tt, cond_tensors):
-        return (tuple(x.shape), x.requires_grad, tuple(tt.shape)) + tuple((tuple(c.shape), c.dtype) for c in cond_tensors) \
+    def make_key(core, x, tt, cond_tensors, overlap=None):
+        return (tuple(x.shape), x.requires_grad, tuple(tt.shape), None if overlap is None else (id(overlap[0]), overlap[1])) \
+            + tuple((tuple(c.shape), c.dtype) for c in cond_tensors) \
             + tuple((p.data_ptr(), p.requires_grad) for p in core.parameters())
 
     def __call__(self, x, tt, cond_tensors):

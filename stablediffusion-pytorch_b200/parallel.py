@@ -39,7 +39,7 @@ def _mean_(flat, group, bucket_elems=None):
 
 class DataParallel(nn.Module):
     def __init__(self, module, device_ids=None, process_group=None, broadcast_buffers=False, bucket_cap_mb=None,
-                 **unused):
+                 overlap=True, **unused):
         super().__init__()
         if not dist.is_initialized():
             raise RuntimeError("DataParallel needs an initialised torch.distributed process group")
@@ -53,6 +53,11 @@ class DataParallel(nn.Module):
         self._broadcast([p.data for p in module.parameters()] + [b.data for b in module.buffers()])
         # captured steps: graphs.TrainGraph calls this with the flat gradient buffer
         module.__dict__["_grad_sync"] = self._sync_flat
+        # NCCL: let the captured backward graph reduce bucket by bucket while it is still producing gradients
+        # (graphs._BucketReducer); 64 MB buckets unless bucket_cap_mb says otherwise
+        module.__dict__.pop("_grad_overlap", None)
+        if overlap and dist.get_backend(self.group) == "nccl" and dist.get_world_size(self.group) > 1:
+            module.__dict__["_grad_overlap"] = (self.group, self.bucket_elems or (64 << 20) // 4)
         for p in self._params:
             p.register_post_accumulate_grad_hook(self._landed)
 
@@ -67,8 +72,9 @@ class DataParallel(nn.Module):
             for t, s in zip(ts, torch._utils._unflatten_dense_tensors(flat, ts)):
                 t.copy_(s)
 
-    def _sync_flat(self, flat):
-        _mean_(flat, self.group, self.bucket_elems)
+    def _sync_flat(self, flat, reduced=False):
+        if not reduced:   # `reduced`: the backward graph already holds the collective
+            _mean_(flat, self.group, self.bucket_elems)
         self._graph_synced = True
 
     def _landed(self, p):
