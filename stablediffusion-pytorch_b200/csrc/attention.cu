@@ -454,7 +454,8 @@ static int launch_resident(const void* q, int64_t ld_q, const void* k, int64_t l
     constexpr int MB256 = D8 <= 4 ? 3 : 0;  // 80 registers -> three 8-warp CTAs per SM for the small head dims
     const size_t smem = resident_smem(D8, lk);
     // 16 warps x 2 CTAs per SM where the 64-register budget holds without heavy spilling (head dim <= 32)
-    const bool big = D8 <= 4 && lq >= 512 && smem <= 112 * 1024;
+    static const int big_min = [] { const char* f = getenv("B200SD_ATT_BIG_MINLQ"); return f ? atoi(f) : 512; }();
+    const bool big = D8 <= 4 && lq >= big_min && smem <= 112 * 1024;
     const int warps = big ? 16 : lq >= 128 ? 8 : lq > 32 ? 4 : lq > 16 ? 2 : 1;
     const int bq = warps * 16;
     static bool configured = false;
