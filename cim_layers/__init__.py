@@ -1,7 +1,7 @@
 """Drop-in for the reference's `cim_layers` package: the LSQ quant-noise layers (layers_qn_lsq.py) and the ADDA
-compute-in-memory layers (layers_qn_lsq_adda_cim.py) on the sm_100a kernels. Modules this repo does not replace
-(the sibling experimental variants, register_dict, optimisers) resolve to the reference's own files when its checkout
-is on sys.path as well."""
+compute-in-memory layers (layers_qn_lsq_adda_cim.py) on the sm_100a kernels, and the CIM trainers' optimizer
+(IBA_optimizer.PercentOptimizerFP). Modules this repo does not replace (the sibling experimental variants,
+register_dict, the other optimisers) resolve to the reference's own files when its checkout is on sys.path as well."""
 import os
 import sys
 

@@ -401,6 +401,14 @@ int b200sd_grad_sqnorm(const void* chunks, int32_t n_chunks, const float* g_base
 int b200sd_adam_ema_step(const void* chunks, int32_t n_chunks, const float* g_base, float* m_base, float* v_base,
                          const float* scalars, float lr, float beta1, float beta2, float eps, float weight_decay,
                          float ema_decay, void* stream);
+/* PercentOptimizerFP.step (cim_layers/IBA_optimizer.py:80-143) for the tensors named by the chunk table: Adam moments
+ * (w1 = fp32(1 - beta1), w2 = fp32(1 - beta2)), u = (adj * m) / (sqrt(v) / bc2_sqrt + eps) with adj = sqrt(bc2) / bc1,
+ * then p -= u * max(lr * max|p| / (max|u| + eps), lr) per TENSOR. tensor_of_chunk: device int32 [n_chunks], the dense
+ * tensor index of each chunk; tensor_max: device uint32 [n_tensors][2], ZEROED by the caller before the call (float
+ * bit patterns of max|u|, max|p|). Two launches, fp32 operation order of the reference, IEEE-rounded each step. */
+int b200sd_percent_opt_step(const void* chunks, const int32_t* tensor_of_chunk, int32_t n_chunks, const float* g_base,
+                            float* m_base, float* v_base, uint32_t* tensor_max, float lr, float beta1, float beta2,
+                            float w1, float w2, float adj, float bc2_sqrt, float eps, void* stream);
 
 #ifdef __cplusplus
 }

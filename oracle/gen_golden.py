@@ -382,7 +382,50 @@ def gen_vqvae_encode():
     return ok
 
 
+def gen_percent_opt():
+    """PercentOptimizerFP (cim_layers/IBA_optimizer.py:80-143): the real class, 4 steps on 4 tensors with recorded
+    gradients (one tensor receives no gradient at step 2: its step counter falls behind, :93-94,105)."""
+    OT = _load(os.path.join(ROOT, "oracle", "optim_torch.py"), "oracle_optim_torch")
+    spec = importlib.util.spec_from_file_location("ref_IBA_optimizer", os.path.join(REF, "cim_layers", "IBA_optimizer.py"))
+    ref_mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref_mod)
+    g = torch.Generator().manual_seed(321)
+    shapes = [(96, 40), (33000,), (7,), (3, 5, 2, 2)]
+    init = [torch.randn(s, generator=g) * (0.5 if i else 0.05) for i, s in enumerate(shapes)]
+    grads = [[torch.randn(s, generator=g) * 10 ** float(torch.randint(-4, 2, (1,), generator=g)) for s in shapes]
+             for _ in range(4)]
+    grads[1][2] = None
+    lr, betas, eps = 2e-3, (0.9, 0.999), 1e-8
+    params = [torch.nn.Parameter(t.clone()) for t in init]
+    opt = ref_mod.PercentOptimizerFP(params, lr=lr, betas=betas, eps=eps)
+    mine = [t.clone() for t in init]
+    m, v, steps = [torch.zeros_like(t) for t in init], [torch.zeros_like(t) for t in init], [0] * len(init)
+    after = []
+    for gs in grads:
+        for p, gr in zip(params, gs):
+            p.grad = None if gr is None else gr.clone()
+        opt.step()
+        for k, gr in enumerate(gs):       # the oracle takes one step count per call: group tensors by their own count
+            if gr is not None:
+                steps[k] += 1
+        for st in sorted(set(steps)):
+            sel = [k for k in range(len(init)) if steps[k] == st and gs[k] is not None]
+            OT.percent_step([mine[k] for k in sel], [gs[k] for k in sel], [m[k] for k in sel], [v[k] for k in sel], st,
+                            lr, betas, eps)
+        for a, b in zip(params, mine):
+            assert torch.equal(a.data, b), "oracle PercentOptimizerFP differs from the reference"
+        after.append([p.data.clone() for p in params])
+    torch.save({"init": init, "grads": grads, "lr": lr, "betas": betas, "eps": eps, "after": {2: after[1], 4: after[3]},
+                "exp_avg": [opt.state[p]["exp_avg"].clone() for p in params],
+                "exp_avg_sq": [opt.state[p]["exp_avg_sq"].clone() for p in params],
+                "steps": [opt.state[p]["step"] for p in params]}, os.path.join(GOLD, "percent_opt.pt"))
+    print("percent_opt: oracle == reference over 4 steps; fixture written")
+
+
 def main():
+    if "--only-percent-opt" in sys.argv:
+        gen_percent_opt()
+        return
     if "--only-vqvae-encode" in sys.argv:
         if not gen_vqvae_encode():
             print("ORACLE DISAGREES WITH THE REFERENCE")

@@ -139,9 +139,91 @@ __global__ void __launch_bounds__(256)
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// PercentOptimizerFP (cim_layers/IBA_optimizer.py:80-143): Adam moments, then the whole tensor's update is rescaled so
+// that its largest element is `lr` times the tensor's largest weight (never below plain `lr`):
+//   m = b1*m + (1-b1)*g;  v = b2*v + (1-b2)*g*g;  u = (adj*m) / (sqrt(v)/sqrt(bc2) + eps)          (:107-123)
+//   scale = max(lr * max|p| / (max|u| + eps), lr);  p -= u * scale                                   (:128-139)
+// The reference walks the parameters in Python with ~14 tensor ops and two host-visible reductions each. Here:
+// percent_moments (moments + per-tensor max|u|, max|p| by integer atomicMax on the float bits — exact and order
+// independent) and percent_apply (u recomputed from the stored moments — same bits — then the scaled update).
+// Every product/sum is an explicitly rounded intrinsic in the reference's operation order: no FMA contraction.
+__device__ __forceinline__ float percent_update(float mv, float vv, float adj, float bc2s, float eps) {
+    const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(vv), bc2s), eps);
+    return __fdiv_rn(__fmul_rn(adj, mv), denom);
+}
+
+__global__ void __launch_bounds__(256)
+    percent_moments_kernel(const OptChunk* __restrict__ tab, const int* __restrict__ tid, const float* __restrict__ g,
+                           float* __restrict__ m, float* __restrict__ v, unsigned int* __restrict__ tmax, float beta1,
+                           float beta2, float w1, float w2, float adj, float bc2s, float eps) {
+    pdl_enter();
+    __shared__ float red_u[8], red_p[8];
+    const OptChunk c = tab[blockIdx.x];
+    const float* gp = g + c.off;
+    float* mp = m + c.off;
+    float* vp = v + c.off;
+    float mu = 0.f, mw = 0.f;
+    for (int i = threadIdx.x; i < c.n; i += 256) {
+        const float gv = gp[i];
+        const float mv = __fadd_rn(__fmul_rn(beta1, mp[i]), __fmul_rn(w1, gv));
+        const float vv = __fadd_rn(__fmul_rn(beta2, vp[i]), __fmul_rn(w2, __fmul_rn(gv, gv)));
+        mp[i] = mv, vp[i] = vv;
+        mu = fmaxf(mu, fabsf(percent_update(mv, vv, adj, bc2s, eps)));
+        mw = fmaxf(mw, fabsf(c.p[i]));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mu = fmaxf(mu, __shfl_xor_sync(0xffffffffu, mu, o));
+        mw = fmaxf(mw, __shfl_xor_sync(0xffffffffu, mw, o));
+    }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) red_u[w] = mu, red_p[w] = mw;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int i = 1; i < 8; ++i) mu = fmaxf(mu, red_u[i]), mw = fmaxf(mw, red_p[i]);
+        const int t = tid[blockIdx.x];
+        atomicMax(tmax + 2 * t, __float_as_uint(mu));       // non-negative floats order like their bit patterns
+        atomicMax(tmax + 2 * t + 1, __float_as_uint(mw));
+    }
+}
+
+__global__ void __launch_bounds__(256)
+    percent_apply_kernel(const OptChunk* __restrict__ tab, const int* __restrict__ tid, const float* __restrict__ m,
+                         const float* __restrict__ v, const unsigned int* __restrict__ tmax, float lr, float adj,
+                         float bc2s, float eps) {
+    pdl_enter();
+    const OptChunk c = tab[blockIdx.x];
+    const int t = tid[blockIdx.x];
+    const float max_u = __uint_as_float(tmax[2 * t]), max_w = __uint_as_float(tmax[2 * t + 1]);
+    float scale = __fdiv_rn(__fmul_rn(lr, max_w), __fadd_rn(max_u, eps));
+    if (lr > scale) scale = lr;   // Python max(tensor, lr): lr only when it is strictly larger
+    const float* mp = m + c.off;
+    const float* vp = v + c.off;
+    for (int i = threadIdx.x; i < c.n; i += 256) {
+        const float u = percent_update(mp[i], vp[i], adj, bc2s, eps);
+        c.p[i] = __fsub_rn(c.p[i], __fmul_rn(u, scale));
+    }
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" int b200sd_percent_opt_step(const void* chunks, const int32_t* tensor_of_chunk, int32_t n_chunks,
+                                       const float* g_base, float* m_base, float* v_base, uint32_t* tensor_max,
+                                       float lr, float beta1, float beta2, float w1, float w2, float adj, float bc2_sqrt,
+                                       float eps, void* stream) {
+    B200_REQUIRE(chunks && tensor_of_chunk && g_base && m_base && v_base && tensor_max && n_chunks > 0,
+                 "percent_opt_step: bad arguments");
+    launch_k(percent_moments_kernel, n_chunks, 256, 0, as_stream(stream), static_cast<const OptChunk*>(chunks),
+             tensor_of_chunk, g_base, m_base, v_base, tensor_max, beta1, beta2, w1, w2, adj, bc2_sqrt, eps);
+    B200_CHECK_LAUNCH("percent_moments");
+    launch_k(percent_apply_kernel, n_chunks, 256, 0, as_stream(stream), static_cast<const OptChunk*>(chunks),
+             tensor_of_chunk, m_base, v_base, tensor_max, lr, adj, bc2_sqrt, eps);
+    B200_CHECK_LAUNCH("percent_apply");
+    return B200SD_OK;
+}
 
 extern "C" int b200sd_opt_chunk_size(void) { return static_cast<int>(sizeof(OptChunk)); }
 extern "C" int b200sd_opt_chunk_elems(void) { return OPT_CHUNK; }

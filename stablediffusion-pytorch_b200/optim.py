@@ -192,3 +192,88 @@ class FusedAdam(torch.optim.Optimizer):
                              "exp_avg": self._m[o:o + n].view(p.shape), "exp_avg_sq": self._v[o:o + n].view(p.shape)}
         self._scalars[3] = step
         self._plans.clear()
+
+
+class PercentOptimizerFP(FusedAdam):
+    """Drop-in for the CIM trainers' `PercentOptimizerFP(params, lr, betas, eps)` (cim_layers/IBA_optimizer.py:80-143):
+    Adam moments, then each tensor's update is rescaled so that its largest element equals `lr` times the tensor's
+    largest weight (and never less than plain `lr`). The reference walks the parameters in Python (~14 tensor ops and
+    two reductions per parameter); here the step is two table-driven launches (`b200sd_percent_opt_step`) over the same
+    flat moment buffers FusedAdam uses, in the reference's fp32 operation order with correctly rounded arithmetic
+    (moments bit-identical, parameters within 1e-6 relative of torch's CPU run, whose MKL sqrt is not correctly rounded). `state_dict()` has the reference's per-parameter `step`, `exp_avg`, `exp_avg_sq`."""
+
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
+        super().__init__(params, lr=lr, betas=betas, eps=eps, weight_decay=0.0, max_grad_norm=None,
+                         skip_nonfinite=False)
+        self._steps = [0] * len(self._all)      # per parameter, as the reference counts them (:101-105)
+        self._ptabs = {}
+
+    def _ptable(self, idxs):
+        """(chunk table, tensor index per chunk, chunk count, per-tensor max buffer) for the parameters `idxs`."""
+        key = (tuple(idxs), tuple(self._all[i].data_ptr() for i in idxs))
+        ent = self._ptabs.get(key)
+        if ent is None:
+            ce = rt.opt_chunk_elems()
+            rows, tid = [], []
+            for k, i in enumerate(idxs):
+                p = self._all[i]
+                for c0 in range(0, p.numel(), ce):
+                    rows.append((p.data_ptr() + 4 * c0, self._off[i] + c0, min(ce, p.numel() - c0)))
+                    tid.append(k)
+            arr = (rt.OptChunk * len(rows))()
+            for k, (pp, oo, nn) in enumerate(rows):
+                arr[k].p, arr[k].ema, arr[k].off, arr[k].n, arr[k].vec = pp, None, oo, nn, 0
+            tab = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(self._dev)
+            ent = (tab, torch.tensor(tid, dtype=torch.int32, device=self._dev), len(rows),
+                   torch.zeros(len(idxs), 2, dtype=torch.int32, device=self._dev))
+            self._ptabs.clear()
+            self._ptabs[key] = ent
+        return ent
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        present = tuple(p.grad is not None for p in self._all)
+        if not any(present):
+            return loss
+        gbase = self._grad_base(present)
+        index = {id(p): i for i, p in enumerate(self._all)}
+        for g in self.param_groups:
+            lr, (b1, b2), eps = g["lr"], g["betas"], g["eps"]
+            by_step = {}
+            for p in g["params"]:
+                i = index[id(p)]
+                if present[i]:
+                    self._steps[i] += 1
+                    by_step.setdefault(self._steps[i], []).append(i)
+            for step, idxs in sorted(by_step.items()):   # one entry unless some parameters skipped earlier steps
+                bc1, bc2 = 1 - b1 ** step, 1 - b2 ** step              # :113-114, in Python doubles as there
+                adj, bc2s = (bc2 ** 0.5) / bc1, bc2 ** 0.5             # :117, :120
+                tab, tid, n, tmax = self._ptable(idxs)
+                tmax.zero_()
+                rt.percent_opt_step(tab, tid, n, gbase, self._m, self._v, tmax, lr, b1, b2, 1 - b1, 1 - b2, adj, bc2s,
+                                    eps)
+        return loss
+
+    def state_dict(self):
+        for p, n in zip(self._all, self._steps):
+            self.state[p]["step"] = n
+        return torch.optim.Optimizer.state_dict(self)
+
+    def load_state_dict(self, state_dict):
+        torch.optim.Optimizer.load_state_dict(self, state_dict)
+        self._all = [p for g in self.param_groups for p in g["params"]]
+        for k, (p, o) in enumerate(zip(self._all, self._off)):
+            st = self.state.get(p, {})
+            n = p.numel()
+            if "exp_avg" in st:
+                self._m[o:o + n].copy_(st["exp_avg"].reshape(-1))
+                self._v[o:o + n].copy_(st["exp_avg_sq"].reshape(-1))
+            self._steps[k] = int(st.get("step", 0))
+            self.state[p] = {"step": self._steps[k], "exp_avg": self._m[o:o + n].view(p.shape),
+                             "exp_avg_sq": self._v[o:o + n].view(p.shape)}
+        self._ptabs.clear()
+

@@ -163,3 +163,24 @@ def test_vqvae_encode_oracle_vs_reference_golden():
     assert relerr(pre, fx["pre_quant"]) < 1e-5
     assert torch.equal(idx, fx["indices"]) and torch.equal(q, fx["quant_out"])
     torch.testing.assert_close(mse, fx["codebook_loss"], rtol=1e-6, atol=0)
+
+
+def test_percent_optimizer_oracle_matches_reference_fixture():
+    """oracle/optim_torch.percent_step reproduces the reference's PercentOptimizerFP (cim_layers/IBA_optimizer.py:80-143)
+    bit for bit on the recorded gradients, including a tensor that skips a step."""
+    from oracle import optim_torch as OT
+    fx = load_golden("percent_opt")
+    p = [t.clone() for t in fx["init"]]
+    m, v, steps = [torch.zeros_like(t) for t in p], [torch.zeros_like(t) for t in p], [0] * len(p)
+    for n, gs in enumerate(fx["grads"], 1):
+        for k, g in enumerate(gs):
+            steps[k] += g is not None
+        for st in sorted(set(steps)):
+            sel = [k for k in range(len(p)) if steps[k] == st and gs[k] is not None]
+            OT.percent_step([p[k] for k in sel], [gs[k] for k in sel], [m[k] for k in sel], [v[k] for k in sel], st,
+                            fx["lr"], fx["betas"], fx["eps"])
+        if n in fx["after"]:
+            assert all(torch.equal(a, b) for a, b in zip(p, fx["after"][n]))
+    assert all(torch.equal(a, b) for a, b in zip(m, fx["exp_avg"]))
+    assert all(torch.equal(a, b) for a, b in zip(v, fx["exp_avg_sq"]))
+    assert steps == [int(s) for s in fx["steps"]]
