@@ -41,32 +41,45 @@ __device__ __forceinline__ float warp_sum(float v) {
 }
 
 // y = LN(x) * (1 + scale[img]) + shift[img]   (scale/shift NULL: plain LN without affine)
+// LPR lanes share one row: 32 (C <= 1024) or 16 (C <= 512: two rows per warp in flight — the DiT's C = 288 is 36
+// chunks, which left 28 lanes idle in the second pass of the one-row-per-warp form and one load in flight per lane).
+template <int LPR>
 __global__ void __launch_bounds__(ROW_WARPS * 32)
     ln_mod_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, __nv_bfloat16* __restrict__ y, long long ld_y,
                   const __nv_bfloat16* __restrict__ shift, const __nv_bfloat16* __restrict__ scale, long long ld_m,
                   long long rows, long long rows_per_img, int c, float eps, float* __restrict__ stats) {
     pdl_enter();
+    constexpr int RPW = 32 / LPR;                     // rows per warp
+    constexpr int NCH = LPR == 32 ? ROW_MAX_CHUNKS : 4;   // 16-byte chunks per lane (16 lanes x 4 x 8 = 512 channels)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sl = lane % LPR, sub = lane / LPR;
     const int nchunk = c >> 3;
     const float inv_c = 1.f / static_cast<float>(c);
-    for (long long r = static_cast<long long>(blockIdx.x) * ROW_WARPS + warp; r < rows;
-         r += static_cast<long long>(gridDim.x) * ROW_WARPS) {
-        float v[ROW_MAX_CHUNKS][8];
+    auto row_sum = [](float v) {
+#pragma unroll
+        for (int o = LPR / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        return v;
+    };
+    for (long long r0 = (static_cast<long long>(blockIdx.x) * ROW_WARPS + warp) * RPW; r0 < rows;
+         r0 += static_cast<long long>(gridDim.x) * ROW_WARPS * RPW) {
+        const long long r = r0 + sub;
+        const bool live = r < rows;                   // (an odd row count leaves the last half-warp idle; it still shuffles)
+        float v[NCH][8];
         float s = 0.f;
 #pragma unroll
-        for (int k = 0; k < ROW_MAX_CHUNKS; ++k) {
-            const int ch = lane + 32 * k;
-            if (ch < nchunk) {
+        for (int k = 0; k < NCH; ++k) {
+            const int ch = sl + LPR * k;
+            if (live && ch < nchunk) {
                 ld8(x + r * ld_x + ch * 8, v[k]);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) s += v[k][j];
             }
         }
-        const float mean = warp_sum(s) * inv_c;
+        const float mean = row_sum(s) * inv_c;
         float q = 0.f;
 #pragma unroll
-        for (int k = 0; k < ROW_MAX_CHUNKS; ++k) {
-            if (lane + 32 * k < nchunk) {
+        for (int k = 0; k < NCH; ++k) {
+            if (live && sl + LPR * k < nchunk) {
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const float d = v[k][j] - mean;
@@ -74,12 +87,13 @@ __global__ void __launch_bounds__(ROW_WARPS * 32)
                 }
             }
         }
-        const float rstd = rsqrtf(warp_sum(q) * inv_c + eps);
-        if (stats && lane == 0) stats[2 * r] = mean, stats[2 * r + 1] = rstd;
+        const float rstd = rsqrtf(row_sum(q) * inv_c + eps);
+        if (!live) continue;
+        if (stats && sl == 0) stats[2 * r] = mean, stats[2 * r + 1] = rstd;
         const long long img = r / rows_per_img;
 #pragma unroll
-        for (int k = 0; k < ROW_MAX_CHUNKS; ++k) {
-            const int ch = lane + 32 * k;
+        for (int k = 0; k < NCH; ++k) {
+            const int ch = sl + LPR * k;
             if (ch < nchunk) {
                 float o[8];
                 if (scale) {
@@ -347,10 +361,16 @@ extern "C" int b200sd_layernorm_mod(const void* x, int64_t ld_x, void* y, int64_
     B200_REQUIRE((shift == nullptr) == (scale == nullptr), "layernorm_mod: shift and scale come together");
     B200_REQUIRE(!scale || (ld_m % 8 == 0 && rows % rows_per_img == 0), "layernorm_mod: modulation pitch / rows_per_img");
     if (rows == 0) return B200SD_OK;
-    launch_k(ln_mod_kernel, grid_for(rows, ROW_WARPS), ROW_WARPS * 32, 0, as_stream(stream), 
-        static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y,
-        static_cast<const __nv_bfloat16*>(shift), static_cast<const __nv_bfloat16*>(scale), ld_m, rows, rows_per_img, c,
-        eps, stats);
+    if (c <= 512)
+        launch_k(ln_mod_kernel<16>, grid_for((rows + 1) / 2, ROW_WARPS), ROW_WARPS * 32, 0, as_stream(stream),
+                 static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y,
+                 static_cast<const __nv_bfloat16*>(shift), static_cast<const __nv_bfloat16*>(scale), ld_m, rows,
+                 rows_per_img, c, eps, stats);
+    else
+        launch_k(ln_mod_kernel<32>, grid_for(rows, ROW_WARPS), ROW_WARPS * 32, 0, as_stream(stream),
+                 static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<__nv_bfloat16*>(y), ld_y,
+                 static_cast<const __nv_bfloat16*>(shift), static_cast<const __nv_bfloat16*>(scale), ld_m, rows,
+                 rows_per_img, c, eps, stats);
     B200_CHECK_LAUNCH("layernorm_mod");
     return B200SD_OK;
 }
