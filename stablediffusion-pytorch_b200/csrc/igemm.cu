@@ -572,33 +572,52 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                     const uint32_t pb = smem_u32(stg) + (colt >> 6) * PANEL_BYTES + (colt & 7) * 2;
                     const int chunk = (colt & 63) >> 3;
                     const bool full = (t.x0 + args.bw <= args.ow) && (t.y0 + args.bh <= args.oh);
-                    const int seg_i = rpi / RL;  // iterations per image
-                    int i = 0;
+                    // Summation order is the same for every column tile width (so a sample's statistics, and with
+                    // them its output, do not depend on the batch it travels in, which picks the tile): per residue
+                    // class r = row % 8 the rows 8j + r are added in increasing j; the eight class sums are then
+                    // combined as the balanced tree ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)) — in-lane for the RG classes a
+                    // lane owns, by xor-shuffles across the row lanes for the rest.
+                    const int seg_j = rpi >> 3;  // 8-row groups per image
                     for (int im = 0; im < args.bn && e * W < BN; ++im) {
-                        float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+                        float a0[RG], a1[RG], b0[RG], b1[RG];
+#pragma unroll
+                        for (int g = 0; g < RG; ++g) a0[g] = a1[g] = b0[g] = b1[g] = 0.f;
                         // branch-free body (staging rows outside the output are readable, just not counted):
                         // a per-lane `if` here cost a BSSY/BSYNC pair per row and made this pass 5 us per tile
                         if (full) {
-#pragma unroll 8
-                            for (int k = 0; k < seg_i; ++k, ++i) {
-                                const int row = rl * RG + (i % RG) + 8 * (i / RG);
-                                const uint32_t u = lds32(pb + row * 128 + ((chunk ^ (row & 7)) << 4));
-                                const float fx = __uint_as_float(u << 16), fy = __uint_as_float(u & 0xffff0000u);
-                                s0 += fx, s1 += fy, q0 = fmaf(fx, fx, q0), q1 = fmaf(fy, fy, q1);
+#pragma unroll 4
+                            for (int j = im * seg_j; j < (im + 1) * seg_j; ++j) {
+#pragma unroll
+                                for (int g = 0; g < RG; ++g) {
+                                    const int row = rl * RG + g + 8 * j;
+                                    const uint32_t u = lds32(pb + row * 128 + ((chunk ^ (row & 7)) << 4));
+                                    const float fx = __uint_as_float(u << 16), fy = __uint_as_float(u & 0xffff0000u);
+                                    a0[g] += fx, a1[g] += fy, b0[g] = fmaf(fx, fx, b0[g]), b1[g] = fmaf(fy, fy, b1[g]);
+                                }
                             }
                         } else {
 #pragma unroll 2
-                            for (int k = 0; k < seg_i; ++k, ++i) {
-                                const int row = rl * RG + (i % RG) + 8 * (i / RG);
-                                const bool ok = (t.x0 + row % args.bw < args.ow) && (t.y0 + (row / args.bw) % args.bh < args.oh);
-                                const uint32_t u = lds32(pb + row * 128 + ((chunk ^ (row & 7)) << 4));
-                                const float fx = ok ? __uint_as_float(u << 16) : 0.f;
-                                const float fy = ok ? __uint_as_float(u & 0xffff0000u) : 0.f;
-                                s0 += fx, s1 += fy, q0 = fmaf(fx, fx, q0), q1 = fmaf(fy, fy, q1);
+                            for (int j = im * seg_j; j < (im + 1) * seg_j; ++j) {
+#pragma unroll
+                                for (int g = 0; g < RG; ++g) {
+                                    const int row = rl * RG + g + 8 * j;
+                                    const bool ok = (t.x0 + row % args.bw < args.ow) && (t.y0 + (row / args.bw) % args.bh < args.oh);
+                                    const uint32_t u = lds32(pb + row * 128 + ((chunk ^ (row & 7)) << 4));
+                                    const float fx = ok ? __uint_as_float(u << 16) : 0.f;
+                                    const float fy = ok ? __uint_as_float(u & 0xffff0000u) : 0.f;
+                                    a0[g] += fx, a1[g] += fy, b0[g] = fmaf(fx, fx, b0[g]), b1[g] = fmaf(fy, fy, b1[g]);
+                                }
                             }
                         }
 #pragma unroll
-                        for (int off = CP; off < 32; off <<= 1) {
+                        for (int w = 1; w < RG; w <<= 1) {   // in-lane levels of the tree
+#pragma unroll
+                            for (int g = 0; g < RG; g += 2 * w)
+                                a0[g] += a0[g + w], a1[g] += a1[g + w], b0[g] += b0[g + w], b1[g] += b1[g + w];
+                        }
+                        float s0 = a0[0], s1 = a1[0], q0 = b0[0], q1 = b1[0];
+#pragma unroll
+                        for (int off = CP; off < 32; off <<= 1) {   // remaining levels across the row lanes
                             s0 += __shfl_xor_sync(0xffffffffu, s0, off);
                             s1 += __shfl_xor_sync(0xffffffffu, s1, off);
                             q0 += __shfl_xor_sync(0xffffffffu, q0, off);
