@@ -398,9 +398,15 @@ def run_ours(args):
     if args.train_steps > 0:
         del pipe, P, model, vae
         torch.cuda.empty_cache()
-        line["train"] = train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks)
+        try:
+            line["train"] = train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks)
+        except Exception as exc:   # the headline (sampling) line must still be printed
+            line["train"] = {"error": f"{type(exc).__name__}: {exc}"[:400]}
     if args.dit_steps > 0:
-        line["dit"] = dit_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, t_dec)
+        try:
+            line["dit"] = dit_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, t_dec)
+        except Exception as exc:
+            line["dit"] = {"error": f"{type(exc).__name__}: {exc}"[:400]}
     if rank == 0:
         print(json.dumps(line))
     if world > 1:
