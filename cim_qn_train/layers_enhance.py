@@ -1,0 +1,252 @@
+"""Enhance wrappers of the CIM quant-noise pipeline (reference cim_qn_train/layers_enhance.py) on the sm_100a engine.
+
+The reference wraps every quantised Linear of the DiT in two ways (cim_qn_train/progressive_qn_train.py:884-950):
+`EnhanceBranchLinear_LoR` adds a low-rank, grouped side branch blended in through a learned sigmoid factor
+(layers_enhance.py:556-621), `EnhanceLayerLinear` appends a grouped Linear (:413-436); both are built from
+`GroupedLinear` (:324-365), a block-diagonal Linear evaluated with an einsum. Here a GroupedLinear is ONE tcgen05 GEMM
+over the block-diagonal dense form of its (groups, out_group, in_group) parameter — assembled with differentiable torch
+ops, so autograd hands the per-group gradient back — and the wrappers expose the engine's leaf protocol
+(`forward_rows`: bf16 token rows in, bf16 rows out), so a DiT whose leaves were swapped for them keeps running on the
+fused path (sdb200.engine.linear). Module names, parameter shapes, initialisation and the group/rank search
+(`analyze_*`) follow the reference, so state_dicts are interchangeable.
+
+Built: the Linear family (what the DiT-9L pipeline instantiates for its 95 Linear leaves). The Conv2d wrappers of the
+reference (EnhanceLayerConv2d, EnhanceBranchConv2d_LoR) are not built yet: constructing them raises.
+"""
+import math
+
+import torch
+import torch.nn as nn
+
+from sdb200 import autograd as AG
+from sdb200 import engine as E
+from sdb200 import ops
+from sdb200 import runtime as rt
+
+
+# ------------------------------------------------------------------------------------------------ group / rank search
+def _divisors(x):
+    small = [d for d in range(1, math.isqrt(x) + 1) if x % d == 0]
+    return sorted(set(small + [x // d for d in small]))
+
+
+def _nearest(target, candidates):
+    """First candidate (in the given order) at minimal distance from target (layers_enhance.py:22-24)."""
+    return min(candidates, key=lambda d: abs(d - target))
+
+
+def ideal_hidden_features(F_in, F_out, ops_factor):
+    """Rank h at which an ungrouped two-layer branch costs ops_factor^(1/3) of the Linear (layers_enhance.py:43-50)."""
+    return (ops_factor ** (1 / 3) * F_in * F_out) / (F_in + F_out)
+
+
+def ideal_hidden_channels(C_in, C_out, k_h, k_w, ops_factor):
+    """Conv counterpart (layers_enhance.py:27-40)."""
+    return max(1, round(ops_factor ** (1 / 3) * C_in * C_out * (k_h * k_w) / (C_in + C_out)))
+
+
+def _search_lora(n_in, n_out, ops_orig, hid_ideal, ops_factor, key):
+    """Joint search of (group1, group2, hidden) shared by the Linear and Conv variants (layers_enhance.py:53-131,
+    134-207): over hidden sizes in [0.1, 10] x ideal, the groups closest to 1 / ops_factor^(1/3) among the common
+    divisors; lexicographic minimum of (|cost ratio - ops_factor|, imbalance of the three compression shares), first
+    hidden size winning ties."""
+    base = ops_factor ** (1 / 3)
+    d_in, d_out = set(_divisors(n_in)), set(_divisors(n_out))
+    best = None
+    for h in range(max(1, int(hid_ideal * 0.1)), max(1, int(hid_ideal * 10)) + 1):
+        d_h = _divisors(h)
+        g1 = _nearest(1 / base, [d for d in d_h if d in d_in])
+        g2 = _nearest(1 / base, [d for d in d_h if d in d_out])
+        factor = (n_in * h // g1 + h * n_out // g2) / ops_orig
+        shares = ((n_in * h + h * n_out) / ops_orig,
+                  (n_in * hid_ideal / g1 + hid_ideal * n_out) / ops_orig,
+                  (n_in * hid_ideal + hid_ideal * n_out / g2) / ops_orig)
+        score = (abs(factor - ops_factor),
+                 math.sqrt((shares[0] - base) ** 2 + (shares[1] - base) ** 2 + (shares[2] - base) ** 2))
+        if best is None or score < best[0]:
+            best = (score, {"group1": g1, "group2": g2, key: h, "estimated_ops_factor": factor})
+    return None if best is None else best[1]
+
+
+def analyze_lora_linear_ops(in_features, out_features, ops_factor):
+    hid = ideal_hidden_features(in_features, out_features, ops_factor)
+    cfg = _search_lora(in_features, out_features, in_features * out_features, hid, ops_factor, "hidden_features")
+    if cfg is None:
+        h = max(1, round(hid))
+        cfg = {"group1": 1, "group2": 1, "hidden_features": h,
+               "estimated_ops_factor": (in_features * h + h * out_features) / (in_features * out_features)}
+    return cfg
+
+
+def analyze_lora_conv_ops(in_channels, out_channels, kh, kw, ops_factor):
+    ops_orig = in_channels * out_channels * kh * kw
+    hid = ideal_hidden_channels(in_channels, out_channels, kh, kw, ops_factor)
+    cfg = _search_lora(in_channels, out_channels, ops_orig, hid, ops_factor, "hidden_channels")
+    if cfg is None:
+        h = max(1, int(hid))
+        cfg = {"group1": 1, "group2": 1, "hidden_channels": h,
+               "estimated_ops_factor": (in_channels * h + h * out_channels) / ops_orig}
+    return cfg
+
+
+def _smallest_group(width, ops_orig, ops_factor, fallback):
+    """Smallest divisor g of `width` whose grouped width x width map costs at most ops_factor of the original layer."""
+    for g in _divisors(width):
+        ratio = (width * width // g) / ops_orig
+        if ratio <= ops_factor:
+            return {"group": g, "estimated_ops_factor": ratio}
+    return {"group": width, "estimated_ops_factor": fallback}
+
+
+def analyze_enhance_conv_ops(in_channels, out_channels, kh, kw, ops_factor):
+    """layers_enhance.py:210-235."""
+    return _smallest_group(out_channels, in_channels * out_channels * kh * kw, ops_factor, 1.0 / (kh * kw))
+
+
+def analyze_enhance_linear_ops(in_features, out_features, ops_factor):
+    """layers_enhance.py:238-261."""
+    return _smallest_group(out_features, in_features * out_features, ops_factor, 1.0)
+
+
+# ------------------------------------------------------------------------------------------------ modules
+def _pad8(n):
+    return (n + 7) // 8 * 8
+
+
+def _as_rows(x):
+    rows = x.reshape(-1, x.shape[-1])
+    rows = rows if rows.dtype == torch.bfloat16 else rows.to(torch.bfloat16)
+    if rows.shape[1] % 8:
+        rows = torch.nn.functional.pad(rows, (0, 8 - rows.shape[1] % 8))
+    return rows.contiguous()
+
+
+class _RowsModule(nn.Module):
+    """forward(x) of a leaf that implements forward_rows: (..., in) -> (..., out) in x's dtype; CUDA only."""
+
+    def forward(self, x):
+        if not x.is_cuda:
+            raise rt.B200Error(f"{type(self).__name__}.forward: CUDA tensors required (this package has no CPU "
+                               "implementation; the reference itself is the CPU path)")
+        with torch.autocast("cuda", enabled=False):
+            out = self.forward_rows(_as_rows(x))
+        return out[:, :self.out_features].reshape(*x.shape[:-1], self.out_features).to(x.dtype)
+
+
+class GroupedLinear(_RowsModule):
+    """Block-diagonal Linear: `groups` independent (in/groups -> out/groups) maps (layers_enhance.py:324-365). Parameters
+    keep the reference's shapes — weight (groups, out_group, in_group) initialised to truncated identities, bias
+    (groups, out_group) zeros — the product runs as one GEMM over the dense block-diagonal matrix."""
+
+    def __init__(self, in_features, out_features, groups, dtype=torch.float32, device=None):
+        super().__init__()
+        assert in_features % groups == 0, "in_features must be divisible by groups"
+        assert out_features % groups == 0, "out_features must be divisible by groups"
+        self.in_features, self.out_features, self.groups = in_features, out_features, groups
+        self.in_group, self.out_group = in_features // groups, out_features // groups
+        eye = torch.eye(self.out_group, self.in_group, device=device, dtype=dtype)
+        self.weight = nn.Parameter(eye.expand(groups, -1, -1).clone())
+        self.bias = nn.Parameter(torch.zeros(groups, self.out_group, device=device, dtype=dtype))
+
+    def dense_weight(self):
+        """[out_features, in_features rounded up to 8] block-diagonal matrix, differentiable w.r.t. `weight`."""
+        w = torch.block_diag(*self.weight.float().unbind(0))
+        kp = _pad8(self.in_features)
+        return w if kp == self.in_features else torch.nn.functional.pad(w, (0, kp - self.in_features))
+
+    def forward_rows(self, rows, act=None):
+        """bf16 rows [M, >= in_features rounded up to 8] (zeros beyond in_features) -> bf16 rows [M, out_features rounded
+        up to 8], padding columns zero."""
+        kp, n = _pad8(self.in_features), self.out_features
+        if rows.shape[1] < kp:
+            raise rt.B200Error("GroupedLinear: input rows narrower than in_features rounded up to 8")
+        x = rows if rows.shape[1] == kp else rows[:, :kp].contiguous()
+        w, b = self.dense_weight(), self.bias.reshape(-1)
+        if E.training():
+            y, _ = AG.LinearFn.apply(x, w, b, None, None, False, act)
+        else:
+            y = rt.linear(x, ops.pack_linear_weight(w.detach()), bias=b.detach().float(), act=act)
+        if n % 8:   # the GEMM leaves the padding columns of its output unwritten: make them zeros
+            y = torch.nn.functional.pad(y[:, :n], (0, _pad8(n) - n))
+        return y
+
+
+def _reject_conv(name):
+    raise NotImplementedError(f"{name}: the Conv2d Enhance wrappers are not built in this package yet "
+                              "(Linear family only, DESIGN.md §7)")
+
+
+class EnhanceLayerConv2d(nn.Module):
+    def __init__(self, original_conv, ops_factor=0.05):
+        super().__init__()
+        _reject_conv("EnhanceLayerConv2d")
+
+
+class EnhanceBranchConv2d_LoR(nn.Module):
+    def __init__(self, original_conv, ops_factor=0.05, relu=False, sigmoid=True):
+        super().__init__()
+        _reject_conv("EnhanceBranchConv2d_LoR")
+
+
+def _leaf_rows(mod, rows):
+    """The wrapped Linear (plain nn.Linear or a cim_layers drop-in) on bf16 rows, through the engine's leaf dispatch."""
+    return E.linear(rows, mod)
+
+
+class EnhanceLayerLinear(_RowsModule):
+    """original Linear followed by a GroupedLinear(out, out) initialised to the identity (layers_enhance.py:413-436)."""
+
+    def __init__(self, original_linear, ops_factor=0.05):
+        super().__init__()
+        self.original_linear = original_linear
+        self.in_features, self.out_features = original_linear.in_features, original_linear.out_features
+        w = original_linear.weight
+        cfg = analyze_enhance_linear_ops(self.in_features, self.out_features, ops_factor)
+        self.fc1 = GroupedLinear(self.out_features, self.out_features, cfg["group"], dtype=w.dtype, device=w.device)
+
+    def forward_rows(self, rows, act=None):
+        return self.fc1.forward_rows(_leaf_rows(self.original_linear, rows), act=act)
+
+
+class EnhanceBranchLinear_LoR(_RowsModule):
+    """original Linear blended with a two-layer grouped low-rank branch (layers_enhance.py:556-621):
+    out = orig * (1 - s) + branch_2(relu?(branch_1(x))) * s,  s = sigmoid(blend_factor) (or blend_factor itself).
+    The blend starts at sigmoid(-6.9068) ~ 1e-3. std/mean of both operands are kept as the reference does (:605-608;
+    progressive_qn_train.py:993-996 reads them)."""
+
+    def __init__(self, original_linear, ops_factor=0.05, relu=False, sigmoid=True):
+        super().__init__()
+        self.original_linear = original_linear
+        self.in_features, self.out_features = original_linear.in_features, original_linear.out_features
+        self.relu, self.sigmoid = relu, sigmoid
+        w = original_linear.weight
+        cfg = analyze_lora_linear_ops(self.in_features, self.out_features, ops_factor)
+        hidden = cfg["hidden_features"]
+        self.enhance_branch_1 = GroupedLinear(self.in_features, hidden, cfg["group1"], dtype=w.dtype, device=w.device)
+        self.enhance_branch_2 = GroupedLinear(hidden, self.out_features, cfg["group2"], dtype=w.dtype, device=w.device)
+        self.blend_factor = nn.Parameter(torch.tensor(-6.9068 if sigmoid else 0.0))
+        for br in (self.enhance_branch_1, self.enhance_branch_2):
+            br.layer_flag, br.distance = 'enhance_branch', 1
+        self.std_ori = self.mean_ori = self.std_enhance = self.mean_enhance = None
+
+    def merge_feature_map(self, original_output, enhance_output):
+        s = torch.sigmoid(self.blend_factor) if self.sigmoid else self.blend_factor
+        combined = original_output * (1 - s) + enhance_output * s
+        with torch.no_grad():
+            self.std_ori, self.mean_ori = original_output.float().std(), original_output.float().mean()
+            self.std_enhance, self.mean_enhance = enhance_output.float().std(), enhance_output.float().mean()
+        return combined
+
+    def forward_rows(self, rows, act=None):
+        n = self.out_features
+        orig = _leaf_rows(self.original_linear, rows)
+        enh = self.enhance_branch_1.forward_rows(rows, act="relu" if self.relu else None)
+        enh = self.enhance_branch_2.forward_rows(enh)
+        out = self.merge_feature_map(orig[:, :n], enh[:, :n]).to(torch.bfloat16)
+        if act is not None:
+            if act != "relu":
+                raise rt.B200Error("EnhanceBranchLinear_LoR: only ReLU may follow the wrapped Linear")
+            out = torch.relu(out)
+        if n % 8:
+            out = torch.nn.functional.pad(out, (0, _pad8(n) - n))
+        return out.contiguous()

@@ -422,7 +422,83 @@ def gen_percent_opt():
     print("percent_opt: oracle == reference over 4 steps; fixture written")
 
 
+def gen_enhance():
+    """Enhance wrappers, Linear family (cim_qn_train/layers_enhance.py): the real modules on CPU with perturbed
+    parameters; outputs and gradients of every parameter and of the input; plus a table of the group / rank search."""
+    import itertools
+    import json
+    from unittest.mock import MagicMock
+    for m in ("matplotlib", "matplotlib.pyplot"):
+        sys.modules.setdefault(m, MagicMock())
+    spec = importlib.util.spec_from_file_location("ref_layers_enhance", os.path.join(REF, "cim_qn_train", "layers_enhance.py"))
+    ref = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref)
+    OE = _load(os.path.join(ROOT, "oracle", "enhance_torch.py"), "oracle_enhance_torch")
+    g = torch.Generator().manual_seed(77)
+    out = {"cases": []}
+    for kind, fin, fout, ops_f, relu, sig in (("branch", 288, 288, 0.05, False, True), ("branch", 96, 64, 0.1, True, True),
+                                              ("branch", 64, 192, 0.05, False, False), ("layer", 96, 192, 0.05, None, None),
+                                              ("layer", 96, 64, 0.25, None, None)):
+        lin = torch.nn.Linear(fin, fout)
+        with torch.no_grad():
+            lin.weight.copy_(torch.randn(fout, fin, generator=g) / fin ** 0.5)
+            lin.bias.copy_(torch.randn(fout, generator=g) * 0.1)
+        mod = ref.EnhanceBranchLinear_LoR(lin, ops_f, relu=relu, sigmoid=sig) if kind == "branch" else \
+            ref.EnhanceLayerLinear(lin, ops_f)
+        with torch.no_grad():
+            for n_, p_ in mod.named_parameters():
+                if "original_linear" in n_:
+                    continue
+                if n_ == "blend_factor":
+                    p_.copy_(torch.tensor(-0.4 if sig else 0.3))
+                else:
+                    p_.add_(torch.randn(p_.shape, generator=g) * 0.1)
+        x = torch.randn(2, 24, fin, generator=g).requires_grad_(True)
+        r = torch.randn(2, 24, fout, generator=g)
+        y = mod(x)
+        (y * r).sum().backward()
+        sd = {k: v.detach().clone() for k, v in mod.state_dict().items()}
+        grads = {k: p_.grad.clone() for k, p_ in mod.named_parameters()}
+        # oracle == reference
+        ps = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+        x2 = x.detach().clone().requires_grad_(True)
+        if kind == "branch":
+            y2, _, _ = OE.enhance_branch_linear(x2, ps["original_linear.weight"], ps["original_linear.bias"],
+                                                ps["enhance_branch_1.weight"], ps["enhance_branch_1.bias"],
+                                                ps["enhance_branch_2.weight"], ps["enhance_branch_2.bias"],
+                                                ps["blend_factor"], relu, sig)
+        else:
+            y2 = OE.enhance_layer_linear(x2, ps["original_linear.weight"], ps["original_linear.bias"],
+                                         ps["fc1.weight"], ps["fc1.bias"])
+        (y2 * r).sum().backward()
+        assert torch.equal(y, y2), "oracle Enhance forward differs"
+        # gradients: same formulas, but autograd may order the accumulation of a tensor used twice differently
+        for name_, a_, b_ in [("x", x.grad, x2.grad)] + [(k, grads[k], ps[k].grad) for k in grads]:
+            d_ = (a_ - b_).abs().max().item() / (a_.abs().max().item() + 1e-30)
+            assert d_ < 1e-5, f"oracle Enhance gradient of {name_} differs: {d_:.2e}"
+        out["cases"].append({"kind": kind, "in": fin, "out": fout, "ops_factor": ops_f, "relu": relu, "sigmoid": sig,
+                             "state": sd, "x": x.detach().clone(), "r": r, "y": y.detach().clone(),
+                             "dx": x.grad.clone(), "grads": grads,
+                             "std_mean": None if kind != "branch" else [float(mod.std_ori.detach()), float(mod.mean_ori.detach()),
+                                                                         float(mod.std_enhance.detach()), float(mod.mean_enhance.detach())]})
+    table = []
+    for i, o, f in itertools.product([28, 96, 192, 288, 512, 864, 1152], [64, 288, 512, 864, 1152, 1728],
+                                     [0.02, 0.05, 0.1, 0.25]):
+        table.append(["lora_linear", i, o, f, ref.analyze_lora_linear_ops(i, o, f)])
+        table.append(["enhance_linear", i, o, f, ref.analyze_enhance_linear_ops(i, o, f)])
+    for i, o, k, f in itertools.product([18, 64, 128, 384], [3, 64, 256, 384], [1, 3], [0.05, 0.1]):
+        table.append(["lora_conv", i, o, k, f, ref.analyze_lora_conv_ops(i, o, k, k, f)])
+        table.append(["enhance_conv", i, o, k, f, ref.analyze_enhance_conv_ops(i, o, k, k, f)])
+    torch.save(out, os.path.join(GOLD, "enhance_linear.pt"))
+    with open(os.path.join(GOLD, "enhance_search_table.json"), "w") as fjs:
+        json.dump(table, fjs)
+    print(f"enhance: oracle == reference on {len(out['cases'])} modules; {len(table)} search results recorded")
+
+
 def main():
+    if "--only-enhance" in sys.argv:
+        gen_enhance()
+        return
     if "--only-percent-opt" in sys.argv:
         gen_percent_opt()
         return

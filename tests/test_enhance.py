@@ -1,0 +1,60 @@
+"""Enhance wrappers (Linear family): CPU checks — the group / rank search against the reference's recorded
+results, the oracle against the reference fixture, and the drop-in modules' structure (state_dict keys and shapes)."""
+import json
+import os
+
+import torch
+
+from util import GOLD, load_golden
+
+
+def test_group_rank_search_matches_reference_table():
+    import cim_qn_train.layers_enhance as en
+    table = json.load(open(os.path.join(GOLD, "enhance_search_table.json")))
+    fn = {"lora_linear": en.analyze_lora_linear_ops, "enhance_linear": en.analyze_enhance_linear_ops,
+          "lora_conv": lambda i, o, k, f: en.analyze_lora_conv_ops(i, o, k, k, f),
+          "enhance_conv": lambda i, o, k, f: en.analyze_enhance_conv_ops(i, o, k, k, f)}
+    assert len(table) > 400
+    for kind, *args, want in table:
+        assert fn[kind](*args) == want, (kind, args)
+
+
+def _oracle_forward(c, ps, x):
+    from oracle import enhance_torch as OE
+    if c["kind"] == "branch":
+        return OE.enhance_branch_linear(x, ps["original_linear.weight"], ps["original_linear.bias"],
+                                        ps["enhance_branch_1.weight"], ps["enhance_branch_1.bias"],
+                                        ps["enhance_branch_2.weight"], ps["enhance_branch_2.bias"], ps["blend_factor"],
+                                        c["relu"], c["sigmoid"])[0]
+    return OE.enhance_layer_linear(x, ps["original_linear.weight"], ps["original_linear.bias"], ps["fc1.weight"],
+                                   ps["fc1.bias"])
+
+
+def test_oracle_matches_reference_fixture():
+    for c in load_golden("enhance_linear")["cases"]:
+        ps = {k: v.clone().requires_grad_(True) for k, v in c["state"].items()}
+        x = c["x"].clone().requires_grad_(True)
+        y = _oracle_forward(c, ps, x)
+        assert torch.equal(y, c["y"])
+        (y * c["r"]).sum().backward()
+        for got, want in [(x.grad, c["dx"])] + [(ps[k].grad, g) for k, g in c["grads"].items()]:
+            assert (got - want).abs().max() <= 1e-5 * want.abs().max()
+
+
+def test_drop_in_modules_have_the_reference_structure():
+    import cim_qn_train.layers_enhance as en
+    for c in load_golden("enhance_linear")["cases"]:
+        lin = torch.nn.Linear(c["in"], c["out"])
+        mod = en.EnhanceBranchLinear_LoR(lin, c["ops_factor"], relu=c["relu"], sigmoid=c["sigmoid"]) \
+            if c["kind"] == "branch" else en.EnhanceLayerLinear(lin, c["ops_factor"])
+        sd = mod.state_dict()
+        assert list(sd.keys()) == list(c["state"].keys())
+        assert all(sd[k].shape == v.shape for k, v in c["state"].items())
+        mod.load_state_dict(c["state"], strict=True)
+        if c["kind"] == "branch":
+            assert mod.enhance_branch_1.layer_flag == "enhance_branch" and mod.enhance_branch_2.distance == 1
+    # initialisation: truncated identities, zero bias, blend at sigmoid^-1(1e-3)
+    gl = en.GroupedLinear(12, 8, 2)
+    assert torch.equal(gl.weight[1], torch.eye(4, 6)) and float(gl.bias.abs().sum()) == 0.0
+    fresh = en.EnhanceBranchLinear_LoR(torch.nn.Linear(96, 64))
+    assert abs(float(fresh.blend_factor) + 6.9068) < 1e-6

@@ -1,0 +1,93 @@
+"""Enhance wrappers on the GPU: forward and gradients of the drop-in modules (one tcgen05 GEMM per GroupedLinear over its
+block-diagonal dense form) against the reference fixture; and a DiT whose Linear leaves are wrapped runs and trains on
+the engine's fused path. Tolerances: bf16 tensor-core arithmetic vs the reference's fp32 CPU run (north_star: 1e-2)."""
+import pytest
+import torch
+
+from util import load_golden, relerr
+
+pytestmark = pytest.mark.gpu
+
+
+def _build(c, dev):
+    import cim_qn_train.layers_enhance as en
+    lin = torch.nn.Linear(c["in"], c["out"])
+    mod = en.EnhanceBranchLinear_LoR(lin, c["ops_factor"], relu=c["relu"], sigmoid=c["sigmoid"]) \
+        if c["kind"] == "branch" else en.EnhanceLayerLinear(lin, c["ops_factor"])
+    mod.load_state_dict(c["state"], strict=True)
+    return mod.to(dev)
+
+
+@pytest.mark.parametrize("idx", range(5))
+def test_enhance_linear_forward_and_gradients_vs_reference(idx):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    dev = torch.device("cuda:0")
+    c = load_golden("enhance_linear")["cases"][idx]
+    mod = _build(c, dev)
+    with torch.no_grad():
+        y = mod.eval()(c["x"].to(dev))
+    assert y.shape == c["y"].shape and y.dtype == torch.float32
+    assert relerr(y.cpu(), c["y"]) < 1e-2
+    if c["kind"] == "branch":   # the statistics progressive_qn_train.py:993-996 reads
+        got = [float(v) for v in (mod.std_ori, mod.mean_ori, mod.std_enhance, mod.mean_enhance)]
+        assert all(abs(a - b) <= 2e-2 * max(abs(b), 0.05) for a, b in zip(got, c["std_mean"]))
+    mod.train()
+    x = c["x"].to(dev).requires_grad_(True)
+    (mod(x) * c["r"].to(dev)).sum().backward()
+    for name, p in mod.named_parameters():
+        want = c["grads"][name]
+        assert p.grad is not None and torch.isfinite(p.grad).all(), name
+        err = float((p.grad.cpu() - want).norm() / (want.norm() + 1e-12))
+        assert err < 3e-2, f"gradient of {name}: relative L2 {err:.3e}"
+    assert float((x.grad.cpu() - c["dx"]).norm() / c["dx"].norm()) < 3e-2
+
+
+def test_dit_with_wrapped_linear_leaves_runs_and_trains():
+    """Module surgery as progressive_qn_train.py:926-950 does it (setattr on the parent), on the small DiT fixture: with
+    the blend closed (sigmoid(-30) = 0) the wrapped model reproduces the plain one; opened, every branch parameter and
+    every blend factor receives a finite gradient through the engine's fused path."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    dev = torch.device("cuda:0")
+    import cim_qn_train.layers_enhance as en
+    from models.transformer import DIT
+    from util import cond_of, randomise_zero_init
+    fd = load_golden("dit_small_cond")
+    torch.manual_seed(fd["seed"])
+    model = DIT(4, fd["config"]).to(dev)
+    randomise_zero_init(model, fd["rand_seed"])
+    inp = fd["inputs"]
+    cond = cond_of(inp, fd["config"], dev)
+    x, t = inp["x"].to(dev), inp["t"].to(dev)
+    with torch.no_grad():
+        plain = model.eval()(x, t, cond)
+    wrapped = []
+    for name, child in list(model.named_modules()):
+        if type(child) is torch.nn.Linear and "layers." in name and child.in_features % 8 == 0 \
+                and child.out_features % 8 == 0:
+            parent = model.get_submodule(name.rsplit(".", 1)[0])
+            new = en.EnhanceBranchLinear_LoR(child, 0.05)
+            with torch.no_grad():
+                new.blend_factor.fill_(-30.0)
+            setattr(parent, name.rsplit(".", 1)[1], new)
+            wrapped.append(new)
+    assert len(wrapped) >= 4
+    model.to(dev)
+    if hasattr(model, "invalidate_plan"):
+        model.invalidate_plan()
+    with torch.no_grad():
+        closed = model.eval()(x, t, cond)
+    # (the wrapped leaves round to bf16 before the gate/residual the plain path fuses into the GEMM epilogue)
+    assert relerr(closed.cpu(), plain.cpu()) < 1e-2
+    for w in wrapped:
+        with torch.no_grad():
+            w.blend_factor.fill_(-0.5)
+            w.enhance_branch_2.weight.add_(torch.randn_like(w.enhance_branch_2.weight) * 0.05)
+    model.train()
+    out = model(x, t, cond)
+    out.square().mean().backward()
+    assert torch.isfinite(out).all()
+    for w in wrapped:
+        for n, p in w.named_parameters():
+            assert p.grad is not None and torch.isfinite(p.grad).all(), n
