@@ -549,6 +549,25 @@ def dit_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, t_dec):
     out["cim_lsq_train"] = train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks,
                                      make_model=lambda: cim_model("lsq"), gflop_fwd=DIT9_GFLOP,
                                      tag="DiT-9L text+image, all 95 Linear + mask conv as LSQ layers")
+    def enhanced_lsq_model():
+        """LSQ stage of the pipeline as Model_DiT_9L_train.py:541-553 leaves it: every quantised Linear wrapped in the
+        low-rank blend branch, then followed by a grouped enhance layer (the mask conv keeps its plain LSQ form: the
+        Conv2d wrappers are not built here)."""
+        import cim_qn_train.layers_enhance as en
+        m = cim_model("lsq")
+        lin = [(n, c) for n, c in m.named_modules() if type(c) is Linear_qn_lsq]
+        for n, c in lin:
+            parent = m.get_submodule(n.rsplit(".", 1)[0]) if "." in n else m
+            br = en.EnhanceBranchLinear_LoR(original_linear=c, relu=False, sigmoid=True, ops_factor=0.05)
+            br.original_linear = en.EnhanceLayerLinear(c, ops_factor=0.05)
+            setattr(parent, n.rsplit(".", 1)[-1], br)
+        return m
+
+    out["cim_lsq_enhance_train"] = train_leg(
+        args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=enhanced_lsq_model, gflop_fwd=DIT9_GFLOP,
+        optimizer="percent",
+        tag="DiT-9L text+image, LSQ leaves + EnhanceBranchLinear_LoR + EnhanceLayerLinear (ops_factor 0.05) around all "
+            "95 Linear, PercentOptimizerFP")
     out["cim_adda_train"] = train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks,
                                       make_model=lambda: cim_model("adda"), gflop_fwd=DIT9_GFLOP,
                                       tag="DiT-9L text+image, all 95 Linear + mask conv as ADDA compute-in-memory layers "
@@ -556,7 +575,8 @@ def dit_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, t_dec):
     return out
 
 
-def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=None, gflop_fwd=None, tag="unet"):
+def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=None, gflop_fwd=None, tag="unet",
+              optimizer=None):
     """BASELINE.json configs[2]: data-parallel training of the same conditioned UNet as
     train_ddpm_cond_celebhq_multi_gpu.py:341-378 does it — add_noise, bf16-autocast forward, MSE, backward (DDP's
     bucketed NCCL all-reduce overlapped with it when world > 1), clip_grad_norm_(1.0), Adam, EMA — per-GPU batch 16
@@ -582,8 +602,12 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=
         else:
             from sdb200.parallel import DataParallel
             net = DataParallel(model, device_ids=[dev.index], broadcast_buffers=False)
-    fused = args.train_opt == "fused"
-    if fused:
+    fused = args.train_opt == "fused" and optimizer is None
+    percent = optimizer == "percent"     # the CIM trainers' optimizer (Model_DiT_9L_train.py:266), no clip / EMA there
+    if percent:
+        from cim_layers.IBA_optimizer import PercentOptimizerFP
+        opt = PercentOptimizerFP(model.parameters(), lr=1e-5)
+    elif fused:
         from sdb200.optim import FusedAdam
         opt = FusedAdam(model.parameters(), lr=1e-5, max_grad_norm=1.0, ema_params=ema.parameters(), ema_decay=0.999)
     else:
@@ -603,7 +627,9 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=
             loss = torch.nn.functional.mse_loss(pred, noise)
         opt.zero_grad(set_to_none=True)
         loss.backward()
-        if fused:
+        if percent:
+            opt.step()      # Adam moments + per-tensor max-scaled update: two launches (csrc/optim.cu)
+        elif fused:
             opt.step()      # clip_grad_norm_(1.0) + finite check + Adam + EMA: two launches (sdb200/optim.py)
         else:
             torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
@@ -643,7 +669,8 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=
         "steps": K, "warmup": W, "batch_per_gpu": B, "global_batch": B * world, "dtype": "bf16",
         "model": tag, "params": sum(p.numel() for p in ema_params),
         "algorithmic_tflops": 3 * gflop_fwd * 1e9 * B / (out["value"][1] / 1e3) / 1e12,
-        "optimizer": ("sdb200.optim.FusedAdam: clip_grad_norm_(1.0) + finite check + Adam + EMA in two launches" if fused
+        "optimizer": ("cim_layers.IBA_optimizer.PercentOptimizerFP on b200sd_percent_opt_step: two launches" if percent else
+                      "sdb200.optim.FusedAdam: clip_grad_norm_(1.0) + finite check + Adam + EMA in two launches" if fused
                       else "Adam + clip_grad_norm_(1.0) + EMA (torch foreach)"), "gpu_launches": out["value"][2],
         "grad_allreduce": None if world == 1 else (
             "torch DistributedDataParallel: 25 MB NCCL buckets, reduced after the backward graph has replayed"
