@@ -551,23 +551,26 @@ def dit_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, t_dec):
                                      tag="DiT-9L text+image, all 95 Linear + mask conv as LSQ layers")
     def enhanced_lsq_model():
         """LSQ stage of the pipeline as Model_DiT_9L_train.py:541-553 leaves it: every quantised Linear wrapped in the
-        low-rank blend branch, then followed by a grouped enhance layer (the mask conv keeps its plain LSQ form: the
-        Conv2d wrappers are not built here)."""
+        low-rank blend branch, then followed by a grouped enhance layer; the 1x1 mask conv likewise with the Conv2d
+        wrappers (progressive_qn_train.py:884-950)."""
         import cim_qn_train.layers_enhance as en
         m = cim_model("lsq")
-        lin = [(n, c) for n, c in m.named_modules() if type(c) is Linear_qn_lsq]
-        for n, c in lin:
+        for n, c in [(n, c) for n, c in m.named_modules() if type(c) in (Linear_qn_lsq, Conv2d_qn_lsq)]:
             parent = m.get_submodule(n.rsplit(".", 1)[0]) if "." in n else m
-            br = en.EnhanceBranchLinear_LoR(original_linear=c, relu=False, sigmoid=True, ops_factor=0.05)
-            br.original_linear = en.EnhanceLayerLinear(c, ops_factor=0.05)
+            if type(c) is Linear_qn_lsq:
+                br = en.EnhanceBranchLinear_LoR(original_linear=c, relu=False, sigmoid=True, ops_factor=0.05)
+                br.original_linear = en.EnhanceLayerLinear(c, ops_factor=0.05)
+            else:
+                br = en.EnhanceBranchConv2d_LoR(original_conv=c, relu=False, sigmoid=True, ops_factor=0.05)
+                br.original_conv = en.EnhanceLayerConv2d(c, ops_factor=0.05)
             setattr(parent, n.rsplit(".", 1)[-1], br)
         return m
 
     out["cim_lsq_enhance_train"] = train_leg(
         args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=enhanced_lsq_model, gflop_fwd=DIT9_GFLOP,
         optimizer="percent",
-        tag="DiT-9L text+image, LSQ leaves + EnhanceBranchLinear_LoR + EnhanceLayerLinear (ops_factor 0.05) around all "
-            "95 Linear, PercentOptimizerFP")
+        tag="DiT-9L text+image, LSQ leaves + EnhanceBranch*_LoR + EnhanceLayer* (ops_factor 0.05) around all 95 Linear "
+            "and the mask conv, PercentOptimizerFP")
     out["cim_adda_train"] = train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks,
                                       make_model=lambda: cim_model("adda"), gflop_fwd=DIT9_GFLOP,
                                       tag="DiT-9L text+image, all 95 Linear + mask conv as ADDA compute-in-memory layers "

@@ -10,8 +10,9 @@ ops, so autograd hands the per-group gradient back — and the wrappers expose t
 fused path (sdb200.engine.linear). Module names, parameter shapes, initialisation and the group/rank search
 (`analyze_*`) follow the reference, so state_dicts are interchangeable.
 
-Built: the Linear family (what the DiT-9L pipeline instantiates for its 95 Linear leaves). The Conv2d wrappers of the
-reference (EnhanceLayerConv2d, EnhanceBranchConv2d_LoR) are not built yet: constructing them raises.
+Built: the Linear family (what the DiT-9L pipeline instantiates for its 95 Linear leaves), EnhanceLayerConv2d (any
+original conv the engine or a cim_layers drop-in runs) and EnhanceBranchConv2d_LoR for 1x1 / stride-1 / unpadded
+original convolutions (the pipeline's one conv, the 18 -> 3 mask conv); other branch shapes raise.
 """
 import math
 
@@ -157,35 +158,121 @@ class GroupedLinear(_RowsModule):
     def forward_rows(self, rows, act=None):
         """bf16 rows [M, >= in_features rounded up to 8] (zeros beyond in_features) -> bf16 rows [M, out_features rounded
         up to 8], padding columns zero."""
-        kp, n = _pad8(self.in_features), self.out_features
-        if rows.shape[1] < kp:
-            raise rt.B200Error("GroupedLinear: input rows narrower than in_features rounded up to 8")
-        x = rows if rows.shape[1] == kp else rows[:, :kp].contiguous()
-        w, b = self.dense_weight(), self.bias.reshape(-1)
-        if E.training():
-            y, _ = AG.LinearFn.apply(x, w, b, None, None, False, act)
-        else:
-            y = rt.linear(x, ops.pack_linear_weight(w.detach()), bias=b.detach().float(), act=act)
-        if n % 8:   # the GEMM leaves the padding columns of its output unwritten: make them zeros
-            y = torch.nn.functional.pad(y[:, :n], (0, _pad8(n) - n))
-        return y
+        return _dense_rows(rows, self.dense_weight(), self.bias.reshape(-1), self.out_features, act)
 
 
-def _reject_conv(name):
-    raise NotImplementedError(f"{name}: the Conv2d Enhance wrappers are not built in this package yet "
-                              "(Linear family only, DESIGN.md §7)")
+def _dense_rows(rows, w_dense, bias, n_out, act=None):
+    """rows [M, Kp] (zeros beyond the true K) @ w_dense[n_out, Kp]^T + bias -> [M, n_out rounded up to 8], padding
+    columns zero; one tcgen05 GEMM (autograd Function in training mode)."""
+    if rows.shape[1] < w_dense.shape[1]:
+        raise rt.B200Error("grouped map: input rows narrower than the channel count rounded up to 8")
+    x = rows if rows.shape[1] == w_dense.shape[1] else rows[:, :w_dense.shape[1]].contiguous()
+    fuse = act if n_out % 8 == 0 else None   # (a fused ReLU's backward wants an unpadded, contiguous output)
+    if E.training():
+        y, _ = AG.LinearFn.apply(x, w_dense, bias, None, None, False, fuse)
+    else:
+        y = rt.linear(x, ops.pack_linear_weight(w_dense.detach()), bias=None if bias is None else bias.detach().float(),
+                      act=fuse)
+    if n_out % 8:
+        y = torch.nn.functional.pad(y[:, :n_out], (0, _pad8(n_out) - n_out))
+    if act is not None and fuse is None:
+        if act != "relu":
+            raise rt.B200Error("grouped map: only ReLU may follow")
+        y = torch.relu(y)
+    return y
 
 
-class EnhanceLayerConv2d(nn.Module):
+def _conv1x1_dense(conv):
+    """Block-diagonal dense [out, in rounded up to 8] matrix of a grouped 1x1 nn.Conv2d, differentiable."""
+    g, co, ci = conv.groups, conv.out_channels, conv.in_channels
+    w = torch.block_diag(*conv.weight.float().reshape(g, co // g, ci // g).unbind(0))
+    return w if ci % 8 == 0 else torch.nn.functional.pad(w, (0, _pad8(ci) - ci))
+
+
+def _clean_rows(a):
+    """Rows of an Act with the columns beyond its channel count zeroed (a producer may leave them unwritten)."""
+    cp = _pad8(a.c)
+    if a.c % 8 == 0:
+        return a.t if a.t.shape[1] == cp else a.t[:, :cp].contiguous()
+    return torch.nn.functional.pad(a.t[:, :a.c], (0, cp - a.c))
+
+
+class _ActModule(nn.Module):
+    """forward(x) of a leaf that implements forward_act: NCHW in, NCHW out in x's dtype; CUDA only."""
+
+    def forward(self, x):
+        if not x.is_cuda:
+            raise rt.B200Error(f"{type(self).__name__}.forward: CUDA tensors required (this package has no CPU "
+                               "implementation; the reference itself is the CPU path)")
+        with torch.autocast("cuda", enabled=False):
+            out = self.forward_act(E.Act.from_nchw(x)).to_nchw()
+        return out.to(x.dtype)
+
+
+class EnhanceLayerConv2d(_ActModule):
+    """original conv followed by a grouped 1x1 convolution (out -> out) initialised to the identity
+    (layers_enhance.py:368-410). The original conv runs on its own path (a cim_layers drop-in or a plain nn.Conv2d the
+    engine supports); the grouped 1x1 map is one GEMM over the pixel rows."""
+
     def __init__(self, original_conv, ops_factor=0.05):
         super().__init__()
-        _reject_conv("EnhanceLayerConv2d")
+        self.original_conv = original_conv
+        co, ci = original_conv.out_channels, original_conv.in_channels
+        kh, kw = original_conv.kernel_size
+        w = original_conv.weight
+        self.groups = analyze_enhance_conv_ops(ci, co, kh, kw, ops_factor)["group"]
+        self.conv_enhance = nn.Conv2d(co, co, kernel_size=1, stride=1, padding=0, groups=self.groups, device=w.device,
+                                      dtype=w.dtype)
+        self.conv_enhance.layer_flag, self.conv_enhance.distance = 'enhance_layer', 1
+        with torch.no_grad():
+            eye = torch.eye(co // self.groups, dtype=w.dtype, device=w.device)
+            self.conv_enhance.weight.copy_(eye.repeat(self.groups, 1).view(co, co // self.groups, 1, 1))
+            self.conv_enhance.bias.fill_(0)
+
+    def forward_act(self, a):
+        y = E.conv2d(a, self.original_conv)
+        rows = _dense_rows(_clean_rows(y), _conv1x1_dense(self.conv_enhance), self.conv_enhance.bias, y.c)
+        return E.Act(rows, y.n, y.h, y.w, y.c)
 
 
-class EnhanceBranchConv2d_LoR(nn.Module):
+class EnhanceBranchConv2d_LoR(_ActModule):
+    """original conv blended with a two-layer grouped 1x1 low-rank branch (layers_enhance.py:439-535). Built for the
+    shape the DiT pipeline has — a 1x1, stride-1, unpadded original conv (the mask conv), where the reference's pooling
+    / padding / cropping of the branch output are no-ops; other shapes raise."""
+
     def __init__(self, original_conv, ops_factor=0.05, relu=False, sigmoid=True):
         super().__init__()
-        _reject_conv("EnhanceBranchConv2d_LoR")
+        if tuple(original_conv.kernel_size) != (1, 1) or tuple(original_conv.stride) != (1, 1) \
+                or tuple(original_conv.padding) != (0, 0):
+            raise NotImplementedError("EnhanceBranchConv2d_LoR: only 1x1 / stride 1 / padding 0 original convolutions are "
+                                      "built in this package (DESIGN.md §7)")
+        self.original_conv = original_conv
+        ci, co = original_conv.in_channels, original_conv.out_channels
+        self.stride, self.padding = original_conv.stride, original_conv.padding
+        self.relu, self.sigmoid = relu, sigmoid
+        w = original_conv.weight
+        cfg = analyze_lora_conv_ops(ci, co, 1, 1, ops_factor)
+        hidden = cfg["hidden_channels"]
+        self.enhance_branch_1 = nn.Conv2d(ci, hidden, kernel_size=1, stride=1, padding=self.padding,
+                                          groups=cfg["group1"], dtype=w.dtype, device=w.device)
+        self.enhance_branch_2 = nn.Conv2d(hidden, co, kernel_size=1, stride=1, padding=self.padding,
+                                          groups=cfg["group2"], dtype=w.dtype, device=w.device)
+        self.enhance_branch_1.layer_flag = self.enhance_branch_2.layer_flag = 'enhance_branch'
+        self.pool = None
+        self.blend_factor = nn.Parameter(torch.tensor(-6.9068 if sigmoid else 0.0))
+        self.std_ori = self.mean_ori = self.std_enhance = self.mean_enhance = None
+
+    merge_feature_map = None   # bound below (shared with the Linear wrapper)
+
+    def forward_act(self, a):
+        y = E.conv2d(a, self.original_conv)
+        b1, b2 = self.enhance_branch_1, self.enhance_branch_2
+        enh = _dense_rows(_clean_rows(a), _conv1x1_dense(b1), b1.bias, b1.out_channels, act="relu" if self.relu else None)
+        enh = _dense_rows(enh, _conv1x1_dense(b2), b2.bias, b2.out_channels)
+        out = self.merge_feature_map(y.t[:, :y.c], enh[:, :y.c]).to(torch.bfloat16)
+        if y.c % 8:
+            out = torch.nn.functional.pad(out, (0, _pad8(y.c) - y.c))
+        return E.Act(out.contiguous(), y.n, y.h, y.w, y.c)
 
 
 def _leaf_rows(mod, rows):
@@ -250,3 +337,7 @@ class EnhanceBranchLinear_LoR(_RowsModule):
         if n % 8:
             out = torch.nn.functional.pad(out, (0, _pad8(n) - n))
         return out.contiguous()
+
+
+EnhanceBranchConv2d_LoR.merge_feature_map = EnhanceBranchLinear_LoR.merge_feature_map
+

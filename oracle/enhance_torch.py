@@ -28,3 +28,21 @@ def enhance_branch_linear(x, lin_w, lin_b, w1, b1, w2, b2, blend, relu=False, si
     enh = grouped_linear(enh, w2, b2)
     s = torch.sigmoid(blend) if sigmoid else blend
     return orig * (1 - s) + enh * s, orig, enh
+
+
+def enhance_layer_conv(x, conv_w, conv_b, stride, padding, enh_w, enh_b, groups):
+    """layers_enhance.py:407-410: original conv, then the grouped 1x1 conv_enhance"""
+    y = torch.nn.functional.conv2d(x, conv_w, conv_b, stride=stride, padding=padding)
+    return torch.nn.functional.conv2d(y, enh_w, enh_b, groups=groups)
+
+
+def enhance_branch_conv1x1(x, conv_w, conv_b, w1, b1, g1, w2, b2, g2, blend, relu=False, sigmoid=True):
+    """layers_enhance.py:509-535 for a 1x1 / stride-1 / unpadded original conv (pool is None and the branch output has
+    the original's size, so the pad / crop block :523-531 does nothing)."""
+    orig = torch.nn.functional.conv2d(x, conv_w, conv_b)
+    enh = torch.nn.functional.conv2d(x, w1, b1, groups=g1)
+    if relu:
+        enh = torch.relu(enh)
+    enh = torch.nn.functional.conv2d(enh, w2, b2, groups=g2)
+    s = torch.sigmoid(blend) if sigmoid else blend
+    return orig * (1 - s) + enh * s

@@ -435,7 +435,20 @@ def gen_enhance():
     spec.loader.exec_module(ref)
     OE = _load(os.path.join(ROOT, "oracle", "enhance_torch.py"), "oracle_enhance_torch")
     g = torch.Generator().manual_seed(77)
+    torch.manual_seed(77)   # the branch convolutions keep nn.Conv2d's default initialisation (global generator)
     out = {"cases": []}
+
+    def bf16_grad_err(mod_, x_, r_, grads_):
+        """The reference module's own bf16-autocast gradient error (relative L2 per parameter): the yardstick the GPU
+        tests hold the kernels to where a ReLU makes the gradient ill-conditioned."""
+        for p_ in mod_.parameters():
+            p_.grad = None
+        xa = x_.detach().clone().requires_grad_(True)
+        with torch.autocast("cpu", dtype=torch.bfloat16):
+            ya = mod_(xa)
+        (ya.float() * r_).sum().backward()
+        return {k_: float((p_.grad - grads_[k_]).norm() / (grads_[k_].norm() + 1e-12)) for k_, p_ in mod_.named_parameters()}
+
     for kind, fin, fout, ops_f, relu, sig in (("branch", 288, 288, 0.05, False, True), ("branch", 96, 64, 0.1, True, True),
                                               ("branch", 64, 192, 0.05, False, False), ("layer", 96, 192, 0.05, None, None),
                                               ("layer", 96, 64, 0.25, None, None)):
@@ -478,9 +491,51 @@ def gen_enhance():
             assert d_ < 1e-5, f"oracle Enhance gradient of {name_} differs: {d_:.2e}"
         out["cases"].append({"kind": kind, "in": fin, "out": fout, "ops_factor": ops_f, "relu": relu, "sigmoid": sig,
                              "state": sd, "x": x.detach().clone(), "r": r, "y": y.detach().clone(),
-                             "dx": x.grad.clone(), "grads": grads,
+                             "dx": x.grad.clone(), "grads": grads, "ref_bf16_grad_err": bf16_grad_err(mod, x, r, grads),
                              "std_mean": None if kind != "branch" else [float(mod.std_ori.detach()), float(mod.mean_ori.detach()),
                                                                          float(mod.std_enhance.detach()), float(mod.mean_enhance.detach())]})
+    out["conv_cases"] = []
+    for kind, ci, co, k, pad, ops_f, relu, sig in (("branch", 16, 8, 1, 0, 0.1, False, True), ("branch", 32, 16, 1, 0, 0.25, True, False),
+                                                    ("layer", 16, 32, 3, 1, 0.05, None, None), ("layer", 16, 8, 1, 0, 0.25, None, None)):
+        conv = torch.nn.Conv2d(ci, co, k, padding=pad)
+        with torch.no_grad():
+            conv.weight.copy_(torch.randn(conv.weight.shape, generator=g) / (ci * k * k) ** 0.5)
+            conv.bias.copy_(torch.randn(co, generator=g) * 0.1)
+        mod = ref.EnhanceBranchConv2d_LoR(conv, ops_f, relu=relu, sigmoid=sig) if kind == "branch" else \
+            ref.EnhanceLayerConv2d(conv, ops_f)
+        with torch.no_grad():
+            for n_, p_ in mod.named_parameters():
+                if "original_conv" in n_:
+                    continue
+                if n_ == "blend_factor":
+                    p_.copy_(torch.tensor(-0.4 if sig else 0.3))
+                else:
+                    p_.add_(torch.randn(p_.shape, generator=g) * 0.1)
+        x = torch.randn(3, ci, 8, 8, generator=g).requires_grad_(True)
+        r = torch.randn(3, co, 8, 8, generator=g)
+        y = mod(x)
+        (y * r).sum().backward()
+        sd = {k_: v.detach().clone() for k_, v in mod.state_dict().items()}
+        grads = {k_: p_.grad.clone() for k_, p_ in mod.named_parameters()}
+        ps = {k_: v.clone().requires_grad_(True) for k_, v in sd.items()}
+        x2 = x.detach().clone().requires_grad_(True)
+        if kind == "branch":
+            y2 = OE.enhance_branch_conv1x1(x2, ps["original_conv.weight"], ps["original_conv.bias"],
+                                           ps["enhance_branch_1.weight"], ps["enhance_branch_1.bias"], mod.enhance_branch_1.groups,
+                                           ps["enhance_branch_2.weight"], ps["enhance_branch_2.bias"], mod.enhance_branch_2.groups,
+                                           ps["blend_factor"], relu, sig)
+        else:
+            y2 = OE.enhance_layer_conv(x2, ps["original_conv.weight"], ps["original_conv.bias"], 1, pad,
+                                       ps["conv_enhance.weight"], ps["conv_enhance.bias"], mod.groups)
+        (y2 * r).sum().backward()
+        assert torch.equal(y, y2), "oracle Enhance conv forward differs"
+        for name_, a_, b_ in [("x", x.grad, x2.grad)] + [(k_, grads[k_], ps[k_].grad) for k_ in grads]:
+            d_ = (a_ - b_).abs().max().item() / (a_.abs().max().item() + 1e-30)
+            assert d_ < 1e-5, f"oracle Enhance conv gradient of {name_} differs: {d_:.2e}"
+        out["conv_cases"].append({"kind": kind, "cin": ci, "cout": co, "k": k, "pad": pad, "ops_factor": ops_f, "relu": relu,
+                                  "sigmoid": sig, "state": sd, "x": x.detach().clone(), "r": r, "y": y.detach().clone(),
+                                  "dx": x.grad.clone(), "grads": grads,
+                                  "ref_bf16_grad_err": bf16_grad_err(mod, x, r, grads)})
     table = []
     for i, o, f in itertools.product([28, 96, 192, 288, 512, 864, 1152], [64, 288, 512, 864, 1152, 1728],
                                      [0.02, 0.05, 0.1, 0.25]):
@@ -492,7 +547,7 @@ def gen_enhance():
     torch.save(out, os.path.join(GOLD, "enhance_linear.pt"))
     with open(os.path.join(GOLD, "enhance_search_table.json"), "w") as fjs:
         json.dump(table, fjs)
-    print(f"enhance: oracle == reference on {len(out['cases'])} modules; {len(table)} search results recorded")
+    print(f"enhance: oracle == reference on {len(out['cases'])} + {len(out['conv_cases'])} modules; {len(table)} search results recorded")
 
 
 def main():

@@ -58,3 +58,45 @@ def test_drop_in_modules_have_the_reference_structure():
     assert torch.equal(gl.weight[1], torch.eye(4, 6)) and float(gl.bias.abs().sum()) == 0.0
     fresh = en.EnhanceBranchLinear_LoR(torch.nn.Linear(96, 64))
     assert abs(float(fresh.blend_factor) + 6.9068) < 1e-6
+
+
+def _oracle_conv_forward(c, ps, x, groups):
+    from oracle import enhance_torch as OE
+    if c["kind"] == "branch":
+        return OE.enhance_branch_conv1x1(x, ps["original_conv.weight"], ps["original_conv.bias"],
+                                         ps["enhance_branch_1.weight"], ps["enhance_branch_1.bias"], groups[0],
+                                         ps["enhance_branch_2.weight"], ps["enhance_branch_2.bias"], groups[1],
+                                         ps["blend_factor"], c["relu"], c["sigmoid"])
+    return OE.enhance_layer_conv(x, ps["original_conv.weight"], ps["original_conv.bias"], 1, c["pad"],
+                                 ps["conv_enhance.weight"], ps["conv_enhance.bias"], groups[0])
+
+
+def _build_conv(c):
+    import cim_qn_train.layers_enhance as en
+    conv = torch.nn.Conv2d(c["cin"], c["cout"], c["k"], padding=c["pad"])
+    mod = en.EnhanceBranchConv2d_LoR(conv, c["ops_factor"], relu=c["relu"], sigmoid=c["sigmoid"]) \
+        if c["kind"] == "branch" else en.EnhanceLayerConv2d(conv, c["ops_factor"])
+    groups = (mod.enhance_branch_1.groups, mod.enhance_branch_2.groups) if c["kind"] == "branch" else (mod.groups,)
+    return mod, groups
+
+
+def test_conv_wrappers_structure_and_oracle():
+    import cim_qn_train.layers_enhance as en
+    import pytest
+    for c in load_golden("enhance_linear")["conv_cases"]:
+        mod, groups = _build_conv(c)
+        sd = mod.state_dict()
+        assert list(sd.keys()) == list(c["state"].keys()) and all(sd[k].shape == v.shape for k, v in c["state"].items())
+        mod.load_state_dict(c["state"], strict=True)
+        ps = {k: v.clone().requires_grad_(True) for k, v in c["state"].items()}
+        x = c["x"].clone().requires_grad_(True)
+        y = _oracle_conv_forward(c, ps, x, groups)
+        assert torch.equal(y, c["y"])
+        (y * c["r"]).sum().backward()
+        for got, want in [(x.grad, c["dx"])] + [(ps[k].grad, g) for k, g in c["grads"].items()]:
+            assert (got - want).abs().max() <= 1e-5 * want.abs().max()
+    fresh = en.EnhanceLayerConv2d(torch.nn.Conv2d(8, 16, 3, padding=1), 0.05)   # identity initialisation (:399-405)
+    g = fresh.groups
+    assert torch.equal(fresh.conv_enhance.weight.view(16, 16 // g), torch.eye(16 // g).repeat(g, 1))
+    with pytest.raises(NotImplementedError):
+        en.EnhanceBranchConv2d_LoR(torch.nn.Conv2d(8, 8, 3, padding=1))

@@ -39,7 +39,40 @@ def test_enhance_linear_forward_and_gradients_vs_reference(idx):
         want = c["grads"][name]
         assert p.grad is not None and torch.isfinite(p.grad).all(), name
         err = float((p.grad.cpu() - want).norm() / (want.norm() + 1e-12))
-        assert err < 3e-2, f"gradient of {name}: relative L2 {err:.3e}"
+        # gate: 3e-2, or 1.5x the reference's own bf16-autocast gradient error where a ReLU in front of a rank-few
+        # bottleneck makes the gradient ill-conditioned for any bf16 pipeline (fixture: ref_bf16_grad_err)
+        gate = max(3e-2, 1.5 * c["ref_bf16_grad_err"][name])
+        assert err < gate, f"gradient of {name}: relative L2 {err:.3e} (gate {gate:.3e})"
+    assert float((x.grad.cpu() - c["dx"]).norm() / c["dx"].norm()) < 3e-2
+
+
+@pytest.mark.parametrize("idx", range(4))
+def test_enhance_conv_forward_and_gradients_vs_reference(idx):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    dev = torch.device("cuda:0")
+    from test_enhance import _build_conv
+    c = load_golden("enhance_linear")["conv_cases"][idx]
+    mod, _ = _build_conv(c)
+    mod.load_state_dict(c["state"], strict=True)
+    mod = mod.to(dev)
+    with torch.no_grad():
+        y = mod.eval()(c["x"].to(dev))
+    # fp32 inputs of the fixture are rounded to bf16 on entry; a rank-2 bottleneck (case 0) amplifies that: the gate is
+    # the relative L2 error at north_star's 1e-2, the single-element max-norm statistic gets twice that
+    l2 = float((y.cpu() - c["y"]).norm() / c["y"].norm())
+    assert y.shape == c["y"].shape and l2 < 1e-2 and relerr(y.cpu(), c["y"]) < 2e-2
+    mod.train()
+    x = c["x"].to(dev).requires_grad_(True)
+    (mod(x) * c["r"].to(dev)).sum().backward()
+    for name, p in mod.named_parameters():
+        want = c["grads"][name]
+        assert p.grad is not None and torch.isfinite(p.grad).all(), name
+        err = float((p.grad.cpu() - want).norm() / (want.norm() + 1e-12))
+        # gate: 3e-2, or 1.5x the reference's own bf16-autocast gradient error where a ReLU in front of a rank-few
+        # bottleneck makes the gradient ill-conditioned for any bf16 pipeline (fixture: ref_bf16_grad_err)
+        gate = max(3e-2, 1.5 * c["ref_bf16_grad_err"][name])
+        assert err < gate, f"gradient of {name}: relative L2 {err:.3e} (gate {gate:.3e})"
     assert float((x.grad.cpu() - c["dx"]).norm() / c["dx"].norm()) < 3e-2
 
 
