@@ -331,7 +331,8 @@ class EnhanceBranchLinear_LoR(_RowsModule):
 
     def merge_feature_map(self, original_output, enhance_output):
         s = torch.sigmoid(self.blend_factor) if self.sigmoid else self.blend_factor
-        combined = original_output * (1 - s) + enhance_output * s
+        # orig * (1 - s) + enh * s as one fused kernel (forward and backward): orig + s * (enh - orig)
+        combined = torch.lerp(original_output, enhance_output, s.to(original_output.dtype))
         with torch.no_grad():   # one fused reduction per operand (the reference: four separate ones, :605-608)
             self.std_ori, self.mean_ori = torch.std_mean(original_output)
             self.std_enhance, self.mean_enhance = torch.std_mean(enhance_output)
