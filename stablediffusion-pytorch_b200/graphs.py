@@ -197,6 +197,30 @@ class _ReplayFn(torch.autograd.Function):
         return (None, tg.dx.clone() if tg.dx is not None else None) + tg.take_grads()
 
 
+def plan_buckets(slots, fired, bucket_elems):
+    """Buckets of parameter indices for the in-graph gradient exchange: the parameters that receive a gradient (`fired`),
+    walked from the LAST to the first (the order backward produces them), closed whenever at least `bucket_elems`
+    elements have been collected. Every bucket is a run of consecutive used parameters, so it owns one contiguous slice
+    [bucket_range] of the flat gradient buffer. slots[i] = (offset, numel, shape) or None."""
+    buckets, cur, size = [], [], 0
+    for i in reversed(sorted(set(fired))):
+        cur.append(i)
+        size += slots[i][1]
+        if size >= bucket_elems:
+            buckets.append(cur)
+            cur, size = [], 0
+    if cur:
+        buckets.append(cur)
+    return buckets
+
+
+def bucket_range(slots, idxs):
+    """[lo, hi) of the flat buffer covered by a bucket (slots are 64-element aligned)."""
+    lo = min(slots[i][0] for i in idxs)
+    hi = max(slots[i][0] + (slots[i][1] + 63) // 64 * 64 for i in idxs)
+    return lo, hi
+
+
 class _BucketReducer:
     """Gradient mean over ranks, captured inside the backward graph. The flat buffer is cut into contiguous buckets in
     REVERSE parameter order (the order backward produces gradients); a tensor hook on every stand-in parameter counts its
@@ -210,18 +234,8 @@ class _BucketReducer:
         self.dist, self.tg = dist, tg
         self.group, bucket_elems = tg.overlap
         self.side = torch.cuda.Stream(device=dev)
-        used = sorted(set(tg._fired))
         self.index_of = {i: k for k, i in enumerate([i for i, sl in enumerate(tg.slots) if sl is not None])}
-        # buckets over parameter indices, walking from the last parameter to the first
-        self.buckets, cur, size = [], [], 0
-        for i in reversed(used):
-            cur.append(i)
-            size += tg.slots[i][1]
-            if size >= bucket_elems:
-                self.buckets.append(cur)
-                cur, size = [], 0
-        if cur:
-            self.buckets.append(cur)
+        self.buckets = plan_buckets(tg.slots, tg._fired, bucket_elems)
         self.bucket_of = {i: b for b, idxs in enumerate(self.buckets) for i in idxs}
         self.pending = [len(b) for b in self.buckets]
         self.done = [False] * len(self.buckets)
@@ -260,8 +274,7 @@ class _BucketReducer:
             srcs.append(g if g.dtype == torch.float32 else g.float())
         if views:
             torch._foreach_copy_(views, srcs)
-        lo = min(tg.slots[i][0] for i in idxs)
-        hi = max(tg.slots[i][0] + (tg.slots[i][1] + 63) // 64 * 64 for i in idxs)
+        lo, hi = bucket_range(tg.slots, idxs)
         main = torch.cuda.current_stream()
         self.side.wait_stream(main)          # fork: the bucket's producers are ordered before the collective
         with torch.cuda.stream(self.side):

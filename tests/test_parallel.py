@@ -81,3 +81,35 @@ def test_bench_batch_sharding_is_disjoint():
     a = bench.synth_inputs(2, cfg, rank=0, pin=False)
     b = bench.synth_inputs(2, cfg, rank=1, pin=False)
     assert a[0].shape == b[0].shape and not torch.equal(a[0], b[0])
+
+
+def test_gradient_bucket_plan_covers_the_flat_buffer_once():
+    """Host logic of the in-graph gradient exchange (graphs.plan_buckets / bucket_range): buckets walk the parameters
+    that receive gradients from last to first, each owns one contiguous slice of the flat buffer, the slices are
+    disjoint, ordered, and together cover every used slot; unused parameters never start or end a bucket."""
+    import importlib
+    G = importlib.import_module("sdb200.graphs")
+    sizes = [300, 7, 4096, 64, 1, 9000, 128, 33, 70000, 5]
+    slots, off = [], 0
+    for i, n in enumerate(sizes):
+        if i == 4:
+            slots.append(None)          # requires_grad = False
+            continue
+        slots.append((off, n, (n,)))
+        off += (n + 63) // 64 * 64
+    fired = [9, 8, 7, 5, 3, 2, 0, 2]    # 6 and 1 receive no gradient; 2 is reported twice
+    for cap in (1, 4000, 10000, 10 ** 9):
+        buckets = G.plan_buckets(slots, fired, cap)
+        flat = [i for b in buckets for i in b]
+        assert flat == [9, 8, 7, 5, 3, 2, 0]
+        ranges = [G.bucket_range(slots, b) for b in buckets]
+        for (lo, hi), b in zip(ranges, buckets):
+            assert lo % 64 == 0 and hi % 64 == 0 and lo < hi <= off
+            assert all(lo <= slots[i][0] and slots[i][0] + slots[i][1] <= hi for i in b)
+        for (lo_a, hi_a), (lo_b, hi_b) in zip(ranges, ranges[1:]):
+            assert hi_b <= lo_a          # later buckets lie below earlier ones, no overlap
+        if cap == 10 ** 9:
+            assert len(buckets) == 1
+        if cap == 1:
+            assert len(buckets) == 7
+        assert all(sum(slots[i][1] for i in b) >= cap for b in buckets[:-1])
