@@ -8,7 +8,10 @@
 // The MMAs are therefore warp-level mma.sync.m16n8k16 (bf16 in, fp32 accumulate) straight from registers, which
 // keeps P in registers between the two GEMMs; tcgen05 would add a TMEM round trip per tile for no gain here.
 //
-// CTA = 4 warps = 64 queries of one (batch, head); KV streamed in 64-key tiles, double-buffered with cp.async.
+// Two kernels: `attention_resident_kernel` (everything in the UNet / DiT: K and V of a (batch, head) staged once in
+// shared memory, 1-16 warps x 16 queries, several query tiles per CTA; 16 warps x 2 CTAs per SM for L >= 512) and the
+// streaming `attention_kernel` below for K/V that do not fit (VQVAE: L = 1024, d = 64): CTA = 4 warps = 64 queries of
+// one (batch, head); KV streamed in 64-key tiles, double-buffered with cp.async.
 #include "host.h"
 #include <cuda_bf16.h>
 #include <type_traits>

@@ -1,12 +1,18 @@
 // Implicit-GEMM core on tcgen05 / TMEM / TMA (SURVEY K1-K4, K6, K9-K13 projections).
 //
-// Persistent kernel, one CTA per SM, each CTA walks output tiles of 128 (pixels) x BN (channels):
+// Persistent kernel, each CTA walks output tiles of 128 (pixels) x BN (channels), BN in {256, 192, 128, 64, 32}. Three
+// residency forms of the same code (template parameters MINB, CL2; b200sd_igemm picks per call):
+//   one CTA per SM                     the default
+//   two CTAs per SM (<128,2,2>,<64,2,2>)  K <= 768 with more than one wave of tiles: overlaps two epilogue chains
+//   CTA pairs, cta_group::2 (CL2)      K >= 1024: two adjacent row tiles of one column tile as ONE 256 x BN MMA, each CTA
+//                                      staging half of the weight tile, which buys a 4-5 stage ring (see CL2 below)
+// Roles inside a CTA:
 //   warp 0      : TMA producer — per 64-channel K chunk one 4-D box load of the activation tile (the conv tap is a
 //                 coordinate offset; image borders are TMA out-of-bounds zero fill = conv padding) and one 2-D box
 //                 load of the weight tile, both landing 128B-swizzled, K-major in a STAGES-deep smem ring
 //   warp 1      : MMA issuer — lane 0 issues 4 x tcgen05.mma (M=128, N=BN, K=16) per chunk into one of TWO TMEM
 //                 accumulators, releases ring stages with tcgen05.commit and hands the accumulator to the epilogue
-//   warps 2..5  : epilogue — tcgen05.ld the accumulator (one TMEM lane = one output pixel per thread), bias /
+//   warps 2..9  : epilogue — tcgen05.ld the accumulator (one TMEM lane = one output pixel per thread), bias /
 //                 time-embedding row bias / activation / gate / residual, bf16 convert into a swizzled smem staging
 //                 tile, optional per-channel sum / sum-of-squares of the tile (the next GroupNorm's statistics), then
 //                 ONE thread issues TMA tensor stores. The residual tile is TMA-loaded into the same staging buffer
