@@ -100,3 +100,25 @@ def test_conv_wrappers_structure_and_oracle():
     assert torch.equal(fresh.conv_enhance.weight.view(16, 16 // g), torch.eye(16 // g).repeat(g, 1))
     with pytest.raises(NotImplementedError):
         en.EnhanceBranchConv2d_LoR(torch.nn.Conv2d(8, 8, 3, padding=1))
+
+
+def test_block_diagonal_dense_form_and_its_gradient():
+    """GroupedLinear.dense_weight / _conv1x1_dense (one cached-index scatter) equal torch.block_diag padded to 8 columns,
+    and the gradient that flows back to the (groups, out_g, in_g) parameter is the block-diagonal part of d(dense)."""
+    import cim_qn_train.layers_enhance as en
+    g = torch.Generator().manual_seed(2)
+    for fin, fout, groups in ((12, 20, 4), (96, 11 * 3, 3), (8, 8, 1), (288, 288, 96)):
+        gl = en.GroupedLinear(fin, fout, groups)
+        with torch.no_grad():
+            gl.weight.copy_(torch.randn(gl.weight.shape, generator=g))
+        dense = gl.dense_weight()
+        want = torch.block_diag(*gl.weight.detach().unbind(0))
+        kp = (fin + 7) // 8 * 8
+        assert dense.shape == (fout, kp) and torch.equal(dense[:, :fin], want) and float(dense[:, fin:].abs().sum()) == 0
+        up = torch.randn(dense.shape, generator=g)
+        (dense * up).sum().backward()
+        blocks = torch.stack([up[k * gl.out_group:(k + 1) * gl.out_group, k * gl.in_group:(k + 1) * gl.in_group]
+                              for k in range(groups)])
+        assert torch.equal(gl.weight.grad, blocks)
+    conv = torch.nn.Conv2d(16, 24, 1, groups=4)
+    assert torch.equal(en._conv1x1_dense(conv), torch.block_diag(*conv.weight.detach().reshape(4, 6, 4).unbind(0)))
