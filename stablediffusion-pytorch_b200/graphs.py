@@ -18,6 +18,28 @@ ENABLE_FORWARD_GRAPHS = True
 ENABLE_TRAIN_GRAPHS = True   # forward AND backward of a training step replay captured graphs (see TrainGraph)
 
 
+def _capture_inference(body):
+    """Capture `body()` (no autograd) into a fresh CUDA graph -> (graph, body's result, library launches captured).
+    `thread_local` error mode: a CUDA call another thread of the process happens to make (allocator housekeeping,
+    event queries) must not invalidate this thread's capture; one retry after a collect if a capture is invalidated
+    anyway — it holds no state besides the graph, so capturing again is safe."""
+    import gc
+    for attempt in (0, 1):
+        graph = torch.cuda.CUDAGraph()
+        before = rt.launch_count()
+        try:
+            with torch.cuda.graph(graph, capture_error_mode="thread_local"), torch.no_grad():
+                out = body()
+            return graph, out, rt.launch_count() - before
+        except Exception as exc:   # noqa: BLE001 - re-raised unless it is a capture invalidation on the first attempt
+            if attempt == 1 or "capture" not in (str(exc) + str(exc.__context__ or "")):
+                raise
+            del graph
+            torch.cuda.synchronize()
+            gc.collect()
+    raise AssertionError("unreachable")
+
+
 def as_nchw(out):
     """A model's `run` returns either an NHWC Act (UNet) or the fp32 NCHW tensor itself (DiT un-patchifies)."""
     return out.to_nchw() if hasattr(out, "to_nchw") else out
@@ -43,11 +65,7 @@ class GraphedForward:
             for _ in range(2):  # warm-up: packs weights, fills the K/V cache, sets kernel attributes
                 model.run(self.x, self.t, st)
         torch.cuda.current_stream().wait_stream(side)
-        self.graph = torch.cuda.CUDAGraph()
-        before = rt.launch_count()
-        with torch.cuda.graph(self.graph), torch.no_grad():
-            self.out = as_nchw(model.run(self.x, self.t, st))
-        self.launches = rt.launch_count() - before
+        self.graph, self.out, self.launches = _capture_inference(lambda: as_nchw(model.run(self.x, self.t, st)))
 
     def valid(self, st):
         return st is self.st and _param_stamp(self.params) == self.stamp
@@ -110,11 +128,7 @@ class SamplingPipeline:
                 body()
                 body()
             torch.cuda.current_stream().wait_stream(side)
-            P.graph = torch.cuda.CUDAGraph()
-            before = rt.launch_count()
-            with torch.cuda.graph(P.graph), torch.no_grad():
-                body()
-            P.launches = rt.launch_count() - before
+            P.graph, _, P.launches = _capture_inference(body)
         return P
 
     def plan(self, xt, cond_input=None, uncond_input=None, cf_guidance_scale=1.0, inject_z=False):
