@@ -195,6 +195,19 @@ int b200sd_groupnorm_bwd(const void* x, int64_t ld_x, const void* dy, int64_t ld
 int b200sd_colsum_blocks(int64_t n, int64_t hw, int c);
 int b200sd_colsum(const void* x, int64_t ld_x, int64_t n, int64_t hw, int c, float* part, float* out, int per_image,
                   uint32_t* counter, void* stream);
+/* b200sd_colsum without caller scratch and without any allocation. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving
+ * loops, harnesses that forbid it). Same result as b200sd_colsum with `counter` (out: fp32 [n, c] if per_image else
+ * [c], bit-identical — same kernel, same row blocks). The row-block partials and tail counters live in a static
+ * __device__ array of the library: n * b200sd_colsum_blocks(n, hw, c) * c must be <= b200sd_colsum_static_max_floats()
+ * (524,288 floats = 2 MiB, held by every GPU that loads the library until exit); larger requests return
+ * B200SD_ERR_ARG with the sizes in b200sd_last_error(). Calls cudaGetSymbolAddress once per device (make the first
+ * call on a device outside stream capture), then only cudaMemsetAsync of the counters + one kernel launch: no
+ * cudaMalloc / cudaFree / allocating library routine. Every call shares the array, so calls that overlap on the GPU
+ * (two streams, parallel graph branches) race; calls ordered on one stream are safe. */
+int64_t b200sd_colsum_static_max_floats(void);
+int b200sd_colsum_static(const void* x, int64_t ld_x, int64_t n, int64_t hw, int c, float* out, int per_image,
+                         void* stream);
 /* out[b, j] (+)= sum_r in[(b*rows + r)*cols*col_stride + j*col_stride], fp32, fixed order. */
 int b200sd_reduce_f32(const float* in, int64_t batch, int64_t rows, int64_t cols, int64_t col_stride, float* out,
                       int accumulate, void* stream);

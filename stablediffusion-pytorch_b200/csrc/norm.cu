@@ -752,3 +752,77 @@ extern "C" int b200sd_reduce_f32(const float* in, int64_t batch, int64_t rows, i
     B200_CHECK_LAUNCH("reduce_f32");
     return B200SD_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// b200sd_colsum_static — the same column sums for callers that may not allocate (CUDA-graph capture, serving loops,
+// harnesses that forbid cudaMalloc). No counterpart in the reference.
+// The row-block partials and the per-slab tail counters live in a file-scope __device__ array (held by every GPU that
+// loads the library until exit). Host code may not use the array's NAME as an address (it is a host-side stand-in):
+// the device address is fetched once per device with cudaGetSymbolAddress and passed to the kernel.
+// All calls share the array: two calls that overlap on the GPU (different streams, or concurrent graph branches) race.
+// ---------------------------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace b200 {
+constexpr long long COLSUM_STATIC_MAX_FLOATS = 512ll * 1024;   // 2 MiB of partials: n * row blocks * c <= this
+constexpr int COLSUM_STATIC_COUNTERS = 64;                     // one per 64-channel slab (c <= 4096)
+struct ColsumStaticScratch {
+    float part[COLSUM_STATIC_MAX_FLOATS];
+    unsigned int counter[COLSUM_STATIC_COUNTERS];
+};
+static __device__ __align__(256) ColsumStaticScratch g_colsum_static;
+constexpr int MAX_DEVICES = 64;
+static ColsumStaticScratch* g_colsum_static_addr[MAX_DEVICES] = {};
+static std::mutex g_colsum_static_mu;
+}  // namespace b200
+
+extern "C" int64_t b200sd_colsum_static_max_floats(void) { return COLSUM_STATIC_MAX_FLOATS; }
+
+extern "C" int b200sd_colsum_static(const void* x, int64_t ld_x, int64_t n, int64_t hw, int c, float* out,
+                                    int per_image, void* stream) {
+    B200_REQUIRE(x && out, "colsum_static: null pointer");
+    B200_REQUIRE(c > 0 && c % 8 == 0 && c <= 4096 && ld_x % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0,
+                 "colsum_static: needs channels %% 8 == 0 (<= 4096) and 16-byte aligned rows");
+    B200_REQUIRE(n >= 0 && n <= 65535 && hw >= 0, "colsum_static: batch exceeds grid limit");
+    const int pb = (n == 0 || hw == 0) ? 0 : colsum_blocks(n, hw, c);
+    const long long need = static_cast<long long>(n) * pb * c;
+    B200_REQUIRE(need <= COLSUM_STATIC_MAX_FLOATS,
+                 "colsum_static: %lld floats of partials (n %lld x %d row blocks x c %d) exceed the static scratch of "
+                 "%lld floats; use b200sd_colsum with caller-owned scratch",
+                 need, static_cast<long long>(n), pb, c, COLSUM_STATIC_MAX_FLOATS);
+    if (n == 0 || hw == 0) return B200SD_OK;
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) {
+        b200::set_error("colsum_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+        return B200SD_ERR_CUDA;
+    }
+    ColsumStaticScratch* scratch;
+    {
+        std::lock_guard<std::mutex> lk(g_colsum_static_mu);
+        if (!g_colsum_static_addr[dev]) {   // set-up, once per device, with that device current
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_colsum_static);
+            if (e != cudaSuccess || !p) {
+                b200::set_error("colsum_static: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+                return B200SD_ERR_CUDA;
+            }
+            g_colsum_static_addr[dev] = static_cast<ColsumStaticScratch*>(p);
+        }
+        scratch = g_colsum_static_addr[dev];
+    }
+    cudaStream_t st = as_stream(stream);
+    const unsigned slabs = (unsigned)((c + 63) / 64);
+    // the counters must start at zero; a launch leaves them there, but an aborted one might not: clear them (no allocation)
+    e = cudaMemsetAsync(scratch->counter, 0, sizeof(unsigned int) * slabs, st);
+    if (e != cudaSuccess) {
+        b200::set_error("colsum_static: cudaMemsetAsync: %s", cudaGetErrorString(e));
+        return B200SD_ERR_CUDA;
+    }
+    const long long rpb = (hw + pb - 1) / pb;
+    dim3 grid(slabs, (unsigned)pb, (unsigned)n);
+    launch_k(colsum_kernel, grid, 256, 0, st, static_cast<const __nv_bfloat16*>(x), ld_x, hw, c, (int)rpb, scratch->part, out,
+             per_image, scratch->counter);
+    B200_CHECK_LAUNCH("colsum_static");
+    return B200SD_OK;
+}
