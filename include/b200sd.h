@@ -56,12 +56,17 @@ int b200sd_sched_add_noise(const float* x0, const float* noise, const int64_t* t
  * x_prev = mean (t == 0) or mean + sqrt((1-acp[t-1])/(1-acp[t])*betas[t]) * z.
  * t is one timestep shared by the batch: read from t_dev (int64 on device) when non-null, else t_host.
  * z: injected N(0,1) noise (parity path) or NULL to draw it in-kernel with Philox4x32-10 (seed, offset).
+ * rng_state (optional): device uint64[2] = {seed, call index}; when non-null the Philox key is
+ * seed + 0x9E3779B97F4A7C15 * call index read from DEVICE memory (the `seed` argument is ignored), so a CUDA graph
+ * that froze its launch arguments still draws a different noise trajectory per sampling call: the host bumps
+ * rng_state[1] between calls. A device-side t outside [0, T) is clamped (the host-side t is range-checked).
  * Optional classifier-free guidance fused in (tools/sample_ddpm_text_image_cond.py:84-86):
  * eps = eps_uncond + cfg_scale*(eps - eps_uncond) when eps_uncond is non-null. */
 int b200sd_sched_prev_step(const float* xt, const float* eps, const float* eps_uncond, float cfg_scale,
                            const float* z, const int64_t* t_dev, int64_t t_host, const float* betas,
                            const float* alphas, const float* acp, const float* sqrt_1m_acp, int num_timesteps,
-                           float* x_prev, float* x0, int64_t n, uint64_t seed, uint64_t offset, void* stream);
+                           float* x_prev, float* x0, int64_t n, uint64_t seed, uint64_t offset,
+                           const uint64_t* rng_state, void* stream);
 
 /* t[i] += delta on device: the `for i in reversed(range(T))` loop counter of tools/sample_ddpm_text_image_cond.py:79-81
  * kept on the device so a whole sampling step (UNet forward + ancestral update + counter) replays as one CUDA graph. */

@@ -32,18 +32,20 @@ class Denoiser(nn.Module):
             return cond_input
         if torch.is_grad_enabled() or not E.HOIST_CONDITIONING:
             return self.prepare_cond(cond_input, x.shape, x.device)
-        key = (tuple(x.shape),) + tuple((k, v.data_ptr(), v._version, tuple(v.shape))
-                                        for k, v in sorted(cond_input.items()) if isinstance(v, torch.Tensor))
-        key += tuple((p.data_ptr(), p._version) for p in self._cond_params())
-        cache = self.__dict__.setdefault("_cond_cache", {})
-        st = cache.get(key)
-        if st is None:
-            st = self.prepare_cond(cond_input, x.shape, x.device)
-            if st.ctx is not None:
-                st.ctx.persistent = True
-            if len(cache) >= 4:  # conditional + unconditional (CFG) and a little slack
-                cache.pop(next(iter(cache)))
-            cache[key] = st
+        # A hit needs the SAME tensor objects (weak references: a freed tensor can never match, and nothing is kept
+        # alive), unmodified since the entry was made (_version), and unchanged conditioning weights. Addresses are
+        # not part of the key: the caching allocator hands the next batch's same-shape tensor the address of the
+        # previous one (batch_condition_image_generator.py builds its conditions with torch.cat(...).to(device) per batch).
+        wstamp = tuple((p.data_ptr(), p._version) for p in self._cond_params())
+        cache = self.__dict__.setdefault("_cond_cache", [])
+        for ent in cache:
+            if ent[0] == tuple(x.shape) and ent[2] == wstamp and G.cond_key_matches(ent[1], cond_input):
+                return ent[3]
+        st = self.prepare_cond(cond_input, x.shape, x.device)
+        if st.ctx is not None:
+            st.ctx.persistent = True
+        cache[:] = [e for e in cache if G.cond_key_alive(e[1])][-3:]   # conditional + unconditional (CFG) and a little slack
+        cache.append((tuple(x.shape), G.cond_key(cond_input), wstamp, st))
         return st
 
     def forward(self, x, t, cond_input=None):

@@ -81,10 +81,16 @@ __global__ void __launch_bounds__(256)
                      const float* __restrict__ betas, const float* __restrict__ alphas,
                      const float* __restrict__ acp, const float* __restrict__ s1m, int T,
                      float* __restrict__ x_prev, float* __restrict__ x0, int64_t n, uint64_t seed,
-                     uint64_t offset) {
+                     uint64_t offset, const uint64_t* __restrict__ rng_state) {
     pdl_enter();
     int64_t tt = t_dev ? *t_dev : t_host;
     tt = tt < 0 ? tt + T : tt;
+    if (t_dev) tt = tt < 0 ? 0 : (tt >= T ? T - 1 : tt);   // a device-side t is not range-checked by the host: clamp
+    if (rng_state) {
+        // launch arguments are frozen inside a CUDA graph: the Philox key of a replayed loop comes from device memory,
+        // {seed, call index}; each sampling call gets its own key, hence its own noise trajectory
+        seed = rng_state[0] + 0x9E3779B97F4A7C15ull * rng_state[1];
+    }
     const PrevCoef c = prev_coef(betas, alphas, acp, s1m, static_cast<int>(tt));
     const int64_t gid = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
@@ -93,7 +99,10 @@ __global__ void __launch_bounds__(256)
     if (draw) {
         // when t is read from the device the launch arguments are frozen inside a CUDA graph, so the stream position
         // is derived from the timestep: every replay draws a fresh, non-overlapping block of the Philox sequence
-        const uint64_t per_call = 4ull * static_cast<uint64_t>((n / 4 + stride - 1) / stride + 1);
+        // 32-bit outputs one thread consumes per launch: a float4 path iteration draws 4 (curand_normal4), a scalar
+        // iteration 1 on average (curand_normal draws 2 and keeps the second Box-Muller value) but 2 at worst
+        const uint64_t iters = static_cast<uint64_t>(VEC ? ((n >> 2) + stride - 1) / stride : (n + stride - 1) / stride);
+        const uint64_t per_call = (VEC ? 4ull : 2ull) * iters + 4ull;
         const uint64_t step = t_dev ? static_cast<uint64_t>(T - 1 - c.t) : 0ull;
         curand_init(seed, gid, offset + step * per_call, &rng);
     }
@@ -213,7 +222,7 @@ extern "C" int b200sd_sched_prev_step(const float* xt, const float* eps, const f
                                       const float* z, const int64_t* t_dev, int64_t t_host, const float* betas,
                                       const float* alphas, const float* acp, const float* sqrt_1m_acp,
                                       int num_timesteps, float* x_prev, float* x0, int64_t n, uint64_t seed,
-                                      uint64_t offset, void* stream) {
+                                      uint64_t offset, const uint64_t* rng_state, void* stream) {
     B200_REQUIRE(xt && eps && betas && alphas && acp && sqrt_1m_acp && x_prev && x0, "prev_step: null pointer");
     B200_REQUIRE(n >= 0, "prev_step: negative size");
     if (!t_dev)
@@ -227,11 +236,11 @@ extern "C" int b200sd_sched_prev_step(const float* xt, const float* eps, const f
     if (vec)
         launch_k(prev_step_kernel<true>, grid, 256, 0, as_stream(stream), xt, eps, eps_uncond, cfg_scale, z, t_dev, t_host,
                                                                       betas, alphas, acp, sqrt_1m_acp, num_timesteps,
-                                                                      x_prev, x0, n, seed, offset);
+                                                                      x_prev, x0, n, seed, offset, rng_state);
     else
         launch_k(prev_step_kernel<false>, grid, 256, 0, as_stream(stream), xt, eps, eps_uncond, cfg_scale, z, t_dev,
                                                                        t_host, betas, alphas, acp, sqrt_1m_acp,
-                                                                       num_timesteps, x_prev, x0, n, seed, offset);
+                                                                       num_timesteps, x_prev, x0, n, seed, offset, rng_state);
     B200_CHECK_LAUNCH("prev_step");
     return B200SD_OK;
 }

@@ -49,6 +49,29 @@ def _param_stamp(params):
     return tuple((p.data_ptr(), p._version) for p in params)
 
 
+def cond_key(cond_input):
+    """Identity stamp of a condition dict: (name, weak reference, _version, shape) per tensor. Identity, not address:
+    the caching allocator reuses the address of a freed same-shape tensor at _version 0, so (data_ptr, _version) alone
+    would match the NEXT batch's conditions against the previous batch's hoisted state."""
+    import weakref
+    if cond_input is None:
+        return None
+    return tuple((k, weakref.ref(v), v._version, tuple(v.shape)) for k, v in sorted(cond_input.items())
+                 if isinstance(v, torch.Tensor))
+
+
+def cond_key_matches(key, cond_input):
+    if key is None or cond_input is None:
+        return key is None and cond_input is None
+    cur = [(k, v) for k, v in sorted(cond_input.items()) if isinstance(v, torch.Tensor)]
+    return len(cur) == len(key) and all(k == kk and ref() is v and v._version == ver and tuple(v.shape) == shp
+                                        for (k, v), (kk, ref, ver, shp) in zip(cur, key))
+
+
+def cond_key_alive(key):
+    return key is None or all(ref() is not None for _, ref, _, _ in key)
+
+
 class GraphedForward:
     """One captured forward of `model.run` for a fixed (shape, t-length, CondState)."""
 
@@ -92,8 +115,8 @@ class SamplingPipeline:
         m, dev = self.model, xt.device
         n = xt.shape[0]
         P = type("Plan", (), {})()
-        P.key = (tuple(xt.shape), id(cond_input), id(uncond_input), float(cfg_scale), inject_z,
-                 _param_stamp(list(m.parameters())))
+        P.key = self._key(xt, cf_scale_key=float(cfg_scale), inject_z=inject_z)
+        P.cond_key, P.uncond_key = cond_key(cond_input), cond_key(uncond_input)
         P.xt = torch.empty_like(xt, dtype=torch.float32)
         P.x0 = torch.empty_like(P.xt)
         P.t = torch.zeros(n, device=dev, dtype=torch.int64)
@@ -106,13 +129,16 @@ class SamplingPipeline:
             if s is not None and s.ctx is not None:
                 s.ctx.persistent = True
         tables = self.scheduler._tables(dev)[:4]
-        seed = self.scheduler.seed
+        # Philox key of the in-kernel noise, read from device memory by the captured launch: {seed, call index}.
+        # sample() refreshes it before every run, so successive batches do not share their noise trajectories and a
+        # changed scheduler.seed takes effect without re-capturing.
+        P.rng = torch.zeros(2, device=dev, dtype=torch.int64)
 
         def body():
             eps = as_nchw(m.run(P.xt, P.t, P.st))
             eps_u = as_nchw(m.run(P.xt, P.t, P.st_u)) if P.st_u is not None else None
             rt.sched_prev_step(P.xt, eps, P.t[:1], tables, z=P.z, eps_uncond=eps_u, cfg_scale=cfg_scale,
-                               seed=seed, offset=0, x_prev=P.xt, x0=P.x0)
+                               seed=0, offset=0, x_prev=P.xt, x0=P.x0, rng_state=P.rng)
             rt.advance_t(P.t, -1)
 
         P.body = body
@@ -131,10 +157,17 @@ class SamplingPipeline:
             P.graph, _, P.launches = _capture_inference(body)
         return P
 
+    def _key(self, xt, cf_scale_key, inject_z):
+        return (tuple(xt.shape), cf_scale_key, inject_z, _param_stamp(list(self.model.parameters())))
+
     def plan(self, xt, cond_input=None, uncond_input=None, cf_guidance_scale=1.0, inject_z=False):
-        key = (tuple(xt.shape), id(cond_input), id(uncond_input), float(cf_guidance_scale), inject_z,
-               _param_stamp(list(self.model.parameters())))
-        if self._plan is None or self._plan.key != key:
+        """The captured loop body for these shapes / conditions / weights / seed. The condition dicts are matched by the
+        identity and _version of the tensors inside them (graphs.cond_key), never by id() of the dict or by address."""
+        key = self._key(xt, float(cf_guidance_scale), inject_z)
+        P = self._plan
+        if P is None or P.key != key or not cond_key_matches(P.cond_key, cond_input) \
+                or not cond_key_matches(P.uncond_key, uncond_input):
+            self._plan = None   # release the old plan's graph and buffers before building the next
             self._plan = self._build(xt, cond_input, uncond_input, cf_guidance_scale, inject_z)
         return self._plan
 
@@ -149,9 +182,11 @@ class SamplingPipeline:
 
     @torch.no_grad()
     def sample(self, xt, cond_input=None, uncond_input=None, cf_guidance_scale=1.0, t_start=None, num_steps=None,
-               z_fn=None, decode=True):
+               z_fn=None, decode=True, noise_call=None):
         """Run timesteps t_start, t_start-1, ... (num_steps of them, default down to 0) from `xt`; returns
-        (x_final, x0_estimate, images or None)."""
+        (x_final, x0_estimate, images or None). The in-kernel noise is keyed by (scheduler.seed, call index): every
+        call draws a fresh trajectory, as the reference's torch.randn does; pass `noise_call` to name the index (the
+        same seed and index reproduce a run bit for bit)."""
         T = self.scheduler.num_timesteps
         t_start = T - 1 if t_start is None else t_start
         num_steps = t_start + 1 if num_steps is None else num_steps
@@ -159,6 +194,9 @@ class SamplingPipeline:
         P = self.plan(xt, cond_input, uncond_input, cf_guidance_scale, inject_z=z_fn is not None)
         P.xt.copy_(xt)
         P.t.fill_(t_start)
+        self._calls = getattr(self, "_calls", 0) + 1
+        P.rng.copy_(torch.tensor([int(self.scheduler.seed), self._calls if noise_call is None else int(noise_call)],
+                                 dtype=torch.int64))
         for k in range(num_steps):
             if z_fn is not None:
                 P.z.copy_(z_fn(t_start - k))
@@ -196,6 +234,7 @@ class _ReplayFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, tg, x, *params):
         ctx.tg = tg
+        tg.generation = ctx.generation = getattr(tg, "generation", 0) + 1
         tg.x.copy_(x)
         tg.fwd_graph.replay()
         rt.count_external(tg.fwd_launches)
@@ -205,6 +244,11 @@ class _ReplayFn(torch.autograd.Function):
     @torch.autograd.function.once_differentiable
     def backward(ctx, g):
         tg = ctx.tg
+        if tg.generation != ctx.generation:
+            # the backward graph differentiates the activations the LAST forward replay left in the graph's pool
+            raise rt.B200Error("backward of a captured training step after another forward of the same model replayed: "
+                               "run two in-flight forwards (f(x1) + f(x2), distillation losses) with "
+                               "sdb200.graphs.ENABLE_TRAIN_GRAPHS = False")
         tg.gout.copy_(g)
         tg.bwd_graph.replay()
         rt.count_external(tg.bwd_launches)

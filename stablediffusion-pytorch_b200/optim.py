@@ -168,7 +168,18 @@ class FusedAdam(torch.optim.Optimizer):
             tab, n = ent
             rt.adam_ema_step(tab, n, gbase, self._m, self._v, self._scalars, g["lr"], g["betas"][0], g["betas"][1],
                              g["eps"], g["weight_decay"], self.ema_decay)
+        self._bump_versions(present)
         return loss
+
+    def _bump_versions(self, present):
+        """The update kernels write parameters and EMA shadows through raw pointers, which autograd's version counters
+        do not see. Every inference-side cache (packed bf16 weights, captured forward graphs, hoisted conditioning) is
+        stamped with (data_ptr, _version): bump the counters so an in-process validation / sampling pass after a
+        training step re-derives them instead of silently running on the weights packed before the step."""
+        written = [p for p, has in zip(self._all, present) if has]
+        if self._ema is not None:
+            written += [e for e, has in zip(self._ema, present) if has]
+        torch.autograd.graph.increment_version(written)
 
     # ------------------------------------------------------------------------------------------ checkpoints
     def state_dict(self):
@@ -256,6 +267,7 @@ class PercentOptimizerFP(FusedAdam):
                 tmax.zero_()
                 rt.percent_opt_step(tab, tid, n, gbase, self._m, self._v, tmax, lr, b1, b2, 1 - b1, 1 - b2, adj, bc2s,
                                     eps)
+        self._bump_versions(present)
         return loss
 
     def state_dict(self):

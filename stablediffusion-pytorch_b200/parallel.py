@@ -78,18 +78,32 @@ class DataParallel(nn.Module):
         self._graph_synced = True
 
     def _landed(self, p):
+        """Post-accumulate hook of every trainable parameter. The FIRST gradient of a backward pass queues one
+        end-of-backward callback; the exchange happens there, so a parameter that receives no gradient in some step
+        (an unused branch, a frozen-by-usage conditioning path) cannot leave a short count behind that would fire the
+        collective in the middle of the next backward."""
         self._pending += 1
-        if self._pending < len(self._params):
-            return
+        if self._pending == 1:
+            torch.autograd.Variable._execution_engine.queue_callback(self._backward_done)
+
+    def _backward_done(self):
         self._pending = 0
         if self._graph_synced:  # this backward already reduced its flat buffer
             self._graph_synced = False
             return
-        grads = [q.grad for q in self._params if q.grad is not None]
-        flat = torch._utils._flatten_dense_tensors(grads)
+        # every rank reduces the SAME layout: one slot per trainable parameter, zeros where this rank has no gradient
+        ref = next((q.grad for q in self._params if q.grad is not None), None)
+        if ref is None:
+            return
+        sizes = [q.numel() for q in self._params]
+        flat = torch.zeros(sum(sizes), device=ref.device, dtype=torch.float32)
+        views = list(flat.split(sizes))
+        have = [(v, q.grad) for v, q in zip(views, self._params) if q.grad is not None]
+        torch._foreach_copy_([v.view(g.shape) for v, g in have], [g for _, g in have])
         _mean_(flat, self.group, self.bucket_elems)
-        for g, s in zip(grads, torch._utils._unflatten_dense_tensors(flat, grads)):
-            g.copy_(s)
+        for v, q in zip(views, self._params):
+            if q.grad is not None:
+                q.grad.copy_(v.view(q.grad.shape))
 
     def forward(self, *args, **kwargs):
         if self.broadcast_buffers and any(True for _ in self.module.buffers()):

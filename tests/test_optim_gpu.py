@@ -161,3 +161,57 @@ def test_percent_optimizer_matches_reference_fixture():
             p.grad = e.clone()
         o.step()
     assert all(torch.equal(a.data, b.data) for a, b in zip(params, params2))
+
+
+def test_inference_caches_see_the_optimizer_step():
+    """The update kernels write parameters and EMA shadows through raw pointers; every inference-side cache (packed bf16
+    weights, captured forward graphs, hoisted conditioning) is stamped with (data_ptr, _version). After a step, an eval
+    forward of the trained model AND of the EMA model must run on the new weights: equal to a fresh model loaded from
+    the state_dict, different from before."""
+    import copy as _copy
+    import sys
+    import os
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from util import cond_of, load_golden
+    from models.unet_cond_base import Unet
+    dev = torch.device("cuda:0")
+    fx = load_golden("unet_small_cond")
+    cfg, inp = fx["config"], fx["inputs"]
+    torch.manual_seed(fx["seed"])
+    model = Unet(4, cfg).to(dev)
+    ema = _copy.deepcopy(model).eval()
+    for p in ema.parameters():
+        p.requires_grad_(False)
+    opt = OPT.FusedAdam(model.parameters(), lr=1e-2, max_grad_norm=1.0, ema_params=ema.parameters(), ema_decay=0.5)
+    x, t, cond = inp["x"].to(dev), inp["t"].to(dev), cond_of(inp, cfg, dev)
+
+    def evaluate(m):
+        was = m.training
+        m.eval()
+        with torch.no_grad():
+            out = m(x, t, cond).clone()
+        m.train(was)
+        return out
+
+    with torch.no_grad():
+        ema_before = ema(x, t, cond).clone()          # the EMA model is never toggled out of eval
+        ema_again = ema(x, t, cond).clone()           # replay of its captured forward
+    assert torch.equal(ema_before, ema_again)
+    before = evaluate(model)
+    model.train()
+    versions = [p._version for p in model.parameters()]
+    torch.nn.functional.mse_loss(model(x, t, cond), torch.zeros_like(x)).backward()
+    opt.step()
+    torch.cuda.synchronize()
+    assert all(p._version > v for p, v in zip(model.parameters(), versions) if p.grad is not None)
+    after = evaluate(model)
+    with torch.no_grad():
+        ema_after = ema(x, t, cond).clone()
+    for m, got, old in ((model, after, before), (ema, ema_after, ema_before)):
+        torch.manual_seed(0)
+        fresh = Unet(4, cfg).to(dev).eval()
+        fresh.load_state_dict(m.state_dict())
+        with torch.no_grad():
+            want = fresh(x, t, cond)
+        assert not torch.equal(got, old), "forward after the optimizer step still runs on the old weights"
+        assert torch.equal(got, want)

@@ -42,6 +42,34 @@ def _worker(rank, world, port, q):
                 ref += torch.cat([p.grad.flatten() for p in net2.parameters()]) / world
             ok_grad &= torch.allclose(mine, ref, rtol=1e-6, atol=1e-7)
 
+        # a trainable parameter that never receives a gradient (unused branch) must not leave a short count behind:
+        # three backward passes, each must end with every used gradient averaged over ranks
+        class Branchy(torch.nn.Module):
+            def __init__(self):
+                super().__init__()
+                self.used, self.unused = torch.nn.Linear(5, 3), torch.nn.Linear(5, 3)
+
+            def forward(self, x):
+                return self.used(x)
+
+        torch.manual_seed(5)
+        bn = Branchy()
+        dpb = DataParallel(bn)
+        ok_unused = True
+        for it in range(3):
+            xr = [torch.randn(4, 5, generator=torch.Generator().manual_seed(31 * it + r)) for r in range(world)]
+            bn.zero_grad()
+            dpb(xr[rank]).square().sum().backward()
+            ref = torch.zeros_like(bn.used.weight)
+            for r in range(world):
+                b2 = Branchy()
+                b2.load_state_dict(bn.state_dict())
+                b2(xr[r]).square().sum().backward()
+                ref += b2.used.weight.grad / world
+            ok_unused &= torch.allclose(bn.used.weight.grad, ref, rtol=1e-6, atol=1e-7) and bn.unused.weight.grad is None
+            ok_unused &= dpb._pending == 0
+        ok_grad &= ok_unused
+
         # flat-buffer path (what a captured step calls), bucketed and unbucketed give the same mean
         flat = torch.arange(1000, dtype=torch.float32) * (rank + 1)
         a = _mean_(flat.clone(), None, None)

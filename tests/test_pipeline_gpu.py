@@ -153,6 +153,36 @@ def test_condition_cache_sees_in_place_edits_and_weight_updates():
     assert not torch.equal(a, b) and not torch.equal(b, c)
 
 
+def test_condition_cache_is_not_fooled_by_a_recycled_address():
+    """The next batch's condition tensors usually get the ADDRESS of the previous batch's (caching allocator, same shape,
+    _version 0 again — batch_condition_image_generator.py builds them with torch.cat(...).to(device) per batch). The
+    hoisted state and the captured forward must follow the tensors' identity, not their address."""
+    dev = _dev()
+    from sdb200.graphs import SamplingPipeline
+    from scheduler.linear_noise_scheduler import LinearNoiseScheduler
+    fx, model = _small_cond(dev)
+    inp, cfg = fx["inputs"], fx["config"]
+    x, t = inp["x"].to(dev), inp["t"].to(dev)
+    host = cond_of(inp, cfg)
+    pipe = SamplingPipeline(model, LinearNoiseScheduler(1000, 0.00085, 0.012), None)
+    z = {i: torch.zeros_like(x) for i in range(1000)}
+    with torch.no_grad():
+        cond = {k: v.to(dev) for k, v in host.items()}
+        ptrs = {k: v.data_ptr() for k, v in cond.items()}
+        a = model(x, t, cond)
+        pa, _, _ = pipe.sample(x, cond, t_start=999, num_steps=2, z_fn=lambda i: z[i], decode=False)
+        del cond
+        cond2 = {k: (v.flip(0) * 0.5).to(dev) for k, v in host.items()}     # same shapes, other contents
+        recycled = all(cond2[k].data_ptr() == ptrs[k] for k in cond2)
+        b = model(x, t, cond2)
+        pb, _, _ = pipe.sample(x, cond2, t_start=999, num_steps=2, z_fn=lambda i: z[i], decode=False)
+        model.invalidate_plan()
+        want = model(x, t, cond2)
+    print("condition tensors re-used the freed addresses:", recycled)
+    assert not torch.equal(a, b) and torch.equal(b, want)
+    assert not torch.equal(pa, pb)
+
+
 @pytest.mark.parametrize("cfg_scale", [1.0, 3.0])
 def test_sampling_pipeline_matches_drop_in_loop(cfg_scale):
     """Device-resident loop (graph, t on device, in-place x update, fused CFG) vs the reference-shaped Python loop
@@ -202,9 +232,17 @@ def test_in_kernel_noise_is_fresh_per_step_under_graph_replay():
     sched = LinearNoiseScheduler(1000, 0.00085, 0.012)
     pipe = SamplingPipeline(model, sched, None)
     x = fx["inputs"]["x"].to(dev)
-    a, _, _ = pipe.sample(x, cond, t_start=999, num_steps=3, decode=False)
-    b, _, _ = pipe.sample(x, cond, t_start=999, num_steps=3, decode=False)
-    assert torch.isfinite(a).all() and torch.equal(a, b)  # same seed, same t sequence -> reproducible
+    a, _, _ = pipe.sample(x, cond, t_start=999, num_steps=3, decode=False, noise_call=7)
+    b, _, _ = pipe.sample(x, cond, t_start=999, num_steps=3, decode=False, noise_call=7)
+    assert torch.isfinite(a).all() and torch.equal(a, b)  # same seed, same call index, same t sequence -> reproducible
+    c, _, _ = pipe.sample(x, cond, t_start=999, num_steps=3, decode=False)
+    d, _, _ = pipe.sample(x, cond, t_start=999, num_steps=3, decode=False)
+    assert not torch.equal(c, d) and not torch.equal(a, c)   # successive calls draw fresh noise trajectories
+    sched.seed = 12345                                        # a changed seed takes effect without a new plan
+    plan_before = pipe._plan
+    e, _, _ = pipe.sample(x, cond, t_start=999, num_steps=3, decode=False, noise_call=7)
+    assert pipe._plan is plan_before and not torch.equal(a, e)
+    sched.seed = 0
     # statistics of the drawn noise: x_{t-1} - mean is sigma*z with z ~ N(0,1); compare two consecutive steps
     P = pipe.plan(x, cond)
     P.xt.copy_(x); P.t.fill_(999); pipe.step(P); x1 = P.xt.clone(); pipe.step(P); x2 = P.xt.clone()

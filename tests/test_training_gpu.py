@@ -146,3 +146,20 @@ def test_parameter_gradients_do_not_share_memory(graphs):
                     p.grad.numel() * p.grad.element_size(), n) for n, p in model.named_parameters())
     for (a, la, na), (b, _, nb) in zip(spans, spans[1:]):
         assert a + la <= b, f"{na} and {nb} gradients overlap"
+
+
+def test_second_in_flight_forward_of_a_captured_step_is_refused():
+    """The captured backward differentiates the activations of the LAST forward replay: loss = f(x1) + f(x2) must raise
+    instead of silently returning f(x2)'s gradients for f(x1)."""
+    dev = _dev()
+    from models.unet_base import Unet
+    from sdb200.runtime import B200Error
+    fx = load_golden("unet_small_uncond")
+    torch.manual_seed(fx["seed"])
+    model = Unet(4, fx["config"]).train().to(dev)
+    x, t = fx["inputs"]["x"].to(dev), fx["inputs"]["t"].to(dev)
+    a = model(x, t)
+    b = model(x * 0.5, t)
+    b.square().mean().backward()          # the latest forward: fine
+    with pytest.raises(B200Error, match="another forward"):
+        a.square().mean().backward()
