@@ -686,6 +686,236 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=
     }
 
 
+# ---------------------------------------------------------------------------------------------- library bar
+def library_bar_leg(args, ucfg, vcfg, dev, steps=10, warmup=3):
+    """The bar this repo has to beat on the same GPU (BASELINE.md §4 "second bar"): the reference's own
+    stock path — PyTorch modules over cuDNN / cuBLAS / SDPA / ATen — restated functionally by oracle/unet_torch.py
+    (pinned to the real reference), run on cuda:0 with none of this repo's kernels. Two regimes:
+      bf16  torch.autocast(bfloat16) around the model call, as train_ddpm_cond_celebhq_multi_gpu.py:281-283,341-362 does
+      fp32  no autocast, as tools/sample_ddpm_text_image_cond.py:79-91 runs (cuDNN convolutions may use TF32, matmuls fp32)
+    Sampling: batch 64, eager per-timestep loop of the reference script (model -> sample_prev_timestep with host-side
+    z and table uploads) + VQVAE decode. Training: batch 16, add_noise -> forward -> MSE -> backward -> clip -> Adam -> EMA.
+    Attention is F.scaled_dot_product_attention (the library's fused kernel), which favours the bar."""
+    from oracle import scheduler_torch as ST
+    from oracle import unet_torch as O
+    from models.unet_cond_base import Unet
+    from models.vqvae import VQVAE
+    O.USE_SDPA = True
+    torch.manual_seed(SEED)
+    usd = {k: v.to(dev) for k, v in Unet(4, ucfg).state_dict().items()}
+    vsd = {k: v.to(dev) for k, v in VQVAE(3, vcfg).state_dict().items()}
+    B = args.batch
+    xt_h, text_h, mask_h = synth_inputs(B, ucfg, 0, pin=False)
+    cond = {"text": text_h.to(dev), "image": mask_h.to(dev)}
+    tb = ST.tables(T_STEPS, 0.00085, 0.012)
+    out = {"what": "reference's stock PyTorch path (cuDNN/cuBLAS/SDPA) on the same GPU, eager, none of this repo's kernels",
+           "torch": torch.__version__, "cudnn_allow_tf32": bool(torch.backends.cudnn.allow_tf32)}
+
+    def sampling(autocast):
+        x = xt_h.to(dev)
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        with torch.no_grad():
+            for k in range(warmup + steps):
+                if k == warmup:
+                    torch.cuda.synchronize()
+                    e0.record()
+                i = T_STEPS - 1 - k
+                with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+                    eps = O.unet_forward(usd, ucfg, x, torch.full((B,), i, device=dev, dtype=torch.long), cond)
+                x, _ = ST.sample_prev_timestep(tb, x, eps.float(), torch.as_tensor(i))
+            e1.record()
+            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+                ims = O.vqvae_decode(vsd, vcfg, x.clamp(-1, 1))
+            e2.record()
+            torch.cuda.synchronize()
+        t_step, t_dec = e0.elapsed_time(e1) / steps / 1e3, e1.elapsed_time(e2) / 1e3
+        return {"value": images_per_s(B, t_step, t_dec), "unit": "images/s", "ms_per_step": 1e3 * t_step,
+                "decode_ms": 1e3 * t_dec, "steps": steps, "batch": B, "finite": bool(torch.isfinite(ims).all().item())}
+
+    out["sampling_bf16_autocast"] = sampling(True)
+    out["sampling_fp32"] = sampling(False)
+
+    if args.train_steps > 0:
+        Bt = args.train_batch
+        leaves = {k: v.clone().requires_grad_(v.dtype.is_floating_point) for k, v in usd.items()}
+        params = [v for v in leaves.values() if v.requires_grad]
+        ema = [p.detach().clone() for p in params]
+        opt = torch.optim.Adam(params, lr=1e-5)
+        x_h, text_t, mask_t = synth_inputs(Bt, ucfg, 0, pin=False)
+        g = torch.Generator().manual_seed(SEED + 5)
+        x0, noise = x_h.to(dev), torch.randn(x_h.shape, generator=g).to(dev)
+        t = torch.randint(0, T_STEPS, (Bt,), generator=g).to(dev)
+        c = {"text": text_t.to(dev), "image": mask_t.to(dev)}
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for k in range(3 + args.train_steps):
+            if k == 3:
+                torch.cuda.synchronize()
+                e0.record()
+            noisy = ST.add_noise(tb, x0, noise, t)
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                pred = O.unet_forward(leaves, ucfg, noisy, t, c)
+                loss = torch.nn.functional.mse_loss(pred, noise)
+            opt.zero_grad(set_to_none=True)
+            loss.backward()
+            torch.nn.utils.clip_grad_norm_(params, 1.0)
+            opt.step()
+            with torch.no_grad():
+                torch._foreach_mul_(ema, 0.999)
+                torch._foreach_add_(ema, params, alpha=0.001)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / args.train_steps
+        out["train_bf16_autocast"] = {"value": Bt / (ms / 1e3), "unit": "samples/s", "ms_per_step": ms, "batch": Bt,
+                                      "steps": args.train_steps, "loss_finite": bool(torch.isfinite(loss).item())}
+        del leaves, params, ema, opt
+    O.USE_SDPA = False
+    del usd, vsd
+    torch.cuda.empty_cache()
+    return out
+
+
+# ---------------------------------------------------------------------------------------------- configs[0]
+def config0_leg(args, dev, cpu_budget_s):
+    """BASELINE.json configs[0] exactly as BASELINE.md §4 words it: the unconditional LDM UNet of config/celebhq.yaml
+    (tools/train_ddpm_vqvae.py:95-107, tools/sample_ddpm_vqvae.py:29-34), batch 4: ONE train step (add_noise -> model ->
+    MSE -> backward -> Adam) + the last 50 timesteps of the sampling loop + one VQVAE decode. GPU: this repo's drop-in
+    modules (bf16 tensor-core arithmetic; the reference runs this config in fp32). CPU: the oracle port on
+    the host cores, timed on a bounded sample (the train step and 3 of the 50 timesteps, decode of 1 of the 4 images),
+    extrapolated as stated."""
+    import numpy as np
+    from models.unet_base import Unet
+    from models.vqvae import VQVAE
+    from scheduler.linear_noise_scheduler import LinearNoiseScheduler
+    g0 = os.path.join(ROOT, "tests", "golden")
+    ucfg = torch.load(os.path.join(g0, "unet_full_uncond.pt"), weights_only=False)["config"]
+    vcfg = torch.load(os.path.join(g0, "vqvae_decode.pt"), weights_only=False)["config"]
+    B, NS = 4, 50
+    torch.manual_seed(SEED)
+    model = Unet(4, ucfg).to(dev)
+    vae = VQVAE(3, vcfg).eval().to(dev)
+    sched = LinearNoiseScheduler(T_STEPS, 0.0015, 0.0195)       # config/celebhq.yaml:9-10
+    opt = torch.optim.Adam(model.parameters(), lr=5e-6)
+    g = torch.Generator().manual_seed(SEED)
+    x0, noise = torch.randn(B, 4, 32, 32, generator=g).to(dev), torch.randn(B, 4, 32, 32, generator=g).to(dev)
+    t = torch.randint(0, T_STEPS, (B,), generator=g).to(dev)
+
+    def job(timed):
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        model.train()
+        ev[0].record()
+        opt.zero_grad()
+        loss = torch.nn.functional.mse_loss(model(sched.add_noise(x0, noise, t), t), noise)
+        loss.backward()
+        opt.step()
+        ev[1].record()
+        model.eval()
+        with torch.no_grad():
+            xt = noise.clone()
+            for i in reversed(range(NS)):
+                xt, _ = sched.sample_prev_timestep(xt, model(xt, torch.as_tensor(i).unsqueeze(0).to(dev)),
+                                                   torch.as_tensor(i))
+            ev[2].record()
+            ims = vae.decode(xt)
+        ev[3].record()
+        torch.cuda.synchronize()
+        return [ev[k].elapsed_time(ev[k + 1]) for k in range(3)], bool(torch.isfinite(ims).all().item() and
+                                                                      torch.isfinite(loss).item())
+
+    job(False)
+    job(False)
+    (ms_train, ms_samp, ms_dec), finite = job(True)
+    gpu_s = (ms_train + ms_samp + ms_dec) / 1e3
+    out = {"workload": "configs[0]: unconditional LDM UNet (config/celebhq.yaml), batch 4: 1 train step + 50 DDPM "
+                       "timesteps + VQVAE decode", "dtype": "bf16 tensor-core arithmetic, fp32 accumulate / scheduler / optimizer",
+           "gpu": {"job_s": gpu_s, "train_step_ms": ms_train, "sampling_50_steps_ms": ms_samp, "decode_ms": ms_dec,
+                   "finite": finite}}
+    del model, vae, opt
+    torch.cuda.empty_cache()
+    if cpu_budget_s > 0:
+        from oracle import scheduler_np as onp
+        from oracle import unet_torch as O
+        torch.set_num_threads(os.cpu_count() or 1)
+        torch.manual_seed(SEED)
+        usd = {k: v.clone().requires_grad_(v.dtype.is_floating_point) for k, v in Unet(4, ucfg).state_dict().items()}
+        vsd = {k: v.clone() for k, v in VQVAE(3, vcfg).state_dict().items()}
+        tb = onp.make_tables(T_STEPS, 0.0015, 0.0195)
+        x0c, nc, tc = x0.cpu(), noise.cpu(), t.cpu()
+        popt = torch.optim.Adam([v for v in usd.values() if v.requires_grad], lr=5e-6)
+        t0 = time.perf_counter()
+        noisy = torch.from_numpy(onp.add_noise(tb, x0c.numpy(), nc.numpy(), tc.numpy()))
+        loss = torch.nn.functional.mse_loss(O.unet_forward(usd, ucfg, noisy, tc), nc)
+        loss.backward()
+        popt.step()
+        cpu_train = time.perf_counter() - t0
+        rng = np.random.default_rng(SEED)
+        xt = nc.clone()
+        t0, done = time.perf_counter(), 0
+        with torch.no_grad():
+            for i in reversed(range(NS)):
+                eps = O.unet_forward(usd, ucfg, xt, torch.full((B,), i, dtype=torch.long))
+                xp, _ = onp.sample_prev_timestep(tb, xt.numpy(), eps.numpy(), i, rng.standard_normal(xt.shape, dtype=np.float32))
+                xt = torch.from_numpy(np.ascontiguousarray(xp))
+                done += 1
+                if done >= 3 and time.perf_counter() - t0 > cpu_budget_s / 2:
+                    break
+            cpu_step = (time.perf_counter() - t0) / done
+            t0 = time.perf_counter()
+            O.vqvae_decode(vsd, vcfg, xt[:1].clamp(-1, 1))
+            cpu_dec = (time.perf_counter() - t0) * B
+        cpu_s = cpu_train + NS * cpu_step + cpu_dec
+        out["cpu"] = {"job_s": cpu_s, "train_step_s": cpu_train, "sampling_step_s": cpu_step, "decode_s": cpu_dec,
+                      "cores": os.cpu_count(), "kind": "port", "dtype": "f32",
+                      "sample": f"the train step, {done} of the 50 timesteps (x50/{done}) and the decode of 1 of the 4 images (x4)"}
+        out["gpu_over_cpu"] = cpu_s / gpu_s
+    return out
+
+
+# ---------------------------------------------------------------------------------------------- HBM-bound kernels
+def hbm_leg(dev, pk):
+    """Achieved bytes/s of the HBM-bound kernels against the measured copy bandwidth: algorithmic bytes /
+    CUDA-event time, at the workload's own size (launch-latency bound) and at a size that cannot sit in L2."""
+    from sdb200 import runtime as rt
+    from scheduler.linear_noise_scheduler import LinearNoiseScheduler
+    sched = LinearNoiseScheduler(T_STEPS, 0.00085, 0.012)
+    out = {}
+
+    def timed(fn, reps):
+        for _ in range(3):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps / 1e3
+
+    for tag, nb, reps in (("batch64", 64, 50), ("batch65536", 65536, 10)):
+        x, n = torch.randn(nb, 4, 32, 32, device=dev), torch.randn(nb, 4, 32, 32, device=dev)
+        t = torch.randint(0, T_STEPS, (nb,), device=dev)
+        s = timed(lambda: sched.add_noise(x, n, t), reps)
+        out[f"add_noise_{tag}"] = {"us": 1e6 * s, "gbps": 49152.0 * nb / s / 1e9, "frac": 49152.0 * nb / s / 1e9 / pk["hbm_gbs"],
+                                   "bytes_per_sample": 49152}
+        s = timed(lambda: sched.sample_prev_timestep(x, n, 500), reps)
+        out[f"prev_step_{tag}"] = {"us": 1e6 * s, "gbps": 65536.0 * nb / s / 1e9, "frac": 65536.0 * nb / s / 1e9 / pk["hbm_gbs"],
+                                   "bytes_per_sample": 65536}
+        del x, n, t
+    from sdb200.optim import FusedAdam
+    p = [torch.randn(118513466, device=dev).requires_grad_()]
+    e = [p[0].detach().clone()]
+    p[0].grad = torch.randn_like(p[0])
+    opt = FusedAdam(p, lr=1e-5, max_grad_norm=1.0, ema_params=e, ema_decay=0.999)
+    s = timed(opt.step, 10)
+    nbytes = 36.0 * p[0].numel() + 4.0 * p[0].numel()        # Adam+EMA 36 B/param + the norm pass's gradient read
+    out["clip_adam_ema_118M"] = {"us": 1e6 * s, "gbps": nbytes / s / 1e9, "frac": nbytes / s / 1e9 / pk["hbm_gbs"],
+                                 "bytes_per_param": 40}
+    out["peak_gbps"] = pk["hbm_gbs"]
+    del p, e, opt
+    torch.cuda.empty_cache()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)

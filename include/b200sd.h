@@ -115,7 +115,7 @@ typedef struct {
 typedef struct {
     int32_t n_src, n_seg;
     b200sd_src srcs[4];
-    b200sd_seg segs[20];
+    b200sd_seg segs[40];
     const void* weight; /* bf16 [n_out, k_total], k_total = 64 * sum(nchunk) */
     int32_t n_out;
     /* output pixel grid and its addressing (element strides; out/residual share geometry, not pointers) */
@@ -138,6 +138,10 @@ typedef struct {
        (b200sd_groupnorm_apply) sums the slots in order. */
     float* stats;
     int32_t stats_p, stats_slot0, stats_ld;
+    /* precise mode: an fp32 output may take its residual and / or its per-image row bias as fp32 too
+       (B200SD_DT_F32; 0 = bf16 as above). With residual == out the call accumulates in place (each thread reads the
+       element it then writes): the second launch of a split-operand product A_hi*[W_hi|W_lo] + A_lo*W_hi. */
+    int32_t residual_dtype, rowbias_dtype;
 } b200sd_igemm_params;
 
 int b200sd_igemm(const b200sd_igemm_params* p, void* stream);
@@ -170,6 +174,19 @@ int b200sd_wgrad_reduce(const float* partial, int splits, int64_t elems, float* 
  * eps inside the sqrt, fp32 arithmetic; y = act((x-mean)*rstd*gamma + beta) written as bf16 [n, hw, ld_y]. */
 int b200sd_groupnorm(const void* x, int64_t ld_x, void* y, int64_t ld_y, const float* gamma, const float* beta,
                      int64_t n, int64_t hw, int c, int groups, float eps, int act, void* stream);
+
+/* Precise mode. nn.GroupNorm (+ activation) of an fp32 NHWC tensor x [n, hw, ld_x], statistics computed here in fp32
+ * (two passes, no E[x^2] - E[x]^2 cancellation), result written as a SPLIT bf16 operand: y [n*hw, ld_y] holds
+ * hi = bf16(v) in columns [0, c) and lo = bf16(v - hi) in columns [lo_off, lo_off + c) — together 16 mantissa bits, the
+ * A operand of the split-operand GEMM (b200sd_igemm called on the hi and on the lo view). lo_off < 0: hi only. */
+int b200sd_groupnorm_split(const float* x, int64_t ld_x, void* y, int64_t ld_y, int32_t lo_off, const float* gamma,
+                           const float* beta, int64_t n, int64_t hw, int c, int groups, float eps, int act,
+                           void* stream);
+/* dst[r, hi_off + j] = hi, dst[r, lo_off + j] = lo of act(src[r, j]) for an fp32 [rows, c] matrix (pitch ld_s): any
+ * fp32 tensor that feeds a GEMM directly in precise mode (block input of the 1x1 shortcut, down / up-sample input,
+ * time embedding, text context). lo_off < 0: hi only (= the autocast cast). */
+int b200sd_split_f32(const float* src, int64_t ld_s, void* dst, int64_t ld_d, int32_t hi_off, int32_t lo_off,
+                     int64_t rows, int32_t c, int act, void* stream);
 
 /* The same normalisation when the producer of x already left partial statistics (b200sd_igemm `stats`): x is read
  * once and written once. Channels [0, c_split) take their statistics from stats0 ([n, p0, ld_s0, 2]) and channels

@@ -39,13 +39,13 @@ class Denoiser(nn.Module):
         wstamp = tuple((p.data_ptr(), p._version) for p in self._cond_params())
         cache = self.__dict__.setdefault("_cond_cache", [])
         for ent in cache:
-            if ent[0] == tuple(x.shape) and ent[2] == wstamp and G.cond_key_matches(ent[1], cond_input):
+            if ent[0] == (tuple(x.shape), E.PARITY_MODE) and ent[2] == wstamp and G.cond_key_matches(ent[1], cond_input):
                 return ent[3]
         st = self.prepare_cond(cond_input, x.shape, x.device)
         if st.ctx is not None:
             st.ctx.persistent = True
         cache[:] = [e for e in cache if G.cond_key_alive(e[1])][-3:]   # conditional + unconditional (CFG) and a little slack
-        cache.append((tuple(x.shape), G.cond_key(cond_input), wstamp, st))
+        cache.append(((tuple(x.shape), E.PARITY_MODE), G.cond_key(cond_input), wstamp, st))
         return st
 
     def forward(self, x, t, cond_input=None):
@@ -86,7 +86,7 @@ class Denoiser(nn.Module):
         st = self._cached_cond(cond_input, x) if self.cond else E.CondState()
         if G.ENABLE_FORWARD_GRAPHS and not torch.is_grad_enabled() and not torch.cuda.is_current_stream_capturing():
             graphs = self.__dict__.setdefault("_graphed", {})
-            key = (tuple(x.shape), tt.numel(), id(st))
+            key = (tuple(x.shape), tt.numel(), id(st), E.PARITY_MODE)
             gf = graphs.get(key)
             if gf is None or not gf.valid(st):
                 if len(graphs) >= 4:

@@ -161,6 +161,18 @@ class UnetCore(Denoiser):
         steps (tools/sample_ddpm_text_image_cond.py:82)."""
         n, c, h, w = x_shape
         st = E.CondState()
+        if E.precise():
+            # precise mode derives its conditioning from the fp32 inputs inside run() (sdb200/precise.py)
+            if self.image_cond:
+                validate_image_conditional_input(cond_input, torch.empty(x_shape, device='meta'))
+            if self.text_cond:
+                assert 'text' in cond_input, \
+                    "Model initialized with text conditioning but cond_input has no text information"
+            if self.class_cond:
+                validate_class_conditional_input(cond_input, torch.empty(x_shape, device='meta'), self.num_classes)
+                st.class_onehot = cond_input['class'].float()
+            st.raw = cond_input
+            return st
         if self.image_cond:
             assert 'image' in cond_input, \
                 "Model initialized with image conditioning but cond_input has no image information"
@@ -194,6 +206,9 @@ class UnetCore(Denoiser):
         noise prediction. Pure kernel enqueues on the current stream (CUDA-graph capturable)."""
         n, c, h, w = x.shape
         dev = x.device
+        if st.raw is not None or (E.precise() and not self.cond):
+            from sdb200 import precise as P
+            return P.unet_run(self, x, tt, st)
         # ---- input assembly: latent (+ cached mask channels) -> NHWC bf16, then conv_in
         if self.image_cond:
             rt.nchw_to_nhwc(x.float(), st.inbuf, 0)

@@ -123,7 +123,11 @@ class VQVAE(nn.Module):
         if torch.is_grad_enabled() and any(p.requires_grad for p in self.post_quant_conv.parameters()) \
                 and z.requires_grad:
             raise rt.B200Error("VQVAE.decode: no backward path (decoder training is out of scope)")
-        a = E.Act.from_nchw(z)
+        if E.precise():
+            from sdb200 import precise as P
+            a = P.PAct.from_nchw(z)
+        else:
+            a = E.Act.from_nchw(z)
         a = E.conv2d(a, self.post_quant_conv)
         a = E.conv2d(a, self.decoder_conv_in)
         for mid in self.decoder_mids:

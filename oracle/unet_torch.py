@@ -52,6 +52,10 @@ def _gn(x, sd, groups):
     return F.group_norm(x, groups, sd["weight"], sd["bias"], 1e-5)
 
 
+USE_SDPA = False   # bench.py's library-bar leg: let torch pick its fused attention (what nn.MultiheadAttention's fast
+                   # path / F.scaled_dot_product_attention run on a GPU) instead of the explicit matmul-softmax-matmul
+
+
 def _mha(sd, q_in, kv_in, heads):
     """nn.MultiheadAttention(batch_first) forward (packed in_proj) or CustomMultiheadAttention (q/k/v_proj) —
     models/blocks.py:128,140; models/multihead_attention.py:41-80. Explicit softmax(QK^T/sqrt(d))V."""
@@ -67,8 +71,11 @@ def _mha(sd, q_in, kv_in, heads):
     q = F.linear(q_in, wq, bq).view(B, Lq, heads, d).transpose(1, 2)
     k = F.linear(kv_in, wk, bk).view(B, Lk, heads, d).transpose(1, 2)
     v = F.linear(kv_in, wv, bv).view(B, Lk, heads, d).transpose(1, 2)
-    p = torch.softmax(q @ k.transpose(-2, -1) / math.sqrt(d), dim=-1)
-    o = (p @ v).transpose(1, 2).reshape(B, Lq, C)
+    if USE_SDPA:
+        o = F.scaled_dot_product_attention(q, k, v).transpose(1, 2).reshape(B, Lq, C)
+    else:
+        p = torch.softmax(q @ k.transpose(-2, -1) / math.sqrt(d), dim=-1)
+        o = (p @ v).transpose(1, 2).reshape(B, Lq, C)
     return F.linear(o, sd["out_proj.weight"], sd["out_proj.bias"])
 
 

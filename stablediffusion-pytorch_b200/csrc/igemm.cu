@@ -31,7 +31,7 @@ namespace b200 {
 constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int IGEMM_THREADS = 320;  // TMA warp, MMA warp, 8 epilogue warps
-constexpr int MAX_SEG = 20;
+constexpr int MAX_SEG = 40;
 constexpr int EPI_THREADS = 256;
 constexpr int PANEL_BYTES = BM * 128;  // 128 rows x 64 bf16
 
@@ -65,6 +65,7 @@ struct alignas(64) IgemmArgs {
     const __nv_bfloat16* residual;
     long long res_sn, res_sy, res_sx;
     int act;
+    int res_f32, rowbias_f32;   // precise mode: fp32 residual / row bias (direct-store epilogue only)
     int vec_ok;    // every optional epilogue operand (and a directly stored output) is 16-byte addressable
     float* stats;  // [on][stats_p][stats_ld][2] partial sums, or null
     int stats_p, stats_slot0, stats_ld;
@@ -160,7 +161,8 @@ __device__ __forceinline__ void epilogue8(const IgemmArgs& args, float (&v)[8], 
         for (int j = 0; j < 8; ++j) v[j] += f[j];
     }
     if (args.rowbias) {
-        load8_bf16(args.rowbias + pn * args.rowbias_ld + col, nv, f);
+        if (args.rowbias_f32) load8_f32(reinterpret_cast<const float*>(args.rowbias) + pn * args.rowbias_ld + col, nv, f);
+        else load8_bf16(args.rowbias + pn * args.rowbias_ld + col, nv, f);
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[j] += f[j];
     }
@@ -402,7 +404,16 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                             v[g][4] += b1.x, v[g][5] += b1.y, v[g][6] += b1.z, v[g][7] += b1.w;
                         }
                     }
-                    if (has_rowbias) {
+                    if (has_rowbias && args.rowbias_f32) {
+                        const float* rp = reinterpret_cast<const float*>(args.rowbias) + pnc * args.rowbias_ld + col0;
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            float f[8];
+                            load8_f32(rp + 8 * g, 8, f);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) v[g][j] += f[j];
+                        }
+                    } else if (has_rowbias) {
                         const uint4* rp = reinterpret_cast<const uint4*>(args.rowbias + pnc * args.rowbias_ld + col0);
 #pragma unroll
                         for (int g = 0; g < 4; ++g) {
@@ -433,7 +444,16 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                             for (int j = 0; j < 8; ++j) v[g][j] *= f[j];
                         }
                     }
-                    if (has_res && !args.tma_res && row_ok) {
+                    if (has_res && args.res_f32 && row_ok) {
+                        // plain loads (not __ldg): with residual == out this launch accumulates in place
+                        const float4* rp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(args.residual) + r_off + col0);
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            const float4 a0 = rp[2 * g], a1 = rp[2 * g + 1];
+                            v[g][0] += a0.x, v[g][1] += a0.y, v[g][2] += a0.z, v[g][3] += a0.w;
+                            v[g][4] += a1.x, v[g][5] += a1.y, v[g][6] += a1.z, v[g][7] += a1.w;
+                        }
+                    } else if (has_res && !args.tma_res && row_ok) {
                         const uint4* rp = reinterpret_cast<const uint4*>(args.residual + r_off + col0);
 #pragma unroll
                         for (int g = 0; g < 4; ++g) {
@@ -510,7 +530,12 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                         }
                         sts128(sp, pack8(v));
                     } else if (row_ok) {
-                        if (args.residual) {
+                        if (args.residual && args.res_f32) {
+                            const float* rp = reinterpret_cast<const float*>(args.residual) + r_off + col;
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                if (j < nv) v[j] += rp[j];
+                        } else if (args.residual) {
                             float f[8];
                             load8_bf16(args.residual + r_off + col, nv, f);
 #pragma unroll
@@ -900,15 +925,20 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
     a.residual = static_cast<const __nv_bfloat16*>(p->residual);
     a.res_sn = p->res_sn, a.res_sy = p->res_sy, a.res_sx = p->res_sx;
     a.act = p->act;
+    a.res_f32 = p->residual && p->residual_dtype == B200SD_DT_F32;
+    a.rowbias_f32 = p->rowbias && p->rowbias_dtype == B200SD_DT_F32;
+    B200_REQUIRE(!a.res_f32 || a.out_f32, "igemm: an fp32 residual needs an fp32 output");
+    B200_REQUIRE(a.res_f32 || !p->residual || p->residual != p->out, "igemm: in-place accumulation needs fp32 residual == out");
 
     {
         auto al = [](const void* ptr, long long bytes_a, long long bytes_b = 16, long long bytes_c = 16) {
             return (reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && bytes_a % 16 == 0 && bytes_b % 16 == 0 && bytes_c % 16 == 0;
         };
         const long long ob = a.out_f32 ? 4 : 2;
-        a.vec_ok = (!p->bias || al(p->bias, 16)) && (!p->rowbias || al(p->rowbias, p->rowbias_ld * 2)) &&
+        const long long rb = a.res_f32 ? 4 : 2, wb = a.rowbias_f32 ? 4 : 2;
+        a.vec_ok = (!p->bias || al(p->bias, 16)) && (!p->rowbias || al(p->rowbias, p->rowbias_ld * wb)) &&
                    (!p->gate || al(p->gate, p->gate_ld * 2)) &&
-                   (!p->residual || al(p->residual, p->res_sn * 2, p->res_sy * 2, p->res_sx * 2)) &&
+                   (!p->residual || al(p->residual, p->res_sn * rb, p->res_sy * rb, p->res_sx * rb)) &&
                    al(p->out, p->out_sn * ob, p->out_sy * ob, p->out_sx * ob);
     }
     // epilogue route: TMA tensor store from a staged bf16 tile when the output is addressable that way

@@ -35,6 +35,29 @@ def _st(stats_t, p_c):
 
 FUSE_GN_STATS = True  # producers leave partial GroupNorm statistics for their consumer (tests flip this)
 
+# "fast": bf16 activations / weights everywhere (what bench.py measures). "precise": fp32 residual stream + split bf16
+# operands (precise.py) — whole-network noise prediction within 1e-2 (measured ~2e-3) of the reference's fp32 output,
+# inference only. Chosen per process (B200SD_PARITY_MODE) or with set_parity_mode().
+import os as _os
+PARITY_MODE = _os.environ.get("B200SD_PARITY_MODE", "fast")
+
+
+def set_parity_mode(mode):
+    global PARITY_MODE
+    if mode not in ("fast", "precise"):
+        raise ValueError("parity mode must be 'fast' or 'precise'")
+    PARITY_MODE = mode
+
+
+def precise():
+    """Precise mode applies to inference; autograd-recording passes always run the fast (bf16) training path."""
+    return PARITY_MODE == "precise" and not torch.is_grad_enabled()
+
+
+def _P():
+    from . import precise as P
+    return P
+
 
 class Act:
     """stats: None, or a list of (fp32 [n, P, ld, 2] partial sums, P, ld, channels) segments covering the channels in
@@ -129,6 +152,8 @@ def _new_stats(n, oh, ow, c, device, phases=1):
 
 def group_norm(a, mod, act=None):
     _require_leaf(mod, (nn.GroupNorm,), "GroupNorm")
+    if not isinstance(a, Act):
+        return _P().gn_split(a, mod, act=act)
     if training():
         segs = a.stats if (a.stats is not None and len(a.stats) <= 2) else [AG.tensor_stats(a.t, a.n, a.hw, a.c) + (a.c,)]
         if a.c % 8 or a.ld % 8 or a.c > 2048:
@@ -149,6 +174,8 @@ def group_norm(a, mod, act=None):
 def conv2d(a, mod, rowbias=None, extra=None, act=None, out=None, c_off=0, out_dtype=torch.bfloat16, stats=True):
     """nn.Conv2d leaf on an Act. `extra` = (Act, 1x1 nn.Conv2d) fuses a second 1x1 convolution of another tensor
     into the same accumulator (ResNet shortcut)."""
+    if not isinstance(a, Act):
+        return _P().conv2d_any(a, mod, out_dtype)
     if hasattr(mod, "forward_act") and extra is None and rowbias is None:
         return mod.forward_act(a)
     _require_leaf(mod, (nn.Conv2d,), "Conv2d")
@@ -334,6 +361,8 @@ def _out_proj(o, mha, a):
 def self_attention(a, norm, mha):
     """x + out_proj(MHA(GN(x))) — blocks.py:122-131. One QKV GEMM, flash attention, out-proj GEMM with the residual
     add in its epilogue."""
+    if not isinstance(a, Act):
+        return _P().self_attention(a, norm, mha)
     C, heads = a.c, mha.num_heads
     xn = group_norm(a, norm)
     if training():
@@ -363,10 +392,10 @@ class Context:
 
 class CondState:
     """The (x, t)-independent part of a conditioned forward; built by Unet.prepare_cond."""
-    __slots__ = ("inbuf", "cin", "ctx", "class_onehot")
+    __slots__ = ("inbuf", "cin", "ctx", "class_onehot", "raw")
 
     def __init__(self):
-        self.inbuf = self.cin = self.ctx = self.class_onehot = None
+        self.inbuf = self.cin = self.ctx = self.class_onehot = self.raw = None
 
 
 HOIST_CONDITIONING = True
@@ -376,6 +405,8 @@ BATCH_TEMB = True  # one GEMM for all per-block time-embedding projections  # te
 def cross_attention(a, norm, mha, ctx_proj_mod, ctx, lk, cache=None):
     """x + out_proj(MHA(q=GN(x), k=v=context_proj(ctx))) — blocks.py:133-145. ctx: bf16 [n*lk, ctx_dim].
     `cache`: a persistent Context whose per-site K/V are reused across forwards."""
+    if not isinstance(a, Act):
+        return _P().cross_attention(a, norm, mha, ctx_proj_mod, ctx, lk, cache=cache)
     C, heads = a.c, mha.num_heads
     xn = group_norm(a, norm)
     if training():
@@ -441,6 +472,8 @@ def resnet(a, first, temb_layer, second, shortcut, temb_act):
     """GN-act-conv3x3 (+ time-embedding row bias) -> GN-act-conv3x3 + 1x1 shortcut of the block input, the shortcut
     fused into the second conv's accumulator — blocks.py:113-119. `first`/`second` are the reference's
     nn.Sequential(GroupNorm, activation, Conv2d); temb_layer is nn.Sequential(activation, Linear) or None."""
+    if not isinstance(a, Act):
+        return _P().resnet(a, first, temb_layer, second, shortcut, temb_act)
     act = _act_name(first[1])
     h = group_norm(a, first[0], act=act)
     rowbias = None
@@ -493,6 +526,8 @@ def prepare_context(context):
 def upsample_concat(a, up_conv, skip):
     """x = up_sample_conv(x); x = cat([x, out_down], dim=1) — blocks.py:461-464. The transposed convolution writes
     straight into the left channel slice of the concat buffer; the skip tensor is copied into the right slice."""
+    if not isinstance(a, Act):
+        return _P().upsample_concat(a, up_conv, skip)
     if up_conv is None and skip is None:
         return a
     h, w = (2 * a.h, 2 * a.w) if up_conv is not None else (a.h, a.w)

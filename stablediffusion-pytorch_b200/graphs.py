@@ -158,7 +158,7 @@ class SamplingPipeline:
         return P
 
     def _key(self, xt, cf_scale_key, inject_z):
-        return (tuple(xt.shape), cf_scale_key, inject_z, _param_stamp(list(self.model.parameters())))
+        return (tuple(xt.shape), cf_scale_key, inject_z, E.PARITY_MODE, _param_stamp(list(self.model.parameters())))
 
     def plan(self, xt, cond_input=None, uncond_input=None, cf_guidance_scale=1.0, inject_z=False):
         """The captured loop body for these shapes / conditions / weights / seed. The condition dicts are matched by the

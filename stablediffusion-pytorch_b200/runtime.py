@@ -17,7 +17,7 @@ _ACT = {None: 0, "none": 0, "silu": 1, "relu": 2}
 
 EXPORTS = [
     "b200sd_last_error", "b200sd_version", "b200sd_launch_count", "b200sd_sched_add_noise",
-    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_attention_lse", "b200sd_attention_bwd", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_rowblocks", "b200sd_groupnorm_bwd", "b200sd_colsum", "b200sd_colsum_blocks", "b200sd_colsum_static", "b200sd_colsum_static_max_floats", "b200sd_vq_blocks", "b200sd_vq_nearest", "b200sd_sampler_step", "b200sd_opt_chunk_size", "b200sd_opt_chunk_elems", "b200sd_grad_sqnorm", "b200sd_adam_ema_step", "b200sd_percent_opt_step",
+    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_attention_lse", "b200sd_attention_bwd", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_groupnorm_split", "b200sd_split_f32", "b200sd_rowblocks", "b200sd_groupnorm_bwd", "b200sd_colsum", "b200sd_colsum_blocks", "b200sd_colsum_static", "b200sd_colsum_static_max_floats", "b200sd_vq_blocks", "b200sd_vq_nearest", "b200sd_sampler_step", "b200sd_opt_chunk_size", "b200sd_opt_chunk_elems", "b200sd_grad_sqnorm", "b200sd_adam_ema_step", "b200sd_percent_opt_step",
     "b200sd_reduce_f32", "b200sd_attention",
     "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16",
     "b200sd_layernorm_mod", "b200sd_layernorm_mod_bwd", "b200sd_rows_per_slot", "b200sd_gate_residual",
@@ -45,7 +45,7 @@ class Seg(C.Structure):
 class IgemmParams(C.Structure):
     _fields_ = [
         ("n_src", C.c_int32), ("n_seg", C.c_int32),
-        ("srcs", Src * 4), ("segs", Seg * 20),
+        ("srcs", Src * 4), ("segs", Seg * 40),
         ("weight", C.c_void_p), ("n_out", C.c_int32),
         ("on", C.c_int32), ("oh", C.c_int32), ("ow", C.c_int32),
         ("out", C.c_void_p), ("out_dtype", C.c_int32),
@@ -55,6 +55,7 @@ class IgemmParams(C.Structure):
         ("residual", C.c_void_p), ("res_sn", C.c_int64), ("res_sy", C.c_int64), ("res_sx", C.c_int64),
         ("act", C.c_int32), ("stats", C.c_void_p),
         ("stats_p", C.c_int32), ("stats_slot0", C.c_int32), ("stats_ld", C.c_int32),
+        ("residual_dtype", C.c_int32), ("rowbias_dtype", C.c_int32),
     ]
 
 
@@ -97,6 +98,8 @@ def lib():
         L.b200sd_groupnorm_apply.argtypes = [vp, i64, vp, i64, vp, i32, i32, i32, vp, i32, i32, vp, vp, i64, i64, i32, i32,
                                              f32, i32, vp]
         L.b200sd_rowblocks.argtypes = [i64, i64, i32]
+        L.b200sd_groupnorm_split.argtypes = [vp, i64, vp, i64, i32, vp, vp, i64, i64, i32, i32, f32, i32, vp]
+        L.b200sd_split_f32.argtypes = [vp, i64, vp, i64, i32, i32, i64, i32, i32, vp]
         L.b200sd_groupnorm_bwd.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, vp, i32, i32, i32, vp, i32, i32, vp, vp, i64,
                                            i64, i32, i32, f32, i32, vp, vp, vp, vp, vp, vp]
         L.b200sd_colsum_blocks.argtypes = [i64, i64, i32]
@@ -315,11 +318,13 @@ def igemm(srcs, segs, weight, n_out, on, oh, ow, out, out_strides, bias=None, ro
     p.bias = _p(bias)
     if rowbias is not None:
         p.rowbias, p.rowbias_ld = rowbias.data_ptr(), rowbias.stride(0)
+        p.rowbias_dtype = DT_F32 if rowbias.dtype == torch.float32 else DT_BF16
     if gate is not None:
         p.gate, p.gate_ld = gate.data_ptr(), gate.stride(0)
     if residual is not None:
         p.residual = residual.data_ptr()
         p.res_sn, p.res_sy, p.res_sx = res_strides
+        p.residual_dtype = DT_F32 if residual.dtype == torch.float32 else DT_BF16
     p.act = _ACT[act] if not isinstance(act, int) else act
     if stats is not None:
         st, sp, s0, sld = stats[:4]
@@ -426,6 +431,35 @@ def groupnorm(x, n, hw, c, groups, gamma, beta, eps=1e-5, act=None, out=None, ld
     check(lib().b200sd_groupnorm(_p(x), ld_x, _p(out), ld_y, _p(gamma), _p(beta), n, hw, c, groups, float(eps),
                                   _ACT[act], stream_ptr()), "groupnorm")
     _pe(tok, "groupnorm", 4.0 * n * hw * c, (n, hw, c))
+    return out
+
+
+def pad8(c):
+    return (c + 7) // 8 * 8
+
+
+def groupnorm_split(x, n, hw, c, groups, gamma, beta, eps=1e-5, act=None):
+    """Precise mode: GroupNorm (+act) of an fp32 [n*hw, ld] tensor -> split bf16 operand [n*hw, 2 * pad8(c)] (hi | lo)."""
+    _cuda(x, torch.float32, "x")
+    cp = pad8(c)
+    out = torch.zeros(n * hw, 2 * cp, device=x.device, dtype=torch.bfloat16) if cp != c else \
+        torch.empty(n * hw, 2 * cp, device=x.device, dtype=torch.bfloat16)
+    check(lib().b200sd_groupnorm_split(_p(x), x.stride(0), _p(out), 2 * cp, cp, _p(gamma), _p(beta), n, hw, c, groups,
+                                        float(eps), _ACT[act], stream_ptr()), "groupnorm_split")
+    return out
+
+
+def split_f32(x, c=None, act=None, lo=True):
+    """Precise mode: fp32 [rows, >= c] -> split bf16 operand [rows, 2 * pad8(c)] (hi | lo), or [rows, pad8(c)] hi only."""
+    _cuda(x, torch.float32, "x")
+    rows = x.shape[0]
+    c = x.shape[1] if c is None else c
+    cp = pad8(c)
+    width = 2 * cp if lo else cp
+    out = torch.zeros(rows, width, device=x.device, dtype=torch.bfloat16) if cp != c else \
+        torch.empty(rows, width, device=x.device, dtype=torch.bfloat16)
+    check(lib().b200sd_split_f32(_p(x), x.stride(0), _p(out), width, 0, cp if lo else -1, rows, c, _ACT[act],
+                                  stream_ptr()), "split_f32")
     return out
 
 

@@ -27,10 +27,10 @@ def test_param_struct_layout_matches_header(rt):
     """ctypes mirror of b200sd_igemm_params must have the C layout (sizes from the header's field list)."""
     assert ctypes.sizeof(rt.Src) == 8 + 16 + 24
     assert ctypes.sizeof(rt.Seg) == 20
-    # 8 (n_src,n_seg) + 4*48 + 20*20 + 8 + 4 + 12 (+pad) ...: just check alignment-sensitive offsets
+    # 8 (n_src,n_seg) + 4*48 + 40*20 + 8 + 4 + 12 (+pad) ...: just check alignment-sensitive offsets
     assert rt.IgemmParams.srcs.offset == 8
     assert rt.IgemmParams.segs.offset == 8 + 4 * 48
-    assert rt.IgemmParams.weight.offset == 8 + 4 * 48 + 20 * 20
+    assert rt.IgemmParams.weight.offset == 8 + 4 * 48 + 40 * 20
     assert rt.IgemmParams.weight.offset % 8 == 0
 
 

@@ -66,3 +66,35 @@ def test_sharded_sampling_equals_single_device_sampling():
         shard = SamplingPipeline(model, sched, None)
         xs, x0s, _ = shard.sample(x[lo:hi].contiguous(), c, t_start=3, z_fn=lambda i: zs[i][lo:hi].contiguous())
         assert torch.equal(xs, xf[lo:hi]) and torch.equal(x0s, x0f[lo:hi])
+
+
+def test_batch64_noise_prediction_vs_cpu_oracle_on_three_of_the_samples():
+    """The batch-64 workload itself against the oracle (not only against itself): samples 0, 31 and 63 of the bench's
+    batch, each computed by the fp32 CPU oracle alone and compared with its row of the batch-64 GPU result — in the fast
+    mode (gate: the whole-network cap of tests/test_parity_gpu.py) and in the precise mode (gate: north_star's 1e-2)."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import sys
+    import os
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from util import l2err, relerr
+    from oracle import unet_torch as O
+    from sdb200 import engine as E
+    dev = torch.device("cuda:0")
+    cfg, model = _full(dev)
+    x, cond = _inputs(cfg, 64, dev)
+    t = torch.randint(0, 1000, (64,), generator=torch.Generator().manual_seed(3)).to(dev)
+    pick = [0, 31, 63]
+    sd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+    with torch.no_grad():
+        ref = O.unet_forward(sd, cfg, x[pick].cpu(), t[pick].cpu(), {k: v[pick].cpu() for k, v in cond.items()})
+        fast = model(x, t, cond)[pick].cpu()
+        E.set_parity_mode("precise")
+        try:
+            prec = model(x, t, cond)[pick].cpu()
+        finally:
+            E.set_parity_mode("fast")
+    ef, lf, ep, lp = relerr(fast, ref), l2err(fast, ref), relerr(prec, ref), l2err(prec, ref)
+    print(f"batch 64 vs oracle on samples {pick}: fast max-norm {ef:.3e} L2 {lf:.3e}; precise max-norm {ep:.3e} L2 {lp:.3e}")
+    assert ef <= 2.5e-2 and lf <= 2.5e-2
+    assert ep <= 1e-2 and lp <= 1e-2
