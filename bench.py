@@ -185,11 +185,16 @@ def run_reference(args):
     if rank != 0:
         return
     ucfg, vcfg = load_cfg()
-    r = cpu_reference_run(ucfg, vcfg, args.steps, min(args.warmup, 1), budget_s=args.cpu_budget, cfg_scale=args.cfg)
+    sb = min(args.cpu_sample, args.batch)
+    r2 = cpu_reference_run(ucfg, vcfg, 2, 1, budget_s=args.cpu_budget / 4, cfg_scale=args.cfg, sample_batch=2)
+    r = cpu_reference_run(ucfg, vcfg, args.steps, min(args.warmup, 1), budget_s=args.cpu_budget, cfg_scale=args.cfg,
+                          sample_batch=sb)
     ips = images_per_s(1, r["t_step_img"], r["t_dec_img"])
     sample = (f"{r['steps_done']} timed DDPM timesteps (of {args.steps} requested; stops at {args.cpu_budget:.0f} s) on "
               f"{r['sample_batch']} of the {args.batch} images + VQVAE decode of 1 image, fp32, oracle port of the "
-              f"reference on {r['cores']} host threads; images/s = 1 / (1000 * s_per_image_step + s_per_image_decode)")
+              f"reference on {r['cores']} host threads; images/s = 1 / (1000 * s_per_image_step + s_per_image_decode); "
+              f"per-image step time {1e3 * r2['t_step_img']:.1f} ms at batch 2 -> {1e3 * r['t_step_img']:.1f} ms at batch "
+              f"{r['sample_batch']}")
     line = {
         "impl": "reference", "metric": "ddpm_sampling_images_per_s", "value": ips, "unit": "images/s",
         "n_gpus": args.gpus, "steps": r["steps_done"], "warmup": min(args.warmup, 1),
@@ -372,13 +377,19 @@ def run_ours(args):
             json.dump({"per_launch": [{"kernel": n, "work": w, "us": round(ms * 1e3, 2), "shape": d}
                                       for n, w, ms, d in rows], "summary": kernels}, f)
 
+    parity = None
+    if rank == 0:
+        try:
+            parity = parity_check(dev)
+        except Exception as exc:   # noqa: BLE001 - reported, never fatal for the measurement
+            parity = {"error": f"{type(exc).__name__}: {exc}"[:200]}
     step_flops = B * UNET_GFLOP * 1e9 * (2 if args.cfg > 1 else 1)
     line = {
         "metric": "ddpm_sampling_images_per_s", "value": value, "unit": "images/s", "n_gpus": world, "steps": K,
         "warmup": W, "ms_per_step": 1e3 * t_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16", "data": "synthetic",
         "config": dict(workload_config(args, ucfg), extrapolated=(K != T_STEPS), decode_ms=ms_dec,
-                       cuda_graph=not args.no_graph, outputs_finite=finite),
+                       cuda_graph=not args.no_graph, outputs_finite=finite, parity_mode="fast", parity=parity),
         "step_tflops": step_flops / t_step / 1e12, "step_frac_of_bf16_sustained": step_flops / t_step / 1e12 / pk["tf_sustained"],
         "decode_tflops": B * VQVAE_DECODE_GFLOP * 1e9 / t_dec / 1e12,
         "roofline": roofline, "kernels": kernels,
@@ -389,24 +400,76 @@ def run_ours(args):
         "gpu_launches": launches, "clocks": clk.summary(),
     }
     if rank == 0 and world == 1 and not args.no_cpu:
-        r = cpu_reference_run(ucfg, vcfg, 3, 1, budget_s=args.cpu_budget, cfg_scale=args.cfg)
+        r2 = cpu_reference_run(ucfg, vcfg, 2, 1, budget_s=args.cpu_budget / 4, cfg_scale=args.cfg, sample_batch=2)
+        r = cpu_reference_run(ucfg, vcfg, 3, 1, budget_s=args.cpu_budget, cfg_scale=args.cfg,
+                              sample_batch=min(args.cpu_sample, B))
         ips = images_per_s(1, r["t_step_img"], r["t_dec_img"])
         line["cpu_baseline"] = {
             "value": ips, "unit": "images/s", "cores": r["cores"], "kind": "port",
             "sample": f"{r['steps_done']} DDPM timesteps on {r['sample_batch']} of the {B} images + VQVAE decode of 1 "
-                      f"image, fp32 oracle port on {r['cores']} host threads, extrapolated to 1000 steps per image"}
+                      f"image, fp32 oracle port on {r['cores']} host threads, extrapolated to 1000 steps per image; "
+                      f"per-image step time {1e3 * r2['t_step_img']:.1f} ms at batch 2 -> {1e3 * r['t_step_img']:.1f} ms "
+                      f"at batch {r['sample_batch']}"}
+    del pipe, P, model, vae
+    torch.cuda.empty_cache()
+
+    def leg(name, fn):
+        """A secondary leg: its full record is printed as its own JSON line ({"leg": name, ...}) BEFORE the headline line,
+        the headline keeps a one-line summary; a failing leg is recorded, the headline still prints."""
+        try:
+            rec = fn()
+        except Exception as exc:   # noqa: BLE001
+            rec = {"error": f"{type(exc).__name__}: {exc}"[:400]}
+        if rank == 0:
+            print(json.dumps({"leg": name, "n_gpus": world, **rec}), flush=True)
+        return rec
+
+    def brief(rec, keys=("value", "unit", "ms_per_step", "batch_per_gpu")):
+        if "error" in rec:
+            return {"error": rec["error"][:120]}
+        return {k: (round(rec[k], 3) if isinstance(rec[k], float) else rec[k]) for k in keys if k in rec}
+
     if args.train_steps > 0:
-        del pipe, P, model, vae
-        torch.cuda.empty_cache()
-        try:
-            line["train"] = train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks)
-        except Exception as exc:   # the headline (sampling) line must still be printed
-            line["train"] = {"error": f"{type(exc).__name__}: {exc}"[:400]}
+        tr = leg("train", lambda: train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks))
+        line["train"] = dict(brief(tr), algorithmic_tflops=round(tr.get("algorithmic_tflops", 0.0), 1),
+                             e2e=brief(tr.get("e2e", {}), ("value", "ms_per_step", "h2d_bytes_per_step")))
+        if args.train_sweep and "error" not in tr:
+            sweep = {}
+            for tb in (32, 64, 128):
+                a2 = argparse.Namespace(**vars(args))
+                a2.train_batch, a2.train_steps = tb, max(5, args.train_steps // 2)
+                r = leg(f"train_b{tb}", lambda: train_leg(a2, ucfg, dev, rank, world, barrier, max_over_ranks, e2e=False))
+                sweep[str(tb)] = dict(brief(r, ("value", "ms_per_step")), algorithmic_tflops=round(r.get("algorithmic_tflops", 0.0), 1))
+            line["train"]["batch_sweep"] = sweep
     if args.dit_steps > 0:
-        try:
-            line["dit"] = dit_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, t_dec)
-        except Exception as exc:
-            line["dit"] = {"error": f"{type(exc).__name__}: {exc}"[:400]}
+        dl = leg("dit", lambda: dit_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, t_dec))
+        line["dit"] = {k: brief(v, ("value", "unit", "ms_per_step", "batch_per_gpu", "step_tflops")) for k, v in dl.items()
+                       if isinstance(v, dict)} if "error" not in dl else brief(dl)
+    if rank == 0 and world == 1:
+        if not args.no_hbm:
+            hb = leg("hbm_kernels", lambda: hbm_leg(dev, pk))
+            line["hbm_kernels"] = {k: {"gbps": round(v["gbps"], 1), "frac": round(v["frac"], 3), "us": round(v["us"], 1)}
+                                   for k, v in hb.items() if isinstance(v, dict)} if "error" not in hb else brief(hb)
+        if not args.no_config0:
+            c0 = leg("config0", lambda: config0_leg(args, dev, 0 if args.no_cpu else args.cpu_budget / 2))
+            line["config0"] = {"gpu_job_s": round(c0["gpu"]["job_s"], 4), "cpu_job_s": round(c0.get("cpu", {}).get("job_s", 0.0), 2),
+                               "gpu_over_cpu": round(c0.get("gpu_over_cpu", 0.0), 1)} if "error" not in c0 else brief(c0)
+        if not args.no_library_bar:
+            lb = leg("library_bar", lambda: library_bar_leg(args, ucfg, vcfg, dev))
+            if "error" not in lb:
+                sb16, s32 = lb["sampling_bf16_autocast"], lb["sampling_fp32"]
+                line["library_bar"] = {
+                    "what": "reference's stock PyTorch path (cuDNN/cuBLAS/SDPA, eager) on this GPU",
+                    "sampling_bf16_autocast": {"images_per_s": round(sb16["value"], 3), "ms_per_step": round(sb16["ms_per_step"], 2)},
+                    "sampling_fp32": {"images_per_s": round(s32["value"], 3), "ms_per_step": round(s32["ms_per_step"], 2)},
+                    "ours_over_bar_sampling": round(value / sb16["value"], 2)}
+                if "train_bf16_autocast" in lb and "value" in line.get("train", {}):
+                    tb16 = lb["train_bf16_autocast"]
+                    line["library_bar"]["train_bf16_autocast"] = {"samples_per_s": round(tb16["value"], 1),
+                                                                  "ms_per_step": round(tb16["ms_per_step"], 2)}
+                    line["library_bar"]["ours_over_bar_train"] = round(line["train"]["value"] / tb16["value"], 2)
+            else:
+                line["library_bar"] = brief(lb)
     if rank == 0:
         print(json.dumps(line))
     if world > 1:
@@ -520,7 +583,7 @@ def dit_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, t_dec):
     if args.train_steps <= 0:
         return out
     out["train"] = train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=lambda: fresh(12, ["image"]),
-                             gflop_fwd=DIT12_GFLOP, tag="DiT-12L image-conditioned")
+                             gflop_fwd=DIT12_GFLOP, tag="DiT-12L image-conditioned", batch=args.dit_train_batch)
 
     def cim_model(kind):
         from cim_layers.layers_qn_lsq_adda_cim import Conv2d_lsq_adda_cim, Linear_lsq_adda_cim, gen_weight_split_dict
@@ -579,7 +642,7 @@ def dit_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, t_dec):
 
 
 def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=None, gflop_fwd=None, tag="unet",
-              optimizer=None):
+              optimizer=None, e2e=True, batch=None):
     """BASELINE.json configs[2]: data-parallel training of the same conditioned UNet as
     train_ddpm_cond_celebhq_multi_gpu.py:341-378 does it — add_noise, bf16-autocast forward, MSE, backward (DDP's
     bucketed NCCL all-reduce overlapped with it when world > 1), clip_grad_norm_(1.0), Adam, EMA — per-GPU batch 16
@@ -592,7 +655,7 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=
     from sdb200 import runtime as rt
     from models.unet_cond_base import Unet
     from scheduler.linear_noise_scheduler import LinearNoiseScheduler
-    B, K, W = args.train_batch, args.train_steps, 3
+    B, K, W = (batch or args.train_batch), args.train_steps, 3
     torch.manual_seed(SEED)
     model = (make_model() if make_model is not None else Unet(4, ucfg)).train().to(dev)
     gflop_fwd = UNET_GFLOP if gflop_fwd is None else gflop_fwd
@@ -648,10 +711,13 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=
         if not from_host:
             return ((res["x"], res["text"], res["mask"], res["noise"], res["t"]) for _ in range(k))
         from sdb200.data import DevicePrefetcher
-        return DevicePrefetcher(((x_h, text_h, mask_h, noise_h, t_h) for _ in range(k)), dev)
+        # the mask travels under its dict key so that the prefetcher can pre-select the 32x32 pixels the model reads
+        gen = ((x_h, text_h, {"image": mask_h}, noise_h, t_h) for _ in range(k))
+        pf = DevicePrefetcher(gen, dev, shrink={"image": (32, 32)} if not args.full_mask_upload else None)
+        return ((x, tx, m["image"], nz, tt) for x, tx, m, nz, tt in pf)
 
     out = {}
-    for name, from_host in (("value", False), ("e2e", True)):
+    for name, from_host in ((("value", False), ("e2e", True)) if e2e else (("value", False),)):
         for b in batches(W, from_host):
             step(b, from_host)
         l0 = rt.launch_count()
@@ -664,7 +730,8 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=
         barrier()
         (ms,) = max_over_ranks([e0.elapsed_time(e1)])
         out[name] = (world * B * K / (ms / 1e3), ms / K, rt.launch_count() - l0, float(last))
-    h2d = (x_h.numel() + text_h.numel() + mask_h.numel() + noise_h.numel()) * 4 + t_h.numel() * 8
+    mask_up = mask_h.numel() if args.full_mask_upload else mask_h.shape[0] * mask_h.shape[1] * 32 * 32
+    h2d = (x_h.numel() + text_h.numel() + mask_up + noise_h.numel()) * 4 + t_h.numel() * 8
     ema_params = list(ema.parameters())
     del net, model, opt
     return {
@@ -681,9 +748,37 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=
             "sdb200.parallel.DataParallel: in-place NCCL AVG all-reduces of 64 MB slices of the flat fp32 gradient "
             "buffer, captured inside the backward graph on a side stream as each bucket's last gradient is produced"),
         "loss_finite": bool(out["value"][3] == out["value"][3]),
-        "e2e": {"value": out["e2e"][0], "unit": "samples/s", "ms_per_step": out["e2e"][1], "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": 4},
+        "e2e": None if not e2e else {"value": out["e2e"][0], "unit": "samples/s", "ms_per_step": out["e2e"][1],
+                                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
     }
+
+
+def parity_check(dev):
+    """Measured error of both parity modes on the committed full-config golden fixture (the REFERENCE's fp32 output of
+    the conditioned UNet, tests/golden/unet_full_cond.pt): what `config.parity_mode` costs in accuracy."""
+    from sdb200 import engine as E
+    from models.unet_cond_base import Unet
+    fx = torch.load(os.path.join(ROOT, "tests", "golden", "unet_full_cond.pt"), weights_only=False)
+    torch.manual_seed(fx["seed"])
+    m = Unet(4, fx["config"]).eval().to(dev)
+    inp = fx["inputs"]
+    ch = fx["config"]["condition_config"]["image_condition_config"]["image_condition_input_channels"]
+    mask = torch.nn.functional.one_hot(inp["mask_classes"].long(), ch + 1)[..., 1:].permute(0, 3, 1, 2).float().contiguous()
+    cond = {"text": inp["text"].to(dev), "image": mask.to(dev)}
+    out = {"fixture": "tests/golden/unet_full_cond.pt (reference fp32 output)", "bound": 1e-2,
+           "reference_bf16_autocast": round(float(fx["ref_bf16_autocast_relerr"]), 5)}
+    ref = fx["output"].float()
+    for mode in ("fast", "precise"):
+        E.set_parity_mode(mode)
+        try:
+            with torch.no_grad():
+                y = m(inp["x"].to(dev), inp["t"].to(dev), cond).cpu()
+        finally:
+            E.set_parity_mode("fast")
+        out[mode] = {"max_norm": round(float((y - ref).abs().max() / ref.abs().max()), 5),
+                     "rel_l2": round(float((y - ref).norm() / ref.norm()), 5)}
+    del m
+    return out
 
 
 # ---------------------------------------------------------------------------------------------- library bar
@@ -790,8 +885,10 @@ def config0_leg(args, dev, cpu_budget_s):
     ucfg = torch.load(os.path.join(g0, "unet_full_uncond.pt"), weights_only=False)["config"]
     vcfg = torch.load(os.path.join(g0, "vqvae_decode.pt"), weights_only=False)["config"]
     B, NS = 4, 50
+    import copy
     torch.manual_seed(SEED)
-    model = Unet(4, ucfg).to(dev)
+    model = Unet(4, ucfg).train().to(dev)        # tools/train_ddpm_vqvae.py's process
+    sampler = copy.deepcopy(model).eval()        # tools/sample_ddpm_vqvae.py's process (loads the checkpoint, eval mode)
     vae = VQVAE(3, vcfg).eval().to(dev)
     sched = LinearNoiseScheduler(T_STEPS, 0.0015, 0.0195)       # config/celebhq.yaml:9-10
     opt = torch.optim.Adam(model.parameters(), lr=5e-6)
@@ -801,18 +898,16 @@ def config0_leg(args, dev, cpu_budget_s):
 
     def job(timed):
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
-        model.train()
         ev[0].record()
         opt.zero_grad()
         loss = torch.nn.functional.mse_loss(model(sched.add_noise(x0, noise, t), t), noise)
         loss.backward()
         opt.step()
         ev[1].record()
-        model.eval()
         with torch.no_grad():
             xt = noise.clone()
             for i in reversed(range(NS)):
-                xt, _ = sched.sample_prev_timestep(xt, model(xt, torch.as_tensor(i).unsqueeze(0).to(dev)),
+                xt, _ = sched.sample_prev_timestep(xt, sampler(xt, torch.as_tensor(i).unsqueeze(0).to(dev)),
                                                    torch.as_tensor(i))
             ev[2].record()
             ims = vae.decode(xt)
@@ -829,7 +924,7 @@ def config0_leg(args, dev, cpu_budget_s):
                        "timesteps + VQVAE decode", "dtype": "bf16 tensor-core arithmetic, fp32 accumulate / scheduler / optimizer",
            "gpu": {"job_s": gpu_s, "train_step_ms": ms_train, "sampling_50_steps_ms": ms_samp, "decode_ms": ms_dec,
                    "finite": finite}}
-    del model, vae, opt
+    del model, sampler, vae, opt
     torch.cuda.empty_cache()
     if cpu_budget_s > 0:
         from oracle import scheduler_np as onp
@@ -936,6 +1031,15 @@ def main():
                     help="optimizer side of the training legs: sdb200.optim.FusedAdam or torch Adam + clip + EMA")
     ap.add_argument("--train-ddp", choices=["ours", "torch"], default="ours",
                     help="N>1 gradient mean: sdb200.parallel.DataParallel (flat buffer) or torch DistributedDataParallel")
+    ap.add_argument("--dit-train-batch", type=int, default=28,
+                    help="per-GPU batch of the DiT-12L training leg (Model_DiT_12L_config.py:83)")
+    ap.add_argument("--full-mask-upload", action="store_true",
+                    help="training e2e legs upload the whole (B,18,512,512) mask as the reference loop does")
+    ap.add_argument("--cpu-sample", type=int, default=8, help="images per step of the CPU legs (of the 64)")
+    ap.add_argument("--train-sweep", action="store_true", help="also time the UNet training step at batch 32 / 64 / 128")
+    ap.add_argument("--no-hbm", action="store_true", help="skip the HBM-bound kernel leg")
+    ap.add_argument("--no-config0", action="store_true", help="skip the configs[0] leg")
+    ap.add_argument("--no-library-bar", action="store_true", help="skip the reference-on-this-GPU leg")
     ap.add_argument("--dump", default="", help="write the per-launch kernel timing of one eager step to this JSON file")
     args = ap.parse_args()
     if args.impl == "reference":

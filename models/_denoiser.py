@@ -83,7 +83,9 @@ class Denoiser(nn.Module):
         return tg(x, tt, cond_t)
 
     def _forward_eager(self, x, tt, cond_input):
-        st = self._cached_cond(cond_input, x) if self.cond else E.CondState()
+        # an unconditional model has ONE (empty) condition state: a fresh object per call would change the captured
+        # forward's key on every call and re-capture the graph on every timestep of tools/sample_ddpm_vqvae.py's loop
+        st = self._cached_cond(cond_input, x) if self.cond else self.__dict__.setdefault("_no_cond", E.CondState())
         if G.ENABLE_FORWARD_GRAPHS and not torch.is_grad_enabled() and not torch.cuda.is_current_stream_capturing():
             graphs = self.__dict__.setdefault("_graphed", {})
             key = (tuple(x.shape), tt.numel(), id(st), E.PARITY_MODE)

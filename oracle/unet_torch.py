@@ -20,7 +20,7 @@ import torch.nn.functional as F
 def time_embedding(t, dim):
     """get_time_embedding — models/blocks.py:5-24."""
     half = dim // 2
-    factor = 10000 ** (torch.arange(0, half, dtype=torch.float32) / half)
+    factor = 10000 ** (torch.arange(0, half, dtype=torch.float32, device=t.device) / half)
     e = t.reshape(-1)[:, None].repeat(1, half) / factor
     return torch.cat([torch.sin(e), torch.cos(e)], dim=-1)
 

@@ -928,7 +928,6 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
     a.res_f32 = p->residual && p->residual_dtype == B200SD_DT_F32;
     a.rowbias_f32 = p->rowbias && p->rowbias_dtype == B200SD_DT_F32;
     B200_REQUIRE(!a.res_f32 || a.out_f32, "igemm: an fp32 residual needs an fp32 output");
-    B200_REQUIRE(a.res_f32 || !p->residual || p->residual != p->out, "igemm: in-place accumulation needs fp32 residual == out");
 
     {
         auto al = [](const void* ptr, long long bytes_a, long long bytes_b = 16, long long bytes_c = 16) {

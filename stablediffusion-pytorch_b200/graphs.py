@@ -18,26 +18,40 @@ ENABLE_FORWARD_GRAPHS = True
 ENABLE_TRAIN_GRAPHS = True   # forward AND backward of a training step replay captured graphs (see TrainGraph)
 
 
+import contextlib
+import gc
+
+
+@contextlib.contextmanager
+def quiesced_capture():
+    """Region in which a stream capture is safe from THIS process's own garbage. Root cause of the "capture invalidated"
+    failures seen in long sequences (round 1: the batch-32 sampling capture inside a full test run; round 2: the DiT leg of
+    bench.py after the training legs): captured graphs of earlier models sit in reference cycles (TrainGraph <-> autograd
+    Function <-> model.__dict__), so they are freed by Python's CYCLIC collector — at whatever allocation happens to
+    trigger it, including one in the middle of a later capture. Destroying a CUDAGraph releases its private memory pool
+    (cudaFree), and a cudaFree while a stream is capturing invalidates the capture. So: collect before the capture, let
+    the device settle, and keep the cyclic collector off until the capture has ended."""
+    gc.collect()
+    torch.cuda.synchronize()
+    was = gc.isenabled()
+    gc.disable()
+    try:
+        yield
+    finally:
+        if was:
+            gc.enable()
+
+
 def _capture_inference(body):
     """Capture `body()` (no autograd) into a fresh CUDA graph -> (graph, body's result, library launches captured).
-    `thread_local` error mode: a CUDA call another thread of the process happens to make (allocator housekeeping,
-    event queries) must not invalidate this thread's capture; one retry after a collect if a capture is invalidated
-    anyway — it holds no state besides the graph, so capturing again is safe."""
-    import gc
-    for attempt in (0, 1):
-        graph = torch.cuda.CUDAGraph()
-        before = rt.launch_count()
-        try:
-            with torch.cuda.graph(graph, capture_error_mode="thread_local"), torch.no_grad():
-                out = body()
-            return graph, out, rt.launch_count() - before
-        except Exception as exc:   # noqa: BLE001 - re-raised unless it is a capture invalidation on the first attempt
-            if attempt == 1 or "capture" not in (str(exc) + str(exc.__context__ or "")):
-                raise
-            del graph
-            torch.cuda.synchronize()
-            gc.collect()
-    raise AssertionError("unreachable")
+    `thread_local` error mode: a CUDA call another thread of the process makes (bench.py's clock sampler thread, a
+    DataLoader's pin-memory thread) must not invalidate this thread's capture."""
+    graph = torch.cuda.CUDAGraph()
+    before = rt.launch_count()
+    with quiesced_capture():
+        with torch.cuda.graph(graph, capture_error_mode="thread_local"), torch.no_grad():
+            out = body()
+    return graph, out, rt.launch_count() - before
 
 
 def as_nchw(out):
@@ -433,13 +447,13 @@ class TrainGraph:
             pool = torch.cuda.graph_pool_handle()
             self.fwd_graph, self.bwd_graph = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
             before = rt.launch_count()
-            with torch.cuda.graph(self.fwd_graph, pool=pool):
+            with quiesced_capture(), torch.cuda.graph(self.fwd_graph, pool=pool, capture_error_mode="thread_local"):
                 self.out = forward()
             self.fwd_launches = rt.launch_count() - before
             self.gout = torch.empty_like(self.out)
             before = rt.launch_count()
             red = _BucketReducer(self, dev) if self.overlap is not None and self._fired else None
-            with torch.cuda.graph(self.bwd_graph, pool=pool):
+            with quiesced_capture(), torch.cuda.graph(self.bwd_graph, pool=pool, capture_error_mode="thread_local"):
                 if red is not None:
                     red.arm()
                 grads = list(torch.autograd.grad((self.out,), wrt, (self.gout,), allow_unused=True))

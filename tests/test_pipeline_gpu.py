@@ -247,3 +247,22 @@ def test_in_kernel_noise_is_fresh_per_step_under_graph_replay():
     P = pipe.plan(x, cond)
     P.xt.copy_(x); P.t.fill_(999); pipe.step(P); x1 = P.xt.clone(); pipe.step(P); x2 = P.xt.clone()
     assert not torch.equal(x1 - x, x2 - x1)
+
+
+def test_unconditional_drop_in_loop_replays_one_captured_forward():
+    """tools/sample_ddpm_vqvae.py:29-34 calls model(xt, t) once per timestep: after the first call every step must be a
+    replay of the same captured forward (a regression re-captured the graph on every call of an unconditional model)."""
+    dev = _dev()
+    from models.unet_base import Unet
+    fx = load_golden("unet_small_uncond")
+    torch.manual_seed(fx["seed"])
+    model = Unet(4, fx["config"]).eval().to(dev)
+    x = fx["inputs"]["x"].to(dev)
+    with torch.no_grad():
+        model(x, torch.as_tensor(9).unsqueeze(0).to(dev))
+        graphs = dict(model.__dict__["_graphed"])
+        assert len(graphs) == 1
+        for i in reversed(range(9)):
+            model(x, torch.as_tensor(i).unsqueeze(0).to(dev))
+    after = model.__dict__["_graphed"]
+    assert len(after) == 1 and all(after[k] is graphs[k] for k in graphs)
