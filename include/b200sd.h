@@ -243,6 +243,15 @@ int b200sd_attention(const void* q, int64_t ld_q, const void* k, int64_t ld_k, c
                      void* out, int64_t ld_o, int64_t batch, int heads, int lq, int lk, int d, float scale,
                      void* stream);
 
+/* The same product on the tcgen05 / TMEM / TMA kernel (csrc/attention_tc.cu: S = Q K^T and O = P V as tcgen05.mma with
+ * TMEM accumulators, Q / K / V tiles by TMA with the head padding done by out-of-bounds zero fill, one softmax thread per
+ * query row). b200sd_attention picks it by shape (head dim >= 32, at least 128 queries and keys); this entry point runs
+ * it for any head dim that is a multiple of 8 in [8, 64]. lse: optional fp32 [batch, heads, lq] (log2 domain) or NULL.
+ * Needs ld_o % 8 == 0, a 16-byte aligned out and scale > 0: B200SD_ERR_UNSUPPORTED otherwise. */
+int b200sd_attention_tc(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v, void* out,
+                        int64_t ld_o, float* lse, int64_t batch, int heads, int lq, int lk, int d, float scale,
+                        void* stream);
+
 /* Training variants. b200sd_attention_lse also writes lse: fp32 [batch, heads, lq], the log2-domain log-sum-exp of the
  * scaled scores. b200sd_attention_bwd recomputes the scores tile by tile from q, k, v and lse and returns dq / dk / dv
  * (bf16, same layout as q / k / v); o and d_o are the forward output and its gradient; dvec is fp32 scratch

@@ -15,6 +15,7 @@
 #include "host.h"
 #include <cuda_bf16.h>
 #include <type_traits>
+#include <stdlib.h>
 
 namespace b200 {
 
@@ -805,6 +806,12 @@ static int attention_bwd_d8(const void* q, int64_t ld_q, const void* k, int64_t 
 
 using namespace b200;
 
+namespace b200 {
+int attention_tc(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v, void* out,
+                 int64_t ld_o, int64_t batch, int heads, int lq, int lk, int d, float scale, float* lse,
+                 cudaStream_t st);   // attention_tc.cu; > 0: not taken
+}
+
 static int attention_fwd(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v,
                          void* out, int64_t ld_o, int64_t batch, int heads, int lq, int lk, int d, float scale,
                          float* lse, void* stream) {
@@ -821,6 +828,19 @@ static int attention_fwd(const void* q, int64_t ld_q, const void* k, int64_t ld_
                  "attention: pointers unaligned");
     if (batch == 0) return B200SD_OK;
     cudaStream_t st = as_stream(stream);
+    // tcgen05 / TMEM kernel (attention_tc.cu) for query counts that fill its 128-row tiles; B200SD_ATTN_TC=0 switches it
+    // off, B200SD_ATTN_TC_MINLQ moves the threshold (tuning aids)
+    // measured on B200 (profiles/r2c_kernel_bench_attention.txt): it wins where the head dim gives the tensor pipe real
+    // work (d >= 32: 148 vs 333 us at L = 1024, d = 64; 45 vs 49 us at L = 256, d = 32) and loses at d = 8 / 16 / 24,
+    // where both kernels are bound by the exponentials and the mma.sync kernel keeps P in registers
+    static const int tc_mode = [] {
+        const char* on = getenv("B200SD_ATTN_TC");   // 0: never, 1: whenever it applies, default: by shape
+        return on ? (on[0] == '0' ? 0 : 1) : 2;
+    }();
+    if (tc_mode == 1 || (tc_mode == 2 && d >= 32 && lq >= 128 && lk >= 128)) {
+        const int rc = attention_tc(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, d, scale, lse, st);
+        if (rc <= 0) return rc;
+    }
     if (resident_smem(d / 8, lk) <= 110 * 1024) {  // two CTAs per SM still fit
         switch (d / 8) {
             case 1: return launch_resident<1>(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, scale, lse, st);
@@ -850,6 +870,24 @@ extern "C" int b200sd_attention(const void* q, int64_t ld_q, const void* k, int6
                                 void* out, int64_t ld_o, int64_t batch, int heads, int lq, int lk, int d, float scale,
                                 void* stream) {
     return attention_fwd(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, d, scale, nullptr, stream);
+}
+
+/* The tcgen05 / TMEM / TMA kernel (csrc/attention_tc.cu) explicitly, for any shape it supports. */
+extern "C" int b200sd_attention_tc(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v, int64_t ld_v,
+                                   void* out, int64_t ld_o, float* lse, int64_t batch, int heads, int lq, int lk, int d,
+                                   float scale, void* stream) {
+    B200_REQUIRE(q && k && v && out, "attention_tc: null pointer");
+    B200_REQUIRE(batch >= 0 && heads >= 1 && lq >= 1 && lk >= 1 && heads <= 65535, "attention_tc: bad sizes");
+    B200_REQUIRE(((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(k) | reinterpret_cast<uintptr_t>(v)) & 15) == 0,
+                 "attention_tc: pointers unaligned");
+    if (batch == 0) return B200SD_OK;
+    const int rc = attention_tc(q, ld_q, k, ld_k, v, ld_v, out, ld_o, batch, heads, lq, lk, d, scale, lse, as_stream(stream));
+    if (rc > 0) {
+        set_error("attention_tc: head dim %d / pitches (%lld, %lld, %lld, %lld) / scale %g not supported", d,
+                  (long long)ld_q, (long long)ld_k, (long long)ld_v, (long long)ld_o, scale);
+        return B200SD_ERR_UNSUPPORTED;
+    }
+    return rc;
 }
 
 extern "C" int b200sd_attention_lse(const void* q, int64_t ld_q, const void* k, int64_t ld_k, const void* v,

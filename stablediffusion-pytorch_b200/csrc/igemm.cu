@@ -780,6 +780,12 @@ static int encode_map(CUtensorMap* m, const void* base, int rank, const uint64_t
     return B200SD_OK;
 }
 
+// bf16, 128-byte swizzle, zero fill out of bounds: shared with csrc/attention_tc.cu
+int encode_tma_map(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_b,
+                   const uint32_t* box) {
+    return encode_map(m, base, rank, dims, strides_b, box);
+}
+
 // (columns, ow, oh, on) view of a pixel-strided bf16 tensor for the epilogue's TMA store / residual load
 static bool pixel_view_ok(const void* base, long long sn, long long sy, long long sx) {
     if (reinterpret_cast<uintptr_t>(base) & 15) return false;

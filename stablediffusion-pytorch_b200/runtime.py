@@ -17,7 +17,7 @@ _ACT = {None: 0, "none": 0, "silu": 1, "relu": 2}
 
 EXPORTS = [
     "b200sd_last_error", "b200sd_version", "b200sd_launch_count", "b200sd_sched_add_noise",
-    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_attention_lse", "b200sd_attention_bwd", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_groupnorm_split", "b200sd_split_f32", "b200sd_rowblocks", "b200sd_groupnorm_bwd", "b200sd_colsum", "b200sd_colsum_blocks", "b200sd_colsum_static", "b200sd_colsum_static_max_floats", "b200sd_vq_blocks", "b200sd_vq_nearest", "b200sd_sampler_step", "b200sd_opt_chunk_size", "b200sd_opt_chunk_elems", "b200sd_grad_sqnorm", "b200sd_adam_ema_step", "b200sd_percent_opt_step",
+    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_attention_lse", "b200sd_attention_tc", "b200sd_attention_bwd", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_groupnorm_split", "b200sd_split_f32", "b200sd_rowblocks", "b200sd_groupnorm_bwd", "b200sd_colsum", "b200sd_colsum_blocks", "b200sd_colsum_static", "b200sd_colsum_static_max_floats", "b200sd_vq_blocks", "b200sd_vq_nearest", "b200sd_sampler_step", "b200sd_opt_chunk_size", "b200sd_opt_chunk_elems", "b200sd_grad_sqnorm", "b200sd_adam_ema_step", "b200sd_percent_opt_step",
     "b200sd_reduce_f32", "b200sd_attention",
     "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16",
     "b200sd_layernorm_mod", "b200sd_layernorm_mod_bwd", "b200sd_rows_per_slot", "b200sd_gate_residual",
@@ -114,6 +114,7 @@ def lib():
         L.b200sd_colsum_static_max_floats.restype = i64
         L.b200sd_reduce_f32.argtypes = [vp, i64, i64, i64, i64, vp, i32, vp]
         L.b200sd_attention.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, i64, i32, i32, i32, i32, f32, vp]
+        L.b200sd_attention_tc.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, vp, i64, i32, i32, i32, i32, f32, vp]
         L.b200sd_attention_lse.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, vp, i64, i32, i32, i32, i32, f32, vp]
         L.b200sd_attention_bwd.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, vp, i64, vp, vp, vp, i64, vp, i64, vp, i64,
                                            i64, i32, i32, i32, i32, f32, vp]
@@ -545,6 +546,18 @@ def attention(q, k, v, batch, heads, lq, lk, d, scale=None, out=None):
                                   batch, heads, lq, lk, d, float(scale), stream_ptr()), "attention")
     _pe(tok, "attention", 4.0 * batch * heads * lq * lk * d, (batch, heads, lq, lk, d))
     return out
+
+
+def attention_tc(q, k, v, batch, heads, lq, lk, d, scale=None, lse=False):
+    """The tcgen05 / TMEM kernel explicitly (b200sd_attention picks it by shape) -> out, or (out, lse)."""
+    out = torch.empty(batch * lq, heads * d, device=q.device, dtype=torch.bfloat16)
+    ls = torch.empty(batch, heads, lq, device=q.device, dtype=torch.float32) if lse else None
+    scale = d ** -0.5 if scale is None else scale
+    tok = _pb()
+    check(lib().b200sd_attention_tc(_p(q), q.stride(0), _p(k), k.stride(0), _p(v), v.stride(0), _p(out), out.stride(0),
+                                     _p(ls), batch, heads, lq, lk, d, float(scale), stream_ptr()), "attention_tc")
+    _pe(tok, "attention", 4.0 * batch * heads * lq * lk * d, (batch, heads, lq, lk, d))
+    return (out, ls) if lse else out
 
 
 def attention_lse(q, k, v, batch, heads, lq, lk, d, scale=None):

@@ -178,6 +178,31 @@ def test_attention(rt, b, heads, lq, lk, d):
     assert relerr(out.cpu(), ref) < 1e-2
 
 
+@pytest.mark.parametrize("b,heads,lq,lk,d", [(2, 16, 1024, 1024, 24), (3, 16, 256, 256, 32), (2, 16, 64, 64, 48),
+                                             (5, 16, 16, 16, 32), (2, 16, 1024, 77, 8), (2, 16, 256, 77, 16),
+                                             (1, 4, 1024, 1024, 64), (2, 9, 256, 256, 32), (3, 16, 16, 77, 32),
+                                             (2, 16, 1024, 1024, 8), (2, 8, 100, 90, 40), (2, 4, 130, 17, 56),
+                                             (1, 2, 48, 200, 64), (2, 16, 64, 77, 24), (1, 16, 1000, 1000, 16),
+                                             (1, 3, 129, 65, 8), (2, 2, 128, 64, 64)])
+def test_attention_tcgen05_kernel(rt, b, heads, lq, lk, d):
+    """The tcgen05 / TMEM kernel on every shape family of the path (ragged tiles, partial key tiles, every head dim),
+    output and log-sum-exp against fp32 torch on the same bf16 inputs."""
+    dev = _dev()
+    g = torch.Generator().manual_seed(7 * lq + lk + d)
+    C = heads * d
+    q = bf(torch.randn(b * lq, C, generator=g) * 1.5)
+    kv = bf(torch.randn(b * lk, 2 * C, generator=g) * 1.5)
+    kvd = kv.to(dev)
+    out, lse = rt.attention_tc(q.to(dev), kvd[:, :C], kvd[:, C:], b, heads, lq, lk, d, lse=True)
+    torch.cuda.synchronize()
+    sh = lambda t, L: t.float().reshape(b, L, heads, d).transpose(1, 2)
+    qr, kr, vr = sh(q, lq), sh(kv[:, :C], lk), sh(kv[:, C:], lk)
+    ref = F.scaled_dot_product_attention(qr, kr, vr).transpose(1, 2).reshape(b * lq, C)
+    assert relerr(out.cpu(), ref) < 1e-2
+    ref_lse = torch.logsumexp((qr @ kr.transpose(-1, -2)) * d ** -0.5, -1) * 1.4426950408889634
+    assert torch.allclose(lse.cpu(), ref_lse, atol=2e-3, rtol=1e-4)
+
+
 def test_attention_unsupported_head_dim(rt):
     dev = _dev()
     x = torch.zeros(16, 3 * 16 * 3, dtype=torch.bfloat16, device=dev)

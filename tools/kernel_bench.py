@@ -111,9 +111,11 @@ def bench_groupnorm(tm, out):
 
 def bench_attention(tm, out):
     hbm, tf = peaks()
-    for lq, lk, c in [(1024, 1024, 384), (1024, 1024, 128), (256, 256, 512), (256, 256, 256), (64, 64, 768),
-                      (1024, 77, 384), (1024, 77, 128), (256, 77, 512), (16, 16, 512)]:
-        n, heads = 64, 16
+    for lq, lk, c, heads in [(1024, 1024, 384, 16), (1024, 1024, 128, 16), (256, 256, 512, 16), (256, 256, 256, 16),
+                             (64, 64, 768, 16), (1024, 77, 384, 16), (1024, 77, 128, 16), (256, 77, 512, 16),
+                             (256, 77, 256, 16), (16, 16, 512, 16), (1024, 1024, 256, 4), (256, 256, 288, 9),
+                             (256, 77, 288, 9)]:
+        n = 64
         d = c // heads
         q = torch.randn(n * lq, c, device="cuda").to(torch.bfloat16)
         kv = torch.randn(n * lk, 2 * c, device="cuda").to(torch.bfloat16)
