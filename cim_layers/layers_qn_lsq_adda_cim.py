@@ -16,8 +16,11 @@ The backward pass (progressive quant-noise training, Model_DiT_9L_train.py:610-6
 graph: straight-through rounds, the ADC clamp mask, bit-split gradient 1/(slices * 2^lsb), LSQ step-size gradients,
 and the ADC-gain gradient through both the scale and the final division (sdb200/quant.py: AddaFn).
 
-Not available yet: convolutions other than 1x1 (the reference maps k x k kernels through nn.Unfold's (c, ky, kx) row
-order)."""
+k x k convolutions (the leaves of the ReLU-UNet pipeline, Model_Unet_train.py) follow the reference's own route
+(:92-94,198-260): the input is unfolded into rows in nn.Unfold's (c, ky, kx) column order — the K axis the mapped weight
+blocks split — by a CUDA im2col kernel (b200sd_im2col, adjoint b200sd_col2im for the backward pass), and the rows run
+through the same block loop as a Linear layer. Quantising before or after the unfold is the same thing element by
+element; padding taps are code 0; the LSQ gradient scale keeps the ORIGINAL tensor's element count."""
 import math
 
 import torch
@@ -45,6 +48,26 @@ def gen_weight_split_dict(module, weight_block_size):
             if rn > 0 and cn > 0:
                 info[f"{rb}_{cb}"] = {"start_row": r0, "start_col": c0, "row_num": rn, "col_num": cn}
     return info
+
+
+class _Im2colFn(torch.autograd.Function):
+    """NHWC bf16 rows -> nn.Unfold rows ((c, ky, kx) order), backward = nn.Fold (b200sd_col2im)."""
+
+    @staticmethod
+    def forward(ctx, x, geom):
+        n, h, w, c, k, stride, pad = geom
+        ctx.geom = geom
+        ctx.ld = x.shape[1]
+        return rt.im2col(x, n, h, w, c, k, stride, pad)
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g):
+        n, h, w, c, k, stride, pad = ctx.geom
+        dx = rt.col2im(g.contiguous(), n, h, w, c, k, stride, pad)
+        if dx.shape[1] != ctx.ld:
+            dx = torch.nn.functional.pad(dx, (0, ctx.ld - dx.shape[1]))
+        return dx, None
 
 
 class _AddaMixin(_LsqMixin):
@@ -234,11 +257,26 @@ class Conv2d_lsq_adda_cim(nn.Conv2d, _AddaMixin):
     def forward_act(self, a):
         if self.use_FP:
             raise rt.B200Error("Conv2d_lsq_adda_cim: use_FP bypass is served by Conv2d_qn_lsq / nn.Conv2d")
-        if self.kernel_size != (1, 1) or self.stride != (1, 1) or self.padding != (0, 0) or self.groups != 1:
-            raise rt.B200Error("Conv2d_lsq_adda_cim: only 1x1 convolutions have a CUDA path (see module docstring)")
-        y = self._cim_rows(self._rows_in(a.t, a.c), self.weight.reshape(self.out_channels, -1), self.bias,
-                           a.n * a.hw * a.c)
-        return E.Act(y, a.n, a.h, a.w, self.out_channels)
+        k, st, pd = self.kernel_size, self.stride, self.padding
+        if isinstance(pd, str) or self.groups != 1 or self.dilation != (1, 1) or k[0] != k[1] or st[0] != st[1] \
+                or pd[0] != pd[1]:
+            raise rt.B200Error("Conv2d_lsq_adda_cim: square kernels with symmetric stride / padding, groups = 1 only")
+        if self.out_channels % 8:
+            # (the 18 -> 3 mask conv of the DiT is a 1x1: its rows are already the GEMM operand)
+            if k != (1, 1):
+                raise rt.B200Error("Conv2d_lsq_adda_cim: k x k convolutions need out_channels % 8 == 0")
+        if k == (1, 1) and st == (1, 1) and pd == (0, 0):
+            y = self._cim_rows(self._rows_in(a.t, a.c), self.weight.reshape(self.out_channels, -1), self.bias,
+                               a.n * a.hw * a.c)
+            return E.Act(y, a.n, a.h, a.w, self.out_channels)
+        geom = (a.n, a.h, a.w, a.c, k[0], st[0], pd[0])
+        oh, ow = (a.h + 2 * pd[0] - k[0]) // st[0] + 1, (a.w + 2 * pd[0] - k[0]) // st[0] + 1
+        if torch.is_grad_enabled() and a.t.requires_grad:
+            rows = _Im2colFn.apply(a.t, geom)
+        else:
+            rows = rt.im2col(a.t, *geom)
+        y = self._cim_rows(rows, self.weight.reshape(self.out_channels, -1), self.bias, a.n * a.hw * a.c)
+        return E.Act(y, a.n, oh, ow, self.out_channels)
 
     def forward(self, x):
         if not x.is_cuda:

@@ -281,6 +281,16 @@ int b200sd_mask_cond(const float* mask, const float* w, void* dst, int64_t ld_ds
 int b200sd_copy_act(const void* src, int64_t ld_src, void* dst, int64_t ld_dst, int c_off, int64_t rows, int c,
                     int act, void* stream);
 
+/* nn.Unfold(k, padding, stride) of an NHWC bf16 tensor x [n*h*w, ld_x] (c channels) into GEMM rows
+ * rows[(img, oy, ox), ch*k*k + ky*k + kx] = x[img, oy*stride - pad + ky, ox*stride - pad + kx, ch] (0 outside): the
+ * (c, ky, kx) K order of weight.view(Cout, -1), which is the axis the compute-in-memory weight blocks split
+ * (cim_layers/layers_qn_lsq_adda_cim.py:92-94,198-215). Columns beyond c*k*k are left untouched.
+ * b200sd_col2im is its adjoint (nn.Fold) for the backward pass: a per-input-element gather in fp32, fixed order. */
+int b200sd_im2col(const void* x, int64_t ld_x, void* rows, int64_t ld_r, int64_t n, int h, int w, int c, int k,
+                  int stride, int pad, void* stream);
+int b200sd_col2im(const void* drows, int64_t ld_r, void* dx, int64_t ld_x, int64_t n, int h, int w, int c, int k,
+                  int stride, int pad, void* stream);
+
 /* dst[i] = bf16(src[i]) — the autocast cast of fp32 inputs (text context, utils/text_utils.py:32 output). */
 int b200sd_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
 

@@ -115,8 +115,11 @@ def adc_scale(p, c):
     return g * c["adc_gain_1_scale"]
 
 
-def adda_linear(p, c, x, mapping, noise_unit=None, gain_noise=None, offset_noise=None):
-    """Linear_lsq_adda_cim.forward on x [B, ..., K]."""
+def adda_linear(p, c, x, mapping, noise_unit=None, gain_noise=None, offset_noise=None, conv=None):
+    """Linear_lsq_adda_cim.forward on x [B, ..., K] (layers_qn_lsq_adda_cim.py:428-522) or, with conv = dict(kernel_size,
+    stride, padding), Conv2d_lsq_adda_cim.forward on x [B, C, H, W] (:198-291): the DAC digits are unfolded with nn.Unfold
+    ((c, ky, kx) row order, matching weight.view(Cout, -1)), the block loop runs on the [slices * B, L, C*k*k] matrix and
+    the result is folded back to [B, Cout, oh, ow]."""
     R = qp_of(c["adc_bit"])
     slice_bit = c["dac_bit"] - 1
     slices = int(math.ceil((c["input_bit"] - 1) / slice_bit))
@@ -124,6 +127,13 @@ def adda_linear(p, c, x, mapping, noise_unit=None, gain_noise=None, offset_noise
     xq, in_scale = quant_lsq(x, c["input_bit"], p["step_size_input"], True)
     xs = bit_split(xq, c["input_bit"], slice_bit)
     w, w_scale = weight_qn(p, c, True, noise_unit)
+    if conv is not None:
+        B, _, H, W = x.shape
+        k, st, pd = conv["kernel_size"], conv["stride"], conv["padding"]
+        oh, ow = (H + 2 * pd - k) // st + 1, (W + 2 * pd - k) // st + 1
+        xs = torch.nn.functional.unfold(xs, kernel_size=k, padding=pd, stride=st).transpose(1, 2)   # [slices*B, L, C*k*k]
+        w = w.reshape(w.shape[0], -1)
+        x = xs[:B]   # only its leading shape is used below
     w2 = w.transpose(0, 1)
     out = torch.zeros(x.shape[:-1] + (w.shape[0],), dtype=x.dtype)
     alpha = adc_scale(p, c)
@@ -142,9 +152,11 @@ def adda_linear(p, c, x, mapping, noise_unit=None, gain_noise=None, offset_noise
         a = a.reshape((slices, a.shape[0] // slices) + a.shape[1:])
         pw = 2.0 ** (slice_bit * torch.arange(slices, dtype=a.dtype))
         out[..., c0:c0 + cn] = out[..., c0:c0 + cn] + torch.einsum('k...,k->...', a, pw)
+    if conv is not None:
+        out = out.transpose(1, 2).reshape(B, w.shape[0], oh, ow)
     y = out / w_scale / in_scale / alpha
     if p.get("bias") is not None:
-        y = y + p["bias"].view(1, -1)
+        y = y + (p["bias"].view(1, -1, 1, 1) if conv is not None else p["bias"].view(1, -1))
     if c.get("output_quant", True):
         lazy_init_(p, "step_size_output", y, c["output_bit"])
         y, _ = quant_lsq(y, c["output_bit"], p["step_size_output"], False)

@@ -272,6 +272,76 @@ def gen_cim():
     return ok
 
 
+def gen_cim_conv():
+    """k x k Conv2d_lsq_adda_cim fixtures (the leaves of the ReLU-UNet CIM pipeline, Model_Unet_train.py): the real
+    reference layer on seeded inputs with injected weight noise; oracle/cim_torch.py adda_linear(conv=...) must reproduce
+    outputs, lazily initialised parameters and every gradient. -> tests/golden/cim_adda_conv.pt"""
+    from unittest.mock import MagicMock
+    for mod in ("onnx", "onnx.shape_inference", "onnx.numpy_helper", "matplotlib", "matplotlib.pyplot"):
+        sys.modules.setdefault(mod, MagicMock())
+    sys.path.insert(0, REF)
+    from cim_layers.layers_qn_lsq_adda_cim import Conv2d_lsq_adda_cim as RConv
+    from cim_weight_mapper.weight_process import gen_weight_split_dict
+    sys.path.pop(0)
+    O = _load(os.path.join(ROOT, "oracle", "cim_torch.py"), "oracle_cim_torch")
+    real_randn_like = torch.randn_like
+
+    def run(layer, x, unit):
+        torch.randn_like = lambda t, **k: unit.to(t)
+        try:
+            return layer(x)
+        finally:
+            torch.randn_like = real_randn_like
+
+    g = torch.Generator().manual_seed(2222)
+    ok, out = True, {}
+    for name, (cin, cout, k, st, pd), hw, extra, block in [
+            ("adda_conv3x3", (32, 48, 3, 1, 1), 12, {}, [128, 2048]),                       # K = 288 -> 3 row blocks
+            ("adda_conv3x3_clean", (24, 40, 3, 1, 1), 8, dict(noise_scale=0.0), [576, 2048]),
+            ("adda_conv4x4s2", (16, 32, 4, 2, 1), 12, dict(noise_scale=0.0), [576, 2048])]:
+        cfgk = dict(ADDA_CFG, **extra)
+        torch.manual_seed(9)
+        layer = RConv(cin, cout, k, st, pd, 1, bias=True, **cfgk)
+        layer.weight_mapping_info = gen_weight_split_dict(layer, block)
+        init = {kk: v.detach().clone() for kk, v in layer.state_dict().items()}
+        unit = torch.randn(layer.weight.shape, generator=g).to(torch.float16).float()
+        x = torch.randn(2, cin, hw, hw, generator=g)
+        x2 = torch.randn(2, cin, hw, hw, generator=g) * 0.7
+        with torch.no_grad():
+            y1 = run(layer, x, unit)
+            after = {kk: v.detach().clone() for kk, v in layer.state_dict().items()}
+        layer.zero_grad()
+        x2r = x2.clone().requires_grad_(True)
+        y2 = run(layer, x2r, unit)
+        tgt = torch.randn(y2.shape, generator=g)
+        ((y2 - tgt) ** 2).mean().backward()
+        grads = {kk: v.grad.detach().clone() for kk, v in layer.named_parameters() if v.grad is not None}
+        grads["x"] = x2r.grad.detach().clone()
+        y2 = y2.detach()
+        c = dict(cfgk, adc_gain_min=layer.adc_gain_min, adc_gain_max=layer.adc_gain_max)
+        conv = dict(kernel_size=k, stride=st, padding=pd)
+        p = {kk: v.clone() for kk, v in init.items()}
+        with torch.no_grad():
+            o1 = O.adda_linear(p, c, x, layer.weight_mapping_info, unit, conv=conv)
+            ep = max((p[kk] - after[kk]).abs().max().item() for kk in after)
+        p2 = {kk: v.clone().requires_grad_(True) for kk, v in p.items()}
+        x2o = x2.clone().requires_grad_(True)
+        o2 = O.adda_linear(p2, c, x2o, layer.weight_mapping_info, unit, conv=conv)
+        ((o2 - tgt) ** 2).mean().backward()
+        og = {kk: v.grad for kk, v in p2.items()}
+        og["x"] = x2o.grad
+        eg = max(((og[kk] - grads[kk]).abs().max() / grads[kk].abs().max().clamp_min(1e-20)).item() for kk in grads)
+        e1, e2 = (o1 - y1).abs().max().item(), (o2.detach() - y2).abs().max().item()
+        print(f"cim {name}: oracle-vs-ref out {e1:.1e} lazy-init params {ep:.1e} second forward {e2:.1e} grads {eg:.1e} "
+              f"blocks {len(layer.weight_mapping_info)} adc_gain {after['adc_gain'].item():.6f}")
+        ok &= e1 == 0 and ep == 0 and e2 == 0 and eg < 1e-5
+        out[name] = {"cfg": dict(c), "conv": conv, "shape": (cin, cout), "mapping": layer.weight_mapping_info, "init": init,
+                     "after": {kk: v for kk, v in after.items() if v.dim() == 0}, "x": x, "x2": x2,
+                     "unit": unit.to(torch.float16), "y1": y1, "y2": y2, "target": tgt, "grads": grads}
+    torch.save(out, os.path.join(GOLD, "cim_adda_conv.pt"))
+    return ok
+
+
 def sampler_model(x, t, cond=None):
     """Deterministic stand-in denoiser whose arithmetic (*, +, / on fp32) is bit-reproducible on any device."""
     s = (t.float() * 0.001).view(-1, 1, 1, 1)   # (not "/ 1000": CUDA divides by a scalar through its reciprocal)
@@ -564,6 +634,11 @@ def main():
         return
     if "--only-samplers" in sys.argv:
         if not gen_samplers():
+            print("ORACLE DISAGREES WITH THE REFERENCE")
+            sys.exit(1)
+        return
+    if "--only-cim-conv" in sys.argv:
+        if not gen_cim_conv():
             print("ORACLE DISAGREES WITH THE REFERENCE")
             sys.exit(1)
         return

@@ -146,6 +146,67 @@ static inline int glue_grid(long long items, int threads) {
     return (int)(b < 1 ? 1 : (b > cap ? cap : b));
 }
 
+// nn.Unfold of an NHWC bf16 tensor into GEMM rows in the (c, ky, kx) column order of weight.view(Cout, -1) — the operand
+// layout of the compute-in-memory convolutions (cim_layers/layers_qn_lsq_adda_cim.py:92-94,198: the mapped weight blocks
+// are row ranges of that K axis, so the explicit matrix is what the array sees). Thread = (output pixel, channel):
+// reads one input channel's k*k window (border taps zero), writes k*k consecutive columns.
+__global__ void im2col_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, __nv_bfloat16* __restrict__ rows,
+                              long long ld_r, long long n, int h, int w, int c, int oh, int ow, int k, int stride,
+                              int pad) {
+    pdl_enter();
+    const long long total = n * oh * ow * c;
+    const int kk = k * k;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int ch = static_cast<int>(i % c);
+        const long long p = i / c;
+        const int ox = static_cast<int>(p % ow), oy = static_cast<int>((p / ow) % oh);
+        const long long img = p / (static_cast<long long>(ow) * oh);
+        __nv_bfloat16* dst = rows + p * ld_r + static_cast<long long>(ch) * kk;
+        for (int ky = 0; ky < k; ++ky) {
+            const int iy = oy * stride - pad + ky;
+            for (int kx = 0; kx < k; ++kx) {
+                const int ix = ox * stride - pad + kx;
+                __nv_bfloat16 v = __float2bfloat16(0.f);
+                if (iy >= 0 && iy < h && ix >= 0 && ix < w) v = x[((img * h + iy) * w + ix) * ld_x + ch];
+                dst[ky * k + kx] = v;
+            }
+        }
+    }
+}
+
+// Its adjoint (nn.Fold): dx[n, y, x, c] = sum over the (ky, kx) whose window covers (y, x) of drows[(n, oy, ox),
+// c*k*k + ky*k + kx], gathered per input element in fp32 (fixed order: deterministic, no atomics).
+__global__ void col2im_kernel(const __nv_bfloat16* __restrict__ drows, long long ld_r, __nv_bfloat16* __restrict__ dx,
+                              long long ld_x, long long n, int h, int w, int c, int oh, int ow, int k, int stride,
+                              int pad) {
+    pdl_enter();
+    const long long total = n * h * w * c;
+    const int kk = k * k;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int ch = static_cast<int>(i % c);
+        const long long p = i / c;
+        const int ix = static_cast<int>(p % w), iy = static_cast<int>((p / w) % h);
+        const long long img = p / (static_cast<long long>(w) * h);
+        float acc = 0.f;
+        for (int ky = 0; ky < k; ++ky) {
+            const int ty = iy + pad - ky;
+            if (ty < 0 || ty % stride) continue;
+            const int oy = ty / stride;
+            if (oy >= oh) continue;
+            for (int kx = 0; kx < k; ++kx) {
+                const int tx = ix + pad - kx;
+                if (tx < 0 || tx % stride) continue;
+                const int ox = tx / stride;
+                if (ox >= ow) continue;
+                acc += __bfloat162float(drows[((img * oh + oy) * ow + ox) * ld_r + static_cast<long long>(ch) * kk + ky * k + kx]);
+            }
+        }
+        dx[p * ld_x + ch] = __float2bfloat16_rn(acc);
+    }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -228,5 +289,31 @@ extern "C" int b200sd_add_bf16(const void* a, const void* b, void* out, int64_t 
     launch_k(add_bf16_kernel, glue_grid(n / 8, 256), 256, 0, as_stream(stream), 
         static_cast<const uint4*>(a), static_cast<const uint4*>(b), static_cast<uint4*>(out), n / 8);
     B200_CHECK_LAUNCH("add_bf16");
+    return B200SD_OK;
+}
+
+extern "C" int b200sd_im2col(const void* x, int64_t ld_x, void* rows, int64_t ld_r, int64_t n, int h, int w, int c, int k,
+                             int stride, int pad, void* stream) {
+    B200_REQUIRE(x && rows, "im2col: null pointer");
+    B200_REQUIRE(k >= 1 && stride >= 1 && pad >= 0 && h + 2 * pad >= k && w + 2 * pad >= k, "im2col: bad geometry");
+    B200_REQUIRE(ld_x >= c && ld_r >= (int64_t)c * k * k, "im2col: pitches too small");
+    const int oh = (h + 2 * pad - k) / stride + 1, ow = (w + 2 * pad - k) / stride + 1;
+    if (n * oh * ow * c == 0) return B200SD_OK;
+    launch_k(im2col_kernel, glue_grid(n * oh * ow * c, 256), 256, 0, as_stream(stream), static_cast<const __nv_bfloat16*>(x),
+             ld_x, static_cast<__nv_bfloat16*>(rows), ld_r, n, h, w, c, oh, ow, k, stride, pad);
+    B200_CHECK_LAUNCH("im2col");
+    return B200SD_OK;
+}
+
+extern "C" int b200sd_col2im(const void* drows, int64_t ld_r, void* dx, int64_t ld_x, int64_t n, int h, int w, int c,
+                             int k, int stride, int pad, void* stream) {
+    B200_REQUIRE(drows && dx, "col2im: null pointer");
+    B200_REQUIRE(k >= 1 && stride >= 1 && pad >= 0 && h + 2 * pad >= k && w + 2 * pad >= k, "col2im: bad geometry");
+    B200_REQUIRE(ld_x >= c && ld_r >= (int64_t)c * k * k, "col2im: pitches too small");
+    const int oh = (h + 2 * pad - k) / stride + 1, ow = (w + 2 * pad - k) / stride + 1;
+    if (n * h * w * c == 0) return B200SD_OK;
+    launch_k(col2im_kernel, glue_grid(n * h * w * c, 256), 256, 0, as_stream(stream), static_cast<const __nv_bfloat16*>(drows),
+             ld_r, static_cast<__nv_bfloat16*>(dx), ld_x, n, h, w, c, oh, ow, k, stride, pad);
+    B200_CHECK_LAUNCH("col2im");
     return B200SD_OK;
 }

@@ -176,8 +176,14 @@ def conv2d(a, mod, rowbias=None, extra=None, act=None, out=None, c_off=0, out_dt
     into the same accumulator (ResNet shortcut)."""
     if not isinstance(a, Act):
         return _P().conv2d_any(a, mod, out_dtype)
-    if hasattr(mod, "forward_act") and extra is None and rowbias is None:
-        return mod.forward_act(a)
+    if hasattr(mod, "forward_act") and extra is None:
+        y = mod.forward_act(a)
+        if rowbias is not None:
+            # a quantised leaf ends in its own output quantiser: the time-embedding row (blocks.py:118) is added afterwards,
+            # as the reference does (a per-image broadcast add on a [n, hw, c] view; elementwise, autograd-visible)
+            t = (y.t[:, :y.c].reshape(y.n, y.hw, y.c) + rowbias[:, None, :y.c].to(y.t.dtype)).reshape(y.n * y.hw, y.c)
+            y = Act(t if t.shape[1] % 8 == 0 else torch.nn.functional.pad(t, (0, 8 - t.shape[1] % 8)), y.n, y.h, y.w, y.c)
+        return y
     _require_leaf(mod, (nn.Conv2d,), "Conv2d")
     k, s, p = mod.kernel_size, mod.stride, mod.padding
     if mod.groups != 1 or mod.dilation != (1, 1):

@@ -19,7 +19,7 @@ EXPORTS = [
     "b200sd_last_error", "b200sd_version", "b200sd_launch_count", "b200sd_sched_add_noise",
     "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_attention_lse", "b200sd_attention_tc", "b200sd_attention_bwd", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_groupnorm_split", "b200sd_split_f32", "b200sd_rowblocks", "b200sd_groupnorm_bwd", "b200sd_colsum", "b200sd_colsum_blocks", "b200sd_colsum_static", "b200sd_colsum_static_max_floats", "b200sd_vq_blocks", "b200sd_vq_nearest", "b200sd_sampler_step", "b200sd_opt_chunk_size", "b200sd_opt_chunk_elems", "b200sd_grad_sqnorm", "b200sd_adam_ema_step", "b200sd_percent_opt_step",
     "b200sd_reduce_f32", "b200sd_attention",
-    "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16",
+    "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16", "b200sd_im2col", "b200sd_col2im",
     "b200sd_layernorm_mod", "b200sd_layernorm_mod_bwd", "b200sd_rows_per_slot", "b200sd_gate_residual",
     "b200sd_gate_residual_bwd", "b200sd_relu_bwd", "b200sd_unpatchify", "b200sd_patchify",
     "b200sd_lsq_init_step", "b200sd_lsq_quant", "b200sd_lsq_quant_bwd", "b200sd_lsq_quant_bwd_blocks", "b200sd_bit_split",
@@ -124,6 +124,8 @@ def lib():
         L.b200sd_copy_act.argtypes = [vp, i64, vp, i64, i32, i64, i32, i32, vp]
         L.b200sd_cast_f32_bf16.argtypes = [vp, vp, i64, vp]
         L.b200sd_add_bf16.argtypes = [vp, vp, vp, i64, vp]
+        L.b200sd_im2col.argtypes = [vp, i64, vp, i64, i64, i32, i32, i32, i32, i32, i32, vp]
+        L.b200sd_col2im.argtypes = [vp, i64, vp, i64, i64, i32, i32, i32, i32, i32, i32, vp]
         L.b200sd_layernorm_mod.argtypes = [vp, i64, vp, i64, vp, vp, i64, i64, i64, i32, f32, vp, vp]
         L.b200sd_layernorm_mod_bwd.argtypes = [vp, i64, vp, i64, vp, vp, i64, vp, i64, vp, i64, i64, i64, i32, vp, vp]
         L.b200sd_rows_per_slot.argtypes = []
@@ -625,6 +627,30 @@ def cast_bf16(src):
     out = torch.empty(src.shape, device=src.device, dtype=torch.bfloat16)
     check(lib().b200sd_cast_f32_bf16(_p(src), _p(out), src.numel(), stream_ptr()), "cast_f32_bf16")
     return out
+
+
+def im2col(x, n, h, w, c, k, stride, pad, ld_x=None):
+    """NHWC bf16 [n*h*w, ld] -> unfolded rows bf16 [n*oh*ow, pad8(c*k*k)] in (c, ky, kx) order (padding columns zero)."""
+    _cuda(x, torch.bfloat16, "x")
+    oh, ow = (h + 2 * pad - k) // stride + 1, (w + 2 * pad - k) // stride + 1
+    K = c * k * k
+    Kp = pad8(K)
+    rows = torch.empty(n * oh * ow, Kp, device=x.device, dtype=torch.bfloat16)
+    if Kp != K:
+        rows[:, K:].zero_()
+    check(lib().b200sd_im2col(_p(x), x.stride(0) if ld_x is None else ld_x, _p(rows), Kp, n, h, w, c, k, stride, pad,
+                              stream_ptr()), "im2col")
+    return rows
+
+
+def col2im(drows, n, h, w, c, k, stride, pad):
+    """Adjoint of im2col: gradient rows bf16 [n*oh*ow, >= c*k*k] -> NHWC bf16 [n*h*w, pad8(c)]."""
+    _cuda(drows, torch.bfloat16, "drows")
+    cp = pad8(c)
+    dx = torch.empty(n * h * w, cp, device=drows.device, dtype=torch.bfloat16) if cp == c else \
+        torch.zeros(n * h * w, cp, device=drows.device, dtype=torch.bfloat16)
+    check(lib().b200sd_col2im(_p(drows), drows.stride(0), _p(dx), cp, n, h, w, c, k, stride, pad, stream_ptr()), "col2im")
+    return dx
 
 
 def add_bf16(a, b, out):

@@ -478,3 +478,94 @@ def test_dit_with_adda_leaves_vs_oracle_and_trains():
     assert not missing, (len(missing), missing[:40])
     gains = [p.grad.abs().item() for k, p in model.named_parameters() if k.endswith("adc_gain")]
     assert len(gains) == 26
+
+
+# ------------------------------------------------------------------------------------- k x k ADDA convolutions
+def _adda_conv(f, dev, train=False, after=False):
+    from cim_layers.layers_qn_lsq_adda_cim import Conv2d_lsq_adda_cim, gen_weight_split_dict
+    cfg, cv = f["cfg"], f["conv"]
+    cin, cout = f["shape"]
+    layer = Conv2d_lsq_adda_cim(cin, cout, cv["kernel_size"], cv["stride"], cv["padding"], 1, weight_bit=cfg["weight_bit"],
+                                input_bit=cfg["input_bit"], output_bit=cfg["output_bit"], noise_scale=cfg["noise_scale"],
+                                dac_bit=cfg["dac_bit"], adc_bit=cfg["adc_bit"], adc_gain_1_scale=cfg["adc_gain_1_scale"],
+                                adc_gain_range=cfg["adc_gain_range"], adc_adjust_mode=cfg["adc_adjust_mode"], bias=True)
+    state = dict(f["init"])
+    if after:
+        state.update(f["after"])
+    layer.load_state_dict(state)
+    layer = layer.to(dev)
+    layer = layer.train() if train else layer.eval()
+    if after:
+        layer.__dict__["_gain_init_pending"] = False
+    layer.weight_noise_unit = f["unit"].float().to(dev)
+    layer.weight_mapping_info = f["mapping"]
+    block = [max(i["row_num"] for i in f["mapping"].values()), max(i["col_num"] for i in f["mapping"].values())]
+    assert gen_weight_split_dict(layer, block) == f["mapping"]
+    return layer, state
+
+
+@pytest.mark.parametrize("name", ["adda_conv3x3", "adda_conv3x3_clean", "adda_conv4x4s2"])
+def test_adda_conv_vs_oracle(name):
+    """Conv2d_lsq_adda_cim with k x k kernels (3x3 same, 4x4 stride 2; K split into row blocks in nn.Unfold's (c, ky, kx)
+    order): output codes against the oracle (== the reference, tests/test_oracle.py), bit-exact without weight noise."""
+    dev = _dev()
+    from oracle import cim_torch as OC
+    f = load_golden("cim_adda_conv")[name]
+    cfg = f["cfg"]
+    layer, _ = _adda_conv(f, dev)
+    x, x2 = _bfr(f["x"]), _bfr(f["x2"])
+    p = {k: v.clone() for k, v in f["init"].items()}
+    with torch.no_grad():
+        ref1 = OC.adda_linear(p, cfg, x, f["mapping"], f["unit"].float(), conv=f["conv"])
+        out1 = layer(x.to(dev))
+        assert layer.step_size_input.item() == p["step_size_input"].item()
+        assert layer.step_size_weight.item() == p["step_size_weight"].item()
+        ref2 = OC.adda_linear(p, cfg, x2, f["mapping"], f["unit"].float(), conv=f["conv"])
+        out2 = layer(x2.to(dev))
+    torch.cuda.synchronize()
+    assert out1.shape == ref1.shape
+    exact = cfg["noise_scale"] == 0
+    if exact:
+        assert abs(layer.adc_gain.item() - p["adc_gain"].item()) <= 1e-7 * p["adc_gain"].item()
+        assert layer.step_size_output.item() == pytest.approx(p["step_size_output"].item(), rel=1e-6)
+    s_out = p["step_size_output"].item()
+    for got, ref in ((out1, ref1), (out2, ref2)):
+        dcode = (torch.round(got.cpu() / s_out) - torch.round(ref / s_out)).abs()
+        same = (dcode < 0.5).float().mean().item()
+        print(f"{name}: output codes identical {100 * same:.2f}% max |dcode| {dcode.max().item():.2f}")
+        if exact:
+            assert dcode.max().item() == 0
+        else:
+            assert dcode.max().item() <= 3 and same > 0.7
+    assert relerr(out1.cpu(), f["y1"]) < 5e-2
+
+
+@pytest.mark.parametrize("name", ["adda_conv3x3", "adda_conv4x4s2"])
+def test_adda_conv_backward_vs_oracle(name):
+    dev = _dev()
+    from oracle import cim_torch as OC
+    f = load_golden("cim_adda_conv")[name]
+    cfg = f["cfg"]
+    layer, state = _adda_conv(f, dev, train=True, after=True)
+    x2, tgt = _bfr(f["x2"]), f["target"]
+    p = {k: v.clone().requires_grad_(True) for k, v in state.items()}
+    xo = x2.clone().requires_grad_(True)
+    ref = OC.adda_linear(p, cfg, xo, f["mapping"], f["unit"].float(), conv=f["conv"])
+    ((ref - tgt) ** 2).mean().backward()
+    p16 = {k: v.clone().requires_grad_(True) for k, v in state.items()}
+    with torch.autocast("cpu", dtype=torch.bfloat16):
+        ref16 = OC.adda_linear(p16, cfg, x2, f["mapping"], f["unit"].float(), conv=f["conv"])
+    ((ref16.float() - tgt) ** 2).mean().backward()
+    xd = x2.to(dev).requires_grad_(True)
+    out = layer(xd)
+    ((out - tgt.to(dev)) ** 2).mean().backward()
+    torch.cuda.synchronize()
+    got = {k: v.grad.cpu() for k, v in layer.named_parameters()}
+    got["x"] = xd.grad.cpu()
+    want = {k: v.grad for k, v in p.items()}
+    want["x"] = xo.grad
+    for k in want:
+        err = ((got[k] - want[k]).norm() / want[k].norm().clamp_min(1e-20)).item()
+        yard = ((p16[k].grad - want[k]).norm() / want[k].norm().clamp_min(1e-20)).item() if k in p16 else 0.0
+        print(f"   {name} grad {k}: rel-L2 {err:.3e} (oracle under bf16 autocast: {yard:.3e})")
+        assert err < max(8e-2 if want[k].dim() == 0 else 4e-2, 1.5 * yard), k

@@ -118,6 +118,29 @@ def test_cim_oracle_vs_reference_golden():
                 assert relerr(got[k], g) < 1e-5, (name, k)
 
 
+def test_cim_conv_oracle_vs_reference_golden():
+    """k x k Conv2d_lsq_adda_cim (nn.Unfold row order, row-block split of K): the oracle against the committed outputs,
+    lazily initialised parameters and gradients of the real reference layer — exactly."""
+    from oracle import cim_torch as OC
+    for name, f in load_golden("cim_adda_conv").items():
+        unit = f["unit"].float()
+        p = {k: v.clone() for k, v in f["init"].items()}
+        with torch.no_grad():
+            y1 = OC.adda_linear(p, f["cfg"], f["x"], f["mapping"], unit, conv=f["conv"])
+        for k, v in f["after"].items():
+            assert torch.equal(p[k], v), (name, k)
+        assert torch.equal(y1, f["y1"]), name
+        p2 = {k: v.clone().requires_grad_(True) for k, v in p.items()}
+        x2 = f["x2"].clone().requires_grad_(True)
+        y2 = OC.adda_linear(p2, f["cfg"], x2, f["mapping"], unit, conv=f["conv"])
+        assert torch.equal(y2.detach(), f["y2"]), name
+        ((y2 - f["target"]) ** 2).mean().backward()
+        got = {k: v.grad for k, v in p2.items()}
+        got["x"] = x2.grad
+        for k, g in f["grads"].items():
+            assert relerr(got[k], g) < 1e-5, (name, k)
+
+
 def _sampler_model(x, t, cond=None):
     """The stand-in denoiser of oracle/gen_golden.py:gen_samplers (fp32 * and + only: bit-reproducible anywhere)."""
     s = (t.float() * 0.001).view(-1, 1, 1, 1)   # (not "/ 1000": CUDA divides by a scalar through its reciprocal)
