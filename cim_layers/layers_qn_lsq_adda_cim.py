@@ -261,10 +261,6 @@ class Conv2d_lsq_adda_cim(nn.Conv2d, _AddaMixin):
         if isinstance(pd, str) or self.groups != 1 or self.dilation != (1, 1) or k[0] != k[1] or st[0] != st[1] \
                 or pd[0] != pd[1]:
             raise rt.B200Error("Conv2d_lsq_adda_cim: square kernels with symmetric stride / padding, groups = 1 only")
-        if self.out_channels % 8:
-            # (the 18 -> 3 mask conv of the DiT is a 1x1: its rows are already the GEMM operand)
-            if k != (1, 1):
-                raise rt.B200Error("Conv2d_lsq_adda_cim: k x k convolutions need out_channels % 8 == 0")
         if k == (1, 1) and st == (1, 1) and pd == (0, 0):
             y = self._cim_rows(self._rows_in(a.t, a.c), self.weight.reshape(self.out_channels, -1), self.bias,
                                a.n * a.hw * a.c)

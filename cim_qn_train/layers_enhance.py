@@ -11,8 +11,9 @@ fused path (sdb200.engine.linear). Module names, parameter shapes, initialisatio
 (`analyze_*`) follow the reference, so state_dicts are interchangeable.
 
 Built: the Linear family (what the DiT-9L pipeline instantiates for its 95 Linear leaves), EnhanceLayerConv2d (any
-original conv the engine or a cim_layers drop-in runs) and EnhanceBranchConv2d_LoR for 1x1 / stride-1 / unpadded
-original convolutions (the pipeline's one conv, the 18 -> 3 mask conv); other branch shapes raise.
+original conv the engine or a cim_layers drop-in runs) and EnhanceBranchConv2d_LoR around any square-kernel original
+conv (the DiT's 1x1 mask conv; the ReLU-UNet's 3x3 and 4x4-stride-2 leaves with the reference's padded-1x1 frame,
+average pooling and top-left crop).
 """
 import math
 
@@ -249,29 +250,35 @@ class EnhanceLayerConv2d(_ActModule):
 
 
 class EnhanceBranchConv2d_LoR(_ActModule):
-    """original conv blended with a two-layer grouped 1x1 low-rank branch (layers_enhance.py:439-535). Built for the
-    shape the DiT pipeline has — a 1x1, stride-1, unpadded original conv (the mask conv), where the reference's pooling
-    / padding / cropping of the branch output are no-ops; other shapes raise."""
+    """original conv blended with a two-layer grouped 1x1 low-rank branch (layers_enhance.py:439-535).
+
+    The two branch convolutions are 1x1 but carry the ORIGINAL conv's padding (:467,:473), so for a padded original the
+    branch output is an (H + 4p) x (W + 4p) map whose interior is the per-pixel map z = W2 act(W1 x + b1) + b2 shifted by
+    2p, framed by a ring of the constant W2 act(b1) + b2 (pixels whose first conv saw only padding) and an outer ring of
+    b2 (pixels whose second conv saw only padding); a strided original average-pools that map by its stride (:484-487);
+    the reference then crops from the TOP-LEFT corner (or zero-pads around) to the original's output size (:520-531).
+    Here z is two grouped GEMMs on the pixel rows (one tcgen05 GEMM each over the block-diagonal dense weights); the
+    frame, the pooling and the crop are assembled exactly as described."""
 
     def __init__(self, original_conv, ops_factor=0.05, relu=False, sigmoid=True):
         super().__init__()
-        if tuple(original_conv.kernel_size) != (1, 1) or tuple(original_conv.stride) != (1, 1) \
-                or tuple(original_conv.padding) != (0, 0):
-            raise NotImplementedError("EnhanceBranchConv2d_LoR: only 1x1 / stride 1 / padding 0 original convolutions are "
-                                      "built in this package (DESIGN.md §7)")
+        kh, kw = original_conv.kernel_size
+        st, pd = tuple(original_conv.stride), original_conv.padding
+        if isinstance(pd, str) or st[0] != st[1] or pd[0] != pd[1]:
+            raise NotImplementedError("EnhanceBranchConv2d_LoR: symmetric integer stride / padding only")
         self.original_conv = original_conv
         ci, co = original_conv.in_channels, original_conv.out_channels
         self.stride, self.padding = original_conv.stride, original_conv.padding
         self.relu, self.sigmoid = relu, sigmoid
         w = original_conv.weight
-        cfg = analyze_lora_conv_ops(ci, co, 1, 1, ops_factor)
+        cfg = analyze_lora_conv_ops(ci, co, kh, kw, ops_factor)
         hidden = cfg["hidden_channels"]
         self.enhance_branch_1 = nn.Conv2d(ci, hidden, kernel_size=1, stride=1, padding=self.padding,
                                           groups=cfg["group1"], dtype=w.dtype, device=w.device)
         self.enhance_branch_2 = nn.Conv2d(hidden, co, kernel_size=1, stride=1, padding=self.padding,
                                           groups=cfg["group2"], dtype=w.dtype, device=w.device)
         self.enhance_branch_1.layer_flag = self.enhance_branch_2.layer_flag = 'enhance_branch'
-        self.pool = None
+        self.pool = nn.AvgPool2d(kernel_size=self.stride, stride=self.stride, padding=0) if any(v != 1 for v in st) else None
         self.blend_factor = nn.Parameter(torch.tensor(-6.9068 if sigmoid else 0.0))
         self.std_ori = self.mean_ori = self.std_enhance = self.mean_enhance = None
 
@@ -282,10 +289,40 @@ class EnhanceBranchConv2d_LoR(_ActModule):
         b1, b2 = self.enhance_branch_1, self.enhance_branch_2
         enh = _dense_rows(_clean_rows(a), _conv1x1_dense(b1), b1.bias, b1.out_channels, act="relu" if self.relu else None)
         enh = _dense_rows(enh, _conv1x1_dense(b2), b2.bias, b2.out_channels)
+        p, st = self.padding[0], self.stride[0]
+        if p != 0 or st != 1 or (y.h, y.w) != (a.h, a.w):
+            enh = self._frame(enh[:, :y.c], a, y, p, st)
         out = self.merge_feature_map(y.t[:, :y.c], enh[:, :y.c]).to(torch.bfloat16)
         if y.c % 8:
             out = torch.nn.functional.pad(out, (0, _pad8(y.c) - y.c))
         return E.Act(out.contiguous(), y.n, y.h, y.w, y.c)
+
+
+def _frame(self, z, a, y, p, st):
+    """Branch output of a padded / strided original conv from the per-pixel map z [n*h*w, co] (see the class docstring)."""
+    b1, b2 = self.enhance_branch_1, self.enhance_branch_2
+    co, n, h, w = y.c, a.n, a.h, a.w
+    f32 = torch.float32
+    bias2 = b2.bias.to(f32) if b2.bias is not None else torch.zeros(co, device=z.device, dtype=f32)
+    bias1 = b1.bias.to(f32) if b1.bias is not None else torch.zeros(b1.out_channels, device=z.device, dtype=f32)
+    hid = torch.relu(bias1) if self.relu else bias1
+    ring = torch.nn.functional.linear(hid, _conv1x1_dense(b2).to(f32)[:, :b2.in_channels], bias2)   # W2 act(b1) + b2
+    e = bias2.view(1, 1, 1, co).expand(n, h + 4 * p, w + 4 * p, co).clone()
+    if p > 0:
+        e[:, p:p + h + 2 * p, p:p + w + 2 * p, :] = ring
+    e[:, 2 * p:2 * p + h, 2 * p:2 * p + w, :] = z.to(f32).reshape(n, h, w, co)
+    if st != 1:
+        e = torch.nn.functional.avg_pool2d(e.permute(0, 3, 1, 2), kernel_size=st, stride=st, padding=0).permute(0, 2, 3, 1)
+    dy, dx = y.h - e.shape[1], y.w - e.shape[2]
+    if dy != 0 or dx != 0:
+        if dy < 0 or dx < 0:
+            e = e[:, :y.h, :y.w, :]
+        elif dy > 0 or dx > 0:
+            e = torch.nn.functional.pad(e, (0, 0, dx // 2, dx - dx // 2, dy // 2, dy - dy // 2))
+    return e.reshape(n * y.h * y.w, co).to(torch.bfloat16)
+
+
+EnhanceBranchConv2d_LoR._frame = _frame
 
 
 def _leaf_rows(mod, rows):

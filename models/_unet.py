@@ -183,8 +183,16 @@ class UnetCore(Denoiser):
             ld = (cin + 7) // 8 * 8
             buf = torch.zeros(n * h * w, ld, device=device, dtype=torch.bfloat16)
             if type(self.cond_conv_in) is not nn.Conv2d:
-                raise rt.B200Error("cond_conv_in: quantised leaf on the mask path is not supported yet")
-            if E.training() and self.cond_conv_in.weight.requires_grad:
+                # quantised / wrapped leaf (cim_qn_train surgery): the nearest resize is a strided read of the mask
+                # (src = dst * ratio for the integer ratios the model asserts), the leaf then runs on those pixel rows
+                sy, sx = mask.shape[2] // h, mask.shape[3] // w
+                mk = mask[:, :, ::sy, ::sx][:, :, :h, :w].permute(0, 2, 3, 1).reshape(n * h * w, -1).to(torch.bfloat16)
+                cm = mk.shape[1]
+                if cm % 8:
+                    mk = torch.nn.functional.pad(mk, (0, 8 - cm % 8))
+                y = self.cond_conv_in.forward_act(E.Act(mk.contiguous(), n, h, w, cm))
+                buf = torch.cat([buf[:, :c], y.t[:, :self.im_cond_output_ch].to(buf.dtype), buf[:, cin:]], dim=1).contiguous()
+            elif E.training() and self.cond_conv_in.weight.requires_grad:
                 buf = AG.MaskCondFn.apply(self.cond_conv_in.weight, mask, buf, c, h, w)
             else:
                 rt.mask_cond(mask.float(), self.cond_conv_in.weight.detach().float().reshape(self.im_cond_output_ch, -1),

@@ -46,3 +46,25 @@ def enhance_branch_conv1x1(x, conv_w, conv_b, w1, b1, g1, w2, b2, g2, blend, rel
     enh = torch.nn.functional.conv2d(enh, w2, b2, groups=g2)
     s = torch.sigmoid(blend) if sigmoid else blend
     return orig * (1 - s) + enh * s
+
+
+def enhance_branch_conv(x, conv_w, conv_b, stride, padding, w1, b1, g1, w2, b2, g2, blend, relu=False, sigmoid=True):
+    """layers_enhance.py:439-535 for ANY original conv: both 1x1 branch convs carry the ORIGINAL's padding (:467,:473), so
+    the branch output is (H + 4p) x (W + 4p); a strided original average-pools it by the stride (:484-487,:516-517); the
+    result is cropped from the top-left corner (:527-528) or zero-padded around (:530-531) to the original's output size."""
+    F = torch.nn.functional
+    orig = F.conv2d(x, conv_w, conv_b, stride=stride, padding=padding)
+    enh = F.conv2d(x, w1, b1, padding=padding, groups=g1)
+    if relu:
+        enh = torch.relu(enh)
+    enh = F.conv2d(enh, w2, b2, padding=padding, groups=g2)
+    if stride != 1:
+        enh = F.avg_pool2d(enh, kernel_size=stride, stride=stride, padding=0)
+    dy, dx = orig.shape[2] - enh.shape[2], orig.shape[3] - enh.shape[3]
+    if dy != 0 or dx != 0:
+        if dy < 0 or dx < 0:
+            enh = enh[:, :, :orig.shape[2], :orig.shape[3]]
+        elif dy > 0 or dx > 0:
+            enh = F.pad(enh, (dx // 2, dx - dx // 2, dy // 2, dy - dy // 2))
+    s = torch.sigmoid(blend) if sigmoid else blend
+    return orig * (1 - s) + enh * s

@@ -620,7 +620,72 @@ def gen_enhance():
     print(f"enhance: oracle == reference on {len(out['cases'])} + {len(out['conv_cases'])} modules; {len(table)} search results recorded")
 
 
+def gen_enhance_conv_kxk():
+    """EnhanceBranchConv2d_LoR around k x k / strided original convolutions (the ReLU-UNet's 3x3 and 4x4-stride-2 leaves,
+    layers_enhance.py:439-535): the real reference module, oracle/enhance_torch.py enhance_branch_conv must reproduce
+    output and gradients. -> tests/golden/enhance_conv_kxk.pt"""
+    from unittest.mock import MagicMock
+    for m in ("matplotlib", "matplotlib.pyplot"):
+        sys.modules.setdefault(m, MagicMock())
+    spec = importlib.util.spec_from_file_location("ref_layers_enhance", os.path.join(REF, "cim_qn_train", "layers_enhance.py"))
+    ref = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref)
+    OE = _load(os.path.join(ROOT, "oracle", "enhance_torch.py"), "oracle_enhance_torch")
+    g = torch.Generator().manual_seed(78)
+    torch.manual_seed(78)
+    cases = []
+    for ci, co, k, st, pad, hw, ops_f, relu, sig in ((16, 16, 3, 1, 1, 8, 0.1, False, True), (16, 24, 3, 1, 1, 8, 0.1, True, False),
+                                                      (16, 16, 4, 2, 1, 8, 0.1, False, True)):
+        conv = torch.nn.Conv2d(ci, co, k, stride=st, padding=pad)
+        with torch.no_grad():
+            conv.weight.copy_(torch.randn(conv.weight.shape, generator=g) / (ci * k * k) ** 0.5)
+            conv.bias.copy_(torch.randn(co, generator=g) * 0.1)
+        mod = ref.EnhanceBranchConv2d_LoR(conv, ops_f, relu=relu, sigmoid=sig)
+        with torch.no_grad():
+            for n_, p_ in mod.named_parameters():
+                if "original_conv" in n_:
+                    continue
+                if n_ == "blend_factor":
+                    p_.copy_(torch.tensor(-0.4 if sig else 0.3))
+                else:
+                    p_.add_(torch.randn(p_.shape, generator=g) * 0.1)
+        x = torch.randn(3, ci, hw, hw, generator=g).requires_grad_(True)
+        y = mod(x)
+        r = torch.randn(y.shape, generator=g)
+        (y * r).sum().backward()
+        sd = {k_: v.detach().clone() for k_, v in mod.state_dict().items()}
+        grads = {k_: p_.grad.clone() for k_, p_ in mod.named_parameters()}
+        ps = {k_: v.clone().requires_grad_(True) for k_, v in sd.items()}
+        x2 = x.detach().clone().requires_grad_(True)
+        y2 = OE.enhance_branch_conv(x2, ps["original_conv.weight"], ps["original_conv.bias"], st, pad,
+                                    ps["enhance_branch_1.weight"], ps["enhance_branch_1.bias"], mod.enhance_branch_1.groups,
+                                    ps["enhance_branch_2.weight"], ps["enhance_branch_2.bias"], mod.enhance_branch_2.groups,
+                                    ps["blend_factor"], relu, sig)
+        (y2 * r).sum().backward()
+        assert torch.equal(y, y2), "oracle Enhance k x k conv forward differs"
+        for name_, a_, b_ in [("x", x.grad, x2.grad)] + [(k_, grads[k_], ps[k_].grad) for k_ in grads]:
+            d_ = (a_ - b_).abs().max().item() / (a_.abs().max().item() + 1e-30)
+            assert d_ < 1e-5, f"oracle Enhance k x k conv gradient of {name_} differs: {d_:.2e}"
+        for p_ in mod.parameters():
+            p_.grad = None
+        xa = x.detach().clone().requires_grad_(True)
+        with torch.autocast("cpu", dtype=torch.bfloat16):
+            ya = mod(xa)
+        (ya.float() * r).sum().backward()
+        bf_err = {k_: float((p_.grad - grads[k_]).norm() / (grads[k_].norm() + 1e-12)) for k_, p_ in mod.named_parameters()}
+        cases.append({"kind": "branch", "cin": ci, "cout": co, "k": k, "stride": st, "pad": pad, "ops_factor": ops_f,
+                      "relu": relu, "sigmoid": sig, "state": sd, "x": x.detach().clone(), "r": r, "y": y.detach().clone(),
+                      "dx": x.grad.clone(), "grads": grads, "ref_bf16_grad_err": bf_err,
+                      "groups": (mod.enhance_branch_1.groups, mod.enhance_branch_2.groups)})
+    torch.save({"conv_cases": cases}, os.path.join(GOLD, "enhance_conv_kxk.pt"))
+    print(f"enhance k x k: oracle == reference on {len(cases)} modules")
+    return True
+
+
 def main():
+    if "--only-enhance-kxk" in sys.argv:
+        gen_enhance_conv_kxk()
+        return
     if "--only-enhance" in sys.argv:
         gen_enhance()
         return

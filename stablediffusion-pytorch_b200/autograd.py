@@ -494,15 +494,16 @@ class ToNchwFn(Function):
     @staticmethod
     def forward(ctx, x, geom):
         n, c, h, w = geom
-        ctx.geom, ctx.ld = geom, x.stride(0)
+        ctx.geom, ctx.ld, ctx.cols, ctx.dt = geom, x.stride(0), x.shape[1], x.dtype
         return rt.nhwc_to_nchw(x, n, c, h, w, ld=x.stride(0))
 
     @staticmethod
     def backward(ctx, g):
         n, c, h, w = ctx.geom
-        buf = torch.zeros(n * h * w, _pad8(c), device=g.device, dtype=torch.bfloat16)
+        width = max(_pad8(c), ctx.cols)   # a quantised conv_out hands over rows padded to 8 columns
+        buf = torch.zeros(n * h * w, width, device=g.device, dtype=torch.bfloat16)
         rt.nchw_to_nhwc(g.float().contiguous(), buf, 0)
-        return buf[:, :c], None
+        return buf[:, :ctx.cols].to(ctx.dt), None
 
 
 class FromNchwFn(Function):

@@ -371,6 +371,15 @@ def self_attention(a, norm, mha):
         return _P().self_attention(a, norm, mha)
     C, heads = a.c, mha.num_heads
     xn = group_norm(a, norm)
+    if not _plain_projections(mha):
+        # CustomMultiheadAttention whose q/k/v/out Linear leaves were swapped (the cim_qn_train surgery on the ReLU UNet,
+        # models/multihead_attention.py:34-37): every projection runs through its own leaf
+        q, k, v = linear(xn.t, mha.q_proj), linear(xn.t, mha.k_proj), linear(xn.t, mha.v_proj)
+        if training():
+            o = AG.AttentionFn.apply(q, torch.cat([k, v], dim=1), (a.n, heads, a.hw, a.hw, C // heads))
+        else:
+            o = rt.attention(q, k, v, a.n, heads, a.hw, a.hw, C // heads)
+        return _out_proj(o, mha, a)
     if training():
         w, b = _mha_params(mha)
         qkv, _ = AG.LinearFn.apply(xn.t, w, b, None, None, False)
@@ -415,6 +424,15 @@ def cross_attention(a, norm, mha, ctx_proj_mod, ctx, lk, cache=None):
         return _P().cross_attention(a, norm, mha, ctx_proj_mod, ctx, lk, cache=cache)
     C, heads = a.c, mha.num_heads
     xn = group_norm(a, norm)
+    if not _plain_projections(mha) or type(ctx_proj_mod) is not nn.Linear:
+        q = linear(xn.t, mha.q_proj)
+        cp = linear(ctx, ctx_proj_mod)
+        k, v = linear(cp, mha.k_proj), linear(cp, mha.v_proj)
+        if training():
+            o = AG.AttentionFn.apply(q, torch.cat([k, v], dim=1), (a.n, heads, a.hw, lk, C // heads))
+        else:
+            o = rt.attention(q, k, v, a.n, heads, a.hw, lk, C // heads)
+        return _out_proj(o, mha, a)
     if training():
         w, b = _mha_params(mha)
         _require_leaf(ctx_proj_mod, (nn.Linear,), "Linear")

@@ -569,3 +569,56 @@ def test_adda_conv_backward_vs_oracle(name):
         yard = ((p16[k].grad - want[k]).norm() / want[k].norm().clamp_min(1e-20)).item() if k in p16 else 0.0
         print(f"   {name} grad {k}: rel-L2 {err:.3e} (oracle under bf16 autocast: {yard:.3e})")
         assert err < max(8e-2 if want[k].dim() == 0 else 4e-2, 1.5 * yard), k
+
+
+# --------------------------------------------------------------------------------------- inside the ReLU UNet
+@pytest.mark.parametrize("kind", ["lsq", "adda"])
+def test_relu_unet_with_cim_leaves_runs_and_trains(kind):
+    """The ReLU / CustomMultiheadAttention UNet variant after the reference's module surgery (Model_Unet_train.py: every
+    nn.Conv2d — 3x3, 1x1 shortcut, 4x4 stride-2 down-sample, the 18 -> 3 mask conv — and every nn.Linear — time
+    embedding, q/k/v/out projections, context projections — becomes a cim_layers leaf; ConvTranspose2d stays float).
+    With 8-bit weights, no weight noise the quantised network tracks the float one; a training step gives every
+    parameter, step size and ADC gain a finite gradient."""
+    dev = _dev()
+    import torch.nn as nn
+    from cim_layers.layers_qn_lsq import Conv2d_qn_lsq, Linear_qn_lsq
+    from cim_layers.layers_qn_lsq_adda_cim import Conv2d_lsq_adda_cim, Linear_lsq_adda_cim, gen_weight_split_dict
+    from models.unet_cond_base_relu import Unet
+    from util import cond_of, l2err
+    fx = load_golden("unet_small_cond_relu")
+    cfg, inp = fx["config"], fx["inputs"]
+    torch.manual_seed(fx["seed"])
+    model = Unet(4, cfg).eval().to(dev)
+    x, t, cond = inp["x"].to(dev), inp["t"].to(dev), cond_of(inp, cfg, dev)
+    with torch.no_grad():
+        plain = model(x, t, cond)
+    n_leaves = sum(1 for m in model.modules() if type(m) in (nn.Conv2d, nn.Linear))
+    kw = dict(weight_bit=8, input_bit=8, output_bit=8, noise_scale=0.0)
+    if kind == "lsq":
+        _convert(model, Linear_qn_lsq, Conv2d_qn_lsq, **kw)
+        leaf_types = (Linear_qn_lsq, Conv2d_qn_lsq)
+    else:
+        kw.update(dac_bit=5, adc_bit=12, adc_gain_1_scale=9.071428571, adc_gain_range=[1 / 64, 1 / 64],
+                  adc_adjust_mode="current")
+        _convert(model, Linear_lsq_adda_cim, Conv2d_lsq_adda_cim, **kw)
+        leaf_types = (Linear_lsq_adda_cim, Conv2d_lsq_adda_cim)
+        for m in model.modules():
+            if type(m) in leaf_types:
+                m.weight_mapping_info = gen_weight_split_dict(m, [576, 2048])
+    leaves = [m for m in model.modules() if type(m) in leaf_types]
+    assert len(leaves) == n_leaves and n_leaves > 40
+    assert any(type(m) is Conv2d_qn_lsq or type(m) is Conv2d_lsq_adda_cim for m in leaves if getattr(m, "kernel_size", None) == (3, 3))
+    model.invalidate_plan()
+    with torch.no_grad():
+        q1 = model(x, t, cond)      # first forward initialises the step sizes (and ADC gains)
+        q2 = model(x, t, cond)
+    err = l2err(q2.cpu(), plain.cpu())
+    print(f"ReLU UNet with {kind} leaves ({n_leaves} of them): rel-L2 vs the float network {err:.3e}")
+    assert torch.isfinite(q1).all() and torch.isfinite(q2).all() and q2.shape == plain.shape
+    assert err < (0.25 if kind == "lsq" else 0.5)
+    model.train()
+    out = model(x, t, cond)
+    out.square().mean().backward()
+    torch.cuda.synchronize()
+    missing = [k for k, p in model.named_parameters() if p.requires_grad and (p.grad is None or not torch.isfinite(p.grad).all())]
+    assert not missing, missing[:6]

@@ -98,8 +98,32 @@ def test_conv_wrappers_structure_and_oracle():
     fresh = en.EnhanceLayerConv2d(torch.nn.Conv2d(8, 16, 3, padding=1), 0.05)   # identity initialisation (:399-405)
     g = fresh.groups
     assert torch.equal(fresh.conv_enhance.weight.view(16, 16 // g), torch.eye(16 // g).repeat(g, 1))
-    with pytest.raises(NotImplementedError):
-        en.EnhanceBranchConv2d_LoR(torch.nn.Conv2d(8, 8, 3, padding=1))
+    kxk = en.EnhanceBranchConv2d_LoR(torch.nn.Conv2d(8, 8, 3, padding=1))      # k x k originals: same search as the reference
+    assert kxk.enhance_branch_1.padding == (1, 1) and kxk.pool is None
+    assert en.EnhanceBranchConv2d_LoR(torch.nn.Conv2d(8, 8, 4, stride=2, padding=1)).pool is not None
+
+
+def test_kxk_branch_conv_oracle_vs_reference_golden():
+    """oracle/enhance_torch.py enhance_branch_conv against the real module's outputs and gradients for padded / strided
+    originals (the frame / pool / top-left crop of layers_enhance.py:509-531), and the product class's structure."""
+    import cim_qn_train.layers_enhance as en
+    from oracle import enhance_torch as OE
+    for c in load_golden("enhance_conv_kxk")["conv_cases"]:
+        conv = torch.nn.Conv2d(c["cin"], c["cout"], c["k"], stride=c["stride"], padding=c["pad"])
+        mod = en.EnhanceBranchConv2d_LoR(conv, c["ops_factor"], relu=c["relu"], sigmoid=c["sigmoid"])
+        assert (mod.enhance_branch_1.groups, mod.enhance_branch_2.groups) == tuple(c["groups"])
+        sd = mod.state_dict()
+        assert list(sd.keys()) == list(c["state"].keys()) and all(sd[k].shape == v.shape for k, v in c["state"].items())
+        ps = {k: v.clone().requires_grad_(True) for k, v in c["state"].items()}
+        x = c["x"].clone().requires_grad_(True)
+        y = OE.enhance_branch_conv(x, ps["original_conv.weight"], ps["original_conv.bias"], c["stride"], c["pad"],
+                                   ps["enhance_branch_1.weight"], ps["enhance_branch_1.bias"], c["groups"][0],
+                                   ps["enhance_branch_2.weight"], ps["enhance_branch_2.bias"], c["groups"][1],
+                                   ps["blend_factor"], c["relu"], c["sigmoid"])
+        assert torch.equal(y, c["y"])
+        (y * c["r"]).sum().backward()
+        for got, want in [(x.grad, c["dx"])] + [(ps[k].grad, g) for k, g in c["grads"].items()]:
+            assert (got - want).abs().max() <= 1e-5 * want.abs().max()
 
 
 def test_block_diagonal_dense_form_and_its_gradient():

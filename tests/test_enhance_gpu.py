@@ -76,6 +76,36 @@ def test_enhance_conv_forward_and_gradients_vs_reference(idx):
     assert float((x.grad.cpu() - c["dx"]).norm() / c["dx"].norm()) < 3e-2
 
 
+@pytest.mark.parametrize("idx", range(3))
+def test_enhance_branch_conv_kxk_vs_reference(idx):
+    """EnhanceBranchConv2d_LoR around 3x3 (padding 1) and 4x4 stride-2 originals: forward and every gradient against
+    the real reference module's (tests/golden/enhance_conv_kxk.pt)."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    dev = torch.device("cuda:0")
+    import cim_qn_train.layers_enhance as en
+    c = load_golden("enhance_conv_kxk")["conv_cases"][idx]
+    conv = torch.nn.Conv2d(c["cin"], c["cout"], c["k"], stride=c["stride"], padding=c["pad"])
+    mod = en.EnhanceBranchConv2d_LoR(conv, c["ops_factor"], relu=c["relu"], sigmoid=c["sigmoid"])
+    mod.load_state_dict(c["state"], strict=True)
+    mod = mod.to(dev)
+    with torch.no_grad():
+        y = mod.eval()(c["x"].to(dev))
+    l2 = float((y.cpu() - c["y"]).norm() / c["y"].norm())
+    print(f"enhance branch conv k={c['k']} s={c['stride']}: L2 {l2:.3e} max-norm {relerr(y.cpu(), c['y']):.3e}")
+    assert y.shape == c["y"].shape and l2 < 1e-2 and relerr(y.cpu(), c["y"]) < 2e-2
+    mod.train()
+    x = c["x"].to(dev).requires_grad_(True)
+    (mod(x) * c["r"].to(dev)).sum().backward()
+    for name, p in mod.named_parameters():
+        want = c["grads"][name]
+        assert p.grad is not None and torch.isfinite(p.grad).all(), name
+        err = float((p.grad.cpu() - want).norm() / (want.norm() + 1e-12))
+        gate = max(3e-2, 1.5 * c["ref_bf16_grad_err"][name])
+        assert err < gate, f"gradient of {name}: relative L2 {err:.3e} (gate {gate:.3e})"
+    assert float((x.grad.cpu() - c["dx"]).norm() / c["dx"].norm()) < 3e-2
+
+
 def test_dit_with_wrapped_linear_leaves_runs_and_trains():
     """Module surgery as progressive_qn_train.py:926-950 does it (setattr on the parent), on the small DiT fixture: with
     the blend closed (sigmoid(-30) = 0) the wrapped model reproduces the plain one; opened, every branch parameter and
