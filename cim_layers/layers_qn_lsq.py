@@ -15,6 +15,9 @@ from sdb200 import quant as Q
 from sdb200 import runtime as rt
 
 
+FUSED_WEIGHT_SIDE = True   # tests flip this to compare the fused kernels with the op-by-op torch formulation
+
+
 class _LsqMixin:
     def _init_lsq(self, weight_bit, input_bit, output_bit, noise_scale, input_quant, output_quant, weight_quant,
                   gain_noise_scale, offset_noise_scale):
@@ -74,6 +77,10 @@ class _LsqMixin:
         """(quantised + noisy weight as a differentiable fp32 tensor, w_scale)."""
         w, scale = self.weight, 1.0
         if self.weight_quant:
+            if FUSED_WEIGHT_SIDE and self.weight.is_cuda and self.weight.dtype == torch.float32:
+                # lazy init + LSQ quantiser + noise: two launches forward, two backward (csrc/wquant.cu)
+                return Q.weight_qn(self, self.weight, self.step_size_weight, self.weight_bit, isint, self.noise_scale,
+                                   self.weight_noise_unit)
             Q.init_weight_step_(self.step_size_weight, self.weight, self.weight_bit)
             w, scale = Q.quantize_weight(self.weight, self.step_size_weight, self.weight_bit, isint)
         return Q.add_weight_noise(w, self.noise_scale, self.weight_noise_unit), scale

@@ -363,6 +363,20 @@ int b200sd_lsq_quant_bwd(const void* dy, int64_t ld_dy, const void* x, int32_t x
                          int32_t mode, float* part, void* stream);
 int b200sd_lsq_quant_bwd_blocks(int64_t rows, int32_t c);
 
+/* Weight side of a cim_layers leaf in two launches: weight_quant_noise (cim_layers/layers_utils_lsq.py:48-64) = lazy
+ * step init (while *step == 1: *step = 1 / (1 / max|w| * qp)), weight_quant_lsq (quant_noise_utils.py:160-179; isint:
+ * q * s' / s') and add_noise (:92-98: + (max wq - min wq) * noise_scale * unit[i]; unit = the caller's N(0,1) draw, required
+ * when noise_scale != 0). w, out: fp32 [n]. scratch: b200sd_wq_scratch_floats() floats, ZEROED once by the caller and
+ * then kept with the layer: it carries the extrema and tie counts to b200sd_weight_qn_bwd, which returns
+ * dw = dL/dw (straight-through round, clamp mask, the noise term's gradient through max / min spread evenly over tied
+ * codes as torch does) and *dstep = dL/dstep including the 1/sqrt(qp n) gradient scale. grad_scale = that factor. */
+int b200sd_wq_scratch_floats(void);
+int b200sd_weight_qn(const float* w, int64_t n, float* step, float qp, float grad_scale, int32_t isint, int32_t lazy_init,
+                     float noise_scale, const float* unit, float* out, float* scratch, void* stream);
+int b200sd_weight_qn_bwd(const float* gout, const float* w, int64_t n, const float* step, float qp, float grad_scale,
+                         int32_t isint, float noise_scale, const float* unit, float* dw, float* dstep, float* scratch,
+                         void* stream);
+
 /* bit_split_tensor (cim_layers/layers_utils_adda.py:161-185): codes [rows, c] -> `slices` signed digits of slice_bit
  * bits stacked along rows, bf16 [slices * rows, c] — the DAC input slices. step == NULL: x holds the codes (bf16 or
  * fp32); step != NULL: x holds activations and the LSQ code (mode 1 above, with qp / grad_scale) is computed in the

@@ -472,6 +472,30 @@ __global__ void reduce_f32_kernel(const float* __restrict__ in, long long batch,
     }
 }
 
+// Few outputs, many rows (the step-size / ADC-gain gradients of the cim_layers: ONE output summed over hundreds of
+// per-CTA partials): one CTA per output, 256 strided partial sums and a shared-memory tree — fixed order, and ~10 us of a
+// single thread's serial loop becomes ~2 us (the LSQ training leg made 229 such launches per step: 2.3 ms).
+__global__ void __launch_bounds__(256)
+    reduce_f32_tall_kernel(const float* __restrict__ in, long long rows, long long cols, long long col_stride,
+                           float* __restrict__ out, int accumulate) {
+    pdl_enter();
+    __shared__ float red[256];
+    const long long o = blockIdx.x;                 // output index = b * cols + cidx
+    const long long b = o / cols, cidx = o - b * cols;
+    const float* p = in + b * rows * cols * col_stride + cidx * col_stride;
+    const long long step = cols * col_stride;
+    float s = 0.f;
+    for (long long r = threadIdx.x; r < rows; r += 256) s += p[r * step];
+    red[threadIdx.x] = s;
+    __syncthreads();
+#pragma unroll
+    for (int w = 128; w > 0; w >>= 1) {
+        if (threadIdx.x < w) red[threadIdx.x] += red[threadIdx.x + w];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[o] = accumulate ? out[o] + red[0] : red[0];
+}
+
 // Column sums of a bf16 [n, hw, ld] tensor. CTA = (64-channel slab, row block, image): 8 lanes x 16 B cover the
 // slab's 128 B of a row, 32 row lanes stride down the block. part[n][pb][c] holds the per-block sums; with `counter`
 // (one zeroed uint32 PER SLAB) the last CTA of each slab folds its 64 columns over the row blocks, so the tails of a
@@ -746,6 +770,12 @@ extern "C" int b200sd_reduce_f32(const float* in, int64_t batch, int64_t rows, i
                                  float* out, int accumulate, void* stream) {
     B200_REQUIRE(in && out && batch >= 0 && rows >= 0 && cols >= 0 && col_stride >= 1, "reduce_f32: bad arguments");
     if (batch * cols == 0) return B200SD_OK;
+    if (batch * cols <= 64 && rows >= 64) {
+        launch_k(reduce_f32_tall_kernel, (int)(batch * cols), 256, 0, as_stream(stream), in, rows, cols, col_stride, out,
+                 accumulate);
+        B200_CHECK_LAUNCH("reduce_f32");
+        return B200SD_OK;
+    }
     long long blocks = (batch * cols + 127) / 128;
     if (blocks > 4ll * sm_count()) blocks = 4ll * sm_count();
     launch_k(reduce_f32_kernel, (int)blocks, 128, 0, as_stream(stream), in, batch, rows, cols, col_stride, out, accumulate);

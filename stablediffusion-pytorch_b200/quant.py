@@ -90,6 +90,41 @@ def add_weight_noise(wq, n_scale, unit=None):
     return wq + (wq.max() - wq.min()) * n_scale * unit
 
 
+class WeightQnFn(Function):
+    """weight_quant_noise (cim_layers/layers_utils_lsq.py:48-64) as two kernels forward and two backward
+    (csrc/wquant.cu) instead of ~50 elementwise / reduction torch kernels per layer and step."""
+
+    @staticmethod
+    def forward(ctx, weight, step, qp, isint, n_scale, unit, scratch):
+        ctx.save_for_backward(weight, step, unit)
+        ctx.cfg = (qp, isint, n_scale, scratch)
+        return rt.weight_qn(weight, step, qp, isint, n_scale, unit, scratch)
+
+    @staticmethod
+    def backward(ctx, g):
+        weight, step, unit = ctx.saved_tensors
+        qp, isint, n_scale, scratch = ctx.cfg
+        dw, ds = rt.weight_qn_bwd(g, weight, step, qp, isint, n_scale, unit, scratch)
+        return dw, ds.reshape(step.shape).to(step.dtype), None, None, None, None, None
+
+
+def weight_qn(owner, weight, step, bits, isint, n_scale, unit=None):
+    """(quantised + noisy weight as a differentiable fp32 tensor, w_scale) of a cim_layers leaf `owner`."""
+    qp = qp_of(bits)
+    scratch = owner.__dict__.get("_wq_scratch")
+    if scratch is None or scratch.device != weight.device:
+        scratch = owner.__dict__["_wq_scratch"] = rt.wq_scratch(weight.device)
+    if n_scale != 0:
+        unit = torch.randn_like(weight) if unit is None else unit.to(weight).contiguous()
+    else:
+        unit = None
+    if torch.is_grad_enabled() and (weight.requires_grad or step.requires_grad):
+        w = WeightQnFn.apply(weight, step, qp, isint, float(n_scale), unit, scratch)
+    else:
+        w = rt.weight_qn(weight.detach(), step, qp, isint, float(n_scale), unit, scratch)
+    return w, ((1.0 / step).detach() if isint else 1.0)
+
+
 def rescale_step_sizes(module, weight_bit_old, input_bit_old, output_bit_old):
     """update_step_size (layers_utils_lsq.py:11-28): a bit-width change by d bits divides the step size by 2^d."""
     for name, new, old in (("weight", module.weight_bit, weight_bit_old), ("input", module.input_bit, input_bit_old),

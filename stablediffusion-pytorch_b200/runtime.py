@@ -22,7 +22,7 @@ EXPORTS = [
     "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16", "b200sd_im2col", "b200sd_col2im",
     "b200sd_layernorm_mod", "b200sd_layernorm_mod_bwd", "b200sd_rows_per_slot", "b200sd_gate_residual",
     "b200sd_gate_residual_bwd", "b200sd_relu_bwd", "b200sd_unpatchify", "b200sd_patchify",
-    "b200sd_lsq_init_step", "b200sd_lsq_quant", "b200sd_lsq_quant_bwd", "b200sd_lsq_quant_bwd_blocks", "b200sd_bit_split",
+    "b200sd_wq_scratch_floats", "b200sd_weight_qn", "b200sd_weight_qn_bwd", "b200sd_lsq_init_step", "b200sd_lsq_quant", "b200sd_lsq_quant_bwd", "b200sd_lsq_quant_bwd_blocks", "b200sd_bit_split",
     "b200sd_adc_combine", "b200sd_adc_bwd", "b200sd_adc_bwd_blocks", "b200sd_bit_split_bwd",
     "b200sd_pack_weights", "b200sd_pack_job_size", "b200sd_wgrad_scatter",
 ]
@@ -98,6 +98,8 @@ def lib():
         L.b200sd_groupnorm_apply.argtypes = [vp, i64, vp, i64, vp, i32, i32, i32, vp, i32, i32, vp, vp, i64, i64, i32, i32,
                                              f32, i32, vp]
         L.b200sd_rowblocks.argtypes = [i64, i64, i32]
+        L.b200sd_weight_qn.argtypes = [vp, i64, vp, f32, f32, i32, i32, f32, vp, vp, vp, vp]
+        L.b200sd_weight_qn_bwd.argtypes = [vp, vp, i64, vp, f32, f32, i32, f32, vp, vp, vp, vp, vp]
         L.b200sd_groupnorm_split.argtypes = [vp, i64, vp, i64, i32, vp, vp, i64, i64, i32, i32, f32, i32, vp]
         L.b200sd_split_f32.argtypes = [vp, i64, vp, i64, i32, i32, i64, i32, i32, vp]
         L.b200sd_groupnorm_bwd.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, vp, i32, i32, i32, vp, i32, i32, vp, vp, i64,
@@ -772,6 +774,34 @@ def lsq_init_step(x, step, qp):
 def lsq_grad_scale(qp, numel):
     """grad_scale_factor (quant_noise_utils.py:57-58); also fixes the value of the step the reference quantises with."""
     return 1.0 / ((qp * numel) ** 0.5)
+
+
+def wq_scratch(device):
+    """Zeroed per-layer scratch of the weight-side kernels (kept with the layer between forward and backward)."""
+    return torch.zeros(int(lib().b200sd_wq_scratch_floats()), device=device, dtype=torch.float32)
+
+
+def weight_qn(w, step, qp, isint, noise_scale, unit, scratch, lazy_init=True):
+    """Quantised (+ noisy) weight, fp32, same shape as w; lazily initialises `step` on the device."""
+    _cuda(w, torch.float32, "weight")
+    w = w.contiguous()
+    out = torch.empty_like(w)
+    check(lib().b200sd_weight_qn(_p(w), w.numel(), step.data_ptr(), float(qp), lsq_grad_scale(qp, w.numel()), int(isint),
+                                 int(lazy_init), float(noise_scale), _p(unit), _p(out), _p(scratch), stream_ptr()),
+          "weight_qn")
+    return out
+
+
+def weight_qn_bwd(g, w, step, qp, isint, noise_scale, unit, scratch):
+    """-> (dL/dw fp32 like w, dL/dstep fp32 0-dim)."""
+    g = g.float().contiguous()
+    w = w.contiguous()
+    dw = torch.empty_like(w)
+    ds = torch.empty((), device=w.device, dtype=torch.float32)
+    check(lib().b200sd_weight_qn_bwd(_p(g), _p(w), w.numel(), step.data_ptr(), float(qp), lsq_grad_scale(qp, w.numel()),
+                                     int(isint), float(noise_scale), _p(unit), _p(dw), _p(ds), _p(scratch), stream_ptr()),
+          "weight_qn_bwd")
+    return dw, ds
 
 
 def lsq_quant(x, step, qp, codes=False, out_dtype=torch.bfloat16, numel=None):

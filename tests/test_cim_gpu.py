@@ -622,3 +622,46 @@ def test_relu_unet_with_cim_leaves_runs_and_trains(kind):
     torch.cuda.synchronize()
     missing = [k for k, p in model.named_parameters() if p.requires_grad and (p.grad is None or not torch.isfinite(p.grad).all())]
     assert not missing, missing[:6]
+
+
+# --------------------------------------------------------------------------------- fused weight-side kernels
+@pytest.mark.parametrize("isint", [False, True])
+@pytest.mark.parametrize("noise", [0.0, 0.08])
+@pytest.mark.parametrize("shape,bits", [((192, 288), 4), ((64, 32, 3, 3), 8), ((3, 18, 1, 1), 4)])
+def test_fused_weight_side_matches_the_torch_formulation(isint, noise, shape, bits):
+    """csrc/wquant.cu (lazy step init + weight_quant_lsq + add_noise in two launches, backward in two) against the
+    op-by-op torch formulation of the same reference formulas (sdb200/quant.py, which the oracle tests pin to the
+    reference): quantised weights bit-identical, lazily initialised step identical, gradients of the weight and of the
+    step size (through the clamp mask, the straight-through round and the noise range's max / min with tied codes)."""
+    dev = _dev()
+    from sdb200 import quant as Q
+    g = torch.Generator().manual_seed(sum(shape) + bits)
+    w0 = (torch.randn(shape, generator=g) * 0.05).to(dev)
+    unit = torch.randn(shape, generator=g).to(dev) if noise else None
+    gout = torch.randn(shape, generator=g).to(dev)
+
+    def torch_path():
+        w = w0.clone().requires_grad_(True)
+        step = torch.ones((), device=dev, requires_grad=True)
+        Q.init_weight_step_(step, w, bits)
+        wq, _ = Q.quantize_weight(w, step, bits, isint)
+        out = Q.add_weight_noise(wq, noise, unit)
+        (out * gout).sum().backward()
+        return out.detach(), step.detach().clone(), w.grad, step.grad
+
+    def fused_path():
+        w = w0.clone().requires_grad_(True)
+        step = torch.ones((), device=dev, requires_grad=True)
+        owner = torch.nn.Module()
+        out, _ = Q.weight_qn(owner, w, step, bits, isint, noise, unit)
+        (out * gout).sum().backward()
+        out2, _ = Q.weight_qn(owner, w, step, bits, isint, noise, unit)     # second call: step no longer 1, scratch reused
+        return out.detach(), step.detach().clone(), w.grad, step.grad, out2.detach()
+
+    ro, rs, rdw, rds = torch_path()
+    fo, fs, fdw, fds, fo2 = fused_path()
+    torch.cuda.synchronize()
+    assert fs.item() == rs.item() and rs.item() != 1.0
+    assert torch.equal(fo, ro) and torch.equal(fo2, ro)
+    assert relerr(fdw, rdw) < 1e-5
+    assert abs(fds.item() - rds.item()) <= 2e-4 * max(abs(rds.item()), 1e-6), (fds.item(), rds.item())
