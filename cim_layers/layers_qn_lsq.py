@@ -63,15 +63,39 @@ class _LsqMixin:
                          act=act)
 
     # ---- the three quantisers ---------------------------------------------------------------------------------
+    def _needs_lazy_init(self, which):
+        """True while step_size_<which> may still be the untouched 1.0 (layers_utils_lsq.py:40-42,57-59,74-76 test it
+        on the host on every forward). Here the test runs on the device (absmax + conditional init: two launches); once a
+        forward outside stream capture has SEEN the step differ from 1 the two launches are dropped for good — 384 launches
+        per training step of the DiT-9L otherwise. Loading a state_dict re-arms the check."""
+        return which not in self.__dict__.setdefault("_lsq_ready", set())
+
+    def _note_lazy_init(self, which, step):
+        if which not in self.__dict__["_lsq_ready"] and not torch.cuda.is_current_stream_capturing() \
+                and step.item() != 1.0:
+            self.__dict__["_lsq_ready"].add(which)
+
     def _q_in(self, rows, numel, isint=False):
         if not self.input_quant:
             return rows
-        return Q.quantize_rows(rows, self.step_size_input, self.input_bit, codes=isint, numel=numel)
+        lazy = self._needs_lazy_init("input")
+        out = Q.quantize_rows(rows, self.step_size_input, self.input_bit, codes=isint, numel=numel, lazy_init=lazy)
+        if lazy:
+            self._note_lazy_init("input", self.step_size_input)
+        return out
 
     def _q_out(self, rows, numel):
         if not self.output_quant:
             return rows
-        return Q.quantize_rows(rows, self.step_size_output, self.output_bit, numel=numel)
+        lazy = self._needs_lazy_init("output")
+        out = Q.quantize_rows(rows, self.step_size_output, self.output_bit, numel=numel, lazy_init=lazy)
+        if lazy:
+            self._note_lazy_init("output", self.step_size_output)
+        return out
+
+    def _rearm_lazy_init(self):
+        self.__dict__.pop("_lsq_ready", None)     # loaded step sizes may be the untouched 1.0 again
+        self.__dict__["_gain_init_pending"] = True
 
     def _w_qn(self, isint=False):
         """(quantised + noisy weight as a differentiable fp32 tensor, w_scale)."""
@@ -195,3 +219,19 @@ class Linear_qn_lsq(nn.Linear, _LsqMixin):
                 rows = torch.nn.functional.pad(rows, (0, 8 - rows.shape[1] % 8))
             out = self.forward_rows(rows.contiguous())
         return out.reshape(*lead, self.out_features).to(x.dtype)
+
+
+def _rearm_on_load(cls):
+    """nn.Conv2d / nn.Linear come first in the MRO, so a mixin cannot override _load_from_state_dict: patch the class."""
+    base = cls._load_from_state_dict
+
+    def _load_from_state_dict(self, *a, **k):
+        self._rearm_lazy_init()
+        return base(self, *a, **k)
+
+    cls._load_from_state_dict = _load_from_state_dict
+    return cls
+
+
+_rearm_on_load(Conv2d_qn_lsq)
+_rearm_on_load(Linear_qn_lsq)

@@ -31,7 +31,7 @@ from sdb200 import engine as E
 from sdb200 import ops
 from sdb200 import quant as Q
 from sdb200 import runtime as rt
-from cim_layers.layers_qn_lsq import _LsqMixin
+from cim_layers.layers_qn_lsq import _LsqMixin, _rearm_on_load
 
 
 def gen_weight_split_dict(module, weight_block_size):
@@ -155,7 +155,9 @@ class _AddaMixin(_LsqMixin):
         if not self.input_quant:
             raise rt.B200Error("ADDA layers: the DAC needs quantised inputs (input_quant=True)")
         qp_in = Q.qp_of(self.input_bit)
-        rt.lsq_init_step(x, self.step_size_input, qp_in)
+        if self._needs_lazy_init("input"):
+            rt.lsq_init_step(x, self.step_size_input, qp_in)
+            self._note_lazy_init("input", self.step_size_input)
         w, w_scale = self._w_qn(isint=True)
         w = w.reshape(N, K)
         if Kp != K or Np != N:
@@ -193,7 +195,11 @@ class _AddaMixin(_LsqMixin):
         if bias is not None:
             y = y + bias.view(1, -1)
         if self.output_quant:
-            return Q.quantize_rows(y, self.step_size_output, self.output_bit, numel=M * N)
+            lazy = self._needs_lazy_init("output")
+            out = Q.quantize_rows(y, self.step_size_output, self.output_bit, numel=M * N, lazy_init=lazy)
+            if lazy:
+                self._note_lazy_init("output", self.step_size_output)
+            return out
         return y.to(torch.bfloat16)
 
     def _rows_in(self, rows, K):
@@ -202,9 +208,6 @@ class _AddaMixin(_LsqMixin):
             raise rt.B200Error("ADDA layers: input rows narrower than in_features rounded up to 8")
         return rows if rows.shape[1] == Kp else rows[:, :Kp].contiguous()
 
-    def _load_from_state_dict(self, *a, **k):
-        self.__dict__["_gain_init_pending"] = True
-        return super()._load_from_state_dict(*a, **k)
 
 
 class Linear_lsq_adda_cim(nn.Linear, _AddaMixin):
@@ -280,3 +283,7 @@ class Conv2d_lsq_adda_cim(nn.Conv2d, _AddaMixin):
         with torch.autocast("cuda", enabled=False):
             out = self.forward_act(E.Act.from_nchw(x)).to_nchw()
         return out.to(x.dtype)
+
+
+_rearm_on_load(Linear_lsq_adda_cim)
+_rearm_on_load(Conv2d_lsq_adda_cim)

@@ -39,6 +39,28 @@ __device__ __forceinline__ bool wq_last_cta(unsigned int* counter, unsigned int 
     return s_last != 0u;
 }
 
+// Fold of the per-CTA partials by ALL threads of the last CTA (a single thread walking a few hundred __ldcg loads took
+// ~10 us per launch — longer than the elementwise pass over an 83 K-element weight). Fixed order: thread t takes
+// partials t, t + 256, ...; warp shuffle tree; warp results in order.
+template <int OP>   // 0: sum, 1: max, 2: min
+__device__ __forceinline__ float wq_combine(float a, float b) {
+    return OP == 0 ? a + b : (OP == 1 ? fmaxf(a, b) : fminf(a, b));
+}
+template <int OP>
+__device__ __forceinline__ float wq_fold(const float* part, int stride, unsigned int count, float identity, float* red) {
+    float v = identity;
+    for (unsigned int k = threadIdx.x; k < count; k += WQ_THREADS) v = wq_combine<OP>(v, __ldcg(part + k * stride));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = wq_combine<OP>(v, __shfl_xor_sync(0xffffffffu, v, o));
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float r = red[0];
+#pragma unroll
+    for (int k = 1; k < WQ_THREADS / 32; ++k) r = wq_combine<OP>(r, red[k]);
+    return r;
+}
+
 // scratch layout (floats unless noted): [0] max|w|  [1] min w  [2] max w  [3] T  [4] d(step)  [5..6] uint tie counts
 // (max, min)  [7] uint arrival counter  [8 ..) per-CTA partials (3 per CTA in kernel 1, 1 per CTA in kernels 3 / 4)
 struct WqScratch {
@@ -70,16 +92,16 @@ __global__ void __launch_bounds__(WQ_THREADS)
         for (int k = 1; k < WQ_THREADS / 32; ++k) a = fmaxf(a, red[0][k]), lo = fminf(lo, red[1][k]), hi = fmaxf(hi, red[2][k]);
         sc->part[3 * blockIdx.x] = a, sc->part[3 * blockIdx.x + 1] = lo, sc->part[3 * blockIdx.x + 2] = hi;
     }
-    if (wq_last_cta(&sc->arrive, gridDim.x) && threadIdx.x == 0) {
-        for (unsigned k = 0; k < gridDim.x; ++k) {
-            a = fmaxf(a, __ldcg(&sc->part[3 * k]));
-            lo = fminf(lo, __ldcg(&sc->part[3 * k + 1]));
-            hi = fmaxf(hi, __ldcg(&sc->part[3 * k + 2]));
+    if (wq_last_cta(&sc->arrive, gridDim.x)) {
+        a = wq_fold<1>(sc->part, 3, gridDim.x, 0.f, red[0]);
+        lo = wq_fold<2>(sc->part + 1, 3, gridDim.x, INFINITY, red[1]);
+        hi = wq_fold<1>(sc->part + 2, 3, gridDim.x, -INFINITY, red[2]);
+        if (threadIdx.x == 0) {
+            sc->absmax = a, sc->wmin = lo, sc->wmax = hi;
+            sc->cnt_max = 0u, sc->cnt_min = 0u;
+            if (lazy_init && *step == 1.0f && a != 0.f)   // init_step_size: 1 / (1 / data_range * Qp), in that order
+                *step = __fdiv_rn(1.0f, __fmul_rn(__fdiv_rn(1.0f, a), qp));
         }
-        sc->absmax = a, sc->wmin = lo, sc->wmax = hi;
-        sc->cnt_max = 0u, sc->cnt_min = 0u;
-        if (lazy_init && *step == 1.0f && a != 0.f)   // init_step_size: 1 / (1 / data_range * Qp), in that order
-            *step = __fdiv_rn(1.0f, __fmul_rn(__fdiv_rn(1.0f, a), qp));
     }
 }
 
@@ -136,10 +158,9 @@ __global__ void __launch_bounds__(WQ_THREADS)
         for (int k = 1; k < WQ_THREADS / 32; ++k) a += red[k];
         sc->part[blockIdx.x] = a;
     }
-    if (wq_last_cta(&sc->arrive, gridDim.x) && threadIdx.x == 0) {
-        float t = 0.f;
-        for (unsigned k = 0; k < gridDim.x; ++k) t += __ldcg(&sc->part[k]);
-        sc->T = t;
+    if (wq_last_cta(&sc->arrive, gridDim.x)) {
+        const float t = wq_fold<0>(sc->part, 1, gridDim.x, 0.f, red);
+        if (threadIdx.x == 0) sc->T = t;
     }
 }
 
@@ -176,10 +197,9 @@ __global__ void __launch_bounds__(WQ_THREADS)
         for (int k = 1; k < WQ_THREADS / 32; ++k) acc += red[k];
         sc->part[blockIdx.x] = acc;
     }
-    if (wq_last_cta(&sc->arrive, gridDim.x) && threadIdx.x == 0) {
-        float t = 0.f;
-        for (unsigned k = 0; k < gridDim.x; ++k) t += __ldcg(&sc->part[k]);
-        *dstep = (isint ? t * inv_s : t) * g;   // grad_scale's backward: the 1/sqrt(Qp numel) factor
+    if (wq_last_cta(&sc->arrive, gridDim.x)) {
+        const float t = wq_fold<0>(sc->part, 1, gridDim.x, 0.f, red);
+        if (threadIdx.x == 0) *dstep = (isint ? t * inv_s : t) * g;   // grad_scale's backward: the 1/sqrt(Qp numel) factor
     }
 }
 
