@@ -97,14 +97,14 @@ class _LsqMixin:
         self.__dict__.pop("_lsq_ready", None)     # loaded step sizes may be the untouched 1.0 again
         self.__dict__["_gain_init_pending"] = True
 
-    def _w_qn(self, isint=False):
+    def _w_qn(self, isint=False, want_scale=True):
         """(quantised + noisy weight as a differentiable fp32 tensor, w_scale)."""
         w, scale = self.weight, 1.0
         if self.weight_quant:
             if FUSED_WEIGHT_SIDE and self.weight.is_cuda and self.weight.dtype == torch.float32:
                 # lazy init + LSQ quantiser + noise: two launches forward, two backward (csrc/wquant.cu)
                 return Q.weight_qn(self, self.weight, self.step_size_weight, self.weight_bit, isint, self.noise_scale,
-                                   self.weight_noise_unit)
+                                   self.weight_noise_unit, want_scale=want_scale)
             Q.init_weight_step_(self.step_size_weight, self.weight, self.weight_bit)
             w, scale = Q.quantize_weight(self.weight, self.step_size_weight, self.weight_bit, isint)
         return Q.add_weight_noise(w, self.noise_scale, self.weight_noise_unit), scale

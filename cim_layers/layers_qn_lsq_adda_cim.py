@@ -122,14 +122,12 @@ class _AddaMixin(_LsqMixin):
         """get_adc_scale (layers_utils_adda.py:40-49) on the device: clamp (straight-through), round the gain ('gain')
         or the range 1/gain (other modes), times the scale of gain 1."""
         g = self.adc_gain
-        gc = torch.clamp(g, self.adc_gain_min, self.adc_gain_max)
-        g = (gc - g).detach() + g
-        if self.adc_adjust_mode == 'gain':
-            g = (torch.round(g) - g).detach() + g
-        else:
-            r = 1 / g
-            g = 1 / ((torch.round(r) - r).detach() + r)
-        return g * self.adc_gain_1_scale
+        if g.is_cuda and g.dtype == torch.float32:
+            mode = self.adc_adjust_mode == 'gain'
+            if torch.is_grad_enabled() and g.requires_grad:
+                return Q.AdcScaleFn.apply(g, self.adc_gain_min, self.adc_gain_max, mode, self.adc_gain_1_scale)
+            return rt.adc_scale(g.detach(), self.adc_gain_min, self.adc_gain_max, mode, self.adc_gain_1_scale)[0]
+        raise rt.B200Error("ADDA layers: adc_gain must be an fp32 CUDA parameter")
 
     def _maybe_init_gain(self, partial):
         """init_adc_gain (layers_utils_adda.py:12-20), fired while adc_gain still equals adc_gain_min and the block
@@ -158,7 +156,7 @@ class _AddaMixin(_LsqMixin):
         if self._needs_lazy_init("input"):
             rt.lsq_init_step(x, self.step_size_input, qp_in)
             self._note_lazy_init("input", self.step_size_input)
-        w, w_scale = self._w_qn(isint=True)
+        w, _ = self._w_qn(isint=True, want_scale=False)   # w_scale = 1 / step_size_weight is read on the device
         w = w.reshape(N, K)
         if Kp != K or Np != N:
             w = torch.nn.functional.pad(w, (0, Kp - K, 0, Np - N))   # zero codes meet zero digits / unused columns
@@ -190,17 +188,17 @@ class _AddaMixin(_LsqMixin):
             acc = Q.AddaFn.apply(x, self.step_size_input, w, alpha, cfg)
         else:
             acc = Q.AddaFn._run(x, self.step_size_input.detach(), w.detach(), alpha.detach(), cfg)
-        in_scale = (1.0 / self.step_size_input).detach()
-        y = acc / w_scale / in_scale / alpha
-        if bias is not None:
-            y = y + bias.view(1, -1)
-        if self.output_quant:
-            lazy = self._needs_lazy_init("output")
-            out = Q.quantize_rows(y, self.step_size_output, self.output_bit, numel=M * N, lazy_init=lazy)
-            if lazy:
-                self._note_lazy_init("output", self.step_size_output)
-            return out
-        return y.to(torch.bfloat16)
+        # / w_scale / in_scale / adc_scale + bias and the output quantiser: one launch (csrc/adda_out.cu)
+        step_w = self.step_size_weight if self.weight_quant else None
+        step_out = self.step_size_output if self.output_quant else None
+        if bias is not None and bias.dtype != torch.float32:
+            bias = bias.float()
+        if step_out is not None and self._needs_lazy_init("output"):
+            y = rt.adda_out(acc.detach(), None if bias is None else bias.detach(), step_w, self.step_size_input,
+                            alpha.detach(), None, 0.0, M * N, 0)
+            rt.lsq_init_step(y, step_out, Q.qp_of(self.output_bit))
+            self._note_lazy_init("output", step_out)
+        return Q.adda_out(self, acc, alpha, bias, step_out, step_w, self.step_size_input, self.output_bit, M * N)
 
     def _rows_in(self, rows, K):
         Kp = (K + 7) // 8 * 8

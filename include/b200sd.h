@@ -357,10 +357,12 @@ int b200sd_lsq_quant(const void* x, int32_t x_f32, int64_t ld_x, void* y, int32_
                      int32_t c, const float* step, float qp, float grad_scale, int32_t mode, void* stream);
 
 /* Its backward (straight-through round, clamp mask, LSQ step-size gradient): dx bf16; part[b200sd_lsq_quant_bwd_blocks()]
- * = fp32 partial sums of d(step) before the 1/sqrt(qp * numel) gradient scale (quant_noise_utils.py:51-58). */
+ * = fp32 partial sums of d(step) before the 1/sqrt(qp * numel) gradient scale (quant_noise_utils.py:51-58).
+ * total / counter (both or neither): the last CTA folds the partials in fixed order and writes
+ * *total = sum(part) * grad_scale; counter = a zeroed uint32 that is returned to zero. */
 int b200sd_lsq_quant_bwd(const void* dy, int64_t ld_dy, const void* x, int32_t x_f32, int64_t ld_x, void* dx,
                          int64_t ld_dx, int64_t rows, int32_t c, const float* step, float qp, float grad_scale,
-                         int32_t mode, float* part, void* stream);
+                         int32_t mode, float* part, float* total, uint32_t* counter, void* stream);
 int b200sd_lsq_quant_bwd_blocks(int64_t rows, int32_t c);
 
 /* Weight side of a cim_layers leaf in two launches: weight_quant_noise (cim_layers/layers_utils_lsq.py:48-64) = lazy
@@ -398,12 +400,39 @@ int b200sd_adc_combine(const float* partial, int64_t ld_p, float* out, int64_t l
  * the block's dgrad / wgrad GEMMs); part[b200sd_adc_bwd_blocks()] = fp32 partial sums of d(adc_scale). */
 int b200sd_adc_bwd(const float* partial, int64_t ld_p, const float* dacc, int64_t ld_g, void* dpartial, int64_t ld_d,
                    int64_t rows, int32_t ncol, int32_t col0, int32_t slices, int32_t slice_bit, const float* adc_scale,
-                   float adc_range, const float* gain_noise, const float* offset_noise, float* part, void* stream);
+                   float adc_range, const float* gain_noise, const float* offset_noise, float* part, float* total,
+                   uint32_t* counter, void* stream);   /* total / counter as in b200sd_lsq_quant_bwd: *total = sum(part) */
 int b200sd_adc_bwd_blocks(int64_t rows, int32_t ncol);
 
 /* Backward of b200sd_bit_split (layers_utils_adda.py:178-183): dcodes = sum_k ddigits_k / (slices * 2^(k*slice_bit)). */
 int b200sd_bit_split_bwd(const void* ddigits, int64_t ld_d, void* dcodes, int64_t ld_q, int64_t rows, int32_t c,
                          int32_t slices, int32_t slice_bit, void* stream);
+
+/* Output side of a compute-in-memory layer in one launch (cim_layers/layers_qn_lsq_adda_cim.py:482-500 — the
+ * reference's `x = x / w_scale / in_scale / adc_scale`, `+ bias`, `data_quant_lsq(x, step_size_output)`):
+ *   y = acc / (1 / *step_w) / (1 / *step_in) / *adc_scale + bias[col]     (true divisions, that order; step_w may be
+ *                                                                          NULL: w_scale = 1)
+ *   mode 0: out = fp32 y;  mode 1: out = bf16 round(clamp(y / s', -qp, qp)) * s', s' from *step_out and grad_scale as
+ *   in b200sd_lsq_quant;  mode 2: out = bf16 y.      acc fp32 [rows, ld_a], c % 8 == 0, bias fp32 [c] or NULL. */
+int b200sd_adda_out(const float* acc, int64_t ld_a, const float* bias, const float* step_w, const float* step_in,
+                    const float* adc_scale, const float* step_out, float qp, float grad_scale, void* out, int64_t ld_o,
+                    int64_t rows, int32_t c, int32_t mode, void* stream);
+
+/* Backward of b200sd_adda_out (step_out NULL: no output quantiser). gout bf16 [rows, ld_g]; dacc fp32 [rows, c];
+ * dy bf16 [rows, c] or NULL = the gradient behind the quantiser's clamp mask (its column sums are d bias);
+ * res[0] = d(step_out) * grad_scale, res[1] = d(adc_scale) through the division. scratch: zero-initialised floats,
+ * b200sd_adda_out_scratch_floats() of them, private to one layer (the last CTA folds the per-CTA partials). */
+int b200sd_adda_out_bwd(const void* gout, int64_t ld_g, const float* acc, int64_t ld_a, const float* bias,
+                        const float* step_w, const float* step_in, const float* adc_scale, const float* step_out,
+                        float qp, float grad_scale, float* dacc, void* dy, int64_t rows, int32_t c, float* scratch,
+                        float* res, void* stream);
+int b200sd_adda_out_scratch_floats(void);
+
+/* get_adc_scale (cim_layers/layers_utils_adda.py:40-49) on the device: out[0] = adc_scale of *gain (clamped to
+ * [gain_min, gain_max] straight-through; gain_mode != 0 rounds the gain, 0 rounds the range 1 / gain) * scale1,
+ * out[1] = d adc_scale / d gain. */
+int b200sd_adc_scale(const float* gain, float gain_min, float gain_max, int32_t gain_mode, float scale1, float* out,
+                     void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------------
  * Weight-side data movement of a training step (csrc/pack.cu).

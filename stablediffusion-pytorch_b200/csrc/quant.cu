@@ -44,6 +44,38 @@ __device__ __forceinline__ float effective_step(float s, float g) {
     return __fadd_rn(__fsub_rn(s, y), y);
 }
 
+// Tail of a reduction kernel: the block's partial is published, and when `total` is given the LAST CTA to arrive folds
+// all partials in fixed order (all 256 threads: strided partial sums, shuffle tree, warps in order) and writes
+// *total = sum * scale — no second launch for a [blocks] -> [1] reduction and no torch multiply behind it.
+// `counter` is a zeroed uint32 that the tail returns to zero.
+__device__ __forceinline__ void q_publish_and_fold(float block_sum, float* __restrict__ part, float* __restrict__ total,
+                                                   unsigned int* counter, float scale, float* wsum) {
+    if (threadIdx.x == 0) part[blockIdx.x] = block_sum;
+    if (!total) return;
+    __shared__ unsigned int s_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int t = atomicAdd(counter, 1u);
+        s_last = (t == gridDim.x - 1u) ? 1u : 0u;
+        if (s_last) *counter = 0u;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    float v = 0.f;
+    for (unsigned int k = threadIdx.x; k < gridDim.x; k += blockDim.x) v += __ldcg(part + k);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+        for (int w = 0; w < 8; ++w) t += wsum[w];
+        *total = t * scale;
+    }
+}
+
 // ---- max |x| over a [rows, c] tensor (pitch ld) into *slot as float bits (non-negative floats order like uints)
 template <typename T>
 __global__ void absmax_kernel(const T* __restrict__ x, long long ld, long long rows, int c, unsigned int* slot) {
@@ -111,7 +143,8 @@ template <typename TI>
 __global__ void __launch_bounds__(256)
     lsq_quant_bwd_kernel(const __nv_bfloat16* __restrict__ dy, long long ld_dy, const TI* __restrict__ x, long long ld_x,
                          __nv_bfloat16* __restrict__ dx, long long ld_dx, long long rows, int c,
-                         const float* __restrict__ step, float qp, float g, int mode, float* __restrict__ part) {
+                         const float* __restrict__ step, float qp, float g, int mode, float* __restrict__ part,
+                         float* __restrict__ sum_out, unsigned int* counter) {
     pdl_enter();
     __shared__ float wsum[8];
     const float s = effective_step(*step, g);
@@ -140,11 +173,12 @@ __global__ void __launch_bounds__(256)
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = acc;
     __syncthreads();
+    float t = 0.f;
     if (threadIdx.x == 0) {
-        float t = 0.f;
         for (int w = 0; w < 8; ++w) t += wsum[w];
-        part[blockIdx.x] = mode == 0 ? t : t * inv_s;
+        t = mode == 0 ? t : t * inv_s;
     }
+    q_publish_and_fold(t, part, sum_out, counter, g, wsum);   // total = d(step) with the LSQ gradient scale applied
 }
 
 // bit_split_tensor (layers_utils_adda.py:161-185): a (nearly) integer code v -> `slices` signed digits of slice_bit
@@ -153,10 +187,13 @@ __global__ void __launch_bounds__(256)
 //   msb = min(lsb + slice_bit, x_bit - 1)
 // evaluated in fp32 like the reference (its codes are q * s' / s', which can sit one ulp below the integer q — the
 // floor then yields q - 1; reproduced, not corrected).
+// Divisions by 2^lsb / 2^msb are written as multiplications by the exact reciprocal power of two: the same fp32
+// result (codes are < 2^9, nowhere near the subnormal range) without four IEEE division sequences per element and
+// slice, which made this kernel instruction-bound (14.6 us per launch in the ADDA training leg).
 __device__ __forceinline__ float split_digit(float v, int lsb, int msb, int slice_bit) {
-    const float a = __fdiv_rn(v, static_cast<float>(1 << lsb));
+    const float a = __fmul_rn(v, __int_as_float((127 - lsb) << 23));
     const float shift = floorf(fabsf(a)) * (a > 0.f ? 1.f : (a < 0.f ? -1.f : 0.f));
-    const float t = __fdiv_rn(v, static_cast<float>(1 << msb));
+    const float t = __fmul_rn(v, __int_as_float((127 - msb) << 23));
     const float resid = (t >= 0.f ? floorf(t) : ceilf(t)) * static_cast<float>(1 << slice_bit);
     return shift - resid;
 }
@@ -233,7 +270,8 @@ __global__ void __launch_bounds__(256)
     adc_bwd_kernel(const float* __restrict__ p, long long ld_p, const float* __restrict__ dacc, long long ld_g,
                    __nv_bfloat16* __restrict__ dp, long long ld_d, long long rows, int ncol, int col0, int slices,
                    int slice_bit, const float* __restrict__ alpha_p, float R, const float* __restrict__ gain_noise,
-                   const float* __restrict__ offset_noise, float* __restrict__ part) {
+                   const float* __restrict__ offset_noise, float* __restrict__ part, float* __restrict__ sum_out,
+                   unsigned int* counter) {
     pdl_enter();
     __shared__ float wsum[8];
     const float alpha = *alpha_p;
@@ -261,11 +299,10 @@ __global__ void __launch_bounds__(256)
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = acc;
     __syncthreads();
-    if (threadIdx.x == 0) {
-        float t = 0.f;
+    float t = 0.f;
+    if (threadIdx.x == 0)
         for (int w = 0; w < 8; ++w) t += wsum[w];
-        part[blockIdx.x] = t;
-    }
+    q_publish_and_fold(t, part, sum_out, counter, 1.f, wsum);
 }
 
 // Backward of bit_split_tensor: d code = sum_k d digit_k / (slices * 2^(k*slice_bit)) (layers_utils_adda.py:178-183:
@@ -351,18 +388,19 @@ extern "C" int b200sd_lsq_quant_bwd_blocks(int64_t rows, int32_t c) { return q_g
 
 extern "C" int b200sd_lsq_quant_bwd(const void* dy, int64_t ld_dy, const void* x, int32_t x_f32, int64_t ld_x, void* dx,
                                     int64_t ld_dx, int64_t rows, int32_t c, const float* step, float qp, float g,
-                                    int32_t mode, float* part, void* stream) {
+                                    int32_t mode, float* part, float* total, uint32_t* counter, void* stream) {
     B200_REQUIRE(dy && x && dx && step && part && rows > 0 && qp >= 1.f && (mode == 0 || mode == 1),
                  "lsq_quant_bwd: bad arguments");
+    B200_REQUIRE((total == nullptr) == (counter == nullptr), "lsq_quant_bwd: total and counter come together");
     B200_REQUIRE(Q_SHAPE_OK(c, ld_dy) && Q_SHAPE_OK(c, ld_x) && Q_SHAPE_OK(c, ld_dx), "lsq_quant_bwd: channels / pitches");
     const int grid = q_grid(rows * (c / 8), 256, 4);
     cudaStream_t st = as_stream(stream);
     if (x_f32)
         launch_k(lsq_quant_bwd_kernel<float>, grid, 256, 0, st, static_cast<const __nv_bfloat16*>(dy), ld_dy, static_cast<const float*>(x), ld_x,
-                                                          static_cast<__nv_bfloat16*>(dx), ld_dx, rows, c, step, qp, g, mode, part);
+                                                          static_cast<__nv_bfloat16*>(dx), ld_dx, rows, c, step, qp, g, mode, part, total, counter);
     else
         launch_k(lsq_quant_bwd_kernel<__nv_bfloat16>, grid, 256, 0, st, static_cast<const __nv_bfloat16*>(dy), ld_dy, static_cast<const __nv_bfloat16*>(x), ld_x,
-                                                                  static_cast<__nv_bfloat16*>(dx), ld_dx, rows, c, step, qp, g, mode, part);
+                                                                  static_cast<__nv_bfloat16*>(dx), ld_dx, rows, c, step, qp, g, mode, part, total, counter);
     B200_CHECK_LAUNCH("lsq_quant_bwd");
     return B200SD_OK;
 }
@@ -408,14 +446,15 @@ extern "C" int b200sd_adc_bwd_blocks(int64_t rows, int32_t ncol) { return q_grid
 extern "C" int b200sd_adc_bwd(const float* partial, int64_t ld_p, const float* dacc, int64_t ld_g, void* dpartial,
                               int64_t ld_d, int64_t rows, int32_t ncol, int32_t col0, int32_t slices, int32_t slice_bit,
                               const float* adc_scale, float adc_range, const float* gain_noise, const float* offset_noise,
-                              float* part, void* stream) {
+                              float* part, float* total, uint32_t* counter, void* stream) {
     B200_REQUIRE(partial && dacc && dpartial && adc_scale && part && rows > 0 && ncol > 0 && col0 >= 0 && slices >= 1 &&
                      slice_bit >= 1, "adc_bwd: bad arguments");
+    B200_REQUIRE((total == nullptr) == (counter == nullptr), "adc_bwd: total and counter come together");
     B200_REQUIRE((gain_noise == nullptr) == (offset_noise == nullptr), "adc_bwd: gain and offset noise come together");
     B200_REQUIRE(ld_d >= ncol, "adc_bwd: gradient pitch too small");
     launch_k(adc_bwd_kernel, q_grid(rows * ncol, 256, 4), 256, 0, as_stream(stream), 
         partial, ld_p, dacc, ld_g, static_cast<__nv_bfloat16*>(dpartial), ld_d, rows, ncol, col0, slices, slice_bit,
-        adc_scale, adc_range, gain_noise, offset_noise, part);
+        adc_scale, adc_range, gain_noise, offset_noise, part, total, counter);
     B200_CHECK_LAUNCH("adc_bwd");
     return B200SD_OK;
 }

@@ -24,8 +24,11 @@ def pack_conv_weight(w):
 def pack_linear_weight(w):
     """nn.Linear weight [N, K] -> bf16 [N, K_pad64]."""
     n, k = w.shape
-    m = torch.zeros(n, _pad64(k), device=w.device, dtype=torch.bfloat16)
-    m[:, :k] = w.detach().to(torch.bfloat16)
+    kp = _pad64(k)
+    m = torch.empty(n, kp, device=w.device, dtype=torch.bfloat16)
+    if kp != k:
+        m[:, k:].zero_()
+    m[:, :k].copy_(w.detach())      # one kernel: dtype conversion and any stride (transposed views) in the copy
     return m
 
 

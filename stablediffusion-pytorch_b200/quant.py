@@ -108,8 +108,9 @@ class WeightQnFn(Function):
         return dw, ds.reshape(step.shape).to(step.dtype), None, None, None, None, None
 
 
-def weight_qn(owner, weight, step, bits, isint, n_scale, unit=None):
-    """(quantised + noisy weight as a differentiable fp32 tensor, w_scale) of a cim_layers leaf `owner`."""
+def weight_qn(owner, weight, step, bits, isint, n_scale, unit=None, want_scale=True):
+    """(quantised + noisy weight as a differentiable fp32 tensor, w_scale) of a cim_layers leaf `owner`; want_scale
+    False skips the 1 / step launch for callers that read the step size on the device themselves."""
     qp = qp_of(bits)
     scratch = owner.__dict__.get("_wq_scratch")
     if scratch is None or scratch.device != weight.device:
@@ -122,7 +123,60 @@ def weight_qn(owner, weight, step, bits, isint, n_scale, unit=None):
         w = WeightQnFn.apply(weight, step, qp, isint, float(n_scale), unit, scratch)
     else:
         w = rt.weight_qn(weight.detach(), step, qp, isint, float(n_scale), unit, scratch)
-    return w, ((1.0 / step).detach() if isint else 1.0)
+    return w, ((1.0 / step).detach() if isint and want_scale else 1.0)
+
+
+class AdcScaleFn(Function):
+    """get_adc_scale (cim_layers/layers_utils_adda.py:40-49) as one launch; backward = one multiplication."""
+
+    @staticmethod
+    def forward(ctx, gain, gmin, gmax, gain_mode, scale1):
+        out = rt.adc_scale(gain.detach(), gmin, gmax, gain_mode, scale1)
+        ctx.save_for_backward(out)
+        ctx.like = (gain.shape, gain.dtype)
+        return out[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        (out,) = ctx.saved_tensors
+        return (g * out[1]).reshape(ctx.like[0]).to(ctx.like[1]), None, None, None, None
+
+
+class AddaOutFn(Function):
+    """`acc / w_scale / in_scale / adc_scale + bias` followed by the LSQ output quantiser (step_out None: none) —
+    cim_layers/layers_qn_lsq_adda_cim.py:482-500 — as one launch forward and one backward (csrc/adda_out.cu).
+    w_scale = 1 / step_w and in_scale = 1 / step_in are detached in the reference: they receive no gradient here."""
+
+    @staticmethod
+    def forward(ctx, acc, alpha, bias, step_out, step_w, step_in, qp, numel, scratch):
+        ctx.save_for_backward(acc, alpha, bias, step_out, step_w, step_in)
+        ctx.cfg = (qp, numel, scratch)
+        return rt.adda_out(acc, bias, step_w, step_in, alpha, step_out, qp, numel, 1 if step_out is not None else 2)
+
+    @staticmethod
+    def backward(ctx, g):
+        acc, alpha, bias, step_out, step_w, step_in = ctx.saved_tensors
+        qp, numel, scratch = ctx.cfg
+        if g.dtype != torch.bfloat16 or g.stride(1) != 1 or g.stride(0) % 8:
+            g = g.to(torch.bfloat16).contiguous()
+        want_b = bias is not None and ctx.needs_input_grad[2]
+        dacc, dy, res = rt.adda_out_bwd(g, acc, bias, step_w, step_in, alpha, step_out, qp, numel, scratch, want_b)
+        dbias = rt.colsum(dy, 1, dy.shape[0], dy.shape[1]).to(bias.dtype) if want_b else None
+        dstep = res[0].reshape(step_out.shape).to(step_out.dtype) if step_out is not None else None
+        return dacc, res[1].reshape(alpha.shape).to(alpha.dtype), dbias, dstep, None, None, None, None, None
+
+
+def adda_out(owner, acc, alpha, bias, step_out, step_w, step_in, bits, numel):
+    """Output side of a compute-in-memory leaf `owner`: bf16 rows [M, Np]."""
+    qp = qp_of(bits) if step_out is not None else 0.0
+    scratch = owner.__dict__.get("_ao_scratch")
+    if scratch is None or scratch.device != acc.device:
+        scratch = owner.__dict__["_ao_scratch"] = rt.adda_out_scratch(acc.device)
+    if bias is not None and bias.dtype != torch.float32:
+        bias = bias.float()
+    if torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in (acc, alpha, bias, step_out)):
+        return AddaOutFn.apply(acc, alpha, bias, step_out, step_w, step_in, qp, numel, scratch)
+    return rt.adda_out(acc, bias, step_w, step_in, alpha, step_out, qp, numel, 1 if step_out is not None else 2)
 
 
 def rescale_step_sizes(module, weight_bit_old, input_bit_old, output_bit_old):
@@ -137,11 +191,22 @@ def rescale_step_sizes(module, weight_bit_old, input_bit_old, output_bit_old):
 from . import ops  # noqa: E402
 
 
+def _covers(ranges, width):
+    """True when the (start, length) ranges tile [0, width) without a gap (overlaps / repeats allowed)."""
+    end = 0
+    for a, n in sorted(set(ranges)):
+        if a > end:
+            return False
+        end = max(end, a + n)
+    return end >= width
+
+
 class AddaFn(Function):
     """Integer accumulation of a compute-in-memory layer (cim_layers/layers_qn_lsq_adda_cim.py:430-480):
     acc[M, N] = sum over mapped blocks and DAC slices of 2^(k*slice_bit) * ADC(alpha * digits_k[:, rows] @ W[cols, rows]^T).
     x: bf16 activation rows; w: fp32 [N, K] weight codes (+ noise), differentiable; alpha: 0-dim ADC scale.
-    Backward recomputes digits and block products (no fp32 block products are kept between forward and backward):
+    Backward recomputes the block products (no fp32 block products are kept between forward and backward; the bf16
+    digits and the packed weight blocks are):
     per block one ADC-backward kernel, a dgrad GEMM (accumulated over column blocks through the residual epilogue) and a
     wgrad GEMM; then bit-split and LSQ-code backward."""
 
@@ -149,7 +214,8 @@ class AddaFn(Function):
     def forward(ctx, x, step_in, w, alpha, cfg):
         ctx.save_for_backward(x, step_in, w, alpha)
         ctx.cfg = cfg
-        return AddaFn._run(x, step_in.detach(), w.detach(), alpha.detach(), cfg)
+        ctx.keep = {}      # DAC digits and packed weight blocks of this forward, reused by its backward
+        return AddaFn._run(x, step_in.detach(), w.detach(), alpha.detach(), cfg, ctx.keep)
 
     @staticmethod
     def _digits(x, step_in, cfg):
@@ -157,15 +223,25 @@ class AddaFn(Function):
                             numel=cfg["numel_in"])
 
     @staticmethod
-    def _run(x, step_in, w, alpha, cfg):
+    def _run(x, step_in, w, alpha, cfg, keep=None):
         M, N = x.shape[0], w.shape[0]
         digits = AddaFn._digits(x, step_in, cfg)
+        if keep is not None:
+            keep["digits"], keep["packed"] = digits, []
         a1 = alpha.reshape(1).float()
-        out = torch.zeros(M, N, device=x.device, dtype=torch.float32)
+        # the first block of a column range stores, later row blocks accumulate; a zero fill only when the blocks
+        # leave columns uncovered (padding columns of a layer whose width is not a multiple of 8)
+        covered = _covers(((c0, cn) for _, _, c0, cn in cfg["blocks"]), N)
+        out = (torch.empty if covered else torch.zeros)(M, N, device=x.device, dtype=torch.float32)
+        seen = set()
         for r0, rn, c0, cn in cfg["blocks"]:
-            part = rt.linear(digits[:, r0:r0 + rn], ops.pack_linear_weight(w[c0:c0 + cn, r0:r0 + rn]), out_dtype=torch.float32)
+            wp = ops.pack_linear_weight(w[c0:c0 + cn, r0:r0 + rn])
+            if keep is not None:
+                keep["packed"].append(wp)
+            part = rt.linear(digits[:, r0:r0 + rn], wp, out_dtype=torch.float32)
             rt.adc_combine(part, out, M, cn, c0, cfg["slices"], cfg["slice_bit"], a1, cfg["R"], cfg["gain_noise"],
-                           cfg["offset_noise"])
+                           cfg["offset_noise"], accumulate=not covered or c0 in seen)
+            seen.add(c0)
         return out
 
     @staticmethod
@@ -178,23 +254,34 @@ class AddaFn(Function):
         dacc = dacc.float().contiguous()
         wd = w.detach()
         a1 = alpha.detach().reshape(1).float()
-        digits = AddaFn._digits(x, step_in.detach(), cfg)
-        ddigits = torch.zeros(S * M, K, device=x.device, dtype=torch.bfloat16)
-        dw = torch.zeros(N, K, device=x.device, dtype=torch.float32)
-        dalpha = torch.zeros(1, device=x.device, dtype=torch.float32)
+        keep = ctx.keep
+        digits = keep["digits"] if "digits" in keep else AddaFn._digits(x, step_in.detach(), cfg)
+        packed = keep.get("packed")
+        blocks = cfg["blocks"]
+        rows_covered = _covers(((r0, rn) for r0, rn, _, _ in blocks), K)
+        ddigits = (torch.empty if rows_covered else torch.zeros)(S * M, K, device=x.device, dtype=torch.bfloat16)
+        single = len(blocks) == 1 and blocks[0][1] == K and blocks[0][3] == N
+        dw = None if single else torch.zeros(N, K, device=x.device, dtype=torch.float32)
+        das = []
         seen = set()
-        for r0, rn, c0, cn in cfg["blocks"]:
+        for bi, (r0, rn, c0, cn) in enumerate(blocks):
             wb = wd[c0:c0 + cn, r0:r0 + rn]
-            part = rt.linear(digits[:, r0:r0 + rn], ops.pack_linear_weight(wb), out_dtype=torch.float32)
+            part = rt.linear(digits[:, r0:r0 + rn], packed[bi] if packed else ops.pack_linear_weight(wb),
+                             out_dtype=torch.float32)
             dp, da = rt.adc_bwd(part, dacc, M, cn, c0, S, sb, a1, cfg["R"], cfg["gain_noise"], cfg["offset_noise"])
-            dalpha = dalpha + da
+            das.append(da)
             view = ddigits[:, r0:r0 + rn]
             rt.linear(dp[:, :cn], ops.pack_linear_weight(wb.t()), out=view, residual=view if r0 in seen else None)
             seen.add(r0)
             kp = (rn + 63) // 64 * 64
             dwp = rt.wgrad([rt.make_src(digits[:, r0:r0 + rn], 1, 1, S * M, rn, ld=K)], [(0, 0, 0, 0, kp // 64)],
                            rt.make_src(dp, 1, 1, S * M, cn, ld=dp.stride(0)), cn, 1, 1, S * M)
-            dw[c0:c0 + cn, r0:r0 + rn] = dwp[:, :rn]
+            if single:
+                dw = dwp[:, :rn]
+            else:
+                dw[c0:c0 + cn, r0:r0 + rn] = dwp[:, :rn]
+        dalpha = das[0] if len(das) == 1 else torch.cat(das).sum()
+        keep.clear()
         dxq = rt.bit_split_bwd(ddigits, M, K, S, sb)
         dx, ds = rt.lsq_quant_bwd(dxq, x, step_in.detach(), cfg["qp_in"], codes=True, numel=cfg["numel_in"])
         return (dx if ctx.needs_input_grad[0] else None), ds.reshape(step_in.shape), dw, \

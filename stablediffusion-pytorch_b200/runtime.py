@@ -24,6 +24,7 @@ EXPORTS = [
     "b200sd_gate_residual_bwd", "b200sd_relu_bwd", "b200sd_unpatchify", "b200sd_patchify",
     "b200sd_wq_scratch_floats", "b200sd_weight_qn", "b200sd_weight_qn_bwd", "b200sd_lsq_init_step", "b200sd_lsq_quant", "b200sd_lsq_quant_bwd", "b200sd_lsq_quant_bwd_blocks", "b200sd_bit_split",
     "b200sd_adc_combine", "b200sd_adc_bwd", "b200sd_adc_bwd_blocks", "b200sd_bit_split_bwd",
+    "b200sd_adda_out", "b200sd_adda_out_bwd", "b200sd_adda_out_scratch_floats", "b200sd_adc_scale",
     "b200sd_pack_weights", "b200sd_pack_job_size", "b200sd_wgrad_scatter",
 ]
 
@@ -138,11 +139,14 @@ def lib():
         L.b200sd_patchify.argtypes = [vp, vp, i64, i64, i32, i32, i32, i32, i32, vp]
         L.b200sd_lsq_init_step.argtypes = [vp, i32, i64, i64, i32, vp, f32, vp, vp]
         L.b200sd_lsq_quant.argtypes = [vp, i32, i64, vp, i32, i64, i64, i32, vp, f32, f32, i32, vp]
-        L.b200sd_lsq_quant_bwd.argtypes = [vp, i64, vp, i32, i64, vp, i64, i64, i32, vp, f32, f32, i32, vp, vp]
+        L.b200sd_lsq_quant_bwd.argtypes = [vp, i64, vp, i32, i64, vp, i64, i64, i32, vp, f32, f32, i32, vp, vp, vp, vp]
         L.b200sd_lsq_quant_bwd_blocks.argtypes = [i64, i32]
         L.b200sd_bit_split.argtypes = [vp, i32, i64, vp, i64, i64, i32, i32, i32, i32, vp, f32, f32, vp]
         L.b200sd_adc_combine.argtypes = [vp, i64, vp, i64, i64, i32, i32, i32, i32, vp, f32, vp, vp, i32, vp]
-        L.b200sd_adc_bwd.argtypes = [vp, i64, vp, i64, vp, i64, i64, i32, i32, i32, i32, vp, f32, vp, vp, vp, vp]
+        L.b200sd_adc_bwd.argtypes = [vp, i64, vp, i64, vp, i64, i64, i32, i32, i32, i32, vp, f32, vp, vp, vp, vp, vp, vp]
+        L.b200sd_adda_out.argtypes = [vp, i64, vp, vp, vp, vp, vp, f32, f32, vp, i64, i64, i32, i32, vp]
+        L.b200sd_adda_out_bwd.argtypes = [vp, i64, vp, i64, vp, vp, vp, vp, vp, f32, f32, vp, vp, i64, i32, vp, vp, vp]
+        L.b200sd_adc_scale.argtypes = [vp, f32, f32, i32, f32, vp, vp]
         L.b200sd_adc_bwd_blocks.argtypes = [i64, i32]
         L.b200sd_bit_split_bwd.argtypes = [vp, i64, vp, i64, i64, i32, i32, i32, vp]
         L.b200sd_pack_weights.argtypes = [vp, i32, i32, vp]
@@ -825,11 +829,11 @@ def lsq_quant_bwd(dy, x, step, qp, codes=False, numel=None):
     dx = torch.empty(rows, c, device=x.device, dtype=torch.bfloat16)
     nb = int(lib().b200sd_lsq_quant_bwd_blocks(rows, c))
     part = torch.empty(nb, device=x.device, dtype=torch.float32)
+    ds = torch.empty((), device=x.device, dtype=torch.float32)
     check(lib().b200sd_lsq_quant_bwd(_p(dy), dy.stride(0), _p(x), int(x.dtype == torch.float32), x.stride(0), _p(dx), c,
-                                     rows, c, step.data_ptr(), float(qp), g, 1 if codes else 0, _p(part), stream_ptr()),
-          "lsq_quant_bwd")
-    ds = reduce_f32(part, 1, nb, 1, 1, torch.empty(1, device=x.device, dtype=torch.float32))
-    return dx, (ds * g).reshape(())
+                                     rows, c, step.data_ptr(), float(qp), g, 1 if codes else 0, _p(part), _p(ds),
+                                     tail_counter(x.device), stream_ptr()), "lsq_quant_bwd")
+    return dx, ds
 
 
 def bit_split(x, slices, slice_bit, x_bit, step=None, qp=0.0, numel=None):
@@ -858,10 +862,53 @@ def adc_bwd(partial, dacc, rows, ncol, col0, slices, slice_bit, adc_scale, adc_r
     dp = (torch.zeros if ld != ncol else torch.empty)(slices * rows, ld, device=partial.device, dtype=torch.bfloat16)
     nb = int(lib().b200sd_adc_bwd_blocks(rows, ncol))
     part = torch.empty(nb, device=partial.device, dtype=torch.float32)
+    da = torch.empty(1, device=partial.device, dtype=torch.float32)
     check(lib().b200sd_adc_bwd(_p(partial), partial.stride(0), _p(dacc), dacc.stride(0), _p(dp), ld, rows, ncol, col0,
                                slices, slice_bit, adc_scale.data_ptr(), float(adc_range), _p(gain_noise), _p(offset_noise),
-                               _p(part), stream_ptr()), "adc_bwd")
-    return dp, reduce_f32(part, 1, nb, 1, 1, torch.empty(1, device=partial.device, dtype=torch.float32))
+                               _p(part), _p(da), tail_counter(partial.device), stream_ptr()), "adc_bwd")
+    return dp, da
+
+
+def adda_out_scratch(device):
+    """Zeroed per-layer scratch of b200sd_adda_out_bwd."""
+    return torch.zeros(int(lib().b200sd_adda_out_scratch_floats()), device=device, dtype=torch.float32)
+
+
+def adda_out(acc, bias, step_w, step_in, adc_scale, step_out, qp, numel, mode):
+    """y = acc / w_scale / in_scale / adc_scale + bias and the LSQ output quantiser in one launch.
+    mode 0: fp32 y; 1: bf16 quantised; 2: bf16 y."""
+    _cuda(acc, torch.float32, "acc")
+    rows, c = acc.shape
+    out = torch.empty(rows, c, device=acc.device, dtype=torch.float32 if mode == 0 else torch.bfloat16)
+    g = lsq_grad_scale(qp, numel) if mode == 1 else 0.0
+    check(lib().b200sd_adda_out(_p(acc), acc.stride(0), _p(bias), None if step_w is None else step_w.data_ptr(),
+                                step_in.data_ptr(), adc_scale.data_ptr(), step_out.data_ptr() if mode == 1 else None,
+                                float(qp), g, _p(out), c, rows, c, mode, stream_ptr()), "adda_out")
+    return out
+
+
+def adda_out_bwd(gout, acc, bias, step_w, step_in, adc_scale, step_out, qp, numel, scratch, want_dy):
+    """-> (d acc fp32 [rows, c], d y bf16 [rows, c] or None, res fp32 [2] = (d step_out incl. the LSQ gradient scale,
+    d adc_scale through the division)). step_out None: no output quantiser."""
+    rows, c = acc.shape
+    dacc = torch.empty(rows, c, device=acc.device, dtype=torch.float32)
+    dy = torch.empty(rows, c, device=acc.device, dtype=torch.bfloat16) if want_dy else None
+    res = torch.empty(2, device=acc.device, dtype=torch.float32)
+    g = lsq_grad_scale(qp, numel) if step_out is not None else 0.0
+    check(lib().b200sd_adda_out_bwd(_p(gout), gout.stride(0), _p(acc), acc.stride(0), _p(bias),
+                                    None if step_w is None else step_w.data_ptr(), step_in.data_ptr(),
+                                    adc_scale.data_ptr(), None if step_out is None else step_out.data_ptr(), float(qp), g,
+                                    _p(dacc), _p(dy), rows, c, _p(scratch), _p(res), stream_ptr()), "adda_out_bwd")
+    return dacc, dy, res
+
+
+def adc_scale(gain, gain_min, gain_max, gain_mode, scale1):
+    """-> fp32 [2]: (adc_scale, d adc_scale / d gain) of the 0-dim fp32 ADC gain."""
+    _cuda(gain, torch.float32, "adc_gain")
+    out = torch.empty(2, device=gain.device, dtype=torch.float32)
+    check(lib().b200sd_adc_scale(gain.data_ptr(), float(gain_min), float(gain_max), 1 if gain_mode else 0, float(scale1),
+                                 _p(out), stream_ptr()), "adc_scale")
+    return out
 
 
 def bit_split_bwd(ddigits, rows, c, slices, slice_bit):

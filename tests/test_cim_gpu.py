@@ -665,3 +665,89 @@ def test_fused_weight_side_matches_the_torch_formulation(isint, noise, shape, bi
     assert torch.equal(fo, ro) and torch.equal(fo2, ro)
     assert relerr(fdw, rdw) < 1e-5
     assert abs(fds.item() - rds.item()) <= 2e-4 * max(abs(rds.item()), 1e-6), (fds.item(), rds.item())
+
+
+@pytest.mark.parametrize("rows,c,bias,quant", [(1024, 768, True, True), (77, 24, False, True), (300, 64, True, False)])
+def test_adda_output_side_matches_the_torch_formulation(rows, c, bias, quant):
+    """b200sd_adda_out / _bwd (one launch each way) against the chain of torch ops they replace — the reference's
+    `x / w_scale / in_scale / adc_scale + bias` and data_quant_lsq (layers_qn_lsq_adda_cim.py:482-500): forward
+    bit-exact (same IEEE divisions in the same order), gradients to fp32 rounding."""
+    dev = _dev()
+    from sdb200 import quant as Q
+    g = torch.Generator().manual_seed(rows + c)
+    acc = torch.round(torch.randn(rows, c, generator=g) * 900).to(dev)
+    step_w = torch.tensor(0.0123, device=dev)
+    step_in = torch.tensor(0.0456, device=dev)
+    b = (torch.randn(c, generator=g) * 0.1).to(dev) if bias else None
+    gout = (torch.randn(rows, c, generator=g) * 0.01).to(torch.bfloat16).to(dev)
+    bits = 8
+    qp = float(Q.qp_of(bits))
+
+    def leaves():
+        a = acc.clone().requires_grad_(True)
+        al = torch.tensor(0.1417, device=dev, requires_grad=True)
+        so = torch.tensor(0.0211, device=dev, requires_grad=True) if quant else None
+        bb = b.clone().requires_grad_(True) if bias else None
+        return a, al, so, bb
+
+    a, al, so, bb = leaves()
+    y = a / (1.0 / step_w).detach() / (1.0 / step_in).detach() / al
+    if bias:
+        y = y + bb.view(1, -1)
+    if quant:
+        s = Q._grad_scale(so, 1.0 / (qp * rows * c) ** 0.5)
+        ref = Q._round_ste(torch.clamp(y / s, -qp, qp)) * s
+    else:
+        ref = y
+    ref.backward(gout.float())
+
+    class Owner:
+        pass
+    a2, al2, so2, bb2 = leaves()
+    out = Q.adda_out(Owner(), a2, al2, bb2, so2, step_w, step_in, bits, rows * c)
+    assert out.dtype == torch.bfloat16
+    assert torch.equal(out, ref.detach().to(torch.bfloat16))
+    out.backward(gout)
+    assert relerr(a2.grad, a.grad) < 1e-5
+    assert relerr(al2.grad, al.grad) < 1e-4
+    if bias:
+        assert relerr(bb2.grad, bb.grad) < 1e-4
+    if quant:
+        assert relerr(so2.grad, so.grad) < 1e-4
+    # a second call in a row reuses the layer's scratch (the last CTA re-arms the arrival counter)
+    a3, al3, so3, bb3 = leaves()
+    owner = Owner()
+    for _ in range(2):
+        for t in (a3, al3, so3, bb3):
+            if t is not None:
+                t.grad = None
+        Q.adda_out(owner, a3, al3, bb3, so3, step_w, step_in, bits, rows * c).backward(gout)
+    assert torch.equal(a3.grad, a2.grad) and torch.equal(al3.grad, al2.grad)
+
+
+@pytest.mark.parametrize("mode", ["gain", "current"])
+def test_adc_scale_kernel_matches_the_torch_formulation(mode):
+    """get_adc_scale (layers_utils_adda.py:40-49) as one launch: value bit-exact, gradient through the straight-through
+    clamp / round as autograd gives it."""
+    dev = _dev()
+    from sdb200 import quant as Q
+    cases = {"gain": ((1 / 64, 1 / 64, 1 / 64), (3.3, 1.0, 8.0), (0.013, 1 / 128, 1 / 16), (20.0, 1.0, 8.0)),
+             # 'current' rounds the range 1 / gain: gains above 2 would round it to zero (the reference divides by it)
+             "current": ((1 / 64, 1 / 64, 1 / 64), (0.013, 1 / 128, 1 / 16), (0.3, 1 / 128, 0.4), (0.001, 1 / 128, 0.4))}
+    for g0, lo, hi in cases[mode]:
+        scale1 = 9.071428571
+        gain = torch.tensor(g0, device=dev, requires_grad=True)
+        gc = torch.clamp(gain, lo, hi)
+        g = (gc - gain).detach() + gain
+        if mode == "gain":
+            g = (torch.round(g) - g).detach() + g
+        else:
+            r = 1 / g
+            g = 1 / ((torch.round(r) - r).detach() + r)
+        ref = g * scale1
+        ref.backward()
+        gain2 = torch.tensor(g0, device=dev, requires_grad=True)
+        got = Q.AdcScaleFn.apply(gain2, lo, hi, mode == "gain", scale1)
+        assert got.item() == ref.item()
+        got.backward()
+        assert abs(gain2.grad.item() - gain.grad.item()) <= 1e-5 * abs(gain.grad.item())
