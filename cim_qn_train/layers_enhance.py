@@ -157,7 +157,7 @@ class GroupedLinear(_RowsModule):
     def forward_rows(self, rows, act=None):
         """bf16 rows [M, >= in_features rounded up to 8] (zeros beyond in_features) -> bf16 rows [M, out_features rounded
         up to 8], padding columns zero."""
-        return _dense_rows(rows, self.dense_weight(), self.bias.reshape(-1), self.out_features, act)
+        return _grouped_rows(self, rows, self.weight, self.bias, self.out_features, act)
 
 
 def _dense_rows(rows, w_dense, bias, n_out, act=None):
@@ -179,6 +179,96 @@ def _dense_rows(rows, w_dense, bias, n_out, act=None):
             raise rt.B200Error("grouped map: only ReLU may follow")
         y = torch.relu(y)
     return y
+
+
+class _GroupedFn(torch.autograd.Function):
+    """y = x @ blockdiag(W)^T + b for a (g, og, ig) parameter W: the bf16 dense matrix and its transpose live in
+    persistent zero-initialised buffers of `owner` whose diagonal blocks one launch rewrites (b200sd_blockdiag_pack);
+    the backward reads the parameter gradient back out of the dense wgrad (b200sd_blockdiag_gather)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, owner, act):
+        g, og, ig = weight.shape
+        n_out = g * og
+        dense, dense_t = _dense_buffers(owner, weight)
+        rt.blockdiag_pack(weight.detach(), dense, dense_t)
+        out = torch.empty(x.shape[0], _pad8(n_out), device=x.device, dtype=torch.bfloat16)[:, :n_out]
+        rt.linear(x, dense, bias=None if bias is None else bias.detach().reshape(-1).float(), out=out, act=act)
+        ctx.save_for_backward(x, weight, out if act else None)
+        ctx.owner, ctx.bias_like = owner, None if bias is None else (bias.shape, bias.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight, y_act = ctx.saved_tensors
+        g, og, ig = weight.shape
+        n_out, kp = g * og, x.shape[1]
+        M = x.shape[0]
+        dy = AG._rows(dy, n_out)
+        if y_act is not None:
+            dy = rt.relu_bwd(dy, y_act)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            _, dense_t = _dense_buffers(ctx.owner, weight)      # written by this step's forward
+            dx = torch.empty(M, kp, device=x.device, dtype=torch.bfloat16)
+            rt.linear(dy, dense_t, out=dx)
+        if ctx.needs_input_grad[1]:
+            k64 = (kp + 63) // 64 * 64
+            dwp = rt.wgrad([rt.make_src(x, 1, 1, M, kp, ld=x.stride(0))], [(0, 0, 0, 0, k64 // 64)],
+                           rt.make_src(dy, 1, 1, M, n_out, ld=dy.stride(0)), n_out, 1, 1, M)
+            dw = rt.blockdiag_gather(dwp, g, og, ig).to(weight.dtype)
+        if ctx.bias_like is not None and ctx.needs_input_grad[2]:
+            db = rt.colsum(dy, 1, M, n_out) if n_out % 8 == 0 else dy.float().sum(0)
+            db = db.reshape(ctx.bias_like[0]).to(ctx.bias_like[1])
+        return dx, dw, db, None, None
+
+
+def _dense_buffers(owner, weight):
+    """Persistent bf16 (dense [g*og, pad64(pad8(g*ig))], dense_t [pad8(g*ig), pad64(g*og)]) of a grouped map, zero
+    outside the diagonal blocks (only those are ever rewritten)."""
+    g, og, ig = weight.shape
+    key = (weight.device, g, og, ig)
+    ent = owner.__dict__.get("_dense_bf16")
+    if ent is None or ent[0] != key:
+        kp = _pad8(g * ig)
+        dense = torch.zeros(g * og, (kp + 63) // 64 * 64, device=weight.device, dtype=torch.bfloat16)
+        dense_t = torch.zeros(kp, (g * og + 63) // 64 * 64, device=weight.device, dtype=torch.bfloat16)
+        ent = owner.__dict__["_dense_bf16"] = (key, dense, dense_t)
+    return ent[1], ent[2]
+
+
+def _grouped_rows(owner, rows, weight3, bias, n_out, act=None):
+    """rows [M, >= pad8(K)] (zeros beyond the true K) through the block-diagonal map of the (g, og, ig) parameter
+    `weight3` -> [M, n_out rounded up to 8], padding columns zero; one scatter launch + one tcgen05 GEMM."""
+    g, og, ig = weight3.shape
+    kp = _pad8(g * ig)
+    if weight3.dtype != torch.float32 or not weight3.is_cuda:
+        return _dense_rows(rows, _block_diag_dense(owner, weight3, g, og, ig), None if bias is None else bias.reshape(-1),
+                           n_out, act)
+    if rows.shape[1] < kp:
+        raise rt.B200Error("grouped map: input rows narrower than the channel count rounded up to 8")
+    x = rows if rows.shape[1] == kp else rows[:, :kp].contiguous()
+    fuse = act if n_out % 8 == 0 else None   # (a fused ReLU's backward wants an unpadded, contiguous output)
+    if E.training():
+        y = _GroupedFn.apply(x, weight3, bias, owner, fuse)
+    else:
+        dense, _ = _dense_buffers(owner, weight3)
+        rt.blockdiag_pack(weight3.detach(), dense)
+        y = rt.linear(x, dense, bias=None if bias is None else bias.detach().reshape(-1).float(), act=fuse)
+    if n_out % 8:
+        y = torch.nn.functional.pad(y[:, :n_out], (0, _pad8(n_out) - n_out))
+    if act is not None and fuse is None:
+        if act != "relu":
+            raise rt.B200Error("grouped map: only ReLU may follow")
+        y = torch.relu(y)
+    return y
+
+
+def _conv_rows(conv, rows, act=None):
+    """A grouped 1x1 nn.Conv2d on pixel rows (its [co, ci/g, 1, 1] weight is the (g, co/g, ci/g) block parameter)."""
+    g = conv.groups
+    return _grouped_rows(conv, rows, conv.weight.view(g, conv.out_channels // g, conv.in_channels // g), conv.bias,
+                         conv.out_channels, act)
 
 
 def _block_diag_dense(owner, weight, g, og, ig):
@@ -245,7 +335,7 @@ class EnhanceLayerConv2d(_ActModule):
 
     def forward_act(self, a):
         y = E.conv2d(a, self.original_conv)
-        rows = _dense_rows(_clean_rows(y), _conv1x1_dense(self.conv_enhance), self.conv_enhance.bias, y.c)
+        rows = _conv_rows(self.conv_enhance, _clean_rows(y))
         return E.Act(rows, y.n, y.h, y.w, y.c)
 
 
@@ -287,15 +377,12 @@ class EnhanceBranchConv2d_LoR(_ActModule):
     def forward_act(self, a):
         y = E.conv2d(a, self.original_conv)
         b1, b2 = self.enhance_branch_1, self.enhance_branch_2
-        enh = _dense_rows(_clean_rows(a), _conv1x1_dense(b1), b1.bias, b1.out_channels, act="relu" if self.relu else None)
-        enh = _dense_rows(enh, _conv1x1_dense(b2), b2.bias, b2.out_channels)
+        enh = _conv_rows(b1, _clean_rows(a), act="relu" if self.relu else None)
+        enh = _conv_rows(b2, enh)
         p, st = self.padding[0], self.stride[0]
         if p != 0 or st != 1 or (y.h, y.w) != (a.h, a.w):
             enh = self._frame(enh[:, :y.c], a, y, p, st)
-        out = self.merge_feature_map(y.t[:, :y.c], enh[:, :y.c]).to(torch.bfloat16)
-        if y.c % 8:
-            out = torch.nn.functional.pad(out, (0, _pad8(y.c) - y.c))
-        return E.Act(out.contiguous(), y.n, y.h, y.w, y.c)
+        return E.Act(self._merge_rows(y.t, enh, y.c), y.n, y.h, y.w, y.c)
 
 
 def _frame(self, z, a, y, p, st):
@@ -375,20 +462,54 @@ class EnhanceBranchLinear_LoR(_RowsModule):
             self.std_enhance, self.mean_enhance = torch.std_mean(enhance_output)
         return combined
 
-    def forward_rows(self, rows, act=None):
-        n = self.out_features
-        orig = _leaf_rows(self.original_linear, rows)
-        enh = self.enhance_branch_1.forward_rows(rows, act="relu" if self.relu else None)
-        enh = self.enhance_branch_2.forward_rows(enh)
+    def _merge_rows(self, orig, enh, n, act=None):
+        """merge_feature_map on bf16 rows -> bf16 rows [M, n rounded up to 8]: one launch (blend + the four moments the
+        trainer logs; backward one launch) when the rows are 8-column aligned, the torch formulation otherwise."""
+        if act not in (None, "relu"):
+            raise rt.B200Error(f"{type(self).__name__}: only ReLU may follow the wrapped layer")
+        fused = n % 8 == 0 and orig.dtype == enh.dtype == torch.bfloat16 and orig.stride(1) == enh.stride(1) == 1 \
+            and orig.stride(0) % 8 == 0 and enh.stride(0) % 8 == 0 and self.blend_factor.dtype == torch.float32
+        if fused:
+            if torch.is_grad_enabled() and any(t.requires_grad for t in (orig, enh, self.blend_factor)):
+                return _BlendFn.apply(orig, enh, self.blend_factor, self, act == "relu", n)
+            out, stats = rt.blend(orig, enh, self.blend_factor, self.sigmoid, act == "relu", n)
+            self.std_ori, self.mean_ori, self.std_enhance, self.mean_enhance = stats.unbind(0)
+            return out
         out = self.merge_feature_map(orig[:, :n], enh[:, :n]).to(torch.bfloat16)
         if act is not None:
-            if act != "relu":
-                raise rt.B200Error("EnhanceBranchLinear_LoR: only ReLU may follow the wrapped Linear")
             out = torch.relu(out)
         if n % 8:
             out = torch.nn.functional.pad(out, (0, _pad8(n) - n))
         return out.contiguous()
 
+    def forward_rows(self, rows, act=None):
+        orig = _leaf_rows(self.original_linear, rows)
+        enh = self.enhance_branch_1.forward_rows(rows, act="relu" if self.relu else None)
+        enh = self.enhance_branch_2.forward_rows(enh)
+        return self._merge_rows(orig, enh, self.out_features, act)
+
+
+class _BlendFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, orig, enh, factor, owner, relu, n):
+        out, stats = rt.blend(orig, enh, factor, owner.sigmoid, relu, n)
+        owner.std_ori, owner.mean_ori, owner.std_enhance, owner.mean_enhance = stats.unbind(0)
+        ctx.save_for_backward(orig, enh, factor, out if relu else None)
+        ctx.cfg = (owner.sigmoid, n)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        orig, enh, factor, out = ctx.saved_tensors
+        sigmoid, n = ctx.cfg
+        d_orig, d_enh, d_f = rt.blend_bwd(AG._rows(g, n), orig, enh, out, factor, sigmoid, n)
+        if orig.shape[1] != n:
+            d_orig = torch.nn.functional.pad(d_orig, (0, orig.shape[1] - n))
+        if enh.shape[1] != n:
+            d_enh = torch.nn.functional.pad(d_enh, (0, enh.shape[1] - n))
+        return d_orig, d_enh, d_f.reshape(factor.shape).to(factor.dtype), None, None, None
+
 
 EnhanceBranchConv2d_LoR.merge_feature_map = EnhanceBranchLinear_LoR.merge_feature_map
+EnhanceBranchConv2d_LoR._merge_rows = EnhanceBranchLinear_LoR._merge_rows
 

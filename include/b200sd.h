@@ -435,6 +435,36 @@ int b200sd_adc_scale(const float* gain, float gain_min, float gain_max, int32_t 
                      void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------------
+ * Enhance wrappers (cim_qn_train/layers_enhance.py), csrc/enhance.cu.
+ * ------------------------------------------------------------------------------------------------------------- */
+
+/* Block-diagonal dense form of a GroupedLinear / grouped 1x1 Conv2d parameter (layers_enhance.py:324-365):
+ * dense[(g*out_group + r) * ld_d + g*in_group + c] = bf16(w[g, r, c]) and, when dense_t is non-NULL, its transpose
+ * dense_t[(g*in_group + c) * ld_t + g*out_group + r]. Only the diagonal blocks are written: the caller keeps both
+ * buffers zero-initialised between calls. */
+int b200sd_blockdiag_pack(const float* w, int32_t groups, int32_t out_group, int32_t in_group, void* dense, int64_t ld_d,
+                          void* dense_t, int64_t ld_t, void* stream);
+
+/* dw[g, r, c] = dense[(g*out_group + r) * ld + g*in_group + c]: the parameter gradient out of a dense weight gradient. */
+int b200sd_blockdiag_gather(const float* dense, int64_t ld, int32_t groups, int32_t out_group, int32_t in_group, float* dw,
+                            void* stream);
+
+/* merge_feature_map (layers_enhance.py:596-608) in one launch: out = orig * (1 - s) + enh * s, s = sigmoid(*blend) when
+ * `sigmoid` else *blend, optional ReLU; bf16 [rows, c] operands, c % 8 == 0. stats (optional) receives std(orig),
+ * mean(orig), std(enh), mean(enh) (unbiased std, as Tensor.std()); it needs part[b200sd_blend_part_floats()] and a
+ * zeroed uint32 counter (returned to zero). */
+int b200sd_blend(const void* orig, int64_t ld_a, const void* enh, int64_t ld_b, const float* blend, int32_t sigmoid,
+                 int32_t relu, void* out, int64_t ld_o, int64_t rows, int32_t c, float* part, uint32_t* counter,
+                 float* stats, void* stream);
+int b200sd_blend_part_floats(void);
+
+/* Its backward: d_orig = g (1 - s), d_enh = g s (bf16 [rows, c] contiguous), *d_blend = sum g (enh - orig) times
+ * s (1 - s) when `sigmoid`. out: the forward result when a ReLU was fused (masks g), else NULL. */
+int b200sd_blend_bwd(const void* g, int64_t ld_g, const void* orig, int64_t ld_a, const void* enh, int64_t ld_b,
+                     const void* out, int64_t ld_o, const float* blend, int32_t sigmoid, void* d_orig, void* d_enh,
+                     int64_t rows, int32_t c, float* part, uint32_t* counter, float* d_blend, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
  * Weight-side data movement of a training step (csrc/pack.cu).
  * ------------------------------------------------------------------------------------------------------------- */
 

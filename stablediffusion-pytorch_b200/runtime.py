@@ -25,6 +25,7 @@ EXPORTS = [
     "b200sd_wq_scratch_floats", "b200sd_weight_qn", "b200sd_weight_qn_bwd", "b200sd_lsq_init_step", "b200sd_lsq_quant", "b200sd_lsq_quant_bwd", "b200sd_lsq_quant_bwd_blocks", "b200sd_bit_split",
     "b200sd_adc_combine", "b200sd_adc_bwd", "b200sd_adc_bwd_blocks", "b200sd_bit_split_bwd",
     "b200sd_adda_out", "b200sd_adda_out_bwd", "b200sd_adda_out_scratch_floats", "b200sd_adc_scale",
+    "b200sd_blockdiag_pack", "b200sd_blockdiag_gather", "b200sd_blend", "b200sd_blend_bwd", "b200sd_blend_part_floats",
     "b200sd_pack_weights", "b200sd_pack_job_size", "b200sd_wgrad_scatter",
 ]
 
@@ -147,6 +148,10 @@ def lib():
         L.b200sd_adda_out.argtypes = [vp, i64, vp, vp, vp, vp, vp, f32, f32, vp, i64, i64, i32, i32, vp]
         L.b200sd_adda_out_bwd.argtypes = [vp, i64, vp, i64, vp, vp, vp, vp, vp, f32, f32, vp, vp, i64, i32, vp, vp, vp]
         L.b200sd_adc_scale.argtypes = [vp, f32, f32, i32, f32, vp, vp]
+        L.b200sd_blockdiag_pack.argtypes = [vp, i32, i32, i32, vp, i64, vp, i64, vp]
+        L.b200sd_blockdiag_gather.argtypes = [vp, i64, i32, i32, i32, vp, vp]
+        L.b200sd_blend.argtypes = [vp, i64, vp, i64, vp, i32, i32, vp, i64, i64, i32, vp, vp, vp, vp]
+        L.b200sd_blend_bwd.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, vp, i32, vp, vp, i64, i32, vp, vp, vp, vp]
         L.b200sd_adc_bwd_blocks.argtypes = [i64, i32]
         L.b200sd_bit_split_bwd.argtypes = [vp, i64, vp, i64, i64, i32, i32, i32, vp]
         L.b200sd_pack_weights.argtypes = [vp, i32, i32, vp]
@@ -909,6 +914,52 @@ def adc_scale(gain, gain_min, gain_max, gain_mode, scale1):
     check(lib().b200sd_adc_scale(gain.data_ptr(), float(gain_min), float(gain_max), 1 if gain_mode else 0, float(scale1),
                                  _p(out), stream_ptr()), "adc_scale")
     return out
+
+
+# ------------------------------------------------------------------------------------------------ Enhance wrappers
+def blockdiag_pack(w, dense, dense_t=None):
+    """Write the diagonal blocks of a (g, og, ig) fp32 parameter into its persistent bf16 dense matrix (and transpose)."""
+    _cuda(w, torch.float32, "grouped weight")
+    g, og, ig = w.shape
+    check(lib().b200sd_blockdiag_pack(_p(w), g, og, ig, _p(dense), dense.stride(0), _p(dense_t),
+                                      0 if dense_t is None else dense_t.stride(0), stream_ptr()), "blockdiag_pack")
+    return dense
+
+
+def blockdiag_gather(dense_grad, g, og, ig):
+    """(g, og, ig) fp32 parameter gradient out of a dense fp32 [g*og, ld] weight gradient."""
+    dw = torch.empty(g, og, ig, device=dense_grad.device, dtype=torch.float32)
+    check(lib().b200sd_blockdiag_gather(_p(dense_grad), dense_grad.stride(0), g, og, ig, _p(dw), stream_ptr()),
+          "blockdiag_gather")
+    return dw
+
+
+def blend(orig, enh, factor, sigmoid, relu, c, want_stats=True):
+    """-> (out bf16 [rows, c], stats fp32 [4] = std/mean of orig, std/mean of enh, or None)."""
+    rows = orig.shape[0]
+    out = torch.empty(rows, c, device=orig.device, dtype=torch.bfloat16)
+    stats = part = None
+    if want_stats:
+        stats = torch.empty(4, device=orig.device, dtype=torch.float32)
+        part = torch.empty(int(lib().b200sd_blend_part_floats()), device=orig.device, dtype=torch.float32)
+    check(lib().b200sd_blend(_p(orig), orig.stride(0), _p(enh), enh.stride(0), factor.data_ptr(), int(sigmoid), int(relu),
+                             _p(out), c, rows, c, _p(part), tail_counter(orig.device) if want_stats else None, _p(stats),
+                             stream_ptr()), "blend")
+    return out, stats
+
+
+def blend_bwd(g, orig, enh, out, factor, sigmoid, c):
+    """-> (d orig bf16, d enh bf16, d blend_factor fp32 0-dim)."""
+    rows = orig.shape[0]
+    d_orig = torch.empty(rows, c, device=orig.device, dtype=torch.bfloat16)
+    d_enh = torch.empty(rows, c, device=orig.device, dtype=torch.bfloat16)
+    d_f = torch.empty((), device=orig.device, dtype=torch.float32)
+    part = torch.empty(int(lib().b200sd_blend_part_floats()), device=orig.device, dtype=torch.float32)
+    check(lib().b200sd_blend_bwd(_p(g), g.stride(0), _p(orig), orig.stride(0), _p(enh), enh.stride(0), _p(out),
+                                 0 if out is None else out.stride(0), factor.data_ptr(), int(sigmoid), _p(d_orig),
+                                 _p(d_enh), rows, c, _p(part), tail_counter(orig.device), _p(d_f), stream_ptr()),
+          "blend_bwd")
+    return d_orig, d_enh, d_f
 
 
 def bit_split_bwd(ddigits, rows, c, slices, slice_bit):

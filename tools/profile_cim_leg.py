@@ -49,8 +49,23 @@ def main():
                 if kind == "adda":
                     new.weight_mapping_info = gen_weight_split_dict(new, [576, 2048])
                 setattr(parent, name, new)
+    if kind == "enhance":       # the wrapping bench.py's cim_lsq_enhance_train leg applies (Model_DiT_9L_train.py:541-553)
+        import cim_qn_train.layers_enhance as en
+        for n, c in [(n, c) for n, c in m.named_modules() if type(c) in (Linear_qn_lsq, Conv2d_qn_lsq)]:
+            parent = m.get_submodule(n.rsplit(".", 1)[0]) if "." in n else m
+            if type(c) is Linear_qn_lsq:
+                br = en.EnhanceBranchLinear_LoR(original_linear=c, relu=False, sigmoid=True, ops_factor=0.05)
+                br.original_linear = en.EnhanceLayerLinear(c, ops_factor=0.05)
+            else:
+                br = en.EnhanceBranchConv2d_LoR(original_conv=c, relu=False, sigmoid=True, ops_factor=0.05)
+                br.original_conv = en.EnhanceLayerConv2d(c, ops_factor=0.05)
+            setattr(parent, n.rsplit(".", 1)[-1], br)
     m = m.train().to(dev)
-    opt = FusedAdam(m.parameters(), lr=1e-5, max_grad_norm=1.0)
+    if kind == "enhance":
+        from sdb200.optim import PercentOptimizerFP
+        opt = PercentOptimizerFP(m.parameters(), lr=1e-5)
+    else:
+        opt = FusedAdam(m.parameters(), lr=1e-5, max_grad_norm=1.0)
     sched = LinearNoiseScheduler(1000, 0.00085, 0.012)
     B = 16
     x, text, mask = (t.to(dev) for t in bench.synth_inputs(B, ucfg, pin=False))
