@@ -97,6 +97,18 @@ class _LsqMixin:
         self.__dict__.pop("_lsq_ready", None)     # loaded step sizes may be the untouched 1.0 again
         self.__dict__["_gain_init_pending"] = True
 
+    _WQ_ISINT = False      # the ADDA classes quantise their weights to integer codes (isint=True)
+
+    def _wq_spec(self):
+        """What sdb200.quant.prepare_weight_side needs to serve this leaf from the model-wide launch, or None when the
+        leaf keeps the per-layer path (bypassed / unquantised / weight not an fp32 CUDA tensor)."""
+        if getattr(self, "use_FP", False) or not self.weight_quant or not FUSED_WEIGHT_SIDE:
+            return None
+        if not self.weight.is_cuda or self.weight.dtype != torch.float32:
+            return None
+        return {"bits": self.weight_bit, "isint": self._WQ_ISINT, "n_scale": self.noise_scale,
+                "unit": self.weight_noise_unit}
+
     def _w_qn(self, isint=False, want_scale=True):
         """(quantised + noisy weight as a differentiable fp32 tensor, w_scale)."""
         w, scale = self.weight, 1.0

@@ -71,6 +71,8 @@ class _Im2colFn(torch.autograd.Function):
 
 
 class _AddaMixin(_LsqMixin):
+    _WQ_ISINT = True
+
     def _init_adda(self, dac_bit, adc_bit, adc_gain_1_scale, adc_gain_range, adc_adjust_mode, seed):
         self.dac_bit = dac_bit
         self.adc_bit = adc_bit

@@ -379,6 +379,25 @@ int b200sd_weight_qn_bwd(const float* gout, const float* w, int64_t n, const flo
                          int32_t isint, float noise_scale, const float* unit, float* dw, float* dstep, float* scratch,
                          void* stream);
 
+/* The same two passes for MANY layers in one launch per phase (forward: statistics, apply; backward: noise dot product,
+ * apply) — the table rides in the kernel parameters, so nothing is uploaded or kept alive and the call is CUDA-graph
+ * capturable. Row fields as the arguments of b200sd_weight_qn / b200sd_weight_qn_bwd: `out` is the quantised weight in
+ * the forward pass and d(weight) in the backward pass (backward != 0), which also needs gout and dstep. `scratch` is
+ * the layer's own b200sd_wq_scratch_floats() buffer, kept from its forward to its backward. */
+typedef struct {
+    const float* w;
+    float* step;
+    const float* unit;
+    float* out;
+    const float* gout;
+    float* dstep;
+    float* scratch;
+    int64_t n;
+    float qp, grad_scale, noise_scale;
+    int32_t isint, lazy_init;
+} b200sd_wq_job;
+int b200sd_weight_qn_multi(const b200sd_wq_job* jobs, int32_t n_jobs, int32_t backward, void* stream);
+
 /* bit_split_tensor (cim_layers/layers_utils_adda.py:161-185): codes [rows, c] -> `slices` signed digits of slice_bit
  * bits stacked along rows, bf16 [slices * rows, c] — the DAC input slices. step == NULL: x holds the codes (bf16 or
  * fp32); step != NULL: x holds activations and the LSQ code (mode 1 above, with qp / grad_scale) is computed in the

@@ -97,6 +97,17 @@ class Denoiser(nn.Module):
             return gf(x, tt)
         return G.as_nchw(self.run(x, tt, st))
 
+    def _weight_side(self, before_cond=False):
+        """Weight side of every cim_layers leaf of this model (LSQ quantiser + noise) as one launch per phase
+        (sdb200.quant.prepare_weight_side). `run` calls it; a caller that also runs the conditioning leaves in the same
+        pass (the captured training step) calls it first with before_cond=True, and `run` then skips its own."""
+        from sdb200 import quant as Q
+        if not before_cond and self.__dict__.pop("_wq_prepared", False):
+            return
+        Q.prepare_weight_side(self)
+        if before_cond:
+            self.__dict__["_wq_prepared"] = True
+
     def invalidate_plan(self):
         """Drop captured graphs / hoisted conditioning (call after swapping sub-modules in place)."""
         self.__dict__.pop("_graphed", None)

@@ -214,6 +214,7 @@ class UnetCore(Denoiser):
         noise prediction. Pure kernel enqueues on the current stream (CUDA-graph capturable)."""
         n, c, h, w = x.shape
         dev = x.device
+        self._weight_side()
         if st.raw is not None or (E.precise() and not self.cond):
             from sdb200 import precise as P
             return P.unet_run(self, x, tt, st)

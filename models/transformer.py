@@ -156,6 +156,7 @@ class DIT(Denoiser):
         kernel enqueues on the current stream (CUDA-graph capturable)."""
         n, c, H, W = x.shape
         p = self.patch_height
+        self._weight_side()
         if st.inbuf is None:  # unconditioned model called through run() directly
             st = self.prepare_cond({}, x.shape, x.device)
         rt.nchw_to_nhwc(x.float(), st.inbuf, 0)

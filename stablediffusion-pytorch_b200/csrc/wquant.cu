@@ -69,14 +69,15 @@ struct WqScratch {
     float part[1];
 };
 
-__global__ void __launch_bounds__(WQ_THREADS)
-    wq_stats_kernel(const float* __restrict__ w, long long n, float* __restrict__ step, float qp, int lazy_init,
-                    WqScratch* __restrict__ sc) {
-    pdl_enter();
+// Every kernel body takes (cta, nctas) instead of reading blockIdx / gridDim: the single-layer kernels pass their own
+// grid, the table-driven kernels (one launch for ALL quantised layers of a model) pass a layer's slice of the grid.
+__device__ __forceinline__ void wq_stats_body(const float* __restrict__ w, long long n, float* __restrict__ step, float qp,
+                                              int lazy_init, WqScratch* __restrict__ sc, unsigned int cta,
+                                              unsigned int nctas) {
     __shared__ float red[3][WQ_THREADS / 32];
     float a = 0.f, lo = INFINITY, hi = -INFINITY;
-    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
-         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    for (long long i = static_cast<long long>(cta) * blockDim.x + threadIdx.x; i < n;
+         i += static_cast<long long>(nctas) * blockDim.x) {
         const float v = w[i];
         a = fmaxf(a, fabsf(v)), lo = fminf(lo, v), hi = fmaxf(hi, v);
     }
@@ -90,12 +91,12 @@ __global__ void __launch_bounds__(WQ_THREADS)
     __syncthreads();
     if (threadIdx.x == 0) {
         for (int k = 1; k < WQ_THREADS / 32; ++k) a = fmaxf(a, red[0][k]), lo = fminf(lo, red[1][k]), hi = fmaxf(hi, red[2][k]);
-        sc->part[3 * blockIdx.x] = a, sc->part[3 * blockIdx.x + 1] = lo, sc->part[3 * blockIdx.x + 2] = hi;
+        sc->part[3 * cta] = a, sc->part[3 * cta + 1] = lo, sc->part[3 * cta + 2] = hi;
     }
-    if (wq_last_cta(&sc->arrive, gridDim.x)) {
-        a = wq_fold<1>(sc->part, 3, gridDim.x, 0.f, red[0]);
-        lo = wq_fold<2>(sc->part + 1, 3, gridDim.x, INFINITY, red[1]);
-        hi = wq_fold<1>(sc->part + 2, 3, gridDim.x, -INFINITY, red[2]);
+    if (wq_last_cta(&sc->arrive, nctas)) {
+        a = wq_fold<1>(sc->part, 3, nctas, 0.f, red[0]);
+        lo = wq_fold<2>(sc->part + 1, 3, nctas, INFINITY, red[1]);
+        hi = wq_fold<1>(sc->part + 2, 3, nctas, -INFINITY, red[2]);
         if (threadIdx.x == 0) {
             sc->absmax = a, sc->wmin = lo, sc->wmax = hi;
             sc->cnt_max = 0u, sc->cnt_min = 0u;
@@ -103,6 +104,12 @@ __global__ void __launch_bounds__(WQ_THREADS)
                 *step = __fdiv_rn(1.0f, __fmul_rn(__fdiv_rn(1.0f, a), qp));
         }
     }
+}
+__global__ void __launch_bounds__(WQ_THREADS)
+    wq_stats_kernel(const float* __restrict__ w, long long n, float* __restrict__ step, float qp, int lazy_init,
+                    WqScratch* __restrict__ sc) {
+    pdl_enter();
+    wq_stats_body(w, n, step, qp, lazy_init, sc, blockIdx.x, gridDim.x);
 }
 
 __device__ __forceinline__ float wq_code(float v, float s, float qp) {
@@ -113,10 +120,10 @@ __device__ __forceinline__ float wq_value(float q, float s, int isint) {
     return isint ? __fdiv_rn(v, s) : v;
 }
 
-__global__ void __launch_bounds__(WQ_THREADS)
-    wq_apply_kernel(const float* __restrict__ w, long long n, const float* __restrict__ step, float qp, float g, int isint,
-                    float n_scale, const float* __restrict__ unit, float* __restrict__ out, WqScratch* __restrict__ sc) {
-    pdl_enter();
+__device__ __forceinline__ void wq_apply_body(const float* __restrict__ w, long long n, const float* __restrict__ step,
+                                              float qp, float g, int isint, float n_scale, const float* __restrict__ unit,
+                                              float* __restrict__ out, WqScratch* __restrict__ sc, unsigned int cta,
+                                              unsigned int nctas) {
     __shared__ unsigned int s_cnt[2];
     if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0u;
     __syncthreads();
@@ -125,8 +132,8 @@ __global__ void __launch_bounds__(WQ_THREADS)
     // (wq.max() - wq.min()) * n_scale, each operation rounded as the chain of torch ops does
     const float amp = __fmul_rn(__fsub_rn(wq_value(q_hi, s, isint), wq_value(q_lo, s, isint)), n_scale);
     unsigned int c_hi = 0u, c_lo = 0u;
-    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
-         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    for (long long i = static_cast<long long>(cta) * blockDim.x + threadIdx.x; i < n;
+         i += static_cast<long long>(nctas) * blockDim.x) {
         const float q = wq_code(w[i], s, qp);
         c_hi += q == q_hi, c_lo += q == q_lo;
         float v = wq_value(q, s, isint);
@@ -140,15 +147,21 @@ __global__ void __launch_bounds__(WQ_THREADS)
         if (threadIdx.x == 0) atomicAdd(&sc->cnt_max, s_cnt[0]), atomicAdd(&sc->cnt_min, s_cnt[1]);
     }
 }
+__global__ void __launch_bounds__(WQ_THREADS)
+    wq_apply_kernel(const float* __restrict__ w, long long n, const float* __restrict__ step, float qp, float g, int isint,
+                    float n_scale, const float* __restrict__ unit, float* __restrict__ out, WqScratch* __restrict__ sc) {
+    pdl_enter();
+    wq_apply_body(w, n, step, qp, g, isint, n_scale, unit, out, sc, blockIdx.x, gridDim.x);
+}
 
 // T = sum_i g_i * unit_i (fixed order: per-CTA partials, folded by the last CTA)
-__global__ void __launch_bounds__(WQ_THREADS)
-    wq_bwd_dot_kernel(const float* __restrict__ gout, const float* __restrict__ unit, long long n, WqScratch* __restrict__ sc) {
-    pdl_enter();
+__device__ __forceinline__ void wq_bwd_dot_body(const float* __restrict__ gout, const float* __restrict__ unit,
+                                                long long n, WqScratch* __restrict__ sc, unsigned int cta,
+                                                unsigned int nctas) {
     __shared__ float red[WQ_THREADS / 32];
     float a = 0.f;
-    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
-         i += static_cast<long long>(gridDim.x) * blockDim.x)
+    for (long long i = static_cast<long long>(cta) * blockDim.x + threadIdx.x; i < n;
+         i += static_cast<long long>(nctas) * blockDim.x)
         a = fmaf(gout[i], unit[i], a);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
@@ -156,19 +169,24 @@ __global__ void __launch_bounds__(WQ_THREADS)
     __syncthreads();
     if (threadIdx.x == 0) {
         for (int k = 1; k < WQ_THREADS / 32; ++k) a += red[k];
-        sc->part[blockIdx.x] = a;
+        sc->part[cta] = a;
     }
-    if (wq_last_cta(&sc->arrive, gridDim.x)) {
-        const float t = wq_fold<0>(sc->part, 1, gridDim.x, 0.f, red);
+    if (wq_last_cta(&sc->arrive, nctas)) {
+        const float t = wq_fold<0>(sc->part, 1, nctas, 0.f, red);
         if (threadIdx.x == 0) sc->T = t;
     }
 }
-
 __global__ void __launch_bounds__(WQ_THREADS)
-    wq_bwd_apply_kernel(const float* __restrict__ gout, const float* __restrict__ w, long long n,
-                        const float* __restrict__ step, float qp, float g, int isint, float n_scale, int noisy,
-                        float* __restrict__ dw, float* __restrict__ dstep, WqScratch* __restrict__ sc) {
+    wq_bwd_dot_kernel(const float* __restrict__ gout, const float* __restrict__ unit, long long n, WqScratch* __restrict__ sc) {
     pdl_enter();
+    wq_bwd_dot_body(gout, unit, n, sc, blockIdx.x, gridDim.x);
+}
+
+__device__ __forceinline__ void wq_bwd_apply_body(const float* __restrict__ gout, const float* __restrict__ w, long long n,
+                                                  const float* __restrict__ step, float qp, float g, int isint,
+                                                  float n_scale, int noisy, float* __restrict__ dw,
+                                                  float* __restrict__ dstep, WqScratch* __restrict__ sc, unsigned int cta,
+                                                  unsigned int nctas) {
     __shared__ float red[WQ_THREADS / 32];
     const float s = wq_effective_step(*step, g);
     const float inv_s = __fdiv_rn(1.0f, s);
@@ -179,8 +197,8 @@ __global__ void __launch_bounds__(WQ_THREADS)
         t_hi = t / static_cast<float>(sc->cnt_max), t_lo = t / static_cast<float>(sc->cnt_min);
     }
     float acc = 0.f;
-    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
-         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    for (long long i = static_cast<long long>(cta) * blockDim.x + threadIdx.x; i < n;
+         i += static_cast<long long>(nctas) * blockDim.x) {
         const float u = __fdiv_rn(w[i], s);
         const bool in = (u >= -qp) && (u <= qp);
         const float q = rintf(fminf(fmaxf(u, -qp), qp));
@@ -195,12 +213,56 @@ __global__ void __launch_bounds__(WQ_THREADS)
     __syncthreads();
     if (threadIdx.x == 0) {
         for (int k = 1; k < WQ_THREADS / 32; ++k) acc += red[k];
-        sc->part[blockIdx.x] = acc;
+        sc->part[cta] = acc;
     }
-    if (wq_last_cta(&sc->arrive, gridDim.x)) {
-        const float t = wq_fold<0>(sc->part, 1, gridDim.x, 0.f, red);
+    if (wq_last_cta(&sc->arrive, nctas)) {
+        const float t = wq_fold<0>(sc->part, 1, nctas, 0.f, red);
         if (threadIdx.x == 0) *dstep = (isint ? t * inv_s : t) * g;   // grad_scale's backward: the 1/sqrt(Qp numel) factor
     }
+}
+__global__ void __launch_bounds__(WQ_THREADS)
+    wq_bwd_apply_kernel(const float* __restrict__ gout, const float* __restrict__ w, long long n,
+                        const float* __restrict__ step, float qp, float g, int isint, float n_scale, int noisy,
+                        float* __restrict__ dw, float* __restrict__ dstep, WqScratch* __restrict__ sc) {
+    pdl_enter();
+    wq_bwd_apply_body(gout, w, n, step, qp, g, isint, n_scale, noisy, dw, dstep, sc, blockIdx.x, gridDim.x);
+}
+
+// ---- table-driven launches: one kernel per phase for up to WQ_MULTI layers, the table passed BY VALUE in the kernel
+// parameters (no device-side table to upload or keep alive, so the same call is CUDA-graph capturable and an eager
+// step may hand in fresh gradient pointers every time). CTA c serves the layer whose [cta0, cta0 + nctas) holds c.
+constexpr int WQ_MULTI = 64;
+struct WqJob {
+    const float* w;
+    float* step;
+    const float* unit;   // N(0,1) draw or null (no noise)
+    float* out;          // forward: quantised (+ noisy) weight; backward: d weight
+    const float* gout;   // backward: gradient of `out`
+    float* dstep;
+    WqScratch* sc;
+    long long n;
+    float qp, g, n_scale;
+    int flags;           // bit 0: isint, bit 1: lazy_init
+    unsigned int cta0, nctas;
+};
+struct WqTable {
+    WqJob job[WQ_MULTI];
+    int n_jobs;
+};
+
+template <int PHASE>   // 0 stats, 1 apply, 2 backward dot, 3 backward apply
+__global__ void __launch_bounds__(WQ_THREADS) wq_multi_kernel(const __grid_constant__ WqTable t) {
+    pdl_enter();
+    int j = 0;
+    while (j + 1 < t.n_jobs && blockIdx.x >= t.job[j + 1].cta0) ++j;
+    const WqJob& q = t.job[j];
+    const unsigned int cta = blockIdx.x - q.cta0;
+    if (PHASE == 0) wq_stats_body(q.w, q.n, q.step, q.qp, (q.flags >> 1) & 1, q.sc, cta, q.nctas);
+    if (PHASE == 1) wq_apply_body(q.w, q.n, q.step, q.qp, q.g, q.flags & 1, q.n_scale, q.unit, q.out, q.sc, cta, q.nctas);
+    if (PHASE == 2) wq_bwd_dot_body(q.gout, q.unit, q.n, q.sc, cta, q.nctas);
+    if (PHASE == 3)
+        wq_bwd_apply_body(q.gout, q.w, q.n, q.step, q.qp, q.g, q.flags & 1, q.n_scale, q.unit != nullptr, q.out, q.dstep,
+                          q.sc, cta, q.nctas);
 }
 
 static int wq_grid(long long n) {
@@ -215,6 +277,55 @@ static int wq_grid(long long n) {
 using namespace b200;
 
 extern "C" int b200sd_wq_scratch_floats(void) { return 8 + 3 * 2 * 148 * 2; }
+
+template <int PHASE>
+static int wq_launch_chunks(const b200sd_wq_job* jobs, int n_jobs, bool noisy_only, cudaStream_t st, const char* what) {
+    WqTable t;
+    int k = 0;
+    unsigned int ctas = 0;
+    auto flush = [&]() -> int {
+        if (k == 0) return B200SD_OK;
+        t.n_jobs = k;
+        launch_k(wq_multi_kernel<PHASE>, ctas, WQ_THREADS, 0, st, t);
+        B200_CHECK_LAUNCH(what);
+        k = 0, ctas = 0;
+        return B200SD_OK;
+    };
+    for (int i = 0; i < n_jobs; ++i) {
+        const b200sd_wq_job& a = jobs[i];
+        if (noisy_only && !(a.noise_scale != 0.f && a.unit)) continue;
+        WqJob& q = t.job[k];
+        q.w = a.w, q.step = a.step, q.unit = a.noise_scale != 0.f ? a.unit : nullptr, q.out = a.out, q.gout = a.gout;
+        q.dstep = a.dstep, q.sc = reinterpret_cast<WqScratch*>(a.scratch), q.n = a.n;
+        q.qp = a.qp, q.g = a.grad_scale, q.n_scale = a.noise_scale;
+        q.flags = (a.isint ? 1 : 0) | (a.lazy_init ? 2 : 0);
+        q.cta0 = ctas, q.nctas = static_cast<unsigned int>(wq_grid(a.n));
+        ctas += q.nctas;
+        if (++k == WQ_MULTI) {
+            const int rc = flush();
+            if (rc != B200SD_OK) return rc;
+        }
+    }
+    return flush();
+}
+
+extern "C" int b200sd_weight_qn_multi(const b200sd_wq_job* jobs, int32_t n_jobs, int32_t backward, void* stream) {
+    B200_REQUIRE(jobs && n_jobs > 0, "weight_qn_multi: bad arguments");
+    for (int i = 0; i < n_jobs; ++i) {
+        const b200sd_wq_job& a = jobs[i];
+        B200_REQUIRE(a.w && a.step && a.out && a.scratch && a.n > 0 && a.qp >= 1.f, "weight_qn_multi: bad table row");
+        B200_REQUIRE(a.noise_scale == 0.f || a.unit, "weight_qn_multi: noise needs the N(0,1) draw");
+        B200_REQUIRE(!backward || (a.gout && a.dstep), "weight_qn_multi: the backward pass needs gout and dstep");
+    }
+    cudaStream_t st = as_stream(stream);
+    int rc;
+    if (!backward) {
+        if ((rc = wq_launch_chunks<0>(jobs, n_jobs, false, st, "weight_qn_multi(stats)")) != B200SD_OK) return rc;
+        return wq_launch_chunks<1>(jobs, n_jobs, false, st, "weight_qn_multi(apply)");
+    }
+    if ((rc = wq_launch_chunks<2>(jobs, n_jobs, true, st, "weight_qn_multi(dot)")) != B200SD_OK) return rc;
+    return wq_launch_chunks<3>(jobs, n_jobs, false, st, "weight_qn_multi(bwd)");
+}
 
 extern "C" int b200sd_weight_qn(const float* w, int64_t n, float* step, float qp, float grad_scale, int32_t isint,
                                 int32_t lazy_init, float noise_scale, const float* unit, float* out, float* scratch,

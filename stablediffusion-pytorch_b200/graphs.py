@@ -403,6 +403,7 @@ class TrainGraph:
             if has_mask:
                 ci["image"] = self.cond[k]
             with swap:
+                core._weight_side(before_cond=True)     # all quantised leaves' weights: one launch per phase
                 st = core.prepare_cond(ci, self.x.shape, dev) if core.cond else E.CondState()
                 return as_nchw(core.run(self.x, self.tt, st))
 

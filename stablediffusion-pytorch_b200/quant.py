@@ -108,10 +108,121 @@ class WeightQnFn(Function):
         return dw, ds.reshape(step.shape).to(step.dtype), None, None, None, None, None
 
 
+class WeightSideFn(Function):
+    """weight_quant_noise of ALL quantised leaves of a model as one launch per phase (b200sd_weight_qn_multi): inputs
+    (w0, s0, w1, s1, ...), outputs the quantised (+ noisy) weights, views of one flat buffer. Rows whose output received
+    no gradient (a leaf the pass did not run) are skipped in the backward pass."""
+
+    @staticmethod
+    def forward(ctx, specs, *tensors):
+        ws, steps = tensors[0::2], tensors[1::2]
+        dev = ws[0].device
+        flat = torch.empty(sum(w.numel() for w in ws), device=dev, dtype=torch.float32)
+        draw = [w.numel() if sp["n_scale"] != 0 and sp["unit"] is None else 0 for w, sp in zip(ws, specs)]
+        noise = torch.randn(sum(draw), device=dev, dtype=torch.float32) if sum(draw) else None
+        rows, outs, units = [], [], []
+        o = z = 0
+        for w, st, sp, nd in zip(ws, steps, specs, draw):
+            n = w.numel()
+            out = flat[o:o + n].view(w.shape)
+            unit = sp["unit"]
+            if nd:
+                unit = noise[z:z + n].view(w.shape)
+                z += n
+            o += n
+            rows.append({"w": w, "step": st, "unit": unit if sp["n_scale"] != 0 else None, "out": out, "qp": sp["qp"],
+                         "n_scale": sp["n_scale"], "isint": sp["isint"], "scratch": sp["scratch"]})
+            outs.append(out)
+            units.append(rows[-1]["unit"])
+        rt.weight_qn_multi(rows, backward=False)
+        ctx.save_for_backward(*tensors, *units)
+        ctx.specs = specs
+        ctx.set_materialize_grads(False)
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, *gouts):
+        k = len(ctx.specs)
+        saved = ctx.saved_tensors
+        tensors, units = saved[:2 * k], saved[2 * k:]
+        ws, steps = tensors[0::2], tensors[1::2]
+        live = [i for i, g in enumerate(gouts) if g is not None]
+        grads = [None] * (2 * k)
+        if live:
+            dev = ws[0].device
+            dflat = torch.empty(sum(ws[i].numel() for i in live), device=dev, dtype=torch.float32)
+            dsteps = torch.empty(len(live), device=dev, dtype=torch.float32)
+            rows = []
+            o = 0
+            for j, i in enumerate(live):
+                sp, w, g = ctx.specs[i], ws[i], gouts[i]
+                if g.dtype != torch.float32 or not g.is_contiguous():
+                    g = g.float().contiguous()
+                dw = dflat[o:o + w.numel()].view(w.shape)
+                o += w.numel()
+                rows.append({"w": w, "step": steps[i], "unit": units[i], "out": dw, "gout": g, "dstep": dsteps[j:j + 1],
+                             "qp": sp["qp"], "n_scale": sp["n_scale"], "isint": sp["isint"], "scratch": sp["scratch"]})
+                grads[2 * i] = dw
+                grads[2 * i + 1] = dsteps[j].reshape(steps[i].shape).to(steps[i].dtype)
+            rt.weight_qn_multi(rows, backward=True)
+        return (None, *grads)
+
+
+FUSED_WEIGHT_BANK = True
+
+
+def prepare_weight_side(root):
+    """Quantise (+ noise) the weights of every cim_layers leaf under `root` in one table-driven launch per phase and park
+    the results on the leaves (`_wq_pending`), where their next `_w_qn()` picks them up; leaves that bypass
+    quantisation, keep a non-fp32 / non-CUDA weight or are disabled simply keep the per-layer path. Returns the number
+    of leaves served."""
+    if not FUSED_WEIGHT_BANK:
+        return 0
+    leaves, specs, tensors = [], [], []
+    for m in root.modules():
+        m.__dict__.pop("_wq_pending", None)            # a result the previous pass did not consume
+        spec = m._wq_spec() if hasattr(m, "_wq_spec") else None
+        if spec is None:
+            continue
+        w, step = m.weight, m.step_size_weight
+        scratch = m.__dict__.get("_wq_scratch")
+        if scratch is None or scratch.device != w.device:
+            scratch = m.__dict__["_wq_scratch"] = rt.wq_scratch(w.device)
+        unit = spec["unit"]
+        if spec["n_scale"] != 0 and unit is not None:
+            unit = unit.to(w).contiguous()
+        leaves.append(m)
+        specs.append({"qp": qp_of(spec["bits"]), "isint": spec["isint"], "n_scale": float(spec["n_scale"]),
+                      "unit": unit if spec["n_scale"] != 0 else None, "scratch": scratch})
+        tensors += [w if w.is_contiguous() else w.contiguous(), step]
+    if len(leaves) < 2:
+        return 0
+    if torch.is_grad_enabled() and any(t.requires_grad for t in tensors):
+        outs = WeightSideFn.apply(specs, *tensors)
+    else:
+        outs = WeightSideFn.forward(_NoCtx(), specs, *[t.detach() for t in tensors])
+    for m, sp, out in zip(leaves, specs, outs):
+        m.__dict__["_wq_pending"] = (out, sp["isint"])
+    return len(leaves)
+
+
+class _NoCtx:
+    """Stand-in for the autograd context when WeightSideFn.forward runs without recording."""
+
+    def save_for_backward(self, *a):
+        pass
+
+    def set_materialize_grads(self, v):
+        pass
+
+
 def weight_qn(owner, weight, step, bits, isint, n_scale, unit=None, want_scale=True):
     """(quantised + noisy weight as a differentiable fp32 tensor, w_scale) of a cim_layers leaf `owner`; want_scale
     False skips the 1 / step launch for callers that read the step size on the device themselves."""
     qp = qp_of(bits)
+    pend = owner.__dict__.pop("_wq_pending", None)
+    if pend is not None and pend[1] == bool(isint) and pend[0].shape == weight.shape:
+        return pend[0], ((1.0 / step).detach() if isint and want_scale else 1.0)
     scratch = owner.__dict__.get("_wq_scratch")
     if scratch is None or scratch.device != weight.device:
         scratch = owner.__dict__["_wq_scratch"] = rt.wq_scratch(weight.device)

@@ -22,7 +22,7 @@ EXPORTS = [
     "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16", "b200sd_im2col", "b200sd_col2im",
     "b200sd_layernorm_mod", "b200sd_layernorm_mod_bwd", "b200sd_rows_per_slot", "b200sd_gate_residual",
     "b200sd_gate_residual_bwd", "b200sd_relu_bwd", "b200sd_unpatchify", "b200sd_patchify",
-    "b200sd_wq_scratch_floats", "b200sd_weight_qn", "b200sd_weight_qn_bwd", "b200sd_lsq_init_step", "b200sd_lsq_quant", "b200sd_lsq_quant_bwd", "b200sd_lsq_quant_bwd_blocks", "b200sd_bit_split",
+    "b200sd_wq_scratch_floats", "b200sd_weight_qn", "b200sd_weight_qn_bwd", "b200sd_weight_qn_multi", "b200sd_lsq_init_step", "b200sd_lsq_quant", "b200sd_lsq_quant_bwd", "b200sd_lsq_quant_bwd_blocks", "b200sd_bit_split",
     "b200sd_adc_combine", "b200sd_adc_bwd", "b200sd_adc_bwd_blocks", "b200sd_bit_split_bwd",
     "b200sd_adda_out", "b200sd_adda_out_bwd", "b200sd_adda_out_scratch_floats", "b200sd_adc_scale",
     "b200sd_blockdiag_pack", "b200sd_blockdiag_gather", "b200sd_blend", "b200sd_blend_bwd", "b200sd_blend_part_floats",
@@ -102,6 +102,7 @@ def lib():
         L.b200sd_rowblocks.argtypes = [i64, i64, i32]
         L.b200sd_weight_qn.argtypes = [vp, i64, vp, f32, f32, i32, i32, f32, vp, vp, vp, vp]
         L.b200sd_weight_qn_bwd.argtypes = [vp, vp, i64, vp, f32, f32, i32, f32, vp, vp, vp, vp, vp]
+        L.b200sd_weight_qn_multi.argtypes = [vp, i32, i32, vp]
         L.b200sd_groupnorm_split.argtypes = [vp, i64, vp, i64, i32, vp, vp, i64, i64, i32, i32, f32, i32, vp]
         L.b200sd_split_f32.argtypes = [vp, i64, vp, i64, i32, i32, i64, i32, i32, vp]
         L.b200sd_groupnorm_bwd.argtypes = [vp, i64, vp, i64, vp, i64, vp, i64, vp, i32, i32, i32, vp, i32, i32, vp, vp, i64,
@@ -799,6 +800,24 @@ def weight_qn(w, step, qp, isint, noise_scale, unit, scratch, lazy_init=True):
                                  int(lazy_init), float(noise_scale), _p(unit), _p(out), _p(scratch), stream_ptr()),
           "weight_qn")
     return out
+
+
+class WqJob(C.Structure):
+    _fields_ = [("w", C.c_void_p), ("step", C.c_void_p), ("unit", C.c_void_p), ("out", C.c_void_p), ("gout", C.c_void_p),
+                ("dstep", C.c_void_p), ("scratch", C.c_void_p), ("n", C.c_int64), ("qp", C.c_float),
+                ("grad_scale", C.c_float), ("noise_scale", C.c_float), ("isint", C.c_int32), ("lazy_init", C.c_int32)]
+
+
+def weight_qn_multi(rows, backward):
+    """rows: list of dicts with the WqJob fields (tensors or None for the pointers); one launch per phase for all."""
+    arr = (WqJob * len(rows))()
+    for j, r in zip(arr, rows):
+        j.w, j.step, j.unit, j.out = _p(r["w"]), r["step"].data_ptr(), _p(r.get("unit")), _p(r["out"])
+        j.gout, j.dstep, j.scratch = _p(r.get("gout")), _p(r.get("dstep")), _p(r["scratch"])
+        j.n, j.qp, j.grad_scale, j.noise_scale = r["w"].numel(), r["qp"], lsq_grad_scale(r["qp"], r["w"].numel()), r["n_scale"]
+        j.isint, j.lazy_init = int(r["isint"]), int(r.get("lazy_init", True))
+    check(lib().b200sd_weight_qn_multi(C.cast(arr, C.c_void_p), len(rows), 1 if backward else 0, stream_ptr()),
+          "weight_qn_multi")
 
 
 def weight_qn_bwd(g, w, step, qp, isint, noise_scale, unit, scratch):

@@ -751,3 +751,73 @@ def test_adc_scale_kernel_matches_the_torch_formulation(mode):
         assert got.item() == ref.item()
         got.backward()
         assert abs(gain2.grad.item() - gain.grad.item()) <= 1e-5 * abs(gain.grad.item())
+
+
+def test_model_wide_weight_side_equals_the_per_layer_launches():
+    """sdb200.quant.prepare_weight_side (b200sd_weight_qn_multi: one launch per phase for every quantised leaf of a
+    model) against the per-layer launches: quantised weights, lazily initialised step sizes and all gradients
+    bit-identical (same kernel bodies, same per-layer CTA split); a bypassed leaf (use_FP) and a leaf the pass never runs
+    are handled; more than 64 leaves exercise the table chunking."""
+    dev = _dev()
+    import torch.nn as nn
+    from cim_layers.layers_qn_lsq import Linear_qn_lsq
+    from cim_layers.layers_qn_lsq_adda_cim import Linear_lsq_adda_cim
+    from sdb200 import quant as Q
+    kw = dict(weight_bit=4, input_bit=8, output_bit=8, noise_scale=0.08)
+    akw = dict(kw, dac_bit=5, adc_bit=8, adc_gain_1_scale=9.071428571, adc_gain_range=[1 / 64, 1 / 64],
+               adc_adjust_mode="current")
+
+    def build():
+        torch.manual_seed(5)
+        leaves = [Linear_qn_lsq(24 + 8 * (i % 5), 16 + 8 * (i % 3), **kw) for i in range(66)]
+        leaves += [Linear_lsq_adda_cim(32, 24, **akw), Linear_qn_lsq(16, 16, **dict(kw, noise_scale=0.0))]
+        m = nn.Sequential(*leaves).to(dev)
+        g = torch.Generator().manual_seed(9)
+        for lf in m:
+            lf.weight_noise_unit = torch.randn(lf.weight.shape, generator=g).to(dev)
+        m[3].use_FP = True
+        return m
+
+    def run(model, banked):
+        Q.FUSED_WEIGHT_BANK = banked
+        try:
+            served = Q.prepare_weight_side(model)
+            outs = []
+            for i, lf in enumerate(model):
+                if i == 7:
+                    continue                                   # a leaf this pass does not run
+                if lf.use_FP:
+                    continue
+                outs.append(lf._w_qn(isint=lf._WQ_ISINT)[0])
+            g = torch.Generator().manual_seed(11)
+            loss = sum((o * torch.randn(o.shape, generator=g).to(dev)).sum() for o in outs)
+            loss.backward()
+        finally:
+            Q.FUSED_WEIGHT_BANK = True
+        return served, [o.detach() for o in outs]
+
+    a, b = build(), build()
+    served_a, outs_a = run(a, True)
+    served_b, outs_b = run(b, False)
+    torch.cuda.synchronize()
+    assert served_a == 67 and served_b == 0
+    assert all(torch.equal(x, y) for x, y in zip(outs_a, outs_b))
+    for i, (la, lb) in enumerate(zip(a, b)):
+        if i != 7:      # (the model-wide pass initialises the step size of a leaf the forward then never runs)
+            assert la.step_size_weight.item() == lb.step_size_weight.item()
+        for pa, pb in ((la.weight, lb.weight), (la.step_size_weight, lb.step_size_weight)):
+            assert (pa.grad is None) == (pb.grad is None)
+            if pa.grad is not None:
+                assert torch.equal(pa.grad, pb.grad)
+    assert a[7].weight.grad is None and a[3].weight.grad is None
+    assert "_wq_pending" in a[7].__dict__                       # parked, dropped by the next pass
+    Q.prepare_weight_side(a)
+    with torch.no_grad():                                       # the no-grad route (sampling) serves the same numbers
+        w_ng = a[0]._w_qn()[0]
+    Q.FUSED_WEIGHT_BANK = False
+    try:
+        with torch.no_grad():
+            w_pl = a[0]._w_qn()[0]
+    finally:
+        Q.FUSED_WEIGHT_BANK = True
+    assert torch.equal(w_ng, w_pl)
