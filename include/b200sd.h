@@ -525,13 +525,14 @@ int b200sd_vq_nearest(const float* x, int64_t ld_x, const float* codebook, int32
 /* ------------------------------------------------------------------------------------------ optimizer step
  * Replaces, for one training step, torch.nn.utils.clip_grad_norm_ + the isfinite(grad_norm) check + Adam.step + the
  * per-parameter EMA loop of train_ddpm_cond_celebhq_multi_gpu.py:362-378 (same code in Model_DiT_9L_train.py).
- * Gradients, exp_avg and exp_avg_sq are flat fp32 buffers sharing one slot layout; a chunk names a run of <=
+ * Gradients, exp_avg and exp_avg_sq are flat fp32 buffers; a chunk names a run of <=
  * b200sd_opt_chunk_elems() consecutive elements of one parameter: its address, its EMA shadow's (or NULL), the run's
- * offset in the flat buffers and its length. vec = 1 when p (and ema) are 16-byte aligned. */
+ * offsets in the moment buffers and in the gradient buffer, and its length. vec = 1 when p (and ema) are 16-byte aligned. */
 typedef struct {
     float* p;
     float* ema;
-    int64_t off;
+    int64_t off;  /* offset of the run in m_base / v_base */
+    int64_t goff; /* offset of the run in g_base (the gradient buffer may use another slot order) */
     int32_t n;
     int32_t vec;
 } b200sd_opt_chunk;

@@ -1,4 +1,5 @@
 #include "host.h"
+#include <cstdlib>
 #include <atomic>
 #include <stdlib.h>
 #include <string.h>
@@ -25,6 +26,12 @@ int sm_count() {
             cached = n;
         else
             cached = 148;
+        // B200SD_SM_LIMIT=<k>: size every persistent grid for k SMs instead of all of them, leaving the rest to kernels
+        // of other streams (the NCCL all-reduce of the data-parallel gradient exchange, tools/overlap_probe.py)
+        if (const char* e = getenv("B200SD_SM_LIMIT")) {
+            const int k = atoi(e) & ~1;
+            if (k >= 8 && k < cached) cached = k;
+        }
     }
     return cached;
 }

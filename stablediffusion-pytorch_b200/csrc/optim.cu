@@ -8,9 +8,10 @@
 //                  ema = decay * ema + (1 - decay) * p   — one pass: 36 B/parameter of HBM traffic,
 //                  skipped entirely (moments untouched) when the norm is not finite, as the reference script does.
 //
-// Gradients and moments live in flat fp32 buffers with the same 64-element-aligned slot layout as the captured
-// training step's gradient buffer (graphs.TrainGraph), addressed by offset; parameters and EMA shadows stay where
-// PyTorch allocated them, addressed by pointer.
+// Gradients and moments live in flat fp32 buffers of 64-element-aligned slots, addressed by offset — the moments in
+// parameter order, the gradients in whatever order the captured training step laid its buffer out (graphs.TrainGraph
+// orders it by gradient arrival when the data-parallel exchange overlaps the backward pass), hence two offsets per
+// chunk; parameters and EMA shadows stay where PyTorch allocated them, addressed by pointer.
 #include "host.h"
 
 namespace b200 {
@@ -20,7 +21,8 @@ constexpr int OPT_CHUNK = 32768;   // elements per table entry (python side spli
 struct OptChunk {                  // = b200sd_opt_chunk
     float* p;
     float* ema;
-    long long off;
+    long long off;                 // offset of the run in the moment buffers
+    long long goff;                // offset of the run in the gradient buffer (its own layout: see graphs.TrainGraph)
     int n;
     int vec;                       // 1: p/ema 16-byte aligned, float4 path
 };
@@ -47,7 +49,7 @@ __global__ void __launch_bounds__(256)
     __shared__ float red[8];
     __shared__ unsigned int s_last;
     const OptChunk c = tab[blockIdx.x];
-    const float* gp = g + c.off;
+    const float* gp = g + c.goff;
     float s = 0.f;
     const int n4 = c.n >> 2;
     for (int i = threadIdx.x; i < n4; i += 256) {
@@ -97,7 +99,7 @@ __global__ void __launch_bounds__(256)
     const float step_size = lr / bc1;
     const float w1 = 1.f - beta1, w2 = 1.f - beta2, we = 1.f - ema_decay;
     const OptChunk c = tab[blockIdx.x];
-    const float* gp = g + c.off;
+    const float* gp = g + c.goff;
     float* mp = m + c.off;
     float* vp = v + c.off;
 
@@ -160,7 +162,7 @@ __global__ void __launch_bounds__(256)
     pdl_enter();
     __shared__ float red_u[8], red_p[8];
     const OptChunk c = tab[blockIdx.x];
-    const float* gp = g + c.off;
+    const float* gp = g + c.goff;
     float* mp = m + c.off;
     float* vp = v + c.off;
     float mu = 0.f, mw = 0.f;

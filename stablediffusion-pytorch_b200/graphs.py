@@ -269,13 +269,32 @@ class _ReplayFn(torch.autograd.Function):
         return (None, tg.dx.clone() if tg.dx is not None else None) + tg.take_grads()
 
 
+def arrival_slots(numels, shapes, trainable, order):
+    """Slot layout of the flat gradient buffer: (offset, numel, shape) per parameter (None when not trainable), slots
+    64-element aligned and laid out in `order` (parameter indices; trainable ones not listed follow at the end). With
+    order = the sequence in which a backward pass produces the gradients, every prefix of the buffer is complete before
+    the rest, so the exchange can start on the first bucket while the backward pass is still producing the later ones —
+    in PARAMETER order the parameters used at the very start of the forward pass (time-embedding bank, conditioning
+    projections) are scattered over all buckets and hold every one of them open until the end of the backward pass
+    (measured: profiles/r2e_overlap_n2.md)."""
+    slots, off = [None] * len(numels), 0
+    seen = set()
+    for i in list(order) + list(range(len(numels))):
+        if i in seen or not trainable[i]:
+            continue
+        seen.add(i)
+        slots[i] = (off, numels[i], tuple(shapes[i]))
+        off += (numels[i] + 63) // 64 * 64
+    return slots, off
+
+
 def plan_buckets(slots, fired, bucket_elems):
     """Buckets of parameter indices for the in-graph gradient exchange: the parameters that receive a gradient (`fired`),
-    walked from the LAST to the first (the order backward produces them), closed whenever at least `bucket_elems`
-    elements have been collected. Every bucket is a run of consecutive used parameters, so it owns one contiguous slice
-    [bucket_range] of the flat gradient buffer. slots[i] = (offset, numel, shape) or None."""
+    walked in slot order (= gradient-arrival order, see arrival_slots), closed whenever at least `bucket_elems` elements
+    have been collected. Every bucket is a run of consecutive used slots, so it owns one contiguous slice [bucket_range]
+    of the flat gradient buffer. slots[i] = (offset, numel, shape) or None."""
     buckets, cur, size = [], [], 0
-    for i in reversed(sorted(set(fired))):
+    for i in sorted(set(fired), key=lambda i: slots[i][0]):
         cur.append(i)
         size += slots[i][1]
         if size >= bucket_elems:
@@ -294,8 +313,8 @@ def bucket_range(slots, idxs):
 
 
 class _BucketReducer:
-    """Gradient mean over ranks, captured inside the backward graph. The flat buffer is cut into contiguous buckets in
-    REVERSE parameter order (the order backward produces gradients); a tensor hook on every stand-in parameter counts its
+    """Gradient mean over ranks, captured inside the backward graph. The flat buffer (slots in gradient-arrival order,
+    arrival_slots) is cut into contiguous buckets; a tensor hook on every stand-in parameter counts its
     bucket down, and the hook that completes a bucket (i) copies the bucket's gradients that were not written in place
     into their slots, (ii) forks a side stream off the capturing stream and issues ONE in-place NCCL all-reduce (AVG) on
     the bucket's slice there. `finish()` reduces whatever is still open and joins the side stream, so the graph ends
@@ -395,8 +414,11 @@ class TrainGraph:
         if not wrt:
             raise rt.B200Error("training graph requested but nothing requires grad")
 
+        self.bank = None
+
         def forward():
-            self.bank.refresh()
+            if self.bank is not None:
+                self.bank.refresh()
             ci, k = {}, 0
             if has_text:
                 ci["text"], k = self.cond[k], k + 1
@@ -407,12 +429,11 @@ class TrainGraph:
                 st = core.prepare_cond(ci, self.x.shape, dev) if core.cond else E.CondState()
                 return as_nchw(core.run(self.x, self.tt, st))
 
-        # slots of the flat gradient buffer
-        self.slots, off = [], 0
-        for p in self.params:
-            self.slots.append((off, p.numel(), tuple(p.shape)) if p.requires_grad else None)
-            if p.requires_grad:
-                off += (p.numel() + 63) // 64 * 64
+        # slots of the flat gradient buffer: parameter order, or — when the gradient exchange is captured inside the
+        # backward graph — the order in which a backward pass produces the gradients (one eager discovery pass)
+        order = self._arrival_order(forward, wrt) if overlap is not None else []
+        self.slots, off = arrival_slots([p.numel() for p in self.params], [p.shape for p in self.params],
+                                        [p.requires_grad for p in self.params], order)
         self.flat = torch.zeros(max(off, 64), device=dev, dtype=torch.float32)
         # packed bf16 forms of every parameter in one launch per step; weight gradients written straight into `flat`
         self.bank = BK.WeightBank(swap.standins, self.flat, self.slots)
@@ -421,6 +442,19 @@ class TrainGraph:
             self._build(forward, wrt, dev)
         finally:
             BK.ACTIVE = None
+
+    def _arrival_order(self, forward, wrt):
+        """Parameter indices in the order one (eager, bank-less) backward pass produces their gradients."""
+        idx = [i for i, p in enumerate(self.params) if p.requires_grad]
+        standins = [t for t in wrt if t is not self.x]
+        fired = []
+        with torch.autocast("cuda", enabled=False), torch.enable_grad():
+            out = forward()
+            hs = [t.register_hook(lambda g, i=i: fired.append(i)) for i, t in zip(idx, standins)]
+            torch.autograd.grad((out,), wrt, (torch.ones_like(out),), allow_unused=True)
+            for h in hs:
+                h.remove()
+        return fired
 
     def _build(self, forward, wrt, dev):
         with torch.autocast("cuda", enabled=False), torch.enable_grad():

@@ -80,8 +80,8 @@ class FusedAdam(torch.optim.Optimizer):
         """1.0 if the last step() updated the parameters, 0.0 if it was skipped (non-finite gradients)."""
         return self._scalars[2]
 
-    def _table(self, present, groups):
-        key = (present, tuple(p.data_ptr() for p in self._all), None if self._ema is None else
+    def _table(self, present, groups, goffs):
+        key = (present, goffs, tuple(p.data_ptr() for p in self._all), None if self._ema is None else
                tuple(e.data_ptr() for e in self._ema))
         plan = self._plans.get(key)
         if plan is not None:
@@ -99,13 +99,13 @@ class FusedAdam(torch.optim.Optimizer):
                 vec = 1 if p.data_ptr() % 16 == 0 and (e is None or e.data_ptr() % 16 == 0) else 0
                 for c0 in range(0, p.numel(), ce):
                     rows.append((p.data_ptr() + 4 * c0, 0 if e is None else e.data_ptr() + 4 * c0, self._off[i] + c0,
-                                 min(ce, p.numel() - c0), vec))
+                                 goffs[i] + c0, min(ce, p.numel() - c0), vec))
             if not rows:
                 plan.append(None)
                 continue
             arr = (rt.OptChunk * len(rows))()
-            for k, (pp, ee, oo, nn, vv) in enumerate(rows):
-                arr[k].p, arr[k].ema, arr[k].off, arr[k].n, arr[k].vec = pp, ee or None, oo, nn, vv
+            for k, (pp, ee, oo, go, nn, vv) in enumerate(rows):
+                arr[k].p, arr[k].ema, arr[k].off, arr[k].goff, arr[k].n, arr[k].vec = pp, ee or None, oo, go, nn, vv
             tab = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(self._dev)
             plan.append((tab, len(rows)))
         # the norm runs over every group's chunks at once
@@ -120,25 +120,29 @@ class FusedAdam(torch.optim.Optimizer):
         return self._plans[key]
 
     def _grad_base(self, present):
-        """Address of a flat fp32 buffer holding every present gradient at this optimizer's slot offsets: the gradients'
-        own storage when they already are views of one such buffer (graphs.TrainGraph hands them out that way),
-        otherwise a private buffer filled by one multi-tensor copy."""
-        base, ok = None, True
-        for p, o, has in zip(self._all, self._off, present):
+        """(address of a flat fp32 buffer, per-parameter element offsets into it) of the present gradients: the
+        gradients' own storage when they are views of ONE buffer (graphs.TrainGraph hands them out that way, in its own
+        slot order — gradient-arrival order when the data-parallel exchange overlaps the backward pass), otherwise a
+        private buffer in this optimizer's slot order filled by one multi-tensor copy."""
+        store, ok = None, True
+        goffs = [None] * len(self._all)
+        for i, (p, has) in enumerate(zip(self._all, present)):
             if not has:
                 continue
             g = p.grad
             if g.dtype != torch.float32 or not g.is_contiguous() or g.is_sparse:
                 ok = False
                 break
-            b = g.data_ptr() - 4 * o
-            if base is None:
-                base = b
-            elif b != base:
+            st = g.untyped_storage().data_ptr()
+            d = g.data_ptr() - st
+            if store is None:
+                store = st
+            if st != store or store % 16 or d % 16:
                 ok = False
                 break
-        if ok and base is not None and base % 16 == 0:
-            return base
+            goffs[i] = d // 4
+        if ok and store is not None:
+            return store, tuple(goffs)
         if self._g is None:
             self._g = torch.zeros(self._total, device=self._dev)
         dst, src = [], []
@@ -147,7 +151,7 @@ class FusedAdam(torch.optim.Optimizer):
                 dst.append(self._g[o:o + p.numel()].view(p.shape))
                 src.append(p.grad if p.grad.dtype == torch.float32 else p.grad.float())
         torch._foreach_copy_(dst, src)
-        return self._g.data_ptr()
+        return self._g.data_ptr(), tuple(o if has else None for o, has in zip(self._off, present))
 
     # ------------------------------------------------------------------------------------------ step
     @torch.no_grad()
@@ -159,8 +163,8 @@ class FusedAdam(torch.optim.Optimizer):
         present = tuple(p.grad is not None for p in self._all)
         if not any(present):
             return loss
-        plan, (norm_tab, n_norm), partial = self._table(present, self.param_groups)
-        gbase = self._grad_base(present)
+        gbase, goffs = self._grad_base(present)
+        plan, (norm_tab, n_norm), partial = self._table(present, self.param_groups, goffs)
         rt.grad_sqnorm(norm_tab, n_norm, gbase, self.max_grad_norm or 0.0, self.skip_nonfinite, partial, self._scalars)
         for g, ent in zip(self.param_groups, plan):
             if ent is None:
@@ -219,9 +223,9 @@ class PercentOptimizerFP(FusedAdam):
         self._steps = [0] * len(self._all)      # per parameter, as the reference counts them (:101-105)
         self._ptabs = {}
 
-    def _ptable(self, idxs):
+    def _ptable(self, idxs, goffs):
         """(chunk table, tensor index per chunk, chunk count, per-tensor max buffer) for the parameters `idxs`."""
-        key = (tuple(idxs), tuple(self._all[i].data_ptr() for i in idxs))
+        key = (tuple(idxs), tuple(goffs[i] for i in idxs), tuple(self._all[i].data_ptr() for i in idxs))
         ent = self._ptabs.get(key)
         if ent is None:
             ce = rt.opt_chunk_elems()
@@ -229,11 +233,11 @@ class PercentOptimizerFP(FusedAdam):
             for k, i in enumerate(idxs):
                 p = self._all[i]
                 for c0 in range(0, p.numel(), ce):
-                    rows.append((p.data_ptr() + 4 * c0, self._off[i] + c0, min(ce, p.numel() - c0)))
+                    rows.append((p.data_ptr() + 4 * c0, self._off[i] + c0, goffs[i] + c0, min(ce, p.numel() - c0)))
                     tid.append(k)
             arr = (rt.OptChunk * len(rows))()
-            for k, (pp, oo, nn) in enumerate(rows):
-                arr[k].p, arr[k].ema, arr[k].off, arr[k].n, arr[k].vec = pp, None, oo, nn, 0
+            for k, (pp, oo, go, nn) in enumerate(rows):
+                arr[k].p, arr[k].ema, arr[k].off, arr[k].goff, arr[k].n, arr[k].vec = pp, None, oo, go, nn, 0
             tab = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(self._dev)
             ent = (tab, torch.tensor(tid, dtype=torch.int32, device=self._dev), len(rows),
                    torch.zeros(len(idxs), 2, dtype=torch.int32, device=self._dev))
@@ -250,7 +254,7 @@ class PercentOptimizerFP(FusedAdam):
         present = tuple(p.grad is not None for p in self._all)
         if not any(present):
             return loss
-        gbase = self._grad_base(present)
+        gbase, goffs = self._grad_base(present)
         index = {id(p): i for i, p in enumerate(self._all)}
         for g in self.param_groups:
             lr, (b1, b2), eps = g["lr"], g["betas"], g["eps"]
@@ -263,7 +267,7 @@ class PercentOptimizerFP(FusedAdam):
             for step, idxs in sorted(by_step.items()):   # one entry unless some parameters skipped earlier steps
                 bc1, bc2 = 1 - b1 ** step, 1 - b2 ** step              # :113-114, in Python doubles as there
                 adj, bc2s = (bc2 ** 0.5) / bc1, bc2 ** 0.5             # :117, :120
-                tab, tid, n, tmax = self._ptable(idxs)
+                tab, tid, n, tmax = self._ptable(idxs, goffs)
                 tmax.zero_()
                 rt.percent_opt_step(tab, tid, n, gbase, self._m, self._v, tmax, lr, b1, b2, 1 - b1, 1 - b2, adj, bc2s,
                                     eps)

@@ -54,10 +54,10 @@ class DataParallel(nn.Module):
         # captured steps: graphs.TrainGraph calls this with the flat gradient buffer
         module.__dict__["_grad_sync"] = self._sync_flat
         # NCCL: let the captured backward graph reduce bucket by bucket while it is still producing gradients
-        # (graphs._BucketReducer); 64 MB buckets unless bucket_cap_mb says otherwise
+        # (graphs._BucketReducer); 32 MB buckets unless bucket_cap_mb says otherwise
         module.__dict__.pop("_grad_overlap", None)
         if overlap and dist.get_backend(self.group) == "nccl" and dist.get_world_size(self.group) > 1:
-            module.__dict__["_grad_overlap"] = (self.group, self.bucket_elems or (64 << 20) // 4)
+            module.__dict__["_grad_overlap"] = (self.group, self.bucket_elems or (32 << 20) // 4)
         for p in self._params:
             p.register_post_accumulate_grad_hook(self._landed)
 

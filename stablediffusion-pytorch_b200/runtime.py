@@ -995,7 +995,8 @@ def pack_weights(table, n_jobs, n_tiles):
 
 # ------------------------------------------------------------------------------------------------ optimizer step
 class OptChunk(C.Structure):
-    _fields_ = [("p", C.c_void_p), ("ema", C.c_void_p), ("off", C.c_int64), ("n", C.c_int32), ("vec", C.c_int32)]
+    _fields_ = [("p", C.c_void_p), ("ema", C.c_void_p), ("off", C.c_int64), ("goff", C.c_int64), ("n", C.c_int32),
+                ("vec", C.c_int32)]
 
 
 def opt_chunk_elems():

@@ -112,32 +112,36 @@ def test_bench_batch_sharding_is_disjoint():
 
 
 def test_gradient_bucket_plan_covers_the_flat_buffer_once():
-    """Host logic of the in-graph gradient exchange (graphs.plan_buckets / bucket_range): buckets walk the parameters
-    that receive gradients from last to first, each owns one contiguous slice of the flat buffer, the slices are
-    disjoint, ordered, and together cover every used slot; unused parameters never start or end a bucket."""
+    """Host logic of the in-graph gradient exchange (graphs.arrival_slots / plan_buckets / bucket_range): the flat
+    buffer is laid out in gradient-arrival order (trainable parameters that never fired follow at the end, frozen ones
+    get no slot); buckets walk the used slots from the first to arrive to the last, each owns one contiguous slice of
+    the flat buffer, the slices are disjoint, ordered, and together cover every used slot."""
     import importlib
     G = importlib.import_module("sdb200.graphs")
     sizes = [300, 7, 4096, 64, 1, 9000, 128, 33, 70000, 5]
-    slots, off = [], 0
-    for i, n in enumerate(sizes):
-        if i == 4:
-            slots.append(None)          # requires_grad = False
-            continue
-        slots.append((off, n, (n,)))
-        off += (n + 63) // 64 * 64
-    fired = [9, 8, 7, 5, 3, 2, 0, 2]    # 6 and 1 receive no gradient; 2 is reported twice
+    trainable = [i != 4 for i in range(len(sizes))]                  # 4: requires_grad = False
+    fired = [9, 8, 7, 5, 3, 0, 2]       # arrival order; 0 (used at the start of the forward) lands before 2; 6, 1 never fire
+    slots, total = G.arrival_slots(sizes, [(n,) for n in sizes], trainable, fired)
+    assert slots[4] is None and all(slots[i] is not None for i in range(len(sizes)) if i != 4)
+    by_off = sorted((sl[0], i) for i, sl in enumerate(slots) if sl is not None)
+    assert [i for _, i in by_off] == fired + [1, 6]                  # arrival order, then the rest in parameter order
+    assert all(o % 64 == 0 for o, _ in by_off) and total == sum((sizes[i] + 63) // 64 * 64 for i in range(10) if i != 4)
     for cap in (1, 4000, 10000, 10 ** 9):
-        buckets = G.plan_buckets(slots, fired, cap)
+        buckets = G.plan_buckets(slots, fired + [2], cap)            # (2 reported twice)
         flat = [i for b in buckets for i in b]
-        assert flat == [9, 8, 7, 5, 3, 2, 0]
+        assert flat == fired
         ranges = [G.bucket_range(slots, b) for b in buckets]
         for (lo, hi), b in zip(ranges, buckets):
-            assert lo % 64 == 0 and hi % 64 == 0 and lo < hi <= off
+            assert lo % 64 == 0 and hi % 64 == 0 and lo < hi <= total
             assert all(lo <= slots[i][0] and slots[i][0] + slots[i][1] <= hi for i in b)
         for (lo_a, hi_a), (lo_b, hi_b) in zip(ranges, ranges[1:]):
-            assert hi_b <= lo_a          # later buckets lie below earlier ones, no overlap
+            assert hi_a <= lo_b          # later buckets lie above earlier ones, no overlap
         if cap == 10 ** 9:
             assert len(buckets) == 1
         if cap == 1:
             assert len(buckets) == 7
         assert all(sum(slots[i][1] for i in b) >= cap for b in buckets[:-1])
+    # without an arrival order (no overlap requested) the layout is plain parameter order
+    plain, _ = G.arrival_slots(sizes, [(n,) for n in sizes], trainable, [])
+    offs = [sl[0] for sl in plain if sl is not None]
+    assert offs == sorted(offs)
