@@ -44,7 +44,14 @@ class Denoiser(nn.Module):
         st = self.prepare_cond(cond_input, x.shape, x.device)
         if st.ctx is not None:
             st.ctx.persistent = True
-        cache[:] = [e for e in cache if G.cond_key_alive(e[1])][-3:]   # conditional + unconditional (CFG) and a little slack
+        # A state whose condition tensors are gone (the previous sampling job's) lends its storage to the new
+        # condition: the forward graphs captured on it keep working (engine.rebind_cond).
+        for k, ent in enumerate(cache):
+            if ent[0] == (tuple(x.shape), E.PARITY_MODE) and not G.cond_key_alive(ent[1]) and E.rebind_cond(ent[3], st):
+                st = ent[3]
+                del cache[k]
+                break
+        cache[:] = cache[-3:]   # conditional + unconditional (CFG) and a little slack; dead entries wait to be rebound
         cache.append(((tuple(x.shape), E.PARITY_MODE), G.cond_key(cond_input), wstamp, st))
         return st
 

@@ -396,10 +396,11 @@ class Context:
     (context_proj -> in_proj[k,v]). The K/V of a site depend only on the context and that site's weights, not on
     x or t, so a Context that outlives one forward (the 1000-step sampling loop keeps `cond_input` fixed,
     tools/sample_ddpm_text_image_cond.py:64-82) computes them once instead of once per step."""
-    __slots__ = ("t", "lk", "dim", "kv", "persistent")
+    __slots__ = ("t", "lk", "dim", "kv", "persistent", "sites")
 
     def __init__(self, t, lk, dim, persistent=False):
         self.t, self.lk, self.dim, self.kv, self.persistent = t, lk, dim, {}, persistent
+        self.sites = {}     # id(mha) -> (context_proj module, mha): who to ask for a cached K/V again (rebind_cond)
 
     def __iter__(self):  # (ctx_t, lk, dim) unpacking used by the block classes
         return iter((self.t, self.lk, self.dim))
@@ -411,6 +412,37 @@ class CondState:
 
     def __init__(self):
         self.inbuf = self.cin = self.ctx = self.class_onehot = self.raw = None
+
+
+def rebind_cond(old, new):
+    """Serve a NEW condition through the storage of an old CondState (same shapes), in place: the captured forward
+    graphs that hold pointers into `old` (input buffer with the mask channels, text context rows, per-site K/V) stay
+    valid, so a sampling job with fresh conditions costs the hoisted conditioning work once — not a re-capture of the
+    whole forward (~65 ms per job, which a 20-step job cannot amortise). The cached K/V are recomputed from the new
+    context with the sites' current weights. Returns False (nothing touched) when the two states do not match."""
+    def same(a, b):
+        return (a is None) == (b is None) and (a is None or (a.shape == b.shape and a.dtype == b.dtype
+                                                              and a.device == b.device))
+    if old.raw is not None or new.raw is not None or old.cin != new.cin:
+        return False       # precise mode keeps the caller's own tensors: nothing to copy into
+    if not same(old.inbuf, new.inbuf) or not same(old.class_onehot, new.class_onehot):
+        return False
+    if (old.ctx is None) != (new.ctx is None):
+        return False
+    if old.ctx is not None and (not same(old.ctx.t, new.ctx.t) or (old.ctx.lk, old.ctx.dim) != (new.ctx.lk, new.ctx.dim)
+                                or set(old.ctx.kv) != set(old.ctx.sites)):
+        return False
+    with torch.no_grad():
+        if old.inbuf is not None:
+            old.inbuf.copy_(new.inbuf)
+        if old.class_onehot is not None:
+            old.class_onehot.copy_(new.class_onehot)
+        if old.ctx is not None:
+            old.ctx.t.copy_(new.ctx.t)
+            for key, (proj, mha) in old.ctx.sites.items():
+                pk = _mha_weights(mha)
+                old.ctx.kv[key].copy_(rt.linear(linear(old.ctx.t, proj), pk["kv"], bias=pk["b_kv"]))
+    return True
 
 
 HOIST_CONDITIONING = True
@@ -448,6 +480,7 @@ def cross_attention(a, norm, mha, ctx_proj_mod, ctx, lk, cache=None):
         kv = rt.linear(cp, pk["kv"], bias=pk["b_kv"])
         if cache is not None and cache.persistent:
             cache.kv[id(mha)] = kv
+            cache.sites[id(mha)] = (ctx_proj_mod, mha)
     o = rt.attention(q, kv[:, :C], kv[:, C:], a.n, heads, a.hw, lk, C // heads)
     return _out_proj(o, mha, a)
 
@@ -658,6 +691,7 @@ def dit_cross_attention(x, norm, mha, ctx_proj_mod, ctx, n, L):
         kv = rt.linear(linear(ctx.t, ctx_proj_mod), pk["kv"], bias=pk["b_kv"])
         if ctx.persistent:
             ctx.kv[id(mha)] = kv
+            ctx.sites[id(mha)] = (ctx_proj_mod, mha)
     o = rt.attention(q, kv[:, :C], kv[:, C:], n, heads, L, ctx.lk, C // heads)
     return linear(o, mha.out_proj, residual=x)
 

@@ -183,6 +183,35 @@ def test_condition_cache_is_not_fooled_by_a_recycled_address():
     assert not torch.equal(pa, pb)
 
 
+def test_a_new_condition_reuses_the_captured_forward():
+    """A sampling job with fresh condition tensors (the previous job's are gone) must not re-capture the forward: the
+    old CondState lends its storage (engine.rebind_cond: mask channels, text rows, per-site K/V recomputed), the graph
+    captured on it is replayed — results bit-identical to a freshly planned model, for the conditional and the
+    unconditional (CFG) state of two successive jobs."""
+    dev = _dev()
+    fx, model = _small_cond(dev)
+    inp, cfg = fx["inputs"], fx["config"]
+    x, t = inp["x"].to(dev), inp["t"].to(dev)
+    host = cond_of(inp, cfg)
+    with torch.no_grad():
+        cond = {k: v.to(dev) for k, v in host.items()}
+        unc = {k: torch.zeros_like(v) for k, v in cond.items()}
+        model(x, t, cond), model(x, t, unc)
+        graphs1 = dict(model.__dict__["_graphed"])
+        assert len(graphs1) == 2
+        del cond, unc
+        cond2 = {k: (v.flip(0) * 0.5).to(dev) for k, v in host.items()}
+        unc2 = {k: torch.full_like(v, 0.25) for k, v in cond2.items()}
+        b, bu = model(x, t, cond2), model(x, t, unc2)
+        graphs2 = model.__dict__["_graphed"]
+        assert len(graphs2) == 2 and all(graphs2[k] is graphs1[k] for k in graphs1)      # replayed, not re-captured
+        b_again = model(x, t, cond2)                                                    # plain cache hit afterwards
+        model.invalidate_plan()
+        want, want_u = model(x, t, cond2), model(x, t, unc2)
+    assert torch.equal(b, want) and torch.equal(bu, want_u) and torch.equal(b_again, want)
+    assert not torch.equal(want, want_u)
+
+
 @pytest.mark.parametrize("cfg_scale", [1.0, 3.0])
 def test_sampling_pipeline_matches_drop_in_loop(cfg_scale):
     """Device-resident loop (graph, t on device, in-place x update, fused CFG) vs the reference-shaped Python loop
