@@ -142,10 +142,25 @@ typedef struct {
        (B200SD_DT_F32; 0 = bf16 as above). With residual == out the call accumulates in place (each thread reads the
        element it then writes): the second launch of a split-operand product A_hi*[W_hi|W_lo] + A_lo*W_hi. */
     int32_t residual_dtype, rowbias_dtype;
+    /* split-K for problems with too few output tiles to fill the GPU (the 4x4 / 8x8 layers of a batch-16 training
+       step: 12-96 tiles on 148 SMs, each CTA bound by its own L2 read bandwidth over a long reduction). With
+       splitk_max > 1 the library may cut the K loop of every tile into up to splitk_max ranges run by different CTAs;
+       they park fp32 partials in splitk_ws and the last one to arrive sums them in split order (deterministic) and
+       runs the epilogue. The split depth depends on the tile count, hence on the batch: leave splitk_max at 0 where a
+       sample's result must not depend on the batch it travels in (inference). splitk_ws: >= splitk_ws_floats floats,
+       16-byte aligned; splitk_counters: splitk_counters_len zero-initialised uint32 (returned to zero). Calls that may
+       run concurrently must not share either buffer. */
+    float* splitk_ws;
+    int64_t splitk_ws_floats;
+    uint32_t* splitk_counters;
+    int32_t splitk_counters_len;
+    int32_t splitk_max;
 } b200sd_igemm_params;
 
 int b200sd_igemm(const b200sd_igemm_params* p, void* stream);
 int b200sd_igemm_stats_slots(int oh, int ow);
+/* split-K depth the most recent b200sd_igemm call of this process chose (1 = none; pair kernels always 1): tests, tools */
+int b200sd_igemm_last_splits(void);
 
 /* ------------------------------------------------------------------------------------------- weight gradient
  * Backward of the same leaves w.r.t. their weights (loss.backward(), train_ddpm_cond_celebhq_multi_gpu.py:362):

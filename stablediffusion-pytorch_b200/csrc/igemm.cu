@@ -21,6 +21,7 @@
 // which per-thread 16-byte loads/stores from 128 threads cannot (r1a profile: 5 % tensor-pipe on K=384 GEMMs).
 // Outputs TMA cannot address (fp32, row pitch not a multiple of 16 B, fewer than 64 columns) take a direct path.
 #include "host.h"
+#include <cstdio>
 #include "ptx.cuh"
 #include <cudaTypedefs.h>
 #include <mutex>
@@ -69,6 +70,12 @@ struct alignas(64) IgemmArgs {
     int vec_ok;    // every optional epilogue operand (and a directly stored output) is 16-byte addressable
     float* stats;  // [on][stats_p][stats_ld][2] partial sums, or null
     int stats_p, stats_slot0, stats_ld;
+    // split-K (non-pair kernels): every tile is S work items, each reducing a contiguous range of the K chunks; the
+    // items store their fp32 accumulators to `sk_ws` [tile][split][128][BN]; the LAST item of a tile to arrive (tile
+    // counter) sums the S partials in split order and runs the epilogue. 1 = off.
+    int splits;
+    float* sk_ws;
+    unsigned int* sk_count;
 };
 
 struct Tile {
@@ -213,11 +220,13 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
     // this CTA's work list: tile_of(i), i < my_tiles
     const int crank = CL2 ? static_cast<int>(cluster_ctarank()) : 0;
     const int unit = CL2 ? blockIdx.x >> 1 : blockIdx.x, nunits = CL2 ? gridDim.x >> 1 : gridDim.x;
-    const int nwork = CL2 ? args.num_ptiles : args.num_tiles;
+    const int S = CL2 ? 1 : args.splits;   // split-K depth (work item = tile * S + split: a tile's items run side by side)
+    const int nwork = CL2 ? args.num_ptiles : args.num_tiles * S;
     const int my_tiles = unit < nwork ? (nwork - unit + nunits - 1) / nunits : 0;
+    auto split_of = [&](int i) -> int { return S == 1 ? 0 : (unit + i * nunits) % S; };
     auto tile_of = [&](int i) -> int {
         const int w = unit + i * nunits;
-        if (!CL2) return w;
+        if (!CL2) return S == 1 ? w : w / S;
         // (row-tile pair, column tile); a pair's second row tile may lie past the last one: every access of such a
         // tile is out of bounds for TMA (zero fill / clipped) and masked in the epilogue
         return (2 * (w / args.tiles_col) + crank) * args.tiles_col + w % args.tiles_col;
@@ -265,10 +274,14 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
             int it = 0;
             for (int lt = 0; lt < my_tiles; ++lt) {
                 const Tile t = decode_tile(args, tile_of(lt));
+                const int sp = split_of(lt);
+                const int kb = static_cast<int>(static_cast<long long>(args.total_chunks) * sp / S);
+                const int ke = static_cast<int>(static_cast<long long>(args.total_chunks) * (sp + 1) / S);
                 int kc = 0;
                 for (int s = 0; s < args.n_seg; ++s) {
                     const SegDev sg = args.seg[s];
-                    for (int ch = 0; ch < sg.nchunk; ++ch, ++it, ++kc) {
+                    for (int ch = 0; ch < sg.nchunk; ++ch, ++kc) {
+                        if (kc < kb || kc >= ke) continue;   // another split's chunk
                         const int stage = it % STAGES;
                         const uint32_t phase = (it / STAGES) & 1;
                         mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -287,6 +300,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                                         t.y0 + sg.dy, t.n0);
                             tma_load_2d(sa + L::A_BYTES, &args.b_map, &full_bar[stage], kc * BK, t.col_t * BN);
                         }
+                        ++it;
                     }
                 }
             }
@@ -300,7 +314,10 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
             mbar_wait(&tempty_bar[buf], ((lt >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
             tc_fence_after();
             const uint32_t tacc = tmem_base + buf * BN;
-            for (int kc = 0; kc < args.total_chunks; ++kc, ++it) {
+            const int sp = split_of(lt);
+            const int kb = static_cast<int>(static_cast<long long>(args.total_chunks) * sp / S);
+            const int ke = static_cast<int>(static_cast<long long>(args.total_chunks) * (sp + 1) / S);
+            for (int kc = kb; kc < ke; ++kc, ++it) {
                 const int stage = it % STAGES;
                 mbar_wait(&full_bar[stage], (it / STAGES) & 1);
                 tc_fence_after();
@@ -312,7 +329,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                     for (int k = 0; k < BK / 16; ++k) {
                         // +32 B per K=16 step inside the 128 B swizzle atom: +2 in the (>>4) start-address field
                         if (CL2) umma_bf16_pair(tacc, da + 2 * k, db + 2 * k, idesc, (kc | k) != 0);
-                        else umma_bf16(tacc, da + 2 * k, db + 2 * k, idesc, (kc | k) != 0);
+                        else umma_bf16(tacc, da + 2 * k, db + 2 * k, idesc, ((kc - kb) | k) != 0);
                     }
                     if (CL2) umma_commit_pair(&empty_bar[stage], 3);
                     else umma_commit(&empty_bar[stage]);
@@ -370,14 +387,69 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
 
             mbar_wait(&tfull_bar[buf], (lt >> 1) & 1);
             tc_fence_after();
+            // ---- split-K: park this item's accumulator, then either leave the tile to a later item or finish it
+            bool discard = false;           // this item is not the tile's last: run the epilogue's motions, write nothing
+            const float* sk_tile = nullptr; // last item: the tile's S partials [S][128][BN]
+            if (!CL2 && S > 1) {
+                const int tile_id = tile_of(lt);
+                float* mine = args.sk_ws + (static_cast<long long>(tile_id) * S + split_of(lt)) * (BM * BN) + r * BN;
+#pragma unroll 1
+                for (int c = cg; c < BN / 32; c += 2) {
+                    if (t.col_t * BN + c * 32 >= args.n_out) break;
+                    uint32_t acc[32];
+                    tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + c * 32, acc);
+                    tmem_ld_wait();
+                    uint4* dst = reinterpret_cast<uint4*>(mine + c * 32);
+#pragma unroll
+                    for (int g = 0; g < 8; ++g) dst[g] = make_uint4(acc[4 * g], acc[4 * g + 1], acc[4 * g + 2], acc[4 * g + 3]);
+                }
+                tc_fence_before();
+                mbar_arrive(&tempty_bar[buf]);   // the accumulator is free already: the MMA warp may start tile lt + 2
+                __threadfence();
+                named_bar_sync(3, EPI_THREADS);
+                if (et == 0) {
+                    const unsigned int seen = atomicAdd(args.sk_count + tile_id, 1u);
+                    const bool last = seen == static_cast<unsigned int>(S - 1);
+                    if (last) args.sk_count[tile_id] = 0u;   // ready for the next launch
+                    red[0] = last ? 1.f : 0.f;
+                }
+                named_bar_sync(3, EPI_THREADS);
+                discard = red[0] == 0.f;
+                named_bar_sync(3, EPI_THREADS);    // red[0] is free again (the statistics path below uses `red`)
+                if (!discard) {
+                    __threadfence();
+                    sk_tile = args.sk_ws + static_cast<long long>(tile_id) * S * (BM * BN) + r * BN;
+                }
+            }
+            const bool row_live = row_ok && !discard;
             if (args.tma_res) mbar_wait(&res_bar[sb], NSTG == 2 ? (lt >> 1) & 1 : lt & 1);
 #pragma unroll 1
             for (int c = cg; c < BN / 32; c += 2) {
                 const int col0 = t.col_t * BN + c * 32;
                 if (col0 >= args.n_out) break;  // warp-uniform
                 uint32_t acc[32];
-                tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + c * 32, acc);
-                tmem_ld_wait();
+                if (!CL2 && S > 1) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) acc[j] = 0u;
+                    if (sk_tile) {   // fixed order: split 0, 1, ..., S-1 (plain loads: written by other CTAs of this launch)
+                        float sum[32];
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) sum[j] = 0.f;
+                        for (int sp = 0; sp < S; ++sp) {
+                            const float4* src = reinterpret_cast<const float4*>(sk_tile + static_cast<long long>(sp) * (BM * BN) + c * 32);
+#pragma unroll
+                            for (int g = 0; g < 8; ++g) {
+                                const float4 f = __ldcg(src + g);
+                                sum[4 * g] += f.x, sum[4 * g + 1] += f.y, sum[4 * g + 2] += f.z, sum[4 * g + 3] += f.w;
+                            }
+                        }
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) acc[j] = __float_as_uint(sum[j]);
+                    }
+                } else {
+                    tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + c * 32, acc);
+                    tmem_ld_wait();
+                }
                 if (fast && col0 + 32 <= args.n_out) {
                     // full 32-column chunk with 16-byte addressable operands: straight-line code, one uniform branch
                     // per optional operand per chunk (the general path below pays them per 8 columns, with scalar
@@ -444,7 +516,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                             for (int j = 0; j < 8; ++j) v[g][j] *= f[j];
                         }
                     }
-                    if (has_res && args.res_f32 && row_ok) {
+                    if (has_res && args.res_f32 && row_live) {
                         // plain loads (not __ldg): with residual == out this launch accumulates in place
                         const float4* rp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(args.residual) + r_off + col0);
 #pragma unroll
@@ -453,7 +525,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                             v[g][0] += a0.x, v[g][1] += a0.y, v[g][2] += a0.z, v[g][3] += a0.w;
                             v[g][4] += a1.x, v[g][5] += a1.y, v[g][6] += a1.z, v[g][7] += a1.w;
                         }
-                    } else if (has_res && !args.tma_res && row_ok) {
+                    } else if (has_res && !args.tma_res && row_live) {
                         const uint4* rp = reinterpret_cast<const uint4*>(args.residual + r_off + col0);
 #pragma unroll
                         for (int g = 0; g < 4; ++g) {
@@ -477,7 +549,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                             }
                             sts128(sa, pack8(v[g]));
                         }
-                    } else if (row_ok) {
+                    } else if (row_live) {
                         if (args.out_f32) {
                             float4* op = reinterpret_cast<float4*>(static_cast<float*>(args.out) + o_off + col0);
 #pragma unroll
@@ -522,14 +594,14 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                             unpack8(lds128(sp), f);
 #pragma unroll
                             for (int j = 0; j < 8; ++j) v[j] += f[j];
-                        } else if (args.residual && row_ok) {
+                        } else if (args.residual && row_live) {
                             float f[8];
                             load8_bf16(args.residual + r_off + col, nv, f);
 #pragma unroll
                             for (int j = 0; j < 8; ++j) v[j] += f[j];
                         }
                         sts128(sp, pack8(v));
-                    } else if (row_ok) {
+                    } else if (row_live) {
                         if (args.residual && args.res_f32) {
                             const float* rp = reinterpret_cast<const float*>(args.residual) + r_off + col;
 #pragma unroll
@@ -565,9 +637,10 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                 }
             }
             tc_fence_before();
-            // accumulator free: the MMA warp may start tile lt+2 in it (CTA pair: the leader's barrier counts both CTAs)
+            // accumulator free: the MMA warp may start tile lt+2 in it (CTA pair: the leader's barrier counts both CTAs;
+            // split-K released it right after parking the partial)
             if (CL2) mbar_arrive_cluster(mapa_rank(&tempty_bar[buf], 0));
-            else mbar_arrive(&tempty_bar[buf]);
+            else if (S == 1) mbar_arrive(&tempty_bar[buf]);
 
             if (BN >= 64 && args.tma_out) {
                 fence_proxy_async();  // staging writes (generic proxy) -> visible to the TMA store (async proxy)
@@ -582,11 +655,13 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
                 if (et == 0) {
 #pragma unroll
                     for (int p = 0; p < PANELS; ++p)
-                        if (t.col_t * BN + p * 64 < args.n_out)
+                        if (!discard && t.col_t * BN + p * 64 < args.n_out)
                             tma_store_4d(&args.out_map, stg + p * PANEL_BYTES, t.col_t * BN + p * 64, t.x0, t.y0, t.n0);
                     tma_store_commit();
                 }
-                if (args.stats && rpi >= 8) {
+                if (discard) {
+                    // nothing to count: another item owns this tile's output and statistics
+                } else if (args.stats && rpi >= 8) {
                     // per-channel sum / sum of squares of the bf16-rounded tile, one partial per (image, tile slot),
                     // deterministic (no atomics). Warp e owns the BN/8 columns [e*W, e*W+W) for ALL 128 rows, so one
                     // image's partial is complete inside the warp: no shared-memory exchange and no barrier (the
@@ -828,6 +903,8 @@ static int launch_igemm(const IgemmArgs& a, int grid, cudaStream_t st) {
 
 using namespace b200;
 
+static int g_last_splits = 1;   // split-K depth the last non-pair launch of this process used (tests, tools)
+
 extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
     B200_REQUIRE(p, "igemm: null params");
     B200_REQUIRE(p->n_src >= 1 && p->n_src <= 4, "igemm: n_src=%d not in [1,4]", p->n_src);
@@ -899,6 +976,31 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
     if (const char* f = getenv("B200SD_FORCE_BN")) {  // tuning aid (tools/kernel_bench.py); not used by the product path
         const int v = atoi(f);
         if ((v == 256 || v == 192 || v == 128 || v == 64) && n > 32) BNsel = v;
+    }
+    // split-K depth (opt-in: the caller passes splitk_max > 1): only where at most half the SMs would have a tile; at
+    // most 4 ranges of at least 16 K chunks each. Measured on B200 (tools/splitk_sweep.py, profiles/r2i_splitk.md): it
+    // pays only for the 4x4-resolution layers of a batch-16 training step (16-24 tiles: -11 % .. -20 % at depth 3-4),
+    // is neutral to harmful from 48 tiles up, and a deeper split loses to the partials' round trip.
+    a.splits = 1;
+    a.sk_ws = p->splitk_ws;
+    a.sk_count = p->splitk_counters;
+    {
+        const long long tl = m_tiles * ((n + BNsel - 1) / BNsel);
+        if (p->splitk_max > 1 && p->splitk_ws && p->splitk_counters && tl * 2 <= sms && total >= 32 &&
+            tl <= p->splitk_counters_len && (reinterpret_cast<uintptr_t>(p->splitk_ws) & 15) == 0) {
+            long long sd = sms / tl;
+            if (sd > p->splitk_max) sd = p->splitk_max;
+            if (sd > 4) sd = 4;
+            if (sd > total / 16) sd = total / 16;
+            if (sd >= 2 && tl * sd * BM * BNsel <= p->splitk_ws_floats) a.splits = (int)sd;
+        }
+    }
+    if (const char* f = getenv("B200SD_FORCE_SPLITS")) {   // tuning aid (tools/splitk_sweep.py), with B200SD_FORCE_BN
+        const long long v = atoi(f);
+        const long long tl = m_tiles * ((n + BNsel - 1) / BNsel);
+        if (p->splitk_ws && p->splitk_counters && v >= 1 && v <= total && tl <= p->splitk_counters_len &&
+            tl * v * BM * BNsel <= p->splitk_ws_floats)
+            a.splits = (int)v;
     }
     a.tiles_col = (n + BNsel - 1) / BNsel;
     const long long tiles_ll = m_tiles * a.tiles_col;
@@ -990,7 +1092,7 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
         const char* f = getenv("B200SD_CL2_MINCHUNKS");
         return f ? atoi(f) : 16;
     }();
-    if (total >= cl2_min && BNsel >= 128 && m_tiles >= 2) {
+    if (a.splits == 1 && total >= cl2_min && BNsel >= 128 && m_tiles >= 2) {
         const int ncl = a.num_ptiles < sms / 2 ? a.num_ptiles : sms / 2;
         switch (BNsel) {
             case 256: return launch_igemm<256, 4, 1, true>(a, 2 * ncl, st);
@@ -998,7 +1100,13 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
             default: return launch_igemm<128, 5, 1, true>(a, 2 * ncl, st);
         }
     }
-    const int grid = a.num_tiles < sms ? a.num_tiles : sms;
+    g_last_splits = a.splits;
+    static const bool dbg = getenv("B200SD_DEBUG_IGEMM") != nullptr;   // one line per launch: shape, tile choice, split depth
+    if (dbg)
+        fprintf(stderr, "igemm M=%lld N=%d chunks=%d BN=%d tiles=%d splits=%d splitk_max=%d\n",
+                (long long)p->on * p->oh * p->ow, n, total, BNsel, a.num_tiles, a.splits, p->splitk_max);
+    const long long items = (long long)a.num_tiles * a.splits;
+    const int grid = items < sms ? (int)items : sms;
     switch (BNsel) {
         case 256: return launch_igemm<256, 3>(a, grid, st);
         case 192: return launch_igemm<192, 3>(a, grid, st);
@@ -1007,6 +1115,8 @@ extern "C" int b200sd_igemm(const b200sd_igemm_params* p, void* stream) {
         default: return launch_igemm<32, 6>(a, grid, st);
     }
 }
+
+extern "C" int b200sd_igemm_last_splits(void) { return g_last_splits; }
 
 /* Number of per-image partial-statistics slots one b200sd_igemm call with this output grid writes. */
 extern "C" int b200sd_igemm_stats_slots(int oh, int ow) {

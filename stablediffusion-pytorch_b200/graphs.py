@@ -457,7 +457,7 @@ class TrainGraph:
         return fired
 
     def _build(self, forward, wrt, dev):
-        with torch.autocast("cuda", enabled=False), torch.enable_grad():
+        with torch.autocast("cuda", enabled=False), torch.enable_grad(), rt.training_pass():
             side = torch.cuda.Stream(device=dev)
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):

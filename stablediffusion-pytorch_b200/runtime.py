@@ -17,7 +17,7 @@ _ACT = {None: 0, "none": 0, "silu": 1, "relu": 2}
 
 EXPORTS = [
     "b200sd_last_error", "b200sd_version", "b200sd_launch_count", "b200sd_sched_add_noise",
-    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_attention_lse", "b200sd_attention_tc", "b200sd_attention_bwd", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_groupnorm_split", "b200sd_split_f32", "b200sd_rowblocks", "b200sd_groupnorm_bwd", "b200sd_colsum", "b200sd_colsum_blocks", "b200sd_colsum_static", "b200sd_colsum_static_max_floats", "b200sd_vq_blocks", "b200sd_vq_nearest", "b200sd_sampler_step", "b200sd_opt_chunk_size", "b200sd_opt_chunk_elems", "b200sd_grad_sqnorm", "b200sd_adam_ema_step", "b200sd_percent_opt_step",
+    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_igemm_last_splits", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_attention_lse", "b200sd_attention_tc", "b200sd_attention_bwd", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_groupnorm_split", "b200sd_split_f32", "b200sd_rowblocks", "b200sd_groupnorm_bwd", "b200sd_colsum", "b200sd_colsum_blocks", "b200sd_colsum_static", "b200sd_colsum_static_max_floats", "b200sd_vq_blocks", "b200sd_vq_nearest", "b200sd_sampler_step", "b200sd_opt_chunk_size", "b200sd_opt_chunk_elems", "b200sd_grad_sqnorm", "b200sd_adam_ema_step", "b200sd_percent_opt_step",
     "b200sd_reduce_f32", "b200sd_attention",
     "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16", "b200sd_im2col", "b200sd_col2im",
     "b200sd_layernorm_mod", "b200sd_layernorm_mod_bwd", "b200sd_rows_per_slot", "b200sd_gate_residual",
@@ -58,6 +58,8 @@ class IgemmParams(C.Structure):
         ("act", C.c_int32), ("stats", C.c_void_p),
         ("stats_p", C.c_int32), ("stats_slot0", C.c_int32), ("stats_ld", C.c_int32),
         ("residual_dtype", C.c_int32), ("rowbias_dtype", C.c_int32),
+        ("splitk_ws", C.c_void_p), ("splitk_ws_floats", C.c_int64), ("splitk_counters", C.c_void_p),
+        ("splitk_counters_len", C.c_int32), ("splitk_max", C.c_int32),
     ]
 
 
@@ -315,6 +317,53 @@ def stats_slots(oh, ow):
     return int(lib().b200sd_igemm_stats_slots(int(oh), int(ow)))
 
 
+# Split-K for the small GEMMs of a training pass (csrc/igemm.cu; tests/test_kernels_gpu.py). Measured
+# (profiles/r2i_splitk.md): it pays for the 4x4-resolution layers only — a dozen launches, 15.40 -> 15.25 ms per
+# forward + backward on the same box — so the library's rule is conservative (at most half the SMs busy, depth <= 4,
+# >= 16 K chunks per range). 0 disables it (B200SD_SPLITK_MAX).
+SPLITK_MAX = int(os.environ.get("B200SD_SPLITK_MAX", "4"))
+_SPLITK = {}
+
+
+def _splitk_buffers(dev):
+    """(workspace fp32, counters uint32) of the split-K GEMMs of one device: room for one launch's partials (at most one
+    work item per SM, 128 x 256 fp32 each); launches on one stream use it one after the other."""
+    key = dev.index if dev.index is not None else torch.cuda.current_device()
+    ent = _SPLITK.get(key)
+    if ent is None:
+        if torch.cuda.is_current_stream_capturing():
+            return None     # first use inside a capture: no split for this launch (warm-up passes allocate it)
+        sms = torch.cuda.get_device_properties(key).multi_processor_count
+        ent = _SPLITK[key] = (torch.empty(sms * 128 * 256, device=dev, dtype=torch.float32),
+                              torch.zeros(4096, device=dev, dtype=torch.int32))
+    return ent
+
+
+_TRAINING_PASS = 0
+
+
+class training_pass:
+    """Marks a region as part of a training step (graphs.TrainGraph wraps its warm-up passes and both captures in it):
+    the backward half runs on autograd's device worker threads with grad mode off, where nothing else tells a GEMM
+    launch that it belongs to a training pass."""
+
+    def __enter__(self):
+        global _TRAINING_PASS
+        _TRAINING_PASS += 1
+
+    def __exit__(self, *exc):
+        global _TRAINING_PASS
+        _TRAINING_PASS -= 1
+
+
+def in_training_pass():
+    """True while autograd records a forward or a captured training step is being built: the only places split-K GEMMs
+    are used (their summation order depends on the tile count, hence on the batch; inference keeps a sample's result
+    independent of the batch it travels in, tests/test_fullsize_gpu.py). An EAGER backward pass (training graphs
+    disabled) is not recognised and runs unsplit."""
+    return _TRAINING_PASS > 0 or torch.is_grad_enabled()
+
+
 def igemm(srcs, segs, weight, n_out, on, oh, ow, out, out_strides, bias=None, rowbias=None, gate=None,
           residual=None, res_strides=None, act=None, stats=None):
     """Raw launcher. srcs: list[Src]; segs: list of (src, dy, dx, c0, nchunk); out_strides=(sn, sy, sx) elements.
@@ -345,6 +394,11 @@ def igemm(srcs, segs, weight, n_out, on, oh, ow, out, out_strides, bias=None, ro
         st, sp, s0, sld = stats[:4]
         coff = stats[4] if len(stats) > 4 else 0
         p.stats, p.stats_p, p.stats_slot0, p.stats_ld = st.data_ptr() + 8 * coff, sp, s0, sld - coff
+    if SPLITK_MAX > 1 and in_training_pass():
+        sk = _splitk_buffers(out.device)
+        if sk is not None:
+            p.splitk_ws, p.splitk_ws_floats = sk[0].data_ptr(), sk[0].numel()
+            p.splitk_counters, p.splitk_counters_len, p.splitk_max = sk[1].data_ptr(), sk[1].numel(), SPLITK_MAX
     tok = _pb()
     check(lib().b200sd_igemm(C.byref(p), stream_ptr()), "igemm")
     if tok is not None:

@@ -32,6 +32,8 @@ def test_param_struct_layout_matches_header(rt):
     assert rt.IgemmParams.segs.offset == 8 + 4 * 48
     assert rt.IgemmParams.weight.offset == 8 + 4 * 48 + 40 * 20
     assert rt.IgemmParams.weight.offset % 8 == 0
+    assert rt.IgemmParams.splitk_ws.offset == 1176 and rt.IgemmParams.splitk_max.offset == 1204   # gcc's offsetof
+    assert ctypes.sizeof(rt.IgemmParams) == 1208
 
 
 def test_no_cpu_fallback(rt):

@@ -426,3 +426,54 @@ def test_attention_backward(rt, b, heads, lq, lk, d):
     assert relerr(dq.cpu(), un(qr.grad, lq)) < 1.5e-2
     assert relerr(dkv[:, :C].cpu(), un(kr.grad, lk)) < 1.5e-2
     assert relerr(dkv[:, C:].cpu(), un(vr.grad, lk)) < 1.5e-2
+
+
+@pytest.mark.parametrize("n,h,w,cin,cout,k", [(16, 4, 4, 768, 768, 3), (16, 8, 8, 512, 384, 3), (4, 8, 8, 384, 200, 3),
+                                              (2, 4, 4, 2048, 96, 1)])
+def test_split_k_matches_the_single_pass_gemm(rt, n, h, w, cin, cout, k):
+    """Split-K (training passes only: the K loop of a tile cut into ranges run by different CTAs, fp32 partials parked in a
+    workspace, the last CTA to arrive sums them in split order and runs the full epilogue — csrc/igemm.cu) against the
+    same launch without it: same epilogue (bias, time-embedding row bias, SiLU, residual, fused GroupNorm statistics),
+    results within fp32 summation-order noise of each other and of the fp32 reference; run twice in a row (the tile
+    counters are returned to zero) and bit-identical between the two runs (fixed summation order)."""
+    dev = _dev()
+    from sdb200 import ops
+    g = torch.Generator().manual_seed(n + h + cin + cout)
+    x = bf(torch.randn(n, cin, h, w, generator=g))
+    wt = torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5
+    b = torch.randn(cout, generator=g)
+    temb = bf(torch.randn(n, cout, generator=g))
+    res = bf(torch.randn(n * h * w, cout, generator=g))
+    xh = x.permute(0, 2, 3, 1).reshape(-1, cin).contiguous().to(dev)
+    wp = ops.pack_conv_weight(wt.to(dev))
+    want_stats = cout % 8 == 0 and cout > 32
+
+    def run():
+        st = None
+        if want_stats:
+            P = rt.stats_slots(h, w)
+            st = (torch.full((n, P, cout, 2), float("nan"), device=dev), P, 0, cout)
+        out = ops.conv_same(xh, n, h, w, cin, wp, cout, k, bias=b.to(dev), rowbias=temb.to(dev), residual=res.to(dev),
+                            act="silu", stats=st)
+        return out, (st[0] if st else None), int(rt.lib().b200sd_igemm_last_splits())
+
+    with torch.no_grad():
+        plain, pst, s_plain = run()
+    keep = rt.SPLITK_MAX
+    rt.SPLITK_MAX = 8          # opt-in (off by default: it pays for a handful of launches only, profiles/r2i_splitk.md)
+    try:
+        with torch.enable_grad():
+            split, sst, s_split = run()
+            split2, sst2, _ = run()
+    finally:
+        rt.SPLITK_MAX = keep
+    torch.cuda.synchronize()
+    assert s_plain == 1 and s_split >= 2, (s_plain, s_split)
+    ref = F.silu(F.conv2d(x.float(), bf(wt).float(), b, padding=k // 2) + temb.float()[:, :, None, None])
+    ref = ref.permute(0, 2, 3, 1).reshape(-1, cout) + res.float()
+    assert relerr(split.cpu(), ref) < 6e-3 and relerr(plain.cpu(), ref) < 6e-3
+    assert relerr(split, plain) < 4e-3                     # one bf16 ulp where the fp32 sums round differently
+    assert torch.equal(split, split2)
+    if want_stats:
+        assert torch.isfinite(sst).all() and torch.equal(sst, sst2)
+        assert relerr(sst.sum(1), pst.sum(1)) < 2e-3
