@@ -163,3 +163,53 @@ def test_second_in_flight_forward_of_a_captured_step_is_refused():
     b.square().mean().backward()          # the latest forward: fine
     with pytest.raises(B200Error, match="another forward"):
         a.square().mean().backward()
+
+
+def test_arrival_order_gradient_layout_trains_like_the_parameter_order_one():
+    """With the gradient exchange captured inside the backward graph, the flat gradient buffer is laid out in
+    gradient-ARRIVAL order (graphs.arrival_slots) and the fused clip + Adam + EMA kernels read the gradients through their
+    own offsets (b200sd_opt_chunk.goff). A one-rank NCCL group exercises exactly that path on one GPU (the all-reduce of a
+    single rank changes nothing): two optimizer steps must leave every parameter bit-identical to the plain
+    parameter-order run, and the layout must really differ from parameter order."""
+    dev = _dev()
+    import copy
+    import os
+    import torch.distributed as dist
+    from models.unet_cond_base import Unet
+    from sdb200.optim import FusedAdam
+    if dist.is_initialized():
+        pytest.skip("a process group is already up in this process")
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29547")
+    dist.init_process_group("nccl", rank=0, world_size=1, device_id=dev)
+    try:
+        fx = load_golden("unet_small_cond")
+        inp, cfg = fx["inputs"], fx["config"]
+        torch.manual_seed(fx["seed"])
+        base = Unet(4, cfg).train().to(dev)
+        cond = cond_of(inp, cfg, dev)
+        x, t = inp["x"].to(dev), inp["t"].to(dev)
+        target = torch.randn(x.shape, generator=torch.Generator().manual_seed(3)).to(dev)
+        runs = {}
+        for name in ("parameter_order", "arrival_order"):
+            m = copy.deepcopy(base)
+            if name == "arrival_order":
+                m.__dict__["_grad_overlap"] = (dist.group.WORLD, (1 << 20) // 4)    # what parallel.DataParallel sets at N > 1
+            opt = FusedAdam(m.parameters(), lr=1e-3, max_grad_norm=1.0)
+            for _ in range(2):
+                opt.zero_grad(set_to_none=True)
+                torch.nn.functional.mse_loss(m(x, t, cond), target).backward()
+                opt.step()
+            tg = m.__dict__["_train_graph"]
+            offs = [sl[0] for sl in tg.slots if sl is not None]
+            runs[name] = ([p.detach().clone() for p in m.parameters()], offs, tg.reduced_in_graph, tg.n_buckets,
+                          opt.grad_norm.item())
+        torch.cuda.synchronize()
+        pa, offs_a, red_a, _, gn_a = runs["parameter_order"]
+        pb, offs_b, red_b, nb, gn_b = runs["arrival_order"]
+        assert offs_a == sorted(offs_a) and offs_b != sorted(offs_b)      # the second layout is a real permutation
+        assert red_b and nb >= 2 and not red_a
+        assert gn_a == gn_b
+        assert all(torch.equal(u, v) for u, v in zip(pa, pb))
+    finally:
+        dist.destroy_process_group()
