@@ -745,8 +745,9 @@ def train_leg(args, ucfg, dev, rank, world, barrier, max_over_ranks, make_model=
         "grad_allreduce": None if world == 1 else (
             "torch DistributedDataParallel: 25 MB NCCL buckets, reduced after the backward graph has replayed"
             if args.train_ddp == "torch" else
-            "sdb200.parallel.DataParallel: in-place NCCL AVG all-reduces of 64 MB slices of the flat fp32 gradient "
-            "buffer, captured inside the backward graph on a side stream as each bucket's last gradient is produced"),
+            "sdb200.parallel.DataParallel: in-place NCCL AVG all-reduces of 32 MB slices of the flat fp32 gradient "
+            "buffer (laid out in gradient-arrival order), captured inside the backward graph on a side stream as each "
+            "bucket's last gradient is produced"),
         "loss_finite": bool(out["value"][3] == out["value"][3]),
         "e2e": None if not e2e else {"value": out["e2e"][0], "unit": "samples/s", "ms_per_step": out["e2e"][1],
                                      "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
