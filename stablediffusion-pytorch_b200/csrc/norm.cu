@@ -3,6 +3,7 @@
 // memory when it fits so that the three passes (mean, centred variance, normalise) touch HBM once for the read
 // and once for the write. Mean/variance use the two-pass form in fp32 (no E[x^2]-E[x]^2 cancellation).
 #include "host.h"
+#include <cstdlib>
 #include <cuda_bf16.h>
 
 namespace b200 {
@@ -127,8 +128,18 @@ struct StatSeg {
 
 // SiLU / ReLU with the activation fixed at compile time. SiLU = v * rcp(1 + ex2(-v log2 e)): two MUFU ops and three
 // FP32 ops per element (an IEEE division here was ~20 instructions per element and made the kernel issue-bound).
+// GN_ACT_SILU_TANH: SiLU = h + h * tanh(h), h = v / 2 — ONE MUFU op (tanh.approx.f32, relative error 2^-11 on tanh,
+// i.e. at most |v| * 2.4e-4 absolute on the result: below the bf16 rounding of the stored output for |v| < 8) instead of
+// two (ex2 + rcp).
+constexpr int GN_ACT_SILU_TANH = 100;
 template <int ACT>
 __device__ __forceinline__ float act_fast(float v) {
+    if (ACT == GN_ACT_SILU_TANH) {
+        const float h = 0.5f * v;
+        float t;
+        asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
+        return fmaf(h, t, h);
+    }
     if (ACT == B200SD_ACT_SILU) return __fdividef(v, 1.f + __expf(-v));
     if (ACT == B200SD_ACT_RELU) return fmaxf(v, 0.f);
     return v;
@@ -658,7 +669,9 @@ extern "C" int b200sd_groupnorm_apply(const void* x, int64_t ld_x, void* y, int6
                  static_cast<__nv_bfloat16*>(y), ld_y, s0, c_split, s1, gamma, beta, hw, c, groups, eps,
                  (int)rows_per_block, rpp);
     };
-    if (act == B200SD_ACT_SILU) go(gn_apply_kernel<B200SD_ACT_SILU>);
+    static const bool silu_tanh = [] { const char* f = getenv("B200SD_GN_SILU_TANH"); return f && atoi(f) != 0; }();
+    if (act == B200SD_ACT_SILU && silu_tanh) go(gn_apply_kernel<GN_ACT_SILU_TANH>);
+    else if (act == B200SD_ACT_SILU) go(gn_apply_kernel<B200SD_ACT_SILU>);
     else if (act == B200SD_ACT_RELU) go(gn_apply_kernel<B200SD_ACT_RELU>);
     else go(gn_apply_kernel<B200SD_ACT_NONE>);
     B200_CHECK_LAUNCH("groupnorm_apply");
