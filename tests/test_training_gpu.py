@@ -30,8 +30,10 @@ def _oracle_grads(model, cfg, x, t, cond, target, relu=False, bf16=False):
     return loss.item(), {k: v.grad for k, v in sd.items() if v.grad is not None}
 
 
-@pytest.mark.parametrize("name", ["unet_small_cond", "unet_small_uncond", "unet_small_cond_relu"])
+@pytest.mark.parametrize("name", ["unet_small_cond", "unet_small_uncond", "unet_small_cond_relu", "unet_full_cond"])
 def test_unet_gradients_vs_oracle(name):
+    """(unet_full_cond: the full config/celebhq_text_image_cond.yaml network, 118 M parameters, batch 2 — the
+    configuration bench.py trains, not only the reduced fixtures.)"""
     dev = _dev()
     fx = load_golden(name)
     if "uncond" in name:
