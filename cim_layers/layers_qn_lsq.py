@@ -97,6 +97,28 @@ class _LsqMixin:
         self.__dict__.pop("_lsq_ready", None)     # loaded step sizes may be the untouched 1.0 again
         self.__dict__["_gain_init_pending"] = True
 
+    # ---- precise parity mode (sdb200.engine.set_parity_mode("precise"), inference): the product in the CODE domain
+    def _exact_mode(self):
+        return E.precise() and self.input_quant and self.weight_quant and self.weight.dtype == torch.float32
+
+    def _eff_step(self, step, bits, numel):
+        """VALUE of the grad-scaled step the reference quantises with (quant_noise_utils.py:51-58), fp32 0-dim."""
+        return Q._grad_scale(step.detach().float(), rt.lsq_grad_scale(Q.qp_of(bits), numel)).reshape(())
+
+    def _exact_weights(self):
+        """Operand list [(bf16-exact weight tensor, fp32 scalar factor or None)] whose products with the integer input
+        codes sum to the reference's fp32 product up to fp32 summation order: without weight noise the integer weight
+        codes (times s_x' s_w' afterwards); with noise the fp32 noisy weight as a (hi, lo) pair of bf16 tensors — 16
+        significand bits instead of 8, so a pre-quantisation value no longer crosses an output rounding boundary
+        because of the operand format (the fast path's 2-10 % of output codes off by one)."""
+        if self.noise_scale == 0:
+            wq, _ = self._w_qn(isint=True)
+            return [torch.round(wq.detach())], self._eff_step(self.step_size_weight, self.weight_bit, self.weight.numel())
+        w, _ = self._w_qn()
+        w = w.detach()
+        hi = w.to(torch.bfloat16).float()
+        return [hi, (w - hi).to(torch.bfloat16).float()], None
+
     _WQ_ISINT = False      # the ADDA classes quantise their weights to integer codes (isint=True)
 
     def _wq_spec(self):
@@ -158,6 +180,29 @@ class Conv2d_qn_lsq(nn.Conv2d, _LsqMixin):
         ops.conv_down4x4(x_rows, a.n, a.h, a.w, a.c, wmat, cout, bias=bias, ld_x=x_rows.stride(0), out=o.t)
         return o
 
+    def _conv_exact(self, a):
+        """Precise parity mode: integer input codes against exact weight operands, fp32 accumulation, the steps applied
+        afterwards (see _exact_weights). 3x3 / 1x1 'same' convolutions with >= 8-aligned output channels; None otherwise."""
+        k, s, p = self.kernel_size, self.stride, self.padding
+        cout = self.out_channels
+        if not (k in ((3, 3), (1, 1)) and s == (1, 1) and p == (k[0] // 2, k[0] // 2) and self.groups == 1 and cout % 8 == 0):
+            return None
+        codes = self._q_in(a.t, a.n * a.hw * a.c, isint=True)
+        ws, sw = self._exact_weights()
+        acc = None
+        for wpart in ws:
+            wm = ops.pack_conv_weight(wpart)
+            if acc is None:
+                acc = torch.empty(a.n * a.hw, cout, device=codes.device, dtype=torch.float32)
+                ops.conv_same(codes, a.n, a.h, a.w, a.c, wm, cout, k[0], ld_x=codes.stride(0), out=acc)
+            else:
+                ops.conv_same(codes, a.n, a.h, a.w, a.c, wm, cout, k[0], ld_x=codes.stride(0), out=acc, residual=acc)
+        sx = self._eff_step(self.step_size_input, self.input_bit, a.n * a.hw * a.c)
+        y = acc * (sx * sw if sw is not None else sx)
+        if self.bias is not None:
+            y = y + self.bias.detach().float()
+        return E.Act(self._q_out(y.contiguous(), a.n * a.hw * cout), a.n, a.h, a.w, cout)
+
     def forward_act(self, a):
         """Engine entry: NHWC bf16 Act -> Act. Channel counts that are not multiples of 8 (the DiT mask conv: 18 -> 3)
         travel in zero-padded rows; zeros quantise to code 0 and do not move the lazily initialised step sizes."""
@@ -166,6 +211,10 @@ class Conv2d_qn_lsq(nn.Conv2d, _LsqMixin):
         cp = (a.c + 7) // 8 * 8
         if a.t.shape[1] != cp:
             raise rt.B200Error("Conv2d_qn_lsq: input rows must be packed to the channel count rounded up to 8")
+        if self._exact_mode():
+            y = self._conv_exact(a)
+            if y is not None:
+                return y
         xq = self._q_in(a.t, a.n * a.hw * a.c)
         w, _ = self._w_qn()
         y = self._conv(a, xq, w)
@@ -206,6 +255,24 @@ class Linear_qn_lsq(nn.Linear, _LsqMixin):
         if rows.shape[1] < Kp:
             raise rt.B200Error("Linear_qn_lsq: input rows narrower than in_features rounded up to 8")
         x = rows if rows.shape[1] == Kp else rows[:, :Kp].contiguous()
+        if self._exact_mode():
+            codes = self._q_in(x, x.shape[0] * K, isint=True)          # bf16 integers: exact
+            ws, sw = self._exact_weights()
+            acc = None
+            for wpart in ws:      # fp32 accumulation; the second operand of a (hi, lo) pair adds in place
+                wp = ops.pack_linear_weight(self._pad_k(wpart))
+                acc = rt.linear(codes, wp, out_dtype=torch.float32) if acc is None else \
+                    rt.linear(codes, wp, out=acc, residual=acc)
+            sx = self._eff_step(self.step_size_input, self.input_bit, x.shape[0] * K)
+            y = acc * (sx * sw if sw is not None else sx)
+            if self.bias is not None:
+                y = y + self.bias.detach().float()
+            y = self._q_out(y.contiguous(), y.shape[0] * N)
+            if act is not None:
+                if act != "relu":
+                    raise rt.B200Error("Linear_qn_lsq: only ReLU may follow a quantised Linear")
+                y = torch.relu(y)
+            return y
         xq = self._q_in(x, x.shape[0] * K)
         w, _ = self._w_qn()
         y = self._linear(xq, self._pad_k(w))

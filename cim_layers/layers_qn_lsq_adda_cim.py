@@ -174,6 +174,7 @@ class _AddaMixin(_LsqMixin):
             raise rt.B200Error("ADDA layers: ADC noise tables hold 1000 columns (layers_utils_adda.py:100-105)")
         cfg = {"slices": self.bit_slices, "slice_bit": self.slice_bit, "input_bit": self.input_bit, "qp_in": qp_in,
                "numel_in": numel_in, "R": float(2 ** (self.adc_bit - 1) - 1), "blocks": blocks,
+               "split_w": E.precise() and self.noise_scale != 0,
                "gain_noise": self.gain_noise.to(x.device, torch.float32) if noisy else None,
                "offset_noise": self.offset_noise.to(x.device, torch.float32) if noisy else None}
         if self.__dict__.get("_gain_init_pending", True):

@@ -346,10 +346,17 @@ class AddaFn(Function):
         out = (torch.empty if covered else torch.zeros)(M, N, device=x.device, dtype=torch.float32)
         seen = set()
         for r0, rn, c0, cn in cfg["blocks"]:
-            wp = ops.pack_linear_weight(w[c0:c0 + cn, r0:r0 + rn])
+            wb = w[c0:c0 + cn, r0:r0 + rn]
+            wp = ops.pack_linear_weight(wb)
             if keep is not None:
                 keep["packed"].append(wp)
             part = rt.linear(digits[:, r0:r0 + rn], wp, out_dtype=torch.float32)
+            if cfg.get("split_w"):
+                # precise parity mode: the noisy (non-integer) weight codes as a (hi, lo) pair of bf16 operands — the
+                # digits are exact, so the analogue partial sums carry 16 significand bits of the weights instead of 8
+                # and the ADC codes stop flipping on the operand format (the fast path: 2-6 % of output codes)
+                lo = ops.pack_linear_weight(wb - wp[:, :rn].float())
+                rt.linear(digits[:, r0:r0 + rn], lo, out=part, residual=part)
             rt.adc_combine(part, out, M, cn, c0, cfg["slices"], cfg["slice_bit"], a1, cfg["R"], cfg["gain_noise"],
                            cfg["offset_noise"], accumulate=not covered or c0 in seen)
             seen.add(c0)

@@ -171,6 +171,20 @@ def test_lsq_layer_forward_backward_vs_oracle(name):
     # now and then: at most one output step, on a small fraction of the outputs
     assert dcode.max().item() <= 1 and frac_same > 0.90
     assert relerr(out1.cpu(), f["y1"]) < 3e-2
+    # precise parity mode: the product runs in the CODE domain (integer input codes against integer weight codes, or
+    # against the noisy fp32 weight as a (hi, lo) pair of bf16 operands) with fp32 accumulation — what is left between
+    # the two outputs is fp32 summation order
+    from sdb200 import engine as E
+    E.set_parity_mode("precise")
+    try:
+        with torch.no_grad():
+            out3 = layer(x2.to(dev))
+    finally:
+        E.set_parity_mode("fast")
+    dcode3 = (torch.round(out3.cpu() / s_out) - torch.round(ref2.detach() / s_out)).abs()
+    same3 = (dcode3 < 0.5).float().mean().item()
+    print(f"{name}: precise mode: output codes identical {100 * same3:.3f}% max |dcode| {dcode3.max().item():.1f}")
+    assert dcode3.max().item() <= 1 and same3 > 0.999
     for k, v in layer.named_parameters():
         ref_g = p2[k].grad
         got = v.grad.cpu()
@@ -253,6 +267,21 @@ def test_adda_linear_vs_oracle(name):
             # by one on some boundaries and the upper DAC slice carries weight 16
             assert dcode.max().item() <= 3 and same > 0.7
     assert relerr(out1.cpu(), f["y1"]) < 5e-2                            # vs the reference on the un-rounded inputs
+    if not exact:
+        # precise parity mode: noisy weight codes as (hi, lo) bf16 operand pairs, so the ADC sees 16 significand bits
+        from sdb200 import engine as E
+        E.set_parity_mode("precise")
+        try:
+            with torch.no_grad():
+                out3 = layer(x2.to(dev))
+        finally:
+            E.set_parity_mode("fast")
+        dcode = (torch.round(out3.cpu() / s_out) - torch.round(ref2 / s_out)).abs()
+        same = (dcode < 0.5).float().mean().item()
+        print(f"{name}: precise mode: output codes identical {100 * same:.3f}% max |dcode| {dcode.max().item():.2f}")
+        # (a single ADC code of the upper DAC slice still flips where the fp32 partial sum sits within summation-order
+        # noise of a rounding boundary; it carries weight 16, hence up to 3 output steps on those few elements)
+        assert dcode.max().item() <= 3 and same > 0.999
 
 
 # --------------------------------------------------------------------------------------------------- inside the DiT
