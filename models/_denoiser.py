@@ -83,7 +83,7 @@ class Denoiser(nn.Module):
         x = x.float().contiguous()
         tg = self.__dict__.get("_train_graph")
         ov = self.__dict__.get("_grad_overlap")   # (process group, bucket elements): set by sdb200.parallel.DataParallel
-        if tg is None or tg.key != G.TrainGraph.make_key(self, x, tt, cond_t, ov):
+        if tg is None or not tg.still_valid(self, x, tt, cond_t, ov):
             tg = G.TrainGraph(self, x, tt, cond_t, self.text_cond, self.image_cond, overlap=ov)
             self.__dict__["_train_graph"] = tg
         tg.grad_sync = self.__dict__.get("_grad_sync")   # set by sdb200.parallel.DataParallel

@@ -381,6 +381,21 @@ class _BucketReducer:
         torch.cuda.current_stream().wait_stream(self.side)   # join
 
 
+# Version of "the module trees of this process": bumped whenever ANY module registers a sub-module, a parameter or a
+# buffer (module surgery of cim_qn_train/progressive_qn_train.py:576-651, `layer.weight = nn.Parameter(...)`, ...). A
+# captured step re-walks its model's tree only when this moved since it last looked.
+STRUCTURE = [0]
+
+
+def _bump_structure(*_a, **_k):
+    STRUCTURE[0] += 1
+
+
+torch.nn.modules.module.register_module_module_registration_hook(_bump_structure)
+torch.nn.modules.module.register_module_parameter_registration_hook(_bump_structure)
+torch.nn.modules.module.register_module_buffer_registration_hook(_bump_structure)
+
+
 class TrainGraph:
     """One training step's forward and backward as two CUDA graphs: ~1200 kernel launches + ~1000 small torch ops per
     step cost ~55 ms of host time when issued one by one, several times the device time at the reference's per-GPU
@@ -400,6 +415,7 @@ class TrainGraph:
         gradient of a bucket has been produced (the reference's DDP reducer does the same from autograd hooks,
         train_ddpm_cond_celebhq_multi_gpu.py:257-263,362) — in place on slices of the flat buffer, no bucket copies."""
         self.params = list(core.parameters())
+        self.structure = STRUCTURE[0]
         self.key = self.make_key(core, x, tt, cond_tensors, overlap)
         self.grad_sync = None
         self.overlap = overlap
@@ -524,14 +540,43 @@ class TrainGraph:
         flat = self.flat.clone()
         if self.grad_sync is not None:
             self.grad_sync(flat, reduced=self.reduced_in_graph)
-        return tuple(None if sl is None or i in self.unused else flat[sl[0]:sl[0] + sl[1]].view(sl[2])
-                     for i, sl in enumerate(self.slots))
+        # one split over the slots in buffer order (one C++ call) instead of a slice + view per parameter: this runs
+        # on the host once per step, between the loss read-back and the next replay (tools/host_profile_train.py)
+        plan = self.__dict__.get("_grad_plan")
+        if plan is None:
+            live = sorted((sl[0], i) for i, sl in enumerate(self.slots) if sl is not None and i not in self.unused)
+            sizes, owner, pos = [], [], 0
+            for off, i in live:
+                if off > pos:
+                    sizes.append(off - pos), owner.append(None)      # alignment gap / unused slot
+                sizes.append(self.slots[i][1]), owner.append(i)
+                pos = off + self.slots[i][1]
+            if pos < self.flat.numel():
+                sizes.append(self.flat.numel() - pos), owner.append(None)
+            plan = self.__dict__["_grad_plan"] = (sizes, owner)
+        out = [None] * len(self.slots)
+        for piece, i in zip(flat.split_with_sizes(plan[0]), plan[1]):
+            if i is not None:
+                out[i] = piece.view(self.slots[i][2])
+        return tuple(out)
 
     @staticmethod
-    def make_key(core, x, tt, cond_tensors, overlap=None):
+    def make_key(core, x, tt, cond_tensors, overlap=None, params=None):
+        """Everything a captured step depends on. `params`: the parameter list of an existing graph — used while the
+        module tree is known to be unchanged (STRUCTURE version, bumped by torch's global module / parameter
+        registration hooks), which saves walking the tree (1.8 ms of host time per step for the 400-parameter UNet)."""
+        ps = core.parameters() if params is None else params
         return (tuple(x.shape), x.requires_grad, tuple(tt.shape), None if overlap is None else (id(overlap[0]), overlap[1])) \
             + tuple((tuple(c.shape), c.dtype) for c in cond_tensors) \
-            + tuple((p.data_ptr(), p.requires_grad) for p in core.parameters())
+            + tuple((p.data_ptr(), p.requires_grad) for p in ps)
+
+    def still_valid(self, core, x, tt, cond_tensors, overlap=None):
+        if self.structure != STRUCTURE[0]:
+            if self.key != self.make_key(core, x, tt, cond_tensors, overlap):     # full walk: the tree may have changed
+                return False
+            self.structure = STRUCTURE[0]
+            return True
+        return self.key == self.make_key(core, x, tt, cond_tensors, overlap, params=self.params)
 
     def __call__(self, x, tt, cond_tensors):
         self.tt.copy_(tt)

@@ -124,6 +124,16 @@ class FusedAdam(torch.optim.Optimizer):
         gradients' own storage when they are views of ONE buffer (graphs.TrainGraph hands them out that way, in its own
         slot order — gradient-arrival order when the data-parallel exchange overlaps the backward pass), otherwise a
         private buffer in this optimizer's slot order filled by one multi-tensor copy."""
+        # fast path: the same layout as last step (a captured training step hands out views of a fresh clone of its
+        # flat buffer every time: new base address, same offsets) — one data_ptr() per parameter instead of storage /
+        # dtype / contiguity queries (0.6 ms of host time per step for 400 parameters, tools/host_profile_train.py)
+        last = self.__dict__.get("_last_layout")
+        if last is not None and last[0] == present:
+            goffs, first = last[1], last[2]
+            base = self._all[first].grad.data_ptr() - 4 * goffs[first]
+            if base % 16 == 0 and all(p.grad.data_ptr() == base + 4 * go
+                                      for p, go in zip(self._all, goffs) if go is not None):
+                return base, goffs
         store, ok = None, True
         goffs = [None] * len(self._all)
         for i, (p, has) in enumerate(zip(self._all, present)):
@@ -142,7 +152,10 @@ class FusedAdam(torch.optim.Optimizer):
                 break
             goffs[i] = d // 4
         if ok and store is not None:
-            return store, tuple(goffs)
+            goffs = tuple(goffs)
+            self.__dict__["_last_layout"] = (present, goffs, next(i for i, go in enumerate(goffs) if go is not None))
+            return store, goffs
+        self.__dict__.pop("_last_layout", None)
         if self._g is None:
             self._g = torch.zeros(self._total, device=self._dev)
         dst, src = [], []
