@@ -50,6 +50,9 @@ def gen_weight_split_dict(module, weight_block_size):
     return info
 
 
+FUSED_SINGLE_BLOCK = True     # single-block layers through AddaLayerFn (tests flip it to compare with the block loop)
+
+
 class _Im2colFn(torch.autograd.Function):
     """NHWC bf16 rows -> nn.Unfold rows ((c, ky, kx) order), backward = nn.Fold (b200sd_col2im)."""
 
@@ -187,13 +190,19 @@ class _AddaMixin(_LsqMixin):
                 self._maybe_init_gain(first)
             self.__dict__["_gain_init_pending"] = False
         alpha = self._adc_scale()
+        step_w = self.step_size_weight if self.weight_quant else None
+        step_out = self.step_size_output if self.output_quant else None
+        single = len(blocks) == 1 and blocks[0] == (0, Kp, 0, Np) and Np % 8 == 0 and Kp == K and Np == N
+        if single and FUSED_SINGLE_BLOCK and not (step_out is not None and self._needs_lazy_init("output")):
+            # the whole weight is one mapped block: digits -> GEMM -> one pass (csrc/adda_out.cu: b200sd_adda_tail)
+            if bias is not None and bias.dtype != torch.float32:
+                bias = bias.float()
+            return Q.adda_layer(self, x, self.step_size_input, w, alpha, bias, step_out, step_w, cfg, self.output_bit, M * N)
         if torch.is_grad_enabled() and any(t.requires_grad for t in (x, w, alpha, self.step_size_input)):
             acc = Q.AddaFn.apply(x, self.step_size_input, w, alpha, cfg)
         else:
             acc = Q.AddaFn._run(x, self.step_size_input.detach(), w.detach(), alpha.detach(), cfg)
         # / w_scale / in_scale / adc_scale + bias and the output quantiser: one launch (csrc/adda_out.cu)
-        step_w = self.step_size_weight if self.weight_quant else None
-        step_out = self.step_size_output if self.output_quant else None
         if bias is not None and bias.dtype != torch.float32:
             bias = bias.float()
         if step_out is not None and self._needs_lazy_init("output"):

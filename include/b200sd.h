@@ -462,6 +462,22 @@ int b200sd_adda_out_bwd(const void* gout, int64_t ld_g, const float* acc, int64_
                         float* res, void* stream);
 int b200sd_adda_out_scratch_floats(void);
 
+/* Single-block layers: b200sd_adc_combine + b200sd_adda_out in one pass over the fp32 block product partial
+ * [slices * rows, ld_p] (the integer accumulation is never written out); out bf16 [rows, c], c % 4 == 0. step_out NULL:
+ * no output quantiser. Same arithmetic in the same order as the two calls it replaces. */
+int b200sd_adda_tail(const float* partial, int64_t ld_p, const float* bias, const float* step_w, const float* step_in,
+                     const float* adc_scale, const float* step_out, float qp, float grad_scale, float adc_range,
+                     int32_t slices, int32_t slice_bit, const float* gain_noise, const float* offset_noise, void* out,
+                     int64_t rows, int32_t c, void* stream);
+/* Its backward = b200sd_adda_out_bwd + b200sd_adc_bwd: dpartial bf16 [slices * rows, ld_d] (operand of the dgrad / wgrad
+ * GEMMs), dy bf16 [rows, c] or NULL (column sums = d bias), res[0] = d(step_out) * grad_scale, res[1] = d(adc_scale)
+ * through both the division and the ADC input; scratch as for b200sd_adda_out_bwd. */
+int b200sd_adda_tail_bwd(const void* gout, int64_t ld_g, const float* partial, int64_t ld_p, const float* bias,
+                         const float* step_w, const float* step_in, const float* adc_scale, const float* step_out,
+                         float qp, float grad_scale, float adc_range, int32_t slices, int32_t slice_bit,
+                         const float* gain_noise, const float* offset_noise, void* dpartial, int64_t ld_d, void* dy,
+                         int64_t rows, int32_t c, float* scratch, float* res, void* stream);
+
 /* get_adc_scale (cim_layers/layers_utils_adda.py:40-49) on the device: out[0] = adc_scale of *gain (clamped to
  * [gain_min, gain_max] straight-through; gain_mode != 0 rounds the gain, 0 rounds the range 1 / gain) * scale1,
  * out[1] = d adc_scale / d gain. */

@@ -262,3 +262,196 @@ extern "C" int b200sd_adc_scale(const float* gain, float gain_min, float gain_ma
     B200_CHECK_LAUNCH("adc_scale");
     return B200SD_OK;
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// Single-block layers (the whole weight fits one array: every Linear of the DiT-9L except the MLP's second): ADC of the
+// slices, their recombination, the division chain, the bias and the output quantiser in ONE pass over the fp32 block
+// product — the integer accumulation `acc` and its gradient are never written to memory. Same arithmetic, in the same
+// order, as adc_combine_kernel followed by adda_out_kernel (csrc/quant.cu, above); the backward is adda_out_bwd_kernel
+// followed by adc_bwd_kernel.
+namespace b200 {
+
+__device__ __forceinline__ float at_adc(float p, float alpha, float R, bool noisy, float gn, float on) {
+    float v = __fmul_rn(alpha, p);
+    if (noisy) {
+        v = __fmul_rn(v, __fadd_rn(1.0f, gn));
+        v = __fadd_rn(v, __fmul_rn(R, on));
+    }
+    return v;
+}
+
+// part fp32 [slices * rows, ld_p]; out bf16 [rows, c]; one thread = 4 consecutive columns of one row
+__global__ void __launch_bounds__(AO_THREADS)
+    adda_tail_kernel(const float* __restrict__ part, long long ld_p, const float* __restrict__ bias,
+                     const float* __restrict__ step_w, const float* __restrict__ step_in, const float* __restrict__ alpha_p,
+                     const float* __restrict__ step_out, float qp, float g, float R, int slices, int slice_bit,
+                     const float* __restrict__ gain_noise, const float* __restrict__ offset_noise,
+                     __nv_bfloat16* __restrict__ out, long long rows, int c) {
+    pdl_enter();
+    const AoScales k = ao_scales(step_w, step_in, alpha_p);
+    const float s = step_out ? ao_effective_step(*step_out, g) : 1.f;
+    const bool noisy = gain_noise != nullptr;
+    const int nq = c >> 2;
+    const long long total = rows * nq;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const long long r = i / nq;
+        const int col = static_cast<int>(i - r * nq) * 4;
+        float sum[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int sl = 0; sl < slices; ++sl) {
+            const float4 p = *reinterpret_cast<const float4*>(part + (static_cast<long long>(sl) * rows + r) * ld_p + col);
+            const float pv[4] = {p.x, p.y, p.z, p.w};
+            const float wgt = static_cast<float>(1 << (sl * slice_bit));
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float v = at_adc(pv[j], k.alpha, R, noisy, noisy ? gain_noise[col + j] : 0.f,
+                                       noisy ? offset_noise[col + j] : 0.f);
+                sum[j] += rintf(fminf(fmaxf(v, -R - 1.0f), R)) * wgt;   // integers: exact in fp32
+            }
+        }
+        __nv_bfloat162 o[2];
+        float y[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float v = ao_rescale(sum[j], k);
+            if (bias) v = __fadd_rn(v, bias[col + j]);
+            if (step_out) v = __fmul_rn(rintf(fminf(fmaxf(__fdiv_rn(v, s), -qp), qp)), s);
+            y[j] = v;
+        }
+        o[0] = __floats2bfloat162_rn(y[0], y[1]), o[1] = __floats2bfloat162_rn(y[2], y[3]);
+        *reinterpret_cast<uint2*>(out + r * static_cast<long long>(c) + col) = *reinterpret_cast<const uint2*>(o);
+    }
+}
+
+// res[0] = d(step_out) * g, res[1] = d(adc_scale) (through the division AND through the ADC's scaled input)
+__global__ void __launch_bounds__(AO_THREADS)
+    adda_tail_bwd_kernel(const __nv_bfloat16* __restrict__ gout, long long ld_g, const float* __restrict__ part,
+                         long long ld_p, const float* __restrict__ bias, const float* __restrict__ step_w,
+                         const float* __restrict__ step_in, const float* __restrict__ alpha_p,
+                         const float* __restrict__ step_out, float qp, float g, float R, int slices, int slice_bit,
+                         const float* __restrict__ gain_noise, const float* __restrict__ offset_noise,
+                         __nv_bfloat16* __restrict__ dp, long long ld_d, __nv_bfloat16* __restrict__ dy, long long rows,
+                         int c, AoScratch* __restrict__ sc, float* __restrict__ res) {
+    pdl_enter();
+    __shared__ float red[AO_THREADS / 32];
+    const AoScales k = ao_scales(step_w, step_in, alpha_p);
+    const float s = step_out ? ao_effective_step(*step_out, g) : 1.f;
+    const float inv_alpha = 1.f / k.alpha, inv_all = 1.f / (k.alpha * k.is * k.ws);
+    const bool noisy = gain_noise != nullptr;
+    const int nq = c >> 2;
+    const long long total = rows * nq;
+    float a_s = 0.f, a_al = 0.f;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const long long r = i / nq;
+        const int col = static_cast<int>(i - r * nq) * 4;
+        // (the slices are walked twice — the second read of the 16 bytes hits L1 — rather than kept in per-thread arrays
+        // indexed by a run-time slice count, which would live in local memory)
+        float sum[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int sl = 0; sl < slices; ++sl) {
+            const float4 p = *reinterpret_cast<const float4*>(part + (static_cast<long long>(sl) * rows + r) * ld_p + col);
+            const float pv[4] = {p.x, p.y, p.z, p.w};
+            const float wgt = static_cast<float>(1 << (sl * slice_bit));
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float v = at_adc(pv[j], k.alpha, R, noisy, noisy ? gain_noise[col + j] : 0.f,
+                                       noisy ? offset_noise[col + j] : 0.f);
+                sum[j] += rintf(fminf(fmaxf(v, -R - 1.0f), R)) * wgt;
+            }
+        }
+        const uint2 gu = *reinterpret_cast<const uint2*>(gout + r * ld_g + col);
+        const __nv_bfloat162* gh = reinterpret_cast<const __nv_bfloat162*>(&gu);
+        const float2 g01 = __bfloat1622float2(gh[0]), g23 = __bfloat1622float2(gh[1]);
+        float gg[4] = {g01.x, g01.y, g23.x, g23.y};
+        float dacc[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float y2 = ao_rescale(sum[j], k);
+            if (step_out) {
+                const float y = bias ? __fadd_rn(y2, bias[col + j]) : y2;
+                const float u = __fdiv_rn(y, s);
+                const bool in = (u >= -qp) && (u <= qp);
+                const float q = rintf(fminf(fmaxf(u, -qp), qp));
+                a_s += gg[j] * (q - (in ? u : 0.f));
+                gg[j] = in ? gg[j] : 0.f;
+            }
+            a_al -= gg[j] * (y2 * inv_alpha);
+            dacc[j] = gg[j] * inv_all;
+        }
+        if (dy) {
+            __nv_bfloat162 o[2] = {__floats2bfloat162_rn(gg[0], gg[1]), __floats2bfloat162_rn(gg[2], gg[3])};
+            *reinterpret_cast<uint2*>(dy + r * static_cast<long long>(c) + col) = *reinterpret_cast<const uint2*>(o);
+        }
+        for (int sl = 0; sl < slices; ++sl) {
+            const float4 p = *reinterpret_cast<const float4*>(part + (static_cast<long long>(sl) * rows + r) * ld_p + col);
+            const float pv[4] = {p.x, p.y, p.z, p.w};
+            const float wgt = static_cast<float>(1 << (sl * slice_bit));
+            float d[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float v = at_adc(pv[j], k.alpha, R, noisy, noisy ? gain_noise[col + j] : 0.f,
+                                       noisy ? offset_noise[col + j] : 0.f);
+                const bool in = (v >= -R - 1.0f) && (v <= R);
+                const float gk = in ? dacc[j] * wgt : 0.f;
+                a_al += gk * pv[j];
+                d[j] = k.alpha * gk;
+            }
+            __nv_bfloat162 o[2] = {__floats2bfloat162_rn(d[0], d[1]), __floats2bfloat162_rn(d[2], d[3])};
+            *reinterpret_cast<uint2*>(dp + (static_cast<long long>(sl) * rows + r) * ld_d + col) = *reinterpret_cast<const uint2*>(o);
+        }
+    }
+    a_s = ao_block_sum(a_s, red);
+    a_al = ao_block_sum(a_al, red);
+    if (threadIdx.x == 0) sc->part[2 * blockIdx.x] = a_s, sc->part[2 * blockIdx.x + 1] = a_al;
+    if (ao_last_cta(&sc->arrive, gridDim.x)) {
+        float v0 = 0.f, v1 = 0.f;
+        for (unsigned int t = threadIdx.x; t < gridDim.x; t += AO_THREADS)
+            v0 += __ldcg(sc->part + 2 * t), v1 += __ldcg(sc->part + 2 * t + 1);
+        v0 = ao_block_sum(v0, red);
+        v1 = ao_block_sum(v1, red);
+        if (threadIdx.x == 0) res[0] = v0 * g, res[1] = v1;
+    }
+}
+
+}  // namespace b200
+
+extern "C" int b200sd_adda_tail(const float* part, int64_t ld_p, const float* bias, const float* step_w,
+                                const float* step_in, const float* adc_scale, const float* step_out, float qp,
+                                float grad_scale, float adc_range, int32_t slices, int32_t slice_bit,
+                                const float* gain_noise, const float* offset_noise, void* out, int64_t rows, int32_t c,
+                                void* stream) {
+    B200_REQUIRE(part && step_in && adc_scale && out && rows >= 0 && slices >= 1 && slices <= 8 && slice_bit >= 1,
+                 "adda_tail: bad arguments");
+    B200_REQUIRE(!step_out || qp >= 1.f, "adda_tail: bad quantiser range");
+    B200_REQUIRE((gain_noise == nullptr) == (offset_noise == nullptr), "adda_tail: gain and offset noise come together");
+    B200_REQUIRE(slices * slice_bit <= 24, "adda_tail: digit weights beyond 2^24 are not exact in fp32");
+    B200_REQUIRE(c > 0 && c % 4 == 0 && ld_p % 4 == 0 && ld_p >= c && (reinterpret_cast<uintptr_t>(part) & 15) == 0,
+                 "adda_tail: columns / pitch must be multiples of 4 (16-byte loads)");
+    if (rows == 0) return B200SD_OK;
+    launch_k(adda_tail_kernel, ao_grid(rows * (c / 4)), AO_THREADS, 0, as_stream(stream), part, ld_p, bias, step_w, step_in,
+             adc_scale, step_out, qp, grad_scale, adc_range, slices, slice_bit, gain_noise, offset_noise,
+             static_cast<__nv_bfloat16*>(out), rows, c);
+    B200_CHECK_LAUNCH("adda_tail");
+    return B200SD_OK;
+}
+
+extern "C" int b200sd_adda_tail_bwd(const void* gout, int64_t ld_g, const float* part, int64_t ld_p, const float* bias,
+                                    const float* step_w, const float* step_in, const float* adc_scale,
+                                    const float* step_out, float qp, float grad_scale, float adc_range, int32_t slices,
+                                    int32_t slice_bit, const float* gain_noise, const float* offset_noise,
+                                    void* dpartial, int64_t ld_d, void* dy, int64_t rows, int32_t c, float* scratch,
+                                    float* res, void* stream) {
+    B200_REQUIRE(gout && part && step_in && adc_scale && dpartial && scratch && res && rows > 0 && slices >= 1 &&
+                     slices <= 8 && slice_bit >= 1, "adda_tail_bwd: bad arguments");
+    B200_REQUIRE(!step_out || qp >= 1.f, "adda_tail_bwd: bad quantiser range");
+    B200_REQUIRE((gain_noise == nullptr) == (offset_noise == nullptr), "adda_tail_bwd: gain and offset noise come together");
+    B200_REQUIRE(c > 0 && c % 4 == 0 && ld_p % 4 == 0 && ld_p >= c && ld_g % 4 == 0 && ld_g >= c && ld_d % 4 == 0 &&
+                     ld_d >= c && (reinterpret_cast<uintptr_t>(part) & 15) == 0,
+                 "adda_tail_bwd: columns / pitches must be multiples of 4");
+    launch_k(adda_tail_bwd_kernel, ao_grid(rows * (c / 4)), AO_THREADS, 0, as_stream(stream),
+             static_cast<const __nv_bfloat16*>(gout), ld_g, part, ld_p, bias, step_w, step_in, adc_scale, step_out, qp,
+             grad_scale, adc_range, slices, slice_bit, gain_noise, offset_noise, static_cast<__nv_bfloat16*>(dpartial),
+             ld_d, static_cast<__nv_bfloat16*>(dy), rows, c, reinterpret_cast<AoScratch*>(scratch), res);
+    B200_CHECK_LAUNCH("adda_tail_bwd");
+    return B200SD_OK;
+}

@@ -277,6 +277,68 @@ class AddaOutFn(Function):
         return dacc, res[1].reshape(alpha.shape).to(alpha.dtype), dbias, dstep, None, None, None, None, None
 
 
+class AddaLayerFn(Function):
+    """A compute-in-memory layer whose whole weight is ONE mapped block (every Linear of the DiT-9L but the MLP's
+    second), end to end: DAC digits -> block product (tcgen05 GEMM, fp32) -> ADC + recombination + division chain + bias +
+    output quantiser in one pass (b200sd_adda_tail). The integer accumulation and its gradient never reach memory, and
+    the fp32 block product is KEPT for the backward pass instead of being recomputed (one GEMM less per layer; 8 bytes
+    per output element and DAC slice held between forward and backward). Same arithmetic as AddaFn + AddaOutFn."""
+
+    @staticmethod
+    def forward(ctx, x, step_in, w, alpha, bias, step_out, step_w, cfg, qp_out, numel_out, scratch):
+        M, N = x.shape[0], w.shape[0]
+        xs, ws = x.detach(), w.detach()
+        digits = AddaFn._digits(xs, step_in.detach(), cfg)
+        wp = ops.pack_linear_weight(ws)
+        part = rt.linear(digits, wp, out_dtype=torch.float32)
+        if cfg.get("split_w"):
+            rt.linear(digits, ops.pack_linear_weight(ws - wp[:, :ws.shape[1]].float()), out=part, residual=part)
+        out = rt.adda_tail(part, M, N, bias, step_w, step_in, alpha.detach().reshape(1).float(), step_out, qp_out, numel_out,
+                           cfg["R"], cfg["slices"], cfg["slice_bit"], cfg["gain_noise"], cfg["offset_noise"])
+        ctx.save_for_backward(x, step_in, w, alpha, bias, step_out, step_w, digits, part)
+        ctx.cfg = (cfg, qp_out, numel_out, scratch)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        x, step_in, w, alpha, bias, step_out, step_w, digits, part = ctx.saved_tensors
+        cfg, qp_out, numel_out, scratch = ctx.cfg
+        M, K = x.shape
+        N = w.shape[0]
+        S, sb = cfg["slices"], cfg["slice_bit"]
+        if g.dtype != torch.bfloat16 or g.stride(1) != 1 or g.stride(0) % 8:
+            g = g.to(torch.bfloat16).contiguous()
+        want_b = bias is not None and ctx.needs_input_grad[4]
+        dp, dy, res = rt.adda_tail_bwd(g, part, M, N, bias, step_w, step_in, alpha.detach().reshape(1).float(), step_out,
+                                       qp_out, numel_out, cfg["R"], S, sb, scratch, want_b, cfg["gain_noise"],
+                                       cfg["offset_noise"])
+        wd = w.detach()
+        ddigits = torch.empty(S * M, K, device=x.device, dtype=torch.bfloat16)
+        rt.linear(dp, ops.pack_linear_weight(wd.t()), out=ddigits)
+        kp = (K + 63) // 64 * 64
+        dwp = rt.wgrad([rt.make_src(digits, 1, 1, S * M, K, ld=K)], [(0, 0, 0, 0, kp // 64)],
+                       rt.make_src(dp, 1, 1, S * M, N, ld=dp.stride(0)), N, 1, 1, S * M)
+        dxq = rt.bit_split_bwd(ddigits, M, K, S, sb)
+        dx, ds = rt.lsq_quant_bwd(dxq, x, step_in.detach(), cfg["qp_in"], codes=True, numel=cfg["numel_in"])
+        dbias = rt.colsum(dy, 1, M, N).to(bias.dtype) if want_b else None
+        dstep_out = res[0].reshape(step_out.shape).to(step_out.dtype) if step_out is not None else None
+        return (dx if ctx.needs_input_grad[0] else None), ds.reshape(step_in.shape), dwp[:, :K], \
+            res[1].reshape(alpha.shape).to(alpha.dtype), dbias, dstep_out, None, None, None, None, None
+
+
+def adda_layer(owner, x, step_in, w, alpha, bias, step_out, step_w, cfg, bits_out, numel_out):
+    """Single-block compute-in-memory layer on bf16 rows [M, K] -> bf16 rows [M, N] (see AddaLayerFn)."""
+    qp = qp_of(bits_out) if step_out is not None else 0.0
+    scratch = owner.__dict__.get("_ao_scratch")
+    if scratch is None or scratch.device != x.device:
+        scratch = owner.__dict__["_ao_scratch"] = rt.adda_out_scratch(x.device)
+    if bias is not None and bias.dtype != torch.float32:
+        bias = bias.float()
+    if torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in (x, step_in, w, alpha, bias, step_out)):
+        return AddaLayerFn.apply(x, step_in, w, alpha, bias, step_out, step_w, cfg, qp, numel_out, scratch)
+    return AddaLayerFn.forward(_NoCtx(), x, step_in, w, alpha, bias, step_out, step_w, cfg, qp, numel_out, scratch)
+
+
 def adda_out(owner, acc, alpha, bias, step_out, step_w, step_in, bits, numel):
     """Output side of a compute-in-memory leaf `owner`: bf16 rows [M, Np]."""
     qp = qp_of(bits) if step_out is not None else 0.0

@@ -25,6 +25,7 @@ EXPORTS = [
     "b200sd_wq_scratch_floats", "b200sd_weight_qn", "b200sd_weight_qn_bwd", "b200sd_weight_qn_multi", "b200sd_lsq_init_step", "b200sd_lsq_quant", "b200sd_lsq_quant_bwd", "b200sd_lsq_quant_bwd_blocks", "b200sd_bit_split",
     "b200sd_adc_combine", "b200sd_adc_bwd", "b200sd_adc_bwd_blocks", "b200sd_bit_split_bwd",
     "b200sd_adda_out", "b200sd_adda_out_bwd", "b200sd_adda_out_scratch_floats", "b200sd_adc_scale",
+    "b200sd_adda_tail", "b200sd_adda_tail_bwd",
     "b200sd_blockdiag_pack", "b200sd_blockdiag_gather", "b200sd_blend", "b200sd_blend_bwd", "b200sd_blend_part_floats",
     "b200sd_pack_weights", "b200sd_pack_job_size", "b200sd_wgrad_scatter",
 ]
@@ -151,6 +152,9 @@ def lib():
         L.b200sd_adda_out.argtypes = [vp, i64, vp, vp, vp, vp, vp, f32, f32, vp, i64, i64, i32, i32, vp]
         L.b200sd_adda_out_bwd.argtypes = [vp, i64, vp, i64, vp, vp, vp, vp, vp, f32, f32, vp, vp, i64, i32, vp, vp, vp]
         L.b200sd_adc_scale.argtypes = [vp, f32, f32, i32, f32, vp, vp]
+        L.b200sd_adda_tail.argtypes = [vp, i64, vp, vp, vp, vp, vp, f32, f32, f32, i32, i32, vp, vp, vp, i64, i32, vp]
+        L.b200sd_adda_tail_bwd.argtypes = [vp, i64, vp, i64, vp, vp, vp, vp, vp, f32, f32, f32, i32, i32, vp, vp, vp, i64,
+                                           vp, i64, i32, vp, vp, vp]
         L.b200sd_blockdiag_pack.argtypes = [vp, i32, i32, i32, vp, i64, vp, i64, vp]
         L.b200sd_blockdiag_gather.argtypes = [vp, i64, i32, i32, i32, vp, vp]
         L.b200sd_blend.argtypes = [vp, i64, vp, i64, vp, i32, i32, vp, i64, i64, i32, vp, vp, vp, vp]
@@ -978,6 +982,36 @@ def adda_out_bwd(gout, acc, bias, step_w, step_in, adc_scale, step_out, qp, nume
                                     adc_scale.data_ptr(), None if step_out is None else step_out.data_ptr(), float(qp), g,
                                     _p(dacc), _p(dy), rows, c, _p(scratch), _p(res), stream_ptr()), "adda_out_bwd")
     return dacc, dy, res
+
+
+def adda_tail(part, rows, c, bias, step_w, step_in, adc_scale, step_out, qp, numel, adc_range, slices, slice_bit,
+              gain_noise=None, offset_noise=None):
+    """Single-block compute-in-memory layer: ADC + slice recombination + division chain + bias + output quantiser over
+    the fp32 block product part [slices * rows, ld] -> bf16 [rows, c]."""
+    _cuda(part, torch.float32, "block product")
+    out = torch.empty(rows, c, device=part.device, dtype=torch.bfloat16)
+    g = lsq_grad_scale(qp, numel) if step_out is not None else 0.0
+    check(lib().b200sd_adda_tail(_p(part), part.stride(0), _p(bias), None if step_w is None else step_w.data_ptr(),
+                                 step_in.data_ptr(), adc_scale.data_ptr(), None if step_out is None else step_out.data_ptr(),
+                                 float(qp), g, float(adc_range), slices, slice_bit, _p(gain_noise), _p(offset_noise),
+                                 _p(out), rows, c, stream_ptr()), "adda_tail")
+    return out
+
+
+def adda_tail_bwd(gout, part, rows, c, bias, step_w, step_in, adc_scale, step_out, qp, numel, adc_range, slices,
+                  slice_bit, scratch, want_dy, gain_noise=None, offset_noise=None):
+    """-> (d partial bf16 [slices * rows, c], d y bf16 [rows, c] or None, res fp32 [2] = (d step_out incl. the LSQ
+    gradient scale, d adc_scale))."""
+    dp = torch.empty(slices * rows, c, device=part.device, dtype=torch.bfloat16)
+    dy = torch.empty(rows, c, device=part.device, dtype=torch.bfloat16) if want_dy else None
+    res = torch.empty(2, device=part.device, dtype=torch.float32)
+    g = lsq_grad_scale(qp, numel) if step_out is not None else 0.0
+    check(lib().b200sd_adda_tail_bwd(_p(gout), gout.stride(0), _p(part), part.stride(0), _p(bias),
+                                     None if step_w is None else step_w.data_ptr(), step_in.data_ptr(),
+                                     adc_scale.data_ptr(), None if step_out is None else step_out.data_ptr(), float(qp), g,
+                                     float(adc_range), slices, slice_bit, _p(gain_noise), _p(offset_noise), _p(dp), c,
+                                     _p(dy), rows, c, _p(scratch), _p(res), stream_ptr()), "adda_tail_bwd")
+    return dp, dy, res
 
 
 def adc_scale(gain, gain_min, gain_max, gain_mode, scale1):

@@ -850,3 +850,47 @@ def test_model_wide_weight_side_equals_the_per_layer_launches():
     finally:
         Q.FUSED_WEIGHT_BANK = True
     assert torch.equal(w_ng, w_pl)
+
+
+@pytest.mark.parametrize("noise,gain_noise", [(0.0, 0.0), (0.08, 0.0), (0.08, 0.02)])
+def test_single_block_adda_layer_equals_the_block_loop(noise, gain_noise):
+    """A compute-in-memory Linear whose weight is one mapped block runs digits -> GEMM -> ONE pass (b200sd_adda_tail: ADC,
+    recombination, division chain, bias, output quantiser; the fp32 block product kept for the backward pass) instead of
+    the block loop's adc_combine + adda_out (and adda_out_bwd + adc_bwd with a recomputed product): outputs bit-identical,
+    every gradient equal to fp32 rounding."""
+    dev = _dev()
+    import copy
+    import cim_layers.layers_qn_lsq_adda_cim as A
+    torch.manual_seed(21)
+    base = A.Linear_lsq_adda_cim(288, 320, weight_bit=4, input_bit=8, output_bit=8, noise_scale=noise, dac_bit=5, adc_bit=8,
+                                 adc_gain_1_scale=9.071428571, adc_gain_range=[1 / 64, 1 / 64], adc_adjust_mode="current",
+                                 gain_noise_scale=gain_noise, offset_noise_scale=gain_noise, bias=True).to(dev)
+    base.weight_noise_unit = torch.randn(base.weight.shape, generator=torch.Generator().manual_seed(4)).to(dev)
+    g = torch.Generator().manual_seed(8)
+    x = (torch.randn(512, 288, generator=g) * 1.5).to(dev)
+    gout = torch.randn(512, 320, generator=g).to(dev)
+    with torch.no_grad():
+        base(x)                                        # lazy step sizes and the ADC gain settle on the block-loop path
+    runs = {}
+    for fused in (False, True):
+        A.FUSED_SINGLE_BLOCK = fused
+        try:
+            layer = copy.deepcopy(base)
+            layer.weight_noise_unit = base.weight_noise_unit
+            xi = x.clone().requires_grad_(True)
+            out = layer(xi)
+            (out * gout).sum().backward()
+            with torch.no_grad():
+                out_ng = layer(x)
+            runs[fused] = (out.detach(), out_ng, xi.grad, {k: v.grad for k, v in layer.named_parameters()})
+        finally:
+            A.FUSED_SINGLE_BLOCK = True
+    torch.cuda.synchronize()
+    o0, n0, dx0, g0 = runs[False]
+    o1, n1, dx1, g1 = runs[True]
+    assert torch.equal(o0, o1) and torch.equal(n0, n1) and torch.equal(o1, n1)
+    assert relerr(dx1, dx0) < 1e-5
+    for k in g0:
+        assert (g0[k] is None) == (g1[k] is None), k
+        if g0[k] is not None:
+            assert relerr(g1[k], g0[k]) < 2e-4, (k, relerr(g1[k], g0[k]))
