@@ -10,9 +10,12 @@ It also hands the backward a parameter-layout fp32 view into the step's flat gra
 GEMM's split-K reduction (b200sd_wgrad_scatter) writes the gradient where the optimizer / all-reduce will read it —
 no packed intermediate, no permute copy, no gather into the flat buffer.
 
-Only tensors that ARE parameter storage (matched by address) go through the bank; derived weights (concatenated
-time-embedding projections, quantised weights, slices) keep the per-use torch path, because their producers run inside
-the step.
+Tensors that ARE parameter storage (matched by address) go through the bank, and so do the quantised (+ noisy) weights
+of the cim_layers leaves: their producer (sdb200.quant.prepare_weight_side, one launch per phase for the whole model)
+writes them into a buffer the bank owns (`derived_buffer`), and a SECOND job table, refreshed right after that
+producer (`refresh_derived`), re-derives their packed forms — one launch instead of one or two per leaf and direction.
+Other derived weights (concatenated time-embedding projections, slices) keep the per-use torch path, because their
+producers run at arbitrary points inside the step.
 """
 import torch
 
@@ -37,15 +40,44 @@ class WeightBank:
         self.n_tiles = 0
         self.uses = {}          # parameter index -> gradient views handed out in the current pass
         self.shared = set()     # parameters used by more than one leaf: their gradients are summed by autograd instead
+        self.dbuf = None        # fp32 buffer of the derived (quantised) weights, written inside the step
+        self.derived = {}       # address -> numel of the derived weights living in dbuf
+        self.djobs, self.dtable, self.dn_tiles = [], None, 0
 
     # ------------------------------------------------------------------------------------------ bookkeeping
     def knows(self, w):
-        return w is not None and w.dtype == torch.float32 and w.is_contiguous() and \
-            self.index.get(w.data_ptr(), -1) >= 0 and self.numel[self.index[w.data_ptr()]] == w.numel()
+        if w is None or w.dtype != torch.float32 or not w.is_contiguous():
+            return False
+        ptr = w.data_ptr()
+        if self.derived.get(ptr) == w.numel():
+            return True
+        return self.index.get(ptr, -1) >= 0 and self.numel[self.index[ptr]] == w.numel()
+
+    def derived_buffer(self, sizes):
+        """Persistent fp32 storage for the derived weights of one pass (numel per weight, in order); the views of it
+        become tensors the bank knows. One buffer per bank: a pass with a different set of sizes replaces it (and the
+        forms registered on the old one, which only warm-up passes can do)."""
+        total = sum(sizes)
+        if self.dbuf is None or self.dbuf.numel() != total or list(self.derived.values()) != list(sizes):
+            if torch.cuda.is_current_stream_capturing():
+                raise rt.B200Error("weight bank: the set of quantised weights changed between warm-up and capture")
+            self.dbuf = torch.empty(max(total, 1), device=self.dev, dtype=torch.float32)
+            stale = set(self.derived)
+            self.entries = {k: v for k, v in self.entries.items() if not (set(k[1:]) & stale)}
+            self.djobs, self.dtable = [], None
+            self.derived, o = {}, 0
+            for n in sizes:
+                self.derived[self.dbuf.data_ptr() + 4 * o] = n
+                o += n
+        return self.dbuf
+
+    def _is_derived(self, src):
+        b = self.dbuf
+        return b is not None and b.data_ptr() <= src.data_ptr() < b.data_ptr() + 4 * b.numel()
 
     def grad_view(self, w):
         """fp32 view of the flat gradient buffer shaped like parameter `w`, or None."""
-        if not self.knows(w):
+        if not self.knows(w) or w.data_ptr() not in self.index:
             return None
         i = self.index[w.data_ptr()]
         sl = self.slots[i]
@@ -62,7 +94,7 @@ class WeightBank:
         for t, o in enumerate(tap_off):
             j.tap_off[t] = o
         j.tiles_c = cp // 32
-        return j, ((rows + 31) // 32) * (cp // 32)
+        return j, ((rows + 31) // 32) * (cp // 32), self._is_derived(src)
 
     def _launch(self, jobs_with_tiles):
         arr = (rt.PackJob * len(jobs_with_tiles))()
@@ -83,11 +115,16 @@ class WeightBank:
         if torch.cuda.is_current_stream_capturing():
             raise rt.B200Error("weight bank: a weight form first appeared during graph capture (warm-up missed it)")
         result, jobs = build()
-        self.jobs.extend(jobs)
-        table, n, tiles = self._launch([(j, nt) for j, nt in jobs])
+        table, n, tiles = self._launch([(j, nt) for j, nt, _ in jobs])
         rt.pack_weights(table, n, tiles)
+        for j, nt, der in jobs:
+            if der:
+                self.djobs.append((j, nt))
+                self.dtable = None
+            else:
+                self.jobs.append((j, nt))
+                self.table = None    # stale: finalize() rebuilds
         self.entries[key] = result
-        self.table = None    # stale: finalize() rebuilds
         return result
 
     def begin_pass(self):
@@ -99,11 +136,18 @@ class WeightBank:
         self.shared |= {i for i, c in self.uses.items() if c > 1}
         if self.jobs and self.table is None:
             self.table, self.n_jobs, self.n_tiles = self._launch(self.jobs)
+        if self.djobs and self.dtable is None:
+            self.dtable, self.dn_jobs, self.dn_tiles = self._launch(self.djobs)
 
     def refresh(self):
         """Re-derive every registered form from the current parameter values: one launch."""
         if self.table is not None:
             rt.pack_weights(self.table, self.n_jobs, self.n_tiles)
+
+    def refresh_derived(self):
+        """Re-derive the forms of the derived weights; their producer calls this right after it has written them."""
+        if self.dtable is not None:
+            rt.pack_weights(self.dtable, self.dn_jobs, self.dn_tiles)
 
     # ------------------------------------------------------------------------------------------ forms
     def _alloc(self, rows, cols):
@@ -128,6 +172,25 @@ class WeightBank:
             dst = self._alloc(k, _pad64(n))
             return dst, [self._job(w, dst, k, n, _pad64(n), 1, 1, k, [0], src_off=row0 * k)]
         return self._add(("linT", w.data_ptr(), row0, n), build)
+
+    def block(self, w, c0, cn, r0, rn):
+        """Rows c0 .. c0 + cn, columns r0 .. r0 + rn of [N, K] (one mapped array block of a compute-in-memory layer)
+        -> [cn, rn_pad64]."""
+        k = w.shape[1]
+
+        def build():
+            dst = self._alloc(cn, _pad64(rn))
+            return dst, [self._job(w, dst, cn, rn, _pad64(rn), 1, k, 1, [0], src_off=c0 * k + r0)]
+        return self._add(("blk", w.data_ptr(), c0, cn, r0, rn), build)
+
+    def block_t(self, w, c0, cn, r0, rn):
+        """The same block transposed -> [rn, cn_pad64] (its input-gradient GEMM)."""
+        k = w.shape[1]
+
+        def build():
+            dst = self._alloc(rn, _pad64(cn))
+            return dst, [self._job(w, dst, rn, cn, _pad64(cn), 1, 1, k, [0], src_off=c0 * k + r0)]
+        return self._add(("blkT", w.data_ptr(), c0, cn, r0, rn), build)
 
     def conv(self, w, w2=None):
         """Conv2d [co, ci, kh, kw] -> [co, kh*kw*ci_pad] (+ a fused 1x1 shortcut's [co, ci2, 1, 1] appended along K)."""

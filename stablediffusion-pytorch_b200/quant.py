@@ -14,6 +14,7 @@ import math
 import torch
 from torch.autograd import Function
 
+from . import bank as BK
 from . import runtime as rt
 
 
@@ -108,6 +109,15 @@ class WeightQnFn(Function):
         return dw, ds.reshape(step.shape).to(step.dtype), None, None, None, None, None
 
 
+BANK_DERIVED = True     # False: quantised weights keep the per-leaf packing launches inside a captured step (tests)
+
+
+def _bank(w):
+    """The active weight bank if it holds `w` (a quantised weight WeightSideFn wrote into the bank's buffer)."""
+    b = BK.ACTIVE
+    return b if b is not None and b.knows(w) else None
+
+
 class WeightSideFn(Function):
     """weight_quant_noise of ALL quantised leaves of a model as one launch per phase (b200sd_weight_qn_multi): inputs
     (w0, s0, w1, s1, ...), outputs the quantised (+ noisy) weights, views of one flat buffer. Rows whose output received
@@ -117,7 +127,13 @@ class WeightSideFn(Function):
     def forward(ctx, specs, *tensors):
         ws, steps = tensors[0::2], tensors[1::2]
         dev = ws[0].device
-        flat = torch.empty(sum(w.numel() for w in ws), device=dev, dtype=torch.float32)
+        # inside a captured training step the results live in the weight bank's buffer: it then re-derives the packed
+        # bf16 forms of all of them with one launch (bank.refresh_derived) instead of one or two per leaf and direction
+        bank = BK.ACTIVE if BANK_DERIVED else None
+        if bank is not None:
+            flat = bank.derived_buffer([w.numel() for w in ws])
+        else:
+            flat = torch.empty(sum(w.numel() for w in ws), device=dev, dtype=torch.float32)
         draw = [w.numel() if sp["n_scale"] != 0 and sp["unit"] is None else 0 for w, sp in zip(ws, specs)]
         noise = torch.randn(sum(draw), device=dev, dtype=torch.float32) if sum(draw) else None
         rows, outs, units = [], [], []
@@ -135,6 +151,8 @@ class WeightSideFn(Function):
             outs.append(out)
             units.append(rows[-1]["unit"])
         rt.weight_qn_multi(rows, backward=False)
+        if bank is not None:
+            bank.refresh_derived()
         ctx.save_for_backward(*tensors, *units)
         ctx.specs = specs
         ctx.set_materialize_grads(False)
@@ -289,7 +307,8 @@ class AddaLayerFn(Function):
         M, N = x.shape[0], w.shape[0]
         xs, ws = x.detach(), w.detach()
         digits = AddaFn._digits(xs, step_in.detach(), cfg)
-        wp = ops.pack_linear_weight(ws)
+        bk = None if cfg.get("split_w") else _bank(ws)
+        wp = bk.linear(ws) if bk else ops.pack_linear_weight(ws)
         part = rt.linear(digits, wp, out_dtype=torch.float32)
         if cfg.get("split_w"):
             rt.linear(digits, ops.pack_linear_weight(ws - wp[:, :ws.shape[1]].float()), out=part, residual=part)
@@ -314,7 +333,8 @@ class AddaLayerFn(Function):
                                        cfg["offset_noise"])
         wd = w.detach()
         ddigits = torch.empty(S * M, K, device=x.device, dtype=torch.bfloat16)
-        rt.linear(dp, ops.pack_linear_weight(wd.t()), out=ddigits)
+        bk = _bank(wd)
+        rt.linear(dp, bk.linear_t(wd) if bk else ops.pack_linear_weight(wd.t()), out=ddigits)
         kp = (K + 63) // 64 * 64
         dwp = rt.wgrad([rt.make_src(digits, 1, 1, S * M, K, ld=K)], [(0, 0, 0, 0, kp // 64)],
                        rt.make_src(dp, 1, 1, S * M, N, ld=dp.stride(0)), N, 1, 1, S * M)
@@ -407,9 +427,10 @@ class AddaFn(Function):
         covered = _covers(((c0, cn) for _, _, c0, cn in cfg["blocks"]), N)
         out = (torch.empty if covered else torch.zeros)(M, N, device=x.device, dtype=torch.float32)
         seen = set()
+        bk = None if cfg.get("split_w") else _bank(w)
         for r0, rn, c0, cn in cfg["blocks"]:
             wb = w[c0:c0 + cn, r0:r0 + rn]
-            wp = ops.pack_linear_weight(wb)
+            wp = bk.block(w, c0, cn, r0, rn) if bk else ops.pack_linear_weight(wb)
             if keep is not None:
                 keep["packed"].append(wp)
             part = rt.linear(digits[:, r0:r0 + rn], wp, out_dtype=torch.float32)
@@ -444,6 +465,7 @@ class AddaFn(Function):
         dw = None if single else torch.zeros(N, K, device=x.device, dtype=torch.float32)
         das = []
         seen = set()
+        bk = _bank(wd)
         for bi, (r0, rn, c0, cn) in enumerate(blocks):
             wb = wd[c0:c0 + cn, r0:r0 + rn]
             part = rt.linear(digits[:, r0:r0 + rn], packed[bi] if packed else ops.pack_linear_weight(wb),
@@ -451,7 +473,8 @@ class AddaFn(Function):
             dp, da = rt.adc_bwd(part, dacc, M, cn, c0, S, sb, a1, cfg["R"], cfg["gain_noise"], cfg["offset_noise"])
             das.append(da)
             view = ddigits[:, r0:r0 + rn]
-            rt.linear(dp[:, :cn], ops.pack_linear_weight(wb.t()), out=view, residual=view if r0 in seen else None)
+            rt.linear(dp[:, :cn], bk.block_t(wd, c0, cn, r0, rn) if bk else ops.pack_linear_weight(wb.t()), out=view,
+                      residual=view if r0 in seen else None)
             seen.add(r0)
             kp = (rn + 63) // 64 * 64
             dwp = rt.wgrad([rt.make_src(digits[:, r0:r0 + rn], 1, 1, S * M, rn, ld=K)], [(0, 0, 0, 0, kp // 64)],

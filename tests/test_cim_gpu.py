@@ -653,6 +653,69 @@ def test_relu_unet_with_cim_leaves_runs_and_trains(kind):
     assert not missing, missing[:6]
 
 
+@pytest.mark.parametrize("kind", ["lsq", "adda"])
+def test_captured_step_packs_the_quantised_weights_in_one_launch(kind):
+    """Inside a captured training step the quantised weights of all cim_layers leaves live in the weight bank's buffer and
+    their bf16 GEMM forms (forward, transposed, convolution, flipped-tap dgrad, mapped array blocks) come from ONE
+    table-driven launch after the weight side (bank.refresh_derived) instead of one or two launches per leaf and
+    direction. Same conversions, so output and every gradient must be bit-identical to the per-leaf route."""
+    dev = _dev()
+    from cim_layers.layers_qn_lsq import Conv2d_qn_lsq, Linear_qn_lsq
+    from cim_layers.layers_qn_lsq_adda_cim import Conv2d_lsq_adda_cim, Linear_lsq_adda_cim, gen_weight_split_dict
+    from models.unet_cond_base_relu import Unet
+    from sdb200 import quant as Q
+    from util import cond_of
+    fx = load_golden("unet_small_cond_relu")
+    cfg, inp = fx["config"], fx["inputs"]
+    torch.manual_seed(fx["seed"])
+    model = Unet(4, cfg).eval().to(dev)
+    x, t, cond = inp["x"].to(dev), inp["t"].to(dev), cond_of(inp, cfg, dev)
+    kw = dict(weight_bit=4, input_bit=8, output_bit=8, noise_scale=0.05)
+    if kind == "lsq":
+        _convert(model, Linear_qn_lsq, Conv2d_qn_lsq, **kw)
+    else:
+        kw.update(dac_bit=5, adc_bit=12, adc_gain_1_scale=9.071428571, adc_gain_range=[1 / 64, 1 / 64],
+                  adc_adjust_mode="current")
+        _convert(model, Linear_lsq_adda_cim, Conv2d_lsq_adda_cim, **kw)
+        for m in model.modules():
+            if type(m) in (Linear_lsq_adda_cim, Conv2d_lsq_adda_cim):
+                m.weight_mapping_info = gen_weight_split_dict(m, [144, 64])   # several row and column blocks per leaf
+    g = torch.Generator().manual_seed(21)
+    for m in model.modules():
+        if hasattr(m, "_wq_spec"):
+            m.weight_noise_unit = torch.randn(m.weight.shape, generator=g).to(dev)   # the same noise in both runs
+    model.invalidate_plan()
+    with torch.no_grad():
+        model(x, t, cond)           # lazy initialisation of the step sizes / ADC gains
+    model.train()
+
+    def step(banked):
+        Q.BANK_DERIVED = banked
+        try:
+            model.invalidate_plan()
+            model.zero_grad(set_to_none=True)
+            out = model(x, t, cond)
+            out.square().mean().backward()
+            torch.cuda.synchronize()
+            tg = model.__dict__.get("_train_graph")
+            assert tg is not None, "the training step was not captured"
+            return out.detach().clone(), {k: p.grad.clone() for k, p in model.named_parameters() if p.grad is not None}, \
+                len(tg.bank.djobs), tg.launches
+        finally:
+            Q.BANK_DERIVED = True
+
+    out_a, ga, jobs_a, launches_a = step(True)
+    out_b, gb, jobs_b, launches_b = step(False)
+    print(f"   {kind}: {jobs_a} packed forms of quantised weights from one launch; captured launches {launches_b} -> {launches_a}")
+    # (tg.launches counts the library's own launches: the per-leaf route packs with torch copy kernels, which it does not
+    #  see, so the banked route shows up as exactly one launch more — the table-driven pack)
+    assert jobs_a > 40 and jobs_b == 0 and launches_a == launches_b + 1
+    assert torch.equal(out_a, out_b)
+    assert ga.keys() == gb.keys() and len(ga) > 100
+    bad = [k for k in ga if not torch.equal(ga[k], gb[k])]
+    assert not bad, bad[:6]
+
+
 # --------------------------------------------------------------------------------- fused weight-side kernels
 @pytest.mark.parametrize("isint", [False, True])
 @pytest.mark.parametrize("noise", [0.0, 0.08])
