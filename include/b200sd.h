@@ -216,7 +216,8 @@ int b200sd_groupnorm_apply(const void* x, int64_t ld_x, void* y, int64_t ld_y, c
  * b200sd_groupnorm_apply), x, and dy = dL/d act(GN(x)):  dx = dL/dx (+ add, an optional extra gradient of x with the
  * same geometry, e.g. the ResNet shortcut's). part: fp32 scratch [n, b200sd_rowblocks(n, hw, c), c, 2]; ab (optional):
  * fp32 [n, c, 2] receiving per-image (sum dz, sum dz*xhat), whose sums over n are dbeta and dgamma.
- * counter (optional): one zero-initialised uint32 in device memory, not shared with a concurrently running launch.
+ * counter (optional): a run of 64 zero-initialised uint32 in device memory, not shared with a concurrently running
+ * launch (the one-pass route keeps one arrival counter per channel chunk, the two-pass route uses the first).
  * With it the last CTA to finish folds ab over the batch into dgamma[c] / dbeta[c] (fixed order) and leaves the
  * counter at 0 again — no second kernel. */
 int b200sd_rowblocks(int64_t n, int64_t hw, int c);

@@ -3,6 +3,7 @@
 // memory when it fits so that the three passes (mean, centred variance, normalise) touch HBM once for the read
 // and once for the write. Mean/variance use the two-pass form in fp32 (no E[x^2]-E[x]^2 cancellation).
 #include "host.h"
+#include "ptx.cuh"
 #include <cstdlib>
 #include <cuda_bf16.h>
 
@@ -468,6 +469,239 @@ __global__ void __launch_bounds__(256)
     }
 }
 
+// ---- one-pass variant: a thread-block CLUSTER of K CTAs owns G whole groups of ONE image (cc = G * c/groups channels,
+// chosen >= 64 where the layer has them so that a row segment is at least 128 contiguous bytes); CTA `rank` keeps rows
+// [rank * rows_per_cta, ...) of that [hw, cc] slab of x and dy in shared memory between the reduction and the apply
+// phase, so x and dy are read from memory ONCE (two-pass: twice, plus a partials round trip and a second launch whose
+// every CTA repeats the statistics prologue for ALL channels). The per-channel sums A / B are exchanged through
+// distributed shared memory: every CTA adds the K partial vectors in rank order. Each thread re-reads exactly the
+// slab entries it copied itself (cp.async, issued before the statistics prologue so that the prologue's dependent loads
+// hide under the slab's flight). The host picks G, K so that the slab fits (gn_fused_plan). Same arithmetic per element as the two-pass kernels; A / B
+// are summed per thread over rows r0, r0 + rpp, ..., over r0 in four interleaved chains, then over ranks (fixed order).
+__device__ __forceinline__ float ld_cluster_f32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void gn_cp_async16(void* dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+
+__global__ void __launch_bounds__(256, 3)
+    gn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, const __nv_bfloat16* __restrict__ dy,
+                        long long ld_dy, const __nv_bfloat16* __restrict__ add, long long ld_add,
+                        __nv_bfloat16* __restrict__ dx, long long ld_dx, StatSeg s0, int c_split, StatSeg s1,
+                        const float* __restrict__ gamma, const float* __restrict__ beta, int hw, int c, int groups,
+                        float eps, int act, int G, int rpp, int K, int rows_per_cta,
+                        float* __restrict__ ab /* [n][c][2] or null */, float* __restrict__ dgamma,
+                        float* __restrict__ dbeta, unsigned int* counter /* one per channel chunk */) {
+    pdl_enter();
+    constexpr int V = 8, H = 4;
+    extern __shared__ __align__(16) unsigned char gnf_raw[];
+    const int rank = K > 1 ? static_cast<int>(cluster_ctarank()) : 0;
+    const int chunk = blockIdx.x / K;
+    const int cpg = c / groups, cc = G * cpg, c0 = chunk * cc, img = blockIdx.y;
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const int row_begin = rank * rows_per_cta;
+    const int nrows = min(hw - row_begin, rows_per_cta);
+    float* sc = reinterpret_cast<float*>(gnf_raw);   // scale = rstd * gamma
+    float* sh = sc + cc;                             // shift = beta - mean * scale
+    float* mu = sh + cc;
+    float* rs = mu + cc;
+    float* gm = rs + cc;                             // gamma
+    float* fa = gm + cc;                             // [cc][2] this CTA's share of A[c] = sum dz, B[c] = sum dz * xhat
+    float* ta = fa + 2 * cc;                         // A, B over the whole image
+    float* tb = ta + cc;
+    float* gs = tb + cc;                             // [G][2] mean, rstd
+    float* g12 = gs + 2 * G;                         // [G][2] S1, S2 scaled by 1 / (hw * cpg)
+    float* red = g12 + 2 * G;                        // [rpp][cc][2]
+    const int cv = cc / V;
+    const size_t slab_off = (static_cast<size_t>(9 * cc + 4 * G + 2 * rpp * cc) * sizeof(float) + 15) & ~size_t(15);
+    uint4* xs = reinterpret_cast<uint4*>(gnf_raw + slab_off);
+    uint4* ds = xs + static_cast<size_t>(rows_per_cta) * cv;
+    uint4* as = ds + static_cast<size_t>(rows_per_cta) * cv;      // the extra gradient's slab (only when add != null)
+
+    // ---- the slab starts flowing in before anything else: each thread copies the entries it will work on itself
+    const int v = tid % cv, r0 = tid / cv;
+    const bool active = r0 < rpp;
+    const long long base = static_cast<long long>(img) * hw + row_begin;
+    if (active) {
+        const __nv_bfloat16* xp = x + base * ld_x + c0 + v * V;
+        const __nv_bfloat16* dp = dy + base * ld_dy + c0 + v * V;
+        for (int rr = r0; rr < nrows; rr += rpp) {
+            gn_cp_async16(&xs[rr * cv + v], xp + rr * ld_x);
+            gn_cp_async16(&ds[rr * cv + v], dp + rr * ld_dy);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        if (add) {                        // needed in phase 2 only: a second group, waited for there
+            const __nv_bfloat16* ap = add + base * ld_add + c0 + v * V;
+            for (int rr = r0; rr < nrows; rr += rpp) gn_cp_async16(&as[rr * cv + v], ap + rr * ld_add);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+
+    // ---- statistics of the cluster's channels, summed exactly like gn_channel_params / gn_apply
+    for (int ch = tid; ch < cc; ch += nt) {
+        const int gch = c0 + ch;
+        const bool first = gch < c_split;
+        const StatSeg sg = first ? s0 : s1;
+        const int idx = first ? gch : gch - c_split;
+        const float* p = sg.ptr + (static_cast<long long>(img) * sg.p * sg.ld + idx) * 2;
+        float a = 0.f, b = 0.f;
+        for (int k = 0; k < sg.p; ++k) {
+            const float2 t = *reinterpret_cast<const float2*>(p + static_cast<long long>(k) * sg.ld * 2);
+            a += t.x, b += t.y;
+        }
+        sc[ch] = a, sh[ch] = b;
+        gm[ch] = gamma ? gamma[gch] : 1.f, mu[ch] = beta ? beta[gch] : 0.f;      // (mu: beta until the next step)
+    }
+    __syncthreads();
+    const float inv_cnt = 1.f / (static_cast<float>(hw) * cpg);
+    for (int g = tid; g < G; g += nt) {
+        float a = 0.f, b = 0.f;
+        for (int k = 0; k < cpg; ++k) a += sc[g * cpg + k], b += sh[g * cpg + k];
+        const float mean = a * inv_cnt;
+        const float var = fmaxf(b * inv_cnt - mean * mean, 0.f);
+        gs[2 * g] = mean, gs[2 * g + 1] = rsqrtf(var + eps);
+    }
+    __syncthreads();
+    for (int ch = tid; ch < cc; ch += nt) {
+        const int g = ch / cpg;
+        const float scale = gs[2 * g + 1] * gm[ch];
+        sc[ch] = scale, sh[ch] = mu[ch] - gs[2 * g] * scale;
+        mu[ch] = gs[2 * g], rs[ch] = gs[2 * g + 1];
+    }
+    __syncthreads();
+
+    // ---- phase 1: per-thread partial A / B over the thread's own slab entries
+    float scl[V], sft[V], m[V], r[V];
+    if (active) {
+#pragma unroll
+        for (int j = 0; j < V; ++j) scl[j] = sc[v * V + j], sft[j] = sh[v * V + j], m[j] = mu[v * V + j], r[j] = rs[v * V + j];
+        float a[V], b[V];
+#pragma unroll
+        for (int j = 0; j < V; ++j) a[j] = b[j] = 0.f;
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+#pragma unroll 2
+        for (int rr = r0; rr < nrows; rr += rpp) {
+            const uint4 ux = xs[rr * cv + v], ud = ds[rr * cv + v];
+            const __nv_bfloat162* hx = reinterpret_cast<const __nv_bfloat162*>(&ux);
+            const __nv_bfloat162* hd = reinterpret_cast<const __nv_bfloat162*>(&ud);
+#pragma unroll
+            for (int j = 0; j < H; ++j) {
+                const float2 fx = __bfloat1622float2(hx[j]), fd = __bfloat1622float2(hd[j]);
+                const float z0 = fx.x * scl[2 * j] + sft[2 * j], z1 = fx.y * scl[2 * j + 1] + sft[2 * j + 1];
+                const float d0 = fd.x * act_grad(z0, act), d1 = fd.y * act_grad(z1, act);
+                a[2 * j] += d0, a[2 * j + 1] += d1;
+                b[2 * j] += d0 * (fx.x - m[2 * j]) * r[2 * j], b[2 * j + 1] += d1 * (fx.y - m[2 * j + 1]) * r[2 * j + 1];
+            }
+        }
+        // red[(j, which)][r0][v]: consecutive threads write consecutive words
+#pragma unroll
+        for (int j = 0; j < V; ++j)
+            red[((2 * j) * rpp + r0) * cv + v] = a[j], red[((2 * j + 1) * rpp + r0) * cv + v] = b[j];
+    }
+    __syncthreads();
+    for (int i = tid; i < 2 * cc; i += nt) {
+        const int ch = i >> 1;
+        const float* p = red + ((2 * (ch % V) + (i & 1)) * rpp) * cv + ch / V;
+        float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f;
+        int k = 0;
+        for (; k + 4 <= rpp; k += 4) {
+            t0 += p[k * cv], t1 += p[(k + 1) * cv];
+            t2 += p[(k + 2) * cv], t3 += p[(k + 3) * cv];
+        }
+        for (; k < rpp; ++k) t0 += p[k * cv];
+        fa[i] = (t0 + t1) + (t2 + t3);
+    }
+    if (K > 1) {
+        cluster_sync_all();              // every CTA's partial vector is in its shared memory
+        for (int i = tid; i < 2 * cc; i += nt) {
+            float part[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) part[k] = k < K ? ld_cluster_f32(mapa_rank(&fa[i], k)) : 0.f;   // all in flight
+            float t = 0.f;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) t += part[k];
+            if (i & 1) tb[i >> 1] = t; else ta[i >> 1] = t;
+        }
+    } else {
+        __syncthreads();
+        for (int i = tid; i < 2 * cc; i += nt)
+            if (i & 1) tb[i >> 1] = fa[i]; else ta[i >> 1] = fa[i];
+    }
+    __syncthreads();
+    if (ab && rank == 0)
+        for (int i = tid; i < 2 * cc; i += nt)
+            ab[(static_cast<long long>(img) * c + c0) * 2 + i] = (i & 1) ? tb[i >> 1] : ta[i >> 1];
+    for (int g = tid; g < G; g += nt) {
+        float a = 0.f, b = 0.f;
+        for (int k = 0; k < cpg; ++k) a += gm[g * cpg + k] * ta[g * cpg + k], b += gm[g * cpg + k] * tb[g * cpg + k];
+        g12[2 * g] = a * inv_cnt, g12[2 * g + 1] = b * inv_cnt;
+    }
+    __syncthreads();
+
+    // ---- phase 2: dx from the slab. With c2 = rstd^2 * S2 and c1 = rstd * S1 - mean * c2 (per channel):
+    //   dx = rstd * (gamma * dz - S1 - xhat * S2) = scale * dz - c1 - x * c2      (scale = rstd * gamma)
+    if (active) {
+        float c1[V], c2[V];
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+            const int g = (v * V + j) / cpg;
+            c2[j] = r[j] * r[j] * g12[2 * g + 1];
+            c1[j] = r[j] * g12[2 * g] - m[j] * c2[j];
+        }
+        __nv_bfloat16* op = dx + base * ld_dx + c0 + v * V;
+        asm volatile("cp.async.wait_all;" ::: "memory");
+#pragma unroll 2
+        for (int rr = r0; rr < nrows; rr += rpp) {
+            const uint4 ux = xs[rr * cv + v], ud = ds[rr * cv + v];
+            uint4 ua = make_uint4(0u, 0u, 0u, 0u);
+            if (add) ua = as[rr * cv + v];
+            const __nv_bfloat162* hx = reinterpret_cast<const __nv_bfloat162*>(&ux);
+            const __nv_bfloat162* hd = reinterpret_cast<const __nv_bfloat162*>(&ud);
+            const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&ua);
+            uint4 o;
+            __nv_bfloat162* ho = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+            for (int j = 0; j < H; ++j) {
+                const float2 fx = __bfloat1622float2(hx[j]), fd = __bfloat1622float2(hd[j]), fa2 = __bfloat1622float2(ha[j]);
+                float res[2];
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int jj = 2 * j + e;
+                    const float xv = e ? fx.y : fx.x, dv = e ? fd.y : fd.x, av = e ? fa2.y : fa2.x;
+                    const float z = xv * scl[jj] + sft[jj];
+                    const float dz = dv * act_grad(z, act);
+                    res[e] = scl[jj] * dz - c1[jj] - xv * c2[jj] + av;
+                }
+                ho[j] = __floats2bfloat162_rn(res[0], res[1]);
+            }
+            *reinterpret_cast<uint4*>(op + rr * ld_dx) = o;
+        }
+    }
+    // ---- dgamma / dbeta of this channel chunk over the batch: whichever image's rank-0 CTA arrives last sums the chunk's
+    // columns of ab in tail_reduce's order (four interleaved chains over ascending images) — one short tail per chunk
+    // running beside the other clusters' streaming instead of one long tail over all channels at the end of the launch
+    if (counter && rank == 0 && last_cta_arrives(counter + chunk, gridDim.y)) {
+        const long long step = static_cast<long long>(c) * 2;
+        const int nimg = gridDim.y;
+        for (int i = tid; i < 2 * cc; i += nt) {
+            const float* p = ab + static_cast<long long>(c0) * 2 + i;
+            float q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
+            int k = 0;
+            for (; k + 4 <= nimg; k += 4) {
+                q0 += __ldcg(p + k * step), q1 += __ldcg(p + (k + 1) * step);
+                q2 += __ldcg(p + (k + 2) * step), q3 += __ldcg(p + (k + 3) * step);
+            }
+            for (; k < nimg; ++k) q0 += __ldcg(p + k * step);
+            ((i & 1) ? dgamma : dbeta)[c0 + (i >> 1)] = (q0 + q1) + (q2 + q3);
+        }
+    }
+    if (K > 1) cluster_sync_all();       // my partial vector stays readable until every CTA of the cluster has read it
+}
+
 // out[b][c] (+)= sum over r of in[b][r][c]  (fp32; bias / GroupNorm-affine / time-embedding gradients)
 __global__ void reduce_f32_kernel(const float* __restrict__ in, long long batch, long long rows, long long cols,
                                   long long col_stride, float* __restrict__ out, int accumulate) {
@@ -705,6 +939,54 @@ extern "C" int b200sd_rowblocks(int64_t n, int64_t hw, int c) {
     return row_geom(n, hw, c).blocks_per_img;
 }
 
+// One-pass GroupNorm backward (gn_bwd_fused_kernel): groups per cluster (G: the fewest that give >= 64 channels in whole
+// 16-byte vectors, else narrower vectors), CTAs per cluster (K: the fewest whose slab share fits beside a second CTA on
+// the SM, doubled while the launch has fewer CTAs than two per SM and a CTA would keep >= 32 rows), rows per pass,
+// shared memory. false -> the two-pass kernels. B200SD_GN_BWD_FUSED=0 (read per call) forces the two-pass route.
+constexpr int GN_FUSED_SMEM_MAX = 200 * 1024;
+struct GnFusedPlan {
+    int V, G, K, rows_per_cta, rpp, threads;
+    size_t smem;
+};
+static bool gn_fused_plan(int64_t n, int64_t hw, int c, int groups, bool with_add, GnFusedPlan& out) {
+    const char* e = getenv("B200SD_GN_BWD_FUSED");
+    if (e && e[0] == '0') return false;
+    if (hw <= 0 || hw > (1 << 20)) return false;
+    const int cpg = c / groups, V = 8;
+    int G = 0;
+    for (int g = 1; g <= groups; ++g)   // (g == groups always qualifies: c is a multiple of 8 and at most 2048)
+        if (groups % g == 0 && (g * cpg) % V == 0 && (g * cpg >= 64 || g == groups) && g * cpg / V <= 256 &&
+            groups / g <= 64) {
+            G = g;
+            break;
+        }
+    if (!G) return false;
+    const int cc = G * cpg, cv = cc / V;
+    auto smem_of = [&](int K, int& rows, int& rpp) {
+        rows = (int)((hw + K - 1) / K);
+        rpp = 256 / cv;
+        if (rpp > rows) rpp = rows;
+        const size_t head = ((size_t)(9 * cc + 4 * G + 2 * rpp * cc) * sizeof(float) + 15) & ~size_t(15);
+        return head + (with_add ? 3 : 2) * (size_t)rows * cc * 2;
+    };
+    const size_t limits[3] = {72 * 1024, 108 * 1024, (size_t)GN_FUSED_SMEM_MAX};   // three, two, one CTA per SM
+    for (int pass = 0; pass < 3; ++pass) {
+        for (int K = 1; K <= 8; K *= 2) {
+            int rows, rpp;
+            if ((int64_t)(K - 1) * ((hw + K - 1) / K) >= hw) break;       // a rank without rows
+            if (smem_of(K, rows, rpp) > limits[pass]) continue;
+            while (K < 8 && n * (groups / G) * K < 2ll * sm_count() && (hw + 2 * K - 1) / (2 * K) >= 32 &&
+                   (int64_t)(2 * K - 1) * ((hw + 2 * K - 1) / (2 * K)) < hw)
+                K *= 2;
+            out.smem = smem_of(K, rows, rpp);
+            out.V = V, out.G = G, out.K = K, out.rows_per_cta = rows, out.rpp = rpp;
+            out.threads = ((cv * rpp + 31) / 32) * 32;
+            return true;
+        }
+    }
+    return false;
+}
+
 extern "C" int b200sd_groupnorm_bwd(const void* x, int64_t ld_x, const void* dy, int64_t ld_dy, const void* add,
                                     int64_t ld_add, void* dx, int64_t ld_dx, const float* stats0, int p0, int ld_s0,
                                     int c_split, const float* stats1, int p1, int ld_s1, const float* gamma,
@@ -722,10 +1004,26 @@ extern "C" int b200sd_groupnorm_bwd(const void* x, int64_t ld_x, const void* dy,
     B200_REQUIRE(c_split >= 0 && c_split <= c && (c_split == c || stats1), "groupnorm_bwd: bad statistics split");
     B200_REQUIRE(n <= 65535, "groupnorm_bwd: batch exceeds grid limit");
     if (n == 0 || hw == 0) return B200SD_OK;
-    const RowGeom g = row_geom(n, hw, c);
     StatSeg s0{stats0, p0, ld_s0}, s1{stats1, p1, ld_s1};
-    dim3 grid((unsigned)g.blocks_per_img, (unsigned)n);
     cudaStream_t st = as_stream(stream);
+    GnFusedPlan fp;
+    if (gn_fused_plan(n, hw, c, groups, add != nullptr, fp)) {
+        static bool fused_configured = false;
+        if (!fused_configured) {
+            cudaFuncSetAttribute(gn_bwd_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GN_FUSED_SMEM_MAX);
+            fused_configured = true;
+        }
+        dim3 fgrid((unsigned)(groups / fp.G * fp.K), (unsigned)n);
+        launch_k_cluster(gn_bwd_fused_kernel, fgrid, fp.threads, fp.smem, st, (unsigned)fp.K,
+                         static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<const __nv_bfloat16*>(dy), ld_dy,
+                         static_cast<const __nv_bfloat16*>(add), ld_add, static_cast<__nv_bfloat16*>(dx), ld_dx, s0, c_split,
+                         s1, gamma, beta, (int)hw, c, groups, eps, act, fp.G, fp.rpp, fp.K, fp.rows_per_cta, ab, dgamma,
+                         dbeta, counter);
+        B200_CHECK_LAUNCH("groupnorm_bwd_fused");
+        return B200SD_OK;
+    }
+    const RowGeom g = row_geom(n, hw, c);
+    dim3 grid((unsigned)g.blocks_per_img, (unsigned)n);
     const size_t sm1 = (size_t)(4 * c + 2 * groups + 2 * g.rpp * c) * sizeof(float);
     const size_t sm2 = (size_t)(6 * c + 4 * groups) * sizeof(float);
     static bool configured = false;

@@ -7,6 +7,7 @@
 // Arithmetic that decides an integer code uses the same IEEE operations in the same order as the reference's fp32
 // torch ops (true division, clamp, round-half-even), so codes are bit-exact for identical inputs. All kernels are
 // HBM-bound streams with 16-byte accesses; reductions are fixed-order partials (no atomics on floats).
+#include <cstdlib>
 #include "host.h"
 #include <cuda_bf16.h>
 
@@ -339,6 +340,17 @@ static int q_grid(long long items, int per_block, int cap_mult = 16) {
     return static_cast<int>(b);
 }
 
+// CTAs per SM of the backward kernels that end in a last-CTA fold (one atomic per CTA on one counter, then a pass over
+// the partials): B200SD_QBWD_CAP overrides (tools/quant_bwd_sweep.py).
+static int qbwd_cap() {
+    static const int cap = [] {
+        const char* e = getenv("B200SD_QBWD_CAP");
+        const int v = e ? atoi(e) : 0;
+        return v > 0 && v <= 16 ? v : 4;
+    }();
+    return cap;
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -384,7 +396,7 @@ extern "C" int b200sd_lsq_quant(const void* x, int32_t x_f32, int64_t ld_x, void
     return B200SD_OK;
 }
 
-extern "C" int b200sd_lsq_quant_bwd_blocks(int64_t rows, int32_t c) { return q_grid(rows * (c / 8), 256, 4); }
+extern "C" int b200sd_lsq_quant_bwd_blocks(int64_t rows, int32_t c) { return q_grid(rows * (c / 8), 256, qbwd_cap()); }
 
 extern "C" int b200sd_lsq_quant_bwd(const void* dy, int64_t ld_dy, const void* x, int32_t x_f32, int64_t ld_x, void* dx,
                                     int64_t ld_dx, int64_t rows, int32_t c, const float* step, float qp, float g,
@@ -393,7 +405,7 @@ extern "C" int b200sd_lsq_quant_bwd(const void* dy, int64_t ld_dy, const void* x
                  "lsq_quant_bwd: bad arguments");
     B200_REQUIRE((total == nullptr) == (counter == nullptr), "lsq_quant_bwd: total and counter come together");
     B200_REQUIRE(Q_SHAPE_OK(c, ld_dy) && Q_SHAPE_OK(c, ld_x) && Q_SHAPE_OK(c, ld_dx), "lsq_quant_bwd: channels / pitches");
-    const int grid = q_grid(rows * (c / 8), 256, 4);
+    const int grid = q_grid(rows * (c / 8), 256, qbwd_cap());
     cudaStream_t st = as_stream(stream);
     if (x_f32)
         launch_k(lsq_quant_bwd_kernel<float>, grid, 256, 0, st, static_cast<const __nv_bfloat16*>(dy), ld_dy, static_cast<const float*>(x), ld_x,

@@ -357,9 +357,21 @@ def test_wgrad_conv(rt, n, h, w, cin, cout, k):
 
 
 # ------------------------------------------------------------------------------------- GroupNorm backward, colsum
+@pytest.mark.parametrize("two_pass", [False, True])
 @pytest.mark.parametrize("n,hw,c,groups,act", [(3, 1024, 128, 32, "silu"), (5, 64, 384, 32, "silu"),
-                                               (4, 16, 512, 32, "relu"), (2, 256, 96, 8, None), (16, 1024, 256, 32, "silu")])
-def test_groupnorm_backward(rt, n, hw, c, groups, act):
+                                               (4, 16, 512, 32, "relu"), (2, 256, 96, 8, None), (16, 1024, 256, 32, "silu"),
+                                               (2, 1024, 320, 32, "silu"),     # 10 channels per group: 8 groups per cluster
+                                               (2, 1024, 960, 32, "silu"),     # 30 per group: 120-channel slabs, 8 CTAs
+                                               (3, 100, 80, 8, "relu"),        # rows not a multiple of the row step
+                                               (2, 64, 48, 8, "silu"),         # 6 per group: all 8 groups in one cluster
+                                               (1, 64, 24, 4, None),           # whole layer narrower than 64 channels
+                                               (2, 4096, 1024, 32, "silu"),    # large slab: 8 CTAs x 150 KB
+                                               (1, 16384, 256, 32, "silu")])   # slab too large: two-pass either way
+def test_groupnorm_backward(rt, n, hw, c, groups, act, two_pass, monkeypatch):
+    """One-pass cluster kernel (slab of x / dy in shared memory) and the two-pass route (B200SD_GN_BWD_FUSED=0, also what
+    shapes whose slab does not fit use) against autograd through F.group_norm."""
+    if two_pass:
+        monkeypatch.setenv("B200SD_GN_BWD_FUSED", "0")
     dev = _dev()
     g = torch.Generator().manual_seed(n + hw + c)
     x = bf(torch.randn(n, hw, c, generator=g) * 1.5 + 0.3)

@@ -1,6 +1,6 @@
 """Per-kernel microbenchmarks at the shapes the conditioned UNet hits at batch 64 (SURVEY §2b shape census).
 
-    python tools/kernel_bench.py [--only igemm|groupnorm|attention|sched] [--iters N] [--json out.json]
+    python tools/kernel_bench.py [--only igemm|groupnorm|groupnorm_bwd|attention|sched] [--iters N] [--json out.json]
 
 Each case: 3 warm-up launches, then N timed launches bracketed by CUDA events on the launching stream, with a 256 MB
 write between launches to flush the 126 MB L2 (the flush is outside the event pair). Prints achieved TFLOP/s (tensor-
@@ -109,6 +109,49 @@ def bench_groupnorm(tm, out):
         out.append({"kernel": "gn_apply", "case": f"{n}x{hw}x{c}", "us": us, "gbs": gbs, "frac": gbs / hbm})
 
 
+def bench_groupnorm_bwd(tm, out):
+    """GroupNorm (+ SiLU) backward at the batch-16 training shapes of the conditioned UNet: the one-pass cluster kernel (the
+    slab of x and dy stays in shared memory between the reduction and the apply phase) against the two-pass route
+    (B200SD_GN_BWD_FUSED=0). Eight calls on eight different input sets inside one CUDA graph (how the training step
+    runs them; L2 flushed before each replay, so every call reads cold inputs). Algorithmic bytes: x, dy, the extra
+    gradient in; dx out = 8 bytes per element."""
+    hbm, tf = peaks()
+    cases = [(16, 1024, 128), (16, 1024, 256), (16, 1024, 384), (16, 1024, 512), (16, 1024, 640), (16, 256, 256),
+             (16, 256, 512), (16, 256, 768), (16, 256, 1024), (16, 64, 768), (16, 64, 1536), (16, 16, 768), (64, 1024, 384)]
+    reps = 8
+    for n, hw, c in cases:
+        sets = []
+        for _ in range(reps):
+            x = torch.randn(n * hw, c, device="cuda").to(torch.bfloat16)
+            dy = torch.randn(n * hw, c, device="cuda").to(torch.bfloat16)
+            extra = torch.randn(n * hw, c, device="cuda").to(torch.bfloat16)
+            xf = x.float().view(n, hw, c)
+            stats = torch.stack([xf.sum(1), (xf * xf).sum(1)], dim=-1).view(n, 1, c, 2).contiguous()
+            del xf
+            sets.append((x, dy, extra, stats))
+        g, b = torch.randn(c, device="cuda"), torch.randn(c, device="cuda")
+        res = {}
+        for mode in ("1", "0"):
+            os.environ["B200SD_GN_BWD_FUSED"] = mode
+
+            def calls():
+                for x, dy, extra, stats in sets:
+                    rt.groupnorm_bwd(x, dy, n, hw, c, 32, g, b, [(stats, 1, c, c)], act="silu", add=extra)
+            calls()
+            torch.cuda.synchronize()
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr):
+                calls()
+            res[mode] = tm.run(gr.replay) / reps
+            del gr
+        os.environ.pop("B200SD_GN_BWD_FUSED", None)
+        gbs = 8.0 * n * hw * c / res["1"] / 1e3
+        print(f"gn_bwd    n={n:4d} hw={hw:5d} c={c:4d} one-pass {res['1']:8.1f} us  two-pass {res['0']:8.1f} us  "
+              f"{gbs:7.0f} GB/s ({gbs / hbm:5.1%} of measured copy)", flush=True)
+        out.append({"kernel": "gn_bwd", "case": f"{n}x{hw}x{c}", "us": res["1"], "us_two_pass": res["0"], "gbs": gbs,
+                    "frac": gbs / hbm})
+
+
 def bench_attention(tm, out):
     hbm, tf = peaks()
     for lq, lk, c, heads in [(1024, 1024, 384, 16), (1024, 1024, 128, 16), (256, 256, 512, 16), (256, 256, 256, 16),
@@ -155,7 +198,8 @@ def main():
     a = ap.parse_args()
     tm = Timer(a.iters)
     out = []
-    for name, fn in [("igemm", bench_igemm), ("groupnorm", bench_groupnorm), ("attention", bench_attention),
+    for name, fn in [("igemm", bench_igemm), ("groupnorm", bench_groupnorm), ("groupnorm_bwd", bench_groupnorm_bwd),
+                     ("attention", bench_attention),
                      ("sched", bench_sched)]:
         if not a.only or a.only == name:
             fn(tm, out)
