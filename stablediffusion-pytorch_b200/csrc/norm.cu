@@ -484,16 +484,33 @@ __device__ __forceinline__ float ld_cluster_f32(uint32_t addr) {
     return v;
 }
 
+// act'(z) with the activation fixed at compile time. SiLU: s = rcp(1 + ex2(-z log2 e)) as two bare MUFU operations
+// (__expf / __fdividef wrap theirs in range-scaling sequences, ~8 more instructions per element in a kernel that is
+// bound by instruction issue), act' = s * (1 + z * (1 - s)). z -> -inf: ex2 overflows to +inf, rcp gives 0, the product
+// is -0 — the limit.
+template <int ACT>
+__device__ __forceinline__ float act_grad_fast(float z) {
+    if (ACT == B200SD_ACT_SILU) {
+        float e, sg;
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(z * -1.4426950408889634f));
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(sg) : "f"(1.f + e));
+        return sg * fmaf(z, 1.f - sg, 1.f);
+    }
+    if (ACT == B200SD_ACT_RELU) return z > 0.f ? 1.f : 0.f;
+    return 1.f;
+}
+
 __device__ __forceinline__ void gn_cp_async16(void* dst, const void* src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
 }
 
+template <int ACT>
 __global__ void __launch_bounds__(256, 3)
     gn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ x, long long ld_x, const __nv_bfloat16* __restrict__ dy,
                         long long ld_dy, const __nv_bfloat16* __restrict__ add, long long ld_add,
                         __nv_bfloat16* __restrict__ dx, long long ld_dx, StatSeg s0, int c_split, StatSeg s1,
                         const float* __restrict__ gamma, const float* __restrict__ beta, int hw, int c, int groups,
-                        float eps, int act, int G, int rpp, int K, int rows_per_cta,
+                        float eps, int G, int rpp, int K, int rows_per_cta,
                         float* __restrict__ ab /* [n][c][2] or null */, float* __restrict__ dgamma,
                         float* __restrict__ dbeta, unsigned int* counter /* one per channel chunk */) {
     pdl_enter();
@@ -527,16 +544,22 @@ __global__ void __launch_bounds__(256, 3)
     const bool active = r0 < rpp;
     const long long base = static_cast<long long>(img) * hw + row_begin;
     if (active) {
-        const __nv_bfloat16* xp = x + base * ld_x + c0 + v * V;
-        const __nv_bfloat16* dp = dy + base * ld_dy + c0 + v * V;
-        for (int rr = r0; rr < nrows; rr += rpp) {
-            gn_cp_async16(&xs[rr * cv + v], xp + rr * ld_x);
-            gn_cp_async16(&ds[rr * cv + v], dp + rr * ld_dy);
+        const __nv_bfloat16* xp = x + (base + r0) * ld_x + c0 + v * V;
+        const __nv_bfloat16* dp = dy + (base + r0) * ld_dy + c0 + v * V;
+        const long long sx = rpp * ld_x, sd = rpp * ld_dy;
+        const uint32_t slab_b = static_cast<uint32_t>(rows_per_cta) * cv * 16, step_b = static_cast<uint32_t>(rpp) * cv * 16;
+        uint32_t sa = smem_u32(&xs[r0 * cv + v]);
+        for (int rr = r0; rr < nrows; rr += rpp, xp += sx, dp += sd, sa += step_b) {
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(xp) : "memory");
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa + slab_b), "l"(dp) : "memory");
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
         if (add) {                        // needed in phase 2 only: a second group, waited for there
-            const __nv_bfloat16* ap = add + base * ld_add + c0 + v * V;
-            for (int rr = r0; rr < nrows; rr += rpp) gn_cp_async16(&as[rr * cv + v], ap + rr * ld_add);
+            const __nv_bfloat16* ap = add + (base + r0) * ld_add + c0 + v * V;
+            const long long sadd = rpp * ld_add;
+            sa = smem_u32(&as[r0 * cv + v]);
+            for (int rr = r0; rr < nrows; rr += rpp, ap += sadd, sa += step_b)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(ap) : "memory");
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
@@ -576,25 +599,33 @@ __global__ void __launch_bounds__(256, 3)
 
     // ---- phase 1: per-thread partial A / B over the thread's own slab entries
     float scl[V], sft[V], m[V], r[V];
+    const int stride_v = rpp * cv;                    // slab entries between a thread's consecutive rows
     if (active) {
+        float mr[V];                                  // xhat = x * rstd - mean * rstd
 #pragma unroll
-        for (int j = 0; j < V; ++j) scl[j] = sc[v * V + j], sft[j] = sh[v * V + j], m[j] = mu[v * V + j], r[j] = rs[v * V + j];
+        for (int j = 0; j < V; ++j) {
+            scl[j] = sc[v * V + j], sft[j] = sh[v * V + j], m[j] = mu[v * V + j], r[j] = rs[v * V + j];
+            mr[j] = m[j] * r[j];
+        }
         float a[V], b[V];
 #pragma unroll
         for (int j = 0; j < V; ++j) a[j] = b[j] = 0.f;
         asm volatile("cp.async.wait_group 1;" ::: "memory");
+        const uint4* px = xs + r0 * cv + v;
+        const uint4* pd = ds + r0 * cv + v;
 #pragma unroll 2
-        for (int rr = r0; rr < nrows; rr += rpp) {
-            const uint4 ux = xs[rr * cv + v], ud = ds[rr * cv + v];
+        for (int rr = r0; rr < nrows; rr += rpp, px += stride_v, pd += stride_v) {
+            const uint4 ux = *px, ud = *pd;
             const __nv_bfloat162* hx = reinterpret_cast<const __nv_bfloat162*>(&ux);
             const __nv_bfloat162* hd = reinterpret_cast<const __nv_bfloat162*>(&ud);
 #pragma unroll
             for (int j = 0; j < H; ++j) {
                 const float2 fx = __bfloat1622float2(hx[j]), fd = __bfloat1622float2(hd[j]);
-                const float z0 = fx.x * scl[2 * j] + sft[2 * j], z1 = fx.y * scl[2 * j + 1] + sft[2 * j + 1];
-                const float d0 = fd.x * act_grad(z0, act), d1 = fd.y * act_grad(z1, act);
+                const float z0 = fmaf(fx.x, scl[2 * j], sft[2 * j]), z1 = fmaf(fx.y, scl[2 * j + 1], sft[2 * j + 1]);
+                const float d0 = fd.x * act_grad_fast<ACT>(z0), d1 = fd.y * act_grad_fast<ACT>(z1);
                 a[2 * j] += d0, a[2 * j + 1] += d1;
-                b[2 * j] += d0 * (fx.x - m[2 * j]) * r[2 * j], b[2 * j + 1] += d1 * (fx.y - m[2 * j + 1]) * r[2 * j + 1];
+                b[2 * j] = fmaf(d0, fmaf(fx.x, r[2 * j], -mr[2 * j]), b[2 * j]);
+                b[2 * j + 1] = fmaf(d1, fmaf(fx.y, r[2 * j + 1], -mr[2 * j + 1]), b[2 * j + 1]);
             }
         }
         // red[(j, which)][r0][v]: consecutive threads write consecutive words
@@ -640,6 +671,10 @@ __global__ void __launch_bounds__(256, 3)
         for (int k = 0; k < cpg; ++k) a += gm[g * cpg + k] * ta[g * cpg + k], b += gm[g * cpg + k] * tb[g * cpg + k];
         g12[2 * g] = a * inv_cnt, g12[2 * g + 1] = b * inv_cnt;
     }
+    // arrival for the dgamma / dbeta tail HERE, while the only stores in flight are the few ab words: the fence inside
+    // would otherwise wait for all of phase 2's dx stores (the tail itself runs after phase 2)
+    bool own_tail = false;
+    if (counter && rank == 0) own_tail = last_cta_arrives(counter + chunk, gridDim.y);
     __syncthreads();
 
     // ---- phase 2: dx from the slab. With c2 = rstd^2 * S2 and c1 = rstd * S1 - mean * c2 (per channel):
@@ -652,13 +687,17 @@ __global__ void __launch_bounds__(256, 3)
             c2[j] = r[j] * r[j] * g12[2 * g + 1];
             c1[j] = r[j] * g12[2 * g] - m[j] * c2[j];
         }
-        __nv_bfloat16* op = dx + base * ld_dx + c0 + v * V;
+        __nv_bfloat16* op = dx + (base + r0) * ld_dx + c0 + v * V;
+        const long long so = rpp * ld_dx;
         asm volatile("cp.async.wait_all;" ::: "memory");
+        const uint4* px = xs + r0 * cv + v;
+        const uint4* pd = ds + r0 * cv + v;
+        const uint4* pa = as + r0 * cv + v;
 #pragma unroll 2
-        for (int rr = r0; rr < nrows; rr += rpp) {
-            const uint4 ux = xs[rr * cv + v], ud = ds[rr * cv + v];
+        for (int rr = r0; rr < nrows; rr += rpp, px += stride_v, pd += stride_v, pa += stride_v, op += so) {
+            const uint4 ux = *px, ud = *pd;
             uint4 ua = make_uint4(0u, 0u, 0u, 0u);
-            if (add) ua = as[rr * cv + v];
+            if (add) ua = *pa;
             const __nv_bfloat162* hx = reinterpret_cast<const __nv_bfloat162*>(&ux);
             const __nv_bfloat162* hd = reinterpret_cast<const __nv_bfloat162*>(&ud);
             const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&ua);
@@ -672,19 +711,19 @@ __global__ void __launch_bounds__(256, 3)
                 for (int e = 0; e < 2; ++e) {
                     const int jj = 2 * j + e;
                     const float xv = e ? fx.y : fx.x, dv = e ? fd.y : fd.x, av = e ? fa2.y : fa2.x;
-                    const float z = xv * scl[jj] + sft[jj];
-                    const float dz = dv * act_grad(z, act);
-                    res[e] = scl[jj] * dz - c1[jj] - xv * c2[jj] + av;
+                    const float z = fmaf(xv, scl[jj], sft[jj]);
+                    const float dz = dv * act_grad_fast<ACT>(z);
+                    res[e] = fmaf(-xv, c2[jj], fmaf(scl[jj], dz, -c1[jj])) + av;
                 }
                 ho[j] = __floats2bfloat162_rn(res[0], res[1]);
             }
-            *reinterpret_cast<uint4*>(op + rr * ld_dx) = o;
+            *reinterpret_cast<uint4*>(op) = o;
         }
     }
     // ---- dgamma / dbeta of this channel chunk over the batch: whichever image's rank-0 CTA arrives last sums the chunk's
     // columns of ab in tail_reduce's order (four interleaved chains over ascending images) — one short tail per chunk
     // running beside the other clusters' streaming instead of one long tail over all channels at the end of the launch
-    if (counter && rank == 0 && last_cta_arrives(counter + chunk, gridDim.y)) {
+    if (own_tail) {
         const long long step = static_cast<long long>(c) * 2;
         const int nimg = gridDim.y;
         for (int i = tid; i < 2 * cc; i += nt) {
@@ -1010,15 +1049,28 @@ extern "C" int b200sd_groupnorm_bwd(const void* x, int64_t ld_x, const void* dy,
     if (gn_fused_plan(n, hw, c, groups, add != nullptr, fp)) {
         static bool fused_configured = false;
         if (!fused_configured) {
-            cudaFuncSetAttribute(gn_bwd_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GN_FUSED_SMEM_MAX);
+            // the plan sizes slabs for two or three CTAs per SM: that needs the full shared-memory carve-out
+#define GN_FUSED_CFG(A)                                                                                                  \
+    cudaFuncSetAttribute(gn_bwd_fused_kernel<A>, cudaFuncAttributeMaxDynamicSharedMemorySize, GN_FUSED_SMEM_MAX);         \
+    cudaFuncSetAttribute(gn_bwd_fused_kernel<A>, cudaFuncAttributePreferredSharedMemoryCarveout,                          \
+                         cudaSharedmemCarveoutMaxShared)
+            GN_FUSED_CFG(B200SD_ACT_NONE);
+            GN_FUSED_CFG(B200SD_ACT_SILU);
+            GN_FUSED_CFG(B200SD_ACT_RELU);
+#undef GN_FUSED_CFG
             fused_configured = true;
         }
         dim3 fgrid((unsigned)(groups / fp.G * fp.K), (unsigned)n);
-        launch_k_cluster(gn_bwd_fused_kernel, fgrid, fp.threads, fp.smem, st, (unsigned)fp.K,
-                         static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<const __nv_bfloat16*>(dy), ld_dy,
-                         static_cast<const __nv_bfloat16*>(add), ld_add, static_cast<__nv_bfloat16*>(dx), ld_dx, s0, c_split,
-                         s1, gamma, beta, (int)hw, c, groups, eps, act, fp.G, fp.rpp, fp.K, fp.rows_per_cta, ab, dgamma,
-                         dbeta, counter);
+#define GN_FUSED_LAUNCH(A)                                                                                               \
+    launch_k_cluster(gn_bwd_fused_kernel<A>, fgrid, fp.threads, fp.smem, st, (unsigned)fp.K,                              \
+                     static_cast<const __nv_bfloat16*>(x), ld_x, static_cast<const __nv_bfloat16*>(dy), ld_dy,            \
+                     static_cast<const __nv_bfloat16*>(add), ld_add, static_cast<__nv_bfloat16*>(dx), ld_dx, s0, c_split, \
+                     s1, gamma, beta, (int)hw, c, groups, eps, fp.G, fp.rpp, fp.K, fp.rows_per_cta, ab, dgamma, dbeta,    \
+                     counter)
+        if (act == B200SD_ACT_SILU) GN_FUSED_LAUNCH(B200SD_ACT_SILU);
+        else if (act == B200SD_ACT_RELU) GN_FUSED_LAUNCH(B200SD_ACT_RELU);
+        else GN_FUSED_LAUNCH(B200SD_ACT_NONE);
+#undef GN_FUSED_LAUNCH
         B200_CHECK_LAUNCH("groupnorm_bwd_fused");
         return B200SD_OK;
     }
