@@ -992,9 +992,11 @@ static bool gn_fused_plan(int64_t n, int64_t hw, int c, int groups, bool with_ad
     if (e && e[0] == '0') return false;
     if (hw <= 0 || hw > (1 << 20)) return false;
     const int cpg = c / groups, V = 8;
+    const char* em = getenv("B200SD_GN_MIN_CH");
+    const int min_ch = em && atoi(em) >= 8 ? atoi(em) : 64;
     int G = 0;
     for (int g = 1; g <= groups; ++g)   // (g == groups always qualifies: c is a multiple of 8 and at most 2048)
-        if (groups % g == 0 && (g * cpg) % V == 0 && (g * cpg >= 64 || g == groups) && g * cpg / V <= 256 &&
+        if (groups % g == 0 && (g * cpg) % V == 0 && (g * cpg >= min_ch || g == groups) && g * cpg / V <= 256 &&
             groups / g <= 64) {
             G = g;
             break;
