@@ -1,12 +1,13 @@
 // Layout and conditioning glue (SURVEY K14 + boundary conversions). All HBM-bound, coalesced on the side that
 // dominates traffic; tiny next to the GEMMs but each replaces several ATen launches in the reference.
 #include "host.h"
+#include "ptx.cuh"
 #include <cuda_bf16.h>
 
 namespace b200 {
 
 __device__ __forceinline__ float glue_act(float v, int act) {
-    if (act == B200SD_ACT_SILU) return __fdividef(v, 1.f + __expf(-v));
+    if (act == B200SD_ACT_SILU) return silu_mufu(v);
     if (act == B200SD_ACT_RELU) return fmaxf(v, 0.f);
     return v;
 }

@@ -98,7 +98,7 @@ __device__ __forceinline__ Tile decode_tile(const IgemmArgs& a, int tile) {
 }
 
 __device__ __forceinline__ float apply_act(float v, int act) {
-    if (act == B200SD_ACT_SILU) return __fdividef(v, 1.f + __expf(-v));
+    if (act == B200SD_ACT_SILU) return silu_mufu(v);
     if (act == B200SD_ACT_RELU) return fmaxf(v, 0.f);
     return v;
 }
@@ -504,7 +504,7 @@ __global__ void __launch_bounds__(IGEMM_THREADS, MINB) igemm_kernel(const __grid
 #pragma unroll
                         for (int g = 0; g < 4; ++g)
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) v[g][j] = __fdividef(v[g][j], 1.f + __expf(-v[g][j]));
+                            for (int j = 0; j < 8; ++j) v[g][j] = silu_mufu(v[g][j]);
                     }
                     if (has_gate) {
                         const uint4* gp = reinterpret_cast<const uint4*>(args.gate + pnc * args.gate_ld + col0);

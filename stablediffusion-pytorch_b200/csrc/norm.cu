@@ -10,7 +10,7 @@
 namespace b200 {
 
 __device__ __forceinline__ float act_apply(float v, int act) {
-    if (act == B200SD_ACT_SILU) return __fdividef(v, 1.f + __expf(-v));
+    if (act == B200SD_ACT_SILU) return silu_mufu(v);
     if (act == B200SD_ACT_RELU) return fmaxf(v, 0.f);
     return v;
 }
@@ -128,7 +128,8 @@ struct StatSeg {
 };
 
 // SiLU / ReLU with the activation fixed at compile time. SiLU = v * rcp(1 + ex2(-v log2 e)): two MUFU ops and three
-// FP32 ops per element (an IEEE division here was ~20 instructions per element and made the kernel issue-bound).
+// FP32 ops per element (silu_mufu, ptx.cuh; an IEEE division here was ~20 instructions per element and made the kernel
+// issue-bound, and even __fdividef / __expf cost 3.5 more than the bare MUFU pair for the same bits).
 // GN_ACT_SILU_TANH: SiLU = h + h * tanh(h), h = v / 2 — ONE MUFU op (tanh.approx.f32, relative error 2^-11 on tanh,
 // i.e. at most |v| * 2.4e-4 absolute on the result: below the bf16 rounding of the stored output for |v| < 8) instead of
 // two (ex2 + rcp).
@@ -141,7 +142,7 @@ __device__ __forceinline__ float act_fast(float v) {
         asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
         return fmaf(h, t, h);
     }
-    if (ACT == B200SD_ACT_SILU) return __fdividef(v, 1.f + __expf(-v));
+    if (ACT == B200SD_ACT_SILU) return silu_mufu(v);
     if (ACT == B200SD_ACT_RELU) return fmaxf(v, 0.f);
     return v;
 }

@@ -106,6 +106,17 @@ __device__ __forceinline__ void tma_load_4d_pair(void* dst, const CUtensorMap* m
         : "memory");
 }
 // shared::cluster address of the same shared-memory location in CTA `rank` of this cluster
+// SiLU(v) = v * rcp(1 + ex2(-v log2 e)) as two bare MUFU operations and three FP32 ones. __fdividef(v, 1 + __expf(-v))
+// computes the same bits (its subnormal / huge-divisor ranges collapse to the same 0 and 1 here: 1 + e is never below
+// 1, and e beyond 2^126 gives v * 0 either way) but wraps both MUFU calls in range-scaling sequences — 3.5 extra
+// instructions per element in kernels that sit at the edge between memory- and issue-bound (gn_apply: 11 -> 8).
+__device__ __forceinline__ float silu_mufu(float v) {
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(v * -1.4426950408889634f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f + e));
+    return v * r;
+}
+
 __device__ __forceinline__ uint32_t mapa_rank(const void* p, uint32_t rank) {
     uint32_t r;
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(p)), "r"(rank));
