@@ -208,18 +208,22 @@ class _GroupedFn(torch.autograd.Function):
         if y_act is not None:
             dy = rt.relu_bwd(dy, y_act)
         dx = dw = db = None
+        want_b = ctx.bias_like is not None and ctx.needs_input_grad[2]
+        # parameter gradients as a branch beside the input-gradient GEMM (runtime.Side)
+        with rt.Side(ctx.needs_input_grad[0] and (ctx.needs_input_grad[1] or want_b), x.device) as side:
+            if ctx.needs_input_grad[1]:
+                k64 = (kp + 63) // 64 * 64
+                dwp = rt.wgrad([rt.make_src(x, 1, 1, M, kp, ld=x.stride(0))], [(0, 0, 0, 0, k64 // 64)],
+                               rt.make_src(dy, 1, 1, M, n_out, ld=dy.stride(0)), n_out, 1, 1, M)
+                dw = rt.blockdiag_gather(dwp, g, og, ig).to(weight.dtype)
+            if want_b:
+                db = rt.colsum(dy, 1, M, n_out) if n_out % 8 == 0 else dy.float().sum(0)
+                db = db.reshape(ctx.bias_like[0]).to(ctx.bias_like[1])
         if ctx.needs_input_grad[0]:
             _, dense_t = _dense_buffers(ctx.owner, weight)      # written by this step's forward
             dx = torch.empty(M, kp, device=x.device, dtype=torch.bfloat16)
             rt.linear(dy, dense_t, out=dx)
-        if ctx.needs_input_grad[1]:
-            k64 = (kp + 63) // 64 * 64
-            dwp = rt.wgrad([rt.make_src(x, 1, 1, M, kp, ld=x.stride(0))], [(0, 0, 0, 0, k64 // 64)],
-                           rt.make_src(dy, 1, 1, M, n_out, ld=dy.stride(0)), n_out, 1, 1, M)
-            dw = rt.blockdiag_gather(dwp, g, og, ig).to(weight.dtype)
-        if ctx.bias_like is not None and ctx.needs_input_grad[2]:
-            db = rt.colsum(dy, 1, M, n_out) if n_out % 8 == 0 else dy.float().sum(0)
-            db = db.reshape(ctx.bias_like[0]).to(ctx.bias_like[1])
+        side.join()
         return dx, dw, db, None, None
 
 

@@ -23,6 +23,9 @@ from . import ops
 from . import runtime as rt
 
 
+_Side = rt.Side     # parameter gradients as a branch beside the input-gradient GEMM (runtime.Side)
+
+
 def _bank(*ws):
     """The active weight bank if every given weight is parameter storage it knows (captured training step), else None."""
     b = BK.ACTIVE
@@ -114,21 +117,24 @@ class LinearFn(Function):
         if y_act is not None:
             dy = rt.relu_bwd(dy, y_act)
         dx = dw = db = dres = None
+        want_b = ctx.has_bias and ctx.needs_input_grad[2]
+        with _Side(ctx.needs_input_grad[0] and (ctx.needs_input_grad[1] or want_b), x.device) as side:
+            if ctx.needs_input_grad[1]:
+                kp = (K + 63) // 64 * 64
+                src = rt.make_src(x, 1, 1, M, K, ld=x.stride(0))
+                b = _bank(weight)
+                gv = b.grad_view(weight) if b else None
+                dwp = rt.wgrad([src], [(0, 0, 0, 0, kp // 64)], rt.make_src(dy, 1, 1, M, N, ld=dy.stride(0)), N, 1, 1, M,
+                               scatter=None if gv is None else [(gv, 0, K, kp, 1, K, 1, [0])])
+                dw = gv if gv is not None else dwp[:, :K]
+            if want_b:
+                db = rt.colsum(dy, 1, M, N) if N % 8 == 0 else dy.float().sum(0)
         if ctx.needs_input_grad[0]:
             b = _bank(weight)
             wt = b.linear_t(weight) if b else ops.pack_linear_weight(weight.detach().t())  # [K, N_pad64]
             dx = torch.empty(M, _pad8(K), device=x.device, dtype=torch.bfloat16)[:, :K]
             rt.linear(dy, wt, out=dx)
-        if ctx.needs_input_grad[1]:
-            kp = (K + 63) // 64 * 64
-            src = rt.make_src(x, 1, 1, M, K, ld=x.stride(0))
-            b = _bank(weight)
-            gv = b.grad_view(weight) if b else None
-            dwp = rt.wgrad([src], [(0, 0, 0, 0, kp // 64)], rt.make_src(dy, 1, 1, M, N, ld=dy.stride(0)), N, 1, 1, M,
-                           scatter=None if gv is None else [(gv, 0, K, kp, 1, K, 1, [0])])
-            dw = gv if gv is not None else dwp[:, :K]
-        if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = rt.colsum(dy, 1, M, N) if N % 8 == 0 else dy.float().sum(0)
+        side.join()
         if ctx.has_res and ctx.needs_input_grad[3]:
             dres = dy
         return dx, dw, db, dres, None, None, None
@@ -176,10 +182,24 @@ class CrossProjFn(Function):
             db = torch.empty(3 * C, device=dev, dtype=torch.float32)
             if dq is None or dkv is None or C % 8:
                 db.zero_()
+        parts = [(None if dy is None else _rows(dy, rn), x, r0, rn, slot) for dy, x, r0, rn, slot in parts]
+        with _Side((ctx.needs_input_grad[0] or ctx.needs_input_grad[1]) and (dw is not None or db is not None), dev) as side:
+            for dy, x, r0, rn, slot in parts:       # parameter gradients: a branch of their own (see _Side)
+                if dy is None:
+                    continue
+                M = x.shape[0]
+                if dw is not None:
+                    rt.wgrad([rt.make_src(x, 1, 1, M, K, ld=x.stride(0))], [(0, 0, 0, 0, kp // 64)],
+                             rt.make_src(dy, 1, 1, M, rn, ld=dy.stride(0)), rn, 1, 1, M,
+                             scatter=[(dw[r0:r0 + rn], 0, K, kp, 1, K, 1, [0])])
+                if db is not None:
+                    if rn % 8 == 0:
+                        rt.colsum(dy, 1, M, rn, out=db[r0:r0 + rn])
+                    else:
+                        db[r0:r0 + rn] = dy.float().sum(0)
         for dy, x, r0, rn, slot in parts:
             if dy is None:
                 continue
-            dy = _rows(dy, rn)
             M = x.shape[0]
             if ctx.needs_input_grad[slot]:
                 wt = bk.linear_t(weight, r0, rn) if bk else ops.pack_linear_weight(wd[r0:r0 + rn].t())
@@ -189,15 +209,7 @@ class CrossProjFn(Function):
                     dxq = dx
                 else:
                     dxkv = dx
-            if dw is not None:
-                rt.wgrad([rt.make_src(x, 1, 1, M, K, ld=x.stride(0))], [(0, 0, 0, 0, kp // 64)],
-                         rt.make_src(dy, 1, 1, M, rn, ld=dy.stride(0)), rn, 1, 1, M,
-                         scatter=[(dw[r0:r0 + rn], 0, K, kp, 1, K, 1, [0])])
-            if db is not None:
-                if rn % 8 == 0:
-                    rt.colsum(dy, 1, M, rn, out=db[r0:r0 + rn])
-                else:
-                    db[r0:r0 + rn] = dy.float().sum(0)
+        side.join()
         return dxq, dxkv, dw, db, None
 
 
@@ -241,6 +253,42 @@ class ConvSameFn(Function):
         dy = _rows(dy, cout)
         P = n * h * w
         dx = dw = db = drb = dx2 = dw2 = db2 = None
+        want_bias = (has_b and ctx.needs_input_grad[2]) or (has_b2 and ctx.needs_input_grad[6]) or has_rb
+        want_w = ctx.needs_input_grad[1] or (w2 is not None and ctx.needs_input_grad[5])
+        with _Side((ctx.needs_input_grad[0] or (x2 is not None and ctx.needs_input_grad[4])) and (want_w or want_bias),
+                   x.device) as side:
+            if ctx.needs_input_grad[1] or (w2 is not None and ctx.needs_input_grad[5]):
+                pad, cp = k // 2, ops._pad64(cin)
+                srcs = [rt.make_src(x, n, h, w, cin, ld=x.stride(0))]
+                segs = [(0, ky - pad, kx - pad, 0, cp // 64) for ky in range(k) for kx in range(k)]
+                if x2 is not None:
+                    srcs.append(rt.make_src(x2, n, h, w, cin2, ld=x2.stride(0)))
+                    segs.append((1, 0, 0, 0, ops._pad64(cin2) // 64))
+                bk = _bank(weight) if x2 is None else _bank(weight, w2)
+                gv = bk.grad_view(weight) if bk else None
+                gv2 = bk.grad_view(w2) if (bk and x2 is not None) else None
+                sc = None
+                if gv is not None and (x2 is None or gv2 is not None):
+                    kk = k * k
+                    sc = [(gv, 0, cin, cp, kk, cin * kk, kk, list(range(kk)))]
+                    if x2 is not None:
+                        sc.append((gv2, kk * cp, cin2, ops._pad64(cin2), 1, cin2, 1, [0]))
+                dwp = rt.wgrad(srcs, segs, rt.make_src(dy, n, h, w, cout, ld=dy.stride(0)), cout, n, h, w, scatter=sc)
+                if sc is not None:
+                    dw, dw2 = gv, gv2
+                else:
+                    dw = dwp[:, :k * k * cp].reshape(cout, k * k, cp)[:, :, :cin].permute(0, 2, 1).reshape(cout, cin, k, k)
+                    if x2 is not None:
+                        dw2 = dwp[:, k * k * cp:k * k * cp + cin2].reshape(cout, cin2, 1, 1)
+            if (has_b and ctx.needs_input_grad[2]) or (has_b2 and ctx.needs_input_grad[6]) or has_rb:
+                if cout % 8 == 0:
+                    per = rt.colsum(dy, n, h * w, cout, per_image=True)  # fp32 [n, cout]
+                else:
+                    per = dy.float().reshape(n, h * w, cout).sum(1)
+                tot = per.sum(0) if (has_b or has_b2) else None
+                db = tot if has_b else None
+                db2 = (tot.clone() if has_b else tot) if has_b2 else None   # never hand one buffer to two parameters
+                drb = per.to(torch.bfloat16) if has_rb else None
         if ctx.needs_input_grad[0]:
             # dgrad of a stride-1 'same' conv = the same conv with taps flipped and in/out channels swapped
             bk = _bank(weight)
@@ -256,38 +304,7 @@ class ConvSameFn(Function):
             dx2 = full[:, :cin2]
             rt.linear(dy, wt, out=dx2)
             dx2 = full if full.shape[1] == x2.shape[1] else dx2
-        if ctx.needs_input_grad[1] or (w2 is not None and ctx.needs_input_grad[5]):
-            pad, cp = k // 2, ops._pad64(cin)
-            srcs = [rt.make_src(x, n, h, w, cin, ld=x.stride(0))]
-            segs = [(0, ky - pad, kx - pad, 0, cp // 64) for ky in range(k) for kx in range(k)]
-            if x2 is not None:
-                srcs.append(rt.make_src(x2, n, h, w, cin2, ld=x2.stride(0)))
-                segs.append((1, 0, 0, 0, ops._pad64(cin2) // 64))
-            bk = _bank(weight) if x2 is None else _bank(weight, w2)
-            gv = bk.grad_view(weight) if bk else None
-            gv2 = bk.grad_view(w2) if (bk and x2 is not None) else None
-            sc = None
-            if gv is not None and (x2 is None or gv2 is not None):
-                kk = k * k
-                sc = [(gv, 0, cin, cp, kk, cin * kk, kk, list(range(kk)))]
-                if x2 is not None:
-                    sc.append((gv2, kk * cp, cin2, ops._pad64(cin2), 1, cin2, 1, [0]))
-            dwp = rt.wgrad(srcs, segs, rt.make_src(dy, n, h, w, cout, ld=dy.stride(0)), cout, n, h, w, scatter=sc)
-            if sc is not None:
-                dw, dw2 = gv, gv2
-            else:
-                dw = dwp[:, :k * k * cp].reshape(cout, k * k, cp)[:, :, :cin].permute(0, 2, 1).reshape(cout, cin, k, k)
-                if x2 is not None:
-                    dw2 = dwp[:, k * k * cp:k * k * cp + cin2].reshape(cout, cin2, 1, 1)
-        if (has_b and ctx.needs_input_grad[2]) or (has_b2 and ctx.needs_input_grad[6]) or has_rb:
-            if cout % 8 == 0:
-                per = rt.colsum(dy, n, h * w, cout, per_image=True)  # fp32 [n, cout]
-            else:
-                per = dy.float().reshape(n, h * w, cout).sum(1)
-            tot = per.sum(0) if (has_b or has_b2) else None
-            db = tot if has_b else None
-            db2 = (tot.clone() if has_b else tot) if has_b2 else None   # never hand one buffer to two parameters
-            drb = per.to(torch.bfloat16) if has_rb else None
+        side.join()
         return dx, dw, db, drb, dx2, dw2, db2, None, None, None
 
 
@@ -330,24 +347,27 @@ class ConvDownFn(Function):
         oh, ow = h // 2, w // 2
         dy = _rows(dy, cout)
         dx = dw = db = None
+        want_b = ctx.has_bias and ctx.needs_input_grad[2]
+        with _Side(ctx.needs_input_grad[0] and (ctx.needs_input_grad[1] or want_b), x.device) as side:
+            if ctx.needs_input_grad[1]:
+                cp = ops._pad64(cin)
+                ld = x.stride(0)
+                srcs = [rt.make_src(x, n, oh, ow, cin, ld=ld, sy=2, sx=2, oy=py, ox=px, hh=h, ww=w) for py in (0, 1)
+                        for px in (0, 1)]
+                bk = _bank(weight)
+                gv = bk.grad_view(weight) if bk else None
+                dwp = rt.wgrad(srcs, _down_segs(cp), rt.make_src(dy, n, oh, ow, cout, ld=dy.stride(0)), cout, n, oh, ow,
+                               scatter=None if gv is None else [(gv, 0, cin, cp, 16, cin * 16, 16, list(range(16)))])
+                dw = gv if gv is not None else dwp.reshape(cout, 16, cp)[:, :, :cin].permute(0, 2, 1).reshape(cout, cin, 4, 4)
+            if want_b:
+                db = rt.colsum(dy, n, oh * ow, cout)
         if ctx.needs_input_grad[0]:
             # adjoint of Conv2d(4, 2, 1) with weight [co, ci] = ConvTranspose2d(4, 2, 1) with the same tensor as [in=co, out=ci]
             bk = _bank(weight)
             phases = bk.convT_phases(weight, _phase_taps(ops._pad64(cout))) if bk else ops.pack_convT_weight(weight.detach())
             dx = torch.empty(n * h * w, cin, device=x.device, dtype=torch.bfloat16)
             ops.conv_up4x4(dy, n, oh, ow, cout, phases, cin, ld_x=dy.stride(0), out=dx)
-        if ctx.needs_input_grad[1]:
-            cp = ops._pad64(cin)
-            ld = x.stride(0)
-            srcs = [rt.make_src(x, n, oh, ow, cin, ld=ld, sy=2, sx=2, oy=py, ox=px, hh=h, ww=w) for py in (0, 1)
-                    for px in (0, 1)]
-            bk = _bank(weight)
-            gv = bk.grad_view(weight) if bk else None
-            dwp = rt.wgrad(srcs, _down_segs(cp), rt.make_src(dy, n, oh, ow, cout, ld=dy.stride(0)), cout, n, oh, ow,
-                           scatter=None if gv is None else [(gv, 0, cin, cp, 16, cin * 16, 16, list(range(16)))])
-            dw = gv if gv is not None else dwp.reshape(cout, 16, cp)[:, :, :cin].permute(0, 2, 1).reshape(cout, cin, 4, 4)
-        if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = rt.colsum(dy, n, oh * ow, cout)
+        side.join()
         return dx, dw, db, None, None
 
 

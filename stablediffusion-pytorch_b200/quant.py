@@ -332,15 +332,17 @@ class AddaLayerFn(Function):
                                        qp_out, numel_out, cfg["R"], S, sb, scratch, want_b, cfg["gain_noise"],
                                        cfg["offset_noise"])
         wd = w.detach()
+        kp = (K + 63) // 64 * 64
+        with rt.Side(True, x.device) as side:      # weight and bias gradients: a branch beside the input-gradient chain
+            dwp = rt.wgrad([rt.make_src(digits, 1, 1, S * M, K, ld=K)], [(0, 0, 0, 0, kp // 64)],
+                           rt.make_src(dp, 1, 1, S * M, N, ld=dp.stride(0)), N, 1, 1, S * M)
+            dbias = rt.colsum(dy, 1, M, N).to(bias.dtype) if want_b else None
         ddigits = torch.empty(S * M, K, device=x.device, dtype=torch.bfloat16)
         bk = _bank(wd)
         rt.linear(dp, bk.linear_t(wd) if bk else ops.pack_linear_weight(wd.t()), out=ddigits)
-        kp = (K + 63) // 64 * 64
-        dwp = rt.wgrad([rt.make_src(digits, 1, 1, S * M, K, ld=K)], [(0, 0, 0, 0, kp // 64)],
-                       rt.make_src(dp, 1, 1, S * M, N, ld=dp.stride(0)), N, 1, 1, S * M)
         dxq = rt.bit_split_bwd(ddigits, M, K, S, sb)
         dx, ds = rt.lsq_quant_bwd(dxq, x, step_in.detach(), cfg["qp_in"], codes=True, numel=cfg["numel_in"])
-        dbias = rt.colsum(dy, 1, M, N).to(bias.dtype) if want_b else None
+        side.join()
         dstep_out = res[0].reshape(step_out.shape).to(step_out.dtype) if step_out is not None else None
         return (dx if ctx.needs_input_grad[0] else None), ds.reshape(step_in.shape), dwp[:, :K], \
             res[1].reshape(alpha.shape).to(alpha.dtype), dbias, dstep_out, None, None, None, None, None

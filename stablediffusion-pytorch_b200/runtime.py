@@ -241,6 +241,44 @@ def launch_count():
     return int(lib().b200sd_launch_count()) + _replayed
 
 
+# In a layer's backward pass the input-gradient GEMM and the parameter gradients (weight-gradient GEMM, its scatter, the
+# bias column sum) depend on dy only, not on each other, and at batch 16 most of them are far too small to fill 148 SMs
+# (work items per launch: a few dozen). They therefore run as two BRANCHES: the parameter gradients on a side stream
+# forked from the current one, the input gradient on the current stream, joined before the Function returns — inside
+# a captured training step these become parallel branches of the CUDA graph. B200SD_PARALLEL_WGRAD=0 serialises them.
+PARALLEL_BRANCHES = os.environ.get("B200SD_PARALLEL_WGRAD", "1") != "0"
+_SIDE_STREAMS = {}
+
+
+class Side:
+    """with Side(on, device) as side: <parameter-gradient launches>;  <input-gradient launches>;  side.join()"""
+
+    def __init__(self, on, dev):
+        self.on = bool(on) and PARALLEL_BRANCHES
+        if self.on:
+            key = dev.index if dev.index is not None else torch.cuda.current_device()
+            s = _SIDE_STREAMS.get(key)
+            if s is None:
+                s = _SIDE_STREAMS[key] = torch.cuda.Stream(device=dev)
+            self.s = s
+
+    def __enter__(self):
+        if self.on:
+            self.s.wait_stream(torch.cuda.current_stream())      # fork: everything dy depends on is ordered before
+            self.cm = torch.cuda.stream(self.s)
+            self.cm.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        if self.on:
+            self.cm.__exit__(*exc)
+        return False
+
+    def join(self):
+        if self.on:
+            torch.cuda.current_stream().wait_stream(self.s)
+
+
 def stream_ptr():
     return torch.cuda.current_stream().cuda_stream
 
