@@ -116,7 +116,7 @@ class LinearFn(Function):
         dy = _rows(dy, N)
         if y_act is not None:
             dy = rt.relu_bwd(dy, y_act)
-        dx = dw = db = dres = None
+        dx = dw = db = dres = gv = None
         want_b = ctx.has_bias and ctx.needs_input_grad[2]
         with _Side(ctx.needs_input_grad[0] and (ctx.needs_input_grad[1] or want_b), x.device) as side:
             if ctx.needs_input_grad[1]:
@@ -134,7 +134,7 @@ class LinearFn(Function):
             wt = b.linear_t(weight) if b else ops.pack_linear_weight(weight.detach().t())  # [K, N_pad64]
             dx = torch.empty(M, _pad8(K), device=x.device, dtype=torch.bfloat16)[:, :K]
             rt.linear(dy, wt, out=dx)
-        side.join()
+        side.join(dy, x, defer_ok=not ctx.needs_input_grad[1] or (dw is not None and gv is not None))
         if ctx.has_res and ctx.needs_input_grad[3]:
             dres = dy
         return dx, dw, db, dres, None, None, None
@@ -171,7 +171,7 @@ class CrossProjFn(Function):
         dev = xq.device
         bk = _bank(weight)
         wd = weight.detach()
-        dxq = dxkv = dw = db = None
+        dxq = dxkv = dw = db = gv = None
         parts = ((dq, xq, 0, C, 0), (dkv, xkv, C, 2 * C, 1))
         if ctx.needs_input_grad[2]:
             gv = bk.grad_view(weight) if bk else None
@@ -209,7 +209,7 @@ class CrossProjFn(Function):
                     dxq = dx
                 else:
                     dxkv = dx
-        side.join()
+        side.join(xq, xkv, *[t for t, *_ in parts], defer_ok=dw is None or gv is not None)
         return dxq, dxkv, dw, db, None
 
 
@@ -252,7 +252,7 @@ class ConvSameFn(Function):
         cout, k = weight.shape[0], weight.shape[2]
         dy = _rows(dy, cout)
         P = n * h * w
-        dx = dw = db = drb = dx2 = dw2 = db2 = None
+        dx = dw = db = drb = dx2 = dw2 = db2 = sc = None
         want_bias = (has_b and ctx.needs_input_grad[2]) or (has_b2 and ctx.needs_input_grad[6]) or has_rb
         want_w = ctx.needs_input_grad[1] or (w2 is not None and ctx.needs_input_grad[5])
         with _Side((ctx.needs_input_grad[0] or (x2 is not None and ctx.needs_input_grad[4])) and (want_w or want_bias),
@@ -304,7 +304,8 @@ class ConvSameFn(Function):
             dx2 = full[:, :cin2]
             rt.linear(dy, wt, out=dx2)
             dx2 = full if full.shape[1] == x2.shape[1] else dx2
-        side.join()
+        # (the row-bias gradient feeds the time-embedding branch of THIS backward pass: no deferral with it)
+        side.join(dy, x, x2, defer_ok=not has_rb and (not want_w or sc is not None))
         return dx, dw, db, drb, dx2, dw2, db2, None, None, None
 
 
@@ -346,7 +347,7 @@ class ConvDownFn(Function):
         cout = weight.shape[0]
         oh, ow = h // 2, w // 2
         dy = _rows(dy, cout)
-        dx = dw = db = None
+        dx = dw = db = gv = None
         want_b = ctx.has_bias and ctx.needs_input_grad[2]
         with _Side(ctx.needs_input_grad[0] and (ctx.needs_input_grad[1] or want_b), x.device) as side:
             if ctx.needs_input_grad[1]:
@@ -367,7 +368,7 @@ class ConvDownFn(Function):
             phases = bk.convT_phases(weight, _phase_taps(ops._pad64(cout))) if bk else ops.pack_convT_weight(weight.detach())
             dx = torch.empty(n * h * w, cin, device=x.device, dtype=torch.bfloat16)
             ops.conv_up4x4(dy, n, oh, ow, cout, phases, cin, ld_x=dy.stride(0), out=dx)
-        side.join()
+        side.join(dy, x, defer_ok=not ctx.needs_input_grad[1] or gv is not None)
         return dx, dw, db, None, None
 
 

@@ -331,6 +331,7 @@ class _BucketReducer:
         self.pending = [len(b) for b in self.buckets]
         self.done = [False] * len(self.buckets)
         self.grads, self.copied, self.handles = {}, set(), []
+        self._keep = []       # sources of copies issued on the side stream: alive until finish() has joined it
 
     def arm(self):
         for i, k in self.index_of.items():
@@ -363,12 +364,15 @@ class _BucketReducer:
                 continue
             views.append(v)
             srcs.append(g if g.dtype == torch.float32 else g.float())
-        if views:
-            torch._foreach_copy_(views, srcs)
         lo, hi = bucket_range(tg.slots, idxs)
         main = torch.cuda.current_stream()
-        self.side.wait_stream(main)          # fork: the bucket's producers are ordered before the collective
+        self.side.wait_stream(main)          # fork: the bucket's producers are ordered before the collective —
+        if rt.Side.FORKED:
+            self.side.wait_stream(rt.Side.stream(tg.flat.device))   # — those on the parameter-gradient branch too
         with torch.cuda.stream(self.side):
+            if views:                        # (bias sums and other gradients not written in place: they may come from
+                torch._foreach_copy_(views, srcs)   # the parameter-gradient branch, so the copy rides this stream)
+                self._keep.extend(srcs)
             self.dist.all_reduce(tg.flat[lo:min(hi, tg.flat.numel())], op=self.dist.ReduceOp.AVG, group=self.group)
         self.done[b] = True
 
@@ -379,6 +383,7 @@ class _BucketReducer:
                     self.grads.pop(i, None)
                 self._flush(b)
         torch.cuda.current_stream().wait_stream(self.side)   # join
+        self._keep.clear()
 
 
 # Version of "the module trees of this process": bumped whenever ANY module registers a sub-module, a parameter or a
@@ -473,6 +478,14 @@ class TrainGraph:
         return fired
 
     def _build(self, forward, wrt, dev):
+        rt.Side.DEFER = True     # parameter-gradient branches join at the end of a backward pass (runtime.Side)
+        try:
+            self._build_deferred(forward, wrt, dev)
+        finally:
+            rt.Side.DEFER = False
+            rt.Side._HELD.clear()
+
+    def _build_deferred(self, forward, wrt, dev):
         with torch.autocast("cuda", enabled=False), torch.enable_grad(), rt.training_pass():
             side = torch.cuda.Stream(device=dev)
             side.wait_stream(torch.cuda.current_stream())
@@ -488,6 +501,7 @@ class TrainGraph:
                         for i, t in zip(idx, self._standins):
                             hs.append(t.register_hook(lambda g, i=i: fired.append(i)))
                     torch.autograd.grad((out,), wrt, (torch.ones_like(out),), allow_unused=True)
+                    rt.Side.join_all(dev)
                     for h in hs:
                         h.remove()
                     self._fired = fired
@@ -508,6 +522,7 @@ class TrainGraph:
                 if red is not None:
                     red.arm()
                 grads = list(torch.autograd.grad((self.out,), wrt, (self.gout,), allow_unused=True))
+                rt.Side.join_all(dev)      # the deferred parameter-gradient branches
                 if red is not None:
                     red.disarm()
                 self.dx = grads.pop(0) if self.x.requires_grad else None

@@ -251,20 +251,36 @@ _SIDE_STREAMS = {}
 
 
 class Side:
-    """with Side(on, device) as side: <parameter-gradient launches>;  <input-gradient launches>;  side.join()"""
+    """with Side(on, device) as side: <parameter-gradient launches>;  <input-gradient launches>;  side.join()
+
+    Deferred joins (Side.DEFER, set by graphs.TrainGraph around its backward passes): a node whose parameter gradients
+    nobody reads before the end of the backward pass — written in place into the flat gradient buffer, bias sums handed
+    to autograd untouched — passes `defer_ok=True` and the tensors its side-stream kernels read; the join is then left to
+    `Side.join_all` (end of the backward pass; the bucketed all-reduce waits on `Side.stream` instead), so the
+    weight-gradient chain of a layer also overlaps the FOLLOWING layers' input-gradient work. The tensors are held until
+    that join: autograd would otherwise free dy / the saved activation when the node returns and the allocator could
+    hand their memory to a main-stream kernel while the side stream still reads it."""
+    DEFER = False
+    FORKED = False      # a branch has been forked since the last full join (its stream is part of a running capture)
+    _HELD = []
 
     def __init__(self, on, dev):
         self.on = bool(on) and PARALLEL_BRANCHES
         if self.on:
-            key = dev.index if dev.index is not None else torch.cuda.current_device()
-            s = _SIDE_STREAMS.get(key)
-            if s is None:
-                s = _SIDE_STREAMS[key] = torch.cuda.Stream(device=dev)
-            self.s = s
+            self.s = Side.stream(dev)
+
+    @staticmethod
+    def stream(dev):
+        key = dev.index if dev.index is not None else torch.cuda.current_device()
+        s = _SIDE_STREAMS.get(key)
+        if s is None:
+            s = _SIDE_STREAMS[key] = torch.cuda.Stream(device=dev)
+        return s
 
     def __enter__(self):
         if self.on:
             self.s.wait_stream(torch.cuda.current_stream())      # fork: everything dy depends on is ordered before
+            Side.FORKED = True
             self.cm = torch.cuda.stream(self.s)
             self.cm.__enter__()
         return self
@@ -274,9 +290,28 @@ class Side:
             self.cm.__exit__(*exc)
         return False
 
-    def join(self):
-        if self.on:
-            torch.cuda.current_stream().wait_stream(self.s)
+    def join(self, *keep, defer_ok=False):
+        if not self.on:
+            return
+        if Side.DEFER and defer_ok and DEFER_JOINS:
+            Side._HELD.extend(t for t in keep if t is not None)
+            return
+        torch.cuda.current_stream().wait_stream(self.s)
+        Side._HELD.clear()
+        Side.FORKED = False
+
+    @staticmethod
+    def join_all(dev):
+        """The current stream waits for every side-stream launch so far (end of a backward pass)."""
+        key = dev.index if dev.index is not None else torch.cuda.current_device()
+        s = _SIDE_STREAMS.get(key)
+        if s is not None and Side.FORKED:
+            torch.cuda.current_stream().wait_stream(s)
+        Side._HELD.clear()
+        Side.FORKED = False
+
+
+DEFER_JOINS = os.environ.get("B200SD_DEFER_JOINS", "1") != "0"
 
 
 def stream_ptr():
