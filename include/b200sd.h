@@ -221,6 +221,10 @@ int b200sd_groupnorm_apply(const void* x, int64_t ld_x, void* y, int64_t ld_y, c
  * With it the last CTA to finish folds ab over the batch into dgamma[c] / dbeta[c] (fixed order) and leaves the
  * counter at 0 again — no second kernel. */
 int b200sd_rowblocks(int64_t n, int64_t hw, int c);
+/* How b200sd_groupnorm_bwd will run this shape: 1 = the one-pass cluster kernel, with out6 (optional) = {groups per
+ * cluster, CTAs per cluster, rows per CTA, rows per pass, threads per CTA, dynamic shared memory in bytes}; 0 = the
+ * two-pass kernels (the slab does not fit, or B200SD_GN_BWD_FUSED=0). Host-only: no device call. */
+int b200sd_groupnorm_bwd_plan(int64_t n, int64_t hw, int c, int groups, int with_add, int32_t* out6);
 int b200sd_groupnorm_bwd(const void* x, int64_t ld_x, const void* dy, int64_t ld_dy, const void* add, int64_t ld_add,
                          void* dx, int64_t ld_dx, const float* stats0, int p0, int ld_s0, int c_split,
                          const float* stats1, int p1, int ld_s1, const float* gamma, const float* beta, int64_t n,

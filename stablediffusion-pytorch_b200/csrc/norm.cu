@@ -1029,6 +1029,17 @@ static bool gn_fused_plan(int64_t n, int64_t hw, int c, int groups, bool with_ad
     return false;
 }
 
+extern "C" int b200sd_groupnorm_bwd_plan(int64_t n, int64_t hw, int c, int groups, int with_add, int32_t* out6) {
+    GnFusedPlan fp;
+    if (n <= 0 || c <= 0 || groups <= 0 || c % groups || c % 8 || c > 2048 || !gn_fused_plan(n, hw, c, groups, with_add != 0, fp))
+        return 0;
+    if (out6) {
+        out6[0] = fp.G, out6[1] = fp.K, out6[2] = fp.rows_per_cta, out6[3] = fp.rpp, out6[4] = fp.threads;
+        out6[5] = static_cast<int32_t>(fp.smem);
+    }
+    return 1;
+}
+
 extern "C" int b200sd_groupnorm_bwd(const void* x, int64_t ld_x, const void* dy, int64_t ld_dy, const void* add,
                                     int64_t ld_add, void* dx, int64_t ld_dx, const float* stats0, int p0, int ld_s0,
                                     int c_split, const float* stats1, int p1, int ld_s1, const float* gamma,

@@ -17,7 +17,7 @@ _ACT = {None: 0, "none": 0, "silu": 1, "relu": 2}
 
 EXPORTS = [
     "b200sd_last_error", "b200sd_version", "b200sd_launch_count", "b200sd_sched_add_noise",
-    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_igemm_last_splits", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_attention_lse", "b200sd_attention_tc", "b200sd_attention_bwd", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_groupnorm_split", "b200sd_split_f32", "b200sd_rowblocks", "b200sd_groupnorm_bwd", "b200sd_colsum", "b200sd_colsum_blocks", "b200sd_colsum_static", "b200sd_colsum_static_max_floats", "b200sd_vq_blocks", "b200sd_vq_nearest", "b200sd_sampler_step", "b200sd_opt_chunk_size", "b200sd_opt_chunk_elems", "b200sd_grad_sqnorm", "b200sd_adam_ema_step", "b200sd_percent_opt_step",
+    "b200sd_sched_prev_step", "b200sd_advance_t", "b200sd_time_embedding", "b200sd_igemm", "b200sd_igemm_stats_slots", "b200sd_igemm_last_splits", "b200sd_wgrad", "b200sd_wgrad_splits", "b200sd_wgrad_reduce", "b200sd_attention_lse", "b200sd_attention_tc", "b200sd_attention_bwd", "b200sd_groupnorm", "b200sd_groupnorm_apply", "b200sd_groupnorm_split", "b200sd_split_f32", "b200sd_rowblocks", "b200sd_groupnorm_bwd_plan", "b200sd_groupnorm_bwd", "b200sd_colsum", "b200sd_colsum_blocks", "b200sd_colsum_static", "b200sd_colsum_static_max_floats", "b200sd_vq_blocks", "b200sd_vq_nearest", "b200sd_sampler_step", "b200sd_opt_chunk_size", "b200sd_opt_chunk_elems", "b200sd_grad_sqnorm", "b200sd_adam_ema_step", "b200sd_percent_opt_step",
     "b200sd_reduce_f32", "b200sd_attention",
     "b200sd_nchw_to_nhwc", "b200sd_nhwc_to_nchw", "b200sd_mask_cond", "b200sd_copy_act", "b200sd_cast_f32_bf16", "b200sd_add_bf16", "b200sd_im2col", "b200sd_col2im",
     "b200sd_layernorm_mod", "b200sd_layernorm_mod_bwd", "b200sd_rows_per_slot", "b200sd_gate_residual",
@@ -103,6 +103,7 @@ def lib():
         L.b200sd_groupnorm_apply.argtypes = [vp, i64, vp, i64, vp, i32, i32, i32, vp, i32, i32, vp, vp, i64, i64, i32, i32,
                                              f32, i32, vp]
         L.b200sd_rowblocks.argtypes = [i64, i64, i32]
+        L.b200sd_groupnorm_bwd_plan.argtypes = [i64, i64, i32, i32, i32, vp]
         L.b200sd_weight_qn.argtypes = [vp, i64, vp, f32, f32, i32, i32, f32, vp, vp, vp, vp]
         L.b200sd_weight_qn_bwd.argtypes = [vp, vp, i64, vp, f32, f32, i32, f32, vp, vp, vp, vp, vp]
         L.b200sd_weight_qn_multi.argtypes = [vp, i32, i32, vp]
@@ -607,6 +608,14 @@ def split_f32(x, c=None, act=None, lo=True):
     check(lib().b200sd_split_f32(_p(x), x.stride(0), _p(out), width, 0, cp if lo else -1, rows, c, _ACT[act],
                                   stream_ptr()), "split_f32")
     return out
+
+
+def groupnorm_bwd_plan(n, hw, c, groups, with_add=False):
+    """None (two-pass kernels) or the one-pass cluster kernel's launch plan for this shape (host-only query)."""
+    out = (C.c_int32 * 6)()
+    if not lib().b200sd_groupnorm_bwd_plan(n, hw, c, groups, 1 if with_add else 0, out):
+        return None
+    return dict(zip(("groups_per_cluster", "ctas_per_cluster", "rows_per_cta", "rows_per_pass", "threads", "smem"), out))
 
 
 def groupnorm_bwd(x, dy, n, hw, c, groups, gamma, beta, segs, eps=1e-5, act=None, add=None, ld_x=None, ld_dy=None):

@@ -365,7 +365,7 @@ def test_wgrad_conv(rt, n, h, w, cin, cout, k):
                                                (3, 100, 80, 8, "relu"),        # rows not a multiple of the row step
                                                (2, 64, 48, 8, "silu"),         # 6 per group: all 8 groups in one cluster
                                                (1, 64, 24, 4, None),           # whole layer narrower than 64 channels
-                                               (2, 4096, 1024, 32, "silu"),    # large slab: 8 CTAs x 150 KB
+                                               (2, 4096, 1024, 32, "silu"),    # slab with the extra gradient too large: two-pass
                                                (1, 16384, 256, 32, "silu")])   # slab too large: two-pass either way
 def test_groupnorm_backward(rt, n, hw, c, groups, act, two_pass, monkeypatch):
     """One-pass cluster kernel (slab of x / dy in shared memory) and the two-pass route (B200SD_GN_BWD_FUSED=0, also what
