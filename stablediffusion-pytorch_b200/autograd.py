@@ -255,6 +255,17 @@ class ConvSameFn(Function):
         dx = dw = db = drb = dx2 = dw2 = db2 = sc = None
         want_bias = (has_b and ctx.needs_input_grad[2]) or (has_b2 and ctx.needs_input_grad[6]) or has_rb
         want_w = ctx.needs_input_grad[1] or (w2 is not None and ctx.needs_input_grad[5])
+
+        def bias_sums():
+            if cout % 8 == 0:
+                per = rt.colsum(dy, n, h * w, cout, per_image=True)  # fp32 [n, cout]
+            else:
+                per = dy.float().reshape(n, h * w, cout).sum(1)
+            tot = per.sum(0) if (has_b or has_b2) else None
+            # (never hand one buffer to two parameters)
+            return (tot if has_b else None), ((tot.clone() if has_b else tot) if has_b2 else None), \
+                (per.to(torch.bfloat16) if has_rb else None)
+
         with _Side((ctx.needs_input_grad[0] or (x2 is not None and ctx.needs_input_grad[4])) and (want_w or want_bias),
                    x.device) as side:
             if ctx.needs_input_grad[1] or (w2 is not None and ctx.needs_input_grad[5]):
@@ -280,15 +291,12 @@ class ConvSameFn(Function):
                     dw = dwp[:, :k * k * cp].reshape(cout, k * k, cp)[:, :, :cin].permute(0, 2, 1).reshape(cout, cin, k, k)
                     if x2 is not None:
                         dw2 = dwp[:, k * k * cp:k * k * cp + cin2].reshape(cout, cin2, 1, 1)
-            if (has_b and ctx.needs_input_grad[2]) or (has_b2 and ctx.needs_input_grad[6]) or has_rb:
-                if cout % 8 == 0:
-                    per = rt.colsum(dy, n, h * w, cout, per_image=True)  # fp32 [n, cout]
-                else:
-                    per = dy.float().reshape(n, h * w, cout).sum(1)
-                tot = per.sum(0) if (has_b or has_b2) else None
-                db = tot if has_b else None
-                db2 = (tot.clone() if has_b else tot) if has_b2 else None   # never hand one buffer to two parameters
-                drb = per.to(torch.bfloat16) if has_rb else None
+            if want_bias and not has_rb:
+                db, db2, drb = bias_sums()
+        if want_bias and has_rb:
+            # the row-bias gradient feeds the time-embedding branch of THIS backward pass: computed on the main stream,
+            # so that the weight gradient beside it can still join late
+            db, db2, drb = bias_sums()
         if ctx.needs_input_grad[0]:
             # dgrad of a stride-1 'same' conv = the same conv with taps flipped and in/out channels swapped
             bk = _bank(weight)
@@ -304,8 +312,7 @@ class ConvSameFn(Function):
             dx2 = full[:, :cin2]
             rt.linear(dy, wt, out=dx2)
             dx2 = full if full.shape[1] == x2.shape[1] else dx2
-        # (the row-bias gradient feeds the time-embedding branch of THIS backward pass: no deferral with it)
-        side.join(dy, x, x2, defer_ok=not has_rb and (not want_w or sc is not None))
+        side.join(dy, x, x2, defer_ok=not want_w or sc is not None)
         return dx, dw, db, drb, dx2, dw2, db2, None, None, None
 
 
